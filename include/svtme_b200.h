@@ -1,0 +1,314 @@
+/*
+ * svtme_b200.h — C ABI of the B200 (sm_100a) open-loop motion-estimation library.
+ *
+ * This is the drop-in boundary for ONE stage of SVT-AV1-PSY 2.3.0-A: the open-loop
+ * motion-estimation stage (pre-HME, HME level 0/1/2, full-pel 64x64 search, ME candidate
+ * construction) that svt_aom_motion_estimation_kernel drives
+ * (Source/Lib/Codec/me_process.c:97, Source/Lib/Codec/motion_estimation.c:3146).
+ *
+ * Everything here is plain C: pointers, sizes, PODs. No torch / C++ types cross the
+ * boundary. All "file:line" citations are relative to the reference tree
+ * (Source/Lib/... of gianni-rosato/svt-av1-psy 2.3.0-A).
+ *
+ * There is NO CPU fallback: every entry point returns SVTME_ERR_CUDA (and logs to stderr)
+ * if the device is missing or a CUDA call fails.
+ */
+#ifndef SVTME_B200_H
+#define SVTME_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- error convention: mirrors EbErrorType (Source/API/EbSvtAv1.h:127-142) ---- */
+#define SVTME_OK 0                                  /* EB_ErrorNone */
+#define SVTME_ERR_INSUFFICIENT_RESOURCES 0x80001000 /* EB_ErrorInsufficientResources */
+#define SVTME_ERR_BAD_PARAMETER 0x80001005          /* EB_ErrorBadParameter */
+#define SVTME_ERR_CUDA 0x80002000                   /* no reference counterpart: device failure */
+
+/* ---- fixed dimensions of the MeContext result layout ---- */
+#define SVTME_MAX_LIST 2   /* MAX_NUM_OF_REF_PIC_LIST */
+#define SVTME_MAX_REF 4    /* REF_LIST_MAX_DEPTH / MAX_REF_IDX (definitions.h:2365) */
+#define SVTME_PU_COUNT 85  /* SQUARE_PU_COUNT (me_sb_results.h:24) */
+#define SVTME_SUB_SAD_SEARCH 0  /* definitions.h:2080 */
+#define SVTME_FULL_SAD_SEARCH 1 /* definitions.h:2081 */
+
+typedef struct SvtMeSearchArea { /* SearchArea, me_context.h:320-323 */
+    uint16_t width;
+    uint16_t height;
+} SvtMeSearchArea;
+
+typedef struct SvtMeSearchAreaMinMax { /* SearchAreaMinMax, me_context.h:324-327 */
+    SvtMeSearchArea sa_min;
+    SvtMeSearchArea sa_max;
+} SvtMeSearchAreaMinMax;
+
+/*
+ * The ME controls that svt_aom_sig_deriv_me (enc_mode_config.c:694-843) writes into
+ * MeContext (me_context.h:366-509), flattened. The host derives them exactly as the
+ * reference does (the reference's own function can be used unchanged; svtme_sig_deriv_me()
+ * in the host library is our C restatement of it) and hands them to the device as launch
+ * parameters.
+ */
+typedef struct SvtMeCtrls {
+    /* HME flags, me_context.h:427-432 */
+    uint8_t enable_hme_flag;
+    uint8_t enable_hme_level0_flag;
+    uint8_t enable_hme_level1_flag;
+    uint8_t enable_hme_level2_flag;
+    uint8_t hme_search_method; /* SVTME_SUB_SAD_SEARCH / SVTME_FULL_SAD_SEARCH */
+    uint8_t me_search_method;
+    uint16_t num_hme_sa_w; /* always 2 (enc_mode_config.c:146) */
+    uint16_t num_hme_sa_h;
+    SvtMeSearchAreaMinMax hme_l0_sa; /* total HME-L0 area */
+    SvtMeSearchArea       hme_l1_sa;
+    SvtMeSearchArea       hme_l2_sa;
+    SvtMeSearchAreaMinMax me_sa; /* full-pel search area min/max */
+    /* PreHmeCtrls, me_context.h:336-341 */
+    uint8_t               prehme_enable;
+    uint8_t               prehme_skip_search_line;
+    uint8_t               prehme_l1_early_exit;
+    SvtMeSearchAreaMinMax prehme_sa_cfg[2];
+    /* MeHmeRefPruneCtrls, me_context.h:280-290 */
+    uint8_t  enable_me_hme_ref_pruning;
+    uint16_t prune_ref_if_hme_sad_dev_bigger_than_th;
+    uint16_t prune_ref_if_me_sad_dev_bigger_than_th;
+    uint32_t zz_sad_th;
+    uint16_t zz_sad_pct;
+    uint32_t phme_sad_th;
+    uint16_t phme_sad_pct;
+    /* MeSrCtrls, me_context.h:292-305 */
+    uint8_t  enable_me_sr_adjustment;
+    uint16_t reduce_me_sr_based_on_mv_length_th;
+    uint16_t stationary_hme_sad_abs_th;
+    uint16_t stationary_me_sr_divisor;
+    uint16_t reduce_me_sr_based_on_hme_sad_abs_th;
+    uint16_t me_sr_divisor_for_low_hme_sad;
+    uint8_t  distance_based_hme_resizing;
+    /* Me8x8VarCtrls, me_context.h:310-318 */
+    uint8_t  me_8x8_var_enabled;
+    uint32_t me_sr_div4_th;
+    uint32_t me_sr_div2_th;
+    uint32_t me_sr_mult2_th;
+    /* MvBasedSearchAdj, me_context.h:356-364 */
+    uint8_t  mv_sa_adj_enabled;
+    uint8_t  mv_sa_adj_nearest_ref_only;
+    uint16_t mv_sa_adj_mv_size_th;
+    uint16_t mv_sa_adj_sa_multiplier;
+    /* scalars, me_context.h:489-508 */
+    uint8_t  reduce_hme_l0_sr_th_min;
+    uint8_t  reduce_hme_l0_sr_th_max;
+    uint32_t me_early_exit_th;
+    uint32_t me_safe_limit_zz_th;
+    uint32_t prev_me_stage_based_exit_th;
+    int32_t  prune_me_candidates_th;
+    uint8_t  use_best_unipred_cand_only;
+} SvtMeCtrls;
+
+/*
+ * Per-picture launch parameters: the PictureParentControlSet / SequenceControlSet fields the
+ * ME path reads (motion_estimation.c, me_process.c:219-262) plus the reference-picture list.
+ */
+typedef struct SvtMePicParams {
+    SvtMeCtrls ctrls;
+    uint64_t picture_number; /* pcs->picture_number */
+    uint8_t  num_of_list_to_search;       /* 1 for P, 2 for B (me_process.c:219-221) */
+    uint8_t  num_of_ref_pic_to_search[2]; /* pcs->ref_list{0,1}_count_try */
+    uint8_t  temporal_layer_index;
+    uint8_t  is_ref;
+    uint8_t  hierarchical_levels;
+    uint8_t  similar_brightness_refs; /* pd_process.c:3444-3461 */
+    uint8_t  enable_me_8x8;           /* pcs.c:1423 */
+    uint8_t  enable_me_16x16;
+    uint8_t  max_cand;   /* pa_me_data->max_cand (pd_process.c:3509) */
+    uint8_t  max_refs;   /* pa_me_data->max_refs */
+    uint8_t  max_l0;     /* pa_me_data->max_l0 */
+    uint8_t  only_l_bwd; /* scs->mrp_ctrls.only_l_bwd */
+    uint8_t  input_resolution; /* EbInputResolution, definitions.h:2088-2094 */
+    uint8_t  gm_enabled;       /* pcs->gm_ctrls.enabled */
+    uint8_t  gm_use_distance_based_active_th;
+    /* reference pictures: ids of pictures previously uploaded with svtme_picture_upload(),
+       [list][ref_idx]; and their display-order numbers (me_ds_ref_array[..].picture_number) */
+    int32_t  ref_pic_id[SVTME_MAX_LIST][SVTME_MAX_REF];
+    uint64_t ref_picture_number[SVTME_MAX_LIST][SVTME_MAX_REF];
+} SvtMePicParams;
+
+/* SearchResults (me_context.h:348-355), one per (b64, list, ref). */
+typedef struct SvtMeSearchResult {
+    int16_t  hme_sc_x;
+    int16_t  hme_sc_y;
+    uint8_t  do_ref;
+    uint8_t  pad_[3];
+    uint64_t hme_sad;
+} SvtMeSearchResult;
+
+/* Full-pel window actually searched for (b64, list, ref): used for the SAD-op count of
+   SURVEY.md §8(d); all zero when the ref was pruned before the integer search. */
+typedef struct SvtMeWindow {
+    int16_t x_origin, y_origin; /* relative to the b64 origin */
+    int16_t width, height;      /* search points */
+} SvtMeWindow;
+
+/*
+ * Result arrays of one picture. Every pointer is caller-owned HOST memory (NULL = not wanted).
+ * n_b64 = ceil(W/64)*ceil(H/64), raster order (me_process.c:177).
+ *   n_pus   = enable_me_8x8 ? 85 : 21 (pcs.c:108-117)
+ */
+typedef struct SvtMePicResults {
+    /* MeContext mirror, me_context.h:395-396: [n_b64][2][4][85], ME z-order PU index */
+    uint32_t          *p_sb_best_sad;
+    uint32_t          *p_sb_best_mv; /* (uint16 y << 16) | uint16 x, full-pel */
+    SvtMeSearchResult *search_results; /* [n_b64][2][4] */
+    SvtMeWindow       *me_windows;     /* [n_b64][2][4] */
+    /* MeSbResults mirror, me_sb_results.h:44-51 */
+    uint8_t  *total_me_candidate_index; /* [n_b64][n_pus] */
+    uint32_t *me_mv_array;              /* [n_b64][n_pus * max_refs]  MvCandidate.as_int */
+    uint8_t  *me_candidate_array;       /* [n_b64][n_pus * max_cand]  MeCandidate bitfield byte */
+    /* per-b64 PCS statistics, pcs.h:835-845 */
+    uint32_t *me_64x64_distortion;
+    uint32_t *me_32x32_distortion;
+    uint32_t *me_16x16_distortion;
+    uint32_t *me_8x8_distortion;
+    uint32_t *rc_me_distortion;
+    uint32_t *me_8x8_cost_variance;
+    uint8_t  *stationary_block_present_sb;
+    uint8_t  *rc_me_allow_gm;
+} SvtMePicResults;
+
+typedef struct SvtMeSession SvtMeSession; /* opaque */
+
+/* ------------------------------------------------------------------------------------------
+ * 1. RTCD-signature kernels (known-answer parity path; one launch per call).
+ *    Pointers are HOST pointers exactly as the reference's callers pass them; the library
+ *    stages the touched bytes to the device, runs the sm_100a kernel and copies the outputs
+ *    back. These can be stored straight into the reference's RTCD pointers.
+ * ---------------------------------------------------------------------------------------- */
+
+/* replaces svt_sad_loop_kernel (aom_dsp_rtcd.h:776; C: C_DEFAULT/compute_sad_c.c:58-101) */
+void svtme_sad_loop_kernel(uint8_t *src, uint32_t src_stride, uint8_t *ref, uint32_t ref_stride,
+                           uint32_t block_height, uint32_t block_width, uint64_t *best_sad,
+                           int16_t *x_search_center, int16_t *y_search_center,
+                           uint32_t src_stride_raw, uint8_t skip_search_line,
+                           int16_t search_area_width, int16_t search_area_height);
+
+/* replaces svt_ext_all_sad_calculation_8x8_16x16 (aom_dsp_rtcd.h:850; C: motion_estimation.c:335-362) */
+void svtme_ext_all_sad_calculation_8x8_16x16(uint8_t *src, uint32_t src_stride, uint8_t *ref,
+                                             uint32_t ref_stride, uint32_t mv,
+                                             uint32_t *p_best_sad_8x8, uint32_t *p_best_sad_16x16,
+                                             uint32_t *p_best_mv8x8, uint32_t *p_best_mv16x16,
+                                             uint32_t p_eight_sad16x16[16][8],
+                                             uint32_t p_eight_sad8x8[64][8], uint8_t sub_sad);
+
+/* replaces svt_ext_eight_sad_calculation_32x32_64x64 (aom_dsp_rtcd.h:851; C: motion_estimation.c:369-425) */
+void svtme_ext_eight_sad_calculation_32x32_64x64(uint32_t p_sad16x16[16][8],
+                                                 uint32_t *p_best_sad_32x32,
+                                                 uint32_t *p_best_sad_64x64,
+                                                 uint32_t *p_best_mv32x32, uint32_t *p_best_mv64x64,
+                                                 uint32_t mv, uint32_t p_sad32x32[4][8]);
+
+/* replaces svt_ext_sad_calculation_8x8_16x16 (aom_dsp_rtcd.h:839; C: motion_estimation.c:98-164) */
+void svtme_ext_sad_calculation_8x8_16x16(uint8_t *src, uint32_t src_stride, uint8_t *ref,
+                                         uint32_t ref_stride, uint32_t *p_best_sad_8x8,
+                                         uint32_t *p_best_sad_16x16, uint32_t *p_best_mv8x8,
+                                         uint32_t *p_best_mv16x16, uint32_t mv,
+                                         uint32_t *p_sad16x16, uint32_t *p_sad8x8, uint8_t sub_sad);
+
+/* replaces svt_ext_sad_calculation_32x32_64x64 (aom_dsp_rtcd.h:845; C: motion_estimation.c:171-205) */
+void svtme_ext_sad_calculation_32x32_64x64(uint32_t *p_sad16x16, uint32_t *p_best_sad_32x32,
+                                           uint32_t *p_best_sad_64x64, uint32_t *p_best_mv32x32,
+                                           uint32_t *p_best_mv64x64, uint32_t mv,
+                                           uint32_t *p_sad32x32);
+
+/* replaces svt_nxm_sad_kernel (aom_dsp_rtcd.h:854; C: C_DEFAULT/compute_sad_c.c:20-37,209-212) */
+uint32_t svtme_nxm_sad_kernel(const uint8_t *src, uint32_t src_stride, const uint8_t *ref,
+                              uint32_t ref_stride, uint32_t height, uint32_t width);
+
+/* replaces svt_initialize_buffer_32bits (aom_dsp_rtcd.h:852; C: me_sad_calculation.c:14-17) */
+void svtme_initialize_buffer_32bits(uint32_t *pointer, uint32_t count128, uint32_t count32,
+                                    uint32_t value);
+
+/* replaces svt_aom_downsample_2d (C: pic_analysis_process.c:131-161): 2x2 box decimation */
+void svtme_downsample_2d(uint8_t *input_samples, uint32_t input_stride, uint32_t input_area_width,
+                         uint32_t input_area_height, uint8_t *decim_samples, uint32_t decim_stride,
+                         uint32_t decim_step);
+
+/* Last error of the calling thread for the void-returning entry points above (SVTME_OK if none). */
+uint32_t svtme_last_error(void);
+
+/* ------------------------------------------------------------------------------------------
+ * 2. Picture-batched path (throughput path): one session per GPU; source/reference luma
+ *    planes and their 1/4 and 1/16 pyramids live in HBM; one call runs the whole ME stage
+ *    of a picture (all b64, all lists/refs) as a fixed kernel sequence on a CUDA stream.
+ *    Replaces the b64 loop of svt_aom_motion_estimation_kernel (me_process.c:174-291) and
+ *    svt_aom_motion_estimation_b64 (motion_estimation.c:3146-3223) for ME_OPEN_LOOP.
+ * ---------------------------------------------------------------------------------------- */
+
+/* Create a session on CUDA device `device`. width/height: luma size (multiples of 8, as the
+   reference guarantees after svt_aom_pad_picture_to_multiple_of_min_blk_size_dimensions);
+   max_pictures: capacity of the device picture store (source + reference pictures alive). */
+uint32_t svtme_session_create(SvtMeSession **out, int device, uint32_t width, uint32_t height,
+                              uint32_t max_pictures);
+void     svtme_session_destroy(SvtMeSession *s);
+
+/* Upload the 8-bit luma plane of one picture (interior only, `stride` bytes per row, HOST
+   memory; pinned memory makes the copy asynchronous). The device builds the replicate-padded
+   full-resolution plane (pad 72, enc_handle.c:4485-4497), the 1/4 (pad 32) and 1/16 (pad 16)
+   planes (pic_analysis_process.c:2139-2196, pic_operators.c:338-384). pic_id is the caller's
+   handle (0 <= pic_id < max_pictures); re-uploading an id replaces its planes (this is how the
+   post-temporal-filter refresh, temporal_filtering.c:3842-3882, is expressed). */
+uint32_t svtme_picture_upload(SvtMeSession *s, int32_t pic_id, const uint8_t *luma,
+                              uint32_t stride);
+
+/* 10-bit input: `luma16` holds 10-bit samples in uint16 (y4m C420p10 layout). ME reads only the
+   8 MSBs (reference_object.c:327, pack_unpack_c.c:77-116); the split is done on the device. */
+uint32_t svtme_picture_upload_10bit(SvtMeSession *s, int32_t pic_id, const uint16_t *luma16,
+                                    uint32_t stride_in_samples);
+
+/* Same as svtme_picture_upload but the luma plane is already in DEVICE memory. */
+uint32_t svtme_picture_upload_device(SvtMeSession *s, int32_t pic_id, const uint8_t *d_luma,
+                                     uint32_t stride);
+
+/* Run open-loop ME of picture pic_id against params->ref_pic_id[][] and copy the requested
+   result arrays to host (asynchronously on the session stream; call svtme_session_sync, or
+   pass sync=1). */
+uint32_t svtme_picture_me(SvtMeSession *s, int32_t pic_id, const SvtMePicParams *params,
+                          SvtMePicResults *results, int sync);
+
+/* Same, but results stay on the device (pointers returned via svtme_device_results). Used to
+   time the kernels with inputs and outputs resident in HBM. */
+uint32_t svtme_picture_me_device(SvtMeSession *s, int32_t pic_id, const SvtMePicParams *params);
+
+/* Copy the device result arrays of the last svtme_picture_me_device call into `results`. */
+uint32_t svtme_fetch_results(SvtMeSession *s, SvtMePicResults *results, int sync);
+
+uint32_t svtme_session_sync(SvtMeSession *s);
+
+/* Read back a device plane (level 0 = full padded, 1 = quarter, 2 = sixteenth) into host memory,
+   including padding; *stride / *rows receive the padded geometry. For parity tests. */
+uint32_t svtme_picture_download_plane(SvtMeSession *s, int32_t pic_id, int level, uint8_t *dst,
+                                      size_t dst_capacity, uint32_t *stride, uint32_t *rows,
+                                      uint32_t *org_x, uint32_t *org_y);
+
+/* The CUDA stream the session launches on (cudaStream_t as void*), so a caller can record
+   events on it; svtme_session_set_stream lets the caller provide one. */
+void    *svtme_session_stream(SvtMeSession *s);
+uint32_t svtme_session_set_stream(SvtMeSession *s, void *cuda_stream);
+
+/* Number of kernel launches issued by this session since creation (bench "gpu_launches"). */
+uint64_t svtme_session_launch_count(SvtMeSession *s);
+
+/* Device time (ms, CUDA events on the session stream) of the dominant full-pel search kernel
+   accumulated since the last call with reset=1, and the number of launches it covers. */
+uint32_t svtme_session_kernel_time(SvtMeSession *s, int reset, double *fullpel_ms,
+                                   double *hme_ms, uint64_t *n_launch);
+
+/* Library/build identification string. */
+const char *svtme_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SVTME_B200_H */

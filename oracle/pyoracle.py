@@ -1,0 +1,189 @@
+"""TEST INFRASTRUCTURE ONLY — ctypes access to the two CPU checkers:
+
+  * oracle/libme_oracle.so    : our plain-C restatement of the reference's ME path (me_oracle.c)
+  * oracle/_ref/libsvtref.so  : the reference's own sources compiled by oracle/Makefile
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
+import this module. The product (svt-av1-psy_b200/) never does."""
+import ctypes as C
+import os
+import subprocess
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+import svtme_b200  # noqa: E402,F401  (registers svt_av1_psy_b200)
+from svt_av1_psy_b200 import abi  # noqa: E402
+
+REFERENCE_ROOT = "/root/reference"
+u8p = C.POINTER(C.c_uint8)
+
+
+class RefMePicIn(C.Structure):
+    _fields_ = [
+        ("enc_mode", C.c_int32),
+        ("width", C.c_int32),
+        ("height", C.c_int32),
+        ("qp", C.c_int32),
+        ("pred_structure", C.c_int32),
+        ("hierarchical_levels", C.c_int32),
+        ("temporal_layer_index", C.c_int32),
+        ("is_ref", C.c_int32),
+        ("sc_class1", C.c_int32),
+        ("frame_rate", C.c_uint32),
+        ("similar_brightness_refs", C.c_int32),
+        ("gm_level", C.c_int32),
+        ("only_l_bwd", C.c_int32),
+        ("safe_limit_nref", C.c_int32),
+        ("safe_limit_zz_th", C.c_int32),
+        ("max_l0", C.c_int32),
+        ("max_l1", C.c_int32),
+        ("picture_number", C.c_uint64),
+        ("num_lists", C.c_int32),
+        ("ref_count", C.c_int32 * 2),
+        ("ref_picture_number", (C.c_uint64 * 4) * 2),
+        ("src_luma", C.c_void_p),
+        ("ref_luma", (C.c_void_p * 4) * 2),
+        ("simd", C.c_int32),
+    ]
+
+
+class RefMeDebug(C.Structure):
+    _q = (C.c_int16 * 2) * 2
+    _fields_ = (
+        [(n, ((C.c_int16 * 2) * 2 * 4) * 2) for n in
+         ("x_hme_l0", "y_hme_l0", "x_hme_l1", "y_hme_l1", "x_hme_l2", "y_hme_l2")]
+        + [(n, ((C.c_uint64 * 2) * 2 * 4) * 2) for n in ("hme_l0_sad", "hme_l1_sad", "hme_l2_sad")]
+        + [("prehme_mv_x", ((C.c_int16 * 2) * 4) * 2), ("prehme_mv_y", ((C.c_int16 * 2) * 4) * 2),
+           ("prehme_sad", ((C.c_uint64 * 2) * 4) * 2),
+           ("zz_sad", (C.c_uint32 * 4) * 2), ("reduce_me_sr_divisor", (C.c_uint32 * 4) * 2)]
+    )
+
+
+DEBUG_DTYPE = np.dtype([
+    ("x_hme_l0", "<i2", (2, 4, 2, 2)), ("y_hme_l0", "<i2", (2, 4, 2, 2)),
+    ("x_hme_l1", "<i2", (2, 4, 2, 2)), ("y_hme_l1", "<i2", (2, 4, 2, 2)),
+    ("x_hme_l2", "<i2", (2, 4, 2, 2)), ("y_hme_l2", "<i2", (2, 4, 2, 2)),
+    ("hme_l0_sad", "<u8", (2, 4, 2, 2)), ("hme_l1_sad", "<u8", (2, 4, 2, 2)), ("hme_l2_sad", "<u8", (2, 4, 2, 2)),
+    ("prehme_mv_x", "<i2", (2, 4, 2)), ("prehme_mv_y", "<i2", (2, 4, 2)), ("prehme_sad", "<u8", (2, 4, 2)),
+    ("zz_sad", "<u4", (2, 4)), ("reduce_me_sr_divisor", "<u4", (2, 4)),
+])
+assert DEBUG_DTYPE.itemsize == C.sizeof(RefMeDebug), (DEBUG_DTYPE.itemsize, C.sizeof(RefMeDebug))
+
+
+def build(ref=True, quiet=True):
+    """(Re)build the checkers. Building the checker is not using it."""
+    targets = ["oracle"]
+    if ref and os.path.isdir(REFERENCE_ROOT):
+        targets.append("ref")
+    out = subprocess.run(["make", "-C", HERE] + targets, capture_output=True, text=True)
+    if out.returncode != 0:
+        raise RuntimeError("oracle build failed:\n" + out.stdout + out.stderr)
+    if not quiet:
+        print(out.stdout)
+
+
+_ref = None
+_orc = None
+
+
+def ref_available():
+    return os.path.exists(os.path.join(HERE, "_ref", "libsvtref.so"))
+
+
+def ref_lib():
+    global _ref
+    if _ref is None:
+        path = os.path.join(HERE, "_ref", "libsvtref.so")
+        if not os.path.exists(path):
+            raise RuntimeError("oracle/_ref/libsvtref.so not built (needs /root/reference): run `make -C oracle ref`")
+        _ref = C.CDLL(path)
+        _ref.ref_me_picture.argtypes = [C.POINTER(RefMePicIn), C.POINTER(abi.MePicResults), C.c_void_p,
+                                        C.POINTER(C.c_double)]
+        _ref.ref_me_picture.restype = C.c_int
+        _ref.ref_derive_params.argtypes = [C.POINTER(RefMePicIn), C.POINTER(abi.MePicParams)]
+        _ref.ref_nxm_sad_kernel.restype = C.c_uint32
+    return _ref
+
+
+def oracle_lib():
+    global _orc
+    if _orc is None:
+        path = os.path.join(HERE, "libme_oracle.so")
+        if not os.path.exists(path):
+            build(ref=False)
+        _orc = C.CDLL(path)
+        _orc.orc_me_picture.restype = C.c_int
+        _orc.orc_nxm_sad_kernel.restype = C.c_uint32
+    return _orc
+
+
+def ptr(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+# ---- mrp levels used by the BASELINE configs (enc_handle.c:3799-3960, :4588-4613) ----
+def mrp_for_preset(enc_mode):
+    """returns dict(only_l_bwd, safe_limit_nref, safe_limit_zz_th, l0, l1) for CRF random access,
+    non-SC content, resolution > 360p, fast_decode 0."""
+    if enc_mode <= -1:  # MR and below: mrp_level 1
+        return dict(only_l_bwd=0, safe_limit_nref=0, safe_limit_zz_th=0, l0=4, l1=3)
+    if enc_mode <= 1:  # mrp_level 2
+        return dict(only_l_bwd=1, safe_limit_nref=0, safe_limit_zz_th=0, l0=4, l1=3)
+    if enc_mode <= 4:  # mrp_level 5
+        return dict(only_l_bwd=1, safe_limit_nref=0, safe_limit_zz_th=0, l0=4, l1=3)
+    if enc_mode <= 8:  # mrp_level 9
+        return dict(only_l_bwd=1, safe_limit_nref=2, safe_limit_zz_th=0, l0=3, l1=2)
+    return dict(only_l_bwd=1, safe_limit_nref=2, safe_limit_zz_th=0, l0=2, l1=2)  # mrp_level 10
+
+
+def make_pic_in(src, refs, ref_pocs, poc, enc_mode, qp=35, temporal_layer=1, hier_levels=5, is_ref=1,
+                simd=0, sc_class1=0, pred_structure=2, frame_rate=30 << 16, similar_brightness=0,
+                gm_level=-1, mrp=None):
+    """src: (H,W) u8; refs: [[l0 planes...],[l1 planes...]]; ref_pocs same shape."""
+    h, w = src.shape
+    mrp = mrp or mrp_for_preset(enc_mode)
+    pin = RefMePicIn()
+    pin.enc_mode, pin.width, pin.height, pin.qp = enc_mode, w, h, qp
+    pin.pred_structure, pin.hierarchical_levels = pred_structure, hier_levels
+    pin.temporal_layer_index, pin.is_ref, pin.sc_class1 = temporal_layer, is_ref, sc_class1
+    pin.frame_rate, pin.similar_brightness_refs, pin.gm_level = frame_rate, similar_brightness, gm_level
+    pin.only_l_bwd, pin.safe_limit_nref, pin.safe_limit_zz_th = mrp["only_l_bwd"], mrp["safe_limit_nref"], mrp["safe_limit_zz_th"]
+    pin.max_l0, pin.max_l1 = mrp["l0"], mrp["l1"]
+    pin.picture_number = poc
+    pin.num_lists = 2 if len(refs) > 1 and len(refs[1]) > 0 else 1
+    keep = [np.ascontiguousarray(src)]
+    pin.src_luma = keep[0].ctypes.data
+    for l in range(pin.num_lists):
+        pin.ref_count[l] = len(refs[l])
+        for r, plane in enumerate(refs[l]):
+            a = np.ascontiguousarray(plane)
+            assert a.shape == (h, w) and a.dtype == np.uint8
+            keep.append(a)
+            pin.ref_luma[l][r] = a.ctypes.data
+            pin.ref_picture_number[l][r] = ref_pocs[l][r]
+    pin.simd = simd
+    pin._keep = keep
+    return pin
+
+
+def ref_derive_params(pin):
+    p = abi.MePicParams()
+    ref_lib().ref_derive_params(C.byref(pin), C.byref(p))
+    return p
+
+
+def ref_me_picture(pin, params=None, debug=False):
+    """run the reference's own ME on one picture -> (PicResultArrays, debug array or None, seconds)"""
+    params = params or ref_derive_params(pin)
+    res = abi.PicResultArrays(pin.width, pin.height, params)
+    dbg = np.zeros(res.n_b64, dtype=DEBUG_DTYPE) if debug else None
+    sec = C.c_double(0)
+    rc = ref_lib().ref_me_picture(C.byref(pin), C.byref(res.struct), ptr(dbg) if debug else None, C.byref(sec))
+    if rc != 0:
+        raise RuntimeError("ref_me_picture failed rc=%d" % rc)
+    return res, dbg, sec.value

@@ -1,0 +1,111 @@
+/*
+ * ref_harness.h — TEST INFRASTRUCTURE ONLY (never linked into the product).
+ *
+ * C interface of oracle/_ref/libsvtref.so: the UNMODIFIED reference sources of the ME path
+ * (compiled where they lie under /root/reference by oracle/Makefile) plus ref_harness.c, a
+ * driver that fakes the few PictureParentControlSet / SequenceControlSet fields the path reads
+ * and then calls the reference's own svt_aom_sig_deriv_me and svt_aom_motion_estimation_b64.
+ */
+#ifndef REF_HARNESS_H
+#define REF_HARNESS_H
+#include <stdint.h>
+#include "svtme_b200.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* "encoder level" description of one picture's ME job: what Picture Decision hands to ME */
+typedef struct RefMePicIn {
+    int32_t  enc_mode;            /* EncMode: -3 (MRS) .. 13 */
+    int32_t  width, height;       /* luma size, multiples of 8 */
+    int32_t  qp;                  /* scs->static_config.qp */
+    int32_t  pred_structure;      /* 1 low-delay-B, 2 random access */
+    int32_t  hierarchical_levels; /* pcs->hierarchical_levels */
+    int32_t  temporal_layer_index;
+    int32_t  is_ref;
+    int32_t  sc_class1;
+    uint32_t frame_rate;          /* scs->frame_rate (Q16) */
+    int32_t  similar_brightness_refs;
+    int32_t  gm_level;            /* -1: derive like the reference (svt_aom_derive_gm_level) */
+    /* scs->mrp_ctrls fields the path reads */
+    int32_t  only_l_bwd, safe_limit_nref, safe_limit_zz_th;
+    int32_t  max_l0, max_l1;      /* ref_count_used_list{0,1} (pd_process.c:3495-3511) */
+    uint64_t picture_number;
+    int32_t  num_lists;           /* 1 = P, 2 = B */
+    int32_t  ref_count[2];
+    uint64_t ref_picture_number[2][4];
+    const uint8_t *src_luma;      /* interior plane, stride = width */
+    const uint8_t *ref_luma[2][4];
+    int32_t  simd;                /* 0 = C kernels, 1 = AVX2 table, 2 = AVX-512 table */
+} RefMePicIn;
+
+/* extra per-b64 state dumped for debugging parity of the HME stages */
+typedef struct RefMeDebug {
+    int16_t  x_hme_l0[2][4][2][2], y_hme_l0[2][4][2][2];
+    int16_t  x_hme_l1[2][4][2][2], y_hme_l1[2][4][2][2];
+    int16_t  x_hme_l2[2][4][2][2], y_hme_l2[2][4][2][2];
+    uint64_t hme_l0_sad[2][4][2][2], hme_l1_sad[2][4][2][2], hme_l2_sad[2][4][2][2];
+    int16_t  prehme_mv_x[2][4][2], prehme_mv_y[2][4][2];
+    uint64_t prehme_sad[2][4][2];
+    uint32_t zz_sad[2][4];
+    uint32_t reduce_me_sr_divisor[2][4];
+} RefMeDebug;
+
+/* Fill `out` with the controls the reference derives for this picture (svt_aom_sig_deriv_me)
+   and the PCS-level fields (enable_me_8x8, max_cand, gm flags ...). */
+int ref_derive_params(const RefMePicIn *in, SvtMePicParams *out);
+
+/* Run the reference ME stage on one picture. `res` arrays follow SvtMePicResults (host memory,
+   NULL = skip). `dbg` is [n_b64] or NULL. Returns 0 on success. *seconds (optional) receives the
+   wall time spent inside svt_aom_motion_estimation_b64 only. */
+int ref_me_picture(const RefMePicIn *in, SvtMePicResults *res, RefMeDebug *dbg, double *seconds);
+
+/* Build the three padded planes of a picture with the reference's own decimation/padding.
+   Buffers must hold (w+2*72)*(h+2*72), (w/2+64)*(h/2+64), (w/4+32)*(h/4+32) bytes. */
+int ref_build_planes(const uint8_t *luma, int width, int height, uint8_t *full, uint8_t *quarter,
+                     uint8_t *sixteenth);
+
+/* RTCD kernels; simd: 0 = C, 1 = AVX2 (SSE4.1 where the reference's x86 table has no AVX2
+   entry), 2 = AVX-512 for the SAD loop */
+void ref_sad_loop_kernel(int simd, uint8_t *src, uint32_t src_stride, uint8_t *ref,
+                         uint32_t ref_stride, uint32_t block_height, uint32_t block_width,
+                         uint64_t *best_sad, int16_t *x_search_center, int16_t *y_search_center,
+                         uint32_t src_stride_raw, uint8_t skip_search_line,
+                         int16_t search_area_width, int16_t search_area_height);
+void ref_ext_all_sad_calculation_8x8_16x16(int simd, uint8_t *src, uint32_t src_stride,
+                                           uint8_t *ref, uint32_t ref_stride, uint32_t mv,
+                                           uint32_t *p_best_sad_8x8, uint32_t *p_best_sad_16x16,
+                                           uint32_t *p_best_mv8x8, uint32_t *p_best_mv16x16,
+                                           uint32_t p_eight_sad16x16[16][8],
+                                           uint32_t p_eight_sad8x8[64][8], uint8_t sub_sad);
+void ref_ext_eight_sad_calculation_32x32_64x64(int simd, uint32_t p_sad16x16[16][8],
+                                               uint32_t *p_best_sad_32x32,
+                                               uint32_t *p_best_sad_64x64,
+                                               uint32_t *p_best_mv32x32, uint32_t *p_best_mv64x64,
+                                               uint32_t mv, uint32_t p_sad32x32[4][8]);
+void ref_ext_sad_calculation_8x8_16x16(int simd, uint8_t *src, uint32_t src_stride, uint8_t *ref,
+                                       uint32_t ref_stride, uint32_t *p_best_sad_8x8,
+                                       uint32_t *p_best_sad_16x16, uint32_t *p_best_mv8x8,
+                                       uint32_t *p_best_mv16x16, uint32_t mv, uint32_t *p_sad16x16,
+                                       uint32_t *p_sad8x8, uint8_t sub_sad);
+void ref_ext_sad_calculation_32x32_64x64(int simd, uint32_t *p_sad16x16, uint32_t *p_best_sad_32x32,
+                                         uint32_t *p_best_sad_64x64, uint32_t *p_best_mv32x32,
+                                         uint32_t *p_best_mv64x64, uint32_t mv,
+                                         uint32_t *p_sad32x32);
+uint32_t ref_nxm_sad_kernel(int simd, const uint8_t *src, uint32_t src_stride, const uint8_t *ref,
+                            uint32_t ref_stride, uint32_t height, uint32_t width);
+void ref_initialize_buffer_32bits(int simd, uint32_t *pointer, uint32_t count128, uint32_t count32,
+                                  uint32_t value);
+void ref_downsample_2d(uint8_t *input_samples, uint32_t input_stride, uint32_t input_area_width,
+                       uint32_t input_area_height, uint8_t *decim_samples, uint32_t decim_stride,
+                       uint32_t decim_step);
+void ref_generate_padding(uint8_t *pic, uint32_t stride, uint32_t width, uint32_t height,
+                          uint32_t pad_w, uint32_t pad_h);
+void ref_unpack_10bit_msb(const uint16_t *in16, uint32_t in_stride, uint8_t *out8,
+                          uint32_t out_stride, uint32_t width, uint32_t height);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,187 @@
+"""ctypes binding of libsvtme_b200.so (CUDA, include/svtme_b200.h) and libsvtme_host.so (host C)."""
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import abi
+
+_PKG = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+_HOST = None
+
+u8p = C.c_void_p
+
+
+class SvtMeError(RuntimeError):
+    def __init__(self, code, what):
+        super().__init__("%s failed: error 0x%08x" % (what, code))
+        self.code = code
+
+
+def lib():
+    """The CUDA C-ABI library. Raises (loudly) if it has not been built: there is no fallback."""
+    global _LIB
+    if _LIB is None:
+        path = os.path.join(_PKG, "libsvtme_b200.so")
+        if not os.path.exists(path):
+            raise RuntimeError(
+                "libsvtme_b200.so is missing (%s). Build it with __graft_entry__.build() or "
+                "`make -C svt-av1-psy_b200/csrc`. There is no CPU fallback." % path)
+        L = C.CDLL(path)
+        L.svtme_version.restype = C.c_char_p
+        L.svtme_last_error.restype = C.c_uint32
+        L.svtme_nxm_sad_kernel.restype = C.c_uint32
+        L.svtme_session_create.argtypes = [C.POINTER(C.c_void_p), C.c_int, C.c_uint32, C.c_uint32, C.c_uint32]
+        L.svtme_session_create.restype = C.c_uint32
+        L.svtme_session_destroy.argtypes = [C.c_void_p]
+        L.svtme_session_destroy.restype = None
+        L.svtme_picture_upload.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_uint32]
+        L.svtme_picture_upload.restype = C.c_uint32
+        L.svtme_picture_upload_10bit.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_uint32]
+        L.svtme_picture_upload_10bit.restype = C.c_uint32
+        L.svtme_picture_upload_device.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_uint32]
+        L.svtme_picture_upload_device.restype = C.c_uint32
+        L.svtme_picture_me.argtypes = [C.c_void_p, C.c_int32, C.POINTER(abi.MePicParams),
+                                       C.POINTER(abi.MePicResults), C.c_int]
+        L.svtme_picture_me.restype = C.c_uint32
+        L.svtme_picture_me_device.argtypes = [C.c_void_p, C.c_int32, C.POINTER(abi.MePicParams)]
+        L.svtme_picture_me_device.restype = C.c_uint32
+        L.svtme_fetch_results.argtypes = [C.c_void_p, C.POINTER(abi.MePicResults), C.c_int]
+        L.svtme_fetch_results.restype = C.c_uint32
+        L.svtme_session_sync.argtypes = [C.c_void_p]
+        L.svtme_session_sync.restype = C.c_uint32
+        L.svtme_picture_download_plane.argtypes = [C.c_void_p, C.c_int32, C.c_int, C.c_void_p, C.c_size_t,
+                                                   C.POINTER(C.c_uint32), C.POINTER(C.c_uint32),
+                                                   C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
+        L.svtme_picture_download_plane.restype = C.c_uint32
+        L.svtme_session_stream.argtypes = [C.c_void_p]
+        L.svtme_session_stream.restype = C.c_void_p
+        L.svtme_session_set_stream.argtypes = [C.c_void_p, C.c_void_p]
+        L.svtme_session_set_stream.restype = C.c_uint32
+        L.svtme_session_launch_count.argtypes = [C.c_void_p]
+        L.svtme_session_launch_count.restype = C.c_uint64
+        L.svtme_session_kernel_time.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_double),
+                                                C.POINTER(C.c_double), C.POINTER(C.c_uint64)]
+        L.svtme_session_kernel_time.restype = C.c_uint32
+        _LIB = L
+    return _LIB
+
+
+def host_lib():
+    """Host-side C logic (signal derivation, prediction structure): no CUDA inside."""
+    global _HOST
+    if _HOST is None:
+        path = os.path.join(_PKG, "libsvtme_host.so")
+        if not os.path.exists(path):
+            raise RuntimeError("libsvtme_host.so is missing (%s): run __graft_entry__.build()" % path)
+        H = C.CDLL(path)
+        H.svtme_sig_deriv_me.restype = C.c_uint32
+        _HOST = H
+    return _HOST
+
+
+def last_error():
+    return lib().svtme_last_error()
+
+
+def _check(code, what):
+    if code != abi.OK:
+        raise SvtMeError(code, what)
+
+
+class SigDerivIn(C.Structure):
+    """SvtMeSigDerivIn of host/me_sig_deriv.h: the encoder-level inputs of svt_aom_sig_deriv_me."""
+    _fields_ = [
+        ("enc_mode", C.c_int32), ("width", C.c_int32), ("height", C.c_int32), ("qp", C.c_int32),
+        ("pred_structure", C.c_int32), ("hierarchical_levels", C.c_int32), ("temporal_layer_index", C.c_int32),
+        ("is_ref", C.c_int32), ("sc_class1", C.c_int32), ("frame_rate", C.c_uint32),
+        ("similar_brightness_refs", C.c_int32), ("gm_level", C.c_int32), ("only_l_bwd", C.c_int32),
+        ("safe_limit_nref", C.c_int32), ("safe_limit_zz_th", C.c_int32), ("max_l0", C.c_int32), ("max_l1", C.c_int32),
+        ("picture_number", C.c_uint64), ("num_lists", C.c_int32), ("ref_count", C.c_int32 * 2),
+        ("ref_picture_number", (C.c_uint64 * 4) * 2),
+    ]
+
+
+def sig_deriv_me(sin):
+    """host C restatement of svt_aom_sig_deriv_me + PCS-level ME fields -> abi.MePicParams"""
+    p = abi.MePicParams()
+    _check(host_lib().svtme_sig_deriv_me(C.byref(sin), C.byref(p)), "svtme_sig_deriv_me")
+    return p
+
+
+class Session:
+    """One GPU's picture store + ME launcher (SvtMeSession)."""
+
+    def __init__(self, width, height, max_pictures=16, device=0):
+        self.width, self.height = width, height
+        self._h = C.c_void_p()
+        _check(lib().svtme_session_create(C.byref(self._h), device, width, height, max_pictures), "svtme_session_create")
+
+    def close(self):
+        if self._h:
+            lib().svtme_session_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def upload(self, pic_id, luma):
+        a = np.ascontiguousarray(luma)
+        if a.dtype == np.uint16:
+            assert a.shape == (self.height, self.width)
+            _check(lib().svtme_picture_upload_10bit(self._h, pic_id, a.ctypes.data, a.strides[0] // 2), "svtme_picture_upload_10bit")
+        else:
+            assert a.dtype == np.uint8 and a.shape == (self.height, self.width)
+            _check(lib().svtme_picture_upload(self._h, pic_id, a.ctypes.data, a.strides[0]), "svtme_picture_upload")
+
+    def upload_ptr(self, pic_id, host_ptr, stride):
+        _check(lib().svtme_picture_upload(self._h, pic_id, host_ptr, stride), "svtme_picture_upload")
+
+    def upload_device(self, pic_id, dev_ptr, stride):
+        _check(lib().svtme_picture_upload_device(self._h, pic_id, dev_ptr, stride), "svtme_picture_upload_device")
+
+    def me(self, pic_id, params, results=None, sync=True):
+        results = results if results is not None else abi.PicResultArrays(self.width, self.height, params)
+        _check(lib().svtme_picture_me(self._h, pic_id, C.byref(params), C.byref(results.struct), 1 if sync else 0),
+               "svtme_picture_me")
+        return results
+
+    def me_device(self, pic_id, params):
+        _check(lib().svtme_picture_me_device(self._h, pic_id, C.byref(params)), "svtme_picture_me_device")
+
+    def fetch(self, results, sync=True):
+        _check(lib().svtme_fetch_results(self._h, C.byref(results.struct), 1 if sync else 0), "svtme_fetch_results")
+        return results
+
+    def sync(self):
+        _check(lib().svtme_session_sync(self._h), "svtme_session_sync")
+
+    def download_plane(self, pic_id, level):
+        pad = (72, 32, 16)[level]
+        w, h = self.width >> level, self.height >> level
+        buf = np.zeros(((h + 2 * pad), (w + 2 * pad)), dtype=np.uint8)
+        st, rows, ox, oy = C.c_uint32(), C.c_uint32(), C.c_uint32(), C.c_uint32()
+        _check(lib().svtme_picture_download_plane(self._h, pic_id, level, buf.ctypes.data, buf.nbytes, C.byref(st),
+                                                  C.byref(rows), C.byref(ox), C.byref(oy)), "svtme_picture_download_plane")
+        assert st.value == buf.shape[1] and rows.value == buf.shape[0], (st.value, rows.value, buf.shape)
+        return buf
+
+    @property
+    def stream(self):
+        return lib().svtme_session_stream(self._h)
+
+    def set_stream(self, cuda_stream_ptr):
+        _check(lib().svtme_session_set_stream(self._h, C.c_void_p(cuda_stream_ptr)), "svtme_session_set_stream")
+
+    def launch_count(self):
+        return int(lib().svtme_session_launch_count(self._h))
+
+    def kernel_time(self, reset=False):
+        f, h, n = C.c_double(), C.c_double(), C.c_uint64()
+        _check(lib().svtme_session_kernel_time(self._h, 1 if reset else 0, C.byref(f), C.byref(h), C.byref(n)),
+               "svtme_session_kernel_time")
+        return f.value, h.value, int(n.value)
