@@ -1,0 +1,422 @@
+#!/usr/bin/env python3
+"""Open-loop ME benchmark (BASELINE.json metric: "open-loop ME frames/s").
+
+One step = the ME stage (pyramid build, pre-HME, HME L0/L1/L2, full-pel search, candidate
+construction) of one mini-GOP of synthetic pictures. Default workload = BASELINE.json configs[1]:
+1920x1080 8-bit, preset 4, random access, 240-frame panning-noise clip, 1 B200.
+
+  python bench.py [--gpus N --steps K --warmup W]          our CUDA path (one rank per GPU under torchrun)
+  python bench.py --impl reference [...]                   the reference's own CPU ME (oracle/_ref) on the host cores
+
+Prints ONE JSON line (rank 0). See DESIGN.md "Measurement" for what each key means."""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+INT_PEAK_LANE_INSTR_PER_CLK_SM = 41.5  # measured VABSDIFF4.U8.ACC issue rate, profiles/r01_pipe_microbench.txt
+N_SM = 148
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=7)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--width", type=int, default=1920)
+    ap.add_argument("--height", type=int, default=1080)
+    ap.add_argument("--preset", type=int, default=4)
+    ap.add_argument("--bits", type=int, default=8, choices=[8, 10])
+    ap.add_argument("--frames", type=int, default=240, help="length of the synthetic clip")
+    ap.add_argument("--qp", type=int, default=35)
+    ap.add_argument("--cpu-baseline-pics", type=int, default=0, help="0 = one picture per host core")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------------------------------------
+# workload description
+# ------------------------------------------------------------------------------------------------
+class Workload:
+    def __init__(self, a):
+        from svt_av1_psy_b200.gop import mrp_for_preset
+        self.w, self.h, self.preset, self.bits, self.n_frames, self.qp = a.width, a.height, a.preset, a.bits, a.frames, a.qp
+        # enc_handle.c:4791-4799: 5 hierarchical levels up to M9 below 8K, else 4
+        self.hier = 4 if (self.w * self.h >= 0x140A000 or self.preset > 9 or (self.preset >= 9 and self.w * self.h >= 0x16DA00)) else 5
+        self.mgop = 1 << self.hier
+        self.mrp = mrp_for_preset(self.preset)
+        self.name = "%dx%d %d-bit preset %d random-access %dL, %d-frame panning-noise clip" % (
+            self.w, self.h, self.bits, self.preset, self.hier, self.n_frames)
+
+    def plan(self, poc):
+        from svt_av1_psy_b200 import gop
+        return gop.picture_plan(poc, self.hier, self.mrp["l0"], self.mrp["l1"], 1 << 30)
+
+    def order(self, first_poc):
+        from svt_av1_psy_b200 import gop
+        return gop.coding_order(first_poc, self.hier, 1 << 30)
+
+
+def make_clip(wl, rank):
+    """n_frames distinct frames; content of picture `poc` is frame poc % n_frames (the POC structure keeps running)"""
+    from svt_av1_psy_b200.synth import PanningNoise
+    clip = PanningNoise(wl.w, wl.h, seed=7 + rank, vx=2, vy=1, max_frames=wl.n_frames, sigma=2.0)
+    rng = np.random.default_rng(1234 + rank)
+    # cheap per-frame noise: crops of one pre-generated noise field (instead of a fresh normal draw per frame)
+    nf = np.rint(rng.normal(0.0, clip.sigma, size=(wl.h + 64, wl.w + 64))).astype(np.int16)
+    frames = np.empty((wl.n_frames, wl.h, wl.w), np.uint8)
+    for t in range(wl.n_frames):
+        x0, y0 = abs(clip.vx) * t, abs(clip.vy) * t
+        oy, ox = rng.integers(0, 64, 2)
+        crop = clip.field[y0:y0 + wl.h, x0:x0 + wl.w].astype(np.int16) + nf[oy:oy + wl.h, ox:ox + wl.w]
+        np.clip(crop, 0, 255, out=crop)
+        frames[t] = crop.astype(np.uint8)
+    return frames
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)"""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm = sorted(float(r[0]) for r in self.rows if len(r) >= 7 and r[0].replace(".", "").isdigit())
+        mx = [float(r[1]) for r in self.rows if len(r) >= 7 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in self.rows if len(r) >= 7 for i in range(4) if r[3 + i].lower().startswith("active")})
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
+                "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------
+# our arm
+# ------------------------------------------------------------------------------------------------
+class Runner:
+    """Drives one Session through consecutive mini-GOPs of a stream (this rank's shard)."""
+    N_SLOTS = 192  # picture store: slot = poc % N_SLOTS; references reach at most 4 mini-GOPs back
+
+    def __init__(self, wl, rank, world, frames_host, device):
+        import torch
+        import svtme_b200 as me
+        from svt_av1_psy_b200 import abi
+        self.wl, self.rank, self.world, self.me, self.abi, self.torch = wl, rank, world, me, abi, torch
+        self.sess = me.Session(wl.w, wl.h, max_pictures=self.N_SLOTS, device=device)
+        self.sess.set_stream(torch.cuda.current_stream().cuda_stream)
+        self.frames_pinned = torch.from_numpy(frames_host).pin_memory()
+        self.frames_dev = self.frames_pinned.to("cuda", non_blocking=False)
+        self.frames16 = None
+        if wl.bits == 10:  # host side holds 10-bit samples (uint16); ME reads their 8 MSBs = frames_host
+            rng = np.random.default_rng(99 + rank)
+            f16 = (frames_host.astype(np.uint16) << 2) | rng.integers(0, 4, frames_host.shape, dtype=np.uint16)
+            self.frames16 = torch.from_numpy(f16.view(np.int16)).pin_memory()
+        self.resident = {}  # slot -> poc whose planes are in the store
+        self.params_cache = {}
+        self.results = None
+        self.h2d = self.d2h = 0
+        self.pics = 0
+
+    def params(self, plan):
+        key = plan["poc"]
+        sin = self.me.binding.SigDerivIn()
+        wl = self.wl
+        sin.enc_mode, sin.width, sin.height, sin.qp = wl.preset, wl.w, wl.h, wl.qp
+        sin.pred_structure, sin.hierarchical_levels = 2, wl.hier
+        sin.temporal_layer_index, sin.is_ref, sin.sc_class1 = plan["tl"], plan["is_ref"], 0
+        sin.frame_rate, sin.similar_brightness_refs, sin.gm_level = 30 << 16, 0, -1
+        sin.only_l_bwd, sin.safe_limit_nref, sin.safe_limit_zz_th = wl.mrp["only_l_bwd"], wl.mrp["safe_limit_nref"], wl.mrp["safe_limit_zz_th"]
+        sin.max_l0, sin.max_l1 = wl.mrp["l0"], wl.mrp["l1"]
+        sin.picture_number, sin.num_lists = key, 2
+        lists = [plan["l0"], plan["l1"]]
+        for l in range(2):
+            sin.ref_count[l] = len(lists[l])
+            for r, p in enumerate(lists[l]):
+                sin.ref_picture_number[l][r] = p
+        p = self.me.sig_deriv_me(sin)
+        for l in range(2):
+            for r, rp in enumerate(lists[l]):
+                p.ref_pic_id[l][r] = rp % self.N_SLOTS
+        return p
+
+    def ensure(self, poc, host):
+        slot = poc % self.N_SLOTS
+        if self.resident.get(slot) == poc:
+            return
+        f = poc % self.wl.n_frames
+        if host and self.frames16 is not None:
+            self.sess.upload_ptr16(slot, self.frames16[f].data_ptr(), self.wl.w)
+            self.h2d += 2 * self.wl.w * self.wl.h
+        elif host:
+            self.sess.upload_ptr(slot, self.frames_pinned[f].data_ptr(), self.wl.w)
+            self.h2d += self.wl.w * self.wl.h
+        else:
+            self.sess.upload_device(slot, self.frames_dev[f].data_ptr(), self.wl.w)
+        self.resident[slot] = poc
+
+    def step(self, step_index, host):
+        """ME of the mini-GOP this rank owns at `step_index` (mini-GOP m = step*world + rank)"""
+        wl = self.wl
+        m = step_index * self.world + self.rank
+        first = m * wl.mgop
+        self.ensure(first, host)  # the base/key picture that precedes the mini-GOP
+        for poc in wl.order(first):
+            plan = wl.plan(poc)
+            for p in plan["l0"] + plan["l1"]:
+                self.ensure(p, host)
+            self.ensure(poc, host)
+            prm = self.params_cache.get(poc)
+            if prm is None:
+                prm = self.params_cache[poc] = self.params(plan)
+            if host:
+                if self.results is None:
+                    self.results = self.abi.PicResultArrays(wl.w, wl.h, prm, pinned=True)
+                    for name in ("p_sb_best_sad", "p_sb_best_mv", "search_results", "me_windows"):
+                        setattr(self.results.struct, name, None)  # MeContext mirrors: debug only, not consumed downstream
+                    self.d2h_per_pic = sum(getattr(self.results, f).nbytes for f in self.results.FIELDS
+                                           if f not in ("p_sb_best_sad", "p_sb_best_mv", "search_results", "me_windows"))
+                self.sess.me(slot_of(poc, self), prm, self.results, sync=False)
+                self.d2h += self.d2h_per_pic
+            else:
+                self.sess.me_device(slot_of(poc, self), prm)
+            self.pics += 1
+        if host:
+            self.sess.sync()  # the step's results are in host memory
+
+
+def slot_of(poc, runner):
+    return poc % runner.N_SLOTS
+
+
+def run_ours(a):
+    import torch
+    import torch.distributed as dist
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device. The ME path has no CPU fallback (use --impl reference for the CPU arm).")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    wl = Workload(a)
+    frames = make_clip(wl, rank)
+    run = Runner(wl, rank, world, frames, local)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+
+    def timed(host, first_step, n_steps, sampler=None):
+        barrier()
+        run.pics = run.h2d = run.d2h = 0
+        l0 = run.sess.launch_count()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        if sampler:
+            sampler.start()
+        e0.record()
+        for s in range(first_step, first_step + n_steps):
+            run.step(s, host)
+        e1.record()
+        barrier()
+        ms = e0.elapsed_time(e1)
+        if world > 1:
+            t = torch.tensor([ms], device="cuda", dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms, run.pics, run.sess.launch_count() - l0
+
+    # ---- device-resident pass: raw frames already in HBM, results stay in HBM ----
+    for s in range(a.warmup):
+        run.step(s, host=False)
+    run.sess.enable_timing(True)
+    run.sess.kernel_time(reset=True)
+    run.sess.sad_ops(reset=True)
+    sampler = ClockSampler(local)
+    ms, pics, launches = timed(False, a.warmup, a.steps, sampler)
+    clocks = sampler.stop()
+    fp_ms, hme_ms, n_timed = run.sess.kernel_time(reset=True)
+    hme_ops, fp_ops = run.sess.sad_ops(reset=True)
+    run.sess.enable_timing(False)
+    value = world * pics / (ms * 1e-3)
+
+    # ---- end-to-end pass: pinned host frames in, MeSbResults + statistics out, every step ----
+    run.resident.clear()
+    base = a.warmup + a.steps
+    for s in range(base, base + min(a.warmup, 2)):
+        run.step(s, host=True)
+    base += min(a.warmup, 2)
+    ms_e, pics_e, _ = timed(True, base, a.steps)
+    h2d_step, d2h_step = run.h2d // max(1, a.steps), run.d2h // max(1, a.steps)
+    e2e = world * pics_e / (ms_e * 1e-3)
+
+    if rank == 0:
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except OSError:
+            pass
+        hbm_peak = peaks.get("hbm_gbs", 6650.0)
+        n_refs = wl.mrp["l0"] + wl.mrp["l1"]
+        dominant, dom_ms, dom_ops = ("k_fullpel", fp_ms, fp_ops) if fp_ms >= hme_ms else ("k_hme", hme_ms, hme_ops)
+        # algorithmic bytes of one launch (one picture): every plane of the source and of each reference read once
+        # (1 + 1/4 + 1/16 of WxH each) + the per-b64 results the launch writes
+        plane = 1.3125 * wl.w * wl.h if dominant == "k_hme" else 1.0 * wl.w * wl.h
+        n_b64 = ((wl.w + 63) // 64) * ((wl.h + 63) // 64)
+        out_b = n_b64 * (1512 if dominant == "k_hme" else 8 * 85 * 8)
+        alg_bytes = (1 + n_refs) * plane + out_b
+        avg_s = dom_ms * 1e-3 / max(1, n_timed)
+        sm_mhz = clocks.get("sm_mhz") or peaks.get("sm_max_mhz", 1965.0)
+        int_peak = INT_PEAK_LANE_INSTR_PER_CLK_SM * 4 * N_SM * sm_mhz * 1e6  # |a-b| ops/s at the sampled clock
+        line = {
+            "metric": "open-loop ME frames/s", "value": round(value, 2), "unit": "frames/s", "n_gpus": world,
+            "steps": a.steps, "warmup": a.warmup, "ms_per_step": round(ms / a.steps, 4), "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": wl.name, "pictures_per_step": wl.mgop, "sharding": "mini-GOP m -> rank m % N",
+                       "l2": "inputs larger than L2: %d distinct %dx%d frames (%.0f MB) stream through the picture store, no explicit flush"
+                             % (wl.n_frames, wl.w, wl.h, wl.n_frames * wl.w * wl.h / 1e6)},
+            "e2e": {"value": round(e2e, 2), "unit": "frames/s", "h2d_bytes_per_step": int(h2d_step), "d2h_bytes_per_step": int(d2h_step),
+                    "ms_per_step": round(ms_e / a.steps, 4)},
+            "gpu_launches": int(launches),
+            "clocks": clocks,
+            "roofline": {"bound": "hbm", "kernel": dominant, "achieved": round(alg_bytes / avg_s / 1e9, 2), "peak": hbm_peak,
+                         "unit": "GB/s", "frac": round(alg_bytes / avg_s / 1e9 / hbm_peak, 5), "traffic": None,
+                         "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback",
+                         "note": "integer-ALU bound kernel (byte SAD); see roofline_int"},
+            "roofline_int": {"bound": "int_alu(VABSDIFF4.U8.ACC)", "kernel": dominant,
+                             "achieved": round(dom_ops / (dom_ms * 1e-3) / 1e12, 3) if dom_ms else None,
+                             "peak": round(int_peak / 1e12, 2), "unit": "T |a-b| ops/s",
+                             "frac": round(dom_ops / (dom_ms * 1e-3) / int_peak, 4) if dom_ms else None,
+                             "peak_def": "41.5 lane-instr/clk/SM (measured) x 4 px x 148 SM x sampled SM clock"},
+            "stage_ms_per_picture": {"k_hme": round(hme_ms / max(1, n_timed), 4), "k_fullpel": round(fp_ms / max(1, n_timed), 4)},
+            "sad_gops": round((hme_ops + fp_ops) / (ms * 1e-3) / 1e9, 1),
+        }
+        if not a.no_cpu_baseline and world == 1:
+            line["cpu_baseline"] = cpu_baseline(wl, frames, a.cpu_baseline_pics)
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU arm: the reference's own ME on the host cores (oracle/_ref), else the oracle port
+# ------------------------------------------------------------------------------------------------
+def cpu_me_pictures(wl, frames, pocs, threads):
+    """-> (seconds wall, kind). Runs the ME stage of the given pictures on `threads` host threads."""
+    from concurrent.futures import ThreadPoolExecutor
+    from oracle import pyoracle as po  # test infrastructure: used here only as the timed CPU baseline
+    import svtme_b200  # noqa: F401
+    from svt_av1_psy_b200 import abi
+    use_ref = po.ref_available()
+    if not use_ref:
+        po.oracle_lib()
+    simd = 2 if "avx512bw" in open("/proc/cpuinfo").read() else 1
+
+    def one(poc):
+        plan = wl.plan(poc)
+        src = frames[poc % wl.n_frames]
+        refs = [[frames[p % wl.n_frames] for p in plan["l0"]], [frames[p % wl.n_frames] for p in plan["l1"]]]
+        pin = po.make_pic_in(src, refs, [plan["l0"], plan["l1"]], poc, wl.preset, qp=wl.qp, temporal_layer=plan["tl"],
+                             hier_levels=wl.hier, is_ref=plan["is_ref"], simd=simd, mrp=wl.mrp)
+        if use_ref:
+            prm = po.ref_derive_params(pin)
+            res = abi.MePicResults()  # no outputs wanted: time the search only
+            rc = po.ref_lib().ref_me_picture(C.byref(pin), C.byref(res), None, None)
+        else:
+            sys.path.insert(0, os.path.join(ROOT, "tests"))
+            from util import orc_me, params_from_encoder_inputs
+            prm = params_from_encoder_inputs(src, refs, [plan["l0"], plan["l1"]], poc, wl.preset, qp=wl.qp,
+                                             temporal_layer=plan["tl"], hier_levels=wl.hier, is_ref=plan["is_ref"], mrp=wl.mrp)
+            orc_me(src, refs, prm, debug=False)
+            rc = 0
+        assert rc == 0
+    t0 = time.time()
+    with ThreadPoolExecutor(max_workers=threads) as ex:
+        list(ex.map(one, pocs))
+    return time.time() - t0, ("reference" if use_ref else "port"), simd
+
+
+def cpu_baseline(wl, frames, n_pics):
+    cores = os.cpu_count() or 1
+    n = n_pics or cores
+    first = wl.mgop  # second mini-GOP: all references exist
+    pocs = wl.order(first)[:n]
+    sec, kind, simd = cpu_me_pictures(wl, frames, pocs, cores)
+    return {"value": round(len(pocs) / sec, 3), "unit": "frames/s", "cores": cores, "kind": kind,
+            "sample": "%d pictures of the same mini-GOP, one per thread, %s ME kernels (%s), ME stage only (planes built outside the "
+                      "timed region are NOT excluded: pyramid build is part of the stage)" % (
+                          len(pocs), "reference C + " + ("AVX-512/AVX2" if simd == 2 else "AVX2") if kind == "reference" else "oracle C port", kind),
+            "seconds": round(sec, 2)}
+
+
+def run_reference(a):
+    rank = int(os.environ.get("RANK", 0))
+    if rank != 0:
+        return
+    wl = Workload(a)
+    frames = make_clip(wl, 0)
+    cores = os.cpu_count() or 1
+    pics_per_step = cores
+    order = []
+    m = 1
+    while len(order) < pics_per_step * (a.steps + a.warmup):
+        order += wl.order(m * wl.mgop)
+        m += 1
+    secs = []
+    kind = simd = None
+    for s in range(a.warmup + a.steps):
+        pocs = order[s * pics_per_step:(s + 1) * pics_per_step]
+        sec, kind, simd = cpu_me_pictures(wl, frames, pocs, cores)
+        if s >= a.warmup:
+            secs.append(sec)
+    total = sum(secs)
+    value = pics_per_step * a.steps / total
+    line = {
+        "impl": "reference", "metric": "open-loop ME frames/s", "value": round(value, 3), "unit": "frames/s",
+        "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup, "ms_per_step": round(1e3 * total / a.steps, 2),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": wl.name, "pictures_per_step": pics_per_step},
+        "cpu_baseline": {"value": round(value, 3), "unit": "frames/s", "cores": cores, "kind": kind,
+                         "sample": "%d pictures per step, one per host thread (%s kernels)" % (pics_per_step, "AVX-512/AVX2" if simd == 2 else "AVX2")},
+        "e2e": {"value": round(value, 3), "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+if __name__ == "__main__":
+    args = parse_args()
+    import svtme_b200  # noqa: F401,E402
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)

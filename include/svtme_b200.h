@@ -300,10 +300,40 @@ uint32_t svtme_session_set_stream(SvtMeSession *s, void *cuda_stream);
 /* Number of kernel launches issued by this session since creation (bench "gpu_launches"). */
 uint64_t svtme_session_launch_count(SvtMeSession *s);
 
+/* Switch per-stage CUDA-event timing of svtme_picture_me* on or off (off by default: each timed
+   call records three events on the session stream). */
+uint32_t svtme_session_enable_timing(SvtMeSession *s, int on);
+
 /* Device time (ms, CUDA events on the session stream) of the dominant full-pel search kernel
    accumulated since the last call with reset=1, and the number of launches it covers. */
 uint32_t svtme_session_kernel_time(SvtMeSession *s, int reset, double *fullpel_ms,
                                    double *hme_ms, uint64_t *n_launch);
+
+/* Algorithmic work done by the kernels since the last reset: "SAD operations" = search positions x
+   block pixels compared (|a-b| and accumulate), the unit of SURVEY.md 8(d) / BASELINE.md. Counted on
+   the device by the thread that sets up each search. */
+uint32_t svtme_session_sad_ops(SvtMeSession *s, int reset, uint64_t *hme_ops, uint64_t *fullpel_ops);
+
+/* Per-b64 HME-stage state of the last svtme_picture_me* call (parity debugging): n_b64 records of
+   SvtMeHmeState. No reference counterpart as an array; the fields mirror MeContext members
+   (me_context.h:435-452, :329-334, :348-355). */
+typedef struct SvtMeHmeState {
+    int16_t  x_hme[3][2][4][2][2]; /* [level][list][ref][sr_w][sr_h] x_hme_levelN_search_center */
+    int16_t  y_hme[3][2][4][2][2];
+    uint64_t hme_sad[3][2][4][2][2];
+    int16_t  prehme_mv_x[2][4][2], prehme_mv_y[2][4][2];
+    uint64_t prehme_sad[2][4][2];
+    uint32_t zz_sad[2][4];
+    uint32_t reduce_me_sr_divisor[2][4];
+    int16_t  hme_sc_x[2][4], hme_sc_y[2][4]; /* before me_prune_ref */
+    uint64_t sr_hme_sad[2][4];
+    uint8_t  do_ref[2][4];
+} SvtMeHmeState;
+uint32_t svtme_fetch_hme_state(SvtMeSession *s, void *dst, size_t dst_bytes);
+
+/* sizeof() of the ABI structs as the library was compiled (0 SvtMeCtrls, 1 SvtMePicParams,
+   2 SvtMeSearchResult, 3 SvtMeWindow, 4 SvtMePicResults, 5 SvtMeHmeState): binding self-check. */
+uint32_t svtme_abi_sizeof(int what);
 
 /* Library/build identification string. */
 const char *svtme_version(void);

@@ -126,19 +126,7 @@ def ptr(a):
     return a.ctypes.data_as(C.c_void_p)
 
 
-# ---- mrp levels used by the BASELINE configs (enc_handle.c:3799-3960, :4588-4613) ----
-def mrp_for_preset(enc_mode):
-    """returns dict(only_l_bwd, safe_limit_nref, safe_limit_zz_th, l0, l1) for CRF random access,
-    non-SC content, resolution > 360p, fast_decode 0."""
-    if enc_mode <= -1:  # MR and below: mrp_level 1
-        return dict(only_l_bwd=0, safe_limit_nref=0, safe_limit_zz_th=0, l0=4, l1=3)
-    if enc_mode <= 1:  # mrp_level 2
-        return dict(only_l_bwd=1, safe_limit_nref=0, safe_limit_zz_th=0, l0=4, l1=3)
-    if enc_mode <= 4:  # mrp_level 5
-        return dict(only_l_bwd=1, safe_limit_nref=0, safe_limit_zz_th=0, l0=4, l1=3)
-    if enc_mode <= 8:  # mrp_level 9
-        return dict(only_l_bwd=1, safe_limit_nref=2, safe_limit_zz_th=0, l0=3, l1=2)
-    return dict(only_l_bwd=1, safe_limit_nref=2, safe_limit_zz_th=0, l0=2, l1=2)  # mrp_level 10
+from svt_av1_psy_b200.gop import mrp_for_preset  # noqa: E402,F401
 
 
 def make_pic_in(src, refs, ref_pocs, poc, enc_mode, qp=35, temporal_layer=1, hier_levels=5, is_ref=1,

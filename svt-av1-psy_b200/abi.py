@@ -143,6 +143,14 @@ assert SEARCH_RESULT_DTYPE.itemsize == C.sizeof(MeSearchResult) == 16
 assert WINDOW_DTYPE.itemsize == C.sizeof(MeWindow) == 8
 
 
+HME_STATE_DTYPE = np.dtype([
+    ("x_hme", "<i2", (3, 2, 4, 2, 2)), ("y_hme", "<i2", (3, 2, 4, 2, 2)), ("hme_sad", "<u8", (3, 2, 4, 2, 2)),
+    ("prehme_mv_x", "<i2", (2, 4, 2)), ("prehme_mv_y", "<i2", (2, 4, 2)), ("prehme_sad", "<u8", (2, 4, 2)),
+    ("zz_sad", "<u4", (2, 4)), ("reduce_me_sr_divisor", "<u4", (2, 4)),
+    ("hme_sc_x", "<i2", (2, 4)), ("hme_sc_y", "<i2", (2, 4)), ("sr_hme_sad", "<u8", (2, 4)), ("do_ref", "u1", (2, 4)),
+], align=True)
+
+
 def n_b64_of(width, height):
     return ((width + 63) // 64) * ((height + 63) // 64)
 

@@ -64,6 +64,14 @@ def lib():
         L.svtme_session_kernel_time.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_double),
                                                 C.POINTER(C.c_double), C.POINTER(C.c_uint64)]
         L.svtme_session_kernel_time.restype = C.c_uint32
+        L.svtme_session_enable_timing.argtypes = [C.c_void_p, C.c_int]
+        L.svtme_session_enable_timing.restype = C.c_uint32
+        L.svtme_fetch_hme_state.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t]
+        L.svtme_fetch_hme_state.restype = C.c_uint32
+        L.svtme_session_sad_ops.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
+        L.svtme_session_sad_ops.restype = C.c_uint32
+        L.svtme_abi_sizeof.argtypes = [C.c_int]
+        L.svtme_abi_sizeof.restype = C.c_uint32
         _LIB = L
     return _LIB
 
@@ -141,6 +149,9 @@ class Session:
     def upload_ptr(self, pic_id, host_ptr, stride):
         _check(lib().svtme_picture_upload(self._h, pic_id, host_ptr, stride), "svtme_picture_upload")
 
+    def upload_ptr16(self, pic_id, host_ptr, stride_in_samples):
+        _check(lib().svtme_picture_upload_10bit(self._h, pic_id, host_ptr, stride_in_samples), "svtme_picture_upload_10bit")
+
     def upload_device(self, pic_id, dev_ptr, stride):
         _check(lib().svtme_picture_upload_device(self._h, pic_id, dev_ptr, stride), "svtme_picture_upload_device")
 
@@ -176,6 +187,20 @@ class Session:
 
     def set_stream(self, cuda_stream_ptr):
         _check(lib().svtme_session_set_stream(self._h, C.c_void_p(cuda_stream_ptr)), "svtme_session_set_stream")
+
+    def enable_timing(self, on=True):
+        _check(lib().svtme_session_enable_timing(self._h, 1 if on else 0), "svtme_session_enable_timing")
+
+    def hme_state(self):
+        n = abi.n_b64_of(self.width, self.height)
+        out = np.zeros(n, dtype=abi.HME_STATE_DTYPE)
+        _check(lib().svtme_fetch_hme_state(self._h, out.ctypes.data, out.nbytes), "svtme_fetch_hme_state")
+        return out
+
+    def sad_ops(self, reset=False):
+        a, b = C.c_uint64(), C.c_uint64()
+        _check(lib().svtme_session_sad_ops(self._h, 1 if reset else 0, C.byref(a), C.byref(b)), "svtme_session_sad_ops")
+        return int(a.value), int(b.value)
 
     def launch_count(self):
         return int(lib().svtme_session_launch_count(self._h))

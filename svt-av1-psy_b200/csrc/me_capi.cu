@@ -1,0 +1,416 @@
+// me_capi.cu — the extern "C" boundary of libsvtme_b200.so (include/svtme_b200.h): session
+// management, picture upload, per-picture ME launch, result fetch. No CPU fallback anywhere: a
+// failing CUDA call is reported on stderr and returned as SVTME_ERR_CUDA.
+#include <cuda_runtime.h>
+
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <vector>
+
+#include "me_device.cuh"
+#include "me_launch.h"
+#include "svtme_b200.h"
+
+#define CU_TRY(expr)                                                                                       \
+    do {                                                                                                   \
+        cudaError_t e_ = (expr);                                                                           \
+        if (e_ != cudaSuccess) {                                                                           \
+            fprintf(stderr, "[svtme_b200] CUDA error %s at %s:%d (%s)\n", cudaGetErrorString(e_), __FILE__, \
+                    __LINE__, #expr);                                                                      \
+            return SVTME_ERR_CUDA;                                                                         \
+        }                                                                                                  \
+    } while (0)
+
+static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+struct ResultLayout { // offsets into the device result slab
+    size_t best_sad, best_mv, search_results, windows, total, mv, cand, d64, d32, d16, d8, rc, var, stat, gm, sb_state, ops, end;
+};
+
+struct SvtMeSession {
+    int          device = 0;
+    int          w = 0, h = 0, max_pics = 0, n_b64 = 0, b64_cols = 0, b64_rows = 0;
+    cudaStream_t stream = nullptr;
+    bool         own_stream = false;
+    uint8_t     *pic_slab = nullptr;
+    size_t       pic_bytes = 0;
+    std::vector<DevPic> pics;
+    std::vector<char>   pic_valid;
+    uint8_t     *res_slab = nullptr;
+    ResultLayout lay{};
+    uint16_t    *d_in16 = nullptr;
+    SvtMePicParams last_pp{};
+    bool         have_results = false;
+    uint64_t     launches = 0;
+    bool         timing = false;
+    std::vector<cudaEvent_t> ev; // triples: before hme, after hme, after full-pel
+    size_t       ev_used = 0;
+    double       acc_hme_ms = 0, acc_fp_ms = 0;
+    uint64_t     n_timed = 0;
+    std::mutex   mu;
+};
+
+static void plane_geom(int w, int h, int level, int *pw, int *ph, int *pad, int *stride, size_t *bytes) {
+    static const int pads[3] = {SVTME_FULL_PAD, SVTME_QUARTER_PAD, SVTME_SIXTEENTH_PAD};
+    *pw     = w >> level;
+    *ph     = h >> level;
+    *pad    = pads[level];
+    *stride = (int)align_up((size_t)(*pw + 2 * *pad), 16);
+    *bytes  = align_up((size_t)*stride * (size_t)(*ph + 2 * *pad) + 2 * SVTME_SLAB_SLACK, 256);
+}
+
+static void result_layout(ResultLayout &L, int n_b64) {
+    size_t o = 0;
+    auto take = [&](size_t bytes) { size_t at = o; o = align_up(o + bytes, 256); return at; };
+    L.best_sad       = take((size_t)n_b64 * 8 * 85 * 4);
+    L.best_mv        = take((size_t)n_b64 * 8 * 85 * 4);
+    L.search_results = take((size_t)n_b64 * 8 * sizeof(SvtMeSearchResult));
+    L.windows        = take((size_t)n_b64 * 8 * sizeof(SvtMeWindow));
+    L.total          = take((size_t)n_b64 * 85);
+    L.mv             = take((size_t)n_b64 * 85 * 8 * 4);
+    L.cand           = take((size_t)n_b64 * 85 * 32);
+    L.d64 = take((size_t)n_b64 * 4); L.d32 = take((size_t)n_b64 * 4); L.d16 = take((size_t)n_b64 * 4);
+    L.d8  = take((size_t)n_b64 * 4); L.rc  = take((size_t)n_b64 * 4); L.var = take((size_t)n_b64 * 4);
+    L.stat = take((size_t)n_b64); L.gm = take((size_t)n_b64);
+    L.sb_state = take((size_t)n_b64 * sizeof(SbState));
+    L.ops = take(64);
+    L.end = o;
+}
+
+extern "C" const char *svtme_version(void) { return "svtme_b200 0.1 (sm_100a, open-loop ME of SVT-AV1-PSY 2.3.0-A)"; }
+
+extern "C" uint32_t svtme_session_create(SvtMeSession **out, int device, uint32_t width, uint32_t height,
+                                         uint32_t max_pictures) {
+    if (!out || width == 0 || height == 0 || (width & 7) || (height & 7) || width > 16384 || height > 16384 ||
+        max_pictures == 0 || max_pictures > 4096)
+        return SVTME_ERR_BAD_PARAMETER;
+    *out = nullptr;
+    int n_dev = 0;
+    CU_TRY(cudaGetDeviceCount(&n_dev));
+    if (device < 0 || device >= n_dev) {
+        fprintf(stderr, "[svtme_b200] no CUDA device %d (found %d); there is no CPU fallback\n", device, n_dev);
+        return SVTME_ERR_CUDA;
+    }
+    CU_TRY(cudaSetDevice(device));
+    SvtMeSession *s = new SvtMeSession();
+    s->device = device; s->w = (int)width; s->h = (int)height; s->max_pics = (int)max_pictures;
+    s->b64_cols = (s->w + 63) / 64; s->b64_rows = (s->h + 63) / 64; s->n_b64 = s->b64_cols * s->b64_rows;
+    size_t off[3], total = 0;
+    int pw[3], ph[3], pad[3], st[3];
+    for (int i = 0; i < 3; i++) {
+        size_t b;
+        plane_geom(s->w, s->h, i, &pw[i], &ph[i], &pad[i], &st[i], &b);
+        off[i] = total;
+        total += b;
+    }
+    s->pic_bytes = total;
+    cudaError_t e = cudaMalloc(&s->pic_slab, total * max_pictures);
+    if (e != cudaSuccess) { delete s; fprintf(stderr, "[svtme_b200] cudaMalloc picture store: %s\n", cudaGetErrorString(e)); return SVTME_ERR_INSUFFICIENT_RESOURCES; }
+    cudaMemset(s->pic_slab, 0, total * max_pictures);
+    s->pics.resize(max_pictures);
+    s->pic_valid.assign(max_pictures, 0);
+    for (uint32_t p = 0; p < max_pictures; p++)
+        for (int i = 0; i < 3; i++) {
+            DevPlane &pl = s->pics[p].lvl[i];
+            pl.buf = s->pic_slab + (size_t)p * total + off[i] + SVTME_SLAB_SLACK;
+            pl.stride = st[i]; pl.org_x = pad[i]; pl.org_y = pad[i]; pl.width = pw[i]; pl.height = ph[i];
+        }
+    result_layout(s->lay, s->n_b64);
+    e = cudaMalloc(&s->res_slab, s->lay.end);
+    if (e != cudaSuccess) { cudaFree(s->pic_slab); delete s; return SVTME_ERR_INSUFFICIENT_RESOURCES; }
+    cudaMemset(s->res_slab, 0, s->lay.end);
+    CU_TRY(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
+    s->own_stream = true;
+    CU_TRY(cudaDeviceSynchronize());
+    *out = s;
+    return SVTME_OK;
+}
+
+extern "C" void svtme_session_destroy(SvtMeSession *s) {
+    if (!s) return;
+    cudaSetDevice(s->device);
+    cudaStreamSynchronize(s->stream);
+    for (auto &e : s->ev) cudaEventDestroy(e);
+    if (s->own_stream) cudaStreamDestroy(s->stream);
+    cudaFree(s->pic_slab);
+    cudaFree(s->res_slab);
+    if (s->d_in16) cudaFree(s->d_in16);
+    delete s;
+}
+
+extern "C" void *svtme_session_stream(SvtMeSession *s) { return s ? (void *)s->stream : nullptr; }
+
+extern "C" uint32_t svtme_session_set_stream(SvtMeSession *s, void *cuda_stream) {
+    if (!s) return SVTME_ERR_BAD_PARAMETER;
+    std::lock_guard<std::mutex> g(s->mu);
+    cudaSetDevice(s->device);
+    CU_TRY(cudaStreamSynchronize(s->stream));
+    if (s->own_stream) cudaStreamDestroy(s->stream);
+    s->stream     = (cudaStream_t)cuda_stream;
+    s->own_stream = false;
+    return SVTME_OK;
+}
+
+extern "C" uint64_t svtme_session_launch_count(SvtMeSession *s) { return s ? s->launches : 0; }
+
+extern "C" uint32_t svtme_session_sync(SvtMeSession *s) {
+    if (!s) return SVTME_ERR_BAD_PARAMETER;
+    cudaSetDevice(s->device);
+    CU_TRY(cudaStreamSynchronize(s->stream));
+    return SVTME_OK;
+}
+
+static uint32_t finish_upload(SvtMeSession *s, int32_t pic_id) {
+    s->launches += (uint64_t)svtme_launch_build_pyramid(s->pics[pic_id], s->stream);
+    CU_TRY(cudaGetLastError());
+    s->pic_valid[pic_id] = 1;
+    return SVTME_OK;
+}
+
+extern "C" uint32_t svtme_picture_upload(SvtMeSession *s, int32_t pic_id, const uint8_t *luma, uint32_t stride) {
+    if (!s || !luma || pic_id < 0 || pic_id >= s->max_pics || stride < (uint32_t)s->w) return SVTME_ERR_BAD_PARAMETER;
+    std::lock_guard<std::mutex> g(s->mu);
+    CU_TRY(cudaSetDevice(s->device));
+    const DevPlane &f = s->pics[pic_id].lvl[0];
+    uint8_t *interior = const_cast<uint8_t *>(f.buf) + (size_t)f.org_y * f.stride + f.org_x;
+    CU_TRY(cudaMemcpy2DAsync(interior, (size_t)f.stride, luma, stride, (size_t)s->w, (size_t)s->h, cudaMemcpyHostToDevice, s->stream));
+    return finish_upload(s, pic_id);
+}
+
+extern "C" uint32_t svtme_picture_upload_device(SvtMeSession *s, int32_t pic_id, const uint8_t *d_luma, uint32_t stride) {
+    if (!s || !d_luma || pic_id < 0 || pic_id >= s->max_pics || stride < (uint32_t)s->w) return SVTME_ERR_BAD_PARAMETER;
+    std::lock_guard<std::mutex> g(s->mu);
+    CU_TRY(cudaSetDevice(s->device));
+    const DevPlane &f = s->pics[pic_id].lvl[0];
+    uint8_t *interior = const_cast<uint8_t *>(f.buf) + (size_t)f.org_y * f.stride + f.org_x;
+    s->launches += (uint64_t)svtme_launch_copy2d(d_luma, (int)stride, interior, f.stride, s->w, s->h, s->stream);
+    return finish_upload(s, pic_id);
+}
+
+extern "C" uint32_t svtme_picture_upload_10bit(SvtMeSession *s, int32_t pic_id, const uint16_t *luma16, uint32_t stride_in_samples) {
+    if (!s || !luma16 || pic_id < 0 || pic_id >= s->max_pics || stride_in_samples < (uint32_t)s->w) return SVTME_ERR_BAD_PARAMETER;
+    std::lock_guard<std::mutex> g(s->mu);
+    CU_TRY(cudaSetDevice(s->device));
+    if (!s->d_in16) {
+        cudaError_t e = cudaMalloc(&s->d_in16, (size_t)s->w * s->h * 2);
+        if (e != cudaSuccess) return SVTME_ERR_INSUFFICIENT_RESOURCES;
+    }
+    CU_TRY(cudaMemcpy2DAsync(s->d_in16, (size_t)s->w * 2, luma16, (size_t)stride_in_samples * 2, (size_t)s->w * 2, (size_t)s->h,
+                             cudaMemcpyHostToDevice, s->stream));
+    const DevPlane &f = s->pics[pic_id].lvl[0];
+    uint8_t *interior = const_cast<uint8_t *>(f.buf) + (size_t)f.org_y * f.stride + f.org_x;
+    s->launches += (uint64_t)svtme_launch_unpack10(s->d_in16, s->w, interior, f.stride, s->w, s->h, s->stream);
+    return finish_upload(s, pic_id);
+}
+
+extern "C" uint32_t svtme_picture_download_plane(SvtMeSession *s, int32_t pic_id, int level, uint8_t *dst, size_t dst_capacity,
+                                                 uint32_t *stride, uint32_t *rows, uint32_t *org_x, uint32_t *org_y) {
+    if (!s || !dst || pic_id < 0 || pic_id >= s->max_pics || level < 0 || level > 2 || !s->pic_valid[pic_id]) return SVTME_ERR_BAD_PARAMETER;
+    std::lock_guard<std::mutex> g(s->mu);
+    CU_TRY(cudaSetDevice(s->device));
+    const DevPlane &p = s->pics[pic_id].lvl[level];
+    const size_t W = (size_t)p.width + 2 * p.org_x, H = (size_t)p.height + 2 * p.org_y;
+    if (dst_capacity < W * H) return SVTME_ERR_BAD_PARAMETER;
+    CU_TRY(cudaMemcpy2DAsync(dst, W, p.buf, (size_t)p.stride, W, H, cudaMemcpyDeviceToHost, s->stream));
+    CU_TRY(cudaStreamSynchronize(s->stream));
+    if (stride) *stride = (uint32_t)W;
+    if (rows) *rows = (uint32_t)H;
+    if (org_x) *org_x = (uint32_t)p.org_x;
+    if (org_y) *org_y = (uint32_t)p.org_y;
+    return SVTME_OK;
+}
+
+static uint32_t validate_params(const SvtMeSession *s, int32_t pic_id, const SvtMePicParams *pp) {
+    if (!s || !pp || pic_id < 0 || pic_id >= s->max_pics || !s->pic_valid[pic_id]) return SVTME_ERR_BAD_PARAMETER;
+    if (pp->num_of_list_to_search < 1 || pp->num_of_list_to_search > 2) return SVTME_ERR_BAD_PARAMETER;
+    if (!pp->enable_me_16x16) return SVTME_ERR_BAD_PARAMETER; // svt_aom_get_enable_me_16x16 is constant 1
+    if (pp->ctrls.num_hme_sa_w != 2 || pp->ctrls.num_hme_sa_h != 2) return SVTME_ERR_BAD_PARAMETER; // enc_mode_config.c:146-147
+    if (pp->max_refs > 8 || pp->max_cand > 32) return SVTME_ERR_BAD_PARAMETER;
+    for (int l = 0; l < pp->num_of_list_to_search; l++) {
+        if (pp->num_of_ref_pic_to_search[l] > SVTME_MAX_REF) return SVTME_ERR_BAD_PARAMETER;
+        for (int r = 0; r < pp->num_of_ref_pic_to_search[l]; r++) {
+            const int id = pp->ref_pic_id[l][r];
+            if (id < 0 || id >= s->max_pics || !s->pic_valid[id]) return SVTME_ERR_BAD_PARAMETER;
+        }
+    }
+    if (pp->num_of_ref_pic_to_search[0] < 1) return SVTME_ERR_BAD_PARAMETER;
+    // the MeSbResults arrays are sized by max_l0 / max_refs (pcs.c:91-96): more refs than that would alias entries
+    if (pp->num_of_ref_pic_to_search[0] > pp->max_l0 || pp->max_l0 > pp->max_refs) return SVTME_ERR_BAD_PARAMETER;
+    if (pp->num_of_list_to_search == 2 && pp->num_of_ref_pic_to_search[1] > pp->max_refs - pp->max_l0) return SVTME_ERR_BAD_PARAMETER;
+    return SVTME_OK;
+}
+
+static void fold_events(SvtMeSession *s) {
+    for (size_t i = 0; i + 3 <= s->ev_used; i += 3) {
+        float a = 0, b = 0;
+        if (cudaEventElapsedTime(&a, s->ev[i], s->ev[i + 1]) == cudaSuccess &&
+            cudaEventElapsedTime(&b, s->ev[i + 1], s->ev[i + 2]) == cudaSuccess) {
+            s->acc_hme_ms += a;
+            s->acc_fp_ms += b;
+            s->n_timed++;
+        }
+    }
+    s->ev_used = 0;
+}
+
+static uint32_t launch_me(SvtMeSession *s, int32_t pic_id, const SvtMePicParams *pp) {
+    uint32_t rc = validate_params(s, pic_id, pp);
+    if (rc != SVTME_OK) return rc;
+    CU_TRY(cudaSetDevice(s->device));
+    PicJob job;
+    memset(&job, 0, sizeof(job));
+    job.pp  = *pp;
+    job.src = s->pics[pic_id];
+    for (int l = 0; l < pp->num_of_list_to_search; l++)
+        for (int r = 0; r < pp->num_of_ref_pic_to_search[l]; r++) job.ref[l][r] = s->pics[pp->ref_pic_id[l][r]];
+    job.pic_w = s->w; job.pic_h = s->h; job.b64_cols = s->b64_cols; job.b64_rows = s->b64_rows; job.n_b64 = s->n_b64;
+    job.n_pus = pp->enable_me_8x8 ? 85 : 21;
+    svtme_smem_plan(*pp, &job.hme_smem_bytes, &job.fp_smem_bytes);
+    uint8_t *R = s->res_slab;
+    job.sb_state       = (SbState *)(R + s->lay.sb_state);
+    job.best_sad       = (uint32_t *)(R + s->lay.best_sad);
+    job.best_mv        = (uint32_t *)(R + s->lay.best_mv);
+    job.windows        = (SvtMeWindow *)(R + s->lay.windows);
+    job.search_results = (SvtMeSearchResult *)(R + s->lay.search_results);
+    job.total_me_candidate_index = R + s->lay.total;
+    job.me_mv_array              = (uint32_t *)(R + s->lay.mv);
+    job.me_candidate_array       = R + s->lay.cand;
+    job.me_64x64_distortion = (uint32_t *)(R + s->lay.d64);
+    job.me_32x32_distortion = (uint32_t *)(R + s->lay.d32);
+    job.me_16x16_distortion = (uint32_t *)(R + s->lay.d16);
+    job.me_8x8_distortion   = (uint32_t *)(R + s->lay.d8);
+    job.rc_me_distortion    = (uint32_t *)(R + s->lay.rc);
+    job.me_8x8_cost_variance = (uint32_t *)(R + s->lay.var);
+    job.stationary_block_present_sb = R + s->lay.stat;
+    job.rc_me_allow_gm              = R + s->lay.gm;
+    job.sad_ops                     = (unsigned long long *)(R + s->lay.ops);
+    cudaEvent_t e0 = nullptr, e1 = nullptr, e2 = nullptr;
+    if (s->timing) {
+        if (s->ev_used + 3 > s->ev.size()) {
+            if (s->ev.size() >= 3 * 2048) {
+                CU_TRY(cudaStreamSynchronize(s->stream));
+                fold_events(s);
+            } else {
+                for (int i = 0; i < 3; i++) {
+                    cudaEvent_t e;
+                    CU_TRY(cudaEventCreate(&e));
+                    s->ev.push_back(e);
+                }
+            }
+        }
+        e0 = s->ev[s->ev_used]; e1 = s->ev[s->ev_used + 1]; e2 = s->ev[s->ev_used + 2];
+        s->ev_used += 3;
+    }
+    s->launches += (uint64_t)svtme_launch_picture_me(job, s->stream, e0, e1, e2);
+    CU_TRY(cudaGetLastError());
+    s->last_pp      = *pp;
+    s->have_results = true;
+    return SVTME_OK;
+}
+
+static uint32_t fetch(SvtMeSession *s, SvtMePicResults *res, int sync) {
+    if (!s->have_results || !res) return SVTME_ERR_BAD_PARAMETER;
+    const SvtMePicParams &pp = s->last_pp;
+    const size_t n = (size_t)s->n_b64, n_pus = pp.enable_me_8x8 ? 85 : 21;
+    uint8_t *R = s->res_slab;
+#define D2H(dst, off, bytes)                                                                               \
+    if (res->dst) CU_TRY(cudaMemcpyAsync(res->dst, R + s->lay.off, (bytes), cudaMemcpyDeviceToHost, s->stream))
+    D2H(p_sb_best_sad, best_sad, n * 8 * 85 * 4);
+    D2H(p_sb_best_mv, best_mv, n * 8 * 85 * 4);
+    D2H(search_results, search_results, n * 8 * sizeof(SvtMeSearchResult));
+    D2H(me_windows, windows, n * 8 * sizeof(SvtMeWindow));
+    D2H(total_me_candidate_index, total, n * n_pus);
+    D2H(me_mv_array, mv, n * n_pus * pp.max_refs * 4);
+    D2H(me_candidate_array, cand, n * n_pus * pp.max_cand);
+    D2H(me_64x64_distortion, d64, n * 4);
+    D2H(me_32x32_distortion, d32, n * 4);
+    D2H(me_16x16_distortion, d16, n * 4);
+    D2H(me_8x8_distortion, d8, n * 4);
+    D2H(rc_me_distortion, rc, n * 4);
+    D2H(me_8x8_cost_variance, var, n * 4);
+    D2H(stationary_block_present_sb, stat, n);
+    D2H(rc_me_allow_gm, gm, n);
+#undef D2H
+    if (sync) CU_TRY(cudaStreamSynchronize(s->stream));
+    return SVTME_OK;
+}
+
+extern "C" uint32_t svtme_picture_me_device(SvtMeSession *s, int32_t pic_id, const SvtMePicParams *params) {
+    if (!s) return SVTME_ERR_BAD_PARAMETER;
+    std::lock_guard<std::mutex> g(s->mu);
+    return launch_me(s, pic_id, params);
+}
+
+extern "C" uint32_t svtme_fetch_results(SvtMeSession *s, SvtMePicResults *results, int sync) {
+    if (!s) return SVTME_ERR_BAD_PARAMETER;
+    std::lock_guard<std::mutex> g(s->mu);
+    CU_TRY(cudaSetDevice(s->device));
+    return fetch(s, results, sync);
+}
+
+extern "C" uint32_t svtme_picture_me(SvtMeSession *s, int32_t pic_id, const SvtMePicParams *params, SvtMePicResults *results,
+                                     int sync) {
+    if (!s) return SVTME_ERR_BAD_PARAMETER;
+    std::lock_guard<std::mutex> g(s->mu);
+    uint32_t rc = launch_me(s, pic_id, params);
+    if (rc != SVTME_OK) return rc;
+    if (results) return fetch(s, results, sync);
+    if (sync) CU_TRY(cudaStreamSynchronize(s->stream));
+    return SVTME_OK;
+}
+
+extern "C" uint32_t svtme_session_enable_timing(SvtMeSession *s, int on) {
+    if (!s) return SVTME_ERR_BAD_PARAMETER;
+    std::lock_guard<std::mutex> g(s->mu);
+    s->timing = on != 0;
+    return SVTME_OK;
+}
+
+extern "C" uint32_t svtme_session_kernel_time(SvtMeSession *s, int reset, double *fullpel_ms, double *hme_ms, uint64_t *n_launch) {
+    if (!s) return SVTME_ERR_BAD_PARAMETER;
+    std::lock_guard<std::mutex> g(s->mu);
+    CU_TRY(cudaSetDevice(s->device));
+    CU_TRY(cudaStreamSynchronize(s->stream));
+    fold_events(s);
+    if (fullpel_ms) *fullpel_ms = s->acc_fp_ms;
+    if (hme_ms) *hme_ms = s->acc_hme_ms;
+    if (n_launch) *n_launch = s->n_timed;
+    if (reset) { s->acc_fp_ms = s->acc_hme_ms = 0; s->n_timed = 0; }
+    return SVTME_OK;
+}
+
+extern "C" uint32_t svtme_fetch_hme_state(SvtMeSession *s, void *dst, size_t dst_bytes) {
+    if (!s || !dst || dst_bytes < (size_t)s->n_b64 * sizeof(SbState)) return SVTME_ERR_BAD_PARAMETER;
+    std::lock_guard<std::mutex> g(s->mu);
+    CU_TRY(cudaSetDevice(s->device));
+    CU_TRY(cudaMemcpyAsync(dst, s->res_slab + s->lay.sb_state, (size_t)s->n_b64 * sizeof(SbState), cudaMemcpyDeviceToHost, s->stream));
+    CU_TRY(cudaStreamSynchronize(s->stream));
+    return SVTME_OK;
+}
+
+extern "C" uint32_t svtme_session_sad_ops(SvtMeSession *s, int reset, uint64_t *hme_ops, uint64_t *fullpel_ops) {
+    if (!s) return SVTME_ERR_BAD_PARAMETER;
+    std::lock_guard<std::mutex> g(s->mu);
+    CU_TRY(cudaSetDevice(s->device));
+    unsigned long long v[2] = {0, 0};
+    CU_TRY(cudaMemcpyAsync(v, s->res_slab + s->lay.ops, sizeof(v), cudaMemcpyDeviceToHost, s->stream));
+    CU_TRY(cudaStreamSynchronize(s->stream));
+    if (hme_ops) *hme_ops = v[0];
+    if (fullpel_ops) *fullpel_ops = v[1];
+    if (reset) CU_TRY(cudaMemsetAsync(s->res_slab + s->lay.ops, 0, sizeof(v), s->stream));
+    return SVTME_OK;
+}
+
+extern "C" uint32_t svtme_abi_sizeof(int what) {
+    switch (what) {
+    case 0: return (uint32_t)sizeof(SvtMeCtrls);
+    case 1: return (uint32_t)sizeof(SvtMePicParams);
+    case 2: return (uint32_t)sizeof(SvtMeSearchResult);
+    case 3: return (uint32_t)sizeof(SvtMeWindow);
+    case 4: return (uint32_t)sizeof(SvtMePicResults);
+    case 5: return (uint32_t)sizeof(SbState);
+    default: return 0;
+    }
+}

@@ -1,0 +1,162 @@
+// me_device.cuh — device-side data layout and the inner byte-SAD routines (sm_100a).
+//
+// Data layout in HBM
+//   * one slab per picture: three replicate-padded luma planes (full: pad 72, 1/4: pad 32,
+//     1/16: pad 16; reference_object.c:320-380, enc_handle.c:4485-4497), row stride rounded up to
+//     16 bytes, 512 bytes of slack before/after so that 4-byte aligned staging reads never leave
+//     the allocation.
+//   * per-b64 HME state (SbState) written by k_hme and read by k_fullpel / k_post.
+//   * per-(b64,list,ref) best SAD / MV arrays [85] written by k_fullpel (MeContext
+//     p_sb_best_sad / p_sb_best_mv, me_context.h:395-396).
+//
+// The arithmetic unit of the whole path is VABSDIFF4.U8.ACC (__vsadu4 + add): 4 pixel
+// |a-b| accumulated per lane-instruction. Measured on B200: 41.5 lane-instr/clk/SM
+// (profiles/r01_pipe_microbench.txt) = the integer roofline of this library.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "svtme_b200.h"
+
+#define SVTME_FULL_PAD 72
+#define SVTME_QUARTER_PAD 32
+#define SVTME_SIXTEENTH_PAD 16
+#define SVTME_SLAB_SLACK 512
+
+#define MAX_SAD_VALUE_U32 (128u * 128u * 255u) /* motion_estimation.h:85 */
+#define MAX_U32_ 0xFFFFFFFFu
+
+struct DevPlane {
+    const uint8_t *buf; // address of padded sample (0,0)
+    int stride, org_x, org_y, width, height;
+};
+struct DevPic {
+    DevPlane lvl[3]; // 0 full, 1 quarter, 2 sixteenth
+};
+
+// per-b64 state produced by the HME stage (the MeContext fields later stages read) + the
+// intermediate HME arrays kept for parity debugging (same layout as OrcDebug / RefMeDebug).
+struct SbState {
+    int16_t  x_hme[3][2][4][2][2]; // [level][list][ref][sr_w][sr_h]
+    int16_t  y_hme[3][2][4][2][2];
+    uint64_t hme_sad[3][2][4][2][2];
+    int16_t  prehme_mv_x[2][4][2], prehme_mv_y[2][4][2];
+    uint64_t prehme_sad[2][4][2];
+    uint32_t zz_sad[2][4];
+    uint32_t reduce_me_sr_divisor[2][4];
+    // SearchResults
+    int16_t  hme_sc_x[2][4], hme_sc_y[2][4];
+    uint64_t sr_hme_sad[2][4];
+    uint8_t  do_ref[2][4];
+};
+
+// everything one picture's kernels need; passed by value as a __grid_constant__ parameter
+struct PicJob {
+    SvtMePicParams pp;
+    DevPic         src;
+    DevPic         ref[2][4];
+    int            pic_w, pic_h, b64_cols, b64_rows, n_b64, n_pus;
+    int            fullpel_phase; // 0: all refs, 1: only (0,0), 2: all but (0,0)
+    int            hme_smem_bytes, fp_smem_bytes;
+    // device buffers
+    SbState       *sb_state;   // [n_b64]
+    uint32_t      *best_sad;   // [n_b64][2][4][85]
+    uint32_t      *best_mv;    // [n_b64][2][4][85]
+    SvtMeWindow   *windows;    // [n_b64][2][4]
+    SvtMeSearchResult *search_results; // [n_b64][2][4]
+    uint8_t       *total_me_candidate_index;
+    uint32_t      *me_mv_array;
+    uint8_t       *me_candidate_array;
+    uint32_t      *me_64x64_distortion, *me_32x32_distortion, *me_16x16_distortion, *me_8x8_distortion;
+    uint32_t      *rc_me_distortion, *me_8x8_cost_variance;
+    uint8_t       *stationary_block_present_sb, *rc_me_allow_gm;
+    unsigned long long *sad_ops; // [0] HME stage, [1] full-pel stage: algorithmic |a-b| operations
+};
+
+// ------------------------------------------------------------------------------------------
+// small helpers
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ int imin(int a, int b) { return a < b ? a : b; }
+__device__ __forceinline__ int imax(int a, int b) { return a > b ? a : b; }
+__device__ __forceinline__ int iabs(int a) { return a < 0 ? -a : a; }
+
+// 4 bytes starting at an arbitrary global address (two aligned loads + funnel shift). Reads at
+// most 3 bytes before and 4..7 bytes after p: callers stay inside the slab slack.
+__device__ __forceinline__ uint32_t ldg_u32_unaligned(const uint8_t *p) {
+    const uintptr_t a  = (uintptr_t)p;
+    const uint32_t *q  = (const uint32_t *)(a & ~(uintptr_t)3);
+    const uint32_t  lo = __ldg(q), hi = __ldg(q + 1);
+    return __funnelshift_r(lo, hi, (uint32_t)(a & 3) * 8);
+}
+
+// acc[p] += SAD of the 16-byte strip s[0..3] against the strip starting p bytes into w[0..5]
+// for the 8 consecutive search positions p = 0..7. 32 VABSDIFF4.U8.ACC + 24 SHF.
+__device__ __forceinline__ void strip16_sad8(const uint32_t (&w)[6], const uint32_t (&s)[4], uint32_t (&acc)[8]) {
+#pragma unroll
+    for (int p = 0; p < 8; p++) {
+        const int o = p >> 2, sh = (p & 3) * 8;
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const uint32_t v = sh ? __funnelshift_r(w[o + k], w[o + k + 1], sh) : w[o + k];
+            acc[p] += __vsadu4(v, s[k]);
+        }
+    }
+}
+
+// same, but the strip is split into its left and right 8 pixels (two 8x8 blocks side by side)
+__device__ __forceinline__ void strip16_sad8_split(const uint32_t (&w)[6], const uint32_t (&s)[4],
+                                                   uint32_t (&accl)[8], uint32_t (&accr)[8]) {
+#pragma unroll
+    for (int p = 0; p < 8; p++) {
+        const int o = p >> 2, sh = (p & 3) * 8;
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const uint32_t v = sh ? __funnelshift_r(w[o + k], w[o + k + 1], sh) : w[o + k];
+            if (k < 2)
+                accl[p] += __vsadu4(v, s[k]);
+            else
+                accr[p] += __vsadu4(v, s[k]);
+        }
+    }
+}
+
+// byte mask keeping the first n (0..4) bytes of a little-endian word
+__device__ __forceinline__ uint32_t lo_bytes_mask(int n) {
+    return n <= 0 ? 0u : (n >= 4 ? 0xFFFFFFFFu : ((1u << (8 * n)) - 1u));
+}
+
+// Stage a rectangle of bytes from global memory (arbitrary alignment) into shared memory whose
+// rows are 4-byte aligned: smem word (r, c) = global bytes [g + r*gstride + 4c, +4).
+__device__ __forceinline__ void stage_rect(uint32_t *smem, int smem_stride_words, const uint8_t *g, int gstride,
+                                           int rows, int words_per_row, int tid, int nthreads) {
+    const int total = rows * words_per_row;
+    for (int i = tid; i < total; i += nthreads) {
+        const int r = i / words_per_row, c = i - r * words_per_row;
+        smem[r * smem_stride_words + c] = ldg_u32_unaligned(g + (size_t)r * gstride + 4 * c);
+    }
+}
+
+// svt_aom_get_scaled_picture_distance, motion_estimation.c:1239-1243
+__device__ __forceinline__ uint16_t scaled_picture_distance(uint16_t dist) {
+    const uint8_t round_up = ((dist % 8) == 0) ? 0 : 1;
+    return (uint16_t)(((dist * 5) / 8) + round_up);
+}
+
+// |poc - ref_poc| as get_me_reference computes it, motion_estimation.c:1232-1234
+__device__ __forceinline__ uint16_t ref_distance(const SvtMePicParams &pp, int l, int r) {
+    long long d = (long long)pp.picture_number - (long long)pp.ref_picture_number[l][r];
+    if (d < 0) d = -d;
+    return (uint16_t)(int16_t)d;
+}
+
+// The edge correction every search stage applies to one axis, in int16 like the reference
+// (motion_estimation.c:848-880, 949-982, 1050-1078, 1481-1500, 1542-1560, 1655-1699). The left/top
+// branch moves the origin first, so the size correction that follows it subtracts zero.
+__device__ __forceinline__ void clamp_axis(int16_t org, int16_t &origin, int16_t &size, int16_t pad, int16_t dim) {
+    if ((org + origin) < -pad) {
+        origin = (int16_t)(-pad - org);
+        size   = (int16_t)(size - (-pad - (org + origin)));
+    }
+    if ((org + origin) > dim - 1) origin = (int16_t)(origin - ((org + origin) - (dim - 1)));
+    if ((org + origin + size) > dim) size = (int16_t)imax(1, size - ((org + origin + size) - dim));
+}

@@ -1,0 +1,98 @@
+"""-m gpu: the CUDA picture pipeline (through the C ABI) against the oracle, bit-exact."""
+import numpy as np
+import pytest
+
+import svtme_b200 as me
+from oracle import pyoracle as po
+from util import (CASES, EXTRA, case_id, case_inputs, compare, compare_hme_state, extra_inputs, gpu_me, orc_me,
+                  params_from_encoder_inputs)
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module", autouse=True)
+def _built(orc):
+    me.lib()  # fails loudly if the CUDA library is missing
+
+
+def planes_oracle(luma):
+    h, w = luma.shape
+    full = np.zeros((h + 144, w + 144), np.uint8)
+    quarter = np.zeros((h // 2 + 64, w // 2 + 64), np.uint8)
+    sixteenth = np.zeros((h // 4 + 32, w // 4 + 32), np.uint8)
+    po.oracle_lib().orc_build_planes(po.ptr(np.ascontiguousarray(luma)), w, h, po.ptr(full), po.ptr(quarter), po.ptr(sixteenth))
+    return full, quarter, sixteenth
+
+
+@pytest.mark.parametrize("w,h", [(320, 192), (200, 72), (1920, 1080), (88, 72)])
+def test_pyramid_matches_oracle(w, h):
+    rng = np.random.default_rng(w * 7 + h)
+    luma = rng.integers(0, 256, (h, w), dtype=np.uint8)
+    s = me.Session(w, h, max_pictures=2)
+    s.upload(1, luma)
+    for lvl, want in enumerate(planes_oracle(luma)):
+        got = s.download_plane(1, lvl)
+        np.testing.assert_array_equal(got, want, err_msg="level %d" % lvl)
+    s.close()
+
+
+def test_pyramid_10bit_upload():
+    rng = np.random.default_rng(3)
+    w, h = 320, 192
+    luma10 = rng.integers(0, 1024, (h, w), dtype=np.uint16)
+    s = me.Session(w, h, max_pictures=2)
+    s.upload(0, luma10)
+    want = planes_oracle((luma10 >> 2).astype(np.uint8))
+    for lvl in range(3):
+        np.testing.assert_array_equal(s.download_plane(0, lvl), want[lvl])
+    s.close()
+
+
+@pytest.mark.parametrize("case", CASES, ids=case_id)
+def test_picture_me_matches_oracle(case):
+    src, refs, pocs, poc, enc_mode, kw = case_inputs(case)
+    params = params_from_encoder_inputs(src, refs, pocs, poc, enc_mode, **kw)
+    want, dbg, ops = orc_me(src, refs, params)
+    got, st = gpu_me(src, refs, params)
+    compare_hme_state(st, dbg, params)
+    compare(want, got, fields=list(got.FIELDS))
+    assert got.sad_ops == ops  # the device's own count of the algorithmic work equals the oracle's
+
+
+@pytest.mark.parametrize("name,geo,kw", EXTRA, ids=[e[0] for e in EXTRA])
+def test_picture_me_variants(name, geo, kw):
+    src, refs, pocs, poc, enc_mode, kw = extra_inputs(geo, kw)
+    params = params_from_encoder_inputs(src, refs, pocs, poc, enc_mode, **kw)
+    want, dbg, _ = orc_me(src, refs, params)
+    got, st = gpu_me(src, refs, params)
+    compare_hme_state(st, dbg, params)
+    compare(want, got, fields=list(got.FIELDS))
+
+
+@pytest.mark.parametrize("enc_mode", [4, 8, -2])
+def test_uncorrelated_and_flat_references(enc_mode):
+    rng = np.random.default_rng(5)
+    w, h = 256, 192
+    src = rng.integers(0, 256, (h, w), dtype=np.uint8)
+    flat = np.full((h, w), 77, np.uint8)  # every SAD ties: the first raster position must win
+    refs = [[rng.integers(0, 256, (h, w), dtype=np.uint8), flat, src.copy()], [flat, np.roll(src, (3, -5), (0, 1))]]
+    params = params_from_encoder_inputs(src, refs, [[2, 0, 1], [8, 6]], 4, enc_mode, temporal_layer=2)
+    want, dbg, _ = orc_me(src, refs, params)
+    got, st = gpu_me(src, refs, params)
+    compare_hme_state(st, dbg, params)
+    compare(want, got, fields=list(got.FIELDS))
+
+
+def test_session_rejects_bad_arguments():
+    s = me.Session(320, 192, max_pictures=2)
+    src = np.zeros((192, 320), np.uint8)
+    params = params_from_encoder_inputs(src, [[src], []], [[0], []], 1, 8)
+    with pytest.raises(me.binding.SvtMeError):
+        s.me(0, params)  # nothing uploaded
+    s.upload(0, src)
+    params.ref_pic_id[0][0] = 1
+    with pytest.raises(me.binding.SvtMeError):
+        s.me(0, params)  # reference picture 1 not uploaded
+    with pytest.raises(me.binding.SvtMeError):
+        me.Session(321, 192)  # width not a multiple of 8
+    s.close()
