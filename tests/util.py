@@ -26,7 +26,7 @@ CASES = [
 EXTRA = [
     ("sc_M4", dict(w=320, h=192, enc_mode=4, tl=1, poc=16, l0=[0, 8], l1=[32, 24]), dict(sc_class1=1)),
     ("sc_M9", dict(w=320, h=192, enc_mode=9, tl=2, poc=6, l0=[4, 0], l1=[8, 16]), dict(sc_class1=1)),
-    ("rtc_M9", dict(w=320, h=192, enc_mode=9, tl=1, poc=6, l0=[5, 4, 2], l1=[3, 1]), dict(pred_structure=1, hier_levels=2)),
+    ("rtc_M9", dict(w=320, h=192, enc_mode=9, tl=1, poc=6, l0=[5, 4], l1=[3, 1]), dict(pred_structure=1, hier_levels=2)),
     ("rtc_sc_M10", dict(w=320, h=192, enc_mode=10, tl=0, poc=6, l0=[5, 4], l1=[5, 4]), dict(pred_structure=1, sc_class1=1, hier_levels=2)),
     ("rtc_M12", dict(w=320, h=192, enc_mode=12, tl=1, poc=6, l0=[5], l1=[4]), dict(pred_structure=1, hier_levels=2)),
     ("gm_M0", dict(w=320, h=192, enc_mode=0, tl=1, poc=8, l0=[0, 4, 2, 6], l1=[16, 12, 10]), dict()),
