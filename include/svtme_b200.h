@@ -235,6 +235,31 @@ void svtme_downsample_2d(uint8_t *input_samples, uint32_t input_stride, uint32_t
                          uint32_t input_area_height, uint8_t *decim_samples, uint32_t decim_stride,
                          uint32_t decim_step);
 
+/* No counterpart in the reference: the same search as svt_sad_loop_kernel, for callers that must
+   not allocate GPU memory. Some users of this library run where cudaMalloc is forbidden or too
+   costly: a real-time encoder thread (cudaMalloc locks the device and can stall other streams), a
+   plug-in inside a host application that has reserved all device memory for itself, or code
+   between cudaStreamBeginCapture and cudaStreamEndCapture. They keep their pictures in device
+   memory already, so every pointer here is a DEVICE pointer (src, ref, and the three outputs),
+   and the kernels are queued on `cuda_stream` (a cudaStream_t, NULL = default stream); the call
+   returns without waiting. The scratch the search needs between its two kernels lives in an 8 KB
+   array compiled into the library (no cudaMalloc, cudaFree or other allocating call is made).
+   Limits: block at most 16x16, ref_stride equal to src_stride_raw or twice it, search area at
+   most SVTME_NOALLOC_MAX_WIDTH wide and SVTME_NOALLOC_MAX_BANDS*32 rows; anything larger is
+   refused with SVTME_ERR_BAD_PARAMETER and a message on stderr. All calls share the one scratch
+   array: do not let two of them run on the GPU at the same time (other streams or threads). The
+   first call on a device fetches the array's address from the CUDA runtime; issue that first call
+   before starting any stream capture. Output semantics are those of svt_sad_loop_kernel:
+   *d_best_sad = 0xffffff and the centres untouched when no position was evaluated. */
+#define SVTME_NOALLOC_MAX_WIDTH 1024
+#define SVTME_NOALLOC_MAX_BANDS 1024
+uint32_t svtme_sad_loop_search_noalloc(const uint8_t *d_src, uint32_t src_stride, const uint8_t *d_ref,
+                                       uint32_t ref_stride, uint32_t block_height, uint32_t block_width,
+                                       uint64_t *d_best_sad, int16_t *d_x_search_center,
+                                       int16_t *d_y_search_center, uint32_t src_stride_raw,
+                                       uint8_t skip_search_line, int16_t search_area_width,
+                                       int16_t search_area_height, void *cuda_stream);
+
 /* Last error of the calling thread for the void-returning entry points above (SVTME_OK if none). */
 uint32_t svtme_last_error(void);
 
