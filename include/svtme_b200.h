@@ -353,6 +353,8 @@ typedef struct SvtMeHmeState {
     int16_t  hme_sc_x[2][4], hme_sc_y[2][4]; /* before me_prune_ref */
     uint64_t sr_hme_sad[2][4];
     uint8_t  do_ref[2][4];
+    uint8_t  performed_phme[2][4][2];
+    uint8_t  prehme_valid[2][4][2];
 } SvtMeHmeState;
 uint32_t svtme_fetch_hme_state(SvtMeSession *s, void *dst, size_t dst_bytes);
 

@@ -148,6 +148,7 @@ HME_STATE_DTYPE = np.dtype([
     ("prehme_mv_x", "<i2", (2, 4, 2)), ("prehme_mv_y", "<i2", (2, 4, 2)), ("prehme_sad", "<u8", (2, 4, 2)),
     ("zz_sad", "<u4", (2, 4)), ("reduce_me_sr_divisor", "<u4", (2, 4)),
     ("hme_sc_x", "<i2", (2, 4)), ("hme_sc_y", "<i2", (2, 4)), ("sr_hme_sad", "<u8", (2, 4)), ("do_ref", "u1", (2, 4)),
+    ("performed_phme", "u1", (2, 4, 2)), ("prehme_valid", "u1", (2, 4, 2)),
 ], align=True)
 
 

@@ -26,7 +26,7 @@
 static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 struct ResultLayout { // offsets into the device result slab
-    size_t best_sad, best_mv, search_results, windows, total, mv, cand, d64, d32, d16, d8, rc, var, stat, gm, sb_state, ops, end;
+    size_t best_sad, best_mv, search_results, windows, total, mv, cand, d64, d32, d16, d8, rc, var, stat, gm, sb_state, ops, hme_jobs, fp_jobs, fp_keys, fp_counters, end;
 };
 
 struct SvtMeSession {
@@ -41,6 +41,8 @@ struct SvtMeSession {
     uint8_t     *res_slab = nullptr;
     ResultLayout lay{};
     uint16_t    *d_in16 = nullptr;
+    uint32_t    *fp_units = nullptr;
+    uint32_t     fp_units_cap = 0;
     SvtMePicParams last_pp{};
     bool         have_results = false;
     uint64_t     launches = 0;
@@ -76,6 +78,10 @@ static void result_layout(ResultLayout &L, int n_b64) {
     L.stat = take((size_t)n_b64); L.gm = take((size_t)n_b64);
     L.sb_state = take((size_t)n_b64 * sizeof(SbState));
     L.ops = take(64);
+    L.hme_jobs    = take((size_t)n_b64 * HME_JOBS_PER_B64 * sizeof(HmeJobG));
+    L.fp_jobs     = take((size_t)n_b64 * 8 * sizeof(FpJobG));
+    L.fp_keys     = take((size_t)n_b64 * 8 * 85 * sizeof(unsigned long long));
+    L.fp_counters = take(64);
     L.end = o;
 }
 
@@ -137,6 +143,7 @@ extern "C" void svtme_session_destroy(SvtMeSession *s) {
     cudaFree(s->pic_slab);
     cudaFree(s->res_slab);
     if (s->d_in16) cudaFree(s->d_in16);
+    if (s->fp_units) cudaFree(s->fp_units);
     delete s;
 }
 
@@ -267,7 +274,15 @@ static uint32_t launch_me(SvtMeSession *s, int32_t pic_id, const SvtMePicParams 
         for (int r = 0; r < pp->num_of_ref_pic_to_search[l]; r++) job.ref[l][r] = s->pics[pp->ref_pic_id[l][r]];
     job.pic_w = s->w; job.pic_h = s->h; job.b64_cols = s->b64_cols; job.b64_rows = s->b64_rows; job.n_b64 = s->n_b64;
     job.n_pus = pp->enable_me_8x8 ? 85 : 21;
-    svtme_smem_plan(*pp, &job.hme_smem_bytes, &job.fp_smem_bytes);
+    const uint32_t need_units = svtme_fp_units_cap(*pp, s->n_b64);
+    if (need_units > s->fp_units_cap) { // the unit queue grows with the largest search window of the controls in use
+        CU_TRY(cudaStreamSynchronize(s->stream));
+        if (s->fp_units) cudaFree(s->fp_units);
+        s->fp_units = nullptr; s->fp_units_cap = 0;
+        cudaError_t e = cudaMalloc(&s->fp_units, (size_t)need_units * sizeof(uint32_t));
+        if (e != cudaSuccess) { fprintf(stderr, "[svtme_b200] cudaMalloc unit queue (%u units): %s\n", need_units, cudaGetErrorString(e)); return SVTME_ERR_INSUFFICIENT_RESOURCES; }
+        s->fp_units_cap = need_units;
+    }
     uint8_t *R = s->res_slab;
     job.sb_state       = (SbState *)(R + s->lay.sb_state);
     job.best_sad       = (uint32_t *)(R + s->lay.best_sad);
@@ -286,6 +301,12 @@ static uint32_t launch_me(SvtMeSession *s, int32_t pic_id, const SvtMePicParams 
     job.stationary_block_present_sb = R + s->lay.stat;
     job.rc_me_allow_gm              = R + s->lay.gm;
     job.sad_ops                     = (unsigned long long *)(R + s->lay.ops);
+    job.hme_jobs     = (HmeJobG *)(R + s->lay.hme_jobs);
+    job.fp_jobs      = (FpJobG *)(R + s->lay.fp_jobs);
+    job.fp_keys      = (unsigned long long *)(R + s->lay.fp_keys);
+    job.fp_counters  = (uint32_t *)(R + s->lay.fp_counters);
+    job.fp_units     = s->fp_units;
+    job.fp_units_cap = s->fp_units_cap;
     cudaEvent_t e0 = nullptr, e1 = nullptr, e2 = nullptr;
     if (s->timing) {
         if (s->ev_used + 3 > s->ev.size()) {

@@ -48,7 +48,35 @@ struct SbState {
     int16_t  hme_sc_x[2][4], hme_sc_y[2][4];
     uint64_t sr_hme_sad[2][4];
     uint8_t  do_ref[2][4];
+    uint8_t  performed_phme[2][4][2];
+    uint8_t  prehme_valid[2][4][2];
 };
+
+// One window search of the HME stage (pre-HME region or HME level-N quadrant), set up by k_hme_ctl
+// and executed by k_search16 / k_search_wide. 32 jobs per b64: slot = (list*4+ref)*4 + quadrant
+// (pre-HME uses quadrant 0/1 for its two regions).
+struct HmeJobG {
+    const uint8_t     *ref;  // window top-left sample in the reference plane
+    unsigned long long key;  // (sad << 32) | (y*sa_w + x), atomicMin over the job's tiles
+    int                ref_stride;
+    int16_t            sa_w, sa_h, origin_x, origin_y;
+    uint16_t           tile_w, tile_h; // positions per tile (tile_w multiple of 8)
+    uint8_t            n_tx, n_ty, active, pad_;
+};
+#define HME_JOBS_PER_B64 32
+#define HME_KEY_NONE ((0xffffffull << 32) | 0xffffffffull) /* best_sad = 0xffffff, nothing found */
+#define S16_WIN_WORDS 1152 /* per-warp staging buffer of k_search16: 4.5 KB */
+
+// Full-pel search of one (b64, list, ref), set up by k_fp_plan and executed by k_fp_search.
+struct FpJobG {
+    int16_t  xc, yc;             // search centre (variance-probe position, scan index 0)
+    int16_t  x_origin, y_origin; // window origin relative to the b64
+    int16_t  sa_w, sa_h;
+    uint16_t n_tx, n_ty;         // tiles of FP_TILE_W x FP_TILE_H positions
+    uint8_t  active, probe, pad_[2];
+};
+#define FP_TILE_W 8
+#define FP_TILE_H 16
 
 // everything one picture's kernels need; passed by value as a __grid_constant__ parameter
 struct PicJob {
@@ -71,6 +99,14 @@ struct PicJob {
     uint32_t      *rc_me_distortion, *me_8x8_cost_variance;
     uint8_t       *stationary_block_present_sb, *rc_me_allow_gm;
     unsigned long long *sad_ops; // [0] HME stage, [1] full-pel stage: algorithmic |a-b| operations
+    // v2 pipeline scratch
+    HmeJobG            *hme_jobs;  // [n_b64][HME_JOBS_PER_B64]
+    FpJobG             *fp_jobs;   // [n_b64][8]
+    unsigned long long *fp_keys;   // [n_b64][8][85]: (sad << 32) | global scan index (0 = probe)
+    uint32_t           *fp_units;  // unit queue: (job index << 16) | tile
+    uint32_t           *fp_counters; // [0] number of units, [1] queue head
+    uint32_t            fp_units_cap;
+    int                 s16_max_tiles; // grid bound of k_search16 for the current stage
 };
 
 // ------------------------------------------------------------------------------------------

@@ -2,8 +2,9 @@
 #include "me_launch.h"
 
 #include "me_device.cuh"
-#include "me_fullpel.cuh"
-#include "me_hme_kernel.cuh"
+#include "me_search.cuh"
+#include "me_ctl.cuh"
+#include "me_fp2.cuh"
 #include "me_post.cuh"
 
 // ------------------------------------------------------------------------------------------
@@ -92,62 +93,158 @@ int svtme_launch_downsample_generic(const uint8_t *d_in, int in_stride, int in_w
 }
 
 // ------------------------------------------------------------------------------------------
-// picture pipeline
+// picture pipeline (v2): flat warp-per-tile searches, control in k_hme_ctl between them
 // ------------------------------------------------------------------------------------------
-static bool g_attr_set = false;
+static int g_fp_search_ctas_per_sm = 0;
 
-void svtme_smem_plan(const SvtMePicParams &pp, int *hme_bytes, int *fp_bytes) {
+static inline int imax_h(int a, int b) { return a > b ? a : b; }
+static int next_pow2(int v) {
+    int p = 1;
+    while (p < v) p <<= 1;
+    return p;
+}
+
+uint32_t svtme_fp_units_cap(const SvtMePicParams &pp, int n_b64) {
     const SvtMeCtrls &c = pp.ctrls;
-    // HME staged searches: a window row is 8*ceil(sa_w/8) + 16 bytes, rows = sa_h + 2*(rows-1) <= sa_h + 30.
-    // Budget: fit the common windows whole, cap at 48 KB (larger windows are tiled in y).
-    size_t need = 16 * 1024;
-    auto   want = [&](int w, int h) {
-        const size_t row = (size_t)(((w + 7) & ~7) + 16);
-        const size_t b   = row * (size_t)(h + 31);
-        if (b > need) need = b;
-    };
-    if (c.prehme_enable)
-        for (int i = 0; i < 2; i++) want(c.prehme_sa_cfg[i].sa_max.width, c.prehme_sa_cfg[i].sa_max.height);
-    want(((c.hme_l0_sa.sa_max.width / 2 + 15) & ~15), c.hme_l0_sa.sa_max.height / 2);
-    if (need > 48 * 1024) need = 48 * 1024;
-    *hme_bytes = (int)((need + 15) & ~(size_t)15);
-    // full-pel: row = 8*ceil(sa_w/8) + 64 bytes, rows = sa_h + 63; widths can double (mv_based_sa_adj) and
-    // grow x1.5 (8x8 variance). Cap at 64 KB; bigger windows are tiled in y.
-    int mw = c.me_sa.sa_max.width, mh = c.me_sa.sa_max.height;
+    long long mw = c.me_sa.sa_max.width, mh = c.me_sa.sa_max.height;
     if (c.mv_sa_adj_enabled) { mw *= c.mv_sa_adj_sa_multiplier; mh *= c.mv_sa_adj_sa_multiplier; }
-    mw = ((mw * 3 / 2) + 7) & ~7;
+    mw = ((mw * 3 / 2) + 7) & ~7LL; // the 8x8-variance rule can grow the window by 3/2 (:1426-1429)
     mh = mh * 3 / 2;
-    size_t fp = (size_t)(mw + 64) * (size_t)(mh + 63);
-    const size_t fp_min = (size_t)(mw + 64) * 64; // one search row per tile at least
-    if (fp > 64 * 1024) fp = 64 * 1024;
-    if (fp < fp_min) fp = fp_min;
-    if (fp < 12 * 1024) fp = 12 * 1024;
-    *fp_bytes = (int)((fp + 15) & ~(size_t)15);
+    if (mw < 8) mw = 8;
+    if (mh < 3) mh = 3;
+    long long tiles = ((mw + FP_TILE_W - 1) / FP_TILE_W) * ((mh + FP_TILE_H - 1) / FP_TILE_H);
+    if (tiles > 65535) tiles = 65535;
+    long long cap = tiles * n_b64 * 8;
+    if (cap > 0x7fffffffLL) cap = 0x7fffffffLL;
+    return (uint32_t)cap;
 }
 
 int svtme_launch_picture_me(PicJob &job, cudaStream_t st, cudaEvent_t ev_hme0, cudaEvent_t ev_hme1, cudaEvent_t ev_fp1) {
-    if (!g_attr_set) {
-        cudaFuncSetAttribute(k_hme, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
-        cudaFuncSetAttribute(k_fullpel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
-        g_attr_set = true;
-    }
+    const SvtMePicParams &pp = job.pp;
+    const SvtMeCtrls     &c  = pp.ctrls;
     int launches = 0;
+    const bool sub = c.hme_search_method == SVTME_SUB_SAD_SEARCH;
+    const int  row_step = sub ? 2 : 1, rows0 = sub ? 8 : 16;
+    const uint32_t ALL = 0xffu, LIST0 = 0x0fu, LIST1 = 0xf0u;
+    const int ctl_grid = (job.n_b64 + CTL_WARPS - 1) / CTL_WARPS;
     if (ev_hme0) cudaEventRecord(ev_hme0, st);
-    k_hme<<<job.n_b64, HME_THREADS, job.hme_smem_bytes, st>>>(job);
-    launches++;
-    if (ev_hme1) cudaEventRecord(ev_hme1, st);
-    const dim3 fgrid(8, (unsigned)job.n_b64, 1);
-    if (job.pp.ctrls.enable_me_sr_adjustment == 2) {
-        // the window of every ref but (0,0) depends on p_sb_best_sad[0][0][0] (motion_estimation.c:1357-1366)
-        job.fullpel_phase = 1;
-        k_fullpel<<<fgrid, FP_THREADS, job.fp_smem_bytes, st>>>(job);
-        job.fullpel_phase = 2;
-        k_fullpel<<<fgrid, FP_THREADS, job.fp_smem_bytes, st>>>(job);
-        launches += 2;
-    } else {
-        job.fullpel_phase = 0;
-        k_fullpel<<<fgrid, FP_THREADS, job.fp_smem_bytes, st>>>(job);
+    cudaMemsetAsync(job.fp_counters, 0, 2 * sizeof(uint32_t), st);
+    if (c.me_early_exit_th || c.me_safe_limit_zz_th) {
+        k_zz<<<(job.n_b64 * 8 + SEARCH_WARPS - 1) / SEARCH_WARPS, 32 * SEARCH_WARPS, 0, st>>>(job);
         launches++;
+    }
+    bool first = true;
+    int  post = ST_NONE;
+    uint32_t pmask = 0;
+    auto emit = [&](int fin, int build, uint32_t bmask) {
+        CtlOp op;
+        op.init = first ? 1 : 0; op.post_stage = post; op.post_mask = pmask; op.finalize = fin; op.build_stage = build; op.build_mask = bmask;
+        k_hme_ctl<<<ctl_grid, 32 * CTL_WARPS, 0, st>>>(job, op);
+        launches++;
+        first = false;
+        post  = ST_NONE;
+    };
+    auto tiles_of = [&](int w, int h) {
+        int tw, th, ntx, nty;
+        s16_tile_geometry(w, h, rows0, row_step, &tw, &th, &ntx, &nty);
+        return ntx * nty < 1 ? 1 : ntx * nty;
+    };
+    auto search16 = [&](int max_tiles, int skip) {
+        job.s16_max_tiles = max_tiles;
+        const long long units = (long long)job.n_b64 * HME_JOBS_PER_B64 * max_tiles;
+        k_search16<<<(unsigned)((units + SEARCH_WARPS - 1) / SEARCH_WARPS), 32 * SEARCH_WARPS, 0, st>>>(job, skip);
+        launches++;
+    };
+    auto search_wide = [&](int level) {
+        const SvtMeSearchArea a = level == 1 ? c.hme_l1_sa : c.hme_l2_sa;
+        const int w = (a.width + 7) & ~7, strips = level == 1 ? 2 : 4;
+        const int tpj = next_pow2(imax_h(4, a.height * (w / 8) * strips));
+        const long long tasks = (long long)job.n_b64 * HME_JOBS_PER_B64 * tpj;
+        k_search_wide<<<(unsigned)((tasks + 32 * SEARCH_WARPS - 1) / (32 * SEARCH_WARPS)), 32 * SEARCH_WARPS, 0, st>>>(job, level, tpj);
+        launches++;
+    };
+    int fin_pending = ST_NONE;
+    if (c.prehme_enable) {
+        const int mt = imax_h(tiles_of(c.prehme_sa_cfg[0].sa_max.width, c.prehme_sa_cfg[0].sa_max.height),
+                              tiles_of(c.prehme_sa_cfg[1].sa_max.width, c.prehme_sa_cfg[1].sa_max.height));
+        const bool l1dep = c.prehme_l1_early_exit && pp.num_of_list_to_search == 2 && pp.temporal_layer_index > 0;
+        if (l1dep) {
+            emit(ST_NONE, ST_PREHME, LIST0);
+            search16(mt, c.prehme_skip_search_line);
+            post = ST_PREHME; pmask = LIST0;
+            emit(ST_NONE, ST_PREHME, LIST1);
+            search16(mt, c.prehme_skip_search_line);
+            post = ST_PREHME; pmask = LIST1;
+        } else {
+            emit(ST_NONE, ST_PREHME, ALL);
+            search16(mt, c.prehme_skip_search_line);
+            post = ST_PREHME; pmask = ALL;
+        }
+        fin_pending = ST_PREHME;
+    }
+    if (c.enable_hme_flag) {
+        if (c.enable_hme_level0_flag) {
+            const int qw = ((((c.hme_l0_sa.sa_max.width / 2) + 15) & ~15) + 7) & ~7;
+            const int mt = tiles_of(qw, c.hme_l0_sa.sa_max.height / 2);
+            const bool dep = c.enable_me_sr_adjustment && c.distance_based_hme_resizing && c.reduce_hme_l0_sr_th_min &&
+                c.reduce_hme_l0_sr_th_max;
+            if (dep) {
+                emit(fin_pending, ST_L0, 0x01u);
+                search16(mt, 0);
+                post = ST_L0; pmask = 0x01u;
+                emit(ST_NONE, ST_L0, ALL & ~0x01u);
+                search16(mt, 0);
+                post = ST_L0; pmask = ALL & ~0x01u;
+            } else {
+                emit(fin_pending, ST_L0, ALL);
+                search16(mt, 0);
+                post = ST_L0; pmask = ALL;
+            }
+            fin_pending = ST_NONE;
+        }
+        if (c.enable_hme_level1_flag) {
+            emit(fin_pending, ST_L1, ALL);
+            fin_pending = ST_NONE;
+            search_wide(1);
+            post = ST_L1; pmask = ALL;
+        }
+        if (c.enable_hme_level2_flag) {
+            emit(fin_pending, ST_L2, ALL);
+            fin_pending = ST_NONE;
+            search_wide(2);
+            post = ST_L2; pmask = ALL;
+        }
+    }
+    if (fin_pending == ST_PREHME) emit(ST_PREHME, ST_NONE, 0);
+    emit(ST_L2, ST_NONE, 0); // posts the last searches, then set_final_seach_centre_sb + pruning
+    if (ev_hme1) cudaEventRecord(ev_hme1, st);
+
+    // ---- full-pel ----
+    if (!g_fp_search_ctas_per_sm) {
+        int n = 0;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_fp_search, 32 * FP_WARPS, 0);
+        g_fp_search_ctas_per_sm = n > 0 ? n : 1;
+    }
+    int n_sm = 148;
+    {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
+    }
+    const int plan_grid = (job.n_b64 * 8 + FP_WARPS - 1) / FP_WARPS;
+    const int search_grid = n_sm * g_fp_search_ctas_per_sm;
+    if (c.enable_me_sr_adjustment == 2) {
+        // the window of every ref but (0,0) depends on p_sb_best_sad[0][0][0] (motion_estimation.c:1357-1366)
+        k_fp_plan<<<plan_grid, 32 * FP_WARPS, 0, st>>>(job, 1);
+        k_fp_search<<<search_grid, 32 * FP_WARPS, 0, st>>>(job);
+        cudaMemsetAsync(job.fp_counters, 0, 2 * sizeof(uint32_t), st);
+        k_fp_plan<<<plan_grid, 32 * FP_WARPS, 0, st>>>(job, 2);
+        k_fp_search<<<search_grid, 32 * FP_WARPS, 0, st>>>(job);
+        launches += 4;
+    } else {
+        k_fp_plan<<<plan_grid, 32 * FP_WARPS, 0, st>>>(job, 0);
+        k_fp_search<<<search_grid, 32 * FP_WARPS, 0, st>>>(job);
+        launches += 2;
     }
     if (ev_fp1) cudaEventRecord(ev_fp1, st);
     k_post<<<job.n_b64, POST_THREADS, 0, st>>>(job);
@@ -157,15 +254,15 @@ int svtme_launch_picture_me(PicJob &job, cudaStream_t st, cudaEvent_t ev_hme0, c
 }
 
 // ------------------------------------------------------------------------------------------
-// RTCD-signature kernels (known-answer path)
+// RTCD-signature kernels (known-answer path): thin wrappers around the same warp-level routines
 // ------------------------------------------------------------------------------------------
 
 // svt_sad_loop_kernel semantics for ANY block shape: one thread per search position, byte loads.
-// Used by the C-ABI wrapper when the shape is outside what the staged strip search covers.
+// Only used for blocks wider than 64 pixels, which the encoder never passes.
 __global__ void k_kat_sad_loop_generic(const uint8_t *src, int src_stride, const uint8_t *ref, int ref_stride, int bh,
                                        int bw, int src_stride_raw, int skip, int sa_w, int sa_h,
                                        unsigned long long *out_key) {
-    unsigned long long best = HME_KEY_INIT;
+    unsigned long long best = HME_KEY_NONE;
     const bool sk = skip && bw == 16 && bh <= 16;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < sa_w * sa_h; i += gridDim.x * blockDim.x) {
         const int y = i / sa_w, x = i - y * sa_w;
@@ -180,106 +277,101 @@ __global__ void k_kat_sad_loop_generic(const uint8_t *src, int src_stride, const
         const unsigned long long k = ((unsigned long long)sad << 32) | (uint32_t)i;
         if (sad < 0xffffff && k < best) best = k;
     }
-    if (best != HME_KEY_INIT) atomicMin(out_key, best);
+    if (best != HME_KEY_NONE) atomicMin(out_key, best);
 }
 
-// svt_sad_loop_kernel through the production staged search (block <= 16 wide) or the direct
-// strip search (17..64 wide); one CTA.
-__global__ void __launch_bounds__(HME_THREADS) k_kat_sad_loop(const uint8_t *src, int src_stride, const uint8_t *ref,
-                                                               int ref_stride, int bh, int bw, int src_stride_raw,
-                                                               int skip, int sa_w, int sa_h, int win_bytes,
-                                                               unsigned long long *out_key) {
-    extern __shared__ __align__(16) uint32_t kat_win[];
-    __shared__ __align__(16) HmeSh sh;
-    const int tid = threadIdx.x;
-    const int strips = (bw + 15) >> 4;
-    // the reference advances the ref row by src_stride_raw per search row and by ref_stride per
-    // block row; the production searches need ref_stride == row_step * src_stride_raw
-    const int row_step = ref_stride / src_stride_raw;
-    if (tid == 0) {
-        HmeJob &j = sh.jobs[0];
-        j.ref = ref; j.ref_stride = src_stride_raw; j.sa_w = sa_w; j.sa_h = sa_h; j.origin_x = j.origin_y = 0;
-        sh.job_key[0] = HME_KEY_INIT;
-        sh.n_jobs = 1;
-        sh.task_prefix[0] = 0;
-        sh.task_prefix[1] = sa_h * ((sa_w + 7) >> 3) * (strips == 3 ? 4 : strips);
+// blocks up to 16x16: the staged tile search of k_search16, one warp per tile
+__global__ void __launch_bounds__(32 * SEARCH_WARPS) k_kat_search16(const uint8_t *src, int src_stride, const uint8_t *ref,
+                                                                     int raw_stride, int row_step, int bh, int bw, int skip,
+                                                                     int sa_w, int sa_h, int tile_w, int tile_h, int n_tx,
+                                                                     int n_ty, unsigned long long *out_key) {
+    __shared__ __align__(16) uint32_t s_win[SEARCH_WARPS][S16_WIN_WORDS];
+    __shared__ __align__(16) uint32_t s_src[SEARCH_WARPS][16 * 4];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int tile = blockIdx.x * SEARCH_WARPS + warp;
+    if (tile >= n_tx * n_ty) return;
+    warp_stage_src(s_src[warp], 4, src, src_stride, 1, bh, bw);
+    const int ty = tile / n_tx, tx = tile - ty * n_tx;
+    const int x0 = tx * tile_w, y0 = ty * tile_h;
+    const unsigned long long key = warp_search16_tile(s_win[warp], s_src[warp], ref, raw_stride, sa_w, x0, y0,
+                                                     imin(tile_w, sa_w - x0), imin(tile_h, sa_h - y0), bw, bh, row_step,
+                                                     skip && bw == 16 && bh <= 16);
+    if (lane == 0 && key != HME_KEY_NONE) atomicMin(out_key, key);
+}
+
+// blocks up to 64 wide, any height: the global-memory strip search of k_search_wide
+__global__ void __launch_bounds__(32 * SEARCH_WARPS) k_kat_search_wide(const uint8_t *src, int src_stride, const uint8_t *ref,
+                                                                        int raw_stride, int ref_stride, int bh, int bw, int sa_w,
+                                                                        int sa_h, int strips, unsigned long long *out_key) {
+    const int t = (blockIdx.x * SEARCH_WARPS + (threadIdx.x >> 5)) * 32 + (threadIdx.x & 31);
+    const int n_oct = (sa_w + 7) >> 3;
+    const int strip = t % strips, oy = t / strips;
+    const int y = oy / n_oct, oct = oy - y * n_oct;
+    const bool active = y < sa_h;
+    uint32_t acc[8];
+    warp_search_wide_task(active, ref, raw_stride, ref_stride, src, src_stride, bw, bh, y, oct, strip, strips, acc);
+    if (active && strip == 0) {
+        const unsigned long long key = octet_best_key(acc, y, oct, sa_w);
+        if ((uint32_t)key != 0xffffffffu) atomicMin(out_key, key);
     }
-    uint32_t *srcw = strips == 1 ? sh.src16 : (strips == 2 ? sh.src4 : sh.src1);
-    const int words = strips == 1 ? 4 : (strips == 2 ? 8 : 16);
-    hme_stage_src(srcw, words, src, src_stride, 1, bh, bw, tid);
-    __syncthreads();
-    if (strips == 1)
-        hme_search_staged(sh, sh.jobs[0], 0, kat_win, win_bytes / 4, sh.src16, bw, bh, row_step, skip && bw == 16 && bh <= 16);
-    else
-        hme_search_direct(sh, srcw, strips == 2 ? 2 : 4, bw, bh, row_step);
-    __syncthreads();
-    if (tid == 0) *out_key = sh.job_key[0];
 }
 
 int svtme_launch_kat_sad_loop(const uint8_t *d_src, int src_stride, const uint8_t *d_ref, int ref_stride, int bh, int bw,
                               int src_stride_raw, int skip, int sa_w, int sa_h, unsigned long long *d_key,
                               cudaStream_t st) {
-    const bool fast = bw >= 1 && bw <= 64 && bh >= 1 && bh <= (bw <= 16 ? 16 : (bw <= 32 ? 32 : 64)) && src_stride_raw > 0 &&
-        (ref_stride == src_stride_raw || ref_stride == 2 * src_stride_raw) && sa_w > 0 && sa_h > 0;
-    if (fast) {
-        const int win_bytes = 48 * 1024;
-        if (!g_attr_set) {
-            cudaFuncSetAttribute(k_hme, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
-            cudaFuncSetAttribute(k_fullpel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
-            g_attr_set = true;
-        }
-        static bool kat_attr = false;
-        if (!kat_attr) {
-            cudaFuncSetAttribute(k_kat_sad_loop, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
-            kat_attr = true;
-        }
-        k_kat_sad_loop<<<1, HME_THREADS, win_bytes, st>>>(d_src, src_stride, d_ref, ref_stride, bh, bw, src_stride_raw, skip,
-                                                         sa_w, sa_h, win_bytes, d_key);
+    const unsigned long long init = HME_KEY_NONE;
+    cudaMemcpyAsync(d_key, &init, sizeof(init), cudaMemcpyHostToDevice, st);
+    if (sa_w <= 0 || sa_h <= 0) return 0;
+    const bool strided = src_stride_raw > 0 && (ref_stride == src_stride_raw || ref_stride == 2 * src_stride_raw);
+    if (strided && bw <= 16 && bh <= 16) {
+        const int row_step = ref_stride / src_stride_raw;
+        int tw, th, ntx, nty;
+        s16_tile_geometry(sa_w, sa_h, bh, row_step, &tw, &th, &ntx, &nty);
+        k_kat_search16<<<(ntx * nty + SEARCH_WARPS - 1) / SEARCH_WARPS, 32 * SEARCH_WARPS, 0, st>>>(
+            d_src, src_stride, d_ref, src_stride_raw, row_step, bh, bw, skip, sa_w, sa_h, tw, th, ntx, nty, d_key);
+    } else if (bw <= 64) {
+        // block rows advance by ref_stride, search rows by src_stride_raw: pass them separately
+        const int strips = bw <= 16 ? 1 : (bw <= 32 ? 2 : 4);
+        const int tasks = sa_h * ((sa_w + 7) / 8) * strips;
+        k_kat_search_wide<<<(tasks + 32 * SEARCH_WARPS - 1) / (32 * SEARCH_WARPS), 32 * SEARCH_WARPS, 0, st>>>(
+            d_src, src_stride, d_ref, src_stride_raw, ref_stride, bh, bw, sa_w, sa_h, strips, d_key);
     } else {
-        const unsigned long long init = HME_KEY_INIT;
-        cudaMemcpyAsync(d_key, &init, sizeof(init), cudaMemcpyHostToDevice, st);
-        if (sa_w > 0 && sa_h > 0) {
-            const int n = sa_w * sa_h;
-            k_kat_sad_loop_generic<<<(n + 127) / 128, 128, 0, st>>>(d_src, src_stride, d_ref, ref_stride, bh, bw,
-                                                                      src_stride_raw, skip, sa_w, sa_h, d_key);
-        }
+        const int n = sa_w * sa_h;
+        k_kat_sad_loop_generic<<<(n + 127) / 128, 128, 0, st>>>(d_src, src_stride, d_ref, ref_stride, bh, bw, src_stride_raw,
+                                                                  skip, sa_w, sa_h, d_key);
     }
     return 1;
 }
 
-// svt_ext_all_sad_calculation_8x8_16x16 + svt_ext_eight_sad_calculation_32x32_64x64 for ONE group of
-// 8 positions, through the production tile routine. d_ref points at position 0; rows: ref_stride.
-// out: sad8[64][8] (z-order), sad16[16][8], sad32[4][8], sad64[8] (un-updated raw SADs, doubled when
-// sub_sad) computed with single-position windows so that every position is observable.
-__global__ void __launch_bounds__(FP_THREADS) k_kat_octet(const uint8_t *src, int src_stride, const uint8_t *ref,
-                                                           int ref_stride, int sub, int n_pos, uint32_t *out /*[8][85]*/) {
-    extern __shared__ __align__(16) uint32_t kat_fp_win[];
-    __shared__ __align__(16) FpSh sh;
-    const int tid = threadIdx.x;
-    for (int i = tid; i < 64 * 16; i += FP_THREADS)
-        sh.src[i] = ldg_u32_unaligned(src + (size_t)(i >> 4) * src_stride + 4 * (i & 15));
-    const int stride = 2 + 16;
+// svt_ext_all_sad_calculation_8x8_16x16 / svt_ext_sad_calculation_8x8_16x16: raw SADs of all 85 PUs at
+// n_pos consecutive horizontal positions, through the tile routine of k_fp_search (one warp).
+__global__ void __launch_bounds__(32) k_kat_octet(const uint8_t *src, int src_stride, const uint8_t *ref, int ref_stride,
+                                                  int sub, int n_pos, uint32_t *out /*[n_pos][85]*/) {
+    __shared__ __align__(16) uint32_t s_src[64 * 16];
+    __shared__ __align__(16) uint32_t s_win[64 * FP_WIN_STRIDE];
+    const int lane = threadIdx.x;
+    warp_stage_src64(s_src, src, src_stride, sub ? 2 : 1);
     for (int p = 0; p < n_pos; p++) {
-        for (int i = tid; i < 85; i += FP_THREADS) sh.gkey[i] = ~0ull;
-        __syncthreads();
-        stage_rect(kat_fp_win, stride, ref + p, ref_stride, 64, stride, tid, FP_THREADS);
-        __syncthreads();
-        fp_search_tile(sh, kat_fp_win, stride, 1, 1, sub != 0, sub ? 13 : 12, 0u);
-        __syncthreads();
-        for (int i = tid; i < 85; i += FP_THREADS) out[p * 85 + i] = (uint32_t)(sh.gkey[i] >> 32) << (sub ? 1 : 0);
-        __syncthreads();
+        __syncwarp();
+        stage_rect(s_win, FP_WIN_STRIDE, ref + p, ref_stride, 64, FP_WIN_STRIDE, lane, 32);
+        __syncwarp();
+        FpKeys K;
+        warp_fp_tile(s_win, s_src, 1, 1, sub != 0, K);
+        fp_for_each_key(K, [&](uint32_t m, int pu) {
+            if (lane < 4) out[p * 85 + pu] = (m >> FP_IDX_BITS) << (sub ? 1 : 0);
+        });
     }
 }
 
 int svtme_launch_kat_octet(const uint8_t *d_src, int src_stride, const uint8_t *d_ref, int ref_stride, int sub, int n_pos,
                            uint32_t *d_out, cudaStream_t st) {
-    k_kat_octet<<<1, FP_THREADS, 64 * 18 * 4, st>>>(d_src, src_stride, d_ref, ref_stride, sub, n_pos, d_out);
+    k_kat_octet<<<1, 32, 0, st>>>(d_src, src_stride, d_ref, ref_stride, sub, n_pos, d_out);
     return 1;
 }
 
 __global__ void k_kat_nxm(const uint8_t *src, int src_stride, const uint8_t *ref, int ref_stride, int h, int w,
                           uint32_t *out) {
-    const uint32_t s = warp_nxm_sad(src, src_stride, ref, ref_stride, h, w);
+    const uint32_t s = warp_nxm_sad2(src, src_stride, ref, ref_stride, h, w);
     if (threadIdx.x == 0) *out = s;
 }
 int svtme_launch_kat_nxm(const uint8_t *d_src, int src_stride, const uint8_t *d_ref, int ref_stride, int h, int w,

@@ -37,6 +37,34 @@ __global__ void __launch_bounds__(POST_THREADS) k_post(const __grid_constant__ P
     const uint8_t *nref = pp.num_of_ref_pic_to_search;
     const int n_lists_cfg = pp.num_of_list_to_search;
 
+    // ---- full-pel keys -> p_sb_best_sad / p_sb_best_mv (me_context.h:395-396) ----
+    if (job.fp_keys) {
+        const bool sub = c.me_search_method == SVTME_SUB_SAD_SEARCH;
+        for (int i = tid; i < 8 * 85; i += POST_THREADS) {
+            const int lr = i / 85, pu = i - lr * 85;
+            const FpJobG &fj = job.fp_jobs[(size_t)b * 8 + lr];
+            if (!fj.active) continue; // not searched: the mirrors keep stale data, as in the reference
+            const unsigned long long k = job.fp_keys[((size_t)b * 8 + lr) * 85 + pu];
+            uint32_t sad = MAX_SAD_VALUE_U32, mv = 0; // initial bests, :1368 and :3119
+            if (k != ~0ull) {
+                sad = (uint32_t)(k >> 32) << (sub ? 1 : 0);
+                const uint32_t gi = (uint32_t)k;
+                int16_t mx, my;
+                if (gi == 0) { // the variance probe at the search centre
+                    mx = fj.xc;
+                    my = fj.yc;
+                } else {
+                    mx = (int16_t)((int32_t)((gi - 1) % (uint32_t)fj.sa_w) + fj.x_origin);
+                    my = (int16_t)((int32_t)((gi - 1) / (uint32_t)fj.sa_w) + fj.y_origin);
+                }
+                mv = ((uint32_t)(uint16_t)my << 16) | (uint16_t)mx;
+            }
+            job.best_sad[((size_t)b * 8 + lr) * 85 + pu] = sad;
+            job.best_mv[((size_t)b * 8 + lr) * 85 + pu]  = mv;
+        }
+        __syncthreads();
+    }
+
     // ---- me_prune_ref ----
     if (tid < 8) {
         const int l = tid >> 2, r = tid & 3;
