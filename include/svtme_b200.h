@@ -302,6 +302,17 @@ uint32_t svtme_picture_upload_device(SvtMeSession *s, int32_t pic_id, const uint
 uint32_t svtme_picture_me(SvtMeSession *s, int32_t pic_id, const SvtMePicParams *params,
                           SvtMePicResults *results, int sync);
 
+/* The same for n pictures at once: every kernel of the stage is launched once for the whole batch
+   (grid.y = picture), which is how a mini-GOP is meant to be submitted — Picture Decision releases
+   all pictures of a mini-GOP together (pd_process.c:4373-4400) and open-loop ME pictures do not
+   depend on each other. pic_ids[i] / params[i] / results[i] belong to picture i (results may be NULL).
+   All pictures of a batch must share the HME stage structure (same enable_hme_* flags, pre-HME on/off,
+   search methods), which holds inside one encode. */
+uint32_t svtme_picture_me_batch(SvtMeSession *s, uint32_t n, const int32_t *pic_ids, const SvtMePicParams *params,
+                                SvtMePicResults *results, int sync);
+/* Copy the device results of picture `index` of the last batch. */
+uint32_t svtme_fetch_results_batch(SvtMeSession *s, uint32_t index, SvtMePicResults *results, int sync);
+
 /* Same, but results stay on the device (pointers returned via svtme_device_results). Used to
    time the kernels with inputs and outputs resident in HBM. */
 uint32_t svtme_picture_me_device(SvtMeSession *s, int32_t pic_id, const SvtMePicParams *params);

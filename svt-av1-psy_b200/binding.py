@@ -64,6 +64,11 @@ def lib():
         L.svtme_session_kernel_time.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_double),
                                                 C.POINTER(C.c_double), C.POINTER(C.c_uint64)]
         L.svtme_session_kernel_time.restype = C.c_uint32
+        L.svtme_picture_me_batch.argtypes = [C.c_void_p, C.c_uint32, C.POINTER(C.c_int32), C.POINTER(abi.MePicParams),
+                                             C.POINTER(abi.MePicResults), C.c_int]
+        L.svtme_picture_me_batch.restype = C.c_uint32
+        L.svtme_fetch_results_batch.argtypes = [C.c_void_p, C.c_uint32, C.POINTER(abi.MePicResults), C.c_int]
+        L.svtme_fetch_results_batch.restype = C.c_uint32
         L.svtme_session_enable_timing.argtypes = [C.c_void_p, C.c_int]
         L.svtme_session_enable_timing.restype = C.c_uint32
         L.svtme_fetch_hme_state.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t]
@@ -159,6 +164,21 @@ class Session:
         results = results if results is not None else abi.PicResultArrays(self.width, self.height, params)
         _check(lib().svtme_picture_me(self._h, pic_id, C.byref(params), C.byref(results.struct), 1 if sync else 0),
                "svtme_picture_me")
+        return results
+
+    def me_batch(self, pic_ids, params_list, results_list=None, sync=True):
+        """ME of several pictures in one launch sequence. results_list: PicResultArrays per picture or None."""
+        n = len(pic_ids)
+        ids = (C.c_int32 * n)(*pic_ids)
+        prm = (abi.MePicParams * n)(*params_list)
+        res = None
+        if results_list is not None:
+            res = (abi.MePicResults * n)(*[r.struct for r in results_list])
+        _check(lib().svtme_picture_me_batch(self._h, n, ids, prm, res, 1 if sync else 0), "svtme_picture_me_batch")
+        return results_list
+
+    def fetch_batch(self, index, results, sync=True):
+        _check(lib().svtme_fetch_results_batch(self._h, index, C.byref(results.struct), 1 if sync else 0), "svtme_fetch_results_batch")
         return results
 
     def me_device(self, pic_id, params):

@@ -38,10 +38,14 @@ struct SvtMeSession {
     size_t       pic_bytes = 0;
     std::vector<DevPic> pics;
     std::vector<char>   pic_valid;
-    uint8_t     *res_slab = nullptr;
+    std::vector<uint8_t *> res_slabs; // one result/scratch slab per picture of a batch
+    uint8_t     *res_slab = nullptr;  // == res_slabs[0]: also holds the counters shared by a batch
+    PicJob      *d_jobs = nullptr;
+    std::vector<PicJob> h_jobs;
+    std::vector<SvtMePicParams> last_pps;
     ResultLayout lay{};
     uint16_t    *d_in16 = nullptr;
-    uint32_t    *fp_units = nullptr;
+    uint2       *fp_units = nullptr;
     uint32_t     fp_units_cap = 0;
     SvtMePicParams last_pp{};
     bool         have_results = false;
@@ -127,6 +131,9 @@ extern "C" uint32_t svtme_session_create(SvtMeSession **out, int device, uint32_
     e = cudaMalloc(&s->res_slab, s->lay.end);
     if (e != cudaSuccess) { cudaFree(s->pic_slab); delete s; return SVTME_ERR_INSUFFICIENT_RESOURCES; }
     cudaMemset(s->res_slab, 0, s->lay.end);
+    s->res_slabs.push_back(s->res_slab);
+    e = cudaMalloc(&s->d_jobs, sizeof(PicJob));
+    if (e != cudaSuccess) { cudaFree(s->pic_slab); cudaFree(s->res_slab); delete s; return SVTME_ERR_INSUFFICIENT_RESOURCES; }
     CU_TRY(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
     s->own_stream = true;
     CU_TRY(cudaDeviceSynchronize());
@@ -141,7 +148,8 @@ extern "C" void svtme_session_destroy(SvtMeSession *s) {
     for (auto &e : s->ev) cudaEventDestroy(e);
     if (s->own_stream) cudaStreamDestroy(s->stream);
     cudaFree(s->pic_slab);
-    cudaFree(s->res_slab);
+    for (uint8_t *p : s->res_slabs) cudaFree(p);
+    if (s->d_jobs) cudaFree(s->d_jobs);
     if (s->d_in16) cudaFree(s->d_in16);
     if (s->fp_units) cudaFree(s->fp_units);
     delete s;
@@ -262,51 +270,90 @@ static void fold_events(SvtMeSession *s) {
     s->ev_used = 0;
 }
 
-static uint32_t launch_me(SvtMeSession *s, int32_t pic_id, const SvtMePicParams *pp) {
-    uint32_t rc = validate_params(s, pic_id, pp);
-    if (rc != SVTME_OK) return rc;
+static uint32_t ensure_batch(SvtMeSession *s, uint32_t n) {
+    if (n <= s->res_slabs.size()) return SVTME_OK;
+    CU_TRY(cudaStreamSynchronize(s->stream));
+    while (s->res_slabs.size() < n) {
+        uint8_t *p = nullptr;
+        cudaError_t e = cudaMalloc(&p, s->lay.end);
+        if (e != cudaSuccess) { fprintf(stderr, "[svtme_b200] cudaMalloc result slab: %s\n", cudaGetErrorString(e)); return SVTME_ERR_INSUFFICIENT_RESOURCES; }
+        cudaMemset(p, 0, s->lay.end);
+        s->res_slabs.push_back(p);
+    }
+    if (s->d_jobs) cudaFree(s->d_jobs);
+    s->d_jobs = nullptr;
+    cudaError_t e = cudaMalloc(&s->d_jobs, sizeof(PicJob) * n);
+    if (e != cudaSuccess) return SVTME_ERR_INSUFFICIENT_RESOURCES;
+    return SVTME_OK;
+}
+
+static uint32_t launch_me_batch(SvtMeSession *s, uint32_t n, const int32_t *pic_ids, const SvtMePicParams *params) {
+    if (!s || !pic_ids || !params || n == 0 || n > 4096) return SVTME_ERR_BAD_PARAMETER;
     CU_TRY(cudaSetDevice(s->device));
-    PicJob job;
-    memset(&job, 0, sizeof(job));
-    job.pp  = *pp;
-    job.src = s->pics[pic_id];
-    for (int l = 0; l < pp->num_of_list_to_search; l++)
-        for (int r = 0; r < pp->num_of_ref_pic_to_search[l]; r++) job.ref[l][r] = s->pics[pp->ref_pic_id[l][r]];
-    job.pic_w = s->w; job.pic_h = s->h; job.b64_cols = s->b64_cols; job.b64_rows = s->b64_rows; job.n_b64 = s->n_b64;
-    job.n_pus = pp->enable_me_8x8 ? 85 : 21;
-    const uint32_t need_units = svtme_fp_units_cap(*pp, s->n_b64);
+    uint64_t need_units = 0;
+    for (uint32_t i = 0; i < n; i++) {
+        uint32_t rc = validate_params(s, pic_ids[i], &params[i]);
+        if (rc != SVTME_OK) return rc;
+        // one launch sequence serves the batch: the stage structure must agree (it does inside one encode)
+        const SvtMeCtrls &a = params[0].ctrls, &b = params[i].ctrls;
+        if (a.enable_hme_flag != b.enable_hme_flag || a.enable_hme_level0_flag != b.enable_hme_level0_flag ||
+            a.enable_hme_level1_flag != b.enable_hme_level1_flag || a.enable_hme_level2_flag != b.enable_hme_level2_flag ||
+            a.prehme_enable != b.prehme_enable || a.hme_search_method != b.hme_search_method ||
+            a.me_search_method != b.me_search_method || a.prehme_skip_search_line != b.prehme_skip_search_line ||
+            a.hme_l1_sa.width != b.hme_l1_sa.width || a.hme_l1_sa.height != b.hme_l1_sa.height ||
+            a.hme_l2_sa.width != b.hme_l2_sa.width || a.hme_l2_sa.height != b.hme_l2_sa.height)
+            return SVTME_ERR_BAD_PARAMETER;
+        need_units += svtme_fp_units_cap(params[i], s->n_b64);
+    }
+    if (need_units > 0x7fffffffull) return SVTME_ERR_INSUFFICIENT_RESOURCES;
+    uint32_t rc = ensure_batch(s, n);
+    if (rc != SVTME_OK) return rc;
     if (need_units > s->fp_units_cap) { // the unit queue grows with the largest search window of the controls in use
         CU_TRY(cudaStreamSynchronize(s->stream));
         if (s->fp_units) cudaFree(s->fp_units);
         s->fp_units = nullptr; s->fp_units_cap = 0;
-        cudaError_t e = cudaMalloc(&s->fp_units, (size_t)need_units * sizeof(uint32_t));
-        if (e != cudaSuccess) { fprintf(stderr, "[svtme_b200] cudaMalloc unit queue (%u units): %s\n", need_units, cudaGetErrorString(e)); return SVTME_ERR_INSUFFICIENT_RESOURCES; }
-        s->fp_units_cap = need_units;
+        cudaError_t e = cudaMalloc(&s->fp_units, (size_t)need_units * sizeof(uint2));
+        if (e != cudaSuccess) { fprintf(stderr, "[svtme_b200] cudaMalloc unit queue (%llu units): %s\n", (unsigned long long)need_units, cudaGetErrorString(e)); return SVTME_ERR_INSUFFICIENT_RESOURCES; }
+        s->fp_units_cap = (uint32_t)need_units;
     }
-    uint8_t *R = s->res_slab;
-    job.sb_state       = (SbState *)(R + s->lay.sb_state);
-    job.best_sad       = (uint32_t *)(R + s->lay.best_sad);
-    job.best_mv        = (uint32_t *)(R + s->lay.best_mv);
-    job.windows        = (SvtMeWindow *)(R + s->lay.windows);
-    job.search_results = (SvtMeSearchResult *)(R + s->lay.search_results);
-    job.total_me_candidate_index = R + s->lay.total;
-    job.me_mv_array              = (uint32_t *)(R + s->lay.mv);
-    job.me_candidate_array       = R + s->lay.cand;
-    job.me_64x64_distortion = (uint32_t *)(R + s->lay.d64);
-    job.me_32x32_distortion = (uint32_t *)(R + s->lay.d32);
-    job.me_16x16_distortion = (uint32_t *)(R + s->lay.d16);
-    job.me_8x8_distortion   = (uint32_t *)(R + s->lay.d8);
-    job.rc_me_distortion    = (uint32_t *)(R + s->lay.rc);
-    job.me_8x8_cost_variance = (uint32_t *)(R + s->lay.var);
-    job.stationary_block_present_sb = R + s->lay.stat;
-    job.rc_me_allow_gm              = R + s->lay.gm;
-    job.sad_ops                     = (unsigned long long *)(R + s->lay.ops);
-    job.hme_jobs     = (HmeJobG *)(R + s->lay.hme_jobs);
-    job.fp_jobs      = (FpJobG *)(R + s->lay.fp_jobs);
-    job.fp_keys      = (unsigned long long *)(R + s->lay.fp_keys);
-    job.fp_counters  = (uint32_t *)(R + s->lay.fp_counters);
-    job.fp_units     = s->fp_units;
-    job.fp_units_cap = s->fp_units_cap;
+    s->h_jobs.resize(n);
+    for (uint32_t i = 0; i < n; i++) {
+        const SvtMePicParams *pp = &params[i];
+        PicJob &job = s->h_jobs[i];
+        memset(&job, 0, sizeof(job));
+        job.pp  = *pp;
+        job.src = s->pics[pic_ids[i]];
+        for (int l = 0; l < pp->num_of_list_to_search; l++)
+            for (int r = 0; r < pp->num_of_ref_pic_to_search[l]; r++) job.ref[l][r] = s->pics[pp->ref_pic_id[l][r]];
+        job.pic_w = s->w; job.pic_h = s->h; job.b64_cols = s->b64_cols; job.b64_rows = s->b64_rows; job.n_b64 = s->n_b64;
+        job.n_pus = pp->enable_me_8x8 ? 85 : 21;
+        uint8_t *R = s->res_slabs[i];
+        job.sb_state       = (SbState *)(R + s->lay.sb_state);
+        job.best_sad       = (uint32_t *)(R + s->lay.best_sad);
+        job.best_mv        = (uint32_t *)(R + s->lay.best_mv);
+        job.windows        = (SvtMeWindow *)(R + s->lay.windows);
+        job.search_results = (SvtMeSearchResult *)(R + s->lay.search_results);
+        job.total_me_candidate_index = R + s->lay.total;
+        job.me_mv_array              = (uint32_t *)(R + s->lay.mv);
+        job.me_candidate_array       = R + s->lay.cand;
+        job.me_64x64_distortion = (uint32_t *)(R + s->lay.d64);
+        job.me_32x32_distortion = (uint32_t *)(R + s->lay.d32);
+        job.me_16x16_distortion = (uint32_t *)(R + s->lay.d16);
+        job.me_8x8_distortion   = (uint32_t *)(R + s->lay.d8);
+        job.rc_me_distortion    = (uint32_t *)(R + s->lay.rc);
+        job.me_8x8_cost_variance = (uint32_t *)(R + s->lay.var);
+        job.stationary_block_present_sb = R + s->lay.stat;
+        job.rc_me_allow_gm              = R + s->lay.gm;
+        job.hme_jobs     = (HmeJobG *)(R + s->lay.hme_jobs);
+        job.fp_jobs      = (FpJobG *)(R + s->lay.fp_jobs);
+        job.fp_keys      = (unsigned long long *)(R + s->lay.fp_keys);
+        // shared by the batch (slab 0)
+        job.sad_ops      = (unsigned long long *)(s->res_slab + s->lay.ops);
+        job.fp_counters  = (uint32_t *)(s->res_slab + s->lay.fp_counters);
+        job.fp_units     = s->fp_units;
+        job.fp_units_cap = s->fp_units_cap;
+    }
+    CU_TRY(cudaMemcpyAsync(s->d_jobs, s->h_jobs.data(), sizeof(PicJob) * n, cudaMemcpyHostToDevice, s->stream));
     cudaEvent_t e0 = nullptr, e1 = nullptr, e2 = nullptr;
     if (s->timing) {
         if (s->ev_used + 3 > s->ev.size()) {
@@ -324,18 +371,18 @@ static uint32_t launch_me(SvtMeSession *s, int32_t pic_id, const SvtMePicParams 
         e0 = s->ev[s->ev_used]; e1 = s->ev[s->ev_used + 1]; e2 = s->ev[s->ev_used + 2];
         s->ev_used += 3;
     }
-    s->launches += (uint64_t)svtme_launch_picture_me(job, s->stream, e0, e1, e2);
+    s->launches += (uint64_t)svtme_launch_picture_me(s->h_jobs.data(), (int)n, s->d_jobs, s->stream, e0, e1, e2);
     CU_TRY(cudaGetLastError());
-    s->last_pp      = *pp;
+    s->last_pps.assign(params, params + n);
     s->have_results = true;
     return SVTME_OK;
 }
 
-static uint32_t fetch(SvtMeSession *s, SvtMePicResults *res, int sync) {
-    if (!s->have_results || !res) return SVTME_ERR_BAD_PARAMETER;
-    const SvtMePicParams &pp = s->last_pp;
+static uint32_t fetch(SvtMeSession *s, uint32_t index, SvtMePicResults *res, int sync) {
+    if (!s->have_results || !res || index >= s->last_pps.size()) return SVTME_ERR_BAD_PARAMETER;
+    const SvtMePicParams &pp = s->last_pps[index];
     const size_t n = (size_t)s->n_b64, n_pus = pp.enable_me_8x8 ? 85 : 21;
-    uint8_t *R = s->res_slab;
+    uint8_t *R = s->res_slabs[index];
 #define D2H(dst, off, bytes)                                                                               \
     if (res->dst) CU_TRY(cudaMemcpyAsync(res->dst, R + s->lay.off, (bytes), cudaMemcpyDeviceToHost, s->stream))
     D2H(p_sb_best_sad, best_sad, n * 8 * 85 * 4);
@@ -358,26 +405,48 @@ static uint32_t fetch(SvtMeSession *s, SvtMePicResults *res, int sync) {
     return SVTME_OK;
 }
 
+extern "C" uint32_t svtme_picture_me_batch(SvtMeSession *s, uint32_t n, const int32_t *pic_ids, const SvtMePicParams *params,
+                                           SvtMePicResults *results, int sync) {
+    if (!s) return SVTME_ERR_BAD_PARAMETER;
+    std::lock_guard<std::mutex> g(s->mu);
+    uint32_t rc = launch_me_batch(s, n, pic_ids, params);
+    if (rc != SVTME_OK) return rc;
+    if (results)
+        for (uint32_t i = 0; i < n; i++) {
+            rc = fetch(s, i, &results[i], 0);
+            if (rc != SVTME_OK) return rc;
+        }
+    if (sync) CU_TRY(cudaStreamSynchronize(s->stream));
+    return SVTME_OK;
+}
+
+extern "C" uint32_t svtme_fetch_results_batch(SvtMeSession *s, uint32_t index, SvtMePicResults *results, int sync) {
+    if (!s) return SVTME_ERR_BAD_PARAMETER;
+    std::lock_guard<std::mutex> g(s->mu);
+    CU_TRY(cudaSetDevice(s->device));
+    return fetch(s, index, results, sync);
+}
+
 extern "C" uint32_t svtme_picture_me_device(SvtMeSession *s, int32_t pic_id, const SvtMePicParams *params) {
     if (!s) return SVTME_ERR_BAD_PARAMETER;
     std::lock_guard<std::mutex> g(s->mu);
-    return launch_me(s, pic_id, params);
+    return launch_me_batch(s, 1, &pic_id, params);
 }
 
 extern "C" uint32_t svtme_fetch_results(SvtMeSession *s, SvtMePicResults *results, int sync) {
     if (!s) return SVTME_ERR_BAD_PARAMETER;
     std::lock_guard<std::mutex> g(s->mu);
     CU_TRY(cudaSetDevice(s->device));
-    return fetch(s, results, sync);
+    return fetch(s, 0, results, sync);
 }
 
 extern "C" uint32_t svtme_picture_me(SvtMeSession *s, int32_t pic_id, const SvtMePicParams *params, SvtMePicResults *results,
                                      int sync) {
     if (!s) return SVTME_ERR_BAD_PARAMETER;
     std::lock_guard<std::mutex> g(s->mu);
-    uint32_t rc = launch_me(s, pic_id, params);
+    uint32_t rc = launch_me_batch(s, 1, &pic_id, params);
     if (rc != SVTME_OK) return rc;
-    if (results) return fetch(s, results, sync);
+    if (results) return fetch(s, 0, results, sync);
     if (sync) CU_TRY(cudaStreamSynchronize(s->stream));
     return SVTME_OK;
 }

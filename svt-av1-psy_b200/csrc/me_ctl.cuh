@@ -88,7 +88,8 @@ __device__ inline void ctl_set_quadrants(SbState &st, int lvl, int l, int r, int
         }
 }
 
-__global__ void __launch_bounds__(32 * CTL_WARPS) k_hme_ctl(const __grid_constant__ PicJob job, const CtlOp op) {
+__global__ void __launch_bounds__(32 * CTL_WARPS) k_hme_ctl(const PicJob *__restrict__ jobs, const CtlOp op) {
+    const PicJob &job = jobs[blockIdx.y];
     __shared__ __align__(16) SbState s_st[CTL_WARPS];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int b = blockIdx.x * CTL_WARPS + warp;

@@ -103,10 +103,9 @@ struct PicJob {
     HmeJobG            *hme_jobs;  // [n_b64][HME_JOBS_PER_B64]
     FpJobG             *fp_jobs;   // [n_b64][8]
     unsigned long long *fp_keys;   // [n_b64][8][85]: (sad << 32) | global scan index (0 = probe)
-    uint32_t           *fp_units;  // unit queue: (job index << 16) | tile
+    uint2              *fp_units;  // unit queue shared by the batch: x = picture in batch, y = (job << 16) | tile
     uint32_t           *fp_counters; // [0] number of units, [1] queue head
     uint32_t            fp_units_cap;
-    int                 s16_max_tiles; // grid bound of k_search16 for the current stage
 };
 
 // ------------------------------------------------------------------------------------------

@@ -138,7 +138,8 @@ __device__ __forceinline__ void fp_for_each_key(const FpKeys &K, F f) {
 
 // ---- k_fp_plan -------------------------------------------------------------------------------
 // phase: 0 all refs, 1 only (0,0), 2 all but (0,0) (enable_me_sr_adjustment == 2, :1357-1366)
-__global__ void __launch_bounds__(32 * FP_WARPS) k_fp_plan(const __grid_constant__ PicJob job, int phase) {
+__global__ void __launch_bounds__(32 * FP_WARPS) k_fp_plan(const PicJob *__restrict__ jobs, int phase) {
+    const PicJob &job = jobs[blockIdx.y];
     __shared__ __align__(16) uint32_t s_src[FP_WARPS][64 * 16];
     __shared__ __align__(16) uint32_t s_win[FP_WARPS][64 * FP_WIN_STRIDE];
     __shared__ uint32_t s_probe[FP_WARPS][85];
@@ -267,32 +268,35 @@ __global__ void __launch_bounds__(32 * FP_WARPS) k_fp_plan(const __grid_constant
         job.windows[u] = SvtMeWindow{x_origin, y_origin, sa_w, sa_h};
         const uint32_t n = (uint32_t)(n_tx * n_ty);
         const uint32_t base = atomicAdd(&job.fp_counters[0], n);
-        for (uint32_t i = 0; i < n && base + i < job.fp_units_cap; i++) job.fp_units[base + i] = ((uint32_t)u << 16) | i;
+        for (uint32_t i = 0; i < n && base + i < job.fp_units_cap; i++) job.fp_units[base + i] = make_uint2(blockIdx.y, ((uint32_t)u << 16) | i);
         ops += ((unsigned long long)sa_w * sa_h + (probe ? 1 : 0)) * 64ull * (sub ? 32 : 64);
         if (job.sad_ops) atomicAdd(&job.sad_ops[1], ops);
     }
 }
 
 // ---- k_fp_search -----------------------------------------------------------------------------
-__global__ void __launch_bounds__(32 * FP_WARPS, 4) k_fp_search(const __grid_constant__ PicJob job) {
+__global__ void __launch_bounds__(32 * FP_WARPS, 4) k_fp_search(const PicJob *__restrict__ jobs) {
+    const PicJob &job0 = jobs[0]; // the unit queue is shared by the batch
     __shared__ __align__(16) uint32_t s_src[FP_WARPS][64 * 16];
     __shared__ __align__(16) uint32_t s_win[FP_WARPS][FP_WIN_ROWS * FP_WIN_STRIDE];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const bool sub = job.pp.ctrls.me_search_method == SVTME_SUB_SAD_SEARCH;
-    const uint32_t n_units = min(job.fp_counters[0], job.fp_units_cap);
-    int cur_job = -1;
+    const bool sub = job0.pp.ctrls.me_search_method == SVTME_SUB_SAD_SEARCH;
+    const uint32_t n_units = min(job0.fp_counters[0], job0.fp_units_cap);
+    int cur_job = -1, cur_pic = -1;
     for (;;) {
         uint32_t ui = 0;
-        if (lane == 0) ui = atomicAdd(&job.fp_counters[1], 1u);
+        if (lane == 0) ui = atomicAdd(&job0.fp_counters[1], 1u);
         ui = __shfl_sync(0xffffffffu, ui, 0);
         if (ui >= n_units) break;
-        const uint32_t unit = job.fp_units[ui];
-        const int u = (int)(unit >> 16), tile = (int)(unit & 0xffff);
+        const uint2 unit = job0.fp_units[ui];
+        const PicJob &job = jobs[unit.x];
+        const int u = (int)(unit.y >> 16), tile = (int)(unit.y & 0xffff);
         const FpJobG &fj = job.fp_jobs[u];
         const int b = u >> 3, l = (u >> 2) & 1, r = u & 3;
         const B64Geo    g   = b64_geo(job, b);
         const DevPlane &ref = job.ref[l][r].lvl[0];
-        if (u != cur_job) {
+        if (u != cur_job || (int)unit.x != cur_pic) {
+            cur_pic = (int)unit.x;
             const DevPlane &sf = job.src.lvl[0];
             __syncwarp();
             warp_stage_src64(s_src[warp], sf.buf + (size_t)(sf.org_y + g.org_y) * sf.stride + sf.org_x + g.org_x, sf.stride, sub ? 2 : 1);

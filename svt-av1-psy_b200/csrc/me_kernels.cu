@@ -119,18 +119,45 @@ uint32_t svtme_fp_units_cap(const SvtMePicParams &pp, int n_b64) {
     return (uint32_t)cap;
 }
 
-int svtme_launch_picture_me(PicJob &job, cudaStream_t st, cudaEvent_t ev_hme0, cudaEvent_t ev_hme1, cudaEvent_t ev_fp1) {
-    const SvtMePicParams &pp = job.pp;
-    const SvtMeCtrls     &c  = pp.ctrls;
+// Launch the whole ME stage for a batch of n pictures (h_jobs: host copy, d_jobs: the same array on
+// the device). Every kernel is launched once for the batch (grid.y = picture); the control sequence
+// is the union of what the pictures need (an extra round is a no-op for pictures without the
+// dependency it serves).
+int svtme_launch_picture_me(const PicJob *h_jobs, int n, const PicJob *d_jobs, cudaStream_t st, cudaEvent_t ev_hme0,
+                            cudaEvent_t ev_hme1, cudaEvent_t ev_fp1) {
+    const PicJob         &j0 = h_jobs[0];
+    const SvtMeCtrls     &c  = j0.pp.ctrls; // HME flags / search methods are equal across a batch (validated by the caller)
     int launches = 0;
     const bool sub = c.hme_search_method == SVTME_SUB_SAD_SEARCH;
     const int  row_step = sub ? 2 : 1, rows0 = sub ? 8 : 16;
     const uint32_t ALL = 0xffu, LIST0 = 0x0fu, LIST1 = 0xf0u;
-    const int ctl_grid = (job.n_b64 + CTL_WARPS - 1) / CTL_WARPS;
+    const int n_b64 = j0.n_b64;
+    const unsigned ny = (unsigned)n;
+    const int ctl_grid = (n_b64 + CTL_WARPS - 1) / CTL_WARPS;
+    auto tiles_of = [&](int w, int h) {
+        int tw, th, ntx, nty;
+        s16_tile_geometry(w, h, rows0, row_step, &tw, &th, &ntx, &nty);
+        return ntx * nty < 1 ? 1 : ntx * nty;
+    };
+    bool any_zz = false, any_l1dep = false, any_dep = false, any_sr2 = false;
+    int  mt_pre = 1, mt_l0 = 1;
+    for (int i = 0; i < n; i++) {
+        const SvtMePicParams &pp = h_jobs[i].pp;
+        const SvtMeCtrls     &ci = pp.ctrls;
+        any_zz |= ci.me_early_exit_th || ci.me_safe_limit_zz_th;
+        any_l1dep |= ci.prehme_enable && ci.prehme_l1_early_exit && pp.num_of_list_to_search == 2 && pp.temporal_layer_index > 0;
+        any_dep |= ci.enable_me_sr_adjustment && ci.distance_based_hme_resizing && ci.reduce_hme_l0_sr_th_min && ci.reduce_hme_l0_sr_th_max;
+        any_sr2 |= ci.enable_me_sr_adjustment == 2;
+        if (ci.prehme_enable)
+            mt_pre = imax_h(mt_pre, imax_h(tiles_of(ci.prehme_sa_cfg[0].sa_max.width, ci.prehme_sa_cfg[0].sa_max.height),
+                                           tiles_of(ci.prehme_sa_cfg[1].sa_max.width, ci.prehme_sa_cfg[1].sa_max.height)));
+        const int qw = ((((ci.hme_l0_sa.sa_max.width / 2) + 15) & ~15) + 7) & ~7;
+        mt_l0 = imax_h(mt_l0, tiles_of(qw, ci.hme_l0_sa.sa_max.height / 2));
+    }
     if (ev_hme0) cudaEventRecord(ev_hme0, st);
-    cudaMemsetAsync(job.fp_counters, 0, 2 * sizeof(uint32_t), st);
-    if (c.me_early_exit_th || c.me_safe_limit_zz_th) {
-        k_zz<<<(job.n_b64 * 8 + SEARCH_WARPS - 1) / SEARCH_WARPS, 32 * SEARCH_WARPS, 0, st>>>(job);
+    cudaMemsetAsync(j0.fp_counters, 0, 2 * sizeof(uint32_t), st);
+    if (any_zz) {
+        k_zz<<<dim3((n_b64 * 8 + SEARCH_WARPS - 1) / SEARCH_WARPS, ny), 32 * SEARCH_WARPS, 0, st>>>(d_jobs);
         launches++;
     }
     bool first = true;
@@ -139,65 +166,52 @@ int svtme_launch_picture_me(PicJob &job, cudaStream_t st, cudaEvent_t ev_hme0, c
     auto emit = [&](int fin, int build, uint32_t bmask) {
         CtlOp op;
         op.init = first ? 1 : 0; op.post_stage = post; op.post_mask = pmask; op.finalize = fin; op.build_stage = build; op.build_mask = bmask;
-        k_hme_ctl<<<ctl_grid, 32 * CTL_WARPS, 0, st>>>(job, op);
+        k_hme_ctl<<<dim3(ctl_grid, ny), 32 * CTL_WARPS, 0, st>>>(d_jobs, op);
         launches++;
         first = false;
         post  = ST_NONE;
     };
-    auto tiles_of = [&](int w, int h) {
-        int tw, th, ntx, nty;
-        s16_tile_geometry(w, h, rows0, row_step, &tw, &th, &ntx, &nty);
-        return ntx * nty < 1 ? 1 : ntx * nty;
-    };
     auto search16 = [&](int max_tiles, int skip) {
-        job.s16_max_tiles = max_tiles;
-        const long long units = (long long)job.n_b64 * HME_JOBS_PER_B64 * max_tiles;
-        k_search16<<<(unsigned)((units + SEARCH_WARPS - 1) / SEARCH_WARPS), 32 * SEARCH_WARPS, 0, st>>>(job, skip);
+        const long long units = (long long)n_b64 * HME_JOBS_PER_B64 * max_tiles;
+        k_search16<<<dim3((unsigned)((units + SEARCH_WARPS - 1) / SEARCH_WARPS), ny), 32 * SEARCH_WARPS, 0, st>>>(d_jobs, skip, max_tiles);
         launches++;
     };
     auto search_wide = [&](int level) {
         const SvtMeSearchArea a = level == 1 ? c.hme_l1_sa : c.hme_l2_sa;
         const int w = (a.width + 7) & ~7, strips = level == 1 ? 2 : 4;
         const int tpj = next_pow2(imax_h(4, a.height * (w / 8) * strips));
-        const long long tasks = (long long)job.n_b64 * HME_JOBS_PER_B64 * tpj;
-        k_search_wide<<<(unsigned)((tasks + 32 * SEARCH_WARPS - 1) / (32 * SEARCH_WARPS)), 32 * SEARCH_WARPS, 0, st>>>(job, level, tpj);
+        const long long tasks = (long long)n_b64 * HME_JOBS_PER_B64 * tpj;
+        k_search_wide<<<dim3((unsigned)((tasks + 32 * SEARCH_WARPS - 1) / (32 * SEARCH_WARPS)), ny), 32 * SEARCH_WARPS, 0, st>>>(d_jobs, level, tpj);
         launches++;
     };
     int fin_pending = ST_NONE;
     if (c.prehme_enable) {
-        const int mt = imax_h(tiles_of(c.prehme_sa_cfg[0].sa_max.width, c.prehme_sa_cfg[0].sa_max.height),
-                              tiles_of(c.prehme_sa_cfg[1].sa_max.width, c.prehme_sa_cfg[1].sa_max.height));
-        const bool l1dep = c.prehme_l1_early_exit && pp.num_of_list_to_search == 2 && pp.temporal_layer_index > 0;
-        if (l1dep) {
+        if (any_l1dep) {
             emit(ST_NONE, ST_PREHME, LIST0);
-            search16(mt, c.prehme_skip_search_line);
+            search16(mt_pre, c.prehme_skip_search_line);
             post = ST_PREHME; pmask = LIST0;
             emit(ST_NONE, ST_PREHME, LIST1);
-            search16(mt, c.prehme_skip_search_line);
+            search16(mt_pre, c.prehme_skip_search_line);
             post = ST_PREHME; pmask = LIST1;
         } else {
             emit(ST_NONE, ST_PREHME, ALL);
-            search16(mt, c.prehme_skip_search_line);
+            search16(mt_pre, c.prehme_skip_search_line);
             post = ST_PREHME; pmask = ALL;
         }
         fin_pending = ST_PREHME;
     }
     if (c.enable_hme_flag) {
         if (c.enable_hme_level0_flag) {
-            const int qw = ((((c.hme_l0_sa.sa_max.width / 2) + 15) & ~15) + 7) & ~7;
-            const int mt = tiles_of(qw, c.hme_l0_sa.sa_max.height / 2);
-            const bool dep = c.enable_me_sr_adjustment && c.distance_based_hme_resizing && c.reduce_hme_l0_sr_th_min &&
-                c.reduce_hme_l0_sr_th_max;
-            if (dep) {
+            if (any_dep) {
                 emit(fin_pending, ST_L0, 0x01u);
-                search16(mt, 0);
+                search16(mt_l0, 0);
                 post = ST_L0; pmask = 0x01u;
                 emit(ST_NONE, ST_L0, ALL & ~0x01u);
-                search16(mt, 0);
+                search16(mt_l0, 0);
                 post = ST_L0; pmask = ALL & ~0x01u;
             } else {
                 emit(fin_pending, ST_L0, ALL);
-                search16(mt, 0);
+                search16(mt_l0, 0);
                 post = ST_L0; pmask = ALL;
             }
             fin_pending = ST_NONE;
@@ -221,9 +235,9 @@ int svtme_launch_picture_me(PicJob &job, cudaStream_t st, cudaEvent_t ev_hme0, c
 
     // ---- full-pel ----
     if (!g_fp_search_ctas_per_sm) {
-        int n = 0;
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_fp_search, 32 * FP_WARPS, 0);
-        g_fp_search_ctas_per_sm = n > 0 ? n : 1;
+        int k = 0;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&k, k_fp_search, 32 * FP_WARPS, 0);
+        g_fp_search_ctas_per_sm = k > 0 ? k : 1;
     }
     int n_sm = 148;
     {
@@ -231,24 +245,24 @@ int svtme_launch_picture_me(PicJob &job, cudaStream_t st, cudaEvent_t ev_hme0, c
         cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
     }
-    const int plan_grid = (job.n_b64 * 8 + FP_WARPS - 1) / FP_WARPS;
+    const dim3 plan_grid((n_b64 * 8 + FP_WARPS - 1) / FP_WARPS, ny);
     const int search_grid = n_sm * g_fp_search_ctas_per_sm;
-    if (c.enable_me_sr_adjustment == 2) {
+    if (any_sr2) {
         // the window of every ref but (0,0) depends on p_sb_best_sad[0][0][0] (motion_estimation.c:1357-1366)
-        k_fp_plan<<<plan_grid, 32 * FP_WARPS, 0, st>>>(job, 1);
-        k_fp_search<<<search_grid, 32 * FP_WARPS, 0, st>>>(job);
-        cudaMemsetAsync(job.fp_counters, 0, 2 * sizeof(uint32_t), st);
-        k_fp_plan<<<plan_grid, 32 * FP_WARPS, 0, st>>>(job, 2);
-        k_fp_search<<<search_grid, 32 * FP_WARPS, 0, st>>>(job);
+        k_fp_plan<<<plan_grid, 32 * FP_WARPS, 0, st>>>(d_jobs, 1);
+        k_fp_search<<<search_grid, 32 * FP_WARPS, 0, st>>>(d_jobs);
+        cudaMemsetAsync(j0.fp_counters, 0, 2 * sizeof(uint32_t), st);
+        k_fp_plan<<<plan_grid, 32 * FP_WARPS, 0, st>>>(d_jobs, 2);
+        k_fp_search<<<search_grid, 32 * FP_WARPS, 0, st>>>(d_jobs);
         launches += 4;
     } else {
-        k_fp_plan<<<plan_grid, 32 * FP_WARPS, 0, st>>>(job, 0);
-        k_fp_search<<<search_grid, 32 * FP_WARPS, 0, st>>>(job);
+        k_fp_plan<<<plan_grid, 32 * FP_WARPS, 0, st>>>(d_jobs, 0);
+        k_fp_search<<<search_grid, 32 * FP_WARPS, 0, st>>>(d_jobs);
         launches += 2;
     }
     if (ev_fp1) cudaEventRecord(ev_fp1, st);
-    k_post<<<job.n_b64, POST_THREADS, 0, st>>>(job);
-    k_mask_unsearched<<<job.n_b64, 96, 0, st>>>(job);
+    k_post<<<dim3(n_b64, ny), POST_THREADS, 0, st>>>(d_jobs);
+    k_mask_unsearched<<<dim3(n_b64, ny), 96, 0, st>>>(d_jobs);
     launches += 2;
     return launches;
 }

@@ -24,7 +24,8 @@ struct PostSh {
     uint32_t me_distortion[85];
 };
 
-__global__ void __launch_bounds__(POST_THREADS) k_post(const __grid_constant__ PicJob job) {
+__global__ void __launch_bounds__(POST_THREADS) k_post(const PicJob *__restrict__ jobs) {
+    const PicJob &job = jobs[blockIdx.y];
     __shared__ PostSh sh;
     const SvtMePicParams &pp  = job.pp;
     const SvtMeCtrls     &c   = pp.ctrls;
@@ -281,7 +282,8 @@ __global__ void __launch_bounds__(POST_THREADS) k_post(const __grid_constant__ P
 
 // zero the MeContext mirrors of refs that ended with do_ref == 0 (their content is stale in the
 // reference) so that dumps are deterministic
-__global__ void k_mask_unsearched(const __grid_constant__ PicJob job) {
+__global__ void k_mask_unsearched(const PicJob *__restrict__ jobs) {
+    const PicJob &job = jobs[blockIdx.y];
     const int b = blockIdx.x, tid = threadIdx.x;
     for (int lr = 0; lr < 8; lr++) {
         const SvtMeSearchResult &sr = job.search_results[(size_t)b * 8 + lr];

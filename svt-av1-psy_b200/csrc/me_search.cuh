@@ -59,7 +59,8 @@ __device__ inline uint32_t warp_nxm_sad2(const uint8_t *src, int src_stride, con
 }
 
 // ---- k_zz ------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(32 * SEARCH_WARPS) k_zz(const __grid_constant__ PicJob job) {
+__global__ void __launch_bounds__(32 * SEARCH_WARPS) k_zz(const PicJob *__restrict__ jobs) {
+    const PicJob &job = jobs[blockIdx.y];
     const int u = blockIdx.x * SEARCH_WARPS + (threadIdx.x >> 5);
     if (u >= job.n_b64 * 8) return;
     const int b = u >> 3, l = (u >> 2) & 1, r = u & 3;
@@ -145,12 +146,13 @@ __device__ inline void warp_stage_src(uint32_t *dst, int words, const uint8_t *s
 
 // ---- k_search16 ------------------------------------------------------------------------------
 // grid: ceil(n_b64 * 32 * max_tiles / SEARCH_WARPS) CTAs; unit -> (b64, job slot, tile)
-__global__ void __launch_bounds__(32 * SEARCH_WARPS, 8) k_search16(const __grid_constant__ PicJob job, int skip_cfg) {
+__global__ void __launch_bounds__(32 * SEARCH_WARPS, 8) k_search16(const PicJob *__restrict__ jobs, int skip_cfg, int max_tiles) {
+    const PicJob &job = jobs[blockIdx.y];
     __shared__ __align__(16) uint32_t s_win[SEARCH_WARPS][S16_WIN_WORDS];
     __shared__ __align__(16) uint32_t s_src[SEARCH_WARPS][16 * 4];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const long long u = (long long)blockIdx.x * SEARCH_WARPS + warp;
-    const int mt = job.s16_max_tiles;
+    const int mt = max_tiles;
     const long long js = u / mt;
     const int tile = (int)(u - js * mt);
     if (js >= (long long)job.n_b64 * HME_JOBS_PER_B64) return;
@@ -237,7 +239,8 @@ __device__ __forceinline__ unsigned long long octet_best_key(const uint32_t (&ac
 // ---- k_search_wide ---------------------------------------------------------------------------
 // level: 1 (1/4 plane, 32-wide blocks, 2 strips) or 2 (full plane, 64-wide, 4 strips).
 // tpj: task slots per job (power of two >= sa_h_max * n_oct_max * strips).
-__global__ void __launch_bounds__(32 * SEARCH_WARPS) k_search_wide(const __grid_constant__ PicJob job, int level, int tpj) {
+__global__ void __launch_bounds__(32 * SEARCH_WARPS) k_search_wide(const PicJob *__restrict__ jobs, int level, int tpj) {
+    const PicJob &job = jobs[blockIdx.y];
     const int lane = threadIdx.x & 31;
     const long long t = ((long long)blockIdx.x * SEARCH_WARPS + (threadIdx.x >> 5)) * 32 + lane;
     const int strips = level == 1 ? 2 : 4, sbits = level == 1 ? 1 : 2;

@@ -96,3 +96,32 @@ def test_session_rejects_bad_arguments():
     with pytest.raises(me.binding.SvtMeError):
         me.Session(321, 192)  # width not a multiple of 8
     s.close()
+
+
+def test_batch_equals_single_picture_calls():
+    """a mini-GOP submitted as one batch gives, picture by picture, what single-picture calls give"""
+    import copy
+    from svt_av1_psy_b200.synth import PanningNoise
+    w, h = 320, 192
+    clip = PanningNoise(w, h, seed=21, vx=2, vy=1, max_frames=40)
+    s = me.Session(w, h, max_pictures=20)
+    for t in range(17):
+        s.upload(t, clip.frame(t))
+    plans = [(8, 1, [0, 4], [16, 12]), (4, 2, [0], [8, 16]), (2, 3, [0], [4, 8]), (16, 0, [0, 8], [0, 8]), (5, 4, [4, 0], [6, 8])]
+    ids, prms, singles = [], [], []
+    for poc, tl, l0, l1 in plans:
+        src = clip.frame(poc)
+        refs = [[clip.frame(p) for p in l0], [clip.frame(p) for p in l1]]
+        p = params_from_encoder_inputs(src, refs, [l0, l1], poc, 4, temporal_layer=tl, hier_levels=5, is_ref=1 if tl < 5 else 0)
+        for l, lst in enumerate((l0, l1)):
+            for r, rp in enumerate(lst):
+                p.ref_pic_id[l][r] = rp
+        ids.append(poc)
+        prms.append(p)
+        singles.append(s.me(poc, copy.copy(p)))
+    from svt_av1_psy_b200 import abi
+    batch = [abi.PicResultArrays(w, h, p) for p in prms]
+    s.me_batch(ids, prms, batch)
+    for a, b in zip(singles, batch):
+        compare(a, b, fields=list(a.FIELDS))
+    s.close()
