@@ -45,8 +45,8 @@ struct SvtMeSession {
     std::vector<SvtMePicParams> last_pps;
     ResultLayout lay{};
     uint16_t    *d_in16 = nullptr;
-    uint2       *fp_units = nullptr;
-    uint32_t     fp_units_cap = 0;
+    uint2       *fp_units = nullptr, *s16_units = nullptr;
+    uint32_t     fp_units_cap = 0, s16_units_cap = 0;
     SvtMePicParams last_pp{};
     bool         have_results = false;
     uint64_t     launches = 0;
@@ -152,6 +152,7 @@ extern "C" void svtme_session_destroy(SvtMeSession *s) {
     if (s->d_jobs) cudaFree(s->d_jobs);
     if (s->d_in16) cudaFree(s->d_in16);
     if (s->fp_units) cudaFree(s->fp_units);
+    if (s->s16_units) cudaFree(s->s16_units);
     delete s;
 }
 
@@ -290,7 +291,7 @@ static uint32_t ensure_batch(SvtMeSession *s, uint32_t n) {
 static uint32_t launch_me_batch(SvtMeSession *s, uint32_t n, const int32_t *pic_ids, const SvtMePicParams *params) {
     if (!s || !pic_ids || !params || n == 0 || n > 4096) return SVTME_ERR_BAD_PARAMETER;
     CU_TRY(cudaSetDevice(s->device));
-    uint64_t need_units = 0;
+    uint64_t need_units = 0, need_s16 = 0;
     for (uint32_t i = 0; i < n; i++) {
         uint32_t rc = validate_params(s, pic_ids[i], &params[i]);
         if (rc != SVTME_OK) return rc;
@@ -304,6 +305,7 @@ static uint32_t launch_me_batch(SvtMeSession *s, uint32_t n, const int32_t *pic_
             a.hme_l2_sa.width != b.hme_l2_sa.width || a.hme_l2_sa.height != b.hme_l2_sa.height)
             return SVTME_ERR_BAD_PARAMETER;
         need_units += svtme_fp_units_cap(params[i], s->n_b64);
+        need_s16 += svtme_s16_units_cap(params[i], s->n_b64);
     }
     if (need_units > 0x7fffffffull) return SVTME_ERR_INSUFFICIENT_RESOURCES;
     uint32_t rc = ensure_batch(s, n);
@@ -315,6 +317,15 @@ static uint32_t launch_me_batch(SvtMeSession *s, uint32_t n, const int32_t *pic_
         cudaError_t e = cudaMalloc(&s->fp_units, (size_t)need_units * sizeof(uint2));
         if (e != cudaSuccess) { fprintf(stderr, "[svtme_b200] cudaMalloc unit queue (%llu units): %s\n", (unsigned long long)need_units, cudaGetErrorString(e)); return SVTME_ERR_INSUFFICIENT_RESOURCES; }
         s->fp_units_cap = (uint32_t)need_units;
+    }
+    if (need_s16 > 0x7fffffffull) return SVTME_ERR_INSUFFICIENT_RESOURCES;
+    if (need_s16 > s->s16_units_cap) {
+        CU_TRY(cudaStreamSynchronize(s->stream));
+        if (s->s16_units) cudaFree(s->s16_units);
+        s->s16_units = nullptr; s->s16_units_cap = 0;
+        cudaError_t e = cudaMalloc(&s->s16_units, (size_t)need_s16 * sizeof(uint2));
+        if (e != cudaSuccess) { fprintf(stderr, "[svtme_b200] cudaMalloc HME unit queue (%llu units): %s\n", (unsigned long long)need_s16, cudaGetErrorString(e)); return SVTME_ERR_INSUFFICIENT_RESOURCES; }
+        s->s16_units_cap = (uint32_t)need_s16;
     }
     s->h_jobs.resize(n);
     for (uint32_t i = 0; i < n; i++) {
@@ -352,6 +363,9 @@ static uint32_t launch_me_batch(SvtMeSession *s, uint32_t n, const int32_t *pic_
         job.fp_counters  = (uint32_t *)(s->res_slab + s->lay.fp_counters);
         job.fp_units     = s->fp_units;
         job.fp_units_cap = s->fp_units_cap;
+        job.s16_units     = s->s16_units;
+        job.s16_counters  = (uint32_t *)(s->res_slab + s->lay.fp_counters) + 4;
+        job.s16_units_cap = s->s16_units_cap;
     }
     CU_TRY(cudaMemcpyAsync(s->d_jobs, s->h_jobs.data(), sizeof(PicJob) * n, cudaMemcpyHostToDevice, s->stream));
     cudaEvent_t e0 = nullptr, e1 = nullptr, e2 = nullptr;

@@ -36,8 +36,12 @@ __host__ __device__ inline void s16_tile_geometry(int sa_w, int sa_h, int rows, 
     if (tw > 128) tw = 128;
     const int stride = tw / 4 + 4, span = row_step * (rows - 1);
     int th = S16_WIN_WORDS / stride - span;
+    // keep a tile to about 3 passes of the warp (96 octet tasks) so that the dynamic queue balances well
+    const int bal = 96 / (tw / 8);
+    if (th > bal) th = bal < 4 ? 4 : bal;
     if (th < 1) th = 1;
     if (th > sa_h) th = sa_h;
+    while (((sa_w + tw - 1) / tw) * ((sa_h + th - 1) / th) > 255) th *= 2; // tile index is 8 bits
     *tile_w = tw; *tile_h = th;
     *n_tx = (sa_w + tw - 1) / tw;
     *n_ty = (sa_h + th - 1) / th;
@@ -60,6 +64,15 @@ __device__ inline void ctl_make_job(HmeJobG &j, const DevPlane &ref, int16_t org
     j.tile_w = (uint16_t)tw; j.tile_h = (uint16_t)th; j.n_tx = (uint8_t)ntx; j.n_ty = (uint8_t)nty;
     j.key    = HME_KEY_NONE;
     j.active = 1;
+}
+
+// append the tiles of a staged search to the batch-wide unit queue of k_search16
+__device__ inline void ctl_enqueue_tiles(const PicJob &job, const HmeJobG &j, int slot_in_pic) {
+    const uint32_t n = (uint32_t)j.n_tx * j.n_ty;
+    if (!n) return;
+    const uint32_t base = atomicAdd(&job.s16_counters[0], n);
+    for (uint32_t i = 0; i < n && base + i < job.s16_units_cap; i++)
+        job.s16_units[base + i] = make_uint2(blockIdx.y, ((uint32_t)slot_in_pic << 8) | i);
 }
 
 // key -> (sad, centre); centre keeps its value when no position was evaluated
@@ -293,6 +306,7 @@ __global__ void __launch_bounds__(32 * CTL_WARPS) k_hme_ctl(const PicJob *__rest
                          w, h, (int16_t)(rf.org_x - 1), (int16_t)(rf.org_y - 1), false, rows0, row_step);
             const bool sk = c.prehme_skip_search_line && bw0 == 16 && rows0 <= 16;
             if (j.sa_w > 0 && j.sa_h > 0) ops += (unsigned long long)j.sa_w * (sk ? j.sa_h / 2 : j.sa_h) * bw0 * rows0;
+            ctl_enqueue_tiles(job, j, b * HME_JOBS_PER_B64 + lane);
         }
     } else if (op.build_stage == ST_L0 && in_build) {
         const int bw0 = g.b64_w >> 2, rows0 = sub ? (g.b64_h >> 2) >> 1 : (g.b64_h >> 2);
@@ -340,6 +354,7 @@ __global__ void __launch_bounds__(32 * CTL_WARPS) k_hme_ctl(const PicJob *__rest
             ctl_make_job(j, rf, (int16_t)(ox16 >> 2), (int16_t)(oy16 >> 2), ox, oy, w, sh0, (int16_t)(rf.org_x - 1),
                          (int16_t)(rf.org_y - 1), true, rows0, row_step);
             if (j.sa_w > 0 && j.sa_h > 0) ops += (unsigned long long)j.sa_w * j.sa_h * bw0 * rows0;
+            ctl_enqueue_tiles(job, j, b * HME_JOBS_PER_B64 + lane);
         }
     } else if ((op.build_stage == ST_L1 || op.build_stage == ST_L2) && in_build && hme_ref) {
         const int lvl = op.build_stage - ST_L0;

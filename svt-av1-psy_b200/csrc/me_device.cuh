@@ -106,6 +106,9 @@ struct PicJob {
     uint2              *fp_units;  // unit queue shared by the batch: x = picture in batch, y = (job << 16) | tile
     uint32_t           *fp_counters; // [0] number of units, [1] queue head
     uint32_t            fp_units_cap;
+    uint2              *s16_units;    // unit queue of k_search16: x = picture in batch, y = (job slot in picture << 8) | tile
+    uint32_t           *s16_counters; // [0] number of units, [1] queue head
+    uint32_t            s16_units_cap;
 };
 
 // ------------------------------------------------------------------------------------------

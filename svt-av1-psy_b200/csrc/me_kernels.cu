@@ -95,13 +95,34 @@ int svtme_launch_downsample_generic(const uint8_t *d_in, int in_stride, int in_w
 // ------------------------------------------------------------------------------------------
 // picture pipeline (v2): flat warp-per-tile searches, control in k_hme_ctl between them
 // ------------------------------------------------------------------------------------------
-static int g_fp_search_ctas_per_sm = 0;
+static int g_fp_search_ctas_per_sm = 0, g_s16_ctas_per_sm = 0;
 
 static inline int imax_h(int a, int b) { return a > b ? a : b; }
 static int next_pow2(int v) {
     int p = 1;
     while (p < v) p <<= 1;
     return p;
+}
+
+uint32_t svtme_s16_units_cap(const SvtMePicParams &pp, int n_b64) {
+    const SvtMeCtrls &c = pp.ctrls;
+    const bool sub = c.hme_search_method == SVTME_SUB_SAD_SEARCH;
+    const int  row_step = sub ? 2 : 1, rows0 = sub ? 8 : 16;
+    auto tiles_of = [&](int w, int h) {
+        int tw, th, ntx, nty;
+        s16_tile_geometry(w, h, rows0, row_step, &tw, &th, &ntx, &nty);
+        return (long long)(ntx * nty < 1 ? 1 : ntx * nty);
+    };
+    long long per_b64 = 0;
+    if (c.prehme_enable)
+        per_b64 = 8 * (tiles_of(c.prehme_sa_cfg[0].sa_max.width, c.prehme_sa_cfg[0].sa_max.height) +
+                       tiles_of(c.prehme_sa_cfg[1].sa_max.width, c.prehme_sa_cfg[1].sa_max.height));
+    const int qw = ((((c.hme_l0_sa.sa_max.width / 2) + 15) & ~15) + 7) & ~7;
+    const long long l0 = 32 * tiles_of(qw, c.hme_l0_sa.sa_max.height / 2);
+    if (l0 > per_b64) per_b64 = l0;
+    long long cap = per_b64 * n_b64;
+    if (cap > 0x7fffffffLL) cap = 0x7fffffffLL;
+    return (uint32_t)cap;
 }
 
 uint32_t svtme_fp_units_cap(const SvtMePicParams &pp, int n_b64) {
@@ -166,14 +187,25 @@ int svtme_launch_picture_me(const PicJob *h_jobs, int n, const PicJob *d_jobs, c
     auto emit = [&](int fin, int build, uint32_t bmask) {
         CtlOp op;
         op.init = first ? 1 : 0; op.post_stage = post; op.post_mask = pmask; op.finalize = fin; op.build_stage = build; op.build_mask = bmask;
+        if (build == ST_PREHME || build == ST_L0) cudaMemsetAsync(j0.s16_counters, 0, 2 * sizeof(uint32_t), st);
         k_hme_ctl<<<dim3(ctl_grid, ny), 32 * CTL_WARPS, 0, st>>>(d_jobs, op);
         launches++;
         first = false;
         post  = ST_NONE;
     };
-    auto search16 = [&](int max_tiles, int skip) {
-        const long long units = (long long)n_b64 * HME_JOBS_PER_B64 * max_tiles;
-        k_search16<<<dim3((unsigned)((units + SEARCH_WARPS - 1) / SEARCH_WARPS), ny), 32 * SEARCH_WARPS, 0, st>>>(d_jobs, skip, max_tiles);
+    int n_sm = 148;
+    {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
+    }
+    if (!g_s16_ctas_per_sm) {
+        int k = 0;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&k, k_search16, 32 * SEARCH_WARPS, 0);
+        g_s16_ctas_per_sm = k > 0 ? k : 1;
+    }
+    auto search16 = [&](int /*max_tiles*/, int skip) {
+        k_search16<<<n_sm * g_s16_ctas_per_sm, 32 * SEARCH_WARPS, 0, st>>>(d_jobs, skip);
         launches++;
     };
     auto search_wide = [&](int level) {
@@ -238,12 +270,6 @@ int svtme_launch_picture_me(const PicJob *h_jobs, int n, const PicJob *d_jobs, c
         int k = 0;
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&k, k_fp_search, 32 * FP_WARPS, 0);
         g_fp_search_ctas_per_sm = k > 0 ? k : 1;
-    }
-    int n_sm = 148;
-    {
-        int dev = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
     }
     const dim3 plan_grid((n_b64 * 8 + FP_WARPS - 1) / FP_WARPS, ny);
     const int search_grid = n_sm * g_fp_search_ctas_per_sm;

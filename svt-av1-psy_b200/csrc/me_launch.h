@@ -15,6 +15,7 @@ int  svtme_launch_copy2d(const uint8_t *d_in, int in_stride, uint8_t *d_out, int
 int  svtme_launch_downsample_generic(const uint8_t *d_in, int in_stride, int in_w, int in_h, uint8_t *d_out, int out_stride,
                                      int step, cudaStream_t st);
 uint32_t svtme_fp_units_cap(const SvtMePicParams &pp, int n_b64);
+uint32_t svtme_s16_units_cap(const SvtMePicParams &pp, int n_b64);
 int  svtme_launch_picture_me(const PicJob *h_jobs, int n, const PicJob *d_jobs, cudaStream_t st, cudaEvent_t ev_hme0,
                              cudaEvent_t ev_hme1, cudaEvent_t ev_fp1);
 int  svtme_launch_kat_sad_loop(const uint8_t *d_src, int src_stride, const uint8_t *d_ref, int ref_stride, int bh, int bw,

@@ -145,34 +145,46 @@ __device__ inline void warp_stage_src(uint32_t *dst, int words, const uint8_t *s
 }
 
 // ---- k_search16 ------------------------------------------------------------------------------
-// grid: ceil(n_b64 * 32 * max_tiles / SEARCH_WARPS) CTAs; unit -> (b64, job slot, tile)
-__global__ void __launch_bounds__(32 * SEARCH_WARPS, 8) k_search16(const PicJob *__restrict__ jobs, int skip_cfg, int max_tiles) {
-    const PicJob &job = jobs[blockIdx.y];
+// persistent warps pull (picture, job, tile) units from the queue k_hme_ctl filled
+__global__ void __launch_bounds__(32 * SEARCH_WARPS, 8) k_search16(const PicJob *__restrict__ jobs, int skip_cfg) {
     __shared__ __align__(16) uint32_t s_win[SEARCH_WARPS][S16_WIN_WORDS];
     __shared__ __align__(16) uint32_t s_src[SEARCH_WARPS][16 * 4];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const long long u = (long long)blockIdx.x * SEARCH_WARPS + warp;
-    const int mt = max_tiles;
-    const long long js = u / mt;
-    const int tile = (int)(u - js * mt);
-    if (js >= (long long)job.n_b64 * HME_JOBS_PER_B64) return;
-    HmeJobG &j = job.hme_jobs[js];
-    if (!j.active || tile >= j.n_tx * j.n_ty) return;
-    const int b = (int)(js / HME_JOBS_PER_B64);
-    const B64Geo g = b64_geo(job, b);
-    const bool sub = job.pp.ctrls.hme_search_method == SVTME_SUB_SAD_SEARCH;
+    const PicJob &job0 = jobs[0];
+    const uint32_t n_units = min(job0.s16_counters[0], job0.s16_units_cap);
+    int cur_b = -1, cur_pic = -1;
+    const bool sub = job0.pp.ctrls.hme_search_method == SVTME_SUB_SAD_SEARCH;
     const int row_step = sub ? 2 : 1;
-    const int bw = g.b64_w >> 2, bh = g.b64_h >> 2, rows = sub ? bh >> 1 : bh;
-    const DevPlane &ss = job.src.lvl[2];
-    const uint8_t *src_s = ss.buf + (size_t)(ss.org_y + (g.org_y >> 2)) * ss.stride + ss.org_x + (g.org_x >> 2);
-    warp_stage_src(s_src[warp], 4, src_s, ss.stride, row_step, rows, bw);
-    const int ty = tile / j.n_tx, tx = tile - ty * j.n_tx;
-    const int x0 = tx * j.tile_w, y0 = ty * j.tile_h;
-    const int tw = imin(j.tile_w, j.sa_w - x0), th = imin(j.tile_h, j.sa_h - y0);
-    const bool skip = skip_cfg && bw == 16 && rows <= 16;
-    const unsigned long long key = warp_search16_tile(s_win[warp], s_src[warp], j.ref, j.ref_stride, j.sa_w, x0, y0, tw, th,
-                                                     bw, rows, row_step, skip);
-    if (lane == 0 && key != HME_KEY_NONE) atomicMin(&j.key, key);
+    int bw = 0, rows = 0;
+    for (;;) {
+        uint32_t ui = 0;
+        if (lane == 0) ui = atomicAdd(&job0.s16_counters[1], 1u);
+        ui = __shfl_sync(0xffffffffu, ui, 0);
+        if (ui >= n_units) break;
+        const uint2 unit = job0.s16_units[ui];
+        const PicJob &job = jobs[unit.x];
+        const int slot = (int)(unit.y >> 8), tile = (int)(unit.y & 0xff);
+        HmeJobG &j = job.hme_jobs[slot];
+        const int b = slot / HME_JOBS_PER_B64;
+        if (b != cur_b || (int)unit.x != cur_pic) { // source block of this b64 on the 1/16 plane
+            const B64Geo g = b64_geo(job, b);
+            bw = g.b64_w >> 2;
+            rows = sub ? (g.b64_h >> 2) >> 1 : (g.b64_h >> 2);
+            const DevPlane &ss = job.src.lvl[2];
+            __syncwarp();
+            warp_stage_src(s_src[warp], 4, ss.buf + (size_t)(ss.org_y + (g.org_y >> 2)) * ss.stride + ss.org_x + (g.org_x >> 2),
+                           ss.stride, row_step, rows, bw);
+            cur_b = b; cur_pic = (int)unit.x;
+        }
+        const int ty = tile / j.n_tx, tx = tile - ty * j.n_tx;
+        const int x0 = tx * j.tile_w, y0 = ty * j.tile_h;
+        const int tw = imin(j.tile_w, j.sa_w - x0), th = imin(j.tile_h, j.sa_h - y0);
+        const bool skip = skip_cfg && bw == 16 && rows <= 16;
+        const unsigned long long key = warp_search16_tile(s_win[warp], s_src[warp], j.ref, j.ref_stride, j.sa_w, x0, y0, tw, th,
+                                                         bw, rows, row_step, skip);
+        if (lane == 0 && key != HME_KEY_NONE) atomicMin(&j.key, key);
+        __syncwarp();
+    }
 }
 
 // ---- wide blocks: one task = (y, octet, 16-pixel strip) of one search, rows from global memory ----
