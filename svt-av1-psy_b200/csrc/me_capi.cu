@@ -255,6 +255,11 @@ static uint32_t validate_params(const SvtMeSession *s, int32_t pic_id, const Svt
     // the MeSbResults arrays are sized by max_l0 / max_refs (pcs.c:91-96): more refs than that would alias entries
     if (pp->num_of_ref_pic_to_search[0] > pp->max_l0 || pp->max_l0 > pp->max_refs) return SVTME_ERR_BAD_PARAMETER;
     if (pp->num_of_list_to_search == 2 && pp->num_of_ref_pic_to_search[1] > pp->max_refs - pp->max_l0) return SVTME_ERR_BAD_PARAMETER;
+    { // full-pel scan indices are 12 bits per chunk of passes (me_fp3.cuh): bound the widest possible window
+        long long mw = pp->ctrls.me_sa.sa_max.width;
+        if (pp->ctrls.mv_sa_adj_enabled) mw *= pp->ctrls.mv_sa_adj_sa_multiplier;
+        if (mw * 3 / 2 + 8 > 1536) return SVTME_ERR_BAD_PARAMETER;
+    }
     return SVTME_OK;
 }
 

@@ -34,7 +34,9 @@ __host__ __device__ inline void s16_tile_geometry(int sa_w, int sa_h, int rows, 
     if (sa_w <= 0 || sa_h <= 0) { *tile_w = 8; *tile_h = 1; *n_tx = 0; *n_ty = 0; return; }
     int tw = (sa_w + 7) & ~7;
     if (tw > 128) tw = 128;
-    const int stride = tw / 4 + 4, span = row_step * (rows - 1);
+    int stride = tw / 4 + 4;
+    if ((stride & 15) == 0) stride += 2; // same pitch rule as warp_search16_tile
+    const int span = row_step * (rows - 1);
     int th = S16_WIN_WORDS / stride - span;
     // keep a tile to about 3 passes of the warp (96 octet tasks) so that the dynamic queue balances well
     const int bal = 96 / (tw / 8);
@@ -70,7 +72,20 @@ __device__ inline void ctl_make_job(HmeJobG &j, const DevPlane &ref, int16_t org
 __device__ inline void ctl_enqueue_tiles(const PicJob &job, const HmeJobG &j, int slot_in_pic) {
     const uint32_t n = (uint32_t)j.n_tx * j.n_ty;
     if (!n) return;
-    const uint32_t base = atomicAdd(&job.s16_counters[0], n);
+    // one atomic per group of lanes that enqueue together (the counter is shared by the whole batch)
+    const uint32_t peers = __activemask();
+    const int      lane  = threadIdx.x & 31;
+    uint32_t pre = 0, tot = 0;
+    for (int i = 0; i < 32; i++) {
+        if (!((peers >> i) & 1)) continue;
+        const uint32_t ni = __shfl_sync(peers, n, i);
+        if (i < lane) pre += ni;
+        tot += ni;
+    }
+    uint32_t base = 0;
+    const int leader = __ffs(peers) - 1;
+    if (lane == leader) base = atomicAdd(&job.s16_counters[0], tot);
+    base = __shfl_sync(peers, base, leader) + pre;
     for (uint32_t i = 0; i < n && base + i < job.s16_units_cap; i++)
         job.s16_units[base + i] = make_uint2(blockIdx.y, ((uint32_t)slot_in_pic << 8) | i);
 }
@@ -391,6 +406,7 @@ __global__ void __launch_bounds__(32 * CTL_WARPS) k_hme_ctl(const PicJob *__rest
             else
                 ctl_make_job(j, rf, ox16, oy16, ox, oy, w, h, 63, 63, true, rows, row_step);
             if (j.sa_w > 0 && j.sa_h > 0) ops += (unsigned long long)j.sa_w * j.sa_h * bw * rows;
+
         }
     }
 #pragma unroll

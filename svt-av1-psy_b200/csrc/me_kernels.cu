@@ -4,7 +4,7 @@
 #include "me_device.cuh"
 #include "me_search.cuh"
 #include "me_ctl.cuh"
-#include "me_fp2.cuh"
+#include "me_fp3.cuh"
 #include "me_post.cuh"
 
 // ------------------------------------------------------------------------------------------
@@ -133,9 +133,9 @@ uint32_t svtme_fp_units_cap(const SvtMePicParams &pp, int n_b64) {
     mh = mh * 3 / 2;
     if (mw < 8) mw = 8;
     if (mh < 3) mh = 3;
-    long long tiles = ((mw + FP_TILE_W - 1) / FP_TILE_W) * ((mh + FP_TILE_H - 1) / FP_TILE_H);
-    if (tiles > 65535) tiles = 65535;
-    long long cap = tiles * n_b64 * 8;
+    long long chunks = ((mw / 8) * mh + FP_CHUNK_PASSES - 1) / FP_CHUNK_PASSES;
+    if (chunks > 65535) chunks = 65535;
+    long long cap = chunks * n_b64 * 8;
     if (cap > 0x7fffffffLL) cap = 0x7fffffffLL;
     return (uint32_t)cap;
 }
@@ -209,11 +209,9 @@ int svtme_launch_picture_me(const PicJob *h_jobs, int n, const PicJob *d_jobs, c
         launches++;
     };
     auto search_wide = [&](int level) {
-        const SvtMeSearchArea a = level == 1 ? c.hme_l1_sa : c.hme_l2_sa;
-        const int w = (a.width + 7) & ~7, strips = level == 1 ? 2 : 4;
-        const int tpj = next_pow2(imax_h(4, a.height * (w / 8) * strips));
-        const long long tasks = (long long)n_b64 * HME_JOBS_PER_B64 * tpj;
-        k_search_wide<<<dim3((unsigned)((tasks + 32 * SEARCH_WARPS - 1) / (32 * SEARCH_WARPS)), ny), 32 * SEARCH_WARPS, 0, st>>>(d_jobs, level, tpj);
+        const dim3 grid((n_b64 * HME_JOBS_PER_B64 + SEARCH_WARPS - 1) / SEARCH_WARPS, ny);
+        if (sub) k_search_blk<true><<<grid, 32 * SEARCH_WARPS, 0, st>>>(d_jobs, level);
+        else k_search_blk<false><<<grid, 32 * SEARCH_WARPS, 0, st>>>(d_jobs, level);
         launches++;
     };
     int fin_pending = ST_NONE;
@@ -266,25 +264,31 @@ int svtme_launch_picture_me(const PicJob *h_jobs, int n, const PicJob *d_jobs, c
     if (ev_hme1) cudaEventRecord(ev_hme1, st);
 
     // ---- full-pel ----
+    const bool fsub = c.me_search_method == SVTME_SUB_SAD_SEARCH;
     if (!g_fp_search_ctas_per_sm) {
         int k = 0;
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&k, k_fp_search, 32 * FP_WARPS, 0);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&k, k_fp_big<true>, 32 * FP_WARPS, 0);
         g_fp_search_ctas_per_sm = k > 0 ? k : 1;
     }
     const dim3 plan_grid((n_b64 * 8 + FP_WARPS - 1) / FP_WARPS, ny);
-    const int search_grid = n_sm * g_fp_search_ctas_per_sm;
+    const int big_grid = n_sm * g_fp_search_ctas_per_sm;
+    auto fp_round = [&](int phase) {
+        if (fsub) {
+            k_fp<true><<<plan_grid, 32 * FP_WARPS, 0, st>>>(d_jobs, phase);
+            k_fp_big<true><<<big_grid, 32 * FP_WARPS, 0, st>>>(d_jobs);
+        } else {
+            k_fp<false><<<plan_grid, 32 * FP_WARPS, 0, st>>>(d_jobs, phase);
+            k_fp_big<false><<<big_grid, 32 * FP_WARPS, 0, st>>>(d_jobs);
+        }
+        launches += 2;
+    };
     if (any_sr2) {
         // the window of every ref but (0,0) depends on p_sb_best_sad[0][0][0] (motion_estimation.c:1357-1366)
-        k_fp_plan<<<plan_grid, 32 * FP_WARPS, 0, st>>>(d_jobs, 1);
-        k_fp_search<<<search_grid, 32 * FP_WARPS, 0, st>>>(d_jobs);
+        fp_round(1);
         cudaMemsetAsync(j0.fp_counters, 0, 2 * sizeof(uint32_t), st);
-        k_fp_plan<<<plan_grid, 32 * FP_WARPS, 0, st>>>(d_jobs, 2);
-        k_fp_search<<<search_grid, 32 * FP_WARPS, 0, st>>>(d_jobs);
-        launches += 4;
+        fp_round(2);
     } else {
-        k_fp_plan<<<plan_grid, 32 * FP_WARPS, 0, st>>>(d_jobs, 0);
-        k_fp_search<<<search_grid, 32 * FP_WARPS, 0, st>>>(d_jobs);
-        launches += 2;
+        fp_round(0);
     }
     if (ev_fp1) cudaEventRecord(ev_fp1, st);
     k_post<<<dim3(n_b64, ny), POST_THREADS, 0, st>>>(d_jobs);
@@ -339,21 +343,12 @@ __global__ void __launch_bounds__(32 * SEARCH_WARPS) k_kat_search16(const uint8_
     if (lane == 0 && key != HME_KEY_NONE) atomicMin(out_key, key);
 }
 
-// blocks up to 64 wide, any height: the global-memory strip search of k_search_wide
-__global__ void __launch_bounds__(32 * SEARCH_WARPS) k_kat_search_wide(const uint8_t *src, int src_stride, const uint8_t *ref,
-                                                                        int raw_stride, int ref_stride, int bh, int bw, int sa_w,
-                                                                        int sa_h, int strips, unsigned long long *out_key) {
-    const int t = (blockIdx.x * SEARCH_WARPS + (threadIdx.x >> 5)) * 32 + (threadIdx.x & 31);
-    const int n_oct = (sa_w + 7) >> 3;
-    const int strip = t % strips, oy = t / strips;
-    const int y = oy / n_oct, oct = oy - y * n_oct;
-    const bool active = y < sa_h;
-    uint32_t acc[8];
-    warp_search_wide_task(active, ref, raw_stride, ref_stride, src, src_stride, bw, bh, y, oct, strip, strips, acc);
-    if (active && strip == 0) {
-        const unsigned long long key = octet_best_key(acc, y, oct, sa_w);
-        if ((uint32_t)key != 0xffffffffu) atomicMin(out_key, key);
-    }
+// blocks 17..64 wide or taller than 16 rows: the block-parallel search of k_search_blk, one warp
+__global__ void __launch_bounds__(32) k_kat_search_blk(const uint8_t *src, int src_stride, const uint8_t *ref, int raw_stride,
+                                                       int ref_stride, int bh, int bw, int sa_w, int sa_h, int ns_bits, int nb_bits,
+                                                       unsigned long long *out_key) {
+    const unsigned long long key = warp_search_blk<8>(src, src_stride, ref, raw_stride, ref_stride, bw, bh, sa_w, sa_h, ns_bits, nb_bits);
+    if (threadIdx.x == 0) *out_key = key;
 }
 
 int svtme_launch_kat_sad_loop(const uint8_t *d_src, int src_stride, const uint8_t *d_ref, int ref_stride, int bh, int bw,
@@ -369,12 +364,12 @@ int svtme_launch_kat_sad_loop(const uint8_t *d_src, int src_stride, const uint8_
         s16_tile_geometry(sa_w, sa_h, bh, row_step, &tw, &th, &ntx, &nty);
         k_kat_search16<<<(ntx * nty + SEARCH_WARPS - 1) / SEARCH_WARPS, 32 * SEARCH_WARPS, 0, st>>>(
             d_src, src_stride, d_ref, src_stride_raw, row_step, bh, bw, skip, sa_w, sa_h, tw, th, ntx, nty, d_key);
-    } else if (bw <= 64) {
-        // block rows advance by ref_stride, search rows by src_stride_raw: pass them separately
-        const int strips = bw <= 16 ? 1 : (bw <= 32 ? 2 : 4);
-        const int tasks = sa_h * ((sa_w + 7) / 8) * strips;
-        k_kat_search_wide<<<(tasks + 32 * SEARCH_WARPS - 1) / (32 * SEARCH_WARPS), 32 * SEARCH_WARPS, 0, st>>>(
-            d_src, src_stride, d_ref, src_stride_raw, ref_stride, bh, bw, sa_w, sa_h, strips, d_key);
+    } else if (bw <= 64 && bh <= 64) {
+        // lanes = strips x row bands (x search rows): 8 rows per band at most
+        const int ns_bits = bw <= 16 ? 0 : (bw <= 32 ? 1 : 2);
+        int nb_bits = 0;
+        while (nb_bits + ns_bits < 5 && (8 << nb_bits) < bh) nb_bits++;
+        k_kat_search_blk<<<1, 32, 0, st>>>(d_src, src_stride, d_ref, src_stride_raw, ref_stride, bh, bw, sa_w, sa_h, ns_bits, nb_bits, d_key);
     } else {
         const int n = sa_w * sa_h;
         k_kat_sad_loop_generic<<<(n + 127) / 128, 128, 0, st>>>(d_src, src_stride, d_ref, ref_stride, bh, bw, src_stride_raw,
@@ -384,28 +379,27 @@ int svtme_launch_kat_sad_loop(const uint8_t *d_src, int src_stride, const uint8_
 }
 
 // svt_ext_all_sad_calculation_8x8_16x16 / svt_ext_sad_calculation_8x8_16x16: raw SADs of all 85 PUs at
-// n_pos consecutive horizontal positions, through the tile routine of k_fp_search (one warp).
+// n_pos consecutive horizontal positions, through the pass routine of k_fp (one warp).
+template <bool SUB>
 __global__ void __launch_bounds__(32) k_kat_octet(const uint8_t *src, int src_stride, const uint8_t *ref, int ref_stride,
-                                                  int sub, int n_pos, uint32_t *out /*[n_pos][85]*/) {
-    __shared__ __align__(16) uint32_t s_src[64 * 16];
-    __shared__ __align__(16) uint32_t s_win[64 * FP_WIN_STRIDE];
-    const int lane = threadIdx.x;
-    warp_stage_src64(s_src, src, src_stride, sub ? 2 : 1);
+                                                  int n_pos, uint32_t *out /*[n_pos][85]*/) {
+    FpLane<SUB> L;
+    fp_lane_init<SUB>(L, src, src_stride);
     for (int p = 0; p < n_pos; p++) {
-        __syncwarp();
-        stage_rect(s_win, FP_WIN_STRIDE, ref + p, ref_stride, 64, FP_WIN_STRIDE, lane, 32);
-        __syncwarp();
-        FpKeys K;
-        warp_fp_tile(s_win, s_src, 1, 1, sub != 0, K);
-        fp_for_each_key(K, [&](uint32_t m, int pu) {
-            if (lane < 4) out[p * 85 + pu] = (m >> FP_IDX_BITS) << (sub ? 1 : 0);
-        });
+        uint32_t raw[5];
+        fp_eval_pass<SUB>(L, ref + p, ref_stride, 1u, 0u, raw);
+        const uint32_t vals[5] = {raw[0], raw[1], raw[2], raw[3], raw[4]};
+        // same ownership walk as the search: (value, PU)
+        FpLane<SUB> V = L;
+        V.kl = vals[0]; V.kr = vals[1]; V.k16 = vals[2]; V.k32 = vals[3]; V.k64 = vals[4];
+        fp_for_owned<SUB>(V, [&](uint32_t v, int pu) { out[p * 85 + pu] = v << (SUB ? 1 : 0); });
     }
 }
 
 int svtme_launch_kat_octet(const uint8_t *d_src, int src_stride, const uint8_t *d_ref, int ref_stride, int sub, int n_pos,
                            uint32_t *d_out, cudaStream_t st) {
-    k_kat_octet<<<1, 32, 0, st>>>(d_src, src_stride, d_ref, ref_stride, sub, n_pos, d_out);
+    if (sub) k_kat_octet<true><<<1, 32, 0, st>>>(d_src, src_stride, d_ref, ref_stride, n_pos, d_out);
+    else k_kat_octet<false><<<1, 32, 0, st>>>(d_src, src_stride, d_ref, ref_stride, n_pos, d_out);
     return 1;
 }
 

@@ -87,16 +87,18 @@ __device__ inline unsigned long long warp_search16_tile(uint32_t *win, const uin
                                                         int n_rows, int row_step, bool skip_lines) {
     const int lane   = threadIdx.x & 31;
     const int n_oct  = (tw + 7) >> 3;
-    const int stride = 2 * n_oct + 4; // words per staged row
+    const int wpr    = 2 * n_oct + 4;                      // words per staged row
+    const int stride = (wpr & 15) == 0 ? wpr + 2 : wpr;    // a row pitch of 16k words would put every row on the same banks
     const int span   = row_step * (n_rows - 1);
-    stage_rect(win, stride, ref + (size_t)y0 * ref_stride + x0, ref_stride, th + span, stride, lane, 32);
+    stage_rect(win, stride, ref + (size_t)y0 * ref_stride + x0, ref_stride, th + span, wpr, lane, 32);
     __syncwarp();
     const bool     partial = bw < 16;
     const uint32_t m0 = lo_bytes_mask(bw), m1 = lo_bytes_mask(bw - 4), m2 = lo_bytes_mask(bw - 8), m3 = lo_bytes_mask(bw - 12);
     uint32_t best_sad = 0xffffff, best_idx = 0xffffffffu;
-    const int n_task = n_oct * th;
-    for (int t = lane; t < n_task; t += 32) {
-        const int yy = t / n_oct, oct = t - yy * n_oct;
+    int yy = lane / n_oct, oct = lane - yy * n_oct;
+    const int dyy = 32 / n_oct, doct = 32 - dyy * n_oct;
+    for (; yy < th; yy += dyy, oct += doct) {
+        if (oct >= n_oct) { oct -= n_oct; yy++; if (yy >= th) break; }
         const int y  = y0 + yy;
         if (skip_lines && (y & 1) == 0) continue;
         uint32_t acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
@@ -248,36 +250,142 @@ __device__ __forceinline__ unsigned long long octet_best_key(const uint32_t (&ac
     return ((unsigned long long)best_sad << 32) | best_idx;
 }
 
-// ---- k_search_wide ---------------------------------------------------------------------------
-// level: 1 (1/4 plane, 32-wide blocks, 2 strips) or 2 (full plane, 64-wide, 4 strips).
-// tpj: task slots per job (power of two >= sa_h_max * n_oct_max * strips).
-__global__ void __launch_bounds__(32 * SEARCH_WARPS) k_search_wide(const PicJob *__restrict__ jobs, int level, int tpj) {
+// ---- block-parallel search for wide blocks (HME level 1 / 2) -----------------------------------
+// Windows here are tiny (8x3 .. 16x16 positions) and blocks large (32x16 .. 64x64 samples), so the
+// lanes are spread over the BLOCK instead of over positions: lane = (ypos, band, strip) with
+// NY*NB*NS = 32; a lane sums RB rows of its 16-pixel strip for 8 consecutive positions of search row
+// y0+ypos, straight from global memory (7 aligned words per row + one funnel shift per word), and
+// shfl_xor adds bands and strips. No shared memory, no staging latency chain, all loads of a pass
+// in flight at once. Leaders (band 0, strip 0) keep the running best of their search rows.
+template <int RB>
+struct BlkLane {
+    uint32_t src[RB][4];
+    uint32_t m[4];     // byte masks of this strip (block narrower than 16*NS)
+    int      strip, band, ypos, row0, n_rows;
+    bool     full;
+};
+
+template <int RB>
+__device__ __forceinline__ void blk_lane_init(BlkLane<RB> &L, const uint8_t *src, int src_blk_stride, int bw, int n_rows,
+                                              int ns_bits, int nb_bits) {
+    const int lane = threadIdx.x & 31;
+    L.strip = lane & ((1 << ns_bits) - 1);
+    L.band  = (lane >> ns_bits) & ((1 << nb_bits) - 1);
+    L.ypos  = lane >> (ns_bits + nb_bits);
+    L.row0  = L.band * RB;
+    L.n_rows = n_rows;
+    const int rem = bw - 16 * L.strip;
+    L.full = rem >= 16;
+    L.m[0] = lo_bytes_mask(rem); L.m[1] = lo_bytes_mask(rem - 4); L.m[2] = lo_bytes_mask(rem - 8); L.m[3] = lo_bytes_mask(rem - 12);
+#pragma unroll
+    for (int q = 0; q < RB; q++)
+#pragma unroll
+        for (int k = 0; k < 4; k++)
+            L.src[q][k] = (L.row0 + q < n_rows) ? (ldg_u32_unaligned(src + (size_t)(L.row0 + q) * src_blk_stride + 16 * L.strip + 4 * k) & L.m[k]) : 0u;
+}
+
+// acc[p] = SAD of the whole block at positions (x+p, y) for the lanes of that ypos group
+template <int RB>
+__device__ __forceinline__ void blk_eval_pass(const BlkLane<RB> &L, const uint8_t *ref /* sample aligned with block (0,0) at position x,y */,
+                                              int ref_blk_stride, bool active, int ns_bits, int nb_bits, uint32_t (&acc)[8]) {
+#pragma unroll
+    for (int p = 0; p < 8; p++) acc[p] = 0;
+    if (active) {
+        const uint8_t *g = ref + (size_t)L.row0 * ref_blk_stride + 16 * L.strip;
+        uint32_t gw[RB][7];
+        uint32_t sa[RB];
+#pragma unroll
+        for (int q = 0; q < RB; q++) {
+            const uintptr_t a = (uintptr_t)(g + (size_t)q * ref_blk_stride);
+            const uint32_t *qp = (const uint32_t *)(a & ~(uintptr_t)3);
+            sa[q] = (uint32_t)(a & 3) * 8;
+            const bool ok = L.row0 + q < L.n_rows;
+#pragma unroll
+            for (int k = 0; k < 7; k++) gw[q][k] = ok ? __ldg(qp + k) : 0u;
+        }
+#pragma unroll
+        for (int q = 0; q < RB; q++) {
+            uint32_t w[6];
+#pragma unroll
+            for (int k = 0; k < 6; k++) w[k] = __funnelshift_r(gw[q][k], gw[q][k + 1], sa[q]);
+            if (L.full) {
+                strip16_sad8(w, L.src[q], acc);
+            } else {
+#pragma unroll
+                for (int p = 0; p < 8; p++) {
+                    const int o = p >> 2, shf = (p & 3) * 8;
+                    const uint32_t v0 = shf ? __funnelshift_r(w[o], w[o + 1], shf) : w[o];
+                    const uint32_t v1 = shf ? __funnelshift_r(w[o + 1], w[o + 2], shf) : w[o + 1];
+                    const uint32_t v2 = shf ? __funnelshift_r(w[o + 2], w[o + 3], shf) : w[o + 2];
+                    const uint32_t v3 = shf ? __funnelshift_r(w[o + 3], w[o + 4], shf) : w[o + 3];
+                    acc[p] += __vsadu4(v0 & L.m[0], L.src[q][0]) + __vsadu4(v1 & L.m[1], L.src[q][1]) +
+                        __vsadu4(v2 & L.m[2], L.src[q][2]) + __vsadu4(v3 & L.m[3], L.src[q][3]);
+                }
+            }
+        }
+    }
+    const int gbits = ns_bits + nb_bits;
+#pragma unroll
+    for (int p = 0; p < 8; p++) {
+        if (gbits >= 1) acc[p] += __shfl_xor_sync(0xffffffffu, acc[p], 1);
+        if (gbits >= 2) acc[p] += __shfl_xor_sync(0xffffffffu, acc[p], 2);
+        if (gbits >= 3) acc[p] += __shfl_xor_sync(0xffffffffu, acc[p], 4);
+        if (gbits >= 4) acc[p] += __shfl_xor_sync(0xffffffffu, acc[p], 8);
+        if (gbits >= 5) acc[p] += __shfl_xor_sync(0xffffffffu, acc[p], 16);
+    }
+}
+
+// whole search of one job by one warp; returns the best key (all lanes)
+template <int RB>
+__device__ inline unsigned long long warp_search_blk(const uint8_t *src, int src_blk_stride, const uint8_t *ref, int search_stride,
+                                                     int ref_blk_stride, int bw, int n_rows, int sa_w, int sa_h, int ns_bits,
+                                                     int nb_bits) {
+    BlkLane<RB> L;
+    blk_lane_init<RB>(L, src, src_blk_stride, bw, n_rows, ns_bits, nb_bits);
+    const int ny = 32 >> (ns_bits + nb_bits); // search rows per pass
+    const int n_oct = (sa_w + 7) >> 3;
+    uint32_t best_sad = 0xffffff, best_idx = 0xffffffffu;
+    for (int y0 = 0; y0 < sa_h; y0 += ny) {
+        const int  y      = y0 + L.ypos;
+        const bool active = y < sa_h;
+        for (int oct = 0; oct < n_oct; oct++) {
+            uint32_t acc[8];
+            blk_eval_pass<RB>(L, ref + (size_t)y * search_stride + 8 * oct, ref_blk_stride, active, ns_bits, nb_bits, acc);
+            if (active && L.band == 0 && L.strip == 0) {
+#pragma unroll
+                for (int p = 0; p < 8; p++) {
+                    const int x = 8 * oct + p;
+                    if (x < sa_w && acc[p] < best_sad) {
+                        best_sad = acc[p];
+                        best_idx = (uint32_t)(y * sa_w + x);
+                    }
+                }
+            }
+        }
+    }
+    return warp_min_u64(((unsigned long long)best_sad << 32) | best_idx);
+}
+
+// ---- k_search_blk ----------------------------------------------------------------------------
+// one warp per job slot; level 1: 1/4 plane (32-wide blocks: 2 strips x 4 bands x 4 search rows),
+// level 2: full plane (64-wide blocks: 4 strips x 8 bands x 1 search row)
+template <bool SUB>
+__global__ void __launch_bounds__(32 * SEARCH_WARPS) k_search_blk(const PicJob *__restrict__ jobs, int level) {
     const PicJob &job = jobs[blockIdx.y];
     const int lane = threadIdx.x & 31;
-    const long long t = ((long long)blockIdx.x * SEARCH_WARPS + (threadIdx.x >> 5)) * 32 + lane;
-    const int strips = level == 1 ? 2 : 4, sbits = level == 1 ? 1 : 2;
-    const long long js = t / tpj;
-    const int local = (int)(t - js * tpj);
-    const bool in_range = js < (long long)job.n_b64 * HME_JOBS_PER_B64;
-    const HmeJobG *jp = in_range ? &job.hme_jobs[js] : &job.hme_jobs[0];
-    const int sa_w = jp->sa_w, sa_h = jp->sa_h;
-    const int n_oct = (sa_w + 7) >> 3;
-    const int strip = local & (strips - 1), oy = local >> sbits;
-    const int y = n_oct > 0 ? oy / n_oct : 0, oct = n_oct > 0 ? oy - y * n_oct : 0;
-    const bool active = in_range && jp->active && sa_w > 0 && y < sa_h;
-    const int b = in_range ? (int)(js / HME_JOBS_PER_B64) : 0;
+    const int slot = blockIdx.x * SEARCH_WARPS + (threadIdx.x >> 5);
+    if (slot >= job.n_b64 * HME_JOBS_PER_B64) return;
+    HmeJobG &j = job.hme_jobs[slot];
+    if (!j.active || j.sa_w <= 0 || j.sa_h <= 0) return;
+    const int b = slot / HME_JOBS_PER_B64;
     const B64Geo g = b64_geo(job, b);
-    const bool sub = job.pp.ctrls.hme_search_method == SVTME_SUB_SAD_SEARCH;
-    const int shift = level == 1 ? 1 : 0;
-    const int bw = g.b64_w >> shift, bh = g.b64_h >> shift, rows = sub ? bh >> 1 : bh;
+    const int row_step = SUB ? 2 : 1, shift = level == 1 ? 1 : 0;
+    const int bw = g.b64_w >> shift, rows = SUB ? (g.b64_h >> shift) >> 1 : (g.b64_h >> shift);
     const DevPlane &sp = job.src.lvl[level == 1 ? 1 : 0];
     const uint8_t *src = sp.buf + (size_t)(sp.org_y + (g.org_y >> shift)) * sp.stride + sp.org_x + (g.org_x >> shift);
-    uint32_t acc[8];
-    const int row_step = sub ? 2 : 1;
-    warp_search_wide_task(active, jp->ref, jp->ref_stride, row_step * jp->ref_stride, src, row_step * sp.stride, bw, rows, y, oct,
-                          strip, strips, acc);
-    if (active && strip == 0) {
-        const unsigned long long key = octet_best_key(acc, y, oct, sa_w);
-        if ((uint32_t)key != 0xffffffffu) atomicMin(&job.hme_jobs[js].key, key);
-    }
+    constexpr int RB = SUB ? 4 : 8;
+    const unsigned long long key = level == 1
+        ? warp_search_blk<RB>(src, row_step * sp.stride, j.ref, j.ref_stride, row_step * j.ref_stride, bw, rows, j.sa_w, j.sa_h, 1, 2)
+        : warp_search_blk<RB>(src, row_step * sp.stride, j.ref, j.ref_stride, row_step * j.ref_stride, bw, rows, j.sa_w, j.sa_h, 2, 3);
+    if (lane == 0) j.key = key;
 }

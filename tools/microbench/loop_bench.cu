@@ -30,7 +30,7 @@ __global__ void k_loop(uint32_t *out, long long *cycles, int stride) {
         for (int rr = 0; rr < ROWS; rr++, row += 2 * stride) {
             const uint4 sv = *(const uint4 *)(src + 4 * rr);
             const uint32_t s[4] = {sv.x, sv.y, sv.z, sv.w};
-            if (V == 0 || V == 4) {
+            if (V == 0 || V == 4 || V == 5 || V == 6) {
                 const uint2 a = *(const uint2 *)(row), b = *(const uint2 *)(row + 2), c = *(const uint2 *)(row + 4);
                 const uint32_t w[6] = {a.x, a.y, b.x, b.y, c.x, c.y};
 #pragma unroll
@@ -40,6 +40,8 @@ __global__ void k_loop(uint32_t *out, long long *cycles, int stride) {
                     for (int k = 0; k < 4; k++) {
                         uint32_t v;
                         if (V == 0) v = sh ? __funnelshift_r(w[o + k], w[o + k + 1], sh) : w[o + k];
+                        else if (V == 5) v = sh ? __umulhi(w[o + k], 1u << (32 - sh)) + w[o + k + 1] * (1u << (32 - sh)) : w[o + k];
+                        else if (V == 6) v = sh ? (uint32_t)(((unsigned long long)w[o + k] * (1u << (32 - sh))) >> 32) + w[o + k + 1] * (1u << (32 - sh)) : w[o + k];
                         else v = sh ? __byte_perm(w[o + k], w[o + k + 1], sh == 8 ? 0x4321 : (sh == 16 ? 0x5432 : 0x6543)) : w[o + k];
                         accv[p] += __vsadu4(v, s[k]);
                     }
@@ -91,7 +93,7 @@ int run(const char *name, int nsm, int nthr, int ctas_per_sm, double vabs_per_ro
     const int smem = (4 * 4096 + 64) * 4;
     CK(cudaFuncSetAttribute(k_loop<V>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     const int nblk = nsm * ctas_per_sm;
-    for (int stride : {6, 18, 36}) {
+    for (int stride : {18}) {
         k_loop<V><<<nblk, nthr, smem>>>(d_out, d_cyc, stride);
         CK(cudaDeviceSynchronize());
         k_loop<V><<<nblk, nthr, smem>>>(d_out, d_cyc, stride);
@@ -112,10 +114,11 @@ int main() {
     uint32_t *d_out; long long *d_cyc;
     CK(cudaMalloc(&d_out, sizeof(uint32_t) * nsm * 8 * 1024));
     CK(cudaMalloc(&d_cyc, sizeof(long long) * nsm * 8));
-    for (int cps : {1, 2, 3}) {
+    for (int cps : {2, 3, 4}) {
         const int nthr = 256;
         run<0>("V0 8pos SHF", nsm, nthr, cps, 32, d_out, d_cyc);
-        run<4>("V4 8pos PRMT", nsm, nthr, cps, 32, d_out, d_cyc);
+        run<5>("V5 8pos umulhi+imad shift", nsm, nthr, cps, 32, d_out, d_cyc);
+        run<6>("V6 8pos wide-mul shift", nsm, nthr, cps, 32, d_out, d_cyc);
         run<1>("V1 16pos SHF", nsm, nthr, cps, 64, d_out, d_cyc);
         run<2>("V2 8pos preshifted copies", nsm, nthr, cps, 32, d_out, d_cyc);
         run<3>("V3 registers only", nsm, nthr, cps, 32, d_out, d_cyc);
