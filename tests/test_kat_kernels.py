@@ -1,5 +1,6 @@
 """RTCD-kernel known-answer tests.
-  * CPU (-m "not gpu"): oracle kernels vs the reference's C and SIMD kernels (needs oracle/_ref).
+  * CPU (-m "not gpu"): oracle kernels vs the reference's C and SIMD kernels (needs oracle/_ref), and vs
+    the committed outputs of the reference's C kernels (tests/golden/kat_rtcd.npz) where it is absent.
   * GPU (-m gpu): the CUDA C-ABI entry points vs the oracle kernels."""
 import os
 
@@ -10,7 +11,11 @@ import kat_cases as kc
 from kat_runner import Impl, same
 from oracle import pyoracle as po
 
+import golden_lib as gl
+
 HAVE_REF = os.path.isdir(po.REFERENCE_ROOT) or po.ref_available()
+KAT_GOLDEN = os.path.join(gl.GOLDEN_DIR, "kat_rtcd.npz")
+GOLDEN_CTX = {"peer": None}  # Recorder (make_golden.py) or Replayer (test_oracle_kernels_match_golden)
 
 
 def impls(kind):
@@ -18,6 +23,8 @@ def impls(kind):
     orc = Impl(po.oracle_lib(), "orc_")
     if kind == "cpu":
         return orc, [Impl(po.ref_lib(), "ref_", simd) for simd in (0, 1, 2)]
+    if kind == "golden":
+        return orc, [GOLDEN_CTX["peer"]]
     import svtme_b200 as me
     return Impl(me.lib(), "svtme_"), [orc]
 
@@ -128,6 +135,16 @@ RUNNERS = [run_sad_loop, run_all_sad, run_eight_sad, run_ext_sad, run_nxm_init_d
 @pytest.mark.parametrize("runner", RUNNERS, ids=lambda f: f.__name__[4:])
 def test_oracle_kernels_match_reference(orc, runner):
     runner("cpu")
+
+
+@pytest.mark.parametrize("runner", RUNNERS, ids=lambda f: f.__name__[4:])
+def test_oracle_kernels_match_golden(orc, runner):
+    """same runners, the reference's recorded outputs instead of the reference (tests/golden/make_golden.py)"""
+    if not os.path.exists(KAT_GOLDEN):
+        pytest.skip("tests/golden/kat_rtcd.npz not generated")
+    peer = GOLDEN_CTX["peer"] = gl.Replayer(np.load(KAT_GOLDEN), runner.__name__)
+    runner("golden")
+    assert peer.pos == len(peer.calls) and peer.pos > 0
 
 
 @pytest.mark.gpu
