@@ -178,8 +178,8 @@ extern "C" uint32_t svtme_session_sync(SvtMeSession *s) {
     return SVTME_OK;
 }
 
-static uint32_t finish_upload(SvtMeSession *s, int32_t pic_id) {
-    s->launches += (uint64_t)svtme_launch_build_pyramid(s->pics[pic_id], s->stream);
+static uint32_t finish_upload(SvtMeSession *s, int32_t pic_id, int mode, const void *d_in, int in_stride) {
+    s->launches += (uint64_t)svtme_launch_build_pyramid(s->pics[pic_id], mode, d_in, in_stride, s->stream);
     CU_TRY(cudaGetLastError());
     s->pic_valid[pic_id] = 1;
     return SVTME_OK;
@@ -192,17 +192,14 @@ extern "C" uint32_t svtme_picture_upload(SvtMeSession *s, int32_t pic_id, const 
     const DevPlane &f = s->pics[pic_id].lvl[0];
     uint8_t *interior = const_cast<uint8_t *>(f.buf) + (size_t)f.org_y * f.stride + f.org_x;
     CU_TRY(cudaMemcpy2DAsync(interior, (size_t)f.stride, luma, stride, (size_t)s->w, (size_t)s->h, cudaMemcpyHostToDevice, s->stream));
-    return finish_upload(s, pic_id);
+    return finish_upload(s, pic_id, 1, nullptr, 0);
 }
 
 extern "C" uint32_t svtme_picture_upload_device(SvtMeSession *s, int32_t pic_id, const uint8_t *d_luma, uint32_t stride) {
     if (!s || !d_luma || pic_id < 0 || pic_id >= s->max_pics || stride < (uint32_t)s->w) return SVTME_ERR_BAD_PARAMETER;
     std::lock_guard<std::mutex> g(s->mu);
     CU_TRY(cudaSetDevice(s->device));
-    const DevPlane &f = s->pics[pic_id].lvl[0];
-    uint8_t *interior = const_cast<uint8_t *>(f.buf) + (size_t)f.org_y * f.stride + f.org_x;
-    s->launches += (uint64_t)svtme_launch_copy2d(d_luma, (int)stride, interior, f.stride, s->w, s->h, s->stream);
-    return finish_upload(s, pic_id);
+    return finish_upload(s, pic_id, 0, d_luma, (int)stride);
 }
 
 extern "C" uint32_t svtme_picture_upload_10bit(SvtMeSession *s, int32_t pic_id, const uint16_t *luma16, uint32_t stride_in_samples) {
@@ -215,10 +212,7 @@ extern "C" uint32_t svtme_picture_upload_10bit(SvtMeSession *s, int32_t pic_id, 
     }
     CU_TRY(cudaMemcpy2DAsync(s->d_in16, (size_t)s->w * 2, luma16, (size_t)stride_in_samples * 2, (size_t)s->w * 2, (size_t)s->h,
                              cudaMemcpyHostToDevice, s->stream));
-    const DevPlane &f = s->pics[pic_id].lvl[0];
-    uint8_t *interior = const_cast<uint8_t *>(f.buf) + (size_t)f.org_y * f.stride + f.org_x;
-    s->launches += (uint64_t)svtme_launch_unpack10(s->d_in16, s->w, interior, f.stride, s->w, s->h, s->stream);
-    return finish_upload(s, pic_id);
+    return finish_upload(s, pic_id, 2, s->d_in16, s->w);
 }
 
 extern "C" uint32_t svtme_picture_download_plane(SvtMeSession *s, int32_t pic_id, int level, uint8_t *dst, size_t dst_capacity,
@@ -227,14 +221,17 @@ extern "C" uint32_t svtme_picture_download_plane(SvtMeSession *s, int32_t pic_id
     std::lock_guard<std::mutex> g(s->mu);
     CU_TRY(cudaSetDevice(s->device));
     const DevPlane &p = s->pics[pic_id].lvl[level];
-    const size_t W = (size_t)p.width + 2 * p.org_x, H = (size_t)p.height + 2 * p.org_y;
-    if (dst_capacity < W * H) return SVTME_ERR_BAD_PARAMETER;
-    CU_TRY(cudaMemcpy2DAsync(dst, W, p.buf, (size_t)p.stride, W, H, cudaMemcpyDeviceToHost, s->stream));
+    // exported with the padding of the reference's buffers (72 / 32 / 16); the store may pad wider for alignment
+    static const int export_pad[3] = {72, SVTME_QUARTER_PAD, SVTME_SIXTEENTH_PAD};
+    const int ep = export_pad[level], skip = p.org_x - ep;
+    const size_t W = (size_t)p.width + 2 * ep, H = (size_t)p.height + 2 * ep;
+    if (dst_capacity < W * H || skip < 0) return SVTME_ERR_BAD_PARAMETER;
+    CU_TRY(cudaMemcpy2DAsync(dst, W, p.buf + (size_t)skip * p.stride + skip, (size_t)p.stride, W, H, cudaMemcpyDeviceToHost, s->stream));
     CU_TRY(cudaStreamSynchronize(s->stream));
     if (stride) *stride = (uint32_t)W;
     if (rows) *rows = (uint32_t)H;
-    if (org_x) *org_x = (uint32_t)p.org_x;
-    if (org_y) *org_y = (uint32_t)p.org_y;
+    if (org_x) *org_x = (uint32_t)ep;
+    if (org_y) *org_y = (uint32_t)ep;
     return SVTME_OK;
 }
 

@@ -18,7 +18,7 @@
 
 #include "svtme_b200.h"
 
-#define SVTME_FULL_PAD 72
+#define SVTME_FULL_PAD 80 /* >= 64 + 4 (the reference pads b64 + ME_FILTER_TAP); 80 keeps b64 origins 16-byte aligned */
 #define SVTME_QUARTER_PAD 32
 #define SVTME_SIXTEENTH_PAD 16
 #define SVTME_SLAB_SLACK 512
@@ -127,6 +127,15 @@ __device__ __forceinline__ uint32_t ldg_u32_unaligned(const uint8_t *p) {
     return __funnelshift_r(lo, hi, (uint32_t)(a & 3) * 8);
 }
 
+// c + sum of |a.byte[i] - b.byte[i]|: one VABSDIFF4.U8.ACC. Written as PTX so that the accumulate operand is
+// used: from `acc += __vsadu4(a, b)` the compiler builds VABSDIFF4(.., RZ) pairs joined by IADD3 (one
+// extra ALU-pipe instruction per two SADs on the pipe that bounds these kernels).
+__device__ __forceinline__ uint32_t sad4_acc(uint32_t a, uint32_t b, uint32_t c) {
+    uint32_t d;
+    asm("vabsdiff4.u32.u32.u32.add %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+
 // acc[p] += SAD of the 16-byte strip s[0..3] against the strip starting p bytes into w[0..5]
 // for the 8 consecutive search positions p = 0..7. 32 VABSDIFF4.U8.ACC + 24 SHF.
 __device__ __forceinline__ void strip16_sad8(const uint32_t (&w)[6], const uint32_t (&s)[4], uint32_t (&acc)[8]) {
@@ -136,7 +145,7 @@ __device__ __forceinline__ void strip16_sad8(const uint32_t (&w)[6], const uint3
 #pragma unroll
         for (int k = 0; k < 4; k++) {
             const uint32_t v = sh ? __funnelshift_r(w[o + k], w[o + k + 1], sh) : w[o + k];
-            acc[p] += __vsadu4(v, s[k]);
+            acc[p] = sad4_acc(v, s[k], acc[p]);
         }
     }
 }
@@ -151,9 +160,9 @@ __device__ __forceinline__ void strip16_sad8_split(const uint32_t (&w)[6], const
         for (int k = 0; k < 4; k++) {
             const uint32_t v = sh ? __funnelshift_r(w[o + k], w[o + k + 1], sh) : w[o + k];
             if (k < 2)
-                accl[p] += __vsadu4(v, s[k]);
+                accl[p] = sad4_acc(v, s[k], accl[p]);
             else
-                accr[p] += __vsadu4(v, s[k]);
+                accr[p] = sad4_acc(v, s[k], accr[p]);
         }
     }
 }

@@ -12,29 +12,101 @@
 // pic_analysis_process.c:131-161, :2139-2196), 10-bit -> 8 MSBs (pack_unpack_c.c:77-116)
 // ------------------------------------------------------------------------------------------
 
-// Fill the padding of a plane whose interior is already in place: every padded sample is the
-// interior sample at the clamped coordinate (what horizontal-then-vertical replication produces).
-__global__ void k_pad_plane(uint8_t *buf, int stride, int pad, int w, int h) {
-    const int W = w + 2 * pad, H = h + 2 * pad;
-    const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
-    if (x >= W || y >= H) return;
-    const int ix = x - pad, iy = y - pad;
-    if (ix >= 0 && ix < w && iy >= 0 && iy < h) return;
-    const int cx = min(max(ix, 0), w - 1), cy = min(max(iy, 0), h - 1);
-    buf[(size_t)y * stride + x] = buf[(size_t)(cy + pad) * stride + cx + pad];
+// One pass over the input builds all three interiors. A thread owns an 8x4 patch of the full-resolution
+// picture: it reads 4 x 8 samples (8-bit, or 16-bit words holding 10-bit samples: 8 MSBs kept,
+// pack_unpack_c.c:77-116), writes them into the full plane unless they already are there (host uploads
+// land in the plane directly), and writes the 4x2 quarter and 2x1 sixteenth samples they decimate to:
+// out = (a + b + c + d + 2) >> 2 per 2x2 box, the sixteenth plane from the ROUNDED quarter samples
+// (pic_operators.c:338-384 applied twice, pic_analysis_process.c:131-161).
+// MODE 0: 8-bit input in `in`; 1: interior already in place; 2: 16-bit input.
+template <int MODE>
+__global__ void __launch_bounds__(256) k_ingest(const void *in, int in_stride /*samples*/, DevPic pic) {
+    const DevPlane &f = pic.lvl[0], &q = pic.lvl[1], &s = pic.lvl[2];
+    const int px = blockIdx.x * blockDim.x + threadIdx.x, py = blockIdx.y * blockDim.y + threadIdx.y;
+    const int x = 8 * px, y = 4 * py;
+    if (x >= f.width || y >= f.height) return;
+    uint8_t *fi = const_cast<uint8_t *>(f.buf) + (size_t)(f.org_y + y) * f.stride + f.org_x + x; // 8-byte aligned
+    uint2 r[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        if (MODE == 1) {
+            r[k] = *(const uint2 *)(fi + (size_t)k * f.stride);
+        } else if (MODE == 0) {
+            const uint8_t *p = (const uint8_t *)in + (size_t)(y + k) * in_stride + x;
+            if ((((uintptr_t)p) & 7) == 0) {
+                r[k] = __ldg((const uint2 *)p);
+            } else {
+                r[k].x = ldg_u32_unaligned(p);
+                r[k].y = ldg_u32_unaligned(p + 4);
+            }
+        } else {
+            const uint16_t *p = (const uint16_t *)in + (size_t)(y + k) * in_stride + x;
+            uint32_t v[8];
+#pragma unroll
+            for (int i = 0; i < 8; i++) v[i] = (uint32_t)(__ldg(p + i) >> 2) & 0xffu;
+            r[k].x = v[0] | (v[1] << 8) | (v[2] << 16) | (v[3] << 24);
+            r[k].y = v[4] | (v[5] << 8) | (v[6] << 16) | (v[7] << 24);
+        }
+        if (MODE != 1) *(uint2 *)(fi + (size_t)k * f.stride) = r[k];
+    }
+    // quarter: 4 samples per row pair. Bytes of a word pair up as (0,1) and (2,3).
+    uint32_t qrow[2];
+#pragma unroll
+    for (int k = 0; k < 2; k++) {
+        const uint2 a = r[2 * k], b = r[2 * k + 1];
+        const uint32_t w[2] = {a.x, a.y}, v[2] = {b.x, b.y};
+        uint32_t out = 0;
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            const uint32_t wa = w[i >> 1] >> (16 * (i & 1)), wb = v[i >> 1] >> (16 * (i & 1));
+            const uint32_t sum = (wa & 0xff) + ((wa >> 8) & 0xff) + (wb & 0xff) + ((wb >> 8) & 0xff);
+            out |= ((sum + 2) >> 2) << (8 * i);
+        }
+        qrow[k] = out;
+        *(uint32_t *)(const_cast<uint8_t *>(q.buf) + (size_t)(q.org_y + (y >> 1) + k) * q.stride + q.org_x + (x >> 1)) = out;
+    }
+    uint32_t s16 = 0;
+#pragma unroll
+    for (int i = 0; i < 2; i++) {
+        const uint32_t wa = qrow[0] >> (16 * i), wb = qrow[1] >> (16 * i);
+        const uint32_t sum = (wa & 0xff) + ((wa >> 8) & 0xff) + (wb & 0xff) + ((wb >> 8) & 0xff);
+        s16 |= ((sum + 2) >> 2) << (8 * i);
+    }
+    *(uint16_t *)(const_cast<uint8_t *>(s.buf) + (size_t)(s.org_y + (y >> 2)) * s.stride + s.org_x + (x >> 2)) = (uint16_t)s16;
 }
 
-// dst (incl. its padding) <- 2x2 box decimation of the interior of src; step 2 only.
-// out[x,y] = (in[2x,2y] + in[2x+1,2y] + in[2x,2y+1] + in[2x+1,2y+1] + 2) >> 2
-__global__ void k_downsample2(const uint8_t *src, int sstride, int spad, uint8_t *dst, int dstride, int dpad, int dw,
-                              int dh) {
-    const int W = dw + 2 * dpad, H = dh + 2 * dpad;
-    const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
-    if (x >= W || y >= H) return;
-    const int cx = min(max(x - dpad, 0), dw - 1), cy = min(max(y - dpad, 0), dh - 1);
-    const uint8_t *p = src + (size_t)(2 * cy + spad) * sstride + 2 * cx + spad;
-    const uint32_t s = (uint32_t)p[0] + p[1] + p[sstride] + p[sstride + 1];
-    dst[(size_t)y * dstride + x] = (uint8_t)((s + 2) >> 2);
+// Replicate padding of the three planes in one launch (blockIdx.z = level): every padded sample is the
+// interior sample at the clamped coordinate. A thread writes one aligned 4-byte group of a padded row;
+// rows that cross the interior only have their left and right bands visited.
+__global__ void __launch_bounds__(128) k_pad_planes(DevPic pic) {
+    const DevPlane &p = pic.lvl[blockIdx.z];
+    const int pad = p.org_x, w = p.width, h = p.height;
+    const int W = w + 2 * pad, H = h + 2 * pad, W4 = (W + 3) >> 2;
+    const int y = blockIdx.y;
+    if (y >= H) return;
+    const bool band = y < pad || y >= pad + h;
+    const int lg = pad >> 2;                       // groups wholly left of the interior (pads are multiples of 4)
+    const int rg0 = (pad + w) >> 2;                // first group that touches the right padding
+    int g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (!band) {
+        const int n = lg + (W4 - rg0);
+        if (g >= n) return;
+        if (g >= lg) g = rg0 + (g - lg);
+    } else if (g >= W4) {
+        return;
+    }
+    uint8_t *row = const_cast<uint8_t *>(p.buf) + (size_t)y * p.stride;
+    const uint8_t *srow = p.buf + (size_t)(min(max(y - pad, 0), h - 1) + pad) * p.stride + pad;
+    const int x0 = 4 * g - pad; // interior coordinate of the group's first byte
+    uint32_t v;
+    if (x0 >= 0 && x0 + 3 < w) {
+        v = *(const uint32_t *)(srow + x0);
+    } else {
+        v = 0;
+#pragma unroll
+        for (int i = 0; i < 4; i++) v |= (uint32_t)srow[min(max(x0 + i, 0), w - 1)] << (8 * i);
+    }
+    *(uint32_t *)(row + 4 * g) = v;
 }
 
 // generic svt_aom_downsample_2d_c semantics (any step), for the RTCD-signature wrapper
@@ -49,39 +121,18 @@ __global__ void k_downsample_generic(const uint8_t *in, int in_stride, int in_w,
     out[(size_t)oy * out_stride + ox] = (uint8_t)((s + 2) >> 2);
 }
 
-__global__ void k_unpack10(const uint16_t *in, int in_stride, uint8_t *out, int out_stride, int w, int h) {
-    const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
-    if (x < w && y < h) out[(size_t)y * out_stride + x] = (uint8_t)(in[(size_t)y * in_stride + x] >> 2);
-}
-
-__global__ void k_copy2d(const uint8_t *in, int in_stride, uint8_t *out, int out_stride, int w, int h) {
-    const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
-    if (x < w && y < h) out[(size_t)y * out_stride + x] = in[(size_t)y * in_stride + x];
-}
-
 static inline dim3 grid2d(int w, int h, int bx) { return dim3((unsigned)((w + bx - 1) / bx), (unsigned)h, 1); }
 
-int svtme_launch_build_pyramid(const DevPic &pic, cudaStream_t st) {
-    const DevPlane &f = pic.lvl[0], &q = pic.lvl[1], &s = pic.lvl[2];
-    k_pad_plane<<<grid2d(f.width + 2 * f.org_x, f.height + 2 * f.org_y, 256), 256, 0, st>>>(
-        const_cast<uint8_t *>(f.buf), f.stride, f.org_x, f.width, f.height);
-    k_downsample2<<<grid2d(q.width + 2 * q.org_x, q.height + 2 * q.org_y, 256), 256, 0, st>>>(
-        f.buf, f.stride, f.org_x, const_cast<uint8_t *>(q.buf), q.stride, q.org_x, q.width, q.height);
-    k_downsample2<<<grid2d(s.width + 2 * s.org_x, s.height + 2 * s.org_y, 256), 256, 0, st>>>(
-        q.buf, q.stride, q.org_x, const_cast<uint8_t *>(s.buf), s.stride, s.org_x, s.width, s.height);
-    return 3;
-}
-
-int svtme_launch_unpack10(const uint16_t *d_in, int in_stride, uint8_t *d_out, int out_stride, int w, int h,
-                          cudaStream_t st) {
-    k_unpack10<<<grid2d(w, h, 256), 256, 0, st>>>(d_in, in_stride, d_out, out_stride, w, h);
-    return 1;
-}
-
-int svtme_launch_copy2d(const uint8_t *d_in, int in_stride, uint8_t *d_out, int out_stride, int w, int h,
-                        cudaStream_t st) {
-    k_copy2d<<<grid2d(w, h, 256), 256, 0, st>>>(d_in, in_stride, d_out, out_stride, w, h);
-    return 1;
+// mode 0: 8-bit device input, 1: the full-resolution interior is already in the plane, 2: 16-bit device input
+int svtme_launch_build_pyramid(const DevPic &pic, int mode, const void *d_in, int in_stride, cudaStream_t st) {
+    const DevPlane &f = pic.lvl[0];
+    const dim3 blk(32, 8), grid((unsigned)((f.width / 8 + 31) / 32), (unsigned)((f.height / 4 + 7) / 8));
+    if (mode == 0) k_ingest<0><<<grid, blk, 0, st>>>(d_in, in_stride, pic);
+    else if (mode == 1) k_ingest<1><<<grid, blk, 0, st>>>(nullptr, 0, pic);
+    else k_ingest<2><<<grid, blk, 0, st>>>(d_in, in_stride, pic);
+    const int W4 = (f.width + 2 * f.org_x + 3) >> 2;
+    k_pad_planes<<<dim3((unsigned)((W4 + 127) / 128), (unsigned)(f.height + 2 * f.org_y), 3), 128, 0, st>>>(pic);
+    return 2;
 }
 
 int svtme_launch_downsample_generic(const uint8_t *d_in, int in_stride, int in_w, int in_h, uint8_t *d_out,

@@ -9,9 +9,7 @@ struct DevPic;
 struct PicJob;
 
 // every launcher returns the number of kernels it launched on `st`
-int  svtme_launch_build_pyramid(const DevPic &pic, cudaStream_t st);
-int  svtme_launch_unpack10(const uint16_t *d_in, int in_stride, uint8_t *d_out, int out_stride, int w, int h, cudaStream_t st);
-int  svtme_launch_copy2d(const uint8_t *d_in, int in_stride, uint8_t *d_out, int out_stride, int w, int h, cudaStream_t st);
+int  svtme_launch_build_pyramid(const DevPic &pic, int mode, const void *d_in, int in_stride, cudaStream_t st);
 int  svtme_launch_downsample_generic(const uint8_t *d_in, int in_stride, int in_w, int in_h, uint8_t *d_out, int out_stride,
                                      int step, cudaStream_t st);
 uint32_t svtme_fp_units_cap(const SvtMePicParams &pp, int n_b64);

@@ -51,7 +51,7 @@ __device__ inline uint32_t warp_nxm_sad2(const uint8_t *src, int src_stride, con
         const uint32_t m = lo_bytes_mask(width - 4 * k);
         const uint32_t a = ldg_u32_unaligned(src + (size_t)r * src_stride + 4 * k) & m;
         const uint32_t b = ldg_u32_unaligned(ref + (size_t)r * ref_stride + 4 * k) & m;
-        sad += __vsadu4(a, b);
+        sad = sad4_acc(a, b, sad);
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) sad += __shfl_xor_sync(0xffffffffu, sad, o);
