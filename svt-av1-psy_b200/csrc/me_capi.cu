@@ -1,6 +1,7 @@
 // me_capi.cu — the extern "C" boundary of libsvtme_b200.so (include/svtme_b200.h): session
 // management, picture upload, per-picture ME launch, result fetch. No CPU fallback anywhere: a
 // failing CUDA call is reported on stderr and returned as SVTME_ERR_CUDA.
+#include <cuda.h>
 #include <cuda_runtime.h>
 
 #include <cstdio>
@@ -10,6 +11,7 @@
 #include <vector>
 
 #include "me_device.cuh"
+#include "me_tma.cuh"
 #include "me_launch.h"
 #include "svtme_b200.h"
 
@@ -35,6 +37,7 @@ struct SvtMeSession {
     cudaStream_t stream = nullptr;
     bool         own_stream = false;
     uint8_t     *pic_slab = nullptr;
+    CUtensorMap *d_tmaps = nullptr; // [max_pics][TM_KINDS]
     size_t       pic_bytes = 0;
     std::vector<DevPic> pics;
     std::vector<char>   pic_valid;
@@ -57,6 +60,32 @@ struct SvtMeSession {
     uint64_t     n_timed = 0;
     std::mutex   mu;
 };
+
+// ---- TMA descriptors -------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                  const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn encode_tiled_fn() {
+    static EncodeTiledFn fn = [] {
+        void *p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess)
+            p = nullptr;
+        return (EncodeTiledFn)p;
+    }();
+    return fn;
+}
+int svtme_encode_tmap(void *out, const void *base, size_t pitch, size_t rows, uint32_t box_w, uint32_t box_h) {
+    EncodeTiledFn fn = encode_tiled_fn();
+    if (!fn || (pitch & 15) || ((uintptr_t)base & 15)) return 1;
+    cuuint64_t dims[2] = {(cuuint64_t)pitch, (cuuint64_t)rows}, strides[1] = {(cuuint64_t)pitch};
+    cuuint32_t box[2] = {box_w, box_h}, es[2] = {1, 1};
+    const CUresult r = fn((CUtensorMap *)out, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<void *>(base), dims, strides, box, es,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { fprintf(stderr, "[svtme_b200] cuTensorMapEncodeTiled failed (%d)\n", (int)r); return 1; }
+    return 0;
+}
 
 static void plane_geom(int w, int h, int level, int *pw, int *ph, int *pad, int *stride, size_t *bytes) {
     static const int pads[3] = {SVTME_FULL_PAD, SVTME_QUARTER_PAD, SVTME_SIXTEENTH_PAD};
@@ -127,6 +156,26 @@ extern "C" uint32_t svtme_session_create(SvtMeSession **out, int device, uint32_
             pl.buf = s->pic_slab + (size_t)p * total + off[i] + SVTME_SLAB_SLACK;
             pl.stride = st[i]; pl.org_x = pad[i]; pl.org_y = pad[i]; pl.width = pw[i]; pl.height = ph[i];
         }
+    { // TMA descriptors of every plane the tile searches read (me_tma.cuh)
+        std::vector<CUtensorMap> maps((size_t)max_pictures * TM_KINDS);
+        e = cudaMalloc(&s->d_tmaps, maps.size() * sizeof(CUtensorMap));
+        if (e != cudaSuccess) { cudaFree(s->pic_slab); delete s; return SVTME_ERR_INSUFFICIENT_RESOURCES; }
+        static const int kind_level[TM_KINDS] = {1, 0, 0};
+        static const uint32_t kind_box[TM_KINDS][2] = {{TM_L1_BOX_W, TM_L1_BOX_H}, {TM_L2_BOX_W, TM_L2_BOX_H}, {TM_FP_BOX_W, TM_FP_BOX_H}};
+        for (uint32_t p = 0; p < max_pictures; p++) {
+            for (int k = 0; k < TM_KINDS; k++) {
+                const DevPlane &pl = s->pics[p].lvl[kind_level[k]];
+                if (svtme_encode_tmap(&maps[(size_t)p * TM_KINDS + k], pl.buf, (size_t)pl.stride, (size_t)pl.height + 2 * pl.org_y,
+                                      kind_box[k][0], kind_box[k][1])) {
+                    cudaFree(s->pic_slab); cudaFree(s->d_tmaps); delete s;
+                    return SVTME_ERR_CUDA;
+                }
+            }
+            s->pics[p].tmap = s->d_tmaps + (size_t)p * TM_KINDS;
+        }
+        e = cudaMemcpy(s->d_tmaps, maps.data(), maps.size() * sizeof(CUtensorMap), cudaMemcpyHostToDevice);
+        if (e != cudaSuccess) { cudaFree(s->pic_slab); cudaFree(s->d_tmaps); delete s; return SVTME_ERR_CUDA; }
+    }
     result_layout(s->lay, s->n_b64);
     e = cudaMalloc(&s->res_slab, s->lay.end);
     if (e != cudaSuccess) { cudaFree(s->pic_slab); delete s; return SVTME_ERR_INSUFFICIENT_RESOURCES; }
@@ -148,6 +197,7 @@ extern "C" void svtme_session_destroy(SvtMeSession *s) {
     for (auto &e : s->ev) cudaEventDestroy(e);
     if (s->own_stream) cudaStreamDestroy(s->stream);
     cudaFree(s->pic_slab);
+    if (s->d_tmaps) cudaFree(s->d_tmaps);
     for (uint8_t *p : s->res_slabs) cudaFree(p);
     if (s->d_jobs) cudaFree(s->d_jobs);
     if (s->d_in16) cudaFree(s->d_in16);

@@ -31,7 +31,8 @@ struct DevPlane {
     int stride, org_x, org_y, width, height;
 };
 struct DevPic {
-    DevPlane lvl[3]; // 0 full, 1 quarter, 2 sixteenth
+    DevPlane    lvl[3]; // 0 full, 1 quarter, 2 sixteenth
+    const void *tmap;   // CUtensorMap[TM_KINDS] of this picture's planes (me_tma.cuh), device memory
 };
 
 // per-b64 state produced by the HME stage (the MeContext fields later stages read) + the

@@ -1,136 +1,153 @@
-// me_fp3.cuh — full-pel (integer) search, block-parallel form.
+// me_fp3.cuh — full-pel (integer) search, block-parallel form over TMA tiles.
 //
 // One warp evaluates 8 consecutive search positions ("octet") of the 64x64 block per pass, with
 // the 32 lanes spread over the BLOCK: lane = band*4 + strip, strip = 16-pixel column (0..3), band =
 // 8-pixel row band (0..7). A lane keeps its 16x8 piece of the source block in registers for the
-// whole job, loads the matching reference rows straight from global memory (7 aligned words per
-// row, funnel-shifted once to the window's byte alignment), and accumulates the two 8x8 blocks of
-// its piece for the 8 positions (strip16_sad8_split). 16x16 / 32x32 / 64x64 SADs are completed with
-// 5 shfl_xor per position. Each lane therefore owns exactly two 8x8 PUs (and some lanes a 16x16,
-// 32x32 or the 64x64 PU): 5 packed keys per lane instead of 85 per thread, no shared memory, no
-// barriers, all lanes busy even for the 8x3 windows that dominate on easy content.
+// whole job and reads the matching reference rows from a shared-memory tile that one TMA load
+// fetched (me_tma.cuh): 16 positions x 8 search rows per tile. It accumulates the two 8x8 blocks
+// of its piece for the 8 positions (strip16_sad8_split); 16x16 / 32x32 / 64x64 SADs are completed with
+// halving exchanges (4 + 2 + 1 + 2 shuffles per pass). Each lane owns exactly two 8x8 PUs (and some
+// lanes a 16x16, 32x32 or the 64x64 PU): 5 packed keys per lane instead of 85 per thread.
 //
 //   k_fp       one warp per (b64, list, ref): window sizing (integer_search_b64,
 //              motion_estimation.c:1296-1561, check_00_center :1139, 8x8-variance probe :1393-1441) and,
 //              when the window is small, the whole scan (open_loop_me_fullpel_search_sblock :781,
 //              svt_ext_all_sad_calculation_8x8_16x16 :335, svt_ext_eight_sad_calculation_32x32_64x64
-//              :369, tails :98-205). Larger windows are cut into chunks of passes and queued.
-//   k_fp_big   persistent warps pull (picture, job, chunk) units and merge with 64-bit atomicMin.
+//              :369, tails :98-205). Larger windows are cut into tiles and queued.
+//   k_fp_big   persistent warps pull (picture, job, tile) units and merge with 64-bit atomicMin.
 //
 // Keys: 32-bit (sad << 12 | index), index 0 = the variance probe (evaluated first in the reference and
 // never reset, so it wins ties), index 1 + y*sa_w + x for window positions; min() = first minimum in
 // raster order = the reference's strict '<'. SADs stay un-doubled (SUB_SAD_SEARCH doubles all alike).
 #pragma once
 #include "me_device.cuh"
+#include "me_tma.cuh"
 #include "me_search.cuh"
 
 #define FP_WARPS 4
-#define FP_IDX_BITS 12 /* 20-bit SAD (64x64x255) + 12-bit index = 32 bits; chunk-local indices stay below 256 + 2*sa_w */
-#define FP_INLINE_PASSES 48 /* windows up to this many octet passes are scanned by the planning warp itself */
-#define FP_CHUNK_PASSES 32
+#define FP_IDX_BITS 12 /* 20-bit SAD (64x64x255) + 12-bit index = 32 bits */
+#define FP_INLINE_TILES 3 /* windows of up to this many tiles are scanned by the planning warp itself */
 
 __constant__ uint8_t c_z16b[16] = {0, 1, 4, 5, 2, 3, 6, 7, 8, 9, 12, 13, 10, 11, 14, 15}; // motion_estimation.c:341
 
 template <bool SUB>
 struct FpLane {
     static constexpr int NR = SUB ? 4 : 8; // rows of the band this lane touches
-    uint32_t src[NR][4];                   // its 16 x NR piece of the source block
-    uint32_t kl, kr, k16, k32, k64;        // running bests (packed keys) of the PUs it may own
-    int      strip, band;
+    TLane<4, NR> T;
+    uint32_t kl, kr, k16, k32, k64; // running bests (packed keys) of the PUs it may own
 };
 
+// rows of a band are visited in a rotated order by the odd bands: two lanes of a quarter-warp then read tile rows
+// 2 or 10 apart, which a 96-byte pitch maps to different banks (rows 8 apart would collide)
 template <bool SUB>
-__device__ __forceinline__ void fp_lane_init(FpLane<SUB> &L, const uint8_t *src_full, int src_stride) {
-    const int lane = threadIdx.x & 31;
-    L.strip = lane & 3;
-    L.band  = lane >> 2;
-    const uint8_t *p = src_full + (size_t)(8 * L.band) * src_stride + 16 * L.strip;
+__device__ __forceinline__ void fp_lane_init(FpLane<SUB> &L, const uint8_t *src_full, int src_stride, int bw, int bh) {
+    constexpr int NR = FpLane<SUB>::NR;
+    const int band = (threadIdx.x & 31) >> 2;
+    int row_of[NR];
 #pragma unroll
-    for (int q = 0; q < FpLane<SUB>::NR; q++)
-#pragma unroll
-        for (int k = 0; k < 4; k++) L.src[q][k] = ldg_u32_unaligned(p + (size_t)(SUB ? 2 * q : q) * src_stride + 4 * k);
+    for (int q = 0; q < NR; q++) row_of[q] = 8 * band + (SUB ? 2 : 1) * ((q + (band & 1) * (SUB ? 1 : 2)) % NR);
+    tlane_init<4, NR>(L.T, src_full, src_stride, row_of, bw, bh, TM_FP_BOX_W);
     L.kl = L.kr = L.k16 = L.k32 = L.k64 = 0xffffffffu;
 }
 
-// One pass: positions (x .. x+7, y) given by `ref` = address of the reference sample that aligns with
-// the block's top-left sample for position x. pmask: which of the 8 positions exist. idx0: key index
-// of position x. Outputs the raw sums of position 0 (for the probe / KAT) when wanted.
+// one pass: 8 positions starting beta bytes into tile row `row_base`; idx0 = key index of the first, nv = how many exist
 template <bool SUB>
-__device__ __forceinline__ void fp_eval_pass(FpLane<SUB> &L, const uint8_t *ref, int ref_stride, uint32_t pmask, uint32_t idx0,
-                                             uint32_t *raw /* [5]: l, r, 16, 32, 64 of position 0, or nullptr */) {
+__device__ __forceinline__ void fp_eval_pass(FpLane<SUB> &L, uint32_t row_base, uint32_t beta, uint32_t idx0, int nv) {
     constexpr int NR = FpLane<SUB>::NR;
-    const uint8_t  *g  = ref + (size_t)(8 * L.band) * ref_stride + 16 * L.strip;
-    const uintptr_t a0 = (uintptr_t)g;
-    const uint32_t  sa = (uint32_t)(a0 & 3) * 8; // strides are multiples of 4: same misalignment on every row
-    const uint32_t *q0 = (const uint32_t *)(a0 & ~(uintptr_t)3);
-    const int       rs4 = (SUB ? 2 : 1) * (ref_stride >> 2);
-    uint32_t gw[NR][7];
-#pragma unroll
-    for (int q = 0; q < NR; q++)
-#pragma unroll
-        for (int k = 0; k < 7; k++) gw[q][k] = __ldg(q0 + (size_t)q * rs4 + k);
-    uint32_t accl[8] = {0, 0, 0, 0, 0, 0, 0, 0}, accr[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-#pragma unroll
-    for (int q = 0; q < NR; q++) {
-        uint32_t w[6];
-#pragma unroll
-        for (int k = 0; k < 6; k++) w[k] = __funnelshift_r(gw[q][k], gw[q][k + 1], sa);
-        strip16_sad8_split(w, L.src[q], accl, accr);
-    }
-    const uint32_t mul = 1u << FP_IDX_BITS;
+    uint32_t accl[8], accr[8];
+    tile_pass<4, NR, true>(L.T, row_base, beta, accl, accr);
+    const int  lane = threadIdx.x & 31;
+    const bool h4 = lane & 4, h1 = lane & 1, h8 = lane & 8;
+    uint32_t s8[8];
 #pragma unroll
     for (int p = 0; p < 8; p++) {
-        const bool     ok  = (pmask >> p) & 1;
-        const uint32_t id  = idx0 + p;
-        const uint32_t s8  = accl[p] + accr[p];
-        const uint32_t t16 = s8 + __shfl_xor_sync(0xffffffffu, s8, 4);       // the other 8-row band of the 16x16
-        uint32_t       t32 = t16 + __shfl_xor_sync(0xffffffffu, t16, 1);     // the other strip of the 32x32
-        t32 += __shfl_xor_sync(0xffffffffu, t32, 8);                         // the other 16-row band
-        uint32_t t64 = t32 + __shfl_xor_sync(0xffffffffu, t32, 2);
-        t64 += __shfl_xor_sync(0xffffffffu, t64, 16);
-        if (ok) {
-            L.kl  = min(L.kl, accl[p] * mul + id);
-            L.kr  = min(L.kr, accr[p] * mul + id);
-            L.k16 = min(L.k16, t16 * mul + id);
-            L.k32 = min(L.k32, t32 * mul + id);
-            L.k64 = min(L.k64, t64 * mul + id);
+        s8[p] = accl[p] + accr[p];
+        if (p < nv) {
+            L.kl = min(L.kl, (accl[p] << FP_IDX_BITS) + idx0 + p);
+            L.kr = min(L.kr, (accr[p] << FP_IDX_BITS) + idx0 + p);
         }
-        if (p == 0 && raw) { raw[0] = accl[0]; raw[1] = accr[0]; raw[2] = t16; raw[3] = t32; raw[4] = t64; }
+    }
+    uint32_t t16[4], u[2];
+    const int p16 = h4 ? 4 : 0;
+#pragma unroll
+    for (int i = 0; i < 4; i++) { // the other 8-row band of the 16x16: it keeps the other four positions
+        const uint32_t mine = h4 ? s8[4 + i] : s8[i], theirs = h4 ? s8[i] : s8[4 + i];
+        t16[i] = mine + __shfl_xor_sync(0xffffffffu, theirs, 4);
+        if (p16 + i < nv) L.k16 = min(L.k16, (t16[i] << FP_IDX_BITS) + idx0 + p16 + i);
+    }
+#pragma unroll
+    for (int i = 0; i < 2; i++) { // the other strip of the 32x32
+        const uint32_t mine = h1 ? t16[2 + i] : t16[i], theirs = h1 ? t16[i] : t16[2 + i];
+        u[i] = mine + __shfl_xor_sync(0xffffffffu, theirs, 1);
+    }
+    const uint32_t mine = h8 ? u[1] : u[0], theirs = h8 ? u[0] : u[1];
+    const uint32_t t32 = mine + __shfl_xor_sync(0xffffffffu, theirs, 8); // the other 16-row band
+    const int p32 = p16 + (h1 ? 2 : 0) + (h8 ? 1 : 0);
+    uint32_t t64 = t32 + __shfl_xor_sync(0xffffffffu, t32, 2);
+    t64 += __shfl_xor_sync(0xffffffffu, t64, 16);
+    if (p32 < nv) {
+        L.k32 = min(L.k32, (t32 << FP_IDX_BITS) + idx0 + p32);
+        L.k64 = min(L.k64, (t64 << FP_IDX_BITS) + idx0 + p32);
     }
 }
 
-// visit the PUs this lane owns: f(key, pu)
+// one position (the variance probe / the RTCD known-answer path): raw = sums of this lane's left 8x8, right 8x8, its
+// 16x16, its 32x32 and the 64x64; keys updated with index idx
+template <bool SUB>
+__device__ __forceinline__ void fp_eval_one(FpLane<SUB> &L, uint32_t row_base, uint32_t beta, uint32_t idx, uint32_t (&raw)[5]) {
+    constexpr int NR = FpLane<SUB>::NR;
+    uint32_t accl[8], accr[8];
+    tile_pass<4, NR, true>(L.T, row_base, beta, accl, accr); // 8 positions computed, the first one used
+    const uint32_t s8  = accl[0] + accr[0];
+    const uint32_t t16 = s8 + __shfl_xor_sync(0xffffffffu, s8, 4);
+    uint32_t       t32 = t16 + __shfl_xor_sync(0xffffffffu, t16, 1);
+    t32 += __shfl_xor_sync(0xffffffffu, t32, 8);
+    uint32_t t64 = t32 + __shfl_xor_sync(0xffffffffu, t32, 2);
+    t64 += __shfl_xor_sync(0xffffffffu, t64, 16);
+    raw[0] = accl[0]; raw[1] = accr[0]; raw[2] = t16; raw[3] = t32; raw[4] = t64;
+    L.kl  = min(L.kl, (accl[0] << FP_IDX_BITS) + idx);
+    L.kr  = min(L.kr, (accr[0] << FP_IDX_BITS) + idx);
+    L.k16 = min(L.k16, (t16 << FP_IDX_BITS) + idx);
+    L.k32 = min(L.k32, (t32 << FP_IDX_BITS) + idx);
+    L.k64 = min(L.k64, (t64 << FP_IDX_BITS) + idx);
+}
+
+// the lanes of a PU hold the bests of different positions: combine, then visit the PUs this lane owns: f(key, pu)
 template <bool SUB, typename F>
 __device__ __forceinline__ void fp_for_owned(const FpLane<SUB> &L, F f) {
-    const int z = c_z16b[4 * (L.band >> 1) + L.strip];
-    const int k = 2 * (L.band & 1);
+    const int lane = threadIdx.x & 31, strip = lane & 3, band = lane >> 2;
+    const uint32_t k16 = min(L.k16, __shfl_xor_sync(0xffffffffu, L.k16, 4));
+    uint32_t k32 = min(L.k32, __shfl_xor_sync(0xffffffffu, L.k32, 4));
+    k32 = min(k32, __shfl_xor_sync(0xffffffffu, k32, 1));
+    k32 = min(k32, __shfl_xor_sync(0xffffffffu, k32, 8));
+    const uint32_t k64 = __reduce_min_sync(0xffffffffu, L.k64);
+    const int z = c_z16b[4 * (band >> 1) + strip];
+    const int k = 2 * (band & 1);
     f(L.kl, 21 + 4 * z + k);
     f(L.kr, 21 + 4 * z + k + 1);
-    if ((L.band & 1) == 0) f(L.k16, 5 + z);
-    if ((L.band & 3) == 0 && (L.strip & 1) == 0) f(L.k32, 1 + 2 * (L.band >> 2) + (L.strip >> 1));
-    if (L.band == 0 && L.strip == 0) f(L.k64, 0);
+    if ((band & 1) == 0) f(k16, 5 + z);
+    if ((band & 3) == 0 && (strip & 1) == 0) f(k32, 1 + 2 * (band >> 2) + (strip >> 1));
+    if (band == 0 && strip == 0) f(k64, 0);
 }
 
+// positions [ox, ox+n_x) x [oy, oy+n_y) of a tile whose position (0,0) lies `a` bytes into its first row;
+// key index of the rectangle's position (0,0) = idx_base, of the next row = idx_base + idx_row
 template <bool SUB>
-__device__ __forceinline__ void fp_scan_passes(FpLane<SUB> &L, const DevPlane &ref, int org_x, int org_y, int x_origin,
-                                               int y_origin, int sa_w, int sa_h, int pass0, int pass1, uint32_t idx_base) {
-    const int n_oct = (sa_w + 7) >> 3;
-    int y = pass0 / n_oct, oct = pass0 - y * n_oct;
-    const uint8_t *row = ref.buf + (size_t)(ref.org_y + org_y + y_origin + y) * ref.stride + (ref.org_x + org_x + x_origin);
-    for (int ps = pass0; ps < pass1; ps++) {
-        const int      x     = 8 * oct;
-        const int      left  = sa_w - x;
-        const uint32_t pmask = left >= 8 ? 0xffu : ((1u << left) - 1u);
-        fp_eval_pass<SUB>(L, row + x, ref.stride, pmask, idx_base + (uint32_t)(y * sa_w + x), nullptr);
-        if (++oct == n_oct) { oct = 0; y++; row += ref.stride; }
+__device__ __forceinline__ void fp_scan_rect(FpLane<SUB> &L, uint32_t buf, uint32_t a, int ox, int oy, int n_x, int n_y, uint32_t idx_base,
+                                             uint32_t idx_row) {
+    for (int yy = 0; yy < n_y; yy++) {
+        const uint32_t row_base = buf + (uint32_t)((oy + yy) * TM_FP_BOX_W);
+        for (int x = 0; x < n_x; x += 8)
+            fp_eval_pass<SUB>(L, row_base, a + (uint32_t)(ox + x), idx_base + (uint32_t)yy * idx_row + (uint32_t)x, imin(8, n_x - x));
     }
-    (void)sa_h;
 }
 
 // ---- k_fp ------------------------------------------------------------------------------------
 // phase: 0 all refs, 1 only (0,0), 2 all but (0,0) (enable_me_sr_adjustment == 2, :1357-1366)
 template <bool SUB>
 __global__ void __launch_bounds__(32 * FP_WARPS) k_fp(const PicJob *__restrict__ jobs, int phase) {
+    extern __shared__ __align__(128) uint8_t s_dyn[];
+    __shared__ __align__(8) uint64_t s_bar[FP_WARPS][2];
     const PicJob &job = jobs[blockIdx.y];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int u = blockIdx.x * FP_WARPS + warp;
@@ -152,9 +169,14 @@ __global__ void __launch_bounds__(32 * FP_WARPS) k_fp(const PicJob *__restrict__
         return;
     }
     const B64Geo    g   = b64_geo(job, b);
-    const DevPlane &ref = job.ref[l][r].lvl[0];
+    const DevPic   &rp  = job.ref[l][r];
+    const DevPlane &ref = rp.lvl[0];
     const DevPlane &sf  = job.src.lvl[0];
     const uint8_t  *src_full = sf.buf + (size_t)(sf.org_y + g.org_y) * sf.stride + sf.org_x + g.org_x;
+    const CUtensorMap *map = (const CUtensorMap *)rp.tmap + TM_FP;
+    uint8_t *sbase = s_dyn + ((128u - (smem_u32(s_dyn) & 127u)) & 127u);
+    TilePipe P;
+    pipe_init(P, sbase + (size_t)warp * 2 * TM_FP_BUF, TM_FP_BUF, s_bar[warp], TM_FP_BOX_W * TM_FP_BOX_H);
     unsigned long long ops = 0;
 
     // window sizing :1296-1366 (all lanes compute the same scalars; SADs are warp-cooperative)
@@ -174,7 +196,8 @@ __global__ void __launch_bounds__(32 * FP_WARPS) k_fp(const PicJob *__restrict__
     uint64_t best_hme_sad = ~0ull;
     if (c.me_early_exit_th) {
         if (st.zz_sad[l][r] < (c.me_early_exit_th / 6)) sa_w = sa_h = 1;
-    } else {
+    }
+    if (!c.me_early_exit_th) {
         uint8_t hme_is_accurate = 1;
         if ((xc != 0 || yc != 0) && pp.is_ref) {
             // check_00_center :1139-1206 (the COST_PRECISION shift is monotonic)
@@ -203,13 +226,17 @@ __global__ void __launch_bounds__(32 * FP_WARPS) k_fp(const PicJob *__restrict__
             }
         }
     }
-    FpLane<SUB> L;
-    fp_lane_init<SUB>(L, src_full, sf.stride);
+    // plane coordinates of the reference sample under the block's top-left sample at MV (0,0)
+    const int bx = ref.org_x + g.org_x, by = ref.org_y + g.org_y;
     const bool probe = c.me_8x8_var_enabled && (sa_w * sa_h > 24);
+    const int  ptx = bx + xc - 8, pty = by + yc - 4; // the probe tile: 16 x 8 positions around the search centre
+    if (probe) pipe_issue(P, 0, map, ptx & ~15, pty);
+    FpLane<SUB> L;
+    fp_lane_init<SUB>(L, src_full, sf.stride, 64, 64); // the full-pel stage always works on 64x64 (padded source)
     if (probe) { // :1393-1441: one position at the search centre, then the variance of its 64 8x8 SADs
+        pipe_wait(P, 0);
         uint32_t raw[5];
-        const uint8_t *pc = ref.buf + (size_t)(ref.org_y + g.org_y + yc) * ref.stride + (ref.org_x + g.org_x + xc);
-        fp_eval_pass<SUB>(L, pc, ref.stride, 1u, 0u, raw);
+        fp_eval_one<SUB>(L, P.buf[0] + 4u * TM_FP_BOX_W, (uint32_t)(ptx & 15) + 8u, 0u, raw);
         const uint32_t dbl  = SUB ? 1 : 0;
         const uint32_t mean = (raw[4] << dbl) / 64;
         const int32_t  dl = (int32_t)(raw[0] << dbl) - (int32_t)mean, dr = (int32_t)(raw[1] << dbl) - (int32_t)mean;
@@ -237,21 +264,43 @@ __global__ void __launch_bounds__(32 * FP_WARPS) k_fp(const PicJob *__restrict__
     clamp_axis((int16_t)g.org_x, x_origin, sa_w, 63, (int16_t)job.pic_w);
     sa_w = (int16_t)((sa_w < 8) ? sa_w : sa_w & ~0x07);
     clamp_axis((int16_t)g.org_y, y_origin, sa_h, 63, (int16_t)job.pic_h);
-    const int n_oct = (sa_w + 7) >> 3, passes = n_oct * sa_h;
-    const bool inline_scan = passes <= FP_INLINE_PASSES;
-    if (inline_scan) fp_scan_passes<SUB>(L, ref, g.org_x, g.org_y, x_origin, y_origin, sa_w, sa_h, 0, passes, 1u);
+    const int ntx = (sa_w + TM_FP_TILE_W - 1) / TM_FP_TILE_W, nty = (sa_h + TM_FP_TILE_H - 1) / TM_FP_TILE_H, n_tiles = ntx * nty;
+    const int wx = bx + x_origin, wy = by + y_origin; // plane coordinates of window position (0,0)
+    const int rx = wx - ptx, ry = wy - pty;           // ... relative to the probe tile
+    const bool in_probe_tile = probe && rx >= 0 && ry >= 0 && rx + sa_w <= TM_FP_TILE_W && ry + sa_h <= TM_FP_TILE_H;
+    const bool inline_scan = in_probe_tile || n_tiles <= FP_INLINE_TILES;
+    if (in_probe_tile) {
+        fp_scan_rect<SUB>(L, P.buf[0], (uint32_t)(ptx & 15), rx, ry, sa_w, sa_h, 1u, (uint32_t)sa_w);
+    } else if (inline_scan) {
+        __syncwarp();
+        int stage = 1; // stage 0 may still be read by slow lanes of the probe pass; __syncwarp above orders it anyway
+        pipe_issue(P, stage, map, wx & ~15, wy);
+        for (int t = 0; t < n_tiles; t++) {
+            const int ty = t / ntx, tx = t - ty * ntx;
+            if (t + 1 < n_tiles) {
+                const int ty1 = (t + 1) / ntx, tx1 = (t + 1) - ty1 * ntx;
+                pipe_issue(P, stage ^ 1, map, (wx + TM_FP_TILE_W * tx1) & ~15, wy + TM_FP_TILE_H * ty1);
+            }
+            pipe_wait(P, stage);
+            fp_scan_rect<SUB>(L, P.buf[stage], (uint32_t)((wx + TM_FP_TILE_W * tx) & 15), 0, 0, imin(TM_FP_TILE_W, sa_w - TM_FP_TILE_W * tx),
+                              imin(TM_FP_TILE_H, sa_h - TM_FP_TILE_H * ty), 1u + (uint32_t)(TM_FP_TILE_H * ty * sa_w + TM_FP_TILE_W * tx),
+                              (uint32_t)sa_w);
+            __syncwarp();
+            stage ^= 1;
+        }
+    }
     // running bests -> 64-bit keys (sad << 32 | scan index); ~0 = untouched (MAX_SAD_VALUE, :1368)
     fp_for_owned<SUB>(L, [&](uint32_t k, int pu) {
         gk[pu] = k == 0xffffffffu ? ~0ull : (((unsigned long long)(k >> FP_IDX_BITS) << 32) | (k & ((1u << FP_IDX_BITS) - 1)));
     });
     if (lane == 0) {
-        const int n_chunks = inline_scan ? 0 : (passes + FP_CHUNK_PASSES - 1) / FP_CHUNK_PASSES;
+        const int n_units = inline_scan ? 0 : n_tiles;
         fj.xc = xc; fj.yc = yc; fj.x_origin = x_origin; fj.y_origin = y_origin; fj.sa_w = sa_w; fj.sa_h = sa_h;
-        fj.n_tx = (uint16_t)n_chunks; fj.n_ty = 1; fj.active = 1; fj.probe = probe ? 1 : 0;
+        fj.n_tx = (uint16_t)ntx; fj.n_ty = (uint16_t)nty; fj.active = 1; fj.probe = probe ? 1 : 0;
         job.windows[u] = SvtMeWindow{x_origin, y_origin, sa_w, sa_h};
-        if (n_chunks) {
-            const uint32_t base = atomicAdd(&job.fp_counters[0], (uint32_t)n_chunks);
-            for (int i = 0; i < n_chunks && base + i < job.fp_units_cap; i++)
+        if (n_units) {
+            const uint32_t base = atomicAdd(&job.fp_counters[0], (uint32_t)n_units);
+            for (int i = 0; i < n_units && base + i < job.fp_units_cap; i++)
                 job.fp_units[base + i] = make_uint2((uint32_t)u, (blockIdx.y << 16) | (uint32_t)i);
         }
         ops += ((unsigned long long)sa_w * sa_h + (probe ? 1 : 0)) * 64ull * (SUB ? 32 : 64);
@@ -260,37 +309,80 @@ __global__ void __launch_bounds__(32 * FP_WARPS) k_fp(const PicJob *__restrict__
 }
 
 // ---- k_fp_big --------------------------------------------------------------------------------
-template <bool SUB>
-__global__ void __launch_bounds__(32 * FP_WARPS) k_fp_big(const PicJob *__restrict__ jobs) {
-    const PicJob &job0 = jobs[0]; // the unit queue is shared by the batch
-    const int lane = threadIdx.x & 31;
-    const uint32_t n_units = min(job0.fp_counters[0], job0.fp_units_cap);
-    for (;;) {
-        uint32_t ui = 0;
-        if (lane == 0) ui = atomicAdd(&job0.fp_counters[1], 1u);
-        ui = __shfl_sync(0xffffffffu, ui, 0);
-        if (ui >= n_units) break;
-        const uint2 unit = job0.fp_units[ui];
-        const PicJob &job = jobs[unit.y >> 16];
-        const int u = (int)unit.x, chunk = (int)(unit.y & 0xffff);
-        const FpJobG &fj = job.fp_jobs[u];
-        const int b = u >> 3, l = (u >> 2) & 1, r = u & 3;
+struct FpUnit {
+    int pic, u, tile, wx, wy, sa_w, sa_h, ntx;
+    bool valid;
+};
+__device__ __forceinline__ FpUnit fp_fetch_unit(const PicJob *__restrict__ jobs, uint32_t n_units) {
+    FpUnit un;
+    uint32_t ui = 0;
+    if ((threadIdx.x & 31) == 0) ui = atomicAdd(&jobs[0].fp_counters[1], 1u);
+    ui = __shfl_sync(0xffffffffu, ui, 0);
+    un.valid = ui < n_units;
+    un.pic = un.u = un.tile = un.wx = un.wy = un.sa_w = un.sa_h = 0; un.ntx = 1;
+    if (un.valid) {
+        const uint2 q = jobs[0].fp_units[ui];
+        un.pic = (int)(q.y >> 16); un.u = (int)q.x; un.tile = (int)(q.y & 0xffff);
+        const PicJob &job = jobs[un.pic];
+        const FpJobG &fj  = job.fp_jobs[un.u];
+        const int b = un.u >> 3, l = (un.u >> 2) & 1, r = un.u & 3;
         const B64Geo    g   = b64_geo(job, b);
         const DevPlane &ref = job.ref[l][r].lvl[0];
-        const DevPlane &sf  = job.src.lvl[0];
-        FpLane<SUB> L;
-        fp_lane_init<SUB>(L, sf.buf + (size_t)(sf.org_y + g.org_y) * sf.stride + sf.org_x + g.org_x, sf.stride);
-        const int n_oct = (fj.sa_w + 7) >> 3, passes = n_oct * fj.sa_h;
-        const int p0 = chunk * FP_CHUNK_PASSES, p1 = imin(passes, p0 + FP_CHUNK_PASSES);
-        // indices inside the chunk start at the chunk's first position so that they fit the 12-bit field
-        const int y_first = p0 / n_oct;
-        const uint32_t gbase = 1u + (uint32_t)(y_first * fj.sa_w);
-        fp_scan_passes<SUB>(L, ref, g.org_x, g.org_y, fj.x_origin, fj.y_origin + y_first, fj.sa_w, fj.sa_h - y_first,
-                            p0 - y_first * n_oct, p1 - y_first * n_oct, 0u);
-        unsigned long long *gk = job.fp_keys + (size_t)u * 85;
+        un.wx = ref.org_x + g.org_x + fj.x_origin; un.wy = ref.org_y + g.org_y + fj.y_origin;
+        un.sa_w = fj.sa_w; un.sa_h = fj.sa_h; un.ntx = fj.n_tx;
+    }
+    return un;
+}
+__device__ __forceinline__ void fp_issue_unit(TilePipe &P, int stage, const PicJob *__restrict__ jobs, const FpUnit &un) {
+    const int l = (un.u >> 2) & 1, r = un.u & 3;
+    const int ty = un.tile / un.ntx, tx = un.tile - ty * un.ntx;
+    const CUtensorMap *map = (const CUtensorMap *)jobs[un.pic].ref[l][r].tmap + TM_FP;
+    pipe_issue(P, stage, map, (un.wx + TM_FP_TILE_W * tx) & ~15, un.wy + TM_FP_TILE_H * ty);
+}
+
+template <bool SUB>
+__global__ void __launch_bounds__(32 * FP_WARPS) k_fp_big(const PicJob *__restrict__ jobs) {
+    extern __shared__ __align__(128) uint8_t s_dyn[];
+    __shared__ __align__(8) uint64_t s_bar[FP_WARPS][2];
+    const int warp = threadIdx.x >> 5;
+    const uint32_t n_units = min(jobs[0].fp_counters[0], jobs[0].fp_units_cap); // the unit queue is shared by the batch
+    if (n_units == 0) return;
+    uint8_t *sbase = s_dyn + ((128u - (smem_u32(s_dyn) & 127u)) & 127u);
+    TilePipe P;
+    pipe_init(P, sbase + (size_t)warp * 2 * TM_FP_BUF, TM_FP_BUF, s_bar[warp], TM_FP_BOX_W * TM_FP_BOX_H);
+    FpUnit cur = fp_fetch_unit(jobs, n_units);
+    if (!cur.valid) return;
+    int stage = 0;
+    fp_issue_unit(P, stage, jobs, cur);
+    FpLane<SUB> L;
+    int have_pic = -1, have_u = -1;
+    while (cur.valid) {
+        const FpUnit nxt = fp_fetch_unit(jobs, n_units);
+        if (nxt.valid) fp_issue_unit(P, stage ^ 1, jobs, nxt);
+        const PicJob &job = jobs[cur.pic];
+        if (cur.pic != have_pic || cur.u != have_u) {
+            const B64Geo    g  = b64_geo(job, cur.u >> 3);
+            const DevPlane &sf = job.src.lvl[0];
+            fp_lane_init<SUB>(L, sf.buf + (size_t)(sf.org_y + g.org_y) * sf.stride + sf.org_x + g.org_x, sf.stride, 64, 64);
+            have_pic = cur.pic; have_u = cur.u;
+        }
+        L.kl = L.kr = L.k16 = L.k32 = L.k64 = 0xffffffffu;
+        const int ty = cur.tile / cur.ntx, tx = cur.tile - ty * cur.ntx;
+        pipe_wait(P, stage);
+        // key indices are local to the tile (row pitch 16) so that they fit the 12-bit field
+        fp_scan_rect<SUB>(L, P.buf[stage], (uint32_t)((cur.wx + TM_FP_TILE_W * tx) & 15), 0, 0, imin(TM_FP_TILE_W, cur.sa_w - TM_FP_TILE_W * tx),
+                          imin(TM_FP_TILE_H, cur.sa_h - TM_FP_TILE_H * ty), 0u, (uint32_t)TM_FP_TILE_W);
+        __syncwarp();
+        unsigned long long *gk = job.fp_keys + (size_t)cur.u * 85;
+        const uint32_t gbase = 1u + (uint32_t)(TM_FP_TILE_H * ty * cur.sa_w + TM_FP_TILE_W * tx);
+        const uint32_t sa_w = (uint32_t)cur.sa_w;
         fp_for_owned<SUB>(L, [&](uint32_t k, int pu) {
-            if (k != 0xffffffffu)
-                atomicMin(&gk[pu], ((unsigned long long)(k >> FP_IDX_BITS) << 32) | (gbase + (k & ((1u << FP_IDX_BITS) - 1))));
+            if (k != 0xffffffffu) {
+                const uint32_t li = k & ((1u << FP_IDX_BITS) - 1);
+                atomicMin(&gk[pu], ((unsigned long long)(k >> FP_IDX_BITS) << 32) | (gbase + (li >> 4) * sa_w + (li & 15u)));
+            }
         });
+        cur = nxt;
+        stage ^= 1;
     }
 }

@@ -32,7 +32,7 @@ struct Scratch {
         return d + SVTME_SLAB_SLACK;
     }
 };
-Scratch g_src, g_ref, g_out;
+Scratch g_src, g_ref, g_out, g_pitched;
 
 bool fail(const char *what, cudaError_t e) {
     fprintf(stderr, "[svtme_b200] %s: %s (no CPU fallback)\n", what, cudaGetErrorString(e));
@@ -75,13 +75,22 @@ extern "C" void svtme_sad_loop_kernel(uint8_t *src, uint32_t src_stride, uint8_t
     const size_t src_bytes = (size_t)(block_height - 1) * src_stride + block_width;
     const size_t ref_bytes = (size_t)(search_area_height - 1) * src_stride_raw + (size_t)(block_height - 1) * ref_stride +
         (size_t)(search_area_width - 1) + block_width;
-    uint8_t *ds = g_src.need(src_bytes), *dr = g_ref.need(ref_bytes), *dk = g_out.need(64);
-    if (!ds || !dr || !dk) { t_last_error = SVTME_ERR_INSUFFICIENT_RESOURCES; return; }
-    if (!ok(cudaMemcpy(ds, src, src_bytes, cudaMemcpyHostToDevice), "H2D src")) return;
+    // blocks up to 64 wide: source rows re-pitched to 64 bytes (the picture store keeps block origins 16-byte aligned)
+    const bool repitch = block_width <= 64;
+    const size_t pitched_cap = ((size_t)search_area_width + block_width + 48) * ((size_t)search_area_height + 64 * 2 + 8);
+    uint8_t *ds = g_src.need(repitch ? (size_t)64 * block_height : src_bytes), *dr = g_ref.need(ref_bytes), *dk = g_out.need(64);
+    uint8_t *dp = g_pitched.need(pitched_cap);
+    if (!ds || !dr || !dk || !dp) { t_last_error = SVTME_ERR_INSUFFICIENT_RESOURCES; return; }
+    if (repitch) {
+        if (!ok(cudaMemset(ds, 0, (size_t)64 * block_height), "memset src")) return;
+        if (!ok(cudaMemcpy2D(ds, 64, src, src_stride, block_width, block_height, cudaMemcpyHostToDevice), "H2D src")) return;
+    } else if (!ok(cudaMemcpy(ds, src, src_bytes, cudaMemcpyHostToDevice), "H2D src")) {
+        return;
+    }
     if (!ok(cudaMemcpy(dr, ref, ref_bytes, cudaMemcpyHostToDevice), "H2D ref")) return;
-    svtme_launch_kat_sad_loop(ds, (int)src_stride, dr, (int)ref_stride, (int)block_height, (int)block_width,
+    svtme_launch_kat_sad_loop(ds, repitch ? 64 : (int)src_stride, dr, (int)ref_stride, (int)block_height, (int)block_width,
                               (int)src_stride_raw, skip_search_line, search_area_width, search_area_height,
-                              (unsigned long long *)dk, 0);
+                              (unsigned long long *)dk, dp, pitched_cap, 0);
     unsigned long long key = 0;
     if (!ok(cudaMemcpy(&key, dk, 8, cudaMemcpyDeviceToHost), "sad_loop kernel")) return;
     *best_sad = key >> 32;
@@ -97,14 +106,15 @@ static bool run_octet(const uint8_t *src, uint32_t src_stride, const uint8_t *re
                       int rows, int cols, uint32_t *h_out) {
     const size_t src_bytes = (size_t)(rows - 1) * src_stride + cols;
     const size_t ref_bytes = (size_t)(rows - 1) * ref_stride + cols + (n_pos - 1);
-    // the device routine always evaluates the full 64x64 block: give it zero-padded 64x64 copies
-    uint8_t *ds = g_src.need((size_t)64 * 64), *dr = g_ref.need((size_t)64 * 80), *dk = g_out.need((size_t)8 * 85 * 4);
+    // the device routine always evaluates the full 64x64 block: give it zero-padded copies, the reference one with the
+    // 96-byte row pitch of a full-pel tile
+    uint8_t *ds = g_src.need((size_t)64 * 64), *dr = g_ref.need((size_t)96 * 72), *dk = g_out.need((size_t)8 * 85 * 4);
     if (!ds || !dr || !dk) { t_last_error = SVTME_ERR_INSUFFICIENT_RESOURCES; return false; }
     (void)src_bytes; (void)ref_bytes;
-    if (!ok(cudaMemset(ds, 0, 64 * 64), "memset") || !ok(cudaMemset(dr, 0, 64 * 80), "memset")) return false;
+    if (!ok(cudaMemset(ds, 0, 64 * 64), "memset") || !ok(cudaMemset(dr, 0, 96 * 72), "memset")) return false;
     if (!ok(cudaMemcpy2D(ds, 64, src, src_stride, (size_t)cols, (size_t)rows, cudaMemcpyHostToDevice), "H2D src")) return false;
-    if (!ok(cudaMemcpy2D(dr, 80, ref, ref_stride, (size_t)cols + (size_t)(n_pos - 1), (size_t)rows, cudaMemcpyHostToDevice), "H2D ref")) return false;
-    svtme_launch_kat_octet(ds, 64, dr, 80, sub, n_pos, (uint32_t *)dk, 0);
+    if (!ok(cudaMemcpy2D(dr, 96, ref, ref_stride, (size_t)cols + (size_t)(n_pos - 1), (size_t)rows, cudaMemcpyHostToDevice), "H2D ref")) return false;
+    if (!svtme_launch_kat_octet(ds, 64, dr, 96, 72, sub, n_pos, (uint32_t *)dk, 0)) { t_last_error = SVTME_ERR_CUDA; return false; }
     return ok(cudaMemcpy(h_out, dk, (size_t)n_pos * 85 * 4, cudaMemcpyDeviceToHost), "octet kernel");
 }
 

@@ -1,4 +1,5 @@
 // me_kernels.cu — kernel definitions and their host-side launchers (sm_100a only).
+#include <cuda.h>
 #include "me_launch.h"
 
 #include "me_device.cuh"
@@ -148,6 +149,24 @@ int svtme_launch_downsample_generic(const uint8_t *d_in, int in_stride, int in_w
 // ------------------------------------------------------------------------------------------
 static int g_fp_search_ctas_per_sm = 0, g_s16_ctas_per_sm = 0;
 
+// kernels whose dynamic shared memory exceeds the 48 KB default opt in once per device
+static void opt_in_shared_memory() {
+    static int done_for = -1;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (done_for == dev) return;
+    const int blk2 = SEARCH_WARPS * 2 * TM_L2_BUF + 128, blk1 = SEARCH_WARPS * 2 * TM_L1_BUF + 128, fp = FP_WARPS * 2 * TM_FP_BUF + 128;
+    cudaFuncSetAttribute(k_search_blk<true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, blk1);
+    cudaFuncSetAttribute(k_search_blk<false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, blk1);
+    cudaFuncSetAttribute(k_search_blk<true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, blk2);
+    cudaFuncSetAttribute(k_search_blk<false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, blk2);
+    cudaFuncSetAttribute(k_fp<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, fp);
+    cudaFuncSetAttribute(k_fp<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, fp);
+    cudaFuncSetAttribute(k_fp_big<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, fp);
+    cudaFuncSetAttribute(k_fp_big<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, fp);
+    done_for = dev;
+}
+
 static inline int imax_h(int a, int b) { return a > b ? a : b; }
 static int next_pow2(int v) {
     int p = 1;
@@ -184,7 +203,7 @@ uint32_t svtme_fp_units_cap(const SvtMePicParams &pp, int n_b64) {
     mh = mh * 3 / 2;
     if (mw < 8) mw = 8;
     if (mh < 3) mh = 3;
-    long long chunks = ((mw / 8) * mh + FP_CHUNK_PASSES - 1) / FP_CHUNK_PASSES;
+    long long chunks = ((mw + TM_FP_TILE_W - 1) / TM_FP_TILE_W) * ((mh + TM_FP_TILE_H - 1) / TM_FP_TILE_H);
     if (chunks > 65535) chunks = 65535;
     long long cap = chunks * n_b64 * 8;
     if (cap > 0x7fffffffLL) cap = 0x7fffffffLL;
@@ -226,6 +245,7 @@ int svtme_launch_picture_me(const PicJob *h_jobs, int n, const PicJob *d_jobs, c
         const int qw = ((((ci.hme_l0_sa.sa_max.width / 2) + 15) & ~15) + 7) & ~7;
         mt_l0 = imax_h(mt_l0, tiles_of(qw, ci.hme_l0_sa.sa_max.height / 2));
     }
+    opt_in_shared_memory();
     if (ev_hme0) cudaEventRecord(ev_hme0, st);
     cudaMemsetAsync(j0.fp_counters, 0, 2 * sizeof(uint32_t), st);
     if (any_zz) {
@@ -260,9 +280,15 @@ int svtme_launch_picture_me(const PicJob *h_jobs, int n, const PicJob *d_jobs, c
         launches++;
     };
     auto search_wide = [&](int level) {
-        const dim3 grid((n_b64 * HME_JOBS_PER_B64 + SEARCH_WARPS - 1) / SEARCH_WARPS, ny);
-        if (sub) k_search_blk<true><<<grid, 32 * SEARCH_WARPS, 0, st>>>(d_jobs, level);
-        else k_search_blk<false><<<grid, 32 * SEARCH_WARPS, 0, st>>>(d_jobs, level);
+        const dim3 grid((n_b64 * 8 + SEARCH_WARPS - 1) / SEARCH_WARPS, ny);
+        const size_t smem = (size_t)SEARCH_WARPS * 2 * (level == 1 ? TM_L1_BUF : TM_L2_BUF) + 128;
+        if (level == 1) {
+            if (sub) k_search_blk<true, 1><<<grid, 32 * SEARCH_WARPS, smem, st>>>(d_jobs);
+            else k_search_blk<false, 1><<<grid, 32 * SEARCH_WARPS, smem, st>>>(d_jobs);
+        } else {
+            if (sub) k_search_blk<true, 2><<<grid, 32 * SEARCH_WARPS, smem, st>>>(d_jobs);
+            else k_search_blk<false, 2><<<grid, 32 * SEARCH_WARPS, smem, st>>>(d_jobs);
+        }
         launches++;
     };
     int fin_pending = ST_NONE;
@@ -316,20 +342,21 @@ int svtme_launch_picture_me(const PicJob *h_jobs, int n, const PicJob *d_jobs, c
 
     // ---- full-pel ----
     const bool fsub = c.me_search_method == SVTME_SUB_SAD_SEARCH;
+    const size_t fp_smem = (size_t)FP_WARPS * 2 * TM_FP_BUF + 128;
     if (!g_fp_search_ctas_per_sm) {
         int k = 0;
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&k, k_fp_big<true>, 32 * FP_WARPS, 0);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&k, k_fp_big<true>, 32 * FP_WARPS, fp_smem);
         g_fp_search_ctas_per_sm = k > 0 ? k : 1;
     }
     const dim3 plan_grid((n_b64 * 8 + FP_WARPS - 1) / FP_WARPS, ny);
     const int big_grid = n_sm * g_fp_search_ctas_per_sm;
     auto fp_round = [&](int phase) {
         if (fsub) {
-            k_fp<true><<<plan_grid, 32 * FP_WARPS, 0, st>>>(d_jobs, phase);
-            k_fp_big<true><<<big_grid, 32 * FP_WARPS, 0, st>>>(d_jobs);
+            k_fp<true><<<plan_grid, 32 * FP_WARPS, fp_smem, st>>>(d_jobs, phase);
+            k_fp_big<true><<<big_grid, 32 * FP_WARPS, fp_smem, st>>>(d_jobs);
         } else {
-            k_fp<false><<<plan_grid, 32 * FP_WARPS, 0, st>>>(d_jobs, phase);
-            k_fp_big<false><<<big_grid, 32 * FP_WARPS, 0, st>>>(d_jobs);
+            k_fp<false><<<plan_grid, 32 * FP_WARPS, fp_smem, st>>>(d_jobs, phase);
+            k_fp_big<false><<<big_grid, 32 * FP_WARPS, fp_smem, st>>>(d_jobs);
         }
         launches += 2;
     };
@@ -394,17 +421,45 @@ __global__ void __launch_bounds__(32 * SEARCH_WARPS) k_kat_search16(const uint8_
     if (lane == 0 && key != HME_KEY_NONE) atomicMin(out_key, key);
 }
 
-// blocks 17..64 wide or taller than 16 rows: the block-parallel search of k_search_blk, one warp
-__global__ void __launch_bounds__(32) k_kat_search_blk(const uint8_t *src, int src_stride, const uint8_t *ref, int raw_stride,
-                                                       int ref_stride, int bh, int bw, int sa_w, int sa_h, int ns_bits, int nb_bits,
+// blocks 17..64 wide or taller than 16 rows: the TMA tile search of k_search_blk, one warp. The reference window was
+// re-pitched by the caller (row pitch multiple of 16, `map` describes it); position (0,0) is its sample (0,0).
+template <int NS, int NR>
+__global__ void __launch_bounds__(32) k_kat_search_blk(const __grid_constant__ CUtensorMap map, const uint8_t *src, int src_stride,
+                                                       int bh, int bw, int row_step, int sa_w, int sa_h,
                                                        unsigned long long *out_key) {
-    const unsigned long long key = warp_search_blk<8>(src, src_stride, ref, raw_stride, ref_stride, bw, bh, sa_w, sa_h, ns_bits, nb_bits);
+    constexpr int PITCH = NS == 2 ? TM_L1_BOX_W : TM_L2_BOX_W;
+    constexpr int BOX_BYTES = NS == 2 ? TM_L1_BOX_W * TM_L1_BOX_H : TM_L2_BOX_W * TM_L2_BOX_H;
+    constexpr int BUF = NS == 2 ? TM_L1_BUF : TM_L2_BUF;
+    __shared__ __align__(128) uint8_t s_buf[2 * BUF];
+    __shared__ __align__(8) uint64_t s_bar[2];
+    TilePipe P;
+    pipe_init(P, s_buf, BUF, s_bar, BOX_BYTES);
+    TLane<NS, NR> L;
+    int row_of[NR];
+    blk_rows<NS, NR>(row_of, row_step);
+    const int ntx = (sa_w + TM_BLK_TILE_W - 1) / TM_BLK_TILE_W, nt = ntx * ((sa_h + TM_BLK_TILE_H - 1) / TM_BLK_TILE_H);
+    pipe_issue(P, 0, &map, 0, 0);
+    tlane_init<NS, NR>(L, src, src_stride, row_of, bw, bh * row_step, PITCH);
+    uint32_t best = 0xffffffffu;
+    int stage = 0;
+    for (int t = 0; t < nt; t++) {
+        const int ty = t / ntx, tx = t - ty * ntx;
+        if (t + 1 < nt) {
+            const int ty1 = (t + 1) / ntx, tx1 = (t + 1) - ty1 * ntx;
+            pipe_issue(P, stage ^ 1, &map, TM_BLK_TILE_W * tx1, TM_BLK_TILE_H * ty1);
+        }
+        pipe_wait(P, stage);
+        blk_tile_eval<NS, NR>(L, P.buf[stage], PITCH, 0, tx, ty, sa_w, sa_h, best);
+        __syncwarp();
+        stage ^= 1;
+    }
+    const unsigned long long key = blk_key64(best);
     if (threadIdx.x == 0) *out_key = key;
 }
 
 int svtme_launch_kat_sad_loop(const uint8_t *d_src, int src_stride, const uint8_t *d_ref, int ref_stride, int bh, int bw,
                               int src_stride_raw, int skip, int sa_w, int sa_h, unsigned long long *d_key,
-                              cudaStream_t st) {
+                              uint8_t *d_pitched, size_t pitched_cap, cudaStream_t st) {
     const unsigned long long init = HME_KEY_NONE;
     cudaMemcpyAsync(d_key, &init, sizeof(init), cudaMemcpyHostToDevice, st);
     if (sa_w <= 0 || sa_h <= 0) return 0;
@@ -415,12 +470,24 @@ int svtme_launch_kat_sad_loop(const uint8_t *d_src, int src_stride, const uint8_
         s16_tile_geometry(sa_w, sa_h, bh, row_step, &tw, &th, &ntx, &nty);
         k_kat_search16<<<(ntx * nty + SEARCH_WARPS - 1) / SEARCH_WARPS, 32 * SEARCH_WARPS, 0, st>>>(
             d_src, src_stride, d_ref, src_stride_raw, row_step, bh, bw, skip, sa_w, sa_h, tw, th, ntx, nty, d_key);
-    } else if (bw <= 64 && bh <= 64) {
-        // lanes = strips x row bands (x search rows): 8 rows per band at most
-        const int ns_bits = bw <= 16 ? 0 : (bw <= 32 ? 1 : 2);
-        int nb_bits = 0;
-        while (nb_bits + ns_bits < 5 && (8 << nb_bits) < bh) nb_bits++;
-        k_kat_search_blk<<<1, 32, 0, st>>>(d_src, src_stride, d_ref, src_stride_raw, ref_stride, bh, bw, sa_w, sa_h, ns_bits, nb_bits, d_key);
+    } else if (strided && bw <= 64 && bh * (ref_stride / src_stride_raw) <= 64 && d_pitched && sa_w * sa_h <= 4096) {
+        // re-pitch the window (rows 16-byte aligned, as the picture store keeps its planes) and describe it to the TMA
+        const int row_step = ref_stride / src_stride_raw;
+        const int w_bytes = sa_w - 1 + bw, rows = sa_h - 1 + (bh - 1) * row_step + 1;
+        const int pitch = (w_bytes + 15 + 16) & ~15;
+        if ((size_t)pitch * rows > pitched_cap) return 0;
+        cudaMemsetAsync(d_pitched, 0, (size_t)pitch * rows, st);
+        cudaMemcpy2DAsync(d_pitched, pitch, d_ref, src_stride_raw, w_bytes, rows, cudaMemcpyDeviceToDevice, st);
+        const bool small = bw <= 32 && bh * row_step <= 32;
+        CUtensorMap map;
+        if (svtme_encode_tmap(&map, d_pitched, pitch, rows, small ? TM_L1_BOX_W : TM_L2_BOX_W, small ? TM_L1_BOX_H : TM_L2_BOX_H)) return 0;
+        if (small) {
+            if (bh <= 16) k_kat_search_blk<2, 1><<<1, 32, 0, st>>>(map, d_src, src_stride / row_step, bh, bw, row_step, sa_w, sa_h, d_key);
+            else k_kat_search_blk<2, 2><<<1, 32, 0, st>>>(map, d_src, src_stride / row_step, bh, bw, row_step, sa_w, sa_h, d_key);
+        } else {
+            if (bh <= 32) k_kat_search_blk<4, 4><<<1, 32, 0, st>>>(map, d_src, src_stride / row_step, bh, bw, row_step, sa_w, sa_h, d_key);
+            else k_kat_search_blk<4, 8><<<1, 32, 0, st>>>(map, d_src, src_stride / row_step, bh, bw, row_step, sa_w, sa_h, d_key);
+        }
     } else {
         const int n = sa_w * sa_h;
         k_kat_sad_loop_generic<<<(n + 127) / 128, 128, 0, st>>>(d_src, src_stride, d_ref, ref_stride, bh, bw, src_stride_raw,
@@ -430,27 +497,39 @@ int svtme_launch_kat_sad_loop(const uint8_t *d_src, int src_stride, const uint8_
 }
 
 // svt_ext_all_sad_calculation_8x8_16x16 / svt_ext_sad_calculation_8x8_16x16: raw SADs of all 85 PUs at
-// n_pos consecutive horizontal positions, through the pass routine of k_fp (one warp).
+// n_pos consecutive horizontal positions, through the tile routines of k_fp (one warp). d_ref: 96-byte pitch.
 template <bool SUB>
-__global__ void __launch_bounds__(32) k_kat_octet(const uint8_t *src, int src_stride, const uint8_t *ref, int ref_stride,
-                                                  int n_pos, uint32_t *out /*[n_pos][85]*/) {
+__global__ void __launch_bounds__(32) k_kat_octet(const __grid_constant__ CUtensorMap map, const uint8_t *src, int src_stride, int n_pos,
+                                                  uint32_t *out /*[n_pos][85]*/) {
+    __shared__ __align__(128) uint8_t s_buf[2 * TM_FP_BUF];
+    __shared__ __align__(8) uint64_t s_bar[2];
+    TilePipe P;
+    pipe_init(P, s_buf, TM_FP_BUF, s_bar, TM_FP_BOX_W * TM_FP_BOX_H);
+    pipe_issue(P, 0, &map, 0, 0);
     FpLane<SUB> L;
-    fp_lane_init<SUB>(L, src, src_stride);
+    fp_lane_init<SUB>(L, src, src_stride, 64, 64);
+    pipe_wait(P, 0);
+    const int lane = threadIdx.x & 31, strip = lane & 3, band = lane >> 2;
+    const int z = c_z16b[4 * (band >> 1) + strip], k = 2 * (band & 1);
     for (int p = 0; p < n_pos; p++) {
         uint32_t raw[5];
-        fp_eval_pass<SUB>(L, ref + p, ref_stride, 1u, 0u, raw);
-        const uint32_t vals[5] = {raw[0], raw[1], raw[2], raw[3], raw[4]};
-        // same ownership walk as the search: (value, PU)
-        FpLane<SUB> V = L;
-        V.kl = vals[0]; V.kr = vals[1]; V.k16 = vals[2]; V.k32 = vals[3]; V.k64 = vals[4];
-        fp_for_owned<SUB>(V, [&](uint32_t v, int pu) { out[p * 85 + pu] = v << (SUB ? 1 : 0); });
+        fp_eval_one<SUB>(L, P.buf[0], (uint32_t)p, 0u, raw);
+        uint32_t *o = out + p * 85;
+        const int dbl = SUB ? 1 : 0;
+        o[21 + 4 * z + k] = raw[0] << dbl;
+        o[21 + 4 * z + k + 1] = raw[1] << dbl;
+        if ((band & 1) == 0) o[5 + z] = raw[2] << dbl;
+        if ((band & 3) == 0 && (strip & 1) == 0) o[1 + 2 * (band >> 2) + (strip >> 1)] = raw[3] << dbl;
+        if (lane == 0) o[0] = raw[4] << dbl;
     }
 }
 
-int svtme_launch_kat_octet(const uint8_t *d_src, int src_stride, const uint8_t *d_ref, int ref_stride, int sub, int n_pos,
+int svtme_launch_kat_octet(const uint8_t *d_src, int src_stride, const uint8_t *d_ref, int ref_pitch, int ref_rows, int sub, int n_pos,
                            uint32_t *d_out, cudaStream_t st) {
-    if (sub) k_kat_octet<true><<<1, 32, 0, st>>>(d_src, src_stride, d_ref, ref_stride, n_pos, d_out);
-    else k_kat_octet<false><<<1, 32, 0, st>>>(d_src, src_stride, d_ref, ref_stride, n_pos, d_out);
+    CUtensorMap map;
+    if (svtme_encode_tmap(&map, d_ref, ref_pitch, ref_rows, TM_FP_BOX_W, TM_FP_BOX_H)) return 0;
+    if (sub) k_kat_octet<true><<<1, 32, 0, st>>>(map, d_src, src_stride, n_pos, d_out);
+    else k_kat_octet<false><<<1, 32, 0, st>>>(map, d_src, src_stride, n_pos, d_out);
     return 1;
 }
 

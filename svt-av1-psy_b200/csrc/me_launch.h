@@ -17,9 +17,12 @@ uint32_t svtme_s16_units_cap(const SvtMePicParams &pp, int n_b64);
 int  svtme_launch_picture_me(const PicJob *h_jobs, int n, const PicJob *d_jobs, cudaStream_t st, cudaEvent_t ev_hme0,
                              cudaEvent_t ev_hme1, cudaEvent_t ev_fp1);
 int  svtme_launch_kat_sad_loop(const uint8_t *d_src, int src_stride, const uint8_t *d_ref, int ref_stride, int bh, int bw,
-                               int src_stride_raw, int skip, int sa_w, int sa_h, unsigned long long *d_key, cudaStream_t st);
-int  svtme_launch_kat_octet(const uint8_t *d_src, int src_stride, const uint8_t *d_ref, int ref_stride, int sub, int n_pos,
-                            uint32_t *d_out, cudaStream_t st);
+                               int src_stride_raw, int skip, int sa_w, int sa_h, unsigned long long *d_key, uint8_t *d_pitched,
+                               size_t pitched_cap, cudaStream_t st);
+int  svtme_launch_kat_octet(const uint8_t *d_src, int src_stride, const uint8_t *d_ref, int ref_pitch, int ref_rows, int sub,
+                            int n_pos, uint32_t *d_out, cudaStream_t st);
+// CUtensorMap (128 bytes at `out`) of a u8 plane: rows of `pitch` bytes (multiple of 16), base 16-byte aligned. 0 = ok.
+int  svtme_encode_tmap(void *out, const void *base, size_t pitch, size_t rows, uint32_t box_w, uint32_t box_h);
 int  svtme_launch_kat_nxm(const uint8_t *d_src, int src_stride, const uint8_t *d_ref, int ref_stride, int h, int w,
                           uint32_t *d_out, cudaStream_t st);
 int  svtme_launch_fill32(uint32_t *d_p, uint32_t n, uint32_t v, cudaStream_t st);

@@ -16,6 +16,7 @@
 // the first minimum in raster order.
 #pragma once
 #include "me_device.cuh"
+#include "me_tma.cuh"
 
 #define SEARCH_WARPS 4
 
@@ -252,140 +253,131 @@ __device__ __forceinline__ unsigned long long octet_best_key(const uint32_t (&ac
 
 // ---- block-parallel search for wide blocks (HME level 1 / 2) -----------------------------------
 // Windows here are tiny (8x3 .. 16x16 positions) and blocks large (32x16 .. 64x64 samples), so the
-// lanes are spread over the BLOCK instead of over positions: lane = (ypos, band, strip) with
-// NY*NB*NS = 32; a lane sums RB rows of its 16-pixel strip for 8 consecutive positions of search row
-// y0+ypos, straight from global memory (7 aligned words per row + one funnel shift per word), and
-// shfl_xor adds bands and strips. No shared memory, no staging latency chain, all loads of a pass
-// in flight at once. Leaders (band 0, strip 0) keep the running best of their search rows.
-template <int RB>
-struct BlkLane {
-    uint32_t src[RB][4];
-    uint32_t m[4];     // byte masks of this strip (block narrower than 16*NS)
-    int      strip, band, ypos, row0, n_rows;
-    bool     full;
-};
+// lanes are spread over the BLOCK instead of over positions: lane = band * NS + strip; a lane sums NR
+// rows of its 16-pixel strip for 8 consecutive positions per pass, from a tile that one TMA load put in
+// shared memory (me_tma.cuh); 9 shuffles add the 32 lanes. Tiles are 16 positions x 4 search rows and
+// double-buffered per warp, across the quadrant searches of one (b64, list, ref).
+#define BLK_IDX_BITS 12 /* y * sa_w + x < 4096; SAD < 2^20 */
 
-template <int RB>
-__device__ __forceinline__ void blk_lane_init(BlkLane<RB> &L, const uint8_t *src, int src_blk_stride, int bw, int n_rows,
-                                              int ns_bits, int nb_bits) {
-    const int lane = threadIdx.x & 31;
-    L.strip = lane & ((1 << ns_bits) - 1);
-    L.band  = (lane >> ns_bits) & ((1 << nb_bits) - 1);
-    L.ypos  = lane >> (ns_bits + nb_bits);
-    L.row0  = L.band * RB;
-    L.n_rows = n_rows;
-    const int rem = bw - 16 * L.strip;
-    L.full = rem >= 16;
-    L.m[0] = lo_bytes_mask(rem); L.m[1] = lo_bytes_mask(rem - 4); L.m[2] = lo_bytes_mask(rem - 8); L.m[3] = lo_bytes_mask(rem - 12);
+// block rows of lane `band` for the HME levels: used row j = band + NB * q, sample row = row_step * j
+template <int NS, int NR>
+__device__ __forceinline__ void blk_rows(int (&row_of)[NR], int row_step) {
+    const int band = (threadIdx.x & 31) / NS;
 #pragma unroll
-    for (int q = 0; q < RB; q++)
-#pragma unroll
-        for (int k = 0; k < 4; k++)
-            L.src[q][k] = (L.row0 + q < n_rows) ? (ldg_u32_unaligned(src + (size_t)(L.row0 + q) * src_blk_stride + 16 * L.strip + 4 * k) & L.m[k]) : 0u;
+    for (int q = 0; q < NR; q++) row_of[q] = row_step * (band + (32 / NS) * q);
 }
 
-// acc[p] = SAD of the whole block at positions (x+p, y) for the lanes of that ypos group
-template <int RB>
-__device__ __forceinline__ void blk_eval_pass(const BlkLane<RB> &L, const uint8_t *ref /* sample aligned with block (0,0) at position x,y */,
-                                              int ref_blk_stride, bool active, int ns_bits, int nb_bits, uint32_t (&acc)[8]) {
-#pragma unroll
-    for (int p = 0; p < 8; p++) acc[p] = 0;
-    if (active) {
-        const uint8_t *g = ref + (size_t)L.row0 * ref_blk_stride + 16 * L.strip;
-        uint32_t gw[RB][7];
-        uint32_t sa[RB];
-#pragma unroll
-        for (int q = 0; q < RB; q++) {
-            const uintptr_t a = (uintptr_t)(g + (size_t)q * ref_blk_stride);
-            const uint32_t *qp = (const uint32_t *)(a & ~(uintptr_t)3);
-            sa[q] = (uint32_t)(a & 3) * 8;
-            const bool ok = L.row0 + q < L.n_rows;
-#pragma unroll
-            for (int k = 0; k < 7; k++) gw[q][k] = ok ? __ldg(qp + k) : 0u;
-        }
-#pragma unroll
-        for (int q = 0; q < RB; q++) {
-            uint32_t w[6];
-#pragma unroll
-            for (int k = 0; k < 6; k++) w[k] = __funnelshift_r(gw[q][k], gw[q][k + 1], sa[q]);
-            if (L.full) {
-                strip16_sad8(w, L.src[q], acc);
-            } else {
-#pragma unroll
-                for (int p = 0; p < 8; p++) {
-                    const int o = p >> 2, shf = (p & 3) * 8;
-                    const uint32_t v0 = shf ? __funnelshift_r(w[o], w[o + 1], shf) : w[o];
-                    const uint32_t v1 = shf ? __funnelshift_r(w[o + 1], w[o + 2], shf) : w[o + 1];
-                    const uint32_t v2 = shf ? __funnelshift_r(w[o + 2], w[o + 3], shf) : w[o + 2];
-                    const uint32_t v3 = shf ? __funnelshift_r(w[o + 3], w[o + 4], shf) : w[o + 3];
-                    acc[p] += __vsadu4(v0 & L.m[0], L.src[q][0]) + __vsadu4(v1 & L.m[1], L.src[q][1]) +
-                        __vsadu4(v2 & L.m[2], L.src[q][2]) + __vsadu4(v3 & L.m[3], L.src[q][3]);
-                }
+// every position of tile (tx, ty) of a window whose position (0,0) is plane sample (px, py); buf = shared address of
+// the tile, loaded from (px + 16 tx) & ~15. best: per-lane running key (sad << BLK_IDX_BITS | y * sa_w + x).
+template <int NS, int NR>
+__device__ __forceinline__ void blk_tile_eval(const TLane<NS, NR> &L, uint32_t buf, int pitch, int px, int tx, int ty, int sa_w,
+                                              int sa_h, uint32_t &best) {
+    const uint32_t a = (uint32_t)(px + TM_BLK_TILE_W * tx) & 15u;
+    const int n_x = imin(TM_BLK_TILE_W, sa_w - TM_BLK_TILE_W * tx), n_y = imin(TM_BLK_TILE_H, sa_h - TM_BLK_TILE_H * ty);
+    const int pos = reduce8_pos();
+    for (int yy = 0; yy < n_y; yy++) {
+        for (int o = 0; 8 * o < n_x; o++) {
+            uint32_t acc[8], unused[8];
+            tile_pass<NS, NR, false>(L, buf + (uint32_t)(yy * pitch), a + 8u * o, acc, unused);
+            const uint32_t sad = reduce8_all(acc);
+            const int x = 8 * o + pos;
+            if (x < n_x) {
+                const uint32_t idx = (uint32_t)((TM_BLK_TILE_H * ty + yy) * sa_w + TM_BLK_TILE_W * tx + x);
+                best = min(best, (sad << BLK_IDX_BITS) | idx);
             }
         }
     }
-    const int gbits = ns_bits + nb_bits;
-#pragma unroll
-    for (int p = 0; p < 8; p++) {
-        if (gbits >= 1) acc[p] += __shfl_xor_sync(0xffffffffu, acc[p], 1);
-        if (gbits >= 2) acc[p] += __shfl_xor_sync(0xffffffffu, acc[p], 2);
-        if (gbits >= 3) acc[p] += __shfl_xor_sync(0xffffffffu, acc[p], 4);
-        if (gbits >= 4) acc[p] += __shfl_xor_sync(0xffffffffu, acc[p], 8);
-        if (gbits >= 5) acc[p] += __shfl_xor_sync(0xffffffffu, acc[p], 16);
-    }
 }
 
-// whole search of one job by one warp; returns the best key (all lanes)
-template <int RB>
-__device__ inline unsigned long long warp_search_blk(const uint8_t *src, int src_blk_stride, const uint8_t *ref, int search_stride,
-                                                     int ref_blk_stride, int bw, int n_rows, int sa_w, int sa_h, int ns_bits,
-                                                     int nb_bits) {
-    BlkLane<RB> L;
-    blk_lane_init<RB>(L, src, src_blk_stride, bw, n_rows, ns_bits, nb_bits);
-    const int ny = 32 >> (ns_bits + nb_bits); // search rows per pass
-    const int n_oct = (sa_w + 7) >> 3;
-    uint32_t best_sad = 0xffffff, best_idx = 0xffffffffu;
-    for (int y0 = 0; y0 < sa_h; y0 += ny) {
-        const int  y      = y0 + L.ypos;
-        const bool active = y < sa_h;
-        for (int oct = 0; oct < n_oct; oct++) {
-            uint32_t acc[8];
-            blk_eval_pass<RB>(L, ref + (size_t)y * search_stride + 8 * oct, ref_blk_stride, active, ns_bits, nb_bits, acc);
-            if (active && L.band == 0 && L.strip == 0) {
-#pragma unroll
-                for (int p = 0; p < 8; p++) {
-                    const int x = 8 * oct + p;
-                    if (x < sa_w && acc[p] < best_sad) {
-                        best_sad = acc[p];
-                        best_idx = (uint32_t)(y * sa_w + x);
-                    }
-                }
-            }
-        }
-    }
-    return warp_min_u64(((unsigned long long)best_sad << 32) | best_idx);
+__device__ __forceinline__ unsigned long long blk_key64(uint32_t best) {
+    best = __reduce_min_sync(0xffffffffu, best);
+    return best == 0xffffffffu ? HME_KEY_NONE
+                               : (((unsigned long long)(best >> BLK_IDX_BITS) << 32) | (best & ((1u << BLK_IDX_BITS) - 1)));
 }
 
 // ---- k_search_blk ----------------------------------------------------------------------------
-// one warp per job slot; level 1: 1/4 plane (32-wide blocks: 2 strips x 4 bands x 4 search rows),
-// level 2: full plane (64-wide blocks: 4 strips x 8 bands x 1 search row)
-template <bool SUB>
-__global__ void __launch_bounds__(32 * SEARCH_WARPS) k_search_blk(const PicJob *__restrict__ jobs, int level) {
+// one warp per (b64, list, ref): its (up to) 4 quadrant searches run back to back through one tile pipeline.
+// level 1: 1/4 plane, 32-wide blocks (NS = 2); level 2: full plane, 64-wide blocks (NS = 4).
+template <bool SUB, int LEVEL>
+__global__ void __launch_bounds__(32 * SEARCH_WARPS) k_search_blk(const PicJob *__restrict__ jobs) {
+    constexpr int NS = LEVEL == 1 ? 2 : 4;
+    constexpr int NR = (LEVEL == 1 ? 1 : 4) * (SUB ? 1 : 2);
+    constexpr int PITCH = LEVEL == 1 ? TM_L1_BOX_W : TM_L2_BOX_W;
+    constexpr int BOX_BYTES = LEVEL == 1 ? TM_L1_BOX_W * TM_L1_BOX_H : TM_L2_BOX_W * TM_L2_BOX_H;
+    constexpr int BUF = LEVEL == 1 ? TM_L1_BUF : TM_L2_BUF;
+    extern __shared__ __align__(128) uint8_t s_dyn[];
+    __shared__ __align__(8) uint64_t s_bar[SEARCH_WARPS][2];
     const PicJob &job = jobs[blockIdx.y];
-    const int lane = threadIdx.x & 31;
-    const int slot = blockIdx.x * SEARCH_WARPS + (threadIdx.x >> 5);
-    if (slot >= job.n_b64 * HME_JOBS_PER_B64) return;
-    HmeJobG &j = job.hme_jobs[slot];
-    if (!j.active || j.sa_w <= 0 || j.sa_h <= 0) return;
-    const int b = slot / HME_JOBS_PER_B64;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int u = blockIdx.x * SEARCH_WARPS + warp; // (b64, list, ref)
+    if (u >= job.n_b64 * 8) return;
+    HmeJobG *jq = job.hme_jobs + (size_t)u * 4;
+    // lanes 0..3 hold the four quadrant jobs
+    int my_act = 0, my_px = 0, my_py = 0, my_sw = 0, my_sh = 0;
+    const int b = u >> 3, l = (u >> 2) & 1, r = u & 3;
+    const DevPic   &rp = job.ref[l][r];
+    const DevPlane &pl = rp.lvl[LEVEL == 1 ? 1 : 0];
+    if (lane < 4) {
+        const HmeJobG &j = jq[lane];
+        if (j.active && j.sa_w > 0 && j.sa_h > 0) {
+            const long long off = j.ref - pl.buf;
+            my_act = 1; my_py = (int)(off / pl.stride); my_px = (int)(off - (long long)my_py * pl.stride);
+            my_sw = j.sa_w; my_sh = j.sa_h;
+        }
+    }
+    const uint32_t act_mask = __ballot_sync(0xffffffffu, my_act) & 0xfu;
+    if (!act_mask) return;
+    const CUtensorMap *map = (const CUtensorMap *)rp.tmap + (LEVEL == 1 ? TM_L1 : TM_L2);
+    uint8_t *sbase = s_dyn + ((128u - (smem_u32(s_dyn) & 127u)) & 127u);
+    TilePipe P;
+    pipe_init(P, sbase + (size_t)warp * 2 * BUF, BUF, s_bar[warp], BOX_BYTES);
+
     const B64Geo g = b64_geo(job, b);
-    const int row_step = SUB ? 2 : 1, shift = level == 1 ? 1 : 0;
-    const int bw = g.b64_w >> shift, rows = SUB ? (g.b64_h >> shift) >> 1 : (g.b64_h >> shift);
-    const DevPlane &sp = job.src.lvl[level == 1 ? 1 : 0];
+    constexpr int shift = LEVEL == 1 ? 1 : 0;
+    const int bw = g.b64_w >> shift, bh = g.b64_h >> shift;
+    const DevPlane &sp = job.src.lvl[LEVEL == 1 ? 1 : 0];
     const uint8_t *src = sp.buf + (size_t)(sp.org_y + (g.org_y >> shift)) * sp.stride + sp.org_x + (g.org_x >> shift);
-    constexpr int RB = SUB ? 4 : 8;
-    const unsigned long long key = level == 1
-        ? warp_search_blk<RB>(src, row_step * sp.stride, j.ref, j.ref_stride, row_step * j.ref_stride, bw, rows, j.sa_w, j.sa_h, 1, 2)
-        : warp_search_blk<RB>(src, row_step * sp.stride, j.ref, j.ref_stride, row_step * j.ref_stride, bw, rows, j.sa_w, j.sa_h, 2, 3);
-    if (lane == 0) j.key = key;
+    TLane<NS, NR> L;
+    int row_of[NR];
+    blk_rows<NS, NR>(row_of, SUB ? 2 : 1);
+
+    int q = __ffs(act_mask) - 1, t = 0;
+    int px = __shfl_sync(0xffffffffu, my_px, q), py = __shfl_sync(0xffffffffu, my_py, q);
+    int sw = __shfl_sync(0xffffffffu, my_sw, q), sh = __shfl_sync(0xffffffffu, my_sh, q);
+    int ntx = (sw + TM_BLK_TILE_W - 1) / TM_BLK_TILE_W, nt = ntx * ((sh + TM_BLK_TILE_H - 1) / TM_BLK_TILE_H);
+    pipe_issue(P, 0, map, (px) & ~15, py);
+    tlane_init<NS, NR>(L, src, sp.stride, row_of, bw, bh, PITCH); // overlaps the first tile load
+    int stage = 0;
+    uint32_t best = 0xffffffffu;
+    while (q < 4) {
+        // the tile after this one: next tile of the job, else first tile of the next active job
+        int nq = q, ntile = t + 1, npx = px, npy = py, nsw = sw, nsh = sh, nntx = ntx, nnt = nt;
+        if (ntile >= nt) {
+            const uint32_t rest = act_mask & ~((2u << q) - 1u);
+            nq = rest ? __ffs(rest) - 1 : 4;
+            ntile = 0;
+            if (nq < 4) {
+                npx = __shfl_sync(0xffffffffu, my_px, nq); npy = __shfl_sync(0xffffffffu, my_py, nq);
+                nsw = __shfl_sync(0xffffffffu, my_sw, nq); nsh = __shfl_sync(0xffffffffu, my_sh, nq);
+                nntx = (nsw + TM_BLK_TILE_W - 1) / TM_BLK_TILE_W; nnt = nntx * ((nsh + TM_BLK_TILE_H - 1) / TM_BLK_TILE_H);
+            }
+        }
+        if (nq < 4) {
+            const int ty = ntile / nntx, tx = ntile - ty * nntx;
+            pipe_issue(P, stage ^ 1, map, (npx + TM_BLK_TILE_W * tx) & ~15, npy + TM_BLK_TILE_H * ty);
+        }
+        pipe_wait(P, stage);
+        {
+            const int ty = t / ntx, tx = t - ty * ntx;
+            blk_tile_eval<NS, NR>(L, P.buf[stage], PITCH, px, tx, ty, sw, sh, best);
+        }
+        __syncwarp();
+        if (nq != q) {
+            const unsigned long long key = blk_key64(best);
+            if (lane == 0) jq[q].key = key;
+            best = 0xffffffffu;
+        }
+        q = nq; t = ntile; px = npx; py = npy; sw = nsw; sh = nsh; ntx = nntx; nt = nnt;
+        stage ^= 1;
+    }
 }

@@ -1,0 +1,229 @@
+// me_tma.cuh — search windows through TMA tile loads, and the block-parallel SAD evaluator that
+// reads them from shared memory.
+//
+// The searches with large blocks and small windows (HME level 1 / 2, full-pel) read a
+// (block + window) rectangle of a reference plane at an arbitrary byte position. Reading it with
+// per-lane LDGs costs one L1 wavefront per row touched per instruction and made those kernels
+// LSU-bound (profiles/r01_v3_summary.md). Here one lane issues ONE cp.async.bulk.tensor.2d per tile
+// (measured: ~2.5 cycles per box row per SM, asynchronous, tools/microbench/tma_box.cu) and the warp
+// reads the tile back with conflict-free LDS.128.
+//
+// TMA constraint (measured, traps otherwise): the innermost start coordinate must be 16-byte
+// aligned. A tile is therefore fetched from x & ~15 and the evaluator starts `beta` bytes into each
+// row: chunk select by address, word select by a warp-uniform 4-way switch, byte select by one
+// funnel shift per word.
+#pragma once
+#include <cuda.h>
+#include "me_device.cuh"
+
+// tensor-map kinds of one picture (DevPic::tmap[kind]); box = bytes per row x rows
+enum { TM_L1 = 0, TM_L2 = 1, TM_FP = 2, TM_KINDS = 3 };
+#define TM_L1_BOX_W 80  /* 32 + 15 (positions) + 15 (alignment) = 62; 80 = 5 chunks makes rows 2 apart hit different banks */
+#define TM_L1_BOX_H 35  /* 32 block rows + 4 search rows - 1 */
+#define TM_L2_BOX_W 96  /* 64 + 15 + 15 = 94 */
+#define TM_L2_BOX_H 67
+#define TM_FP_BOX_W 96
+#define TM_FP_BOX_H 71  /* 64 + 8 search rows - 1 */
+#define TM_BLK_TILE_W 16
+#define TM_BLK_TILE_H 4
+#define TM_FP_TILE_W 16
+#define TM_FP_TILE_H 8
+#define TM_ALIGN128(x) (((x) + 127) & ~127)
+#define TM_L1_BUF TM_ALIGN128(TM_L1_BOX_W * TM_L1_BOX_H)
+#define TM_L2_BUF TM_ALIGN128(TM_L2_BOX_W * TM_L2_BOX_H)
+#define TM_FP_BUF TM_ALIGN128(TM_FP_BOX_W * TM_FP_BOX_H)
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t *bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_fence_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+}
+// x must be a multiple of 16 (bytes); coordinates are relative to the plane buffer and may lie outside it (zero fill)
+__device__ __forceinline__ void tma_load_box(void *dst, const CUtensorMap *map, int x, int y, uint64_t *bar) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(
+                     smem_u32(dst)),
+                 "l"(map), "r"(x), "r"(y), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ uint4 lds128(uint32_t addr) {
+    uint4 v;
+    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+    return v;
+}
+
+// one warp's double-buffered tile pipeline
+struct TilePipe {
+    uint32_t  buf[2]; // shared addresses of the two stages
+    uint64_t *bar;    // two mbarriers
+    uint32_t  phase;  // bit s = parity the next wait on stage s expects
+    uint32_t  bytes;
+};
+__device__ __forceinline__ void pipe_init(TilePipe &P, uint8_t *stage0, uint32_t stage_bytes, uint64_t *bars, uint32_t box_bytes) {
+    P.buf[0] = smem_u32(stage0);
+    P.buf[1] = P.buf[0] + stage_bytes;
+    P.bar = bars;
+    P.phase = 0;
+    P.bytes = box_bytes;
+    if ((threadIdx.x & 31) == 0) { mbar_init(&bars[0], 1); mbar_init(&bars[1], 1); }
+    mbar_fence_init();
+    __syncwarp();
+}
+// the caller guarantees that every lane has finished reading stage s (a __syncwarp after the reads)
+__device__ __forceinline__ void pipe_issue(TilePipe &P, int s, const CUtensorMap *map, int x_aligned, int y) {
+    if ((threadIdx.x & 31) == 0) {
+        mbar_expect_tx(&P.bar[s], P.bytes);
+        asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(
+                         P.buf[s]),
+                     "l"(map), "r"(x_aligned), "r"(y), "r"(smem_u32(&P.bar[s]))
+                     : "memory");
+    }
+}
+__device__ __forceinline__ void pipe_wait(TilePipe &P, int s) {
+    mbar_wait(&P.bar[s], (P.phase >> s) & 1u);
+    P.phase ^= 1u << s;
+}
+
+// ---- the evaluator ---------------------------------------------------------------------------
+// lane = band * NS + strip: strip = 16-pixel column of the block, band = group of NR block rows.
+// roff[q]: byte offset inside the tile of the q-th row this lane sums, for search row 0.
+template <int NS, int NR>
+struct TLane {
+    uint32_t src[NR][4];
+    uint32_t roff[NR];
+    uint32_t m[4];   // byte masks of a strip that is cut by the block's right edge
+    uint32_t rowok;  // bit q: row q exists (blocks cut by the picture's bottom edge)
+    int      strip, band;
+    bool     full;   // warp-uniform: the block has all its columns and rows
+};
+
+// rows: lane-specific block rows row_of[q] (block coordinates, already multiplied by the row step); pitch: tile row pitch
+template <int NS, int NR>
+__device__ __forceinline__ void tlane_init(TLane<NS, NR> &L, const uint8_t *src, int src_stride, const int (&row_of)[NR], int bw, int bh,
+                                           int pitch) {
+    const int lane = threadIdx.x & 31;
+    L.strip = lane % NS;
+    L.band  = lane / NS;
+    const int rem = bw - 16 * L.strip;
+    L.m[0] = lo_bytes_mask(rem); L.m[1] = lo_bytes_mask(rem - 4); L.m[2] = lo_bytes_mask(rem - 8); L.m[3] = lo_bytes_mask(rem - 12);
+    L.rowok = 0;
+    bool all = rem >= 16;
+#pragma unroll
+    for (int q = 0; q < NR; q++) {
+        const bool ok = row_of[q] < bh;
+        all = all && ok;
+        L.rowok |= ok ? (1u << q) : 0u;
+        L.roff[q] = (uint32_t)(row_of[q] * pitch + 16 * L.strip);
+        uint4 v = make_uint4(0, 0, 0, 0);
+        if (ok && rem > 0) v = __ldg((const uint4 *)(src + (size_t)row_of[q] * src_stride + 16 * L.strip)); // block origins are 16-byte aligned
+        L.src[q][0] = v.x & L.m[0]; L.src[q][1] = v.y & L.m[1]; L.src[q][2] = v.z & L.m[2]; L.src[q][3] = v.w & L.m[3];
+    }
+    L.full = __all_sync(0xffffffffu, all);
+}
+
+// w[0..5] = the 24 bytes that start (16*cj + 4*J + t) bytes into the row: J = word offset inside the first chunk
+template <int J>
+__device__ __forceinline__ void tile_row_words(uint32_t addr, uint32_t t8, uint32_t (&w)[6]) {
+    uint32_t c[12];
+    const uint4 a = lds128(addr), b = lds128(addr + 16);
+    c[0] = a.x; c[1] = a.y; c[2] = a.z; c[3] = a.w; c[4] = b.x; c[5] = b.y; c[6] = b.z; c[7] = b.w;
+    if (J >= 2) {
+        const uint4 d = lds128(addr + 32);
+        c[8] = d.x; c[9] = d.y; c[10] = d.z; c[11] = d.w;
+    } else {
+        c[8] = c[9] = c[10] = c[11] = 0;
+    }
+    // J <= 1 needs c[J+6] <= c[7]; the funnel of the last word with shift 0 only reads its low operand
+#pragma unroll
+    for (int k = 0; k < 6; k++) w[k] = __funnelshift_r(c[J + k], c[J + k + 1], t8);
+}
+
+// one pass: the 8 positions whose first byte lies beta bytes into tile row `yy` (row_base = shared address of that row).
+// SPLIT: left / right 8 pixels of the strip kept apart (accl, accr), else summed into accl.
+template <int NS, int NR, bool SPLIT, int J>
+__device__ __forceinline__ void tile_pass_j(const TLane<NS, NR> &L, uint32_t row_base, uint32_t beta, uint32_t (&accl)[8], uint32_t (&accr)[8]) {
+    const uint32_t base = row_base + (beta & ~15u), t8 = (beta & 3u) * 8u;
+#pragma unroll
+    for (int q = 0; q < NR; q++) {
+        uint32_t w[6];
+        tile_row_words<J>(base + L.roff[q], t8, w);
+        if (!L.full) {
+            const uint32_t rm = (L.rowok >> q) & 1u ? 0xffffffffu : 0u;
+            // a strip narrower than 16 pixels: positions read past it, mask what the source masks
+            uint32_t x[8][4];
+#pragma unroll
+            for (int p = 0; p < 8; p++) {
+                const int o = p >> 2, sh = (p & 3) * 8;
+#pragma unroll
+                for (int k = 0; k < 4; k++) {
+                    const uint32_t v = sh ? __funnelshift_r(w[o + k], w[o + k + 1], sh) : w[o + k];
+                    x[p][k] = v & L.m[k] & rm;
+                }
+            }
+#pragma unroll
+            for (int p = 0; p < 8; p++)
+#pragma unroll
+                for (int k = 0; k < 4; k++) {
+                    if (SPLIT && k >= 2) accr[p] = sad4_acc(x[p][k], L.src[q][k], accr[p]);
+                    else accl[p] = sad4_acc(x[p][k], L.src[q][k], accl[p]);
+                }
+        } else if (SPLIT) {
+            strip16_sad8_split(w, L.src[q], accl, accr);
+        } else {
+            strip16_sad8(w, L.src[q], accl);
+        }
+    }
+}
+
+template <int NS, int NR, bool SPLIT>
+__device__ __forceinline__ void tile_pass(const TLane<NS, NR> &L, uint32_t row_base, uint32_t beta, uint32_t (&accl)[8], uint32_t (&accr)[8]) {
+#pragma unroll
+    for (int p = 0; p < 8; p++) accl[p] = accr[p] = 0;
+    switch ((beta & 15u) >> 2) { // warp-uniform
+    case 0: tile_pass_j<NS, NR, SPLIT, 0>(L, row_base, beta, accl, accr); break;
+    case 1: tile_pass_j<NS, NR, SPLIT, 1>(L, row_base, beta, accl, accr); break;
+    case 2: tile_pass_j<NS, NR, SPLIT, 2>(L, row_base, beta, accl, accr); break;
+    default: tile_pass_j<NS, NR, SPLIT, 3>(L, row_base, beta, accl, accr); break;
+    }
+}
+
+// Sum 8 per-lane values over the 32 lanes with halving exchanges (9 shuffles instead of 40). Every lane returns
+// the total of position reduce8_pos(lane).
+__device__ __forceinline__ uint32_t reduce8_all(const uint32_t (&v)[8]) {
+    const int  lane = threadIdx.x & 31;
+    const bool h16 = lane & 16, h8 = lane & 8, h4 = lane & 4;
+    uint32_t u[4], t[2];
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        const uint32_t mine = h16 ? v[4 + i] : v[i], theirs = h16 ? v[i] : v[4 + i];
+        u[i] = mine + __shfl_xor_sync(0xffffffffu, theirs, 16);
+    }
+#pragma unroll
+    for (int i = 0; i < 2; i++) {
+        const uint32_t mine = h8 ? u[2 + i] : u[i], theirs = h8 ? u[i] : u[2 + i];
+        t[i] = mine + __shfl_xor_sync(0xffffffffu, theirs, 8);
+    }
+    const uint32_t mine = h4 ? t[1] : t[0], theirs = h4 ? t[0] : t[1];
+    uint32_t r = mine + __shfl_xor_sync(0xffffffffu, theirs, 4);
+    r += __shfl_xor_sync(0xffffffffu, r, 2);
+    r += __shfl_xor_sync(0xffffffffu, r, 1);
+    return r;
+}
+__device__ __forceinline__ int reduce8_pos() {
+    const int lane = threadIdx.x & 31;
+    return ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
+}
