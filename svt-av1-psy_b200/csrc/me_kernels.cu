@@ -76,38 +76,46 @@ __global__ void __launch_bounds__(256) k_ingest(const void *in, int in_stride /*
     *(uint16_t *)(const_cast<uint8_t *>(s.buf) + (size_t)(s.org_y + (y >> 2)) * s.stride + s.org_x + (x >> 2)) = (uint16_t)s16;
 }
 
-// Replicate padding of the three planes in one launch (blockIdx.z = level): every padded sample is the
-// interior sample at the clamped coordinate. A thread writes one aligned 4-byte group of a padded row;
-// rows that cross the interior only have their left and right bands visited.
-__global__ void __launch_bounds__(128) k_pad_planes(DevPic pic) {
-    const DevPlane &p = pic.lvl[blockIdx.z];
-    const int pad = p.org_x, w = p.width, h = p.height;
-    const int W = w + 2 * pad, H = h + 2 * pad, W4 = (W + 3) >> 2;
-    const int y = blockIdx.y;
-    if (y >= H) return;
-    const bool band = y < pad || y >= pad + h;
-    const int lg = pad >> 2;                       // groups wholly left of the interior (pads are multiples of 4)
-    const int rg0 = (pad + w) >> 2;                // first group that touches the right padding
-    int g = blockIdx.x * blockDim.x + threadIdx.x;
-    if (!band) {
-        const int n = lg + (W4 - rg0);
-        if (g >= n) return;
-        if (g >= lg) g = rg0 + (g - lg);
-    } else if (g >= W4) {
+// Replicate padding of the three planes in one launch: every padded sample is the interior sample at the
+// clamped coordinate. A thread writes one aligned 4-byte group; only groups that hold padding are enumerated
+// (top band, bottom band, then the left and right bands of the interior rows), level after level.
+__global__ void __launch_bounds__(256) k_pad_planes(DevPic pic) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+#pragma unroll
+    for (int lv = 0; lv < 3; lv++) {
+        const DevPlane &p = pic.lvl[lv];
+        const int pad = p.org_x, w = p.width, h = p.height;
+        const int W4 = (w + 2 * pad + 3) >> 2;
+        const int lg = pad >> 2;          // groups wholly left of the interior (pads are multiples of 4)
+        const int rg0 = (pad + w) >> 2;   // first group that touches the right padding
+        const int side = lg + (W4 - rg0);
+        const int n_band = pad * W4, n_mid = h * side;
+        if (i >= 2 * n_band + n_mid) { i -= 2 * n_band + n_mid; continue; }
+        int y, g;
+        if (i < 2 * n_band) {
+            const int r = i / W4;
+            g = i - r * W4;
+            y = r < pad ? r : h + r; // r in [pad, 2 pad) -> rows pad + h ..
+        } else {
+            const int k = i - 2 * n_band, r = k / side;
+            g = k - r * side;
+            if (g >= lg) g = rg0 + (g - lg);
+            y = pad + r;
+        }
+        uint8_t *row = const_cast<uint8_t *>(p.buf) + (size_t)y * p.stride;
+        const uint8_t *srow = p.buf + (size_t)(min(max(y - pad, 0), h - 1) + pad) * p.stride + pad;
+        const int x0 = 4 * g - pad; // interior coordinate of the group's first byte
+        uint32_t v;
+        if (x0 >= 0 && x0 + 3 < w) {
+            v = *(const uint32_t *)(srow + x0);
+        } else {
+            v = 0;
+#pragma unroll
+            for (int k = 0; k < 4; k++) v |= (uint32_t)srow[min(max(x0 + k, 0), w - 1)] << (8 * k);
+        }
+        *(uint32_t *)(row + 4 * g) = v;
         return;
     }
-    uint8_t *row = const_cast<uint8_t *>(p.buf) + (size_t)y * p.stride;
-    const uint8_t *srow = p.buf + (size_t)(min(max(y - pad, 0), h - 1) + pad) * p.stride + pad;
-    const int x0 = 4 * g - pad; // interior coordinate of the group's first byte
-    uint32_t v;
-    if (x0 >= 0 && x0 + 3 < w) {
-        v = *(const uint32_t *)(srow + x0);
-    } else {
-        v = 0;
-#pragma unroll
-        for (int i = 0; i < 4; i++) v |= (uint32_t)srow[min(max(x0 + i, 0), w - 1)] << (8 * i);
-    }
-    *(uint32_t *)(row + 4 * g) = v;
 }
 
 // generic svt_aom_downsample_2d_c semantics (any step), for the RTCD-signature wrapper
@@ -131,8 +139,13 @@ int svtme_launch_build_pyramid(const DevPic &pic, int mode, const void *d_in, in
     if (mode == 0) k_ingest<0><<<grid, blk, 0, st>>>(d_in, in_stride, pic);
     else if (mode == 1) k_ingest<1><<<grid, blk, 0, st>>>(nullptr, 0, pic);
     else k_ingest<2><<<grid, blk, 0, st>>>(d_in, in_stride, pic);
-    const int W4 = (f.width + 2 * f.org_x + 3) >> 2;
-    k_pad_planes<<<dim3((unsigned)((W4 + 127) / 128), (unsigned)(f.height + 2 * f.org_y), 3), 128, 0, st>>>(pic);
+    long long groups = 0;
+    for (int lv = 0; lv < 3; lv++) {
+        const DevPlane &p = pic.lvl[lv];
+        const int W4 = (p.width + 2 * p.org_x + 3) >> 2;
+        groups += 2LL * p.org_x * W4 + (long long)p.height * ((p.org_x >> 2) + W4 - ((p.org_x + p.width) >> 2));
+    }
+    k_pad_planes<<<(unsigned)((groups + 255) / 256), 256, 0, st>>>(pic);
     return 2;
 }
 
