@@ -135,69 +135,74 @@ __device__ __forceinline__ void tlane_init(TLane<NS, NR> &L, const uint8_t *src,
     L.full = __all_sync(0xffffffffu, all);
 }
 
-// w[0..5] = the 24 bytes that start (16*cj + 4*J + t) bytes into the row: J = word offset inside the first chunk
-template <int J>
-__device__ __forceinline__ void tile_row_words(uint32_t addr, uint32_t t8, uint32_t (&w)[6]) {
-    uint32_t c[12];
-    const uint4 a = lds128(addr), b = lds128(addr + 16);
-    c[0] = a.x; c[1] = a.y; c[2] = a.z; c[3] = a.w; c[4] = b.x; c[5] = b.y; c[6] = b.z; c[7] = b.w;
-    if (J >= 2) {
-        const uint4 d = lds128(addr + 32);
-        c[8] = d.x; c[9] = d.y; c[10] = d.z; c[11] = d.w;
-    } else {
-        c[8] = c[9] = c[10] = c[11] = 0;
-    }
-    // J <= 1 needs c[J+6] <= c[7]; the funnel of the last word with shift 0 only reads its low operand
+// w[q][0..5] = the 24 bytes that start 4*J + t8/8 bytes into the 16-byte chunk at base + roff[q], for every row q of the
+// lane. Only this extraction depends on the alignment: it is the body of a warp-uniform 4-way switch, the SAD code
+// after it exists once (instruction-cache footprint: the first version unrolled everything four times and stalled
+// on instruction fetch, profiles/r01_v4_summary.md).
+template <int NR, int J>
+__device__ __forceinline__ void tile_rows_words(const uint32_t (&roff)[NR], uint32_t base, uint32_t t8, uint32_t (&w)[NR][6]) {
 #pragma unroll
-    for (int k = 0; k < 6; k++) w[k] = __funnelshift_r(c[J + k], c[J + k + 1], t8);
+    for (int q = 0; q < NR; q++) {
+        const uint32_t addr = base + roff[q];
+        uint32_t c[12];
+        const uint4 a = lds128(addr), b = lds128(addr + 16);
+        c[0] = a.x; c[1] = a.y; c[2] = a.z; c[3] = a.w; c[4] = b.x; c[5] = b.y; c[6] = b.z; c[7] = b.w;
+        if (J >= 2) {
+            const uint4 d = lds128(addr + 32);
+            c[8] = d.x; c[9] = d.y; c[10] = d.z; c[11] = d.w;
+        } else {
+            c[8] = c[9] = c[10] = c[11] = 0; // J <= 1 stops at c[J+6] <= c[7]
+        }
+#pragma unroll
+        for (int k = 0; k < 6; k++) w[q][k] = __funnelshift_r(c[J + k], c[J + k + 1], t8);
+    }
 }
 
 // one pass: the 8 positions whose first byte lies beta bytes into tile row `yy` (row_base = shared address of that row).
 // SPLIT: left / right 8 pixels of the strip kept apart (accl, accr), else summed into accl.
-template <int NS, int NR, bool SPLIT, int J>
-__device__ __forceinline__ void tile_pass_j(const TLane<NS, NR> &L, uint32_t row_base, uint32_t beta, uint32_t (&accl)[8], uint32_t (&accr)[8]) {
-    const uint32_t base = row_base + (beta & ~15u), t8 = (beta & 3u) * 8u;
+template <int NS, int NR, bool SPLIT>
+__device__ __forceinline__ void tile_pass(const TLane<NS, NR> &L, uint32_t row_base, uint32_t beta, uint32_t (&accl)[8], uint32_t (&accr)[8]) {
 #pragma unroll
-    for (int q = 0; q < NR; q++) {
-        uint32_t w[6];
-        tile_row_words<J>(base + L.roff[q], t8, w);
-        if (!L.full) {
+    for (int p = 0; p < 8; p++) accl[p] = accr[p] = 0;
+    const uint32_t base = row_base + (beta & ~15u), t8 = (beta & 3u) * 8u;
+    uint32_t w[NR][6];
+    switch ((beta & 15u) >> 2) { // warp-uniform
+    case 0: tile_rows_words<NR, 0>(L.roff, base, t8, w); break;
+    case 1: tile_rows_words<NR, 1>(L.roff, base, t8, w); break;
+    case 2: tile_rows_words<NR, 2>(L.roff, base, t8, w); break;
+    default: tile_rows_words<NR, 3>(L.roff, base, t8, w); break;
+    }
+    if (L.full) {
+#pragma unroll
+        for (int q = 0; q < NR; q++) {
+            if (SPLIT) strip16_sad8_split(w[q], L.src[q], accl, accr);
+            else strip16_sad8(w[q], L.src[q], accl);
+        }
+    } else {
+        // a strip cut by the block's right edge or a row below its bottom edge: mask what the source masks
+#pragma unroll 1
+        for (int q = 0; q < NR; q++) {
             const uint32_t rm = (L.rowok >> q) & 1u ? 0xffffffffu : 0u;
-            // a strip narrower than 16 pixels: positions read past it, mask what the source masks
-            uint32_t x[8][4];
+            uint32_t wq[6], sq[4];
+#pragma unroll
+            for (int qq = 0; qq < NR; qq++)
+                if (qq == q) {
+#pragma unroll
+                    for (int k = 0; k < 6; k++) wq[k] = w[qq][k];
+#pragma unroll
+                    for (int k = 0; k < 4; k++) sq[k] = L.src[qq][k];
+                }
 #pragma unroll
             for (int p = 0; p < 8; p++) {
                 const int o = p >> 2, sh = (p & 3) * 8;
 #pragma unroll
                 for (int k = 0; k < 4; k++) {
-                    const uint32_t v = sh ? __funnelshift_r(w[o + k], w[o + k + 1], sh) : w[o + k];
-                    x[p][k] = v & L.m[k] & rm;
+                    const uint32_t v = (sh ? __funnelshift_r(wq[o + k], wq[o + k + 1], sh) : wq[o + k]) & L.m[k] & rm;
+                    if (SPLIT && k >= 2) accr[p] = sad4_acc(v, sq[k], accr[p]);
+                    else accl[p] = sad4_acc(v, sq[k], accl[p]);
                 }
             }
-#pragma unroll
-            for (int p = 0; p < 8; p++)
-#pragma unroll
-                for (int k = 0; k < 4; k++) {
-                    if (SPLIT && k >= 2) accr[p] = sad4_acc(x[p][k], L.src[q][k], accr[p]);
-                    else accl[p] = sad4_acc(x[p][k], L.src[q][k], accl[p]);
-                }
-        } else if (SPLIT) {
-            strip16_sad8_split(w, L.src[q], accl, accr);
-        } else {
-            strip16_sad8(w, L.src[q], accl);
         }
-    }
-}
-
-template <int NS, int NR, bool SPLIT>
-__device__ __forceinline__ void tile_pass(const TLane<NS, NR> &L, uint32_t row_base, uint32_t beta, uint32_t (&accl)[8], uint32_t (&accr)[8]) {
-#pragma unroll
-    for (int p = 0; p < 8; p++) accl[p] = accr[p] = 0;
-    switch ((beta & 15u) >> 2) { // warp-uniform
-    case 0: tile_pass_j<NS, NR, SPLIT, 0>(L, row_base, beta, accl, accr); break;
-    case 1: tile_pass_j<NS, NR, SPLIT, 1>(L, row_base, beta, accl, accr); break;
-    case 2: tile_pass_j<NS, NR, SPLIT, 2>(L, row_base, beta, accl, accr); break;
-    default: tile_pass_j<NS, NR, SPLIT, 3>(L, row_base, beta, accl, accr); break;
     }
 }
 
