@@ -320,7 +320,18 @@ uint32_t svtme_picture_me_device(SvtMeSession *s, int32_t pic_id, const SvtMePic
 /* Copy the device result arrays of the last svtme_picture_me_device call into `results`. */
 uint32_t svtme_fetch_results(SvtMeSession *s, SvtMePicResults *results, int sync);
 
+/* Wait for everything queued on the session: host uploads, ME kernels, result downloads. */
 uint32_t svtme_session_sync(SvtMeSession *s);
+
+/* Pipelining across batches. The session runs host uploads, the ME kernels and the result downloads on three
+   streams: with sync = 0, svtme_picture_me_batch returns once the batch is queued, and the uploads of the next
+   pictures and the next batch's kernels overlap its downloads. svtme_session_batch_seq returns the sequence number
+   (1, 2, ...) of the batch queued last; svtme_session_wait_batch blocks until the results of batch `seq` are in the
+   host arrays it was given. At most two batches may be in flight per set of host arrays (the caller alternates two
+   sets and waits for batch seq - 2 before reusing a set). No reference counterpart: the reference's ME threads
+   synchronise through the picture-decision / ME FIFOs (me_process.c:75-330). */
+uint64_t svtme_session_batch_seq(SvtMeSession *s);
+uint32_t svtme_session_wait_batch(SvtMeSession *s, uint64_t seq);
 
 /* Read back a device plane (level 0 = full padded, 1 = quarter, 2 = sixteenth) into host memory,
    including padding; *stride / *rows receive the padded geometry. For parity tests. */

@@ -203,3 +203,11 @@ class PicResultArrays:
 
     def nbytes(self):
         return sum(getattr(self, f).nbytes for f in self.FIELDS)
+
+    def snapshot(self):
+        """plain copies of the arrays (the originals may be reused by a later batch)"""
+        import types
+        out = types.SimpleNamespace(FIELDS=self.FIELDS, n_b64=self.n_b64, n_pus=self.n_pus)
+        for f in self.FIELDS:
+            setattr(out, f, getattr(self, f).copy())
+        return out

@@ -51,6 +51,10 @@ def lib():
         L.svtme_fetch_results.restype = C.c_uint32
         L.svtme_session_sync.argtypes = [C.c_void_p]
         L.svtme_session_sync.restype = C.c_uint32
+        L.svtme_session_batch_seq.argtypes = [C.c_void_p]
+        L.svtme_session_batch_seq.restype = C.c_uint64
+        L.svtme_session_wait_batch.argtypes = [C.c_void_p, C.c_uint64]
+        L.svtme_session_wait_batch.restype = C.c_uint32
         L.svtme_picture_download_plane.argtypes = [C.c_void_p, C.c_int32, C.c_int, C.c_void_p, C.c_size_t,
                                                    C.POINTER(C.c_uint32), C.POINTER(C.c_uint32),
                                                    C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
@@ -190,6 +194,14 @@ class Session:
 
     def sync(self):
         _check(lib().svtme_session_sync(self._h), "svtme_session_sync")
+
+    def batch_seq(self):
+        """sequence number (1, 2, ...) of the batch queued last"""
+        return int(lib().svtme_session_batch_seq(self._h))
+
+    def wait_batch(self, seq):
+        """block until the results of batch `seq` are in the host arrays it was given"""
+        _check(lib().svtme_session_wait_batch(self._h, seq), "svtme_session_wait_batch")
 
     def download_plane(self, pic_id, level):
         pad = (72, 32, 16)[level]

@@ -41,8 +41,16 @@ struct SvtMeSession {
     size_t       pic_bytes = 0;
     std::vector<DevPic> pics;
     std::vector<char>   pic_valid;
-    std::vector<uint8_t *> res_slabs; // one result/scratch slab per picture of a batch
-    uint8_t     *res_slab = nullptr;  // == res_slabs[0]: also holds the counters shared by a batch
+    // Result slabs come in two sets used by alternate batches: the D2H copies of batch k (download stream) run
+    // while batch k+1 (compute stream) writes the other set. res_slab (set 0, slab 0) also holds the counters.
+    std::vector<uint8_t *> res_sets[2]; // one result/scratch slab per picture of a batch
+    uint8_t     *res_slab = nullptr;
+    cudaStream_t up_stream = nullptr, dl_stream = nullptr; // host uploads (H2D + pyramid) / result downloads (D2H)
+    cudaEvent_t  ev_up = nullptr, ev_sync = nullptr;
+    cudaEvent_t  ev_me[8] = {}, ev_dl[2] = {};
+    bool         up_pending = false, dev_upload_pending = false, dl_recorded[2] = {false, false};
+    uint64_t     batch_seq = 0; // sequence number of the last launched batch (1-based)
+    std::vector<uint64_t> slot_last_seq; // last batch that reads each picture slot
     PicJob      *d_jobs = nullptr;
     std::vector<PicJob> h_jobs;
     std::vector<SvtMePicParams> last_pps;
@@ -180,11 +188,18 @@ extern "C" uint32_t svtme_session_create(SvtMeSession **out, int device, uint32_
     e = cudaMalloc(&s->res_slab, s->lay.end);
     if (e != cudaSuccess) { cudaFree(s->pic_slab); delete s; return SVTME_ERR_INSUFFICIENT_RESOURCES; }
     cudaMemset(s->res_slab, 0, s->lay.end);
-    s->res_slabs.push_back(s->res_slab);
+    s->res_sets[0].push_back(s->res_slab);
+    s->slot_last_seq.assign(max_pictures, 0);
     e = cudaMalloc(&s->d_jobs, sizeof(PicJob));
     if (e != cudaSuccess) { cudaFree(s->pic_slab); cudaFree(s->res_slab); delete s; return SVTME_ERR_INSUFFICIENT_RESOURCES; }
     CU_TRY(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
     s->own_stream = true;
+    CU_TRY(cudaStreamCreateWithFlags(&s->up_stream, cudaStreamNonBlocking));
+    CU_TRY(cudaStreamCreateWithFlags(&s->dl_stream, cudaStreamNonBlocking));
+    CU_TRY(cudaEventCreateWithFlags(&s->ev_up, cudaEventDisableTiming));
+    CU_TRY(cudaEventCreateWithFlags(&s->ev_sync, cudaEventDisableTiming));
+    for (auto &e2 : s->ev_me) CU_TRY(cudaEventCreateWithFlags(&e2, cudaEventDisableTiming));
+    for (auto &e2 : s->ev_dl) CU_TRY(cudaEventCreateWithFlags(&e2, cudaEventDisableTiming));
     CU_TRY(cudaDeviceSynchronize());
     *out = s;
     return SVTME_OK;
@@ -193,12 +208,21 @@ extern "C" uint32_t svtme_session_create(SvtMeSession **out, int device, uint32_
 extern "C" void svtme_session_destroy(SvtMeSession *s) {
     if (!s) return;
     cudaSetDevice(s->device);
+    cudaStreamSynchronize(s->up_stream);
     cudaStreamSynchronize(s->stream);
+    cudaStreamSynchronize(s->dl_stream);
     for (auto &e : s->ev) cudaEventDestroy(e);
+    for (auto &e : s->ev_me) if (e) cudaEventDestroy(e);
+    for (auto &e : s->ev_dl) if (e) cudaEventDestroy(e);
+    if (s->ev_up) cudaEventDestroy(s->ev_up);
+    if (s->ev_sync) cudaEventDestroy(s->ev_sync);
+    if (s->up_stream) cudaStreamDestroy(s->up_stream);
+    if (s->dl_stream) cudaStreamDestroy(s->dl_stream);
     if (s->own_stream) cudaStreamDestroy(s->stream);
     cudaFree(s->pic_slab);
     if (s->d_tmaps) cudaFree(s->d_tmaps);
-    for (uint8_t *p : s->res_slabs) cudaFree(p);
+    for (auto &set : s->res_sets)
+        for (uint8_t *p : set) cudaFree(p);
     if (s->d_jobs) cudaFree(s->d_jobs);
     if (s->d_in16) cudaFree(s->d_in16);
     if (s->fp_units) cudaFree(s->fp_units);
@@ -212,7 +236,9 @@ extern "C" uint32_t svtme_session_set_stream(SvtMeSession *s, void *cuda_stream)
     if (!s) return SVTME_ERR_BAD_PARAMETER;
     std::lock_guard<std::mutex> g(s->mu);
     cudaSetDevice(s->device);
+    CU_TRY(cudaStreamSynchronize(s->up_stream));
     CU_TRY(cudaStreamSynchronize(s->stream));
+    CU_TRY(cudaStreamSynchronize(s->dl_stream));
     if (s->own_stream) cudaStreamDestroy(s->stream);
     s->stream     = (cudaStream_t)cuda_stream;
     s->own_stream = false;
@@ -221,16 +247,54 @@ extern "C" uint32_t svtme_session_set_stream(SvtMeSession *s, void *cuda_stream)
 
 extern "C" uint64_t svtme_session_launch_count(SvtMeSession *s) { return s ? s->launches : 0; }
 
-extern "C" uint32_t svtme_session_sync(SvtMeSession *s) {
-    if (!s) return SVTME_ERR_BAD_PARAMETER;
-    cudaSetDevice(s->device);
+static uint32_t sync_all(SvtMeSession *s) {
+    CU_TRY(cudaStreamSynchronize(s->up_stream));
     CU_TRY(cudaStreamSynchronize(s->stream));
+    CU_TRY(cudaStreamSynchronize(s->dl_stream));
     return SVTME_OK;
 }
 
-static uint32_t finish_upload(SvtMeSession *s, int32_t pic_id, int mode, const void *d_in, int in_stride) {
-    s->launches += (uint64_t)svtme_launch_build_pyramid(s->pics[pic_id], mode, d_in, in_stride, s->stream);
+extern "C" uint32_t svtme_session_sync(SvtMeSession *s) {
+    if (!s) return SVTME_ERR_BAD_PARAMETER;
+    cudaSetDevice(s->device);
+    return sync_all(s);
+}
+
+extern "C" uint64_t svtme_session_batch_seq(SvtMeSession *s) { return s ? s->batch_seq : 0; }
+
+extern "C" uint32_t svtme_session_wait_batch(SvtMeSession *s, uint64_t seq) {
+    if (!s) return SVTME_ERR_BAD_PARAMETER;
+    if (seq == 0 || seq > s->batch_seq) return SVTME_OK;
+    cudaSetDevice(s->device);
+    // results of batch `seq` were copied by the download recorded in ev_dl[seq & 1] (or by a later one of the same set)
+    if (s->dl_recorded[seq & 1]) CU_TRY(cudaEventSynchronize(s->ev_dl[seq & 1]));
+    else CU_TRY(cudaEventSynchronize(s->ev_me[seq % 8]));
+    return SVTME_OK;
+}
+
+// Host uploads run on the upload stream so that they overlap the ME of earlier pictures; device uploads stay on the
+// compute stream (their input is ordered by it). A slot is not overwritten before the last batch that reads it is done.
+static uint32_t begin_host_upload(SvtMeSession *s, int32_t pic_id) {
+    if (s->slot_last_seq[pic_id]) CU_TRY(cudaStreamWaitEvent(s->up_stream, s->ev_me[s->slot_last_seq[pic_id] % 8], 0));
+    if (s->dev_upload_pending) {
+        CU_TRY(cudaEventRecord(s->ev_sync, s->stream));
+        CU_TRY(cudaStreamWaitEvent(s->up_stream, s->ev_sync, 0));
+        s->dev_upload_pending = false;
+    }
+    return SVTME_OK;
+}
+
+static uint32_t finish_upload(SvtMeSession *s, int32_t pic_id, int mode, const void *d_in, int in_stride, bool host) {
+    cudaStream_t st = host ? s->up_stream : s->stream;
+    if (!host && s->up_pending) CU_TRY(cudaStreamWaitEvent(s->stream, s->ev_up, 0));
+    s->launches += (uint64_t)svtme_launch_build_pyramid(s->pics[pic_id], mode, d_in, in_stride, st);
     CU_TRY(cudaGetLastError());
+    if (host) {
+        CU_TRY(cudaEventRecord(s->ev_up, s->up_stream));
+        s->up_pending = true;
+    } else {
+        s->dev_upload_pending = true;
+    }
     s->pic_valid[pic_id] = 1;
     return SVTME_OK;
 }
@@ -241,15 +305,17 @@ extern "C" uint32_t svtme_picture_upload(SvtMeSession *s, int32_t pic_id, const 
     CU_TRY(cudaSetDevice(s->device));
     const DevPlane &f = s->pics[pic_id].lvl[0];
     uint8_t *interior = const_cast<uint8_t *>(f.buf) + (size_t)f.org_y * f.stride + f.org_x;
-    CU_TRY(cudaMemcpy2DAsync(interior, (size_t)f.stride, luma, stride, (size_t)s->w, (size_t)s->h, cudaMemcpyHostToDevice, s->stream));
-    return finish_upload(s, pic_id, 1, nullptr, 0);
+    uint32_t rc = begin_host_upload(s, pic_id);
+    if (rc != SVTME_OK) return rc;
+    CU_TRY(cudaMemcpy2DAsync(interior, (size_t)f.stride, luma, stride, (size_t)s->w, (size_t)s->h, cudaMemcpyHostToDevice, s->up_stream));
+    return finish_upload(s, pic_id, 1, nullptr, 0, true);
 }
 
 extern "C" uint32_t svtme_picture_upload_device(SvtMeSession *s, int32_t pic_id, const uint8_t *d_luma, uint32_t stride) {
     if (!s || !d_luma || pic_id < 0 || pic_id >= s->max_pics || stride < (uint32_t)s->w) return SVTME_ERR_BAD_PARAMETER;
     std::lock_guard<std::mutex> g(s->mu);
     CU_TRY(cudaSetDevice(s->device));
-    return finish_upload(s, pic_id, 0, d_luma, (int)stride);
+    return finish_upload(s, pic_id, 0, d_luma, (int)stride, false);
 }
 
 extern "C" uint32_t svtme_picture_upload_10bit(SvtMeSession *s, int32_t pic_id, const uint16_t *luma16, uint32_t stride_in_samples) {
@@ -260,9 +326,11 @@ extern "C" uint32_t svtme_picture_upload_10bit(SvtMeSession *s, int32_t pic_id, 
         cudaError_t e = cudaMalloc(&s->d_in16, (size_t)s->w * s->h * 2);
         if (e != cudaSuccess) return SVTME_ERR_INSUFFICIENT_RESOURCES;
     }
+    uint32_t rc = begin_host_upload(s, pic_id);
+    if (rc != SVTME_OK) return rc;
     CU_TRY(cudaMemcpy2DAsync(s->d_in16, (size_t)s->w * 2, luma16, (size_t)stride_in_samples * 2, (size_t)s->w * 2, (size_t)s->h,
-                             cudaMemcpyHostToDevice, s->stream));
-    return finish_upload(s, pic_id, 2, s->d_in16, s->w);
+                             cudaMemcpyHostToDevice, s->up_stream));
+    return finish_upload(s, pic_id, 2, s->d_in16, s->w, true);
 }
 
 extern "C" uint32_t svtme_picture_download_plane(SvtMeSession *s, int32_t pic_id, int level, uint8_t *dst, size_t dst_capacity,
@@ -276,6 +344,7 @@ extern "C" uint32_t svtme_picture_download_plane(SvtMeSession *s, int32_t pic_id
     const int ep = export_pad[level], skip = p.org_x - ep;
     const size_t W = (size_t)p.width + 2 * ep, H = (size_t)p.height + 2 * ep;
     if (dst_capacity < W * H || skip < 0) return SVTME_ERR_BAD_PARAMETER;
+    CU_TRY(cudaStreamSynchronize(s->up_stream));
     CU_TRY(cudaMemcpy2DAsync(dst, W, p.buf + (size_t)skip * p.stride + skip, (size_t)p.stride, W, H, cudaMemcpyDeviceToHost, s->stream));
     CU_TRY(cudaStreamSynchronize(s->stream));
     if (stride) *stride = (uint32_t)W;
@@ -324,15 +393,17 @@ static void fold_events(SvtMeSession *s) {
 }
 
 static uint32_t ensure_batch(SvtMeSession *s, uint32_t n) {
-    if (n <= s->res_slabs.size()) return SVTME_OK;
-    CU_TRY(cudaStreamSynchronize(s->stream));
-    while (s->res_slabs.size() < n) {
-        uint8_t *p = nullptr;
-        cudaError_t e = cudaMalloc(&p, s->lay.end);
-        if (e != cudaSuccess) { fprintf(stderr, "[svtme_b200] cudaMalloc result slab: %s\n", cudaGetErrorString(e)); return SVTME_ERR_INSUFFICIENT_RESOURCES; }
-        cudaMemset(p, 0, s->lay.end);
-        s->res_slabs.push_back(p);
-    }
+    if (n <= s->res_sets[0].size() && n <= s->res_sets[1].size()) return SVTME_OK;
+    uint32_t rc = sync_all(s);
+    if (rc != SVTME_OK) return rc;
+    for (auto &set : s->res_sets)
+        while (set.size() < n) {
+            uint8_t *p = nullptr;
+            cudaError_t e = cudaMalloc(&p, s->lay.end);
+            if (e != cudaSuccess) { fprintf(stderr, "[svtme_b200] cudaMalloc result slab: %s\n", cudaGetErrorString(e)); return SVTME_ERR_INSUFFICIENT_RESOURCES; }
+            cudaMemset(p, 0, s->lay.end);
+            set.push_back(p);
+        }
     if (s->d_jobs) cudaFree(s->d_jobs);
     s->d_jobs = nullptr;
     cudaError_t e = cudaMalloc(&s->d_jobs, sizeof(PicJob) * n);
@@ -379,6 +450,13 @@ static uint32_t launch_me_batch(SvtMeSession *s, uint32_t n, const int32_t *pic_
         if (e != cudaSuccess) { fprintf(stderr, "[svtme_b200] cudaMalloc HME unit queue (%llu units): %s\n", (unsigned long long)need_s16, cudaGetErrorString(e)); return SVTME_ERR_INSUFFICIENT_RESOURCES; }
         s->s16_units_cap = (uint32_t)need_s16;
     }
+    const uint64_t seq = ++s->batch_seq;
+    const int set = (int)(seq & 1);
+    if (s->up_pending) { // pictures uploaded from the host since the last batch
+        CU_TRY(cudaStreamWaitEvent(s->stream, s->ev_up, 0));
+        s->up_pending = false;
+    }
+    if (s->dl_recorded[set]) CU_TRY(cudaStreamWaitEvent(s->stream, s->ev_dl[set], 0)); // the set's previous results left for the host
     s->h_jobs.resize(n);
     for (uint32_t i = 0; i < n; i++) {
         const SvtMePicParams *pp = &params[i];
@@ -386,11 +464,15 @@ static uint32_t launch_me_batch(SvtMeSession *s, uint32_t n, const int32_t *pic_
         memset(&job, 0, sizeof(job));
         job.pp  = *pp;
         job.src = s->pics[pic_ids[i]];
+        s->slot_last_seq[pic_ids[i]] = seq;
         for (int l = 0; l < pp->num_of_list_to_search; l++)
-            for (int r = 0; r < pp->num_of_ref_pic_to_search[l]; r++) job.ref[l][r] = s->pics[pp->ref_pic_id[l][r]];
+            for (int r = 0; r < pp->num_of_ref_pic_to_search[l]; r++) {
+                job.ref[l][r] = s->pics[pp->ref_pic_id[l][r]];
+                s->slot_last_seq[pp->ref_pic_id[l][r]] = seq;
+            }
         job.pic_w = s->w; job.pic_h = s->h; job.b64_cols = s->b64_cols; job.b64_rows = s->b64_rows; job.n_b64 = s->n_b64;
         job.n_pus = pp->enable_me_8x8 ? 85 : 21;
-        uint8_t *R = s->res_slabs[i];
+        uint8_t *R = s->res_sets[set][i];
         job.sb_state       = (SbState *)(R + s->lay.sb_state);
         job.best_sad       = (uint32_t *)(R + s->lay.best_sad);
         job.best_mv        = (uint32_t *)(R + s->lay.best_mv);
@@ -439,6 +521,7 @@ static uint32_t launch_me_batch(SvtMeSession *s, uint32_t n, const int32_t *pic_
     }
     s->launches += (uint64_t)svtme_launch_picture_me(s->h_jobs.data(), (int)n, s->d_jobs, s->stream, e0, e1, e2);
     CU_TRY(cudaGetLastError());
+    CU_TRY(cudaEventRecord(s->ev_me[seq % 8], s->stream));
     s->last_pps.assign(params, params + n);
     s->have_results = true;
     return SVTME_OK;
@@ -448,9 +531,11 @@ static uint32_t fetch(SvtMeSession *s, uint32_t index, SvtMePicResults *res, int
     if (!s->have_results || !res || index >= s->last_pps.size()) return SVTME_ERR_BAD_PARAMETER;
     const SvtMePicParams &pp = s->last_pps[index];
     const size_t n = (size_t)s->n_b64, n_pus = pp.enable_me_8x8 ? 85 : 21;
-    uint8_t *R = s->res_slabs[index];
+    const int set = (int)(s->batch_seq & 1);
+    uint8_t *R = s->res_sets[set][index];
+    CU_TRY(cudaStreamWaitEvent(s->dl_stream, s->ev_me[s->batch_seq % 8], 0));
 #define D2H(dst, off, bytes)                                                                               \
-    if (res->dst) CU_TRY(cudaMemcpyAsync(res->dst, R + s->lay.off, (bytes), cudaMemcpyDeviceToHost, s->stream))
+    if (res->dst) CU_TRY(cudaMemcpyAsync(res->dst, R + s->lay.off, (bytes), cudaMemcpyDeviceToHost, s->dl_stream))
     D2H(p_sb_best_sad, best_sad, n * 8 * 85 * 4);
     D2H(p_sb_best_mv, best_mv, n * 8 * 85 * 4);
     D2H(search_results, search_results, n * 8 * sizeof(SvtMeSearchResult));
@@ -467,7 +552,9 @@ static uint32_t fetch(SvtMeSession *s, uint32_t index, SvtMePicResults *res, int
     D2H(stationary_block_present_sb, stat, n);
     D2H(rc_me_allow_gm, gm, n);
 #undef D2H
-    if (sync) CU_TRY(cudaStreamSynchronize(s->stream));
+    CU_TRY(cudaEventRecord(s->ev_dl[set], s->dl_stream));
+    s->dl_recorded[set] = true;
+    if (sync) CU_TRY(cudaStreamSynchronize(s->dl_stream));
     return SVTME_OK;
 }
 
@@ -482,7 +569,7 @@ extern "C" uint32_t svtme_picture_me_batch(SvtMeSession *s, uint32_t n, const in
             rc = fetch(s, i, &results[i], 0);
             if (rc != SVTME_OK) return rc;
         }
-    if (sync) CU_TRY(cudaStreamSynchronize(s->stream));
+    if (sync) CU_TRY(cudaStreamSynchronize(results ? s->dl_stream : s->stream)); // the download waits for the batch's kernels
     return SVTME_OK;
 }
 
@@ -541,7 +628,7 @@ extern "C" uint32_t svtme_fetch_hme_state(SvtMeSession *s, void *dst, size_t dst
     if (!s || !dst || dst_bytes < (size_t)s->n_b64 * sizeof(SbState)) return SVTME_ERR_BAD_PARAMETER;
     std::lock_guard<std::mutex> g(s->mu);
     CU_TRY(cudaSetDevice(s->device));
-    CU_TRY(cudaMemcpyAsync(dst, s->res_slab + s->lay.sb_state, (size_t)s->n_b64 * sizeof(SbState), cudaMemcpyDeviceToHost, s->stream));
+    CU_TRY(cudaMemcpyAsync(dst, s->res_sets[s->batch_seq & 1][0] + s->lay.sb_state, (size_t)s->n_b64 * sizeof(SbState), cudaMemcpyDeviceToHost, s->stream));
     CU_TRY(cudaStreamSynchronize(s->stream));
     return SVTME_OK;
 }

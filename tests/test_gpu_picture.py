@@ -125,3 +125,57 @@ def test_batch_equals_single_picture_calls():
     for a, b in zip(singles, batch):
         compare(a, b, fields=list(a.FIELDS))
     s.close()
+
+
+def test_pipelined_batches_equal_synchronous_ones():
+    """batches queued back to back (sync=0, uploads of later pictures in between, two sets of host arrays) give what
+    the same batches give one at a time; a slot re-uploaded while an earlier batch may still read it is ordered"""
+    from svt_av1_psy_b200 import abi
+    from svt_av1_psy_b200.synth import PanningNoise
+    w, h = 320, 192
+    clip = PanningNoise(w, h, seed=33, vx=3, vy=1, max_frames=64)
+    n_slots = 24
+
+    def plan(poc):
+        return [p for p in (poc - 1, poc - 2) if p >= 0], [p for p in (poc + 1,) if p < 40]
+
+    def run(pipelined):
+        s = me.Session(w, h, max_pictures=n_slots)
+        out, sets, seqs = [], [None, None], [0, 0]
+        for t in range(10):
+            s.upload(t % n_slots, clip.frame(t))
+        for k in range(6):  # batch k: pictures 4k+1 .. 4k+4; picture 4k+5 (list 1 of the last one) is uploaded first
+            for t in range(10 + 4 * k, 10 + 4 * (k + 1)):
+                s.upload(t % n_slots, clip.frame(t))  # wraps onto slots that earlier batches read
+            ids, prms = [], []
+            for poc in range(4 * k + 1, 4 * k + 5):
+                l0, l1 = plan(poc)
+                refs = [[clip.frame(p) for p in l0], [clip.frame(p) for p in l1]]
+                p = params_from_encoder_inputs(clip.frame(poc), refs, [l0, l1], poc, 6, temporal_layer=2, hier_levels=5)
+                for l, lst in enumerate((l0, l1)):
+                    for r, rp in enumerate(lst):
+                        p.ref_pic_id[l][r] = rp % n_slots
+                ids.append(poc % n_slots)
+                prms.append(p)
+            if not pipelined:
+                out.append(s.me_batch(ids, prms, [abi.PicResultArrays(w, h, p) for p in prms], sync=True))
+                continue
+            j = k & 1
+            if sets[j] is not None:
+                s.wait_batch(seqs[j])
+                out.append([r.snapshot() for r in sets[j]])
+            sets[j] = [abi.PicResultArrays(w, h, p, pinned=True) for p in prms]
+            s.me_batch(ids, prms, sets[j], sync=False)
+            seqs[j] = s.batch_seq()
+        if pipelined:
+            s.sync()
+            tail = sorted(((seqs[j], [r.snapshot() for r in sets[j]]) for j in range(2)), key=lambda t: t[0])
+            out += [t[1] for t in tail]
+        s.close()
+        return out
+
+    a, b = run(False), run(True)
+    assert len(a) == len(b) == 6
+    for ba, bb in zip(a, b):
+        for ra, rb in zip(ba, bb):
+            compare(ra, rb, fields=list(ra.FIELDS))
