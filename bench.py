@@ -38,6 +38,7 @@ def parse_args():
     ap.add_argument("--preset", type=int, default=4)
     ap.add_argument("--bits", type=int, default=8, choices=[8, 10])
     ap.add_argument("--frames", type=int, default=240, help="length of the synthetic clip")
+    ap.add_argument("--e2e-probe", default="full", choices=["full", "h2d", "d2h"], help="diagnostic: drop one direction of the end-to-end copies")
     ap.add_argument("--qp", type=int, default=35)
     ap.add_argument("--cpu-baseline-pics", type=int, default=0, help="0 = one picture per host core")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -157,6 +158,7 @@ class Runner:
         self.h2d = self.d2h = 0
         self.pics = 0
         self.host_batches = 0
+        self.probe = "full"
 
     def params(self, plan):
         key = plan["poc"]
@@ -185,7 +187,9 @@ class Runner:
         if self.resident.get(slot) == poc:
             return
         f = poc % self.wl.n_frames
-        if host and self.frames16 is not None:
+        if host and self.probe == "d2h":
+            self.sess.upload_device(slot, self.frames_dev[f].data_ptr(), self.wl.w)
+        elif host and self.frames16 is not None:
             self.sess.upload_ptr16(slot, self.frames16[f].data_ptr(), self.wl.w)
             self.h2d += 2 * self.wl.w * self.wl.h
         elif host:
@@ -228,6 +232,10 @@ class Runner:
                                        if f not in ("p_sb_best_sad", "p_sb_best_mv", "search_results", "me_windows"))
                 self.seqs = [0, 0]
             k = self.host_batches & 1
+            if self.probe == "h2d":
+                self.sess.me_batch(ids, prms, None, sync=False)
+                self.pics += len(ids)
+                return
             self.sess.wait_batch(self.seqs[k])  # this set's previous results are in host memory (and consumed) before reuse
             self.sess.me_batch(ids, prms, self.results[k][:len(ids)], sync=False)
             self.seqs[k] = self.sess.batch_seq()
@@ -257,6 +265,7 @@ def run_ours(a):
     wl = Workload(a)
     frames = make_clip(wl, rank)
     run = Runner(wl, rank, world, frames, local)
+    run.probe = a.e2e_probe
 
     def barrier():
         torch.cuda.synchronize()
@@ -272,6 +281,7 @@ def run_ours(a):
         e0.record()
         for s in range(first_step, first_step + n_steps):
             run.step(s, host)
+        run.host_ms = (time.time() - t0) * 1e3 / n_steps  # host time to queue one step (no waiting unless the pipeline is full)
         if host:
             run.sess.sync()  # uploads, kernels and downloads of every step: results are in host memory
         e1.record()
@@ -294,6 +304,7 @@ def run_ours(a):
     run.sess.kernel_time(reset=True)
     run.sess.sad_ops(reset=True)
     ms, pics, launches = timed(False, a.warmup, a.steps, sampler)
+    host_ms_resident = run.host_ms
     fp_ms, hme_ms, n_timed = run.sess.kernel_time(reset=True)
     hme_ops, fp_ops = run.sess.sad_ops(reset=True)
     n_timed = pics  # events bracket one batch; report per picture
@@ -307,6 +318,7 @@ def run_ours(a):
         run.step(s, host=True)
     base += min(a.warmup, 2)
     ms_e, pics_e, _ = timed(True, base, a.steps, sampler)
+    host_ms_e2e = run.host_ms
     clocks = sampler.stop()
     h2d_step, d2h_step = run.h2d // max(1, a.steps), run.d2h // max(1, a.steps)
     e2e = world * pics_e / (ms_e * 1e-3)
@@ -338,7 +350,8 @@ def run_ours(a):
                        "l2": "inputs larger than L2: %d distinct %dx%d frames (%.0f MB) stream through the picture store, no explicit flush"
                              % (wl.n_frames, wl.w, wl.h, wl.n_frames * wl.w * wl.h / 1e6)},
             "e2e": {"value": round(e2e, 2), "unit": "frames/s", "h2d_bytes_per_step": int(h2d_step), "d2h_bytes_per_step": int(d2h_step),
-                    "ms_per_step": round(ms_e / a.steps, 4)},
+                    "ms_per_step": round(ms_e / a.steps, 4), "host_queue_ms_per_step": round(host_ms_e2e, 3)},
+            "host_queue_ms_per_step": round(host_ms_resident, 3),
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": {"bound": "hbm", "kernel": dominant, "achieved": round(alg_bytes / avg_s / 1e9, 2), "peak": hbm_peak,

@@ -46,16 +46,18 @@ struct SvtMeSession {
     std::vector<uint8_t *> res_sets[2]; // one result/scratch slab per picture of a batch
     uint8_t     *res_slab = nullptr;
     cudaStream_t up_stream = nullptr, dl_stream = nullptr; // host uploads (H2D + pyramid) / result downloads (D2H)
-    cudaEvent_t  ev_up = nullptr, ev_sync = nullptr;
     cudaEvent_t  ev_me[8] = {}, ev_dl[2] = {};
-    bool         up_pending = false, dev_upload_pending = false, dl_recorded[2] = {false, false};
+    bool         dl_recorded[2] = {false, false};
     uint64_t     batch_seq = 0; // sequence number of the last launched batch (1-based)
-    std::vector<uint64_t> slot_last_seq; // last batch that reads each picture slot
     PicJob      *d_jobs = nullptr;
     std::vector<PicJob> h_jobs;
     std::vector<SvtMePicParams> last_pps;
     ResultLayout lay{};
-    uint16_t    *d_in16 = nullptr;
+    uint8_t     *stage_slab = nullptr; // ring of staging frames for host uploads
+    cudaEvent_t  ev_copied[40] = {}, ev_ingested[40] = {};
+    bool         stage_used[40] = {};
+    uint64_t     stage_head = 0;
+    int          stage_last = 0;
     uint2       *fp_units = nullptr, *s16_units = nullptr;
     uint32_t     fp_units_cap = 0, s16_units_cap = 0;
     SvtMePicParams last_pp{};
@@ -189,15 +191,12 @@ extern "C" uint32_t svtme_session_create(SvtMeSession **out, int device, uint32_
     if (e != cudaSuccess) { cudaFree(s->pic_slab); delete s; return SVTME_ERR_INSUFFICIENT_RESOURCES; }
     cudaMemset(s->res_slab, 0, s->lay.end);
     s->res_sets[0].push_back(s->res_slab);
-    s->slot_last_seq.assign(max_pictures, 0);
     e = cudaMalloc(&s->d_jobs, sizeof(PicJob));
     if (e != cudaSuccess) { cudaFree(s->pic_slab); cudaFree(s->res_slab); delete s; return SVTME_ERR_INSUFFICIENT_RESOURCES; }
     CU_TRY(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
     s->own_stream = true;
     CU_TRY(cudaStreamCreateWithFlags(&s->up_stream, cudaStreamNonBlocking));
     CU_TRY(cudaStreamCreateWithFlags(&s->dl_stream, cudaStreamNonBlocking));
-    CU_TRY(cudaEventCreateWithFlags(&s->ev_up, cudaEventDisableTiming));
-    CU_TRY(cudaEventCreateWithFlags(&s->ev_sync, cudaEventDisableTiming));
     for (auto &e2 : s->ev_me) CU_TRY(cudaEventCreateWithFlags(&e2, cudaEventDisableTiming));
     for (auto &e2 : s->ev_dl) CU_TRY(cudaEventCreateWithFlags(&e2, cudaEventDisableTiming));
     CU_TRY(cudaDeviceSynchronize());
@@ -214,8 +213,6 @@ extern "C" void svtme_session_destroy(SvtMeSession *s) {
     for (auto &e : s->ev) cudaEventDestroy(e);
     for (auto &e : s->ev_me) if (e) cudaEventDestroy(e);
     for (auto &e : s->ev_dl) if (e) cudaEventDestroy(e);
-    if (s->ev_up) cudaEventDestroy(s->ev_up);
-    if (s->ev_sync) cudaEventDestroy(s->ev_sync);
     if (s->up_stream) cudaStreamDestroy(s->up_stream);
     if (s->dl_stream) cudaStreamDestroy(s->dl_stream);
     if (s->own_stream) cudaStreamDestroy(s->stream);
@@ -224,7 +221,9 @@ extern "C" void svtme_session_destroy(SvtMeSession *s) {
     for (auto &set : s->res_sets)
         for (uint8_t *p : set) cudaFree(p);
     if (s->d_jobs) cudaFree(s->d_jobs);
-    if (s->d_in16) cudaFree(s->d_in16);
+    if (s->stage_slab) cudaFree(s->stage_slab);
+    for (auto &e : s->ev_copied) if (e) cudaEventDestroy(e);
+    for (auto &e : s->ev_ingested) if (e) cudaEventDestroy(e);
     if (s->fp_units) cudaFree(s->fp_units);
     if (s->s16_units) cudaFree(s->s16_units);
     delete s;
@@ -272,29 +271,41 @@ extern "C" uint32_t svtme_session_wait_batch(SvtMeSession *s, uint64_t seq) {
     return SVTME_OK;
 }
 
-// Host uploads run on the upload stream so that they overlap the ME of earlier pictures; device uploads stay on the
-// compute stream (their input is ordered by it). A slot is not overwritten before the last batch that reads it is done.
-static uint32_t begin_host_upload(SvtMeSession *s, int32_t pic_id) {
-    if (s->slot_last_seq[pic_id]) CU_TRY(cudaStreamWaitEvent(s->up_stream, s->ev_me[s->slot_last_seq[pic_id] % 8], 0));
-    if (s->dev_upload_pending) {
-        CU_TRY(cudaEventRecord(s->ev_sync, s->stream));
-        CU_TRY(cudaStreamWaitEvent(s->up_stream, s->ev_sync, 0));
-        s->dev_upload_pending = false;
+// Host uploads: the frame crosses PCIe as ONE linear copy into a ring of staging frames on the upload stream (pure
+// copy-engine work, runs ahead of the kernels); the pyramid build reads the staging frame on the COMPUTE stream, so
+// picture planes are only ever written in compute-stream order (no hazard with the ME kernels of earlier batches).
+// Measured: building the pyramid on the upload stream gated every copy behind a kernel waiting for an SM slot next
+// to the persistent search kernels, and a pitched 2-D copy into the padded plane reaches ~11 GB/s.
+#define SVTME_STAGE_FRAMES 40
+static uint32_t stage_host_frame(SvtMeSession *s, const void *host, size_t row_bytes, size_t host_pitch, void **staged) {
+    const size_t frame_bytes = (size_t)s->w * s->h * 2; // fits 8-bit and 16-bit input
+    if (!s->stage_slab) {
+        cudaError_t e = cudaMalloc(&s->stage_slab, frame_bytes * SVTME_STAGE_FRAMES);
+        if (e != cudaSuccess) { fprintf(stderr, "[svtme_b200] cudaMalloc staging ring: %s\n", cudaGetErrorString(e)); return SVTME_ERR_INSUFFICIENT_RESOURCES; }
+        for (int i = 0; i < SVTME_STAGE_FRAMES; i++) {
+            CU_TRY(cudaEventCreateWithFlags(&s->ev_copied[i], cudaEventDisableTiming));
+            CU_TRY(cudaEventCreateWithFlags(&s->ev_ingested[i], cudaEventDisableTiming));
+        }
     }
+    const int j = (int)(s->stage_head++ % SVTME_STAGE_FRAMES);
+    uint8_t *dst = s->stage_slab + frame_bytes * j;
+    if (s->stage_used[j]) CU_TRY(cudaStreamWaitEvent(s->up_stream, s->ev_ingested[j], 0)); // its previous frame was consumed
+    if (host_pitch == row_bytes)
+        CU_TRY(cudaMemcpyAsync(dst, host, row_bytes * s->h, cudaMemcpyHostToDevice, s->up_stream));
+    else
+        CU_TRY(cudaMemcpy2DAsync(dst, row_bytes, host, host_pitch, row_bytes, (size_t)s->h, cudaMemcpyHostToDevice, s->up_stream));
+    CU_TRY(cudaEventRecord(s->ev_copied[j], s->up_stream));
+    CU_TRY(cudaStreamWaitEvent(s->stream, s->ev_copied[j], 0));
+    s->stage_used[j] = true;
+    s->stage_last = j;
+    *staged = dst;
     return SVTME_OK;
 }
 
-static uint32_t finish_upload(SvtMeSession *s, int32_t pic_id, int mode, const void *d_in, int in_stride, bool host) {
-    cudaStream_t st = host ? s->up_stream : s->stream;
-    if (!host && s->up_pending) CU_TRY(cudaStreamWaitEvent(s->stream, s->ev_up, 0));
-    s->launches += (uint64_t)svtme_launch_build_pyramid(s->pics[pic_id], mode, d_in, in_stride, st);
+static uint32_t finish_upload(SvtMeSession *s, int32_t pic_id, int mode, const void *d_in, int in_stride, bool staged) {
+    s->launches += (uint64_t)svtme_launch_build_pyramid(s->pics[pic_id], mode, d_in, in_stride, s->stream);
     CU_TRY(cudaGetLastError());
-    if (host) {
-        CU_TRY(cudaEventRecord(s->ev_up, s->up_stream));
-        s->up_pending = true;
-    } else {
-        s->dev_upload_pending = true;
-    }
+    if (staged) CU_TRY(cudaEventRecord(s->ev_ingested[s->stage_last], s->stream));
     s->pic_valid[pic_id] = 1;
     return SVTME_OK;
 }
@@ -303,12 +314,10 @@ extern "C" uint32_t svtme_picture_upload(SvtMeSession *s, int32_t pic_id, const 
     if (!s || !luma || pic_id < 0 || pic_id >= s->max_pics || stride < (uint32_t)s->w) return SVTME_ERR_BAD_PARAMETER;
     std::lock_guard<std::mutex> g(s->mu);
     CU_TRY(cudaSetDevice(s->device));
-    const DevPlane &f = s->pics[pic_id].lvl[0];
-    uint8_t *interior = const_cast<uint8_t *>(f.buf) + (size_t)f.org_y * f.stride + f.org_x;
-    uint32_t rc = begin_host_upload(s, pic_id);
+    void *staged = nullptr;
+    uint32_t rc = stage_host_frame(s, luma, (size_t)s->w, stride, &staged);
     if (rc != SVTME_OK) return rc;
-    CU_TRY(cudaMemcpy2DAsync(interior, (size_t)f.stride, luma, stride, (size_t)s->w, (size_t)s->h, cudaMemcpyHostToDevice, s->up_stream));
-    return finish_upload(s, pic_id, 1, nullptr, 0, true);
+    return finish_upload(s, pic_id, 0, staged, s->w, true);
 }
 
 extern "C" uint32_t svtme_picture_upload_device(SvtMeSession *s, int32_t pic_id, const uint8_t *d_luma, uint32_t stride) {
@@ -322,15 +331,10 @@ extern "C" uint32_t svtme_picture_upload_10bit(SvtMeSession *s, int32_t pic_id, 
     if (!s || !luma16 || pic_id < 0 || pic_id >= s->max_pics || stride_in_samples < (uint32_t)s->w) return SVTME_ERR_BAD_PARAMETER;
     std::lock_guard<std::mutex> g(s->mu);
     CU_TRY(cudaSetDevice(s->device));
-    if (!s->d_in16) {
-        cudaError_t e = cudaMalloc(&s->d_in16, (size_t)s->w * s->h * 2);
-        if (e != cudaSuccess) return SVTME_ERR_INSUFFICIENT_RESOURCES;
-    }
-    uint32_t rc = begin_host_upload(s, pic_id);
+    void *staged = nullptr;
+    uint32_t rc = stage_host_frame(s, luma16, (size_t)s->w * 2, (size_t)stride_in_samples * 2, &staged);
     if (rc != SVTME_OK) return rc;
-    CU_TRY(cudaMemcpy2DAsync(s->d_in16, (size_t)s->w * 2, luma16, (size_t)stride_in_samples * 2, (size_t)s->w * 2, (size_t)s->h,
-                             cudaMemcpyHostToDevice, s->up_stream));
-    return finish_upload(s, pic_id, 2, s->d_in16, s->w, true);
+    return finish_upload(s, pic_id, 2, staged, s->w, true);
 }
 
 extern "C" uint32_t svtme_picture_download_plane(SvtMeSession *s, int32_t pic_id, int level, uint8_t *dst, size_t dst_capacity,
@@ -452,10 +456,6 @@ static uint32_t launch_me_batch(SvtMeSession *s, uint32_t n, const int32_t *pic_
     }
     const uint64_t seq = ++s->batch_seq;
     const int set = (int)(seq & 1);
-    if (s->up_pending) { // pictures uploaded from the host since the last batch
-        CU_TRY(cudaStreamWaitEvent(s->stream, s->ev_up, 0));
-        s->up_pending = false;
-    }
     if (s->dl_recorded[set]) CU_TRY(cudaStreamWaitEvent(s->stream, s->ev_dl[set], 0)); // the set's previous results left for the host
     s->h_jobs.resize(n);
     for (uint32_t i = 0; i < n; i++) {
@@ -464,11 +464,9 @@ static uint32_t launch_me_batch(SvtMeSession *s, uint32_t n, const int32_t *pic_
         memset(&job, 0, sizeof(job));
         job.pp  = *pp;
         job.src = s->pics[pic_ids[i]];
-        s->slot_last_seq[pic_ids[i]] = seq;
         for (int l = 0; l < pp->num_of_list_to_search; l++)
             for (int r = 0; r < pp->num_of_ref_pic_to_search[l]; r++) {
                 job.ref[l][r] = s->pics[pp->ref_pic_id[l][r]];
-                s->slot_last_seq[pp->ref_pic_id[l][r]] = seq;
             }
         job.pic_w = s->w; job.pic_h = s->h; job.b64_cols = s->b64_cols; job.b64_rows = s->b64_rows; job.n_b64 = s->n_b64;
         job.n_pus = pp->enable_me_8x8 ? 85 : 21;
