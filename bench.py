@@ -339,6 +339,9 @@ def run_ours(a):
         out_b = n_b64 * (1512 if dominant == "k_hme" else 8 * 85 * 8)
         alg_bytes = (1 + n_refs) * plane + out_b
         avg_s = dom_ms * 1e-3 / max(1, n_timed)
+        # dram__bytes_read.sum + dram__bytes_write.sum of the HME-stage kernels, per picture, from the ncu --set full
+        # capture of this workload (profiles/r01_v4_summary.md: 172 MB per launch of 32 pictures); null for other workloads
+        traffic = round(172.3e6 / 32) if (dominant == "k_hme" and (wl.w, wl.h, wl.preset, wl.bits) == (1920, 1080, 4, 8)) else None
         sm_mhz = clocks.get("sm_mhz") or peaks.get("sm_max_mhz", 1965.0)
         int_peak = INT_PEAK_LANE_INSTR_PER_CLK_SM * 4 * N_SM * sm_mhz * 1e6  # |a-b| ops/s at the sampled clock
         line = {
@@ -355,7 +358,7 @@ def run_ours(a):
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": {"bound": "hbm", "kernel": dominant, "achieved": round(alg_bytes / avg_s / 1e9, 2), "peak": hbm_peak,
-                         "unit": "GB/s", "frac": round(alg_bytes / avg_s / 1e9 / hbm_peak, 5), "traffic": None,
+                         "unit": "GB/s", "frac": round(alg_bytes / avg_s / 1e9 / hbm_peak, 5), "traffic": traffic,
                          "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback",
                          "note": "integer-ALU bound kernel (byte SAD); see roofline_int"},
             "roofline_int": {"bound": "int_alu(VABSDIFF4.U8.ACC)", "kernel": dominant,
