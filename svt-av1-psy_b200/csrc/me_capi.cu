@@ -170,8 +170,9 @@ extern "C" uint32_t svtme_session_create(SvtMeSession **out, int device, uint32_
         std::vector<CUtensorMap> maps((size_t)max_pictures * TM_KINDS);
         e = cudaMalloc(&s->d_tmaps, maps.size() * sizeof(CUtensorMap));
         if (e != cudaSuccess) { cudaFree(s->pic_slab); delete s; return SVTME_ERR_INSUFFICIENT_RESOURCES; }
-        static const int kind_level[TM_KINDS] = {1, 0, 0};
-        static const uint32_t kind_box[TM_KINDS][2] = {{TM_L1_BOX_W, TM_L1_BOX_H}, {TM_L2_BOX_W, TM_L2_BOX_H}, {TM_FP_BOX_W, TM_FP_BOX_H}};
+        static const int kind_level[TM_KINDS] = {1, 0, 0, 2, 2};
+        static const uint32_t kind_box[TM_KINDS][2] = {{TM_L1_BOX_W, TM_L1_BOX_H}, {TM_L2_BOX_W, TM_L2_BOX_H}, {TM_FP_BOX_W, TM_FP_BOX_H},
+                                                        {TM_S16T_BOX_W, TM_S16T_BOX_H}, {TM_S16W_BOX_W, TM_S16W_BOX_H}};
         for (uint32_t p = 0; p < max_pictures; p++) {
             for (int k = 0; k < TM_KINDS; k++) {
                 const DevPlane &pl = s->pics[p].lvl[kind_level[k]];

@@ -28,25 +28,14 @@ struct CtlOp {
     uint32_t build_mask;
 };
 
-// tile geometry of a staged search: shared by the builder (device) and the grid bound (host)
-__host__ __device__ inline void s16_tile_geometry(int sa_w, int sa_h, int rows, int row_step, int *tile_w, int *tile_h,
-                                                  int *n_tx, int *n_ty) {
-    if (sa_w <= 0 || sa_h <= 0) { *tile_w = 8; *tile_h = 1; *n_tx = 0; *n_ty = 0; return; }
-    int tw = (sa_w + 7) & ~7;
-    if (tw > 128) tw = 128;
-    int stride = tw / 4 + 4;
-    if ((stride & 15) == 0) stride += 2; // same pitch rule as warp_search16_tile
-    const int span = row_step * (rows - 1);
-    int th = S16_WIN_WORDS / stride - span;
-    // keep a tile to about 3 passes of the warp (96 octet tasks) so that the dynamic queue balances well
-    const int bal = 96 / (tw / 8);
-    if (th > bal) th = bal < 4 ? 4 : bal;
-    if (th < 1) th = 1;
-    if (th > sa_h) th = sa_h;
-    while (((sa_w + tw - 1) / tw) * ((sa_h + th - 1) / th) > 255) th *= 2; // tile index is 8 bits
-    *tile_w = tw; *tile_h = th;
-    *n_tx = (sa_w + tw - 1) / tw;
-    *n_ty = (sa_h + th - 1) / th;
+// tile geometry of a 1/16-plane search: shared by the builder (device) and the queue bound (host)
+__host__ __device__ inline void s16_tile_geometry(int sa_w, int sa_h, int *tile_w, int *tile_h, int *n_tx, int *n_ty, int *wide) {
+    *wide = sa_w > S16T_TILE_W;
+    *tile_w = *wide ? S16W_TILE_W : S16T_TILE_W;
+    *tile_h = *wide ? S16W_TILE_H : S16T_TILE_H;
+    if (sa_w <= 0 || sa_h <= 0) { *n_tx = 0; *n_ty = 0; return; }
+    *n_tx = (sa_w + *tile_w - 1) / *tile_w;
+    *n_ty = (sa_h + *tile_h - 1) / *tile_h;
 }
 
 // window clamp + plane address shared by prehme_core and hme_level_0/1/2
@@ -61,9 +50,11 @@ __device__ inline void ctl_make_job(HmeJobG &j, const DevPlane &ref, int16_t org
     j.ref        = ref.buf + (x_tl + y_tl * ref.stride);
     j.ref_stride = ref.stride;
     j.sa_w = sa_w; j.sa_h = sa_h; j.origin_x = origin_x; j.origin_y = origin_y;
-    int tw, th, ntx, nty;
-    s16_tile_geometry(sa_w, sa_h, rows, row_step, &tw, &th, &ntx, &nty);
-    j.tile_w = (uint16_t)tw; j.tile_h = (uint16_t)th; j.n_tx = (uint8_t)ntx; j.n_ty = (uint8_t)nty;
+    int tw, th, ntx, nty, wide;
+    s16_tile_geometry(sa_w, sa_h, &tw, &th, &ntx, &nty, &wide);
+    j.tile_w = (uint16_t)tw; j.tile_h = (uint16_t)th; j.n_tx = (uint8_t)ntx; j.n_ty = (uint8_t)nty; j.wide = (uint8_t)wide;
+    j.px = x_tl; j.py = y_tl;
+    (void)rows; (void)row_step;
     j.key    = HME_KEY_NONE;
     j.active = 1;
 }
@@ -87,7 +78,7 @@ __device__ inline void ctl_enqueue_tiles(const PicJob &job, const HmeJobG &j, in
     if (lane == leader) base = atomicAdd(&job.s16_counters[0], tot);
     base = __shfl_sync(peers, base, leader) + pre;
     for (uint32_t i = 0; i < n && base + i < job.s16_units_cap; i++)
-        job.s16_units[base + i] = make_uint2(blockIdx.y, ((uint32_t)slot_in_pic << 8) | i);
+        job.s16_units[base + i] = make_uint2(blockIdx.y, ((uint32_t)slot_in_pic << 10) | i);
 }
 
 // key -> (sad, centre); centre keeps its value when no position was evaluated

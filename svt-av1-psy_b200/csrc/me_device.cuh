@@ -62,11 +62,11 @@ struct HmeJobG {
     int                ref_stride;
     int16_t            sa_w, sa_h, origin_x, origin_y;
     uint16_t           tile_w, tile_h; // positions per tile (tile_w multiple of 8)
-    uint8_t            n_tx, n_ty, active, pad_;
+    uint8_t            n_tx, n_ty, active, wide; // wide: 1 = 128x16-position tiles, 0 = 16x96 (1/16-plane searches)
+    int16_t            px, py;                   // plane coordinates of the window's top-left sample
 };
 #define HME_JOBS_PER_B64 32
 #define HME_KEY_NONE ((0xffffffull << 32) | 0xffffffffull) /* best_sad = 0xffffff, nothing found */
-#define S16_WIN_WORDS 1152 /* per-warp staging buffer of k_search16: 4.5 KB */
 
 // Full-pel search of one (b64, list, ref), set up by k_fp_plan and executed by k_fp_search.
 struct FpJobG {

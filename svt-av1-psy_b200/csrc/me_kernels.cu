@@ -189,11 +189,9 @@ static int next_pow2(int v) {
 
 uint32_t svtme_s16_units_cap(const SvtMePicParams &pp, int n_b64) {
     const SvtMeCtrls &c = pp.ctrls;
-    const bool sub = c.hme_search_method == SVTME_SUB_SAD_SEARCH;
-    const int  row_step = sub ? 2 : 1, rows0 = sub ? 8 : 16;
     auto tiles_of = [&](int w, int h) {
-        int tw, th, ntx, nty;
-        s16_tile_geometry(w, h, rows0, row_step, &tw, &th, &ntx, &nty);
+        int tw, th, ntx, nty, wide;
+        s16_tile_geometry(w, h, &tw, &th, &ntx, &nty, &wide);
         return (long long)(ntx * nty < 1 ? 1 : ntx * nty);
     };
     long long per_b64 = 0;
@@ -233,18 +231,11 @@ int svtme_launch_picture_me(const PicJob *h_jobs, int n, const PicJob *d_jobs, c
     const SvtMeCtrls     &c  = j0.pp.ctrls; // HME flags / search methods are equal across a batch (validated by the caller)
     int launches = 0;
     const bool sub = c.hme_search_method == SVTME_SUB_SAD_SEARCH;
-    const int  row_step = sub ? 2 : 1, rows0 = sub ? 8 : 16;
     const uint32_t ALL = 0xffu, LIST0 = 0x0fu, LIST1 = 0xf0u;
     const int n_b64 = j0.n_b64;
     const unsigned ny = (unsigned)n;
     const int ctl_grid = (n_b64 + CTL_WARPS - 1) / CTL_WARPS;
-    auto tiles_of = [&](int w, int h) {
-        int tw, th, ntx, nty;
-        s16_tile_geometry(w, h, rows0, row_step, &tw, &th, &ntx, &nty);
-        return ntx * nty < 1 ? 1 : ntx * nty;
-    };
     bool any_zz = false, any_l1dep = false, any_dep = false, any_sr2 = false;
-    int  mt_pre = 1, mt_l0 = 1;
     for (int i = 0; i < n; i++) {
         const SvtMePicParams &pp = h_jobs[i].pp;
         const SvtMeCtrls     &ci = pp.ctrls;
@@ -252,11 +243,6 @@ int svtme_launch_picture_me(const PicJob *h_jobs, int n, const PicJob *d_jobs, c
         any_l1dep |= ci.prehme_enable && ci.prehme_l1_early_exit && pp.num_of_list_to_search == 2 && pp.temporal_layer_index > 0;
         any_dep |= ci.enable_me_sr_adjustment && ci.distance_based_hme_resizing && ci.reduce_hme_l0_sr_th_min && ci.reduce_hme_l0_sr_th_max;
         any_sr2 |= ci.enable_me_sr_adjustment == 2;
-        if (ci.prehme_enable)
-            mt_pre = imax_h(mt_pre, imax_h(tiles_of(ci.prehme_sa_cfg[0].sa_max.width, ci.prehme_sa_cfg[0].sa_max.height),
-                                           tiles_of(ci.prehme_sa_cfg[1].sa_max.width, ci.prehme_sa_cfg[1].sa_max.height)));
-        const int qw = ((((ci.hme_l0_sa.sa_max.width / 2) + 15) & ~15) + 7) & ~7;
-        mt_l0 = imax_h(mt_l0, tiles_of(qw, ci.hme_l0_sa.sa_max.height / 2));
     }
     opt_in_shared_memory();
     if (ev_hme0) cudaEventRecord(ev_hme0, st);
@@ -283,13 +269,14 @@ int svtme_launch_picture_me(const PicJob *h_jobs, int n, const PicJob *d_jobs, c
         cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
     }
+    const size_t s16_smem = (size_t)SEARCH_WARPS * 2 * TM_S16_BUF + 128;
     if (!g_s16_ctas_per_sm) {
         int k = 0;
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&k, k_search16, 32 * SEARCH_WARPS, 0);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&k, k_search16, 32 * SEARCH_WARPS, s16_smem);
         g_s16_ctas_per_sm = k > 0 ? k : 1;
     }
-    auto search16 = [&](int /*max_tiles*/, int skip) {
-        k_search16<<<n_sm * g_s16_ctas_per_sm, 32 * SEARCH_WARPS, 0, st>>>(d_jobs, skip);
+    auto search16 = [&](int skip) {
+        k_search16<<<n_sm * g_s16_ctas_per_sm, 32 * SEARCH_WARPS, s16_smem, st>>>(d_jobs, skip);
         launches++;
     };
     auto search_wide = [&](int level) {
@@ -308,14 +295,14 @@ int svtme_launch_picture_me(const PicJob *h_jobs, int n, const PicJob *d_jobs, c
     if (c.prehme_enable) {
         if (any_l1dep) {
             emit(ST_NONE, ST_PREHME, LIST0);
-            search16(mt_pre, c.prehme_skip_search_line);
+            search16(c.prehme_skip_search_line);
             post = ST_PREHME; pmask = LIST0;
             emit(ST_NONE, ST_PREHME, LIST1);
-            search16(mt_pre, c.prehme_skip_search_line);
+            search16(c.prehme_skip_search_line);
             post = ST_PREHME; pmask = LIST1;
         } else {
             emit(ST_NONE, ST_PREHME, ALL);
-            search16(mt_pre, c.prehme_skip_search_line);
+            search16(c.prehme_skip_search_line);
             post = ST_PREHME; pmask = ALL;
         }
         fin_pending = ST_PREHME;
@@ -324,14 +311,14 @@ int svtme_launch_picture_me(const PicJob *h_jobs, int n, const PicJob *d_jobs, c
         if (c.enable_hme_level0_flag) {
             if (any_dep) {
                 emit(fin_pending, ST_L0, 0x01u);
-                search16(mt_l0, 0);
+                search16(0);
                 post = ST_L0; pmask = 0x01u;
                 emit(ST_NONE, ST_L0, ALL & ~0x01u);
-                search16(mt_l0, 0);
+                search16(0);
                 post = ST_L0; pmask = ALL & ~0x01u;
             } else {
                 emit(fin_pending, ST_L0, ALL);
-                search16(mt_l0, 0);
+                search16(0);
                 post = ST_L0; pmask = ALL;
             }
             fin_pending = ST_NONE;
@@ -415,21 +402,28 @@ __global__ void k_kat_sad_loop_generic(const uint8_t *src, int src_stride, const
     if (best != HME_KEY_NONE) atomicMin(out_key, best);
 }
 
-// blocks up to 16x16: the staged tile search of k_search16, one warp per tile
-__global__ void __launch_bounds__(32 * SEARCH_WARPS) k_kat_search16(const uint8_t *src, int src_stride, const uint8_t *ref,
-                                                                     int raw_stride, int row_step, int bh, int bw, int skip,
+// blocks up to 16x16: the TMA tile search of k_search16, one warp per tile. The window was re-pitched by the caller
+// (row pitch multiple of 16, `map` describes it with the tall or the wide box); position (0,0) is its sample (0,0).
+__global__ void __launch_bounds__(32 * SEARCH_WARPS) k_kat_search16(const __grid_constant__ CUtensorMap map, const uint8_t *src,
+                                                                     int src_stride, int row_step, int bh, int bw, int skip,
                                                                      int sa_w, int sa_h, int tile_w, int tile_h, int n_tx,
-                                                                     int n_ty, unsigned long long *out_key) {
-    __shared__ __align__(16) uint32_t s_win[SEARCH_WARPS][S16_WIN_WORDS];
+                                                                     int n_ty, int wide, unsigned long long *out_key) {
+    __shared__ __align__(128) uint8_t s_buf[SEARCH_WARPS][TM_S16_BUF];
     __shared__ __align__(16) uint32_t s_src[SEARCH_WARPS][16 * 4];
+    __shared__ __align__(8) uint64_t s_bar[SEARCH_WARPS][2];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int tile = blockIdx.x * SEARCH_WARPS + warp;
     if (tile >= n_tx * n_ty) return;
-    warp_stage_src(s_src[warp], 4, src, src_stride, 1, bh, bw);
+    TilePipe P;
+    pipe_init(P, s_buf[warp], 0, s_bar[warp], 0);
     const int ty = tile / n_tx, tx = tile - ty * n_tx;
     const int x0 = tx * tile_w, y0 = ty * tile_h;
-    const unsigned long long key = warp_search16_tile(s_win[warp], s_src[warp], ref, raw_stride, sa_w, x0, y0,
-                                                     imin(tile_w, sa_w - x0), imin(tile_h, sa_h - y0), bw, bh, row_step,
+    pipe_issue_bytes(P, 0, &map, x0 & ~15, y0, wide ? TM_S16W_BOX_W * TM_S16W_BOX_H : TM_S16T_BOX_W * TM_S16T_BOX_H);
+    warp_stage_src16(smem_u32(s_src[warp]), src, src_stride, 1, bh, bw);
+    pipe_wait(P, 0);
+    __syncwarp();
+    const unsigned long long key = warp_search16_tile(P.buf[0], wide ? TM_S16W_BOX_W : TM_S16T_BOX_W, smem_u32(s_src[warp]), (uint32_t)x0 & 15u,
+                                                     sa_w, x0, y0, imin(tile_w, sa_w - x0), imin(tile_h, sa_h - y0), bw, bh, row_step,
                                                      skip && bw == 16 && bh <= 16);
     if (lane == 0 && key != HME_KEY_NONE) atomicMin(out_key, key);
 }
@@ -477,12 +471,19 @@ int svtme_launch_kat_sad_loop(const uint8_t *d_src, int src_stride, const uint8_
     cudaMemcpyAsync(d_key, &init, sizeof(init), cudaMemcpyHostToDevice, st);
     if (sa_w <= 0 || sa_h <= 0) return 0;
     const bool strided = src_stride_raw > 0 && (ref_stride == src_stride_raw || ref_stride == 2 * src_stride_raw);
-    if (strided && bw <= 16 && bh <= 16) {
-        const int row_step = ref_stride / src_stride_raw;
-        int tw, th, ntx, nty;
-        s16_tile_geometry(sa_w, sa_h, bh, row_step, &tw, &th, &ntx, &nty);
+    if (strided && bw <= 16 && bh <= 16 && d_pitched && (bh - 1) * (ref_stride / src_stride_raw) <= 15) {
+        const int row_step = ref_stride / src_stride_raw; // the production shapes: 16 rows, or 8 rows two apart
+        const int w_bytes = sa_w - 1 + bw, rows = sa_h - 1 + (bh - 1) * row_step + 1;
+        const int pitch = (w_bytes + 15 + 16) & ~15;
+        if ((size_t)pitch * rows > pitched_cap) return 0;
+        cudaMemsetAsync(d_pitched, 0, (size_t)pitch * rows, st);
+        cudaMemcpy2DAsync(d_pitched, pitch, d_ref, src_stride_raw, w_bytes, rows, cudaMemcpyDeviceToDevice, st);
+        int tw, th, ntx, nty, wide;
+        s16_tile_geometry(sa_w, sa_h, &tw, &th, &ntx, &nty, &wide);
+        CUtensorMap map;
+        if (svtme_encode_tmap(&map, d_pitched, pitch, rows, wide ? TM_S16W_BOX_W : TM_S16T_BOX_W, wide ? TM_S16W_BOX_H : TM_S16T_BOX_H)) return 0;
         k_kat_search16<<<(ntx * nty + SEARCH_WARPS - 1) / SEARCH_WARPS, 32 * SEARCH_WARPS, 0, st>>>(
-            d_src, src_stride, d_ref, src_stride_raw, row_step, bh, bw, skip, sa_w, sa_h, tw, th, ntx, nty, d_key);
+            map, d_src, src_stride, row_step, bh, bw, skip, sa_w, sa_h, tw, th, ntx, nty, wide, d_key);
     } else if (strided && bw <= 64 && bh * (ref_stride / src_stride_raw) <= 64 && d_pitched && sa_w * sa_h <= 4096) {
         // re-pitch the window (rows 16-byte aligned, as the picture store keeps its planes) and describe it to the TMA
         const int row_step = ref_stride / src_stride_raw;

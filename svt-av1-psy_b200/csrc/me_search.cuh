@@ -3,13 +3,12 @@
 //
 //   k_zz          zero-MV SAD per (b64, ref)                      init_zz_sad        motion_estimation.c:2452
 //   k_search16    pre-HME regions and HME level-0 quadrants       prehme_core :1638, hme_level_0 :820
-//                 (blocks <= 16 wide on the 1/16 plane): unit = (job, tile of the window); the warp
-//                 stages the tile (+ the rows/cols the block reaches) in its own 4.5 KB of shared
-//                 memory with 4-byte aligned rows, then each lane evaluates 8 consecutive positions
-//                 per task (strip16_sad8: 6 words -> 24 SHF + 32 VABSDIFF4 per block row)
-//   k_search_wide HME level 1 / 2 (32- / 64-wide blocks, windows of 8x3 .. 16x16 positions): unit =
-//                 32 consecutive tasks (job, y, octet, 16-pixel strip) of a flat list with a fixed
-//                 number of task slots per job; reference rows straight from global memory
+//                 (blocks <= 16 wide on the 1/16 plane): unit = (job, tile of the window); one TMA load
+//                 brings the tile (+ the rows/cols the block reaches) into the warp's shared memory,
+//                 then each lane evaluates 8 consecutive positions per task (strip16_sad8: 15 SHF +
+//                 32 VABSDIFF4 per block row, + 6 SHF when the window is not 8-byte aligned)
+//   k_search_blk  HME level 1 / 2 (32- / 64-wide blocks, windows of 8x3 .. 16x16 positions): lanes
+//                 spread over the block, TMA tiles (see below)
 //
 // All follow svt_sad_loop_kernel (compute_sad_c.c:58-101): raster order, strict '<', best starts at
 // 0xffffff. Result = 64-bit key (sad << 32 | y*sa_w + x); atomicMin over the tiles of a job keeps
@@ -80,35 +79,38 @@ __global__ void __launch_bounds__(32 * SEARCH_WARPS) k_zz(const PicJob *__restri
     }
 }
 
-// ---- warp-level staged search of one tile, block <= 16 wide -----------------------------------
-// win: this warp's staging buffer (S16_WIN_WORDS words, 16-byte aligned); src: n_rows x 4 words,
-// bytes >= bw zeroed. Returns the warp-wide best key of the tile (positions indexed in the window).
-__device__ inline unsigned long long warp_search16_tile(uint32_t *win, const uint32_t *src, const uint8_t *ref,
-                                                        int ref_stride, int sa_w, int x0, int y0, int tw, int th, int bw,
-                                                        int n_rows, int row_step, bool skip_lines) {
-    const int lane   = threadIdx.x & 31;
-    const int n_oct  = (tw + 7) >> 3;
-    const int wpr    = 2 * n_oct + 4;                      // words per staged row
-    const int stride = (wpr & 15) == 0 ? wpr + 2 : wpr;    // a row pitch of 16k words would put every row on the same banks
-    const int span   = row_step * (n_rows - 1);
-    stage_rect(win, stride, ref + (size_t)y0 * ref_stride + x0, ref_stride, th + span, wpr, lane, 32);
-    __syncwarp();
+// ---- 1/16-plane searches (blocks <= 16 wide): tiles through TMA ---------------------------------
+// One tile = TM_S16T (16 positions x 96 rows) or TM_S16W (128 x 16) of a window, fetched from the 16-byte boundary at
+// or before its first position. lane = (search row, octet of 8 positions); a lane reads 32 bytes per block row from
+// the 8-byte boundary at or before its octet (4 LDS.64, consecutive lanes = consecutive 8-byte units), and the
+// remaining 0..7 bytes of misalignment are the same for every octet of the job: one warp-uniform word select (JW)
+// and one funnel shift per word. src: n_rows x 16 bytes in shared memory, bytes >= bw zeroed.
+// Returns the warp-wide best key of the tile (positions indexed in the window).
+template <int JW>
+__device__ __forceinline__ void s16_tile_tasks(uint32_t buf, int pitch, uint32_t src, uint32_t h8, uint32_t t8, int sa_w, int x0,
+                                               int y0, int tw, int th, int bw, int n_rows, int row_step, bool skip_lines,
+                                               uint32_t &best_sad, uint32_t &best_idx) {
+    const int lane  = threadIdx.x & 31;
+    const int n_oct = (tw + 7) >> 3;
     const bool     partial = bw < 16;
     const uint32_t m0 = lo_bytes_mask(bw), m1 = lo_bytes_mask(bw - 4), m2 = lo_bytes_mask(bw - 8), m3 = lo_bytes_mask(bw - 12);
-    uint32_t best_sad = 0xffffff, best_idx = 0xffffffffu;
     int yy = lane / n_oct, oct = lane - yy * n_oct;
     const int dyy = 32 / n_oct, doct = 32 - dyy * n_oct;
+    const uint32_t rstep = (uint32_t)(row_step * pitch);
     for (; yy < th; yy += dyy, oct += doct) {
         if (oct >= n_oct) { oct -= n_oct; yy++; if (yy >= th) break; }
-        const int y  = y0 + yy;
+        const int y = y0 + yy;
         if (skip_lines && (y & 1) == 0) continue;
         uint32_t acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-        const uint32_t *row = win + yy * stride + 2 * oct;
+        uint32_t row = buf + (uint32_t)(yy * pitch) + 8u * (h8 + (uint32_t)oct);
 #pragma unroll 2
-        for (int rr = 0; rr < n_rows; rr++, row += row_step * stride) {
-            const uint2 a = *(const uint2 *)(row), b = *(const uint2 *)(row + 2), cc = *(const uint2 *)(row + 4);
-            const uint4 sv = *(const uint4 *)(src + 4 * rr);
-            const uint32_t w[6] = {a.x, a.y, b.x, b.y, cc.x, cc.y};
+        for (int rr = 0; rr < n_rows; rr++, row += rstep) {
+            const uint2 c0 = lds64(row), c1 = lds64(row + 8), c2 = lds64(row + 16), c3 = lds64(row + 24);
+            const uint4 sv = lds128(src + 16u * rr);
+            const uint32_t c[8] = {c0.x, c0.y, c1.x, c1.y, c2.x, c2.y, c3.x, c3.y};
+            uint32_t w[6];
+#pragma unroll
+            for (int k = 0; k < 6; k++) w[k] = __funnelshift_r(c[JW + k], c[JW + k + 1], t8);
             const uint32_t s[4] = {sv.x, sv.y, sv.z, sv.w};
             if (!partial) {
                 strip16_sad8(w, s, acc);
@@ -120,7 +122,10 @@ __device__ inline unsigned long long warp_search16_tile(uint32_t *win, const uin
                     const uint32_t v1 = shf ? __funnelshift_r(w[o + 1], w[o + 2], shf) : w[o + 1];
                     const uint32_t v2 = shf ? __funnelshift_r(w[o + 2], w[o + 3], shf) : w[o + 2];
                     const uint32_t v3 = shf ? __funnelshift_r(w[o + 3], w[o + 4], shf) : w[o + 3];
-                    acc[p] += __vsadu4(v0 & m0, s[0]) + __vsadu4(v1 & m1, s[1]) + __vsadu4(v2 & m2, s[2]) + __vsadu4(v3 & m3, s[3]);
+                    acc[p] = sad4_acc(v0 & m0, s[0], acc[p]);
+                    acc[p] = sad4_acc(v1 & m1, s[1], acc[p]);
+                    acc[p] = sad4_acc(v2 & m2, s[2], acc[p]);
+                    acc[p] = sad4_acc(v3 & m3, s[3], acc[p]);
                 }
             }
         }
@@ -133,122 +138,104 @@ __device__ inline unsigned long long warp_search16_tile(uint32_t *win, const uin
             }
         }
     }
-    __syncwarp();
+}
+
+// a: byte offset of the tile's position 0 inside its rows ((plane x of the position) & 15)
+__device__ inline unsigned long long warp_search16_tile(uint32_t buf, int pitch, uint32_t src, uint32_t a, int sa_w, int x0, int y0,
+                                                        int tw, int th, int bw, int n_rows, int row_step, bool skip_lines) {
+    uint32_t best_sad = 0xffffff, best_idx = 0xffffffffu;
+    const uint32_t h8 = a >> 3, t8 = (a & 3u) * 8u;
+    if (a & 4u) s16_tile_tasks<1>(buf, pitch, src, h8, t8, sa_w, x0, y0, tw, th, bw, n_rows, row_step, skip_lines, best_sad, best_idx);
+    else s16_tile_tasks<0>(buf, pitch, src, h8, t8, sa_w, x0, y0, tw, th, bw, n_rows, row_step, skip_lines, best_sad, best_idx);
     return warp_min_u64(((unsigned long long)best_sad << 32) | best_idx);
 }
 
-// stage the source block rows of one pyramid level for one warp: n_rows x `words` words
-__device__ inline void warp_stage_src(uint32_t *dst, int words, const uint8_t *src, int stride, int row_step, int n_rows,
-                                      int bw) {
+// source block rows of the 1/16 plane -> shared memory (n_rows x 16 bytes, bytes >= bw zeroed); block origins are 16-byte aligned
+__device__ __forceinline__ void warp_stage_src16(uint32_t dst, const uint8_t *src, int stride, int row_step, int n_rows, int bw) {
     const int lane = threadIdx.x & 31;
-    for (int i = lane; i < n_rows * words; i += 32) {
-        const int r = i / words, k = i - r * words;
-        dst[i] = ldg_u32_unaligned(src + (size_t)r * row_step * stride + 4 * k) & lo_bytes_mask(bw - 4 * k);
+    if (lane < n_rows) {
+        uint4 v = __ldg((const uint4 *)(src + (size_t)lane * row_step * stride));
+        v.x &= lo_bytes_mask(bw); v.y &= lo_bytes_mask(bw - 4); v.z &= lo_bytes_mask(bw - 8); v.w &= lo_bytes_mask(bw - 12);
+        asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(dst + 16u * lane), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
     }
 }
 
 // ---- k_search16 ------------------------------------------------------------------------------
-// persistent warps pull (picture, job, tile) units from the queue k_hme_ctl filled
-__global__ void __launch_bounds__(32 * SEARCH_WARPS, 8) k_search16(const PicJob *__restrict__ jobs, int skip_cfg) {
-    __shared__ __align__(16) uint32_t s_win[SEARCH_WARPS][S16_WIN_WORDS];
-    __shared__ __align__(16) uint32_t s_src[SEARCH_WARPS][16 * 4];
+// persistent warps pull (picture, job, tile) units from the queue k_hme_ctl filled; the tile of the next unit is
+// in flight while the current one is searched
+struct S16Unit {
+    int  pic, slot, tile;
+    int  px, py, sa_w, sa_h, tile_w, tile_h, n_tx, wide;
+    bool valid;
+};
+__device__ __forceinline__ S16Unit s16_fetch_unit(const PicJob *__restrict__ jobs, uint32_t n_units) {
+    S16Unit un;
+    uint32_t ui = 0;
+    if ((threadIdx.x & 31) == 0) ui = atomicAdd(&jobs[0].s16_counters[1], 1u);
+    ui = __shfl_sync(0xffffffffu, ui, 0);
+    un.valid = ui < n_units;
+    un.pic = un.slot = un.tile = un.px = un.py = un.sa_w = un.sa_h = un.wide = 0;
+    un.tile_w = un.tile_h = un.n_tx = 1;
+    if (un.valid) {
+        const uint2 q = jobs[0].s16_units[ui];
+        un.pic = (int)q.x; un.slot = (int)(q.y >> 10); un.tile = (int)(q.y & 1023u);
+        const HmeJobG &j = jobs[un.pic].hme_jobs[un.slot];
+        un.px = j.px; un.py = j.py; un.sa_w = j.sa_w; un.sa_h = j.sa_h;
+        un.tile_w = j.tile_w; un.tile_h = j.tile_h; un.n_tx = j.n_tx; un.wide = j.wide;
+    }
+    return un;
+}
+
+__global__ void __launch_bounds__(32 * SEARCH_WARPS) k_search16(const PicJob *__restrict__ jobs, int skip_cfg) {
+    extern __shared__ __align__(128) uint8_t s_dyn[];
+    __shared__ __align__(16) uint32_t s_src[SEARCH_WARPS][2][16 * 4];
+    __shared__ __align__(8) uint64_t s_bar[SEARCH_WARPS][2];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const PicJob &job0 = jobs[0];
     const uint32_t n_units = min(job0.s16_counters[0], job0.s16_units_cap);
-    int cur_b = -1, cur_pic = -1;
+    if (n_units == 0) return;
     const bool sub = job0.pp.ctrls.hme_search_method == SVTME_SUB_SAD_SEARCH;
     const int row_step = sub ? 2 : 1;
-    int bw = 0, rows = 0;
-    for (;;) {
-        uint32_t ui = 0;
-        if (lane == 0) ui = atomicAdd(&job0.s16_counters[1], 1u);
-        ui = __shfl_sync(0xffffffffu, ui, 0);
-        if (ui >= n_units) break;
-        const uint2 unit = job0.s16_units[ui];
-        const PicJob &job = jobs[unit.x];
-        const int slot = (int)(unit.y >> 8), tile = (int)(unit.y & 0xff);
-        HmeJobG &j = job.hme_jobs[slot];
-        const int b = slot / HME_JOBS_PER_B64;
-        if (b != cur_b || (int)unit.x != cur_pic) { // source block of this b64 on the 1/16 plane
-            const B64Geo g = b64_geo(job, b);
-            bw = g.b64_w >> 2;
-            rows = sub ? (g.b64_h >> 2) >> 1 : (g.b64_h >> 2);
-            const DevPlane &ss = job.src.lvl[2];
-            __syncwarp();
-            warp_stage_src(s_src[warp], 4, ss.buf + (size_t)(ss.org_y + (g.org_y >> 2)) * ss.stride + ss.org_x + (g.org_x >> 2),
-                           ss.stride, row_step, rows, bw);
-            cur_b = b; cur_pic = (int)unit.x;
-        }
-        const int ty = tile / j.n_tx, tx = tile - ty * j.n_tx;
-        const int x0 = tx * j.tile_w, y0 = ty * j.tile_h;
-        const int tw = imin(j.tile_w, j.sa_w - x0), th = imin(j.tile_h, j.sa_h - y0);
+    uint8_t *sbase = s_dyn + ((128u - (smem_u32(s_dyn) & 127u)) & 127u);
+    TilePipe P;
+    pipe_init(P, sbase + (size_t)warp * 2 * TM_S16_BUF, TM_S16_BUF, s_bar[warp], 0);
+    // issue: the tile load and the source rows of the unit's b64 (both land in stage `st`)
+    auto issue = [&](const S16Unit &un, int st) {
+        const PicJob &job = jobs[un.pic];
+        const int lr = (un.slot % HME_JOBS_PER_B64) >> 2, b = un.slot / HME_JOBS_PER_B64;
+        const CUtensorMap *map = (const CUtensorMap *)job.ref[lr >> 2][lr & 3].tmap + (un.wide ? TM_S16W : TM_S16T);
+        const int ty = un.tile / un.n_tx, tx = un.tile - ty * un.n_tx;
+        pipe_issue_bytes(P, st, map, (un.px + tx * un.tile_w) & ~15, un.py + ty * un.tile_h,
+                         un.wide ? TM_S16W_BOX_W * TM_S16W_BOX_H : TM_S16T_BOX_W * TM_S16T_BOX_H);
+        const B64Geo g = b64_geo(job, b);
+        const DevPlane &ss = job.src.lvl[2];
+        const int rows = sub ? (g.b64_h >> 2) >> 1 : (g.b64_h >> 2);
+        warp_stage_src16(smem_u32(s_src[warp][st]), ss.buf + (size_t)(ss.org_y + (g.org_y >> 2)) * ss.stride + ss.org_x + (g.org_x >> 2),
+                         ss.stride, row_step, rows, g.b64_w >> 2);
+    };
+    S16Unit cur = s16_fetch_unit(jobs, n_units);
+    if (!cur.valid) return;
+    int stage = 0;
+    issue(cur, stage);
+    while (cur.valid) {
+        const S16Unit nxt = s16_fetch_unit(jobs, n_units);
+        if (nxt.valid) issue(nxt, stage ^ 1);
+        const PicJob &job = jobs[cur.pic];
+        const B64Geo g = b64_geo(job, cur.slot / HME_JOBS_PER_B64);
+        const int bw = g.b64_w >> 2, rows = sub ? (g.b64_h >> 2) >> 1 : (g.b64_h >> 2);
+        const int ty = cur.tile / cur.n_tx, tx = cur.tile - ty * cur.n_tx;
+        const int x0 = tx * cur.tile_w, y0 = ty * cur.tile_h;
         const bool skip = skip_cfg && bw == 16 && rows <= 16;
-        const unsigned long long key = warp_search16_tile(s_win[warp], s_src[warp], j.ref, j.ref_stride, j.sa_w, x0, y0, tw, th,
-                                                         bw, rows, row_step, skip);
-        if (lane == 0 && key != HME_KEY_NONE) atomicMin(&j.key, key);
+        pipe_wait(P, stage);
+        __syncwarp(); // the source rows written by other lanes
+        const unsigned long long key = warp_search16_tile(P.buf[stage], cur.wide ? TM_S16W_BOX_W : TM_S16T_BOX_W, smem_u32(s_src[warp][stage]),
+                                                         (uint32_t)(cur.px + x0) & 15u, cur.sa_w, x0, y0, imin(cur.tile_w, cur.sa_w - x0),
+                                                         imin(cur.tile_h, cur.sa_h - y0), bw, rows, row_step, skip);
+        if (lane == 0 && key != HME_KEY_NONE) atomicMin(&job.hme_jobs[cur.slot].key, key);
         __syncwarp();
+        cur = nxt;
+        stage ^= 1;
     }
-}
-
-// ---- wide blocks: one task = (y, octet, 16-pixel strip) of one search, rows from global memory ----
-// Returns in acc[] the strip-summed SADs of the 8 positions (valid in every lane of the strip group).
-// search rows advance by search_stride, block rows by ref_blk_stride / src_blk_stride.
-__device__ inline void warp_search_wide_task(bool active, const uint8_t *ref, int search_stride, int ref_blk_stride,
-                                             const uint8_t *src, int src_blk_stride, int bw, int rows, int y, int oct,
-                                             int strip, int strips, uint32_t (&acc)[8]) {
-#pragma unroll
-    for (int p = 0; p < 8; p++) acc[p] = 0;
-    if (active) {
-        const uint8_t *s  = src + 16 * strip;
-        const uint8_t *gr = ref + (size_t)y * search_stride + 8 * oct + 16 * strip;
-        const int rstr = ref_blk_stride, sstr = src_blk_stride;
-        const int rem = bw - 16 * strip; // valid bytes of this strip
-        const uint32_t m0 = lo_bytes_mask(rem), m1 = lo_bytes_mask(rem - 4), m2 = lo_bytes_mask(rem - 8), m3 = lo_bytes_mask(rem - 12);
-#pragma unroll 2
-        for (int rr = 0; rr < rows; rr++, gr += rstr, s += sstr) {
-            const uintptr_t a  = (uintptr_t)gr;
-            const uint32_t *q  = (const uint32_t *)(a & ~(uintptr_t)3);
-            const uint32_t  sa = (uint32_t)(a & 3) * 8;
-            uint32_t gw[7], w[6];
-#pragma unroll
-            for (int k = 0; k < 7; k++) gw[k] = __ldg(q + k);
-#pragma unroll
-            for (int k = 0; k < 6; k++) w[k] = __funnelshift_r(gw[k], gw[k + 1], sa);
-            const uint32_t sv[4] = {ldg_u32_unaligned(s) & m0, ldg_u32_unaligned(s + 4) & m1, ldg_u32_unaligned(s + 8) & m2,
-                                    ldg_u32_unaligned(s + 12) & m3};
-            if (rem >= 16) {
-                strip16_sad8(w, sv, acc);
-            } else {
-#pragma unroll
-                for (int p = 0; p < 8; p++) {
-                    const int o = p >> 2, shf = (p & 3) * 8;
-                    const uint32_t v0 = shf ? __funnelshift_r(w[o], w[o + 1], shf) : w[o];
-                    const uint32_t v1 = shf ? __funnelshift_r(w[o + 1], w[o + 2], shf) : w[o + 1];
-                    const uint32_t v2 = shf ? __funnelshift_r(w[o + 2], w[o + 3], shf) : w[o + 2];
-                    const uint32_t v3 = shf ? __funnelshift_r(w[o + 3], w[o + 4], shf) : w[o + 3];
-                    acc[p] += __vsadu4(v0 & m0, sv[0]) + __vsadu4(v1 & m1, sv[1]) + __vsadu4(v2 & m2, sv[2]) + __vsadu4(v3 & m3, sv[3]);
-                }
-            }
-        }
-    }
-#pragma unroll
-    for (int p = 0; p < 8; p++) {
-        if (strips >= 2) acc[p] += __shfl_xor_sync(0xffffffffu, acc[p], 1);
-        if (strips >= 4) acc[p] += __shfl_xor_sync(0xffffffffu, acc[p], 2);
-    }
-}
-
-__device__ __forceinline__ unsigned long long octet_best_key(const uint32_t (&acc)[8], int y, int oct, int sa_w) {
-    uint32_t best_sad = 0xffffff, best_idx = 0xffffffffu;
-#pragma unroll
-    for (int p = 0; p < 8; p++) {
-        const int x = 8 * oct + p;
-        if (x < sa_w && acc[p] < best_sad) {
-            best_sad = acc[p];
-            best_idx = (uint32_t)(y * sa_w + x);
-        }
-    }
-    return ((unsigned long long)best_sad << 32) | best_idx;
 }
 
 // ---- block-parallel search for wide blocks (HME level 1 / 2) -----------------------------------
@@ -316,12 +303,10 @@ __global__ void __launch_bounds__(32 * SEARCH_WARPS) k_search_blk(const PicJob *
     int my_act = 0, my_px = 0, my_py = 0, my_sw = 0, my_sh = 0;
     const int b = u >> 3, l = (u >> 2) & 1, r = u & 3;
     const DevPic   &rp = job.ref[l][r];
-    const DevPlane &pl = rp.lvl[LEVEL == 1 ? 1 : 0];
     if (lane < 4) {
         const HmeJobG &j = jq[lane];
         if (j.active && j.sa_w > 0 && j.sa_h > 0) {
-            const long long off = j.ref - pl.buf;
-            my_act = 1; my_py = (int)(off / pl.stride); my_px = (int)(off - (long long)my_py * pl.stride);
+            my_act = 1; my_px = j.px; my_py = j.py;
             my_sw = j.sa_w; my_sh = j.sa_h;
         }
     }

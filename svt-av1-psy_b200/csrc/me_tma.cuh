@@ -17,13 +17,24 @@
 #include "me_device.cuh"
 
 // tensor-map kinds of one picture (DevPic::tmap[kind]); box = bytes per row x rows
-enum { TM_L1 = 0, TM_L2 = 1, TM_FP = 2, TM_KINDS = 3 };
+enum { TM_L1 = 0, TM_L2 = 1, TM_FP = 2, TM_S16T = 3, TM_S16W = 4, TM_KINDS = 5 };
 #define TM_L1_BOX_W 80  /* 32 + 15 (positions) + 15 (alignment) = 62; 80 = 5 chunks makes rows 2 apart hit different banks */
 #define TM_L1_BOX_H 35  /* 32 block rows + 4 search rows - 1 */
 #define TM_L2_BOX_W 96  /* 64 + 15 + 15 = 94 */
 #define TM_L2_BOX_H 67
 #define TM_FP_BOX_W 96
 #define TM_FP_BOX_H 71  /* 64 + 8 search rows - 1 */
+/* 1/16 plane, 16-wide blocks (pre-HME, HME level 0): a tall tile for windows up to 16 positions wide, a wide one otherwise.
+   Rows are read with LDS.64 from the 8-byte boundary at or before a position: 8 * 17 + 32 = 168 > 160 never happens
+   because the last octet of a wide tile starts at most 8 * 16 bytes in (8 * (1 + 15) + 32 = 160). */
+#define TM_S16T_BOX_W 48
+#define TM_S16T_BOX_H 111 /* 96 search rows + 15 block rows */
+#define TM_S16W_BOX_W 160
+#define TM_S16W_BOX_H 31  /* 16 search rows + 15 */
+#define S16T_TILE_W 16
+#define S16T_TILE_H 96
+#define S16W_TILE_W 128
+#define S16W_TILE_H 16
 #define TM_BLK_TILE_W 16
 #define TM_BLK_TILE_H 4
 #define TM_FP_TILE_W 16
@@ -32,6 +43,7 @@ enum { TM_L1 = 0, TM_L2 = 1, TM_FP = 2, TM_KINDS = 3 };
 #define TM_L1_BUF TM_ALIGN128(TM_L1_BOX_W * TM_L1_BOX_H)
 #define TM_L2_BUF TM_ALIGN128(TM_L2_BOX_W * TM_L2_BOX_H)
 #define TM_FP_BUF TM_ALIGN128(TM_FP_BOX_W * TM_FP_BOX_H)
+#define TM_S16_BUF TM_ALIGN128(TM_S16T_BOX_W * TM_S16T_BOX_H) /* 5376 >= the wide box (4960) */
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t *bar, int count) {
@@ -60,6 +72,11 @@ __device__ __forceinline__ void tma_load_box(void *dst, const CUtensorMap *map, 
                  "l"(map), "r"(x), "r"(y), "r"(smem_u32(bar))
                  : "memory");
 }
+__device__ __forceinline__ uint2 lds64(uint32_t addr) {
+    uint2 v;
+    asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr));
+    return v;
+}
 __device__ __forceinline__ uint4 lds128(uint32_t addr) {
     uint4 v;
     asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
@@ -87,6 +104,15 @@ __device__ __forceinline__ void pipe_init(TilePipe &P, uint8_t *stage0, uint32_t
 __device__ __forceinline__ void pipe_issue(TilePipe &P, int s, const CUtensorMap *map, int x_aligned, int y) {
     if ((threadIdx.x & 31) == 0) {
         mbar_expect_tx(&P.bar[s], P.bytes);
+        asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(
+                         P.buf[s]),
+                     "l"(map), "r"(x_aligned), "r"(y), "r"(smem_u32(&P.bar[s]))
+                     : "memory");
+    }
+}
+__device__ __forceinline__ void pipe_issue_bytes(TilePipe &P, int s, const CUtensorMap *map, int x_aligned, int y, uint32_t bytes) {
+    if ((threadIdx.x & 31) == 0) {
+        mbar_expect_tx(&P.bar[s], bytes);
         asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(
                          P.buf[s]),
                      "l"(map), "r"(x_aligned), "r"(y), "r"(smem_u32(&P.bar[s]))
