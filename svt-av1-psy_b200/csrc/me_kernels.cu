@@ -169,6 +169,7 @@ static void opt_in_shared_memory() {
     cudaGetDevice(&dev);
     if (done_for == dev) return;
     const int blk2 = SEARCH_WARPS * 2 * TM_L2_BUF + 128, blk1 = SEARCH_WARPS * 2 * TM_L1_BUF + 128, fp = FP_WARPS * 2 * TM_FP_BUF + 128;
+    cudaFuncSetAttribute(k_search16, cudaFuncAttributeMaxDynamicSharedMemorySize, SEARCH_WARPS * 2 * TM_S16_BUF + 128);
     cudaFuncSetAttribute(k_search_blk<true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, blk1);
     cudaFuncSetAttribute(k_search_blk<false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, blk1);
     cudaFuncSetAttribute(k_search_blk<true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, blk2);

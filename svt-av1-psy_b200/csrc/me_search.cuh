@@ -140,9 +140,98 @@ __device__ __forceinline__ void s16_tile_tasks(uint32_t buf, int pitch, uint32_t
     }
 }
 
+// Vertically blocked form for the common shape (16x16 block, rows two apart: 8 block rows): a lane takes G search
+// rows of the same parity (yy0, yy0+2, ...) of one octet. Search rows two apart read the same reference rows against
+// different source rows, so each reference row is loaded and funnel-shifted ONCE (7 LDS + 21 SHF) and feeds up to G
+// x 32 VABSDIFF4: 21 SHF per 128 SADs instead of per 32. Keys: (sad << 16 | yy << 8 | x), first minimum in raster
+// order. par0 / npar: first parity and number of parities searched (skip_search_line searches odd rows only).
+// G = 3: blocks of 6 search rows. Lanes then sit 6 rows apart (72 words at the 48-byte pitch of the tall tile = 8
+// banks): 4-way conflicts on the LDS.32, 28 cycles per reference row against ~58 of ALU work. With G = 4 lanes sit 8
+// rows apart = a multiple of 32 words for ANY pitch the TMA allows (multiples of 16 bytes): 16-way conflicts, measured
+// 30 % slower than no blocking at all.
+#define S16_VB_G 3
+template <int G>
+__device__ __forceinline__ void s16_tile_tasks_vb(uint32_t buf, int pitch, uint32_t src, uint32_t a, int tw, int th, int par0, int npar,
+                                                  uint32_t &best) {
+    const int lane  = threadIdx.x & 31;
+    const int n_oct = (tw + 7) >> 3;
+    const int n_tasks = n_oct * ((th + 2 * G - 1) / (2 * G)) * npar;
+    const uint32_t t8 = (a & 3u) * 8u;
+    for (int t = lane; t < n_tasks; t += 32) {
+        const int ch = t / n_oct, oct = t - ch * n_oct;
+        const int yy0 = npar == 2 ? (ch >> 1) * 2 * G + (ch & 1) : ch * 2 * G + par0;
+        if (yy0 >= th) continue;
+        uint32_t acc[G][8];
+#pragma unroll
+        for (int g = 0; g < G; g++)
+#pragma unroll
+            for (int p = 0; p < 8; p++) acc[g][p] = 0;
+        // word address of the octet's first byte (LDS.32: lanes 8 bytes apart, 2-way bank conflict, far below the ALU time)
+        uint32_t row = buf + (uint32_t)(yy0 * pitch) + ((a + 8u * (uint32_t)oct) & ~3u);
+        // a real loop over the reference rows (the source row each one meets is read from shared memory, a broadcast):
+        // unrolled it is ~1100 instructions and the kernel stalls on instruction fetch
+#pragma unroll 1
+        for (int k = 0; k < 8 + G - 1; k++, row += (uint32_t)(2 * pitch)) {
+            uint32_t c[7], w[6], s1[5], s2[5], s3[5];
+#pragma unroll
+            for (int i = 0; i < 7; i++) asm volatile("ld.shared.u32 %0, [%1];" : "=r"(c[i]) : "r"(row + 4u * i));
+#pragma unroll
+            for (int i = 0; i < 6; i++) w[i] = __funnelshift_r(c[i], c[i + 1], t8);
+#pragma unroll
+            for (int i = 0; i < 5; i++) {
+                s1[i] = __funnelshift_r(w[i], w[i + 1], 8);
+                s2[i] = __funnelshift_r(w[i], w[i + 1], 16);
+                s3[i] = __funnelshift_r(w[i], w[i + 1], 24);
+            }
+#pragma unroll
+            for (int g = 0; g < G; g++) {
+                const int rr = k - g; // block row this reference row meets for search row yy0 + 2g (warp-uniform)
+                if ((unsigned)rr < 8u) {
+                    const uint4 sv = lds128(src + 16u * (uint32_t)rr);
+                    const uint32_t s[4] = {sv.x, sv.y, sv.z, sv.w};
+#pragma unroll
+                    for (int i = 0; i < 4; i++) {
+                        acc[g][0] = sad4_acc(w[i], s[i], acc[g][0]);
+                        acc[g][4] = sad4_acc(w[i + 1], s[i], acc[g][4]);
+                        acc[g][1] = sad4_acc(s1[i], s[i], acc[g][1]);
+                        acc[g][5] = sad4_acc(s1[i + 1], s[i], acc[g][5]);
+                        acc[g][2] = sad4_acc(s2[i], s[i], acc[g][2]);
+                        acc[g][6] = sad4_acc(s2[i + 1], s[i], acc[g][6]);
+                        acc[g][3] = sad4_acc(s3[i], s[i], acc[g][3]);
+                        acc[g][7] = sad4_acc(s3[i + 1], s[i], acc[g][7]);
+                    }
+                }
+            }
+        }
+#pragma unroll
+        for (int g = 0; g < G; g++) {
+            const int yy = yy0 + 2 * g;
+            if (yy < th) {
+                const uint32_t idx = ((uint32_t)yy << 8) | (uint32_t)(8 * oct);
+#pragma unroll
+                for (int p = 0; p < 8; p++)
+                    if (8 * oct + p < tw) best = min(best, (acc[g][p] << 16) + idx + p);
+            }
+        }
+    }
+}
+
 // a: byte offset of the tile's position 0 inside its rows ((plane x of the position) & 15)
 __device__ inline unsigned long long warp_search16_tile(uint32_t buf, int pitch, uint32_t src, uint32_t a, int sa_w, int x0, int y0,
                                                         int tw, int th, int bw, int n_rows, int row_step, bool skip_lines) {
+    // blocked form only where it fills the warp: >= 24 (octet, chain) tasks and at most one partial block in four
+    const int vb_blocks = (th + 2 * S16_VB_G - 1) / (2 * S16_VB_G);
+    const bool vb_ok = ((tw + 7) >> 3) * vb_blocks * (skip_lines ? 1 : 2) >= 24 && (th % (2 * S16_VB_G) == 0 || vb_blocks >= 4);
+    if (bw == 16 && n_rows == 8 && row_step == 2 && vb_ok) {
+        uint32_t best = 0xffffffffu;
+        // skip_search_line drops the even rows of the WINDOW: parity is relative to y0
+        const int par0 = skip_lines ? ((y0 & 1) ? 0 : 1) : 0;
+        s16_tile_tasks_vb<S16_VB_G>(buf, pitch, src, a, tw, th, par0, skip_lines ? 1 : 2, best);
+        best = __reduce_min_sync(0xffffffffu, best);
+        if (best == 0xffffffffu || (best >> 16) >= 0xffffffu) return HME_KEY_NONE;
+        const uint32_t yy = (best >> 8) & 0xffu, x = best & 0xffu;
+        return ((unsigned long long)(best >> 16) << 32) | (uint32_t)((y0 + (int)yy) * sa_w + x0 + (int)x);
+    }
     uint32_t best_sad = 0xffffff, best_idx = 0xffffffffu;
     const uint32_t h8 = a >> 3, t8 = (a & 3u) * 8u;
     if (a & 4u) s16_tile_tasks<1>(buf, pitch, src, h8, t8, sa_w, x0, y0, tw, th, bw, n_rows, row_step, skip_lines, best_sad, best_idx);

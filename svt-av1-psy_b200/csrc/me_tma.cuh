@@ -24,17 +24,17 @@ enum { TM_L1 = 0, TM_L2 = 1, TM_FP = 2, TM_S16T = 3, TM_S16W = 4, TM_KINDS = 5 }
 #define TM_L2_BOX_H 67
 #define TM_FP_BOX_W 96
 #define TM_FP_BOX_H 71  /* 64 + 8 search rows - 1 */
-/* 1/16 plane, 16-wide blocks (pre-HME, HME level 0): a tall tile for windows up to 16 positions wide, a wide one otherwise.
+/* 1/16 plane, 16-wide blocks (pre-HME, HME level 0): a tall tile (16 x 96 positions) for windows up to 16 positions wide, a wide one otherwise.
    Rows are read with LDS.64 from the 8-byte boundary at or before a position: 8 * 17 + 32 = 168 > 160 never happens
    because the last octet of a wide tile starts at most 8 * 16 bytes in (8 * (1 + 15) + 32 = 160). */
 #define TM_S16T_BOX_W 48
 #define TM_S16T_BOX_H 111 /* 96 search rows + 15 block rows */
 #define TM_S16W_BOX_W 160
-#define TM_S16W_BOX_H 31  /* 16 search rows + 15 */
+#define TM_S16W_BOX_H 33  /* 18 search rows + 15 */
 #define S16T_TILE_W 16
 #define S16T_TILE_H 96
 #define S16W_TILE_W 128
-#define S16W_TILE_H 16
+#define S16W_TILE_H 18
 #define TM_BLK_TILE_W 16
 #define TM_BLK_TILE_H 4
 #define TM_FP_TILE_W 16
@@ -43,7 +43,7 @@ enum { TM_L1 = 0, TM_L2 = 1, TM_FP = 2, TM_S16T = 3, TM_S16W = 4, TM_KINDS = 5 }
 #define TM_L1_BUF TM_ALIGN128(TM_L1_BOX_W * TM_L1_BOX_H)
 #define TM_L2_BUF TM_ALIGN128(TM_L2_BOX_W * TM_L2_BOX_H)
 #define TM_FP_BUF TM_ALIGN128(TM_FP_BOX_W * TM_FP_BOX_H)
-#define TM_S16_BUF TM_ALIGN128(TM_S16T_BOX_W * TM_S16T_BOX_H) /* 5376 >= the wide box (4960) */
+#define TM_S16_BUF TM_ALIGN128(TM_S16T_BOX_W * TM_S16T_BOX_H) /* 5376 >= the wide box (5280) */
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t *bar, int count) {
