@@ -380,6 +380,22 @@ typedef struct SvtMeHmeState {
 } SvtMeHmeState;
 uint32_t svtme_fetch_hme_state(SvtMeSession *s, void *dst, size_t dst_bytes);
 
+/* --- 3b. Dynamic-GOP detector HME ---------------------------------------------------------
+   Replaces dg_detector_hme_level0 + early_hme_b64 (Codec/pd_process.c:392-589): for every b64 one svt_sad_loop_kernel
+   search of its 16x16 block of the 1/16 picture (FULL_SAD_SEARCH, window 16 / 64 / 128 square by input resolution,
+   :494-495) in the 1/16 picture of `ref_pic_id`, and the DGDetectorMetrics sums (Codec/pcs.h:696-702) over the picture.
+   Both pictures must have been uploaded. b64_sad / b64_mv (col, row per b64, 1/4-pel units as in the reference:
+   x4) may be NULL. Synchronous. */
+typedef struct SvtMeDgMetrics {
+    uint64_t tot_dist;        /* sum of the best SADs */
+    uint32_t tot_cplx;        /* b64s with SAD > 16*16*30 */
+    uint32_t tot_active;      /* b64s with a non-zero vector */
+    int32_t  sum_in_vectors;  /* inward minus outward pointing vector components */
+    uint32_t input_resolution; /* in: EbInputResolution class (0 = <=240p .. 6 = 8K); svtme_sig_deriv_me derives it */
+} SvtMeDgMetrics;
+uint32_t svtme_dg_detector_hme(SvtMeSession *s, int32_t src_pic_id, int32_t ref_pic_id, SvtMeDgMetrics *metrics,
+                               uint64_t *b64_sad, int16_t *b64_mv);
+
 /* sizeof() of the ABI structs as the library was compiled (0 SvtMeCtrls, 1 SvtMePicParams,
    2 SvtMeSearchResult, 3 SvtMeWindow, 4 SvtMePicResults, 5 SvtMeHmeState): binding self-check. */
 uint32_t svtme_abi_sizeof(int what);

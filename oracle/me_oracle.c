@@ -1258,3 +1258,73 @@ int orc_me_picture(const uint8_t *src_luma, const uint8_t *const ref_luma[2][4],
     free(x);
     return 0;
 }
+
+
+/* ====================================================================================== */
+/* Dynamic-GOP detector HME: dg_detector_hme_level0 + early_hme_b64, Codec/pd_process.c:392-589 */
+/* ====================================================================================== */
+int orc_dg_detector(const uint8_t *src_luma, const uint8_t *ref_luma, int width, int height, SvtMeDgMetrics *m,
+                    uint64_t *b64_sad, int16_t *b64_mv) {
+    if (!src_luma || !ref_luma || !m || width <= 0 || height <= 0 || (width & 7) || (height & 7)) return -1;
+    const int sw = width >> 2, sh = height >> 2, pad = ORC_SIXTEENTH_PAD, stride = sw + 2 * pad;
+    const size_t fb = (size_t)(width + 2 * ORC_FULL_PAD) * (height + 2 * ORC_FULL_PAD);
+    const size_t qb = (size_t)((width >> 1) + 2 * ORC_QUARTER_PAD) * ((height >> 1) + 2 * ORC_QUARTER_PAD);
+    const size_t sb = (size_t)stride * (sh + 2 * pad);
+    uint8_t *full = (uint8_t *)calloc(fb, 1), *quarter = (uint8_t *)calloc(qb, 1);
+    uint8_t *s16 = (uint8_t *)calloc(sb, 1), *r16 = (uint8_t *)calloc(sb, 1);
+    orc_build_planes(src_luma, width, height, full, quarter, s16);
+    orc_build_planes(ref_luma, width, height, full, quarter, r16);
+    /* :494-495: INPUT_SIZE_360p_RANGE = 1, INPUT_SIZE_480p_RANGE = 2 (definitions.h:2088-2090) */
+    const int16_t sa0 = m->input_resolution <= 1 ? 16 : m->input_resolution <= 2 ? 64 : 128;
+    const uint32_t cols = (uint32_t)(width + 63) / 64, rows = (uint32_t)(height + 63) / 64;
+    m->tot_dist = 0; m->tot_cplx = 0; m->tot_active = 0; m->sum_in_vectors = 0;
+    /* declared outside the b64 loops as in the reference (:499-500): svt_sad_loop_kernel resets best_sad but leaves the
+       centre untouched when nothing beats 0xffffff (cannot happen for a 16x16 8-bit block) */
+    uint64_t sad = ~0ull;
+    int16_t  col = 0, row = 0;
+    for (uint32_t by = 0; by < rows; by++) {
+        for (uint32_t bx = 0; bx < cols; bx++) {
+            /* early_hme_b64 :392-487, all in int16_t as there */
+            const int16_t org_x = (int16_t)(((int16_t)(bx * 64)) >> 2), org_y = (int16_t)(((int16_t)(by * 64)) >> 2);
+            int16_t sa_w = (int16_t)((sa0 + 7) & ~0x07), sa_h = sa0;
+            const int16_t pad_w = (int16_t)pad - 1, pad_h = (int16_t)pad - 1;
+            int16_t ox = (int16_t)(-(sa_w >> 1)), oy = (int16_t)(-(sa_h >> 1));
+            if ((org_x + ox) < -pad_w) { /* :424-427: origin reassigned first: the width is not reduced */
+                ox   = (int16_t)(-pad_w - org_x);
+                sa_w = (int16_t)(sa_w - (-pad_w - (org_x + ox)));
+            }
+            if ((org_x + ox) > (int16_t)sw - 1) ox = (int16_t)(ox - ((org_x + ox) - ((int16_t)sw - 1)));
+            if ((org_x + ox + sa_w) > (int16_t)sw) {
+                const int v = sa_w - ((org_x + ox + sa_w) - (int16_t)sw);
+                sa_w = (int16_t)(v > 1 ? v : 1);
+            }
+            sa_w = (int16_t)((sa_w < 8) ? sa_w : sa_w & ~0x07);
+            if ((org_y + oy) < -pad_h) {
+                oy   = (int16_t)(-pad_h - org_y);
+                sa_h = (int16_t)(sa_h - (-pad_h - (org_y + oy)));
+            }
+            if ((org_y + oy) > (int16_t)sh - 1) oy = (int16_t)(oy - ((org_y + oy) - ((int16_t)sh - 1)));
+            if ((org_y + oy + sa_h) > (int16_t)sh) {
+                const int v = sa_h - ((org_y + oy + sa_h) - (int16_t)sh);
+                sa_h = (int16_t)(v > 1 ? v : 1);
+            }
+            const int16_t x_tl = (int16_t)(((int16_t)pad + org_x) + ox), y_tl = (int16_t)(((int16_t)pad + org_y) + oy);
+            const uint8_t *src = s16 + (size_t)(pad + (by * 64 >> 2)) * stride + pad + (bx * 64 >> 2);
+            orc_sad_loop_kernel(src, (uint32_t)stride, r16 + (x_tl + y_tl * stride), (uint32_t)stride, 16, 16, &sad, &col, &row,
+                                (uint32_t)stride, 0, sa_w, sa_h);
+            col = (int16_t)(col + ox); col = (int16_t)(col * 4);
+            row = (int16_t)(row + oy); row = (int16_t)(row * 4);
+            m->tot_dist += sad;
+            m->tot_cplx += (sad > (16 * 16 * 30));
+            m->tot_active += ((abs(col) > 0) || (abs(row) > 0));
+            if (by < rows / 2) { if (row > 0) --m->sum_in_vectors; else if (row < 0) ++m->sum_in_vectors; }
+            else if (by > rows / 2) { if (row > 0) ++m->sum_in_vectors; else if (row < 0) --m->sum_in_vectors; }
+            if (bx < cols / 2) { if (col > 0) --m->sum_in_vectors; else if (col < 0) ++m->sum_in_vectors; }
+            else if (bx > cols / 2) { if (col > 0) ++m->sum_in_vectors; else if (col < 0) --m->sum_in_vectors; }
+            if (b64_sad) b64_sad[by * cols + bx] = sad;
+            if (b64_mv) { b64_mv[2 * (by * cols + bx)] = col; b64_mv[2 * (by * cols + bx) + 1] = row; }
+        }
+    }
+    free(full); free(quarter); free(s16); free(r16);
+    return 0;
+}

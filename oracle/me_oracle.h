@@ -84,6 +84,11 @@ void orc_initialize_buffer_32bits(uint32_t *pointer, uint32_t count128, uint32_t
 int orc_me_picture(const uint8_t *src_luma, const uint8_t *const ref_luma[2][4], int width, int height,
                    const SvtMePicParams *params, SvtMePicResults *res, OrcDebug *dbg, uint64_t *sad_ops);
 
+/* dg_detector_hme_level0, Codec/pd_process.c:392-589: metrics of one (source, reference) pair; m->input_resolution is
+   an input. b64_sad [n_b64] and b64_mv [n_b64][2] (col, row) are optional. */
+int orc_dg_detector(const uint8_t *src_luma, const uint8_t *ref_luma, int width, int height, SvtMeDgMetrics *m,
+                    uint64_t *b64_sad, int16_t *b64_mv);
+
 #ifdef __cplusplus
 }
 #endif

@@ -175,3 +175,21 @@ def ref_me_picture(pin, params=None, debug=False):
     if rc != 0:
         raise RuntimeError("ref_me_picture failed rc=%d" % rc)
     return res, dbg, sec.value
+
+
+def dg_detector(lib, prefix, src, ref, per_b64=False):
+    """dynamic-GOP detector metrics through `orc_dg_detector` (oracle) or `ref_dg_detector` (the reference's own code)"""
+    h, w = src.shape
+    m = abi.DgMetrics()
+    m.input_resolution = abi.input_resolution_of(w, h)
+    s, r = np.ascontiguousarray(src), np.ascontiguousarray(ref)
+    if prefix == "ref_":
+        rc = lib.ref_dg_detector(C.c_void_p(s.ctypes.data), C.c_void_p(r.ctypes.data), w, h, C.byref(m))
+        assert rc == 0
+        return m, None, None
+    n = abi.n_b64_of(w, h)
+    sad, mv = np.zeros(n, np.uint64), np.zeros((n, 2), np.int16)
+    rc = lib.orc_dg_detector(C.c_void_p(s.ctypes.data), C.c_void_p(r.ctypes.data), w, h, C.byref(m),
+                             C.c_void_p(sad.ctypes.data), C.c_void_p(mv.ctypes.data))
+    assert rc == 0
+    return m, sad, mv

@@ -631,3 +631,42 @@ int ref_me_picture(const RefMePicIn *in, SvtMePicResults *res, RefMeDebug *dbg, 
     fake_free(&f);
     return 0;
 }
+
+
+/* ---------------- dynamic-GOP detector HME (pd_process.c:392-589) ---------------- */
+void dg_detector_hme_level0(struct PictureParentControlSet *ppcs, uint32_t seg_idx); /* pd_process.c:490 */
+/* the detector takes a mutex per b64 and posts a semaphore at the end: single-threaded here */
+EbErrorType svt_block_on_mutex(EbHandle h) { (void)h; return EB_ErrorNone; }
+EbErrorType svt_release_mutex(EbHandle h) { (void)h; return EB_ErrorNone; }
+EbErrorType svt_post_semaphore(EbHandle h) { (void)h; return EB_ErrorNone; }
+
+int ref_dg_detector(const uint8_t *src_luma, const uint8_t *ref_luma, int width, int height, SvtMeDgMetrics *out) {
+    Planes ps, pr;
+    planes_alloc(&ps, src_luma, width, height);
+    planes_alloc(&pr, ref_luma, width, height);
+    set_rtcd(0);
+    SequenceControlSet      *scs  = (SequenceControlSet *)calloc(1, sizeof(*scs));
+    PictureParentControlSet *src  = (PictureParentControlSet *)calloc(1, sizeof(*src));
+    PictureParentControlSet *refp = (PictureParentControlSet *)calloc(1, sizeof(*refp));
+    EbObjectWrapper          ws, wr;
+    EbPaReferenceObject      os, orf;
+    DGDetectorSeg            dg;
+    memset(&ws, 0, sizeof(ws)); memset(&wr, 0, sizeof(wr)); memset(&os, 0, sizeof(os)); memset(&orf, 0, sizeof(orf));
+    memset(&dg, 0, sizeof(dg));
+    scs->b64_size = 64;
+    os.sixteenth_downsampled_picture_ptr  = &ps.sixteenth;
+    orf.sixteenth_downsampled_picture_ptr = &pr.sixteenth;
+    ws.object_ptr = &os; wr.object_ptr = &orf;
+    src->pa_ref_pic_wrapper = &ws; refp->pa_ref_pic_wrapper = &wr;
+    src->scs = scs; src->aligned_width = (uint16_t)width; src->aligned_height = (uint16_t)height;
+    src->input_resolution = derive_input_resolution((uint32_t)width * (uint32_t)height);
+    src->me_segments_column_count = 1; src->me_segments_row_count = 1; src->me_segments_total_count = 1;
+    src->dg_detector = &dg;
+    dg.ref_pic = refp;
+    dg_detector_hme_level0(src, 0);
+    out->tot_dist = dg.metrics.tot_dist; out->tot_cplx = dg.metrics.tot_cplx; out->tot_active = dg.metrics.tot_active;
+    out->sum_in_vectors = dg.metrics.sum_in_vectors; out->input_resolution = (uint32_t)src->input_resolution;
+    free(scs); free(src); free(refp);
+    planes_free(&ps); planes_free(&pr);
+    return 0;
+}

@@ -105,6 +105,9 @@ void ref_generate_padding(uint8_t *pic, uint32_t stride, uint32_t width, uint32_
 void ref_unpack_10bit_msb(const uint16_t *in16, uint32_t in_stride, uint8_t *out8,
                           uint32_t out_stride, uint32_t width, uint32_t height);
 
+/* dynamic-GOP detector metrics of one (source, reference) pair through the reference's dg_detector_hme_level0 */
+int ref_dg_detector(const uint8_t *src_luma, const uint8_t *ref_luma, int width, int height, SvtMeDgMetrics *out);
+
 #ifdef __cplusplus
 }
 #endif

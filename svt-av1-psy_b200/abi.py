@@ -112,6 +112,24 @@ class MeWindow(C.Structure):
     _fields_ = [("x_origin", C.c_int16), ("y_origin", C.c_int16), ("width", C.c_int16), ("height", C.c_int16)]
 
 
+class DgMetrics(C.Structure):
+    """SvtMeDgMetrics (include/svtme_b200.h): DGDetectorMetrics of pcs.h:696-702 + the resolution class as input"""
+    _fields_ = [("tot_dist", C.c_uint64), ("tot_cplx", C.c_uint32), ("tot_active", C.c_uint32),
+                ("sum_in_vectors", C.c_int32), ("input_resolution", C.c_uint32)]
+
+    def as_tuple(self):
+        return (self.tot_dist, self.tot_cplx, self.tot_active, self.sum_in_vectors)
+
+
+def input_resolution_of(width, height):
+    """EbInputResolution class (definitions.h:2088-2094, thresholds :2060-2066)"""
+    n = width * height
+    for cls, th in enumerate((0x28500, 0x4CE00, 0xA1400, 0x16DA00, 0x535200, 0x140A000)):
+        if n < th:
+            return cls
+    return 6
+
+
 class MePicResults(C.Structure):
     _fields_ = [
         ("p_sb_best_sad", C.c_void_p),

@@ -51,6 +51,8 @@ def lib():
         L.svtme_fetch_results.restype = C.c_uint32
         L.svtme_session_sync.argtypes = [C.c_void_p]
         L.svtme_session_sync.restype = C.c_uint32
+        L.svtme_dg_detector_hme.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.POINTER(abi.DgMetrics), C.c_void_p, C.c_void_p]
+        L.svtme_dg_detector_hme.restype = C.c_uint32
         L.svtme_session_batch_seq.argtypes = [C.c_void_p]
         L.svtme_session_batch_seq.restype = C.c_uint64
         L.svtme_session_wait_batch.argtypes = [C.c_void_p, C.c_uint64]
@@ -194,6 +196,17 @@ class Session:
 
     def sync(self):
         _check(lib().svtme_session_sync(self._h), "svtme_session_sync")
+
+    def dg_detector(self, src_pic_id, ref_pic_id, per_b64=True):
+        """dynamic-GOP detector HME of an uploaded (source, reference) pair -> (DgMetrics, sad[n_b64], mv[n_b64][2])"""
+        m = abi.DgMetrics()
+        m.input_resolution = abi.input_resolution_of(self.width, self.height)
+        n = abi.n_b64_of(self.width, self.height)
+        sad = np.zeros(n, np.uint64) if per_b64 else None
+        mv = np.zeros((n, 2), np.int16) if per_b64 else None
+        _check(lib().svtme_dg_detector_hme(self._h, src_pic_id, ref_pic_id, C.byref(m), sad.ctypes.data if per_b64 else None,
+                                           mv.ctypes.data if per_b64 else None), "svtme_dg_detector_hme")
+        return m, sad, mv
 
     def batch_seq(self):
         """sequence number (1, 2, ...) of the batch queued last"""

@@ -603,6 +603,60 @@ extern "C" uint32_t svtme_picture_me(SvtMeSession *s, int32_t pic_id, const SvtM
     return SVTME_OK;
 }
 
+// dg_detector_hme_level0 (pd_process.c:490-589) for one (source, reference) pair of uploaded pictures
+extern "C" uint32_t svtme_dg_detector_hme(SvtMeSession *s, int32_t src_pic_id, int32_t ref_pic_id, SvtMeDgMetrics *metrics,
+                                          uint64_t *b64_sad, int16_t *b64_mv) {
+    if (!s || !metrics || src_pic_id < 0 || src_pic_id >= s->max_pics || ref_pic_id < 0 || ref_pic_id >= s->max_pics ||
+        !s->pic_valid[src_pic_id] || !s->pic_valid[ref_pic_id])
+        return SVTME_ERR_BAD_PARAMETER;
+    std::lock_guard<std::mutex> g(s->mu);
+    CU_TRY(cudaSetDevice(s->device));
+    const int sa0 = metrics->input_resolution <= 1 ? 16 : metrics->input_resolution <= 2 ? 64 : 128; // :494-495
+    uint32_t rc = ensure_batch(s, 1);
+    if (rc != SVTME_OK) return rc;
+    const uint32_t need = svtme_dg_units_cap(sa0, s->n_b64);
+    if (need > s->s16_units_cap) {
+        rc = sync_all(s);
+        if (rc != SVTME_OK) return rc;
+        if (s->s16_units) cudaFree(s->s16_units);
+        s->s16_units = nullptr; s->s16_units_cap = 0;
+        if (cudaMalloc(&s->s16_units, (size_t)need * sizeof(uint2)) != cudaSuccess) return SVTME_ERR_INSUFFICIENT_RESOURCES;
+        s->s16_units_cap = need;
+    }
+    const uint64_t seq = ++s->batch_seq;
+    const int set = (int)(seq & 1);
+    if (s->dl_recorded[set]) CU_TRY(cudaStreamWaitEvent(s->stream, s->ev_dl[set], 0));
+    s->h_jobs.resize(1);
+    PicJob &job = s->h_jobs[0];
+    memset(&job, 0, sizeof(job));
+    job.pp.ctrls.hme_search_method = SVTME_FULL_SAD_SEARCH; // :501
+    job.dg_mode = 1;
+    job.src = s->pics[src_pic_id];
+    job.ref[0][0] = s->pics[ref_pic_id];
+    job.pic_w = s->w; job.pic_h = s->h; job.b64_cols = s->b64_cols; job.b64_rows = s->b64_rows; job.n_b64 = s->n_b64;
+    uint8_t *R = s->res_sets[set][0];
+    job.hme_jobs      = (HmeJobG *)(R + s->lay.hme_jobs);
+    job.s16_units     = s->s16_units;
+    job.s16_counters  = (uint32_t *)(s->res_slab + s->lay.fp_counters) + 4;
+    job.s16_units_cap = s->s16_units_cap;
+    CU_TRY(cudaMemcpyAsync(s->d_jobs, &job, sizeof(PicJob), cudaMemcpyHostToDevice, s->stream));
+    uint8_t *d_out = R + s->lay.ops + 32;
+    unsigned long long *d_sad = (unsigned long long *)(R + s->lay.best_sad);
+    int16_t *d_mv = (int16_t *)(R + s->lay.best_mv);
+    s->launches += (uint64_t)svtme_launch_dg_detector(&job, s->d_jobs, sa0, d_out, d_sad, d_mv, s->stream);
+    CU_TRY(cudaGetLastError());
+    CU_TRY(cudaEventRecord(s->ev_me[seq % 8], s->stream));
+    s->have_results = false; // the slab no longer holds ME results
+    struct { unsigned long long tot_dist; unsigned int tot_cplx, tot_active; int sum_in_vectors; } out;
+    CU_TRY(cudaMemcpyAsync(&out, d_out, sizeof(out), cudaMemcpyDeviceToHost, s->stream));
+    if (b64_sad) CU_TRY(cudaMemcpyAsync(b64_sad, d_sad, (size_t)s->n_b64 * 8, cudaMemcpyDeviceToHost, s->stream));
+    if (b64_mv) CU_TRY(cudaMemcpyAsync(b64_mv, d_mv, (size_t)s->n_b64 * 4, cudaMemcpyDeviceToHost, s->stream));
+    CU_TRY(cudaStreamSynchronize(s->stream));
+    metrics->tot_dist = out.tot_dist; metrics->tot_cplx = out.tot_cplx; metrics->tot_active = out.tot_active;
+    metrics->sum_in_vectors = out.sum_in_vectors;
+    return SVTME_OK;
+}
+
 extern "C" uint32_t svtme_session_enable_timing(SvtMeSession *s, int on) {
     if (!s) return SVTME_ERR_BAD_PARAMETER;
     std::lock_guard<std::mutex> g(s->mu);

@@ -85,8 +85,8 @@ struct PicJob {
     DevPic         src;
     DevPic         ref[2][4];
     int            pic_w, pic_h, b64_cols, b64_rows, n_b64, n_pus;
-    int            fullpel_phase; // 0: all refs, 1: only (0,0), 2: all but (0,0)
-    int            hme_smem_bytes, fp_smem_bytes;
+    int            dg_mode; // 1: dynamic-GOP detector search (16x16 blocks of the 1/16 plane whatever the picture edge, pd_process.c:532-533)
+    int            reserved_[2];
     // device buffers
     SbState       *sb_state;   // [n_b64]
     uint32_t      *best_sad;   // [n_b64][2][4][85]

@@ -188,6 +188,81 @@ static int next_pow2(int v) {
     return p;
 }
 
+// ------------------------------------------------------------------------------------------
+// dynamic-GOP detector HME (dg_detector_hme_level0 + early_hme_b64, pd_process.c:392-589)
+// ------------------------------------------------------------------------------------------
+struct DgOut { // device mirror of SvtMeDgMetrics' outputs
+    unsigned long long tot_dist;
+    unsigned int       tot_cplx, tot_active;
+    int                sum_in_vectors;
+};
+
+// one lane per b64: window of its 16x16 block (:410-455), job + tiles for k_search16
+__global__ void __launch_bounds__(128) k_dg_build(const PicJob *__restrict__ jobs, int sa0) {
+    const PicJob &job = jobs[0];
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= job.n_b64) return;
+    const B64Geo    g   = b64_geo(job, b);
+    const DevPlane &ref = job.ref[0][0].lvl[2];
+    HmeJobG &j = job.hme_jobs[(size_t)b * HME_JOBS_PER_B64];
+    int16_t sa_w = (int16_t)((sa0 + 7) & ~0x07), sa_h = (int16_t)sa0;
+    const int16_t ox = (int16_t)(-(sa_w >> 1)), oy = (int16_t)(-(sa_h >> 1));
+    ctl_make_job(j, ref, (int16_t)(g.org_x >> 2), (int16_t)(g.org_y >> 2), ox, oy, sa_w, sa_h, (int16_t)(ref.org_x - 1),
+                 (int16_t)(ref.org_y - 1), true, 16, 1);
+    ctl_enqueue_tiles(job, j, b * HME_JOBS_PER_B64);
+}
+
+// per-b64 result (:470-486) and the metrics (:540-575)
+__global__ void __launch_bounds__(128) k_dg_reduce(const PicJob *__restrict__ jobs, DgOut *out, unsigned long long *b64_sad,
+                                                   int16_t *b64_mv) {
+    const PicJob &job = jobs[0];
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= job.n_b64) return;
+    const HmeJobG &j = job.hme_jobs[(size_t)b * HME_JOBS_PER_B64];
+    uint64_t sad = 0;
+    int16_t  col = 0, row = 0;
+    ctl_job_result(j, false, 4, sad, col, row);
+    b64_sad[b] = sad;
+    b64_mv[2 * b] = col; b64_mv[2 * b + 1] = row;
+    const int bx = b % job.b64_cols, by = b / job.b64_cols, cols = job.b64_cols, rows = job.b64_rows;
+    int in = 0;
+    if (by < rows / 2) in += row > 0 ? -1 : (row < 0 ? 1 : 0);
+    else if (by > rows / 2) in += row > 0 ? 1 : (row < 0 ? -1 : 0);
+    if (bx < cols / 2) in += col > 0 ? -1 : (col < 0 ? 1 : 0);
+    else if (bx > cols / 2) in += col > 0 ? 1 : (col < 0 ? -1 : 0);
+    atomicAdd(&out->tot_dist, (unsigned long long)sad);
+    if (sad > 16 * 16 * 30) atomicAdd(&out->tot_cplx, 1u);
+    if (col != 0 || row != 0) atomicAdd(&out->tot_active, 1u);
+    if (in) atomicAdd(&out->sum_in_vectors, in);
+}
+
+uint32_t svtme_dg_units_cap(int sa0, int n_b64) {
+    int tw, th, ntx, nty, wide;
+    s16_tile_geometry((sa0 + 7) & ~7, sa0, &tw, &th, &ntx, &nty, &wide);
+    return (uint32_t)(ntx * nty * n_b64);
+}
+
+int svtme_launch_dg_detector(const PicJob *h_job, const PicJob *d_job, int sa0, void *d_out, unsigned long long *d_b64_sad,
+                             int16_t *d_b64_mv, cudaStream_t st) {
+    opt_in_shared_memory();
+    const int n_b64 = h_job->n_b64;
+    cudaMemsetAsync(h_job->s16_counters, 0, 2 * sizeof(uint32_t), st);
+    cudaMemsetAsync(d_out, 0, sizeof(DgOut), st);
+    k_dg_build<<<(n_b64 + 127) / 128, 128, 0, st>>>(d_job, sa0);
+    int n_sm = 148, dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
+    const size_t s16_smem = (size_t)SEARCH_WARPS * 2 * TM_S16_BUF + 128;
+    if (!g_s16_ctas_per_sm) {
+        int k = 0;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&k, k_search16, 32 * SEARCH_WARPS, s16_smem);
+        g_s16_ctas_per_sm = k > 0 ? k : 1;
+    }
+    k_search16<<<n_sm * g_s16_ctas_per_sm, 32 * SEARCH_WARPS, s16_smem, st>>>(d_job, 0);
+    k_dg_reduce<<<(n_b64 + 127) / 128, 128, 0, st>>>(d_job, (DgOut *)d_out, d_b64_sad, d_b64_mv);
+    return 3;
+}
+
 uint32_t svtme_s16_units_cap(const SvtMePicParams &pp, int n_b64) {
     const SvtMeCtrls &c = pp.ctrls;
     auto tiles_of = [&](int w, int h) {

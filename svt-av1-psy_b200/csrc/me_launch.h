@@ -12,6 +12,9 @@ struct PicJob;
 int  svtme_launch_build_pyramid(const DevPic &pic, int mode, const void *d_in, int in_stride, cudaStream_t st);
 int  svtme_launch_downsample_generic(const uint8_t *d_in, int in_stride, int in_w, int in_h, uint8_t *d_out, int out_stride,
                                      int step, cudaStream_t st);
+uint32_t svtme_dg_units_cap(int sa0, int n_b64);
+int  svtme_launch_dg_detector(const PicJob *h_job, const PicJob *d_job, int sa0, void *d_out, unsigned long long *d_b64_sad,
+                              int16_t *d_b64_mv, cudaStream_t st);
 uint32_t svtme_fp_units_cap(const SvtMePicParams &pp, int n_b64);
 uint32_t svtme_s16_units_cap(const SvtMePicParams &pp, int n_b64);
 int  svtme_launch_picture_me(const PicJob *h_jobs, int n, const PicJob *d_jobs, cudaStream_t st, cudaEvent_t ev_hme0,

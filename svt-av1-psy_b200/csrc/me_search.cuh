@@ -298,9 +298,10 @@ __global__ void __launch_bounds__(32 * SEARCH_WARPS) k_search16(const PicJob *__
                          un.wide ? TM_S16W_BOX_W * TM_S16W_BOX_H : TM_S16T_BOX_W * TM_S16T_BOX_H);
         const B64Geo g = b64_geo(job, b);
         const DevPlane &ss = job.src.lvl[2];
-        const int rows = sub ? (g.b64_h >> 2) >> 1 : (g.b64_h >> 2);
+        const int bh16 = job.dg_mode ? 16 : (g.b64_h >> 2);
+        const int rows = sub ? bh16 >> 1 : bh16;
         warp_stage_src16(smem_u32(s_src[warp][st]), ss.buf + (size_t)(ss.org_y + (g.org_y >> 2)) * ss.stride + ss.org_x + (g.org_x >> 2),
-                         ss.stride, row_step, rows, g.b64_w >> 2);
+                         ss.stride, row_step, rows, job.dg_mode ? 16 : (g.b64_w >> 2));
     };
     S16Unit cur = s16_fetch_unit(jobs, n_units);
     if (!cur.valid) return;
@@ -311,7 +312,8 @@ __global__ void __launch_bounds__(32 * SEARCH_WARPS) k_search16(const PicJob *__
         if (nxt.valid) issue(nxt, stage ^ 1);
         const PicJob &job = jobs[cur.pic];
         const B64Geo g = b64_geo(job, cur.slot / HME_JOBS_PER_B64);
-        const int bw = g.b64_w >> 2, rows = sub ? (g.b64_h >> 2) >> 1 : (g.b64_h >> 2);
+        const int bh16 = job.dg_mode ? 16 : (g.b64_h >> 2);
+        const int bw = job.dg_mode ? 16 : (g.b64_w >> 2), rows = sub ? bh16 >> 1 : bh16;
         const int ty = cur.tile / cur.n_tx, tx = cur.tile - ty * cur.n_tx;
         const int x0 = tx * cur.tile_w, y0 = ty * cur.tile_h;
         const bool skip = skip_cfg && bw == 16 && rows <= 16;

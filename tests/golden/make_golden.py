@@ -9,6 +9,7 @@ oracle/Makefile from /root/reference). Run in the development container only:
   me_<case>.npz           svt_aom_motion_estimation_b64 outputs of every b64 of one picture (MeSbResults,
                           PCS statistics, MeContext bests, HME state) for the cases of tests/util.py
   kat_rtcd.npz            outputs of the reference's C RTCD kernels for a thinned list of kat_cases.py
+  dg_detector.json        DGDetectorMetrics of dg_detector_hme_level0 (pd_process.c:490) for the pairs of test_dg_detector.py
 
 Inputs are NOT stored: they are regenerated from their seeds (numpy Generator streams are stable); the
 CRC32 of every input picture is stored so that a drifting generator fails loudly instead of silently.
@@ -69,6 +70,18 @@ def kat_fixture():
     print("kat_rtcd.npz:", len(out), "arrays")
 
 
+def dg_fixture():
+    import test_dg_detector as td
+    out = {}
+    for case in td.CASES:
+        src, ref = td.pair(case)
+        m, _, _ = po.dg_detector(po.ref_lib(), "ref_", src, ref)
+        out[td.key(case)] = list(m.as_tuple())
+    with open(os.path.join(HERE, "dg_detector.json"), "w") as f:
+        json.dump(out, f, indent=1, sort_keys=True)
+    print("dg_detector.json:", len(out), "pairs")
+
+
 def main():
     if not po.ref_available():
         po.build(ref=True)
@@ -79,6 +92,7 @@ def main():
     for name, geo, kw in EXTRA:
         picture_fixture(name, *extra_inputs(geo, kw))
     kat_fixture()
+    dg_fixture()
 
 
 if __name__ == "__main__":
