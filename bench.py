@@ -323,6 +323,20 @@ def run_ours(a):
     h2d_step, d2h_step = run.h2d // max(1, a.steps), run.d2h // max(1, a.steps)
     e2e = world * pics_e / (ms_e * 1e-3)
 
+    # ---- dynamic-GOP detector HME: pairs of resident pictures, metrics back to the host each call ----
+    dg_pairs = 64
+    run.sess.sync()
+    slots = sorted(run.resident.keys())
+    d0, d1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    for i in range(4):
+        run.sess.dg_detector(slots[i % len(slots)], slots[(i + 1) % len(slots)], per_b64=False)
+    d0.record()
+    for i in range(dg_pairs):
+        run.sess.dg_detector(slots[i % len(slots)], slots[(i + 3) % len(slots)], per_b64=False)
+    d1.record()
+    torch.cuda.synchronize()
+    dg_ms = d0.elapsed_time(d1) / dg_pairs
+
     if rank == 0:
         peaks = {}
         try:
@@ -368,6 +382,9 @@ def run_ours(a):
                              "peak_def": "64 lane-instr/clk/SM (ALU pipe, measured 57 VABS + 7 IADD) x 4 px x 148 SM x sampled SM clock"},
             "stage_ms_per_picture": {"k_hme": round(hme_ms / max(1, n_timed), 4), "k_fullpel": round(fp_ms / max(1, n_timed), 4)},
             "sad_gops": round((hme_ops + fp_ops) / (ms * 1e-3) / 1e9, 1),
+            "dg_detector": {"metric": "dynamic-GOP detector HME picture pairs/s (svtme_dg_detector_hme, synchronous, metrics to host)",
+                            "value": round(1e3 / dg_ms, 1), "ms_per_pair": round(dg_ms, 4),
+                            "sad_gops_nominal_window": round(n_b64 * 128 * 128 * 256 / (dg_ms * 1e-3) / 1e9, 1) if wl.w * wl.h >= 0xA1400 else None},
         }
         if not a.no_cpu_baseline and world == 1:
             line["cpu_baseline"] = cpu_baseline(wl, frames, a.cpu_baseline_pics)
