@@ -337,6 +337,27 @@ def run_ours(a):
     torch.cuda.synchronize()
     dg_ms = d0.elapsed_time(d1) / dg_pairs
 
+    # ---- temporal-filter ME: (centre, neighbour) pairs of resident pictures, batches of 32 ----
+    from svt_av1_psy_b200 import binding as _b
+    tf_level, tf_batches = 1, 6
+    tf_ids = [slots[i % len(slots)] for i in range(32)]
+    tf_prms = []
+    for i, sid in enumerate(tf_ids):
+        p = _b.sig_deriv_me_tf(wl.preset, wl.w, wl.h, tf_level, qp_opt=1, me_exit_th=0, qp=wl.qp, centre_poc=100 + i, ref_poc=99 + i)
+        p.ref_pic_id[0][0] = slots[(i + 1) % len(slots)]
+        tf_prms.append(p)
+    run.sess.me_batch(tf_ids, tf_prms, None, sync=True)
+    run.sess.sad_ops(reset=True)
+    t0e, t1e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0e.record()
+    for _ in range(tf_batches):
+        run.sess.me_batch(tf_ids, tf_prms, None, sync=False)
+    run.sess.sync()
+    t1e.record()
+    torch.cuda.synchronize()
+    tf_ms = t0e.elapsed_time(t1e) / (tf_batches * 32)
+    tf_ops = sum(run.sess.sad_ops(reset=True)) / (tf_batches * 32)
+
     if rank == 0:
         peaks = {}
         try:
@@ -382,6 +403,8 @@ def run_ours(a):
                              "peak_def": "64 lane-instr/clk/SM (ALU pipe, measured 57 VABS + 7 IADD) x 4 px x 148 SM x sampled SM clock"},
             "stage_ms_per_picture": {"k_hme": round(hme_ms / max(1, n_timed), 4), "k_fullpel": round(fp_ms / max(1, n_timed), 4)},
             "sad_gops": round((hme_ops + fp_ops) / (ms * 1e-3) / 1e9, 1),
+            "tf_me": {"metric": "temporal-filter ME (ME_MCTF, tf hme_me_level %d, FULL_SAD) picture pairs/s, resident" % tf_level,
+                      "value": round(1e3 / tf_ms, 1), "ms_per_pair": round(tf_ms, 4), "sad_gops": round(tf_ops / (tf_ms * 1e-3) / 1e9, 1)},
             "dg_detector": {"metric": "dynamic-GOP detector HME picture pairs/s (svtme_dg_detector_hme, synchronous, metrics to host)",
                             "value": round(1e3 / dg_ms, 1), "ms_per_pair": round(dg_ms, 4),
                             "sad_gops_nominal_window": round(n_b64 * 128 * 128 * 256 / (dg_ms * 1e-3) / 1e9, 1) if wl.w * wl.h >= 0xA1400 else None},

@@ -106,7 +106,13 @@ typedef struct SvtMeCtrls {
     uint32_t prev_me_stage_based_exit_th;
     int32_t  prune_me_candidates_th;
     uint8_t  use_best_unipred_cand_only;
+    /* the three bytes that used to be tail padding (sizeof stays 128) */
+    uint8_t  me_type;        /* SVTME_ME_OPEN_LOOP / SVTME_ME_MCTF (EbMeType, me_context.h): temporal-filter ME, SURVEY 8f row f1 */
+    uint16_t tf_me_exit_th;  /* me_ctx->tf_me_exit_th (uint16_t, me_context.h:495): MCTF skips the full-pel search of a b64 whose
+                                HME SAD is below it (motion_estimation.c:3179-3183) */
 } SvtMeCtrls;
+#define SVTME_ME_OPEN_LOOP 0
+#define SVTME_ME_MCTF 1
 
 /*
  * Per-picture launch parameters: the PictureParentControlSet / SequenceControlSet fields the
@@ -377,6 +383,8 @@ typedef struct SvtMeHmeState {
     uint8_t  do_ref[2][4];
     uint8_t  performed_phme[2][4][2];
     uint8_t  prehme_valid[2][4][2];
+    uint8_t  tf_exit;  /* ME_MCTF: the HME SAD of (0,0) was below tf_me_exit_th, no full-pel search (motion_estimation.c:3179-3183) */
+    uint8_t  pad_[7];
 } SvtMeHmeState;
 uint32_t svtme_fetch_hme_state(SvtMeSession *s, void *dst, size_t dst_bytes);
 

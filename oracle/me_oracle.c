@@ -780,7 +780,7 @@ static void integer_search_b64(Ctx *x) {
             if (x->sr[l][r].do_ref == 0) continue;
             int16_t xc = x->sr[l][r].hme_sc_x, yc = x->sr[l][r].hme_sc_y;
             int16_t sa_w = (int16_t)c->me_sa.sa_min.width, sa_h = (int16_t)c->me_sa.sa_min.height;
-            dist = scaled_dist(dist); /* me_type != ME_MCTF */
+            if (c->me_type != SVTME_ME_MCTF) dist = scaled_dist(dist); /* :1302-1304 */
             sa_w = (int16_t)ORC_MIN((sa_w * dist), c->me_sa.sa_max.width);
             sa_h = (int16_t)ORC_MIN((sa_h * dist), c->me_sa.sa_max.height);
             if (c->mv_sa_adj_enabled && (!c->mv_sa_adj_nearest_ref_only || r == 0)) {
@@ -1103,12 +1103,14 @@ static void init_me_hme_data(Ctx *x) {
     memset(x->performed_phme, 0, sizeof(x->performed_phme));
 }
 
-/* svt_aom_motion_estimation_b64, Codec/motion_estimation.c:3146-3223 (me_type == ME_OPEN_LOOP) */
-static void motion_estimation_b64(Ctx *x, SvtMePicResults *res, SbOut *o) {
+/* svt_aom_motion_estimation_b64, Codec/motion_estimation.c:3146-3223 (ME_OPEN_LOOP and ME_MCTF). Returns 1 when the
+   temporal-filter early exit skipped the full-pel search (:3179-3183): p_sb_best_* of this b64 are then not produced. */
+static int motion_estimation_b64(Ctx *x, SvtMePicResults *res, SbOut *o) {
     const SvtMePicParams *pp = x->pp;
     const SvtMeCtrls     *c  = x->c;
     const uint32_t n_lists = pp->num_of_list_to_search;
-    const uint8_t  prune_ref = c->enable_hme_flag; /* && me_type != ME_MCTF */
+    const int      mctf = c->me_type == SVTME_ME_MCTF;
+    const uint8_t  prune_ref = c->enable_hme_flag && !mctf; /* :3173 */
     init_me_hme_data(x);
     /* hme_b64 :2511-2545 */
     if (c->me_early_exit_th || c->me_safe_limit_zz_th) init_zz_sad(x);
@@ -1119,9 +1121,11 @@ static void motion_estimation_b64(Ctx *x, SvtMePicResults *res, SbOut *o) {
         if (c->enable_hme_level2_flag) hme_level2_b64(x);
     }
     set_final_search_centre(x);
+    if (mctf && x->sr[0][0].hme_sad < c->tf_me_exit_th) return 1;
     if (prune_ref) hme_prune_ref_and_adjust_sr(x);
     integer_search_b64(x);
     if (prune_ref && c->enable_me_hme_ref_pruning) me_prune_ref(x);
+    if (mctf) return 0; /* :3196: no candidate lists, statistics or GM flags for the temporal filter */
     if (pp->num_of_ref_pic_to_search[0] == 1 && pp->num_of_ref_pic_to_search[1] == 0)
         cand_single_ref(x, o);
     else if (pp->num_of_ref_pic_to_search[0] == 1 && pp->num_of_ref_pic_to_search[1] == 1)
@@ -1133,6 +1137,7 @@ static void motion_estimation_b64(Ctx *x, SvtMePicResults *res, SbOut *o) {
     if (pp->gm_enabled) gm_detection(x, o, &stationary, &allow_gm);
     if (res->stationary_block_present_sb) res->stationary_block_present_sb[x->b64_index] = stationary;
     if (res->rc_me_allow_gm) res->rc_me_allow_gm[x->b64_index] = allow_gm;
+    return 0;
 }
 
 static void pic_alloc(OrcPic *p, const uint8_t *luma, int w, int h, uint8_t *mem[3]) {
@@ -1199,12 +1204,12 @@ int orc_me_picture(const uint8_t *src_luma, const uint8_t *const ref_luma[2][4],
             memset(o.total, 0, n_pus);
             memset(o.mv, 0, (size_t)n_pus * params->max_refs * 4);
             memset(o.cand, 0, (size_t)n_pus * params->max_cand);
-            motion_estimation_b64(x, res, &o);
+            const int tf_exit = motion_estimation_b64(x, res, &o);
             for (int l = 0; l < 2; l++)
                 for (int r = 0; r < 4; r++) {
                     const size_t k        = ((size_t)b * 2 + (size_t)l) * 4 + (size_t)r;
                     const int    searched = l < params->num_of_list_to_search && r < params->num_of_ref_pic_to_search[l];
-                    const int    valid    = searched && x->sr[l][r].do_ref;
+                    const int    valid    = searched && x->sr[l][r].do_ref && !tf_exit;
                     for (int p = 0; p < 85; p++) {
                         if (res->p_sb_best_sad) res->p_sb_best_sad[k * 85 + (size_t)p] = valid ? x->best_sad[l][r][p] : 0;
                         if (res->p_sb_best_mv) res->p_sb_best_mv[k * 85 + (size_t)p] = valid ? x->best_mv[l][r][p] : 0;
@@ -1221,7 +1226,7 @@ int orc_me_picture(const uint8_t *src_luma, const uint8_t *const ref_luma[2][4],
                     }
                     if (res->me_windows) {
                         memset(&res->me_windows[k], 0, sizeof(SvtMeWindow));
-                        if (searched) res->me_windows[k] = x->win[l][r];
+                        if (searched && !tf_exit) res->me_windows[k] = x->win[l][r];
                     }
                 }
             if (dbg) {

@@ -193,3 +193,38 @@ def dg_detector(lib, prefix, src, ref, per_b64=False):
                              C.c_void_p(sad.ctypes.data), C.c_void_p(mv.ctypes.data))
     assert rc == 0
     return m, sad, mv
+
+
+class RefTfIn(C.Structure):
+    """RefTfIn of oracle/ref_harness.h"""
+    _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("enc_mode", C.c_int32), ("qp", C.c_int32),
+                ("tf_hme_me_level", C.c_int32), ("tf_qp_opt", C.c_int32), ("tf_me_exit_th", C.c_uint32),
+                ("temporal_layer_index", C.c_int32), ("is_ref", C.c_int32),
+                ("centre_picture_number", C.c_uint64), ("ref_picture_number", C.c_uint64),
+                ("centre_luma", C.c_void_p), ("ref_luma", C.c_void_p), ("simd", C.c_int32)]
+
+
+def ref_tf_me_picture(centre, ref, enc_mode, hme_me_level, qp_opt=0, me_exit_th=0, qp=35, centre_poc=8, ref_poc=7,
+                      temporal_layer=0, is_ref=1, simd=0, debug=True):
+    """temporal-filter ME of `centre` against `ref` through the reference's own code
+    -> (params, PicResultArrays, debug array)"""
+    h, w = centre.shape
+    tin = RefTfIn()
+    tin.width, tin.height, tin.enc_mode, tin.qp = w, h, enc_mode, qp
+    tin.tf_hme_me_level, tin.tf_qp_opt, tin.tf_me_exit_th = hme_me_level, qp_opt, me_exit_th
+    tin.temporal_layer_index, tin.is_ref = temporal_layer, is_ref
+    tin.centre_picture_number, tin.ref_picture_number = centre_poc, ref_poc
+    c8, r8 = np.ascontiguousarray(centre), np.ascontiguousarray(ref)
+    tin.centre_luma, tin.ref_luma, tin.simd = c8.ctypes.data, r8.ctypes.data, simd
+    params = abi.MePicParams()
+    tmp = abi.MePicParams()
+    tmp.enable_me_8x8, tmp.max_refs, tmp.max_cand = 1, 2, 3
+    res = abi.PicResultArrays(w, h, tmp)
+    dbg = np.zeros(res.n_b64, dtype=DEBUG_DTYPE) if debug else None
+    f = ref_lib().ref_tf_me_picture
+    f.argtypes = [C.POINTER(RefTfIn), C.POINTER(abi.MePicParams), C.POINTER(abi.MePicResults), C.c_void_p]
+    f.restype = C.c_int
+    rc = f(C.byref(tin), C.byref(params), C.byref(res.struct), ptr(dbg) if debug else None)
+    if rc != 0:
+        raise RuntimeError("ref_tf_me_picture failed rc=%d" % rc)
+    return params, res, dbg

@@ -670,3 +670,124 @@ int ref_dg_detector(const uint8_t *src_luma, const uint8_t *ref_luma, int width,
     planes_free(&ps); planes_free(&pr);
     return 0;
 }
+
+
+/* ---------------- temporal-filter ME (ME_MCTF) ---------------- */
+void svt_aom_sig_deriv_me_tf(PictureParentControlSet *pcs, MeContext *me_ctx); /* enc_mode_config.c:849 */
+
+static void dump_debug(RefMeDebug *d, const MeContext *me) {
+    memcpy(d->x_hme_l0, me->x_hme_level0_search_center, sizeof(d->x_hme_l0));
+    memcpy(d->y_hme_l0, me->y_hme_level0_search_center, sizeof(d->y_hme_l0));
+    memcpy(d->x_hme_l1, me->x_hme_level1_search_center, sizeof(d->x_hme_l1));
+    memcpy(d->y_hme_l1, me->y_hme_level1_search_center, sizeof(d->y_hme_l1));
+    memcpy(d->x_hme_l2, me->x_hme_level2_search_center, sizeof(d->x_hme_l2));
+    memcpy(d->y_hme_l2, me->y_hme_level2_search_center, sizeof(d->y_hme_l2));
+    memcpy(d->hme_l0_sad, me->hme_level0_sad, sizeof(d->hme_l0_sad));
+    memcpy(d->hme_l1_sad, me->hme_level1_sad, sizeof(d->hme_l1_sad));
+    memcpy(d->hme_l2_sad, me->hme_level2_sad, sizeof(d->hme_l2_sad));
+    for (int l = 0; l < 2; l++)
+        for (int r = 0; r < 4; r++) {
+            for (int s = 0; s < 2; s++) {
+                d->prehme_mv_x[l][r][s] = me->prehme_data[l][r][s].best_mv.as_mv.col;
+                d->prehme_mv_y[l][r][s] = me->prehme_data[l][r][s].best_mv.as_mv.row;
+                d->prehme_sad[l][r][s]  = me->prehme_data[l][r][s].sad;
+            }
+            d->zz_sad[l][r]               = me->zz_sad[l][r];
+            d->reduce_me_sr_divisor[l][r] = me->reduce_me_sr_divisor[l][r];
+        }
+}
+
+int ref_tf_me_picture(const RefTfIn *in, SvtMePicParams *params_out, SvtMePicResults *res, RefMeDebug *dbg) {
+    if (in->width % 8 || in->height % 8 || in->tf_hme_me_level < 0 || in->tf_hme_me_level > 4) return -1;
+    set_rtcd(in->simd);
+    RefMePicIn pin;
+    memset(&pin, 0, sizeof(pin));
+    pin.enc_mode = in->enc_mode; pin.width = in->width; pin.height = in->height; pin.qp = in->qp;
+    pin.pred_structure = 2; pin.hierarchical_levels = 5;
+    pin.temporal_layer_index = in->temporal_layer_index; pin.is_ref = in->is_ref;
+    pin.frame_rate = 30 << 16; pin.gm_level = -1;
+    pin.max_l0 = 1; pin.max_l1 = 1; pin.picture_number = in->centre_picture_number;
+    pin.num_lists = 1; pin.ref_count[0] = 1; pin.ref_picture_number[0][0] = in->ref_picture_number;
+    Fake f;
+    fake_init(&f, &pin);
+    PictureParentControlSet *pcs = f.pcs;
+    pcs->tf_ctrls.hme_me_level = (uint8_t)in->tf_hme_me_level;
+    pcs->tf_ctrls.qp_opt       = (uint8_t)in->tf_qp_opt;
+    pcs->tf_ctrls.me_exit_th   = in->tf_me_exit_th;
+    /* enc_mode_config.c:1832-1856 (svt_aom_sig_deriv_multi_processes) */
+    pcs->tf_enable_hme_flag        = 1;
+    pcs->tf_enable_hme_level0_flag = 1;
+    pcs->tf_enable_hme_level1_flag = in->tf_hme_me_level <= 2;
+    pcs->tf_enable_hme_level2_flag = in->tf_hme_me_level == 0;
+
+    Planes src, ref;
+    planes_alloc(&src, in->centre_luma, in->width, in->height);
+    planes_alloc(&ref, in->ref_luma, in->width, in->height);
+    MeContext *me = (MeContext *)calloc(1, sizeof(MeContext));
+    me->me_type   = ME_MCTF;
+    svt_aom_sig_deriv_me_tf(pcs, me); /* me_process.c:124 */
+
+    for (uint32_t y_b64 = 0; y_b64 < f.b64_h; y_b64++) {
+        for (uint32_t x_b64 = 0; x_b64 < f.b64_w; x_b64++) {
+            const uint32_t b64_index = x_b64 + y_b64 * f.b64_w, ox = x_b64 * 64, oy = y_b64 * 64;
+            EbPictureBufferDesc *ip = &src.full, *qp = &src.quarter, *sp = &src.sixteenth;
+            /* create_me_context_and_picture_control, temporal_filtering.c:288-343 */
+            me->me_type           = ME_MCTF;
+            me->hme_search_method = FULL_SAD_SEARCH;
+            me->b64_src_ptr       = &ip->buffer_y[(ip->org_y + oy) * ip->stride_y + ip->org_x + ox];
+            me->b64_src_stride    = ip->stride_y;
+            me->quarter_b64_buffer          = &qp->buffer_y[(qp->org_y + (oy >> 1)) * qp->stride_y + qp->org_x + (ox >> 1)];
+            me->quarter_b64_buffer_stride   = qp->stride_y;
+            me->sixteenth_b64_buffer        = &sp->buffer_y[(sp->org_y + (oy >> 2)) * sp->stride_y + sp->org_x + (ox >> 2)];
+            me->sixteenth_b64_buffer_stride = sp->stride_y;
+            /* temporal_filtering.c:3112-3140 */
+            me->num_of_list_to_search       = 1;
+            me->num_of_ref_pic_to_search[0] = 1;
+            me->num_of_ref_pic_to_search[1] = 0;
+            me->temporal_layer_index        = pcs->temporal_layer_index;
+            me->is_ref                      = pcs->is_ref;
+            me->me_ds_ref_array[0][0].picture_ptr           = &ref.full;
+            me->me_ds_ref_array[0][0].quarter_picture_ptr   = &ref.quarter;
+            me->me_ds_ref_array[0][0].sixteenth_picture_ptr = &ref.sixteenth;
+            me->me_ds_ref_array[0][0].picture_number        = in->ref_picture_number;
+            me->tf_me_exit_th             = (uint16_t)pcs->tf_ctrls.me_exit_th;
+            me->tf_use_pred_64x64_only_th = 0;
+            me->hme_l0_sa = me->hme_l0_sa_default_tf; /* set_hme_search_params_mctf(ctx, 0), :2752-2760 */
+            if (params_out && b64_index == 0) {
+                export_params(&pin, &f, me, params_out);
+                params_out->ctrls.me_type       = SVTME_ME_MCTF;
+                params_out->ctrls.tf_me_exit_th = me->tf_me_exit_th;
+                /* PCS-level fields of the open-loop stage that MCTF never reads (candidate lists, GM): the values
+                   svtme_sig_deriv_me_tf writes */
+                params_out->enable_me_8x8 = params_out->enable_me_16x16 = 1;
+                params_out->max_cand = 3; params_out->max_refs = 2; params_out->max_l0 = 1;
+                params_out->only_l_bwd = 0; params_out->similar_brightness_refs = 0;
+                params_out->gm_enabled = 0; params_out->gm_use_distance_based_active_th = 0;
+                params_out->hierarchical_levels = 5;
+            }
+            svt_aom_motion_estimation_b64(pcs, b64_index, ox, oy, me, ip);
+            const int exited = me->tf_use_pred_64x64_only_th == (uint8_t)~0; /* motion_estimation.c:3179-3183 */
+            if (res) {
+                const size_t o = (size_t)b64_index * 8;
+                for (int p = 0; p < 85; p++) {
+                    if (res->p_sb_best_sad) res->p_sb_best_sad[o * 85 + p] = exited ? 0 : me->p_sb_best_sad[0][0][p];
+                    if (res->p_sb_best_mv) res->p_sb_best_mv[o * 85 + p] = exited ? 0 : me->p_sb_best_mv[0][0][p];
+                }
+                if (res->search_results) {
+                    SvtMeSearchResult *sr = &res->search_results[o];
+                    memset(sr, 0, sizeof(*sr));
+                    sr->hme_sc_x = me->search_results[0][0].hme_sc_x;
+                    sr->hme_sc_y = me->search_results[0][0].hme_sc_y;
+                    sr->do_ref   = me->search_results[0][0].do_ref;
+                    sr->hme_sad  = me->search_results[0][0].hme_sad;
+                }
+            }
+            if (dbg) dump_debug(&dbg[b64_index], me);
+        }
+    }
+    free(me);
+    planes_free(&src);
+    planes_free(&ref);
+    fake_free(&f);
+    return 0;
+}

@@ -105,6 +105,21 @@ void ref_generate_padding(uint8_t *pic, uint32_t stride, uint32_t width, uint32_
 void ref_unpack_10bit_msb(const uint16_t *in16, uint32_t in_stride, uint8_t *out8,
                           uint32_t out_stride, uint32_t width, uint32_t height);
 
+/* Temporal-filter ME (ME_MCTF, temporal_filtering.c:3095-3146) of the centre picture against ONE neighbouring picture:
+   svt_aom_sig_deriv_me_tf + the per-block set-up of create_me_context_and_picture_control + svt_aom_motion_estimation_b64.
+   params_out (optional) receives the controls as the product's SvtMePicParams; res: p_sb_best_sad / p_sb_best_mv /
+   search_results (entries of b64s that took the HME early exit are zero). */
+typedef struct RefTfIn {
+    int32_t  width, height, enc_mode, qp;
+    int32_t  tf_hme_me_level, tf_qp_opt; /* pcs->tf_ctrls.hme_me_level (0..4), .qp_opt */
+    uint32_t tf_me_exit_th;              /* pcs->tf_ctrls.me_exit_th */
+    int32_t  temporal_layer_index, is_ref;
+    uint64_t centre_picture_number, ref_picture_number;
+    const uint8_t *centre_luma, *ref_luma;
+    int32_t  simd;
+} RefTfIn;
+int ref_tf_me_picture(const RefTfIn *in, SvtMePicParams *params_out, SvtMePicResults *res, RefMeDebug *dbg);
+
 /* dynamic-GOP detector metrics of one (source, reference) pair through the reference's dg_detector_hme_level0 */
 int ref_dg_detector(const uint8_t *src_luma, const uint8_t *ref_luma, int width, int height, SvtMeDgMetrics *out);
 

@@ -71,6 +71,8 @@ class MeCtrls(C.Structure):
         ("prev_me_stage_based_exit_th", C.c_uint32),
         ("prune_me_candidates_th", C.c_int32),
         ("use_best_unipred_cand_only", C.c_uint8),
+        ("me_type", C.c_uint8),
+        ("tf_me_exit_th", C.c_uint16),
     ]
 
 
@@ -166,7 +168,7 @@ HME_STATE_DTYPE = np.dtype([
     ("prehme_mv_x", "<i2", (2, 4, 2)), ("prehme_mv_y", "<i2", (2, 4, 2)), ("prehme_sad", "<u8", (2, 4, 2)),
     ("zz_sad", "<u4", (2, 4)), ("reduce_me_sr_divisor", "<u4", (2, 4)),
     ("hme_sc_x", "<i2", (2, 4)), ("hme_sc_y", "<i2", (2, 4)), ("sr_hme_sad", "<u8", (2, 4)), ("do_ref", "u1", (2, 4)),
-    ("performed_phme", "u1", (2, 4, 2)), ("prehme_valid", "u1", (2, 4, 2)),
+    ("performed_phme", "u1", (2, 4, 2)), ("prehme_valid", "u1", (2, 4, 2)), ("tf_exit", "u1"), ("pad_", "u1", (7,)),
 ], align=True)
 
 

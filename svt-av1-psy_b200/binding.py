@@ -109,6 +109,26 @@ def _check(code, what):
         raise SvtMeError(code, what)
 
 
+class SigDerivTfIn(C.Structure):
+    """SvtMeSigDerivTfIn (svt-av1-psy_b200/host/me_sig_deriv.h)"""
+    _fields_ = [("enc_mode", C.c_int32), ("width", C.c_int32), ("height", C.c_int32), ("qp", C.c_int32),
+                ("tf_hme_me_level", C.c_int32), ("tf_qp_opt", C.c_int32), ("tf_me_exit_th", C.c_uint32),
+                ("temporal_layer_index", C.c_int32), ("is_ref", C.c_int32),
+                ("centre_picture_number", C.c_uint64), ("ref_picture_number", C.c_uint64)]
+
+
+def sig_deriv_me_tf(enc_mode, width, height, hme_me_level, qp_opt=0, me_exit_th=0, qp=35, centre_poc=8, ref_poc=7,
+                    temporal_layer=0, is_ref=1):
+    """temporal-filter ME controls through the product's host C logic (svtme_sig_deriv_me_tf)"""
+    t = SigDerivTfIn(enc_mode, width, height, qp, hme_me_level, qp_opt, me_exit_th, temporal_layer, is_ref, centre_poc, ref_poc)
+    p = abi.MePicParams()
+    f = host_lib().svtme_sig_deriv_me_tf
+    f.argtypes = [C.POINTER(SigDerivTfIn), C.POINTER(abi.MePicParams)]
+    f.restype = C.c_uint32
+    _check(f(C.byref(t), C.byref(p)), "svtme_sig_deriv_me_tf")
+    return p
+
+
 class SigDerivIn(C.Structure):
     """SvtMeSigDerivIn of host/me_sig_deriv.h: the encoder-level inputs of svt_aom_sig_deriv_me."""
     _fields_ = [

@@ -428,7 +428,7 @@ static uint32_t launch_me_batch(SvtMeSession *s, uint32_t n, const int32_t *pic_
         if (a.enable_hme_flag != b.enable_hme_flag || a.enable_hme_level0_flag != b.enable_hme_level0_flag ||
             a.enable_hme_level1_flag != b.enable_hme_level1_flag || a.enable_hme_level2_flag != b.enable_hme_level2_flag ||
             a.prehme_enable != b.prehme_enable || a.hme_search_method != b.hme_search_method ||
-            a.me_search_method != b.me_search_method || a.prehme_skip_search_line != b.prehme_skip_search_line ||
+            a.me_search_method != b.me_search_method || a.prehme_skip_search_line != b.prehme_skip_search_line || a.me_type != b.me_type ||
             a.hme_l1_sa.width != b.hme_l1_sa.width || a.hme_l1_sa.height != b.hme_l1_sa.height ||
             a.hme_l2_sa.width != b.hme_l2_sa.width || a.hme_l2_sa.height != b.hme_l2_sa.height)
             return SVTME_ERR_BAD_PARAMETER;

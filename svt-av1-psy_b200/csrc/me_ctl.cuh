@@ -259,7 +259,9 @@ __global__ void __launch_bounds__(32 * CTL_WARPS) k_hme_ctl(const PicJob *__rest
                 st.hme_sc_y[ll][rr]   = scy;
                 st.sr_hme_sad[ll][rr] = hsad;
             }
-        if (c.enable_hme_flag) { // hme_prune_ref_and_adjust_sr :2547-2588 (loops over all [2][4])
+        const bool mctf = c.me_type == SVTME_ME_MCTF;
+        st.tf_exit = mctf && st.sr_hme_sad[0][0] < c.tf_me_exit_th; // :3179-3183
+        if (c.enable_hme_flag && !mctf) { // hme_prune_ref_and_adjust_sr :2547-2588 (loops over all [2][4]); never for MCTF (:3173)
             const uint16_t th = c.prune_ref_if_hme_sad_dev_bigger_than_th;
             if (c.enable_me_hme_ref_pruning && th != (uint16_t)~0) {
                 uint64_t best = ~0ull;

@@ -51,6 +51,8 @@ struct SbState {
     uint8_t  do_ref[2][4];
     uint8_t  performed_phme[2][4][2];
     uint8_t  prehme_valid[2][4][2];
+    uint8_t  tf_exit; // ME_MCTF: skip the full-pel search of this b64 (motion_estimation.c:3179-3183)
+    uint8_t  pad_[7];
 };
 
 // One window search of the HME stage (pre-HME region or HME level-N quadrant), set up by k_hme_ctl

@@ -164,7 +164,7 @@ __global__ void __launch_bounds__(32 * FP_WARPS) k_fp(const PicJob *__restrict__
     if (phase == 2 && !(l || r)) return;
     const SbState &st = job.sb_state[b];
     unsigned long long *gk = job.fp_keys + (size_t)u * 85;
-    if (!st.do_ref[l][r]) { // :1294-1295
+    if (!st.do_ref[l][r] || st.tf_exit) { // :1294-1295; temporal filter: HME was good enough (:3179-3183)
         if (lane == 0) { fj.active = 0; job.windows[u] = SvtMeWindow{0, 0, 0, 0}; }
         return;
     }
@@ -182,7 +182,7 @@ __global__ void __launch_bounds__(32 * FP_WARPS) k_fp(const PicJob *__restrict__
     // window sizing :1296-1366 (all lanes compute the same scalars; SADs are warp-cooperative)
     int16_t xc = st.hme_sc_x[l][r], yc = st.hme_sc_y[l][r];
     int16_t sa_w = (int16_t)c.me_sa.sa_min.width, sa_h = (int16_t)c.me_sa.sa_min.height;
-    const uint16_t dist = scaled_picture_distance(ref_distance(pp, l, r));
+    const uint16_t dist = c.me_type == SVTME_ME_MCTF ? ref_distance(pp, l, r) : scaled_picture_distance(ref_distance(pp, l, r)); // :1302-1304
     sa_w = (int16_t)imin((sa_w * dist), c.me_sa.sa_max.width);
     sa_h = (int16_t)imin((sa_h * dist), c.me_sa.sa_max.height);
     if (c.mv_sa_adj_enabled && (!c.mv_sa_adj_nearest_ref_only || r == 0)) {

@@ -66,12 +66,13 @@ __global__ void __launch_bounds__(POST_THREADS) k_post(const PicJob *__restrict_
         __syncthreads();
     }
 
+    const bool mctf = c.me_type == SVTME_ME_MCTF; // no pruning, candidate lists, statistics or GM flags (:3173, :3196)
     // ---- me_prune_ref ----
     if (tid < 8) {
         const int l = tid >> 2, r = tid & 3;
         uint64_t  h = st.sr_hme_sad[l][r];
         sh.do_ref[l][r] = st.do_ref[l][r];
-        if (c.enable_hme_flag && c.enable_me_hme_ref_pruning && l < n_lists_cfg && r < nref[l]) {
+        if (!mctf && c.enable_hme_flag && c.enable_me_hme_ref_pruning && l < n_lists_cfg && r < nref[l]) {
             h = 0;
             if (st.do_ref[l][r] == 0)
                 h = (uint64_t)(MAX_SAD_VALUE_U32 * 64u);
@@ -81,7 +82,7 @@ __global__ void __launch_bounds__(POST_THREADS) k_post(const PicJob *__restrict_
         sh.hme_sad[l][r] = h;
     }
     __syncthreads();
-    if (tid == 0 && c.enable_hme_flag && c.enable_me_hme_ref_pruning) {
+    if (tid == 0 && !mctf && c.enable_hme_flag && c.enable_me_hme_ref_pruning) {
         const uint16_t th = c.prune_ref_if_me_sad_dev_bigger_than_th;
         if (th != (uint16_t)~0) {
             uint64_t best = ~0ull;
@@ -99,6 +100,32 @@ __global__ void __launch_bounds__(POST_THREADS) k_post(const PicJob *__restrict_
     uint8_t  *o_total = job.total_me_candidate_index + (size_t)b * n_pus;
     uint32_t *o_mv    = job.me_mv_array + (size_t)b * n_pus * pp.max_refs;
     uint8_t  *o_cand  = job.me_candidate_array + (size_t)b * n_pus * pp.max_cand;
+    if (mctf) { // the temporal filter consumes p_sb_best_sad / p_sb_best_mv and SearchResults only
+        for (uint32_t i = tid; i < n_pus; i += POST_THREADS) o_total[i] = 0;
+        for (uint32_t i = tid; i < n_pus * pp.max_refs; i += POST_THREADS) o_mv[i] = 0;
+        for (uint32_t i = tid; i < n_pus * pp.max_cand; i += POST_THREADS) o_cand[i] = 0;
+        if (tid == 0) {
+            job.me_64x64_distortion[b] = job.me_32x32_distortion[b] = job.me_16x16_distortion[b] = job.me_8x8_distortion[b] = 0;
+            job.rc_me_distortion[b] = job.me_8x8_cost_variance[b] = 0;
+            job.stationary_block_present_sb[b] = 0;
+            job.rc_me_allow_gm[b]              = 0;
+        }
+        if (tid < 8) {
+            const int l = tid >> 2, r = tid & 3;
+            SvtMeSearchResult sr;
+            sr.hme_sc_x = 0; sr.hme_sc_y = 0; sr.do_ref = 0; sr.pad_[0] = sr.pad_[1] = sr.pad_[2] = 0; sr.hme_sad = 0;
+            if (l < n_lists_cfg && r < nref[l]) {
+                sr.hme_sc_x = st.hme_sc_x[l][r];
+                sr.hme_sc_y = st.hme_sc_y[l][r];
+                sr.do_ref   = sh.do_ref[l][r];
+                sr.hme_sad  = sh.hme_sad[l][r];
+            } else {
+                job.windows[(size_t)b * 8 + tid] = SvtMeWindow{0, 0, 0, 0};
+            }
+            job.search_results[(size_t)b * 8 + tid] = sr;
+        }
+        return;
+    }
     // the two special builders start from memset(total_me_candidate_index, 1, number_of_pus) (:2625, :2734)
     const uint8_t total_init = (nref[0] == 1 && nref[1] <= 1) ? 1 : 0;
     for (uint32_t i = tid; i < n_pus; i += POST_THREADS) o_total[i] = total_init;
@@ -289,7 +316,7 @@ __global__ void k_mask_unsearched(const PicJob *__restrict__ jobs) {
         const SvtMeSearchResult &sr = job.search_results[(size_t)b * 8 + lr];
         const int l = lr >> 2, r = lr & 3;
         const bool searched = l < job.pp.num_of_list_to_search && r < job.pp.num_of_ref_pic_to_search[l];
-        if (searched && sr.do_ref) continue;
+        if (searched && sr.do_ref && !job.sb_state[b].tf_exit) continue;
         for (int i = tid; i < 85; i += blockDim.x) {
             job.best_sad[((size_t)b * 8 + lr) * 85 + i] = 0;
             job.best_mv[((size_t)b * 8 + lr) * 85 + i]  = 0;

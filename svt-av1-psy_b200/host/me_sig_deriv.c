@@ -265,6 +265,68 @@ uint32_t svtme_sig_deriv_me(const SvtMeSigDerivIn *in, SvtMePicParams *out) {
     return SVTME_OK;
 }
 
+/* svt_aom_sig_deriv_me_tf, enc_mode_config.c:849-895 with tf_set_me_hme_params_oq :611-688 */
+uint32_t svtme_sig_deriv_me_tf(const SvtMeSigDerivTfIn *in, SvtMePicParams *out) {
+    if (!in || !out || in->width <= 0 || in->height <= 0 || (in->width & 7) || (in->height & 7) || in->tf_hme_me_level < 0 ||
+        in->tf_hme_me_level > 4)
+        return SVTME_ERR_BAD_PARAMETER;
+    memset(out, 0, sizeof(*out));
+    SvtMeCtrls *c   = &out->ctrls;
+    const int   m   = in->enc_mode, lvl = in->tf_hme_me_level;
+    const int   res = input_resolution((uint32_t)in->width * (uint32_t)in->height);
+    c->num_hme_sa_w = c->num_hme_sa_h = 2;
+    SvtMeSearchArea l0mn, l0mx, l1, l2, memn, memx;
+    switch (lvl) {
+    case 0: l0mn = SA(30, 30); l0mx = SA(60, 60); l1 = l2 = SA(16, 16); memn = SA(60, 60); memx = SA(120, 120); break;
+    case 1: l0mn = SA(16, 16); l0mx = SA(32, 32); l1 = l2 = SA(16, 16); memn = SA(16, 16); memx = SA(32, 32); break;
+    case 2:
+        if (res <= RES_360) { l0mn = SA(8, 8); l0mx = SA(8, 8); l1 = SA(8, 8); }
+        else if (res <= RES_480) { l0mn = SA(8, 8); l0mx = SA(16, 16); l1 = SA(8, 8); }
+        else { l0mn = SA(16, 16); l0mx = SA(32, 32); l1 = SA(16, 16); }
+        l2 = SA(16, 16); memn = memx = SA(8, 8);
+        break;
+    case 3: l0mn = l0mx = SA(8, 8); l1 = l2 = SA(8, 8); memn = memx = SA(8, 8); break;
+    default: l0mn = l0mx = SA(4, 4); l1 = l2 = SA(8, 8); memn = memx = SA(8, 8); break;
+    }
+    if (in->tf_qp_opt) { /* :679-687 */
+        const uint16_t qw = (uint16_t)CLIP3(250, 1000, (int)((8 * in->qp) - 125));
+        memn.width  = (uint16_t)MAXV(8, (memn.width * qw) / 1000);
+        memn.height = (uint16_t)MAXV(8, (memn.height * qw) / 1000);
+        memx.width  = (uint16_t)MAXV(8, (memx.width * qw) / 1000);
+        memx.height = (uint16_t)MAXV(8, (memx.height * qw) / 1000);
+    }
+    c->hme_l0_sa.sa_min = l0mn; c->hme_l0_sa.sa_max = l0mx; /* set_hme_search_params_mctf(ctx, 0): the defaults as they are */
+    c->hme_l1_sa = l1; c->hme_l2_sa = l2;
+    c->me_sa.sa_min = memn; c->me_sa.sa_max = memx;
+    /* :1832-1856 */
+    c->enable_hme_flag = c->enable_hme_level0_flag = 1;
+    c->enable_hme_level1_flag = lvl <= 2;
+    c->enable_hme_level2_flag = lvl == 0;
+    c->hme_search_method = SVTME_FULL_SAD_SEARCH; /* temporal_filtering.c:313, whatever the level */
+    c->me_search_method  = lvl <= 2 ? SVTME_FULL_SAD_SEARCH : SVTME_SUB_SAD_SEARCH; /* :859-869 */
+    prehme_ctrls(c, 0);
+    ref_prune_ctrls(c, 0);
+    sr_adjustment_ctrls(c, 0);
+    /* svt_aom_set_mv_based_sa_ctrls(0), svt_aom_set_me_8x8_var_ctrls(0): disabled = all zero */
+    c->me_early_exit_th            = (m <= 6 || res <= RES_720) ? 0 : 64 * 64 * 4; /* :884-886 */
+    c->prev_me_stage_based_exit_th = (m <= 7 || res <= RES_720) ? 0 : 64 * 64 * 4; /* :891-893 */
+    c->me_type       = SVTME_ME_MCTF;
+    c->tf_me_exit_th = (uint16_t)in->tf_me_exit_th; /* me_context.h:495 */
+    out->picture_number              = in->centre_picture_number;
+    out->num_of_list_to_search       = 1;
+    out->num_of_ref_pic_to_search[0] = 1;
+    out->temporal_layer_index        = (uint8_t)in->temporal_layer_index;
+    out->is_ref                      = (uint8_t)in->is_ref;
+    out->hierarchical_levels         = 5;
+    out->enable_me_8x8 = out->enable_me_16x16 = 1;
+    out->max_cand = 3; out->max_refs = 2; out->max_l0 = 1; /* unused by MCTF: sizes of the (empty) candidate arrays */
+    out->input_resolution = (uint8_t)res;
+    for (int l = 0; l < 2; l++)
+        for (int r = 0; r < 4; r++) out->ref_pic_id[l][r] = -1;
+    out->ref_picture_number[0][0] = in->ref_picture_number;
+    return SVTME_OK;
+}
+
 int32_t svtme_shard_owner(int64_t picture_number, int32_t mini_gop_size, int32_t stream, int32_t world_size) {
     if (world_size <= 1 || mini_gop_size <= 0) return 0;
     /* picture 0 (key frame) belongs to the first mini-GOP; pictures 1..N form mini-GOP 0, and so on */

@@ -36,6 +36,20 @@ typedef struct SvtMeSigDerivIn {
 
 uint32_t svtme_sig_deriv_me(const SvtMeSigDerivIn *in, SvtMePicParams *out);
 
+/* Temporal-filter ME controls (ME_MCTF): svt_aom_sig_deriv_me_tf + tf_set_me_hme_params_oq (enc_mode_config.c:611-688,
+   :849-895), the tf_enable_hme_* switch (:1832-1856), and what create_me_context_and_picture_control /
+   set_hme_search_params_mctf / the block loop set per block (temporal_filtering.c:288-343, :2752-2760, :3112-3140):
+   one list, one reference (the neighbouring picture being aligned to the centre picture), FULL_SAD HME. */
+typedef struct SvtMeSigDerivTfIn {
+    int32_t  enc_mode, width, height, qp;
+    int32_t  tf_hme_me_level; /* pcs->tf_ctrls.hme_me_level, 0..4 */
+    int32_t  tf_qp_opt;       /* pcs->tf_ctrls.qp_opt */
+    uint32_t tf_me_exit_th;   /* pcs->tf_ctrls.me_exit_th (stored in a uint16_t by the reference) */
+    int32_t  temporal_layer_index, is_ref; /* of the centre picture */
+    uint64_t centre_picture_number, ref_picture_number;
+} SvtMeSigDerivTfIn;
+uint32_t svtme_sig_deriv_me_tf(const SvtMeSigDerivTfIn *in, SvtMePicParams *out);
+
 /* Picture-level sharding of the ME stage over GPUs: mini-GOP g of a stream goes to
    rank (g + stream) % world; pictures inside a mini-GOP stay together so most refs are local. */
 int32_t svtme_shard_owner(int64_t picture_number, int32_t mini_gop_size, int32_t stream, int32_t world_size);

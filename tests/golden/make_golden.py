@@ -9,6 +9,7 @@ oracle/Makefile from /root/reference). Run in the development container only:
   me_<case>.npz           svt_aom_motion_estimation_b64 outputs of every b64 of one picture (MeSbResults,
                           PCS statistics, MeContext bests, HME state) for the cases of tests/util.py
   kat_rtcd.npz            outputs of the reference's C RTCD kernels for a thinned list of kat_cases.py
+  tf_me.npz               temporal-filter ME (ME_MCTF) controls and results of the cases of test_tf_me.py
   dg_detector.json        DGDetectorMetrics of dg_detector_hme_level0 (pd_process.c:490) for the pairs of test_dg_detector.py
 
 Inputs are NOT stored: they are regenerated from their seeds (numpy Generator streams are stable); the
@@ -82,6 +83,20 @@ def dg_fixture():
     print("dg_detector.json:", len(out), "pairs")
 
 
+def tf_fixture():
+    import test_tf_me as tt
+    out = {}
+    for case in tt.CASES:
+        w, h, m, lvl, qo, th, qp, cp, rp = case
+        centre, ref, _ = tt.inputs(case)
+        prm, res, _ = po.ref_tf_me_picture(centre, ref, m, lvl, qp_opt=qo, me_exit_th=th, qp=qp, centre_poc=cp, ref_poc=rp)
+        out[tt.key(case) + "/params"] = np.frombuffer(gl.struct_bytes(prm), np.uint8).copy()
+        for f in tt.TF_FIELDS:
+            out[tt.key(case) + "/" + f] = getattr(res, f)
+    np.savez_compressed(os.path.join(HERE, "tf_me.npz"), **out)
+    print("tf_me.npz:", len(tt.CASES), "cases")
+
+
 def main():
     if not po.ref_available():
         po.build(ref=True)
@@ -93,6 +108,7 @@ def main():
         picture_fixture(name, *extra_inputs(geo, kw))
     kat_fixture()
     dg_fixture()
+    tf_fixture()
 
 
 if __name__ == "__main__":
