@@ -47,8 +47,6 @@ __device__ inline void ctl_make_job(HmeJobG &j, const DevPlane &ref, int16_t org
     clamp_axis(org_y, origin_y, sa_h, pad_h, (int16_t)ref.height);
     const int16_t x_tl = (int16_t)(((int16_t)ref.org_x + org_x) + origin_x);
     const int16_t y_tl = (int16_t)(((int16_t)ref.org_y + org_y) + origin_y);
-    j.ref        = ref.buf + (x_tl + y_tl * ref.stride);
-    j.ref_stride = ref.stride;
     j.sa_w = sa_w; j.sa_h = sa_h; j.origin_x = origin_x; j.origin_y = origin_y;
     int tw, th, ntx, nty, wide;
     s16_tile_geometry(sa_w, sa_h, &tw, &th, &ntx, &nty, &wide);

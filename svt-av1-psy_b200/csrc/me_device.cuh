@@ -59,27 +59,23 @@ struct SbState {
 // and executed by k_search16 / k_search_wide. 32 jobs per b64: slot = (list*4+ref)*4 + quadrant
 // (pre-HME uses quadrant 0/1 for its two regions).
 struct HmeJobG {
-    const uint8_t     *ref;  // window top-left sample in the reference plane
     unsigned long long key;  // (sad << 32) | (y*sa_w + x), atomicMin over the job's tiles
-    int                ref_stride;
     int16_t            sa_w, sa_h, origin_x, origin_y;
     uint16_t           tile_w, tile_h; // positions per tile (tile_w multiple of 8)
-    uint8_t            n_tx, n_ty, active, wide; // wide: 1 = 128x16-position tiles, 0 = 16x96 (1/16-plane searches)
+    uint8_t            n_tx, n_ty, active, wide; // wide: 1 = 128x18-position tiles, 0 = 16x96 (1/16-plane searches)
     int16_t            px, py;                   // plane coordinates of the window's top-left sample
 };
 #define HME_JOBS_PER_B64 32
 #define HME_KEY_NONE ((0xffffffull << 32) | 0xffffffffull) /* best_sad = 0xffffff, nothing found */
 
-// Full-pel search of one (b64, list, ref), set up by k_fp_plan and executed by k_fp_search.
+// Full-pel search of one (b64, list, ref), set up by k_fp; windows of more than FP_INLINE_TILES tiles are finished by k_fp_big.
 struct FpJobG {
     int16_t  xc, yc;             // search centre (variance-probe position, scan index 0)
     int16_t  x_origin, y_origin; // window origin relative to the b64
     int16_t  sa_w, sa_h;
-    uint16_t n_tx, n_ty;         // tiles of FP_TILE_W x FP_TILE_H positions
+    uint16_t n_tx, n_ty;         // tiles of TM_FP_TILE_W x TM_FP_TILE_H positions (me_tma.cuh)
     uint8_t  active, probe, pad_[2];
 };
-#define FP_TILE_W 8
-#define FP_TILE_H 16
 
 // everything one picture's kernels need; passed by value as a __grid_constant__ parameter
 struct PicJob {

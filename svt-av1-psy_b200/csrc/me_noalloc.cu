@@ -24,7 +24,7 @@
 #include <cstdio>
 #include <mutex>
 
-#include "me_hme.cuh"
+#include "me_noalloc_search.cuh"
 #include "svtme_b200.h"
 
 #define NOALLOC_MAX_BANDS SVTME_NOALLOC_MAX_BANDS
