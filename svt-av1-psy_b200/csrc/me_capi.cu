@@ -254,10 +254,25 @@ static uint32_t sync_all(SvtMeSession *s) {
     return SVTME_OK;
 }
 
+// The unit queues are sized from the largest windows the controls allow; a kernel that finds one too small raises a
+// flag instead of dropping work silently. Checked at every synchronisation point.
+static uint32_t check_queue_overflow(SvtMeSession *s) {
+    uint32_t flag = 0;
+    CU_TRY(cudaMemcpyAsync(&flag, (uint32_t *)(s->res_slab + s->lay.fp_counters) + 8, sizeof(flag), cudaMemcpyDeviceToHost, s->stream));
+    CU_TRY(cudaStreamSynchronize(s->stream));
+    if (flag) {
+        fprintf(stderr, "[svtme_b200] a search-unit queue overflowed: results of the last batches are incomplete\n");
+        cudaMemsetAsync((uint32_t *)(s->res_slab + s->lay.fp_counters) + 8, 0, sizeof(flag), s->stream);
+        return SVTME_ERR_INSUFFICIENT_RESOURCES;
+    }
+    return SVTME_OK;
+}
+
 extern "C" uint32_t svtme_session_sync(SvtMeSession *s) {
     if (!s) return SVTME_ERR_BAD_PARAMETER;
     cudaSetDevice(s->device);
-    return sync_all(s);
+    uint32_t rc = sync_all(s);
+    return rc != SVTME_OK ? rc : check_queue_overflow(s);
 }
 
 extern "C" uint64_t svtme_session_batch_seq(SvtMeSession *s) { return s ? s->batch_seq : 0; }
@@ -638,6 +653,7 @@ extern "C" uint32_t svtme_dg_detector_hme(SvtMeSession *s, int32_t src_pic_id, i
     job.hme_jobs      = (HmeJobG *)(R + s->lay.hme_jobs);
     job.s16_units     = s->s16_units;
     job.s16_counters  = (uint32_t *)(s->res_slab + s->lay.fp_counters) + 4;
+    job.fp_counters   = (uint32_t *)(s->res_slab + s->lay.fp_counters);
     job.s16_units_cap = s->s16_units_cap;
     CU_TRY(cudaMemcpyAsync(s->d_jobs, &job, sizeof(PicJob), cudaMemcpyHostToDevice, s->stream));
     uint8_t *d_out = R + s->lay.ops + 32;

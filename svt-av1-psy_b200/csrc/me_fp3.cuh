@@ -346,6 +346,7 @@ __global__ void __launch_bounds__(32 * FP_WARPS) k_fp_big(const PicJob *__restri
     __shared__ __align__(8) uint64_t s_bar[FP_WARPS][2];
     const int warp = threadIdx.x >> 5;
     const uint32_t n_units = min(jobs[0].fp_counters[0], jobs[0].fp_units_cap); // the unit queue is shared by the batch
+    if (blockIdx.x == 0 && threadIdx.x == 0 && jobs[0].fp_counters[0] > jobs[0].fp_units_cap) jobs[0].fp_counters[8] = 1; // queue overflow: reported by the host
     if (n_units == 0) return;
     uint8_t *sbase = s_dyn + ((128u - (smem_u32(s_dyn) & 127u)) & 127u);
     TilePipe P;

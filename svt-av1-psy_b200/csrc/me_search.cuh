@@ -282,6 +282,7 @@ __global__ void __launch_bounds__(32 * SEARCH_WARPS) k_search16(const PicJob *__
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const PicJob &job0 = jobs[0];
     const uint32_t n_units = min(job0.s16_counters[0], job0.s16_units_cap);
+    if (blockIdx.x == 0 && threadIdx.x == 0 && job0.s16_counters[0] > job0.s16_units_cap) job0.fp_counters[8] = 1; // queue overflow: reported by the host
     if (n_units == 0) return;
     const bool sub = job0.pp.ctrls.hme_search_method == SVTME_SUB_SAD_SEARCH;
     const int row_step = sub ? 2 : 1;
