@@ -150,16 +150,12 @@ __global__ void __launch_bounds__(32 * FP_WARPS) k_fp(const PicJob *__restrict__
     __shared__ __align__(8) uint64_t s_bar[FP_WARPS][2];
     const PicJob &job = jobs[blockIdx.y];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int u = blockIdx.x * FP_WARPS + warp;
-    if (u >= job.n_b64 * 8) return;
-    const int b = u >> 3, l = (u >> 2) & 1, r = u & 3;
+    int b, l, r;
+    if (!compact_unit(job, blockIdx.x * FP_WARPS + warp, b, l, r)) return; // slots the picture does not have: k_post skips them
+    const int u = b * 8 + l * 4 + r;
     const SvtMePicParams &pp = job.pp;
     const SvtMeCtrls     &c  = pp.ctrls;
     FpJobG &fj = job.fp_jobs[u];
-    if (l >= pp.num_of_list_to_search || r >= pp.num_of_ref_pic_to_search[l]) {
-        if (lane == 0 && phase != 2) { fj.active = 0; job.windows[u] = SvtMeWindow{0, 0, 0, 0}; }
-        return;
-    }
     if (phase == 1 && (l || r)) return;
     if (phase == 2 && !(l || r)) return;
     const SbState &st = job.sb_state[b];

@@ -312,6 +312,7 @@ int svtme_launch_picture_me(const PicJob *h_jobs, int n, const PicJob *d_jobs, c
     const unsigned ny = (unsigned)n;
     const int ctl_grid = (n_b64 + CTL_WARPS - 1) / CTL_WARPS;
     bool any_zz = false, any_l1dep = false, any_dep = false, any_sr2 = false;
+    int  max_act = 1; // most (list, ref) combinations of a picture of the batch: sizes the grids of the per-(b64, list, ref) kernels
     for (int i = 0; i < n; i++) {
         const SvtMePicParams &pp = h_jobs[i].pp;
         const SvtMeCtrls     &ci = pp.ctrls;
@@ -319,12 +320,13 @@ int svtme_launch_picture_me(const PicJob *h_jobs, int n, const PicJob *d_jobs, c
         any_l1dep |= ci.prehme_enable && ci.prehme_l1_early_exit && pp.num_of_list_to_search == 2 && pp.temporal_layer_index > 0;
         any_dep |= ci.enable_me_sr_adjustment && ci.distance_based_hme_resizing && ci.reduce_hme_l0_sr_th_min && ci.reduce_hme_l0_sr_th_max;
         any_sr2 |= ci.enable_me_sr_adjustment == 2;
+        max_act = imax_h(max_act, pp.num_of_ref_pic_to_search[0] + (pp.num_of_list_to_search > 1 ? pp.num_of_ref_pic_to_search[1] : 0));
     }
     opt_in_shared_memory();
     if (ev_hme0) cudaEventRecord(ev_hme0, st);
     cudaMemsetAsync(j0.fp_counters, 0, 2 * sizeof(uint32_t), st);
     if (any_zz) {
-        k_zz<<<dim3((n_b64 * 8 + SEARCH_WARPS - 1) / SEARCH_WARPS, ny), 32 * SEARCH_WARPS, 0, st>>>(d_jobs);
+        k_zz<<<dim3((n_b64 * max_act + SEARCH_WARPS - 1) / SEARCH_WARPS, ny), 32 * SEARCH_WARPS, 0, st>>>(d_jobs);
         launches++;
     }
     bool first = true;
@@ -356,7 +358,7 @@ int svtme_launch_picture_me(const PicJob *h_jobs, int n, const PicJob *d_jobs, c
         launches++;
     };
     auto search_wide = [&](int level) {
-        const dim3 grid((n_b64 * 8 + SEARCH_WARPS - 1) / SEARCH_WARPS, ny);
+        const dim3 grid((n_b64 * max_act + SEARCH_WARPS - 1) / SEARCH_WARPS, ny);
         const size_t smem = (size_t)SEARCH_WARPS * 2 * (level == 1 ? TM_L1_BUF : TM_L2_BUF) + 128;
         if (level == 1) {
             if (sub) k_search_blk<true, 1><<<grid, 32 * SEARCH_WARPS, smem, st>>>(d_jobs);
@@ -424,7 +426,7 @@ int svtme_launch_picture_me(const PicJob *h_jobs, int n, const PicJob *d_jobs, c
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&k, k_fp_big<true>, 32 * FP_WARPS, fp_smem);
         g_fp_search_ctas_per_sm = k > 0 ? k : 1;
     }
-    const dim3 plan_grid((n_b64 * 8 + FP_WARPS - 1) / FP_WARPS, ny);
+    const dim3 plan_grid((n_b64 * max_act + FP_WARPS - 1) / FP_WARPS, ny);
     const int big_grid = n_sm * g_fp_search_ctas_per_sm;
     auto fp_round = [&](int phase) {
         if (fsub) {

@@ -43,6 +43,7 @@ __global__ void __launch_bounds__(POST_THREADS) k_post(const PicJob *__restrict_
         const bool sub = c.me_search_method == SVTME_SUB_SAD_SEARCH;
         for (int i = tid; i < 8 * 85; i += POST_THREADS) {
             const int lr = i / 85, pu = i - lr * 85;
+            if ((lr >> 2) >= n_lists_cfg || (lr & 3) >= nref[lr >> 2]) continue; // a slot the picture does not have
             const FpJobG &fj = job.fp_jobs[(size_t)b * 8 + lr];
             if (!fj.active) continue; // not searched: the mirrors keep stale data, as in the reference
             const unsigned long long k = job.fp_keys[((size_t)b * 8 + lr) * 85 + pu];

@@ -31,6 +31,20 @@ __device__ __forceinline__ B64Geo b64_geo(const PicJob &job, int b) {
     return g;
 }
 
+// Warps are handed only the (b64, list, ref) combinations the picture has: compact unit uc -> b64 and slot
+// u = b64 * 8 + list * 4 + ref. (Mapping warps to all 8 slots left half of every CTA idle while it kept its shared memory.)
+__device__ __forceinline__ bool compact_unit(const PicJob &job, int uc, int &b, int &l, int &r) {
+    const SvtMePicParams &pp = job.pp;
+    const int n0 = pp.num_of_ref_pic_to_search[0], n1 = pp.num_of_list_to_search > 1 ? pp.num_of_ref_pic_to_search[1] : 0;
+    const int na = n0 + n1;
+    if (na <= 0 || uc >= job.n_b64 * na) return false;
+    b = uc / na;
+    const int k = uc - b * na;
+    l = k >= n0 ? 1 : 0;
+    r = l ? k - n0 : k;
+    return true;
+}
+
 __device__ __forceinline__ unsigned long long warp_min_u64(unsigned long long key) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
@@ -61,11 +75,9 @@ __device__ inline uint32_t warp_nxm_sad2(const uint8_t *src, int src_stride, con
 // ---- k_zz ------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(32 * SEARCH_WARPS) k_zz(const PicJob *__restrict__ jobs) {
     const PicJob &job = jobs[blockIdx.y];
-    const int u = blockIdx.x * SEARCH_WARPS + (threadIdx.x >> 5);
-    if (u >= job.n_b64 * 8) return;
-    const int b = u >> 3, l = (u >> 2) & 1, r = u & 3;
+    int b, l, r;
+    if (!compact_unit(job, blockIdx.x * SEARCH_WARPS + (threadIdx.x >> 5), b, l, r)) return;
     const SvtMePicParams &pp = job.pp;
-    if (l >= pp.num_of_list_to_search || r >= pp.num_of_ref_pic_to_search[l]) return;
     if (!(pp.temporal_layer_index > 0 || l == 0)) return;
     const B64Geo    g  = b64_geo(job, b);
     const DevPlane &sf = job.src.lvl[0], &rf = job.ref[l][r].lvl[0];
@@ -388,12 +400,12 @@ __global__ void __launch_bounds__(32 * SEARCH_WARPS) k_search_blk(const PicJob *
     __shared__ __align__(8) uint64_t s_bar[SEARCH_WARPS][2];
     const PicJob &job = jobs[blockIdx.y];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int u = blockIdx.x * SEARCH_WARPS + warp; // (b64, list, ref)
-    if (u >= job.n_b64 * 8) return;
+    int b, l, r;
+    if (!compact_unit(job, blockIdx.x * SEARCH_WARPS + warp, b, l, r)) return;
+    const int u = b * 8 + l * 4 + r; // (b64, list, ref)
     HmeJobG *jq = job.hme_jobs + (size_t)u * 4;
     // lanes 0..3 hold the four quadrant jobs
     int my_act = 0, my_px = 0, my_py = 0, my_sw = 0, my_sh = 0;
-    const int b = u >> 3, l = (u >> 2) & 1, r = u & 3;
     const DevPic   &rp = job.ref[l][r];
     if (lane < 4) {
         const HmeJobG &j = jq[lane];
