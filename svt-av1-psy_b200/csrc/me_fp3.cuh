@@ -51,8 +51,10 @@ __device__ __forceinline__ void fp_lane_init(FpLane<SUB> &L, const uint8_t *src_
 }
 
 // one pass: 8 positions starting beta bytes into tile row `row_base`; idx0 = key index of the first, nv = how many exist
+// raw (optional): this lane's left / right 8x8 sums and the 64x64 sum of the FIRST position (the variance probe)
 template <bool SUB>
-__device__ __forceinline__ void fp_eval_pass(FpLane<SUB> &L, uint32_t row_base, uint32_t beta, uint32_t idx0, int nv) {
+__device__ __forceinline__ void fp_eval_pass(FpLane<SUB> &L, uint32_t row_base, uint32_t beta, uint32_t idx0, int nv,
+                                             uint32_t *raw = nullptr) {
     constexpr int NR = FpLane<SUB>::NR;
     uint32_t accl[8], accr[8];
     tile_pass<4, NR, true>(L.T, row_base, beta, accl, accr);
@@ -88,6 +90,11 @@ __device__ __forceinline__ void fp_eval_pass(FpLane<SUB> &L, uint32_t row_base, 
     if (p32 < nv) {
         L.k32 = min(L.k32, (t32 << FP_IDX_BITS) + idx0 + p32);
         L.k64 = min(L.k64, (t64 << FP_IDX_BITS) + idx0 + p32);
+    }
+    if (raw) {
+        raw[0] = accl[0];
+        raw[1] = accr[0];
+        raw[2] = __shfl_sync(0xffffffffu, t64, 0); // lane 0 holds position 0 after the halving exchanges
     }
 }
 
@@ -231,10 +238,10 @@ __global__ void __launch_bounds__(32 * FP_WARPS) k_fp(const PicJob *__restrict__
     fp_lane_init<SUB>(L, src_full, sf.stride, 64, 64); // the full-pel stage always works on 64x64 (padded source)
     if (probe) { // :1393-1441: one position at the search centre, then the variance of its 64 8x8 SADs
         pipe_wait(P, 0);
-        uint32_t raw[5];
-        fp_eval_one<SUB>(L, P.buf[0] + 4u * TM_FP_BOX_W, (uint32_t)(ptx & 15) + 8u, 0u, raw);
+        uint32_t raw[3];
+        fp_eval_pass<SUB>(L, P.buf[0] + 4u * TM_FP_BOX_W, (uint32_t)(ptx & 15) + 8u, 0u, 1, raw);
         const uint32_t dbl  = SUB ? 1 : 0;
-        const uint32_t mean = (raw[4] << dbl) / 64;
+        const uint32_t mean = (raw[2] << dbl) / 64;
         const int32_t  dl = (int32_t)(raw[0] << dbl) - (int32_t)mean, dr = (int32_t)(raw[1] << dbl) - (int32_t)mean;
         uint32_t sumsq = (uint32_t)(dl * dl) + (uint32_t)(dr * dr);
 #pragma unroll
@@ -265,22 +272,29 @@ __global__ void __launch_bounds__(32 * FP_WARPS) k_fp(const PicJob *__restrict__
     const int rx = wx - ptx, ry = wy - pty;           // ... relative to the probe tile
     const bool in_probe_tile = probe && rx >= 0 && ry >= 0 && rx + sa_w <= TM_FP_TILE_W && ry + sa_h <= TM_FP_TILE_H;
     const bool inline_scan = in_probe_tile || n_tiles <= FP_INLINE_TILES;
-    if (in_probe_tile) {
-        fp_scan_rect<SUB>(L, P.buf[0], (uint32_t)(ptx & 15), rx, ry, sa_w, sa_h, 1u, (uint32_t)sa_w);
-    } else if (inline_scan) {
+    // one loop, one call site of the scan (code size): the probe tile when it covers the window, else the window's tiles
+    if (inline_scan) {
         __syncwarp();
-        int stage = 1; // stage 0 may still be read by slow lanes of the probe pass; __syncwarp above orders it anyway
-        pipe_issue(P, stage, map, wx & ~15, wy);
-        for (int t = 0; t < n_tiles; t++) {
+        int stage = in_probe_tile ? 0 : 1;
+        if (!in_probe_tile) pipe_issue(P, stage, map, wx & ~15, wy);
+        const int n_iter = in_probe_tile ? 1 : n_tiles;
+        for (int t = 0; t < n_iter; t++) {
             const int ty = t / ntx, tx = t - ty * ntx;
-            if (t + 1 < n_tiles) {
-                const int ty1 = (t + 1) / ntx, tx1 = (t + 1) - ty1 * ntx;
-                pipe_issue(P, stage ^ 1, map, (wx + TM_FP_TILE_W * tx1) & ~15, wy + TM_FP_TILE_H * ty1);
+            uint32_t a = (uint32_t)(ptx & 15), idx_base = 1u;
+            int ox = rx, oy = ry, nx = sa_w, ny = sa_h;
+            if (!in_probe_tile) {
+                if (t + 1 < n_tiles) {
+                    const int ty1 = (t + 1) / ntx, tx1 = (t + 1) - ty1 * ntx;
+                    pipe_issue(P, stage ^ 1, map, (wx + TM_FP_TILE_W * tx1) & ~15, wy + TM_FP_TILE_H * ty1);
+                }
+                pipe_wait(P, stage);
+                a = (uint32_t)((wx + TM_FP_TILE_W * tx) & 15);
+                ox = oy = 0;
+                nx = imin(TM_FP_TILE_W, sa_w - TM_FP_TILE_W * tx);
+                ny = imin(TM_FP_TILE_H, sa_h - TM_FP_TILE_H * ty);
+                idx_base = 1u + (uint32_t)(TM_FP_TILE_H * ty * sa_w + TM_FP_TILE_W * tx);
             }
-            pipe_wait(P, stage);
-            fp_scan_rect<SUB>(L, P.buf[stage], (uint32_t)((wx + TM_FP_TILE_W * tx) & 15), 0, 0, imin(TM_FP_TILE_W, sa_w - TM_FP_TILE_W * tx),
-                              imin(TM_FP_TILE_H, sa_h - TM_FP_TILE_H * ty), 1u + (uint32_t)(TM_FP_TILE_H * ty * sa_w + TM_FP_TILE_W * tx),
-                              (uint32_t)sa_w);
+            fp_scan_rect<SUB>(L, P.buf[stage], a, ox, oy, nx, ny, idx_base, (uint32_t)sa_w);
             __syncwarp();
             stage ^= 1;
         }
