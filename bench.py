@@ -158,6 +158,7 @@ class Runner:
         self.h2d = self.d2h = 0
         self.pics = 0
         self.host_batches = 0
+        self.pending = {}
         self.probe = "full"
 
     def params(self, plan):
@@ -183,21 +184,31 @@ class Runner:
         return p
 
     def ensure(self, poc, host):
+        """queue the upload of picture `poc` unless its slot already holds it (flushed by one batched call per step)"""
         slot = poc % self.N_SLOTS
         if self.resident.get(slot) == poc:
             return
         f = poc % self.wl.n_frames
         if host and self.probe == "d2h":
-            self.sess.upload_device(slot, self.frames_dev[f].data_ptr(), self.wl.w)
+            kind, ptr = "device", self.frames_dev[f].data_ptr()
         elif host and self.frames16 is not None:
-            self.sess.upload_ptr16(slot, self.frames16[f].data_ptr(), self.wl.w)
+            kind, ptr = "host10", self.frames16[f].data_ptr()
             self.h2d += 2 * self.wl.w * self.wl.h
         elif host:
-            self.sess.upload_ptr(slot, self.frames_pinned[f].data_ptr(), self.wl.w)
+            kind, ptr = "host8", self.frames_pinned[f].data_ptr()
             self.h2d += self.wl.w * self.wl.h
         else:
-            self.sess.upload_device(slot, self.frames_dev[f].data_ptr(), self.wl.w)
+            kind, ptr = "device", self.frames_dev[f].data_ptr()
+        self.pending.setdefault(kind, ([], []))
+        self.pending[kind][0].append(slot)
+        self.pending[kind][1].append(ptr)
         self.resident[slot] = poc
+
+    def flush_uploads(self):
+        for kind, (ids, ptrs) in self.pending.items():
+            for i in range(0, len(ids), 32):
+                self.sess.upload_batch(ids[i:i + 32], ptrs[i:i + 32], self.wl.w, kind)
+        self.pending = {}
 
     def step(self, step_index, host):
         """ME of the mini-GOP this rank owns at `step_index` (mini-GOP m = step*world + rank): upload its
@@ -217,6 +228,7 @@ class Runner:
                 prm = self.params_cache[poc] = self.params(plan)
             ids.append(slot_of(poc, self))
             prms.append(prm)
+        self.flush_uploads()
         if host:
             if self.results is None:
                 # two sets of pinned result arrays: batch k's downloads overlap batch k+1's uploads and kernels

@@ -302,6 +302,15 @@ uint32_t svtme_picture_upload_10bit(SvtMeSession *s, int32_t pic_id, const uint1
 uint32_t svtme_picture_upload_device(SvtMeSession *s, int32_t pic_id, const uint8_t *d_luma,
                                      uint32_t stride);
 
+/* The same uploads for several pictures at once (n <= 40): the pyramids of all of them are built by two kernel
+   launches. Host frames may have any pitch; device frames must be dense (stride == width). */
+uint32_t svtme_picture_upload_batch(SvtMeSession *s, uint32_t n, const int32_t *pic_ids, const uint8_t *const *luma,
+                                    uint32_t stride);
+uint32_t svtme_picture_upload_10bit_batch(SvtMeSession *s, uint32_t n, const int32_t *pic_ids,
+                                          const uint16_t *const *luma16, uint32_t stride_in_samples);
+uint32_t svtme_picture_upload_device_batch(SvtMeSession *s, uint32_t n, const int32_t *pic_ids,
+                                           const uint8_t *const *d_luma, uint32_t stride);
+
 /* Run open-loop ME of picture pic_id against params->ref_pic_id[][] and copy the requested
    result arrays to host (asynchronously on the session stream; call svtme_session_sync, or
    pass sync=1). */

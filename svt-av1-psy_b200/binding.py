@@ -186,6 +186,18 @@ class Session:
     def upload_device(self, pic_id, dev_ptr, stride):
         _check(lib().svtme_picture_upload_device(self._h, pic_id, dev_ptr, stride), "svtme_picture_upload_device")
 
+    def upload_batch(self, pic_ids, ptrs, stride, kind="host8"):
+        """several pictures at once (two kernel launches for all their pyramids). kind: host8 / host10 / device;
+        ptrs: raw addresses (pinned host memory or device memory)"""
+        n = len(pic_ids)
+        ids = (C.c_int32 * n)(*pic_ids)
+        pp = (C.c_void_p * n)(*ptrs)
+        fn = {"host8": lib().svtme_picture_upload_batch, "host10": lib().svtme_picture_upload_10bit_batch,
+              "device": lib().svtme_picture_upload_device_batch}[kind]
+        fn.argtypes = [C.c_void_p, C.c_uint32, C.POINTER(C.c_int32), C.POINTER(C.c_void_p), C.c_uint32]
+        fn.restype = C.c_uint32
+        _check(fn(self._h, n, ids, pp, stride), "svtme_picture_upload_*_batch")
+
     def me(self, pic_id, params, results=None, sync=True):
         results = results if results is not None else abi.PicResultArrays(self.width, self.height, params)
         _check(lib().svtme_picture_me(self._h, pic_id, C.byref(params), C.byref(results.struct), 1 if sync else 0),

@@ -353,6 +353,56 @@ extern "C" uint32_t svtme_picture_upload_10bit(SvtMeSession *s, int32_t pic_id, 
     return finish_upload(s, pic_id, 2, staged, s->w, true);
 }
 
+// Batched uploads: the pyramids of n pictures are built by two launches instead of 2n.
+static uint32_t upload_batch(SvtMeSession *s, uint32_t n, const int32_t *pic_ids, const void *const *src, size_t row_bytes,
+                             size_t host_pitch, int mode, bool host) {
+    if (!s || !pic_ids || !src || n == 0 || n > SVTME_STAGE_FRAMES) return SVTME_ERR_BAD_PARAMETER;
+    for (uint32_t i = 0; i < n; i++)
+        if (pic_ids[i] < 0 || pic_ids[i] >= s->max_pics || !src[i]) return SVTME_ERR_BAD_PARAMETER;
+    std::lock_guard<std::mutex> g(s->mu);
+    CU_TRY(cudaSetDevice(s->device));
+    std::vector<DevPic>       pics(n);
+    std::vector<const void *> in(n);
+    std::vector<int>          ring(n, -1);
+    for (uint32_t i = 0; i < n; i++) {
+        pics[i] = s->pics[pic_ids[i]];
+        if (host) {
+            void *staged = nullptr;
+            uint32_t rc = stage_host_frame(s, src[i], row_bytes, host_pitch, &staged);
+            if (rc != SVTME_OK) return rc;
+            in[i] = staged;
+            ring[i] = s->stage_last;
+        } else {
+            in[i] = src[i];
+        }
+    }
+    s->launches += (uint64_t)svtme_launch_build_pyramids(pics.data(), in.data(), s->w, (int)n, mode, s->stream);
+    CU_TRY(cudaGetLastError());
+    for (uint32_t i = 0; i < n; i++) {
+        if (host) CU_TRY(cudaEventRecord(s->ev_ingested[ring[i]], s->stream));
+        s->pic_valid[pic_ids[i]] = 1;
+    }
+    return SVTME_OK;
+}
+
+extern "C" uint32_t svtme_picture_upload_batch(SvtMeSession *s, uint32_t n, const int32_t *pic_ids, const uint8_t *const *luma,
+                                               uint32_t stride) {
+    if (!s || stride < (uint32_t)s->w) return SVTME_ERR_BAD_PARAMETER;
+    return upload_batch(s, n, pic_ids, (const void *const *)luma, (size_t)s->w, stride, 0, true);
+}
+
+extern "C" uint32_t svtme_picture_upload_10bit_batch(SvtMeSession *s, uint32_t n, const int32_t *pic_ids,
+                                                     const uint16_t *const *luma16, uint32_t stride_in_samples) {
+    if (!s || stride_in_samples < (uint32_t)s->w) return SVTME_ERR_BAD_PARAMETER;
+    return upload_batch(s, n, pic_ids, (const void *const *)luma16, (size_t)s->w * 2, (size_t)stride_in_samples * 2, 2, true);
+}
+
+extern "C" uint32_t svtme_picture_upload_device_batch(SvtMeSession *s, uint32_t n, const int32_t *pic_ids,
+                                                      const uint8_t *const *d_luma, uint32_t stride) {
+    if (!s || stride != (uint32_t)s->w) return SVTME_ERR_BAD_PARAMETER; // dense device frames only
+    return upload_batch(s, n, pic_ids, (const void *const *)d_luma, 0, 0, 0, false);
+}
+
 extern "C" uint32_t svtme_picture_download_plane(SvtMeSession *s, int32_t pic_id, int level, uint8_t *dst, size_t dst_capacity,
                                                  uint32_t *stride, uint32_t *rows, uint32_t *org_x, uint32_t *org_y) {
     if (!s || !dst || pic_id < 0 || pic_id >= s->max_pics || level < 0 || level > 2 || !s->pic_valid[pic_id]) return SVTME_ERR_BAD_PARAMETER;

@@ -1,5 +1,6 @@
 // me_kernels.cu — kernel definitions and their host-side launchers (sm_100a only).
 #include <cuda.h>
+#include <cstring>
 #include "me_launch.h"
 
 #include "me_device.cuh"
@@ -20,8 +21,24 @@
 // out = (a + b + c + d + 2) >> 2 per 2x2 box, the sixteenth plane from the ROUNDED quarter samples
 // (pic_operators.c:338-384 applied twice, pic_analysis_process.c:131-161).
 // MODE 0: 8-bit input in `in`; 1: interior already in place; 2: 16-bit input.
+// Up to INGEST_BATCH pictures per launch (blockIdx.z / blockIdx.y = picture): the jobs travel as a kernel parameter.
+#define INGEST_BATCH 32
+struct IngestJob {
+    DevPic      pic;
+    const void *in;
+    int         in_stride; // samples
+    int         pad_;
+};
+struct IngestBatch {
+    IngestJob j[INGEST_BATCH];
+};
+
 template <int MODE>
-__global__ void __launch_bounds__(256) k_ingest(const void *in, int in_stride /*samples*/, DevPic pic) {
+__global__ void __launch_bounds__(256) k_ingest(const __grid_constant__ IngestBatch batch) {
+    const IngestJob &job = batch.j[blockIdx.z];
+    const DevPic &pic = job.pic;
+    const void *in = job.in;
+    const int in_stride = job.in_stride;
     const DevPlane &f = pic.lvl[0], &q = pic.lvl[1], &s = pic.lvl[2];
     const int px = blockIdx.x * blockDim.x + threadIdx.x, py = blockIdx.y * blockDim.y + threadIdx.y;
     const int x = 8 * px, y = 4 * py;
@@ -79,7 +96,8 @@ __global__ void __launch_bounds__(256) k_ingest(const void *in, int in_stride /*
 // Replicate padding of the three planes in one launch: every padded sample is the interior sample at the
 // clamped coordinate. A thread writes one aligned 4-byte group; only groups that hold padding are enumerated
 // (top band, bottom band, then the left and right bands of the interior rows), level after level.
-__global__ void __launch_bounds__(256) k_pad_planes(DevPic pic) {
+__global__ void __launch_bounds__(256) k_pad_planes(const __grid_constant__ IngestBatch batch) {
+    const DevPic &pic = batch.j[blockIdx.y].pic;
     int i = blockIdx.x * blockDim.x + threadIdx.x;
 #pragma unroll
     for (int lv = 0; lv < 3; lv++) {
@@ -132,21 +150,38 @@ __global__ void k_downsample_generic(const uint8_t *in, int in_stride, int in_w,
 
 static inline dim3 grid2d(int w, int h, int bx) { return dim3((unsigned)((w + bx - 1) / bx), (unsigned)h, 1); }
 
-// mode 0: 8-bit device input, 1: the full-resolution interior is already in the plane, 2: 16-bit device input
-int svtme_launch_build_pyramid(const DevPic &pic, int mode, const void *d_in, int in_stride, cudaStream_t st) {
-    const DevPlane &f = pic.lvl[0];
-    const dim3 blk(32, 8), grid((unsigned)((f.width / 8 + 31) / 32), (unsigned)((f.height / 4 + 7) / 8));
-    if (mode == 0) k_ingest<0><<<grid, blk, 0, st>>>(d_in, in_stride, pic);
-    else if (mode == 1) k_ingest<1><<<grid, blk, 0, st>>>(nullptr, 0, pic);
-    else k_ingest<2><<<grid, blk, 0, st>>>(d_in, in_stride, pic);
-    long long groups = 0;
-    for (int lv = 0; lv < 3; lv++) {
-        const DevPlane &p = pic.lvl[lv];
-        const int W4 = (p.width + 2 * p.org_x + 3) >> 2;
-        groups += 2LL * p.org_x * W4 + (long long)p.height * ((p.org_x >> 2) + W4 - ((p.org_x + p.width) >> 2));
+// mode 0: 8-bit device input, 1: the full-resolution interior is already in the plane, 2: 16-bit device input.
+// All pictures of a call share the mode and the geometry (one session).
+int svtme_launch_build_pyramids(const DevPic *pics, const void *const *d_in, int in_stride, int n, int mode, cudaStream_t st) {
+    int launches = 0;
+    for (int base = 0; base < n; base += INGEST_BATCH) {
+        const int m = n - base < INGEST_BATCH ? n - base : INGEST_BATCH;
+        IngestBatch b;
+        memset(&b, 0, sizeof(b));
+        for (int i = 0; i < m; i++) {
+            b.j[i].pic = pics[base + i];
+            b.j[i].in = d_in ? d_in[base + i] : nullptr;
+            b.j[i].in_stride = in_stride;
+        }
+        const DevPlane &f = pics[base].lvl[0];
+        const dim3 blk(32, 8), grid((unsigned)((f.width / 8 + 31) / 32), (unsigned)((f.height / 4 + 7) / 8), (unsigned)m);
+        if (mode == 0) k_ingest<0><<<grid, blk, 0, st>>>(b);
+        else if (mode == 1) k_ingest<1><<<grid, blk, 0, st>>>(b);
+        else k_ingest<2><<<grid, blk, 0, st>>>(b);
+        long long groups = 0;
+        for (int lv = 0; lv < 3; lv++) {
+            const DevPlane &p = pics[base].lvl[lv];
+            const int W4 = (p.width + 2 * p.org_x + 3) >> 2;
+            groups += 2LL * p.org_x * W4 + (long long)p.height * ((p.org_x >> 2) + W4 - ((p.org_x + p.width) >> 2));
+        }
+        k_pad_planes<<<dim3((unsigned)((groups + 255) / 256), (unsigned)m), 256, 0, st>>>(b);
+        launches += 2;
     }
-    k_pad_planes<<<(unsigned)((groups + 255) / 256), 256, 0, st>>>(pic);
-    return 2;
+    return launches;
+}
+
+int svtme_launch_build_pyramid(const DevPic &pic, int mode, const void *d_in, int in_stride, cudaStream_t st) {
+    return svtme_launch_build_pyramids(&pic, &d_in, in_stride, 1, mode, st);
 }
 
 int svtme_launch_downsample_generic(const uint8_t *d_in, int in_stride, int in_w, int in_h, uint8_t *d_out,

@@ -10,6 +10,7 @@ struct PicJob;
 
 // every launcher returns the number of kernels it launched on `st`
 int  svtme_launch_build_pyramid(const DevPic &pic, int mode, const void *d_in, int in_stride, cudaStream_t st);
+int  svtme_launch_build_pyramids(const DevPic *pics, const void *const *d_in, int in_stride, int n, int mode, cudaStream_t st);
 int  svtme_launch_downsample_generic(const uint8_t *d_in, int in_stride, int in_w, int in_h, uint8_t *d_out, int out_stride,
                                      int step, cudaStream_t st);
 uint32_t svtme_dg_units_cap(int sa0, int n_b64);

@@ -179,3 +179,24 @@ def test_pipelined_batches_equal_synchronous_ones():
     for ba, bb in zip(a, b):
         for ra, rb in zip(ba, bb):
             compare(ra, rb, fields=list(ra.FIELDS))
+
+
+def test_batched_uploads_build_the_same_pyramids():
+    """svtme_picture_upload_batch / _10bit_batch / _device_batch: two launches for all pictures, same planes"""
+    import torch
+    rng = np.random.default_rng(12)
+    w, h, n = 200, 72, 5
+    frames = [rng.integers(0, 256, (h, w), dtype=np.uint8) for _ in range(n)]
+    frames10 = [(f.astype(np.uint16) << 2) | rng.integers(0, 4, f.shape, dtype=np.uint16) for f in frames]
+    s = me.Session(w, h, max_pictures=3 * n)
+    s.upload_batch(list(range(n)), [f.ctypes.data for f in frames], w, "host8")
+    s.upload_batch(list(range(n, 2 * n)), [f.ctypes.data for f in frames10], w, "host10")
+    dev = [torch.from_numpy(f).cuda() for f in frames]
+    torch.cuda.synchronize()
+    s.upload_batch(list(range(2 * n, 3 * n)), [d.data_ptr() for d in dev], w, "device")
+    for i, f in enumerate(frames):
+        want = planes_oracle(f)
+        for lvl in range(3):
+            for slot in (i, n + i, 2 * n + i):
+                np.testing.assert_array_equal(s.download_plane(slot, lvl), want[lvl], err_msg="picture %d slot %d level %d" % (i, slot, lvl))
+    s.close()
