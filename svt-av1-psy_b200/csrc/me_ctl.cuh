@@ -41,7 +41,7 @@ __host__ __device__ inline void s16_tile_geometry(int sa_w, int sa_h, int *tile_
 // window clamp + plane address shared by prehme_core and hme_level_0/1/2
 __device__ inline void ctl_make_job(HmeJobG &j, const DevPlane &ref, int16_t org_x, int16_t org_y, int16_t origin_x,
                                     int16_t origin_y, int16_t sa_w, int16_t sa_h, int16_t pad_w, int16_t pad_h,
-                                    bool round_w8, int rows, int row_step) {
+                                    bool round_w8, int rows, int bw) {
     clamp_axis(org_x, origin_x, sa_w, pad_w, (int16_t)ref.width);
     if (round_w8) sa_w = (int16_t)((sa_w < 8) ? sa_w : sa_w & ~0x07);
     clamp_axis(org_y, origin_y, sa_h, pad_h, (int16_t)ref.height);
@@ -52,7 +52,10 @@ __device__ inline void ctl_make_job(HmeJobG &j, const DevPlane &ref, int16_t org
     s16_tile_geometry(sa_w, sa_h, &tw, &th, &ntx, &nty, &wide);
     j.tile_w = (uint16_t)tw; j.tile_h = (uint16_t)th; j.n_tx = (uint8_t)ntx; j.n_ty = (uint8_t)nty; j.wide = (uint8_t)wide;
     j.px = x_tl; j.py = y_tl;
-    (void)rows; (void)row_step;
+    // the block the job compares: offset of its top-left sample in the SOURCE plane of the same level (all planes of a
+    // session share one geometry), width, and rows after sub-sampling
+    j.src_off = (int32_t)((ref.org_y + org_y) * ref.stride + ref.org_x + org_x);
+    j.bw = (uint8_t)bw; j.rows = (uint8_t)rows;
     j.key    = HME_KEY_NONE;
     j.active = 1;
 }
@@ -309,7 +312,7 @@ __global__ void __launch_bounds__(32 * CTL_WARPS) k_hme_ctl(const PicJob *__rest
             const int16_t h = (int16_t)(uint16_t)min((uint32_t)c.prehme_sa_cfg[s].sa_min.height * factor, (uint32_t)c.prehme_sa_cfg[s].sa_max.height);
             const DevPlane &rf = job.ref[l][r].lvl[2];
             ctl_make_job(j, rf, (int16_t)(ox16 >> 2), (int16_t)(oy16 >> 2), (int16_t)(-(int16_t)(w >> 1)), (int16_t)(-(int16_t)(h >> 1)),
-                         w, h, (int16_t)(rf.org_x - 1), (int16_t)(rf.org_y - 1), false, rows0, row_step);
+                         w, h, (int16_t)(rf.org_x - 1), (int16_t)(rf.org_y - 1), false, rows0, bw0);
             const bool sk = c.prehme_skip_search_line && bw0 == 16 && rows0 <= 16;
             if (j.sa_w > 0 && j.sa_h > 0) ops += (unsigned long long)j.sa_w * (sk ? j.sa_h / 2 : j.sa_h) * bw0 * rows0;
             ctl_enqueue_tiles(job, j, b * HME_JOBS_PER_B64 + lane);
@@ -358,7 +361,7 @@ __global__ void __launch_bounds__(32 * CTL_WARPS) k_hme_ctl(const PicJob *__rest
             const int16_t oy = (int16_t)(-(int16_t)((sh0 * c.num_hme_sa_h) >> 1) + (int16_t)(sh0 * qb));
             const DevPlane &rf = job.ref[l][r].lvl[2];
             ctl_make_job(j, rf, (int16_t)(ox16 >> 2), (int16_t)(oy16 >> 2), ox, oy, w, sh0, (int16_t)(rf.org_x - 1),
-                         (int16_t)(rf.org_y - 1), true, rows0, row_step);
+                         (int16_t)(rf.org_y - 1), true, rows0, bw0);
             if (j.sa_w > 0 && j.sa_h > 0) ops += (unsigned long long)j.sa_w * j.sa_h * bw0 * rows0;
             ctl_enqueue_tiles(job, j, b * HME_JOBS_PER_B64 + lane);
         }
@@ -393,9 +396,9 @@ __global__ void __launch_bounds__(32 * CTL_WARPS) k_hme_ctl(const PicJob *__rest
             const DevPlane &rf = job.ref[l][r].lvl[lvl == 1 ? 1 : 0];
             if (lvl == 1)
                 ctl_make_job(j, rf, (int16_t)(ox16 >> 1), (int16_t)(oy16 >> 1), ox, oy, w, h, (int16_t)(rf.org_x - 1),
-                             (int16_t)(rf.org_y - 1), true, rows, row_step);
+                             (int16_t)(rf.org_y - 1), true, rows, bw);
             else
-                ctl_make_job(j, rf, ox16, oy16, ox, oy, w, h, 63, 63, true, rows, row_step);
+                ctl_make_job(j, rf, ox16, oy16, ox, oy, w, h, 63, 63, true, rows, bw);
             if (j.sa_w > 0 && j.sa_h > 0) ops += (unsigned long long)j.sa_w * j.sa_h * bw * rows;
 
         }

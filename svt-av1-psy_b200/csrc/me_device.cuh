@@ -64,6 +64,8 @@ struct HmeJobG {
     uint16_t           tile_w, tile_h; // positions per tile (tile_w multiple of 8)
     uint8_t            n_tx, n_ty, active, wide; // wide: 1 = 128x18-position tiles, 0 = 16x96 (1/16-plane searches)
     int16_t            px, py;                   // plane coordinates of the window's top-left sample
+    int32_t            src_off;                  // offset of the block's top-left sample in the source plane of the level
+    uint8_t            bw, rows, pad_[2];        // block width, block rows compared (after row sub-sampling)
 };
 #define HME_JOBS_PER_B64 32
 #define HME_KEY_NONE ((0xffffffull << 32) | 0xffffffffull) /* best_sad = 0xffffff, nothing found */

@@ -243,7 +243,7 @@ __global__ void __launch_bounds__(128) k_dg_build(const PicJob *__restrict__ job
     int16_t sa_w = (int16_t)((sa0 + 7) & ~0x07), sa_h = (int16_t)sa0;
     const int16_t ox = (int16_t)(-(sa_w >> 1)), oy = (int16_t)(-(sa_h >> 1));
     ctl_make_job(j, ref, (int16_t)(g.org_x >> 2), (int16_t)(g.org_y >> 2), ox, oy, sa_w, sa_h, (int16_t)(ref.org_x - 1),
-                 (int16_t)(ref.org_y - 1), true, 16, 1);
+                 (int16_t)(ref.org_y - 1), true, 16, 16);
     ctl_enqueue_tiles(job, j, b * HME_JOBS_PER_B64);
 }
 

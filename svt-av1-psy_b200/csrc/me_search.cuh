@@ -263,10 +263,11 @@ __device__ __forceinline__ void warp_stage_src16(uint32_t dst, const uint8_t *sr
 
 // ---- k_search16 ------------------------------------------------------------------------------
 // persistent warps pull (picture, job, tile) units from the queue k_hme_ctl filled; the tile of the next unit is
-// in flight while the current one is searched
+// in flight while the current one is searched. Everything a unit needs was precomputed into its HmeJobG: the
+// per-unit code runs once per ~1-3 rounds of tasks and used to be a quarter of the kernel's instructions.
 struct S16Unit {
-    int  pic, slot, tile;
-    int  px, py, sa_w, sa_h, tile_w, tile_h, n_tx, wide;
+    int  pic, slot;
+    int  px, py, sa_w, sa_h, x0, y0, tw, th, wide, src_off, bw, rows;
     bool valid;
 };
 __device__ __forceinline__ S16Unit s16_fetch_unit(const PicJob *__restrict__ jobs, uint32_t n_units) {
@@ -275,14 +276,19 @@ __device__ __forceinline__ S16Unit s16_fetch_unit(const PicJob *__restrict__ job
     if ((threadIdx.x & 31) == 0) ui = atomicAdd(&jobs[0].s16_counters[1], 1u);
     ui = __shfl_sync(0xffffffffu, ui, 0);
     un.valid = ui < n_units;
-    un.pic = un.slot = un.tile = un.px = un.py = un.sa_w = un.sa_h = un.wide = 0;
-    un.tile_w = un.tile_h = un.n_tx = 1;
+    un.pic = un.slot = un.px = un.py = un.sa_w = un.sa_h = un.x0 = un.y0 = un.wide = un.src_off = 0;
+    un.tw = un.th = un.bw = un.rows = 1;
     if (un.valid) {
         const uint2 q = jobs[0].s16_units[ui];
-        un.pic = (int)q.x; un.slot = (int)(q.y >> 10); un.tile = (int)(q.y & 1023u);
+        un.pic = (int)q.x; un.slot = (int)(q.y >> 10);
+        const int tile = (int)(q.y & 1023u);
         const HmeJobG &j = jobs[un.pic].hme_jobs[un.slot];
-        un.px = j.px; un.py = j.py; un.sa_w = j.sa_w; un.sa_h = j.sa_h;
-        un.tile_w = j.tile_w; un.tile_h = j.tile_h; un.n_tx = j.n_tx; un.wide = j.wide;
+        un.px = j.px; un.py = j.py; un.sa_w = j.sa_w; un.sa_h = j.sa_h; un.wide = j.wide;
+        un.src_off = j.src_off; un.bw = j.bw; un.rows = j.rows;
+        int tx = 0, ty = tile;
+        if (j.n_tx > 1) { ty = tile / j.n_tx; tx = tile - ty * j.n_tx; } // only windows wider than 128 positions
+        un.x0 = tx * j.tile_w; un.y0 = ty * j.tile_h;
+        un.tw = imin(j.tile_w, un.sa_w - un.x0); un.th = imin(j.tile_h, un.sa_h - un.y0);
     }
     return un;
 }
@@ -296,25 +302,19 @@ __global__ void __launch_bounds__(32 * SEARCH_WARPS) k_search16(const PicJob *__
     const uint32_t n_units = min(job0.s16_counters[0], job0.s16_units_cap);
     if (blockIdx.x == 0 && threadIdx.x == 0 && job0.s16_counters[0] > job0.s16_units_cap) job0.fp_counters[8] = 1; // queue overflow: reported by the host
     if (n_units == 0) return;
-    const bool sub = job0.pp.ctrls.hme_search_method == SVTME_SUB_SAD_SEARCH;
-    const int row_step = sub ? 2 : 1;
+    const int row_step = job0.pp.ctrls.hme_search_method == SVTME_SUB_SAD_SEARCH ? 2 : 1;
     uint8_t *sbase = s_dyn + ((128u - (smem_u32(s_dyn) & 127u)) & 127u);
     TilePipe P;
     pipe_init(P, sbase + (size_t)warp * 2 * TM_S16_BUF, TM_S16_BUF, s_bar[warp], 0);
-    // issue: the tile load and the source rows of the unit's b64 (both land in stage `st`)
+    // issue: the tile load and the source rows of the unit's block (both land in stage `st`)
     auto issue = [&](const S16Unit &un, int st) {
         const PicJob &job = jobs[un.pic];
-        const int lr = (un.slot % HME_JOBS_PER_B64) >> 2, b = un.slot / HME_JOBS_PER_B64;
+        const int lr = (un.slot & (HME_JOBS_PER_B64 - 1)) >> 2;
         const CUtensorMap *map = (const CUtensorMap *)job.ref[lr >> 2][lr & 3].tmap + (un.wide ? TM_S16W : TM_S16T);
-        const int ty = un.tile / un.n_tx, tx = un.tile - ty * un.n_tx;
-        pipe_issue_bytes(P, st, map, (un.px + tx * un.tile_w) & ~15, un.py + ty * un.tile_h,
+        pipe_issue_bytes(P, st, map, (un.px + un.x0) & ~15, un.py + un.y0,
                          un.wide ? TM_S16W_BOX_W * TM_S16W_BOX_H : TM_S16T_BOX_W * TM_S16T_BOX_H);
-        const B64Geo g = b64_geo(job, b);
         const DevPlane &ss = job.src.lvl[2];
-        const int bh16 = job.dg_mode ? 16 : (g.b64_h >> 2);
-        const int rows = sub ? bh16 >> 1 : bh16;
-        warp_stage_src16(smem_u32(s_src[warp][st]), ss.buf + (size_t)(ss.org_y + (g.org_y >> 2)) * ss.stride + ss.org_x + (g.org_x >> 2),
-                         ss.stride, row_step, rows, job.dg_mode ? 16 : (g.b64_w >> 2));
+        warp_stage_src16(smem_u32(s_src[warp][st]), ss.buf + un.src_off, ss.stride, row_step, un.rows, un.bw);
     };
     S16Unit cur = s16_fetch_unit(jobs, n_units);
     if (!cur.valid) return;
@@ -323,19 +323,13 @@ __global__ void __launch_bounds__(32 * SEARCH_WARPS) k_search16(const PicJob *__
     while (cur.valid) {
         const S16Unit nxt = s16_fetch_unit(jobs, n_units);
         if (nxt.valid) issue(nxt, stage ^ 1);
-        const PicJob &job = jobs[cur.pic];
-        const B64Geo g = b64_geo(job, cur.slot / HME_JOBS_PER_B64);
-        const int bh16 = job.dg_mode ? 16 : (g.b64_h >> 2);
-        const int bw = job.dg_mode ? 16 : (g.b64_w >> 2), rows = sub ? bh16 >> 1 : bh16;
-        const int ty = cur.tile / cur.n_tx, tx = cur.tile - ty * cur.n_tx;
-        const int x0 = tx * cur.tile_w, y0 = ty * cur.tile_h;
-        const bool skip = skip_cfg && bw == 16 && rows <= 16;
+        const bool skip = skip_cfg && cur.bw == 16 && cur.rows <= 16;
         pipe_wait(P, stage);
         __syncwarp(); // the source rows written by other lanes
         const unsigned long long key = warp_search16_tile(P.buf[stage], cur.wide ? TM_S16W_BOX_W : TM_S16T_BOX_W, smem_u32(s_src[warp][stage]),
-                                                         (uint32_t)(cur.px + x0) & 15u, cur.sa_w, x0, y0, imin(cur.tile_w, cur.sa_w - x0),
-                                                         imin(cur.tile_h, cur.sa_h - y0), bw, rows, row_step, skip);
-        if (lane == 0 && key != HME_KEY_NONE) atomicMin(&job.hme_jobs[cur.slot].key, key);
+                                                         (uint32_t)(cur.px + cur.x0) & 15u, cur.sa_w, cur.x0, cur.y0, cur.tw, cur.th, cur.bw,
+                                                         cur.rows, row_step, skip);
+        if (lane == 0 && key != HME_KEY_NONE) atomicMin(&jobs[cur.pic].hme_jobs[cur.slot].key, key);
         __syncwarp();
         cur = nxt;
         stage ^= 1;
