@@ -359,16 +359,17 @@ __device__ __forceinline__ void blk_tile_eval(const TLane<NS, NR> &L, uint32_t b
                                               int sa_h, uint32_t &best) {
     const uint32_t a = (uint32_t)(px + TM_BLK_TILE_W * tx) & 15u;
     const int n_x = imin(TM_BLK_TILE_W, sa_w - TM_BLK_TILE_W * tx), n_y = imin(TM_BLK_TILE_H, sa_h - TM_BLK_TILE_H * ty);
-    const int pos = reduce8_pos();
     for (int yy = 0; yy < n_y; yy++) {
         for (int o = 0; 8 * o < n_x; o++) {
             uint32_t acc[8], unused[8];
             tile_pass<NS, NR, false>(L, buf + (uint32_t)(yy * pitch), a + 8u * o, acc, unused);
-            const uint32_t sad = reduce8_all(acc);
-            const int x = 8 * o + pos;
-            if (x < n_x) {
-                const uint32_t idx = (uint32_t)((TM_BLK_TILE_H * ty + yy) * sa_w + TM_BLK_TILE_W * tx + x);
-                best = min(best, (sad << BLK_IDX_BITS) | idx);
+            // warp-wide sums on the reduction unit (REDUX.SUM), one per position, instead of a shuffle tree on the
+            // ALU pipe that bounds this kernel; every lane then keeps the running minimum (the values are uniform)
+            const uint32_t idx0 = (uint32_t)((TM_BLK_TILE_H * ty + yy) * sa_w + TM_BLK_TILE_W * tx + 8 * o);
+#pragma unroll
+            for (int p = 0; p < 8; p++) {
+                const uint32_t sad = __reduce_add_sync(0xffffffffu, acc[p]);
+                if (8 * o + p < n_x) best = min(best, (sad << BLK_IDX_BITS) | (idx0 + (uint32_t)p));
             }
         }
     }
