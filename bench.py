@@ -387,8 +387,8 @@ def run_ours(a):
         alg_bytes = (1 + n_refs) * plane + out_b
         avg_s = dom_ms * 1e-3 / max(1, n_timed)
         # dram__bytes_read.sum + dram__bytes_write.sum of the HME-stage kernels, per picture, from the ncu --set full
-        # capture of this workload (profiles/r01_v4_summary.md: 172 MB per launch of 32 pictures); null for other workloads
-        traffic = round(172.3e6 / 32) if (dominant == "k_hme" and (wl.w, wl.h, wl.preset, wl.bits) == (1920, 1080, 4, 8)) else None
+        # capture of this workload (profiles/r01_final_summary.md: 355 MB per mini-GOP of 32 pictures); null for other workloads
+        traffic = round(355.4e6 / 32) if (dominant == "k_hme" and (wl.w, wl.h, wl.preset, wl.bits) == (1920, 1080, 4, 8)) else None
         sm_mhz = clocks.get("sm_mhz") or peaks.get("sm_max_mhz", 1965.0)
         int_peak = INT_PEAK_LANE_INSTR_PER_CLK_SM * 4 * N_SM * sm_mhz * 1e6  # |a-b| ops/s at the sampled clock
         line = {
