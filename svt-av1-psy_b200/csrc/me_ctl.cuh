@@ -56,6 +56,7 @@ __device__ inline void ctl_make_job(HmeJobG &j, const DevPlane &ref, int16_t org
     // session share one geometry), width, and rows after sub-sampling
     j.src_off = (int32_t)((ref.org_y + org_y) * ref.stride + ref.org_x + org_x);
     j.bw = (uint8_t)bw; j.rows = (uint8_t)rows;
+    j.merged = 0; j.m_w = j.m_h = 0;
     j.key    = HME_KEY_NONE;
     j.active = 1;
 }
@@ -286,6 +287,7 @@ __global__ void __launch_bounds__(32 * CTL_WARPS) k_hme_ctl(const PicJob *__rest
     __syncwarp();
 
     // ---- BUILD ----
+    bool l0_built = false;
     const bool in_build = searched && ((op.build_mask >> lr) & 1);
     const int16_t ox16 = (int16_t)g.org_x, oy16 = (int16_t)g.org_y;
     if (op.build_stage == ST_PREHME && in_build && q < 2 && hme_ref) {
@@ -363,7 +365,7 @@ __global__ void __launch_bounds__(32 * CTL_WARPS) k_hme_ctl(const PicJob *__rest
             ctl_make_job(j, rf, (int16_t)(ox16 >> 2), (int16_t)(oy16 >> 2), ox, oy, w, sh0, (int16_t)(rf.org_x - 1),
                          (int16_t)(rf.org_y - 1), true, rows0, bw0);
             if (j.sa_w > 0 && j.sa_h > 0) ops += (unsigned long long)j.sa_w * j.sa_h * bw0 * rows0;
-            ctl_enqueue_tiles(job, j, b * HME_JOBS_PER_B64 + lane);
+            l0_built = true; // enqueued below, once the four quadrants of a reference know whether they merge
         }
     } else if ((op.build_stage == ST_L1 || op.build_stage == ST_L2) && in_build && hme_ref) {
         const int lvl = op.build_stage - ST_L0;
@@ -401,6 +403,38 @@ __global__ void __launch_bounds__(32 * CTL_WARPS) k_hme_ctl(const PicJob *__rest
                 ctl_make_job(j, rf, ox16, oy16, ox, oy, w, h, 63, 63, true, rows, bw);
             if (j.sa_w > 0 && j.sa_h > 0) ops += (unsigned long long)j.sa_w * j.sa_h * bw * rows;
 
+        }
+    }
+    if (op.build_stage == ST_L0) { // warp-uniform: all lanes are here
+        // The four quadrant windows of one reference (lanes 4k..4k+3: q = qa + 2 qb) are adjacent unless the picture edge
+        // clamped them differently. When they form an exact 2 x 2 grid, ONE unit searches their union (k_search16 keeps a
+        // best per quadrant): a quarter of the units, and lanes that a 16 x 8 quadrant alone leaves idle are filled.
+        const int act = l0_built && j.sa_w > 0 && j.sa_h > 0;
+        const int base = lane & ~3;
+        int v_act[4], v_px[4], v_py[4], v_w[4], v_h[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            v_act[k] = __shfl_sync(0xffffffffu, act, base + k);
+            v_px[k]  = __shfl_sync(0xffffffffu, (int)j.px, base + k);
+            v_py[k]  = __shfl_sync(0xffffffffu, (int)j.py, base + k);
+            v_w[k]   = __shfl_sync(0xffffffffu, (int)j.sa_w, base + k);
+            v_h[k]   = __shfl_sync(0xffffffffu, (int)j.sa_h, base + k);
+        }
+        const bool grid = v_act[0] && v_act[1] && v_act[2] && v_act[3] && v_w[0] == v_w[2] && v_w[1] == v_w[3] && v_h[0] == v_h[1] &&
+            v_h[2] == v_h[3] && v_px[1] == v_px[0] + v_w[0] && v_px[2] == v_px[0] && v_px[3] == v_px[1] && v_py[1] == v_py[0] &&
+            v_py[2] == v_py[0] + v_h[0] && v_py[3] == v_py[2] && (v_w[0] & 7) == 0;
+        if (grid) {
+            if (q == 0) {
+                int tw, th, ntx, nty, wide;
+                s16_tile_geometry(v_w[0] + v_w[1], v_h[0] + v_h[2], &tw, &th, &ntx, &nty, &wide);
+                j.merged = 1; j.m_w = (int16_t)(v_w[0] + v_w[1]); j.m_h = (int16_t)(v_h[0] + v_h[2]);
+                j.tile_w = (uint16_t)tw; j.tile_h = (uint16_t)th; j.n_tx = (uint8_t)ntx; j.n_ty = (uint8_t)nty; j.wide = (uint8_t)wide;
+                ctl_enqueue_tiles(job, j, b * HME_JOBS_PER_B64 + lane);
+            } else {
+                j.merged = 2;
+            }
+        } else if (l0_built) {
+            ctl_enqueue_tiles(job, j, b * HME_JOBS_PER_B64 + lane);
         }
     }
 #pragma unroll

@@ -65,7 +65,10 @@ struct HmeJobG {
     uint8_t            n_tx, n_ty, active, wide; // wide: 1 = 128x18-position tiles, 0 = 16x96 (1/16-plane searches)
     int16_t            px, py;                   // plane coordinates of the window's top-left sample
     int32_t            src_off;                  // offset of the block's top-left sample in the source plane of the level
-    uint8_t            bw, rows, pad_[2];        // block width, block rows compared (after row sub-sampling)
+    uint8_t            bw, rows;                 // block width, block rows compared (after row sub-sampling)
+    uint8_t            merged, pad_;             // 1: this job's unit covers the 2 x 2 union of the windows of slots +0..+3
+                                                 //    (m_w x m_h, split at this job's own sa_w / sa_h); 2: covered by that unit
+    int16_t            m_w, m_h;
 };
 #define HME_JOBS_PER_B64 32
 #define HME_KEY_NONE ((0xffffffull << 32) | 0xffffffffull) /* best_sad = 0xffffff, nothing found */

@@ -310,7 +310,10 @@ uint32_t svtme_s16_units_cap(const SvtMePicParams &pp, int n_b64) {
         per_b64 = 8 * (tiles_of(c.prehme_sa_cfg[0].sa_max.width, c.prehme_sa_cfg[0].sa_max.height) +
                        tiles_of(c.prehme_sa_cfg[1].sa_max.width, c.prehme_sa_cfg[1].sa_max.height));
     const int qw = ((((c.hme_l0_sa.sa_max.width / 2) + 15) & ~15) + 7) & ~7;
-    const long long l0 = 32 * tiles_of(qw, c.hme_l0_sa.sa_max.height / 2);
+    // per reference: four quadrant windows, or their 2 x 2 union as one window (k_hme_ctl merges exact grids)
+    const int qh = c.hme_l0_sa.sa_max.height / 2;
+    const long long l0_sep = 4 * tiles_of(qw, qh), l0_mrg = tiles_of(2 * qw, 2 * qh);
+    const long long l0 = 8 * (l0_sep > l0_mrg ? l0_sep : l0_mrg);
     if (l0 > per_b64) per_b64 = l0;
     long long cap = per_b64 * n_b64;
     if (cap > 0x7fffffffLL) cap = 0x7fffffffLL;
@@ -535,9 +538,11 @@ __global__ void __launch_bounds__(32 * SEARCH_WARPS) k_kat_search16(const __grid
     warp_stage_src16(smem_u32(s_src[warp]), src, src_stride, 1, bh, bw);
     pipe_wait(P, 0);
     __syncwarp();
-    const unsigned long long key = warp_search16_tile(P.buf[0], wide ? TM_S16W_BOX_W : TM_S16T_BOX_W, smem_u32(s_src[warp]), (uint32_t)x0 & 15u,
-                                                     sa_w, x0, y0, imin(tile_w, sa_w - x0), imin(tile_h, sa_h - y0), bw, bh, row_step,
-                                                     skip && bw == 16 && bh <= 16);
+    uint32_t best[4];
+    const S16Split sp = {32767, 32767};
+    warp_search16_tile(P.buf[0], wide ? TM_S16W_BOX_W : TM_S16T_BOX_W, smem_u32(s_src[warp]), (uint32_t)x0 & 15u, x0, y0,
+                       imin(tile_w, sa_w - x0), imin(tile_h, sa_h - y0), bw, bh, row_step, skip && bw == 16 && bh <= 16, sp, best);
+    const unsigned long long key = best[0] == 0xffffffffu ? HME_KEY_NONE : s16_key64(best[0], x0, y0, 0, sp, sa_w);
     if (lane == 0 && key != HME_KEY_NONE) atomicMin(out_key, key);
 }
 

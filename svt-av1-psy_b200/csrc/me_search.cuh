@@ -92,16 +92,30 @@ __global__ void __launch_bounds__(32 * SEARCH_WARPS) k_zz(const PicJob *__restri
 }
 
 // ---- 1/16-plane searches (blocks <= 16 wide): tiles through TMA ---------------------------------
-// One tile = TM_S16T (16 positions x 96 rows) or TM_S16W (128 x 16) of a window, fetched from the 16-byte boundary at
-// or before its first position. lane = (search row, octet of 8 positions); a lane reads 32 bytes per block row from
-// the 8-byte boundary at or before its octet (4 LDS.64, consecutive lanes = consecutive 8-byte units), and the
-// remaining 0..7 bytes of misalignment are the same for every octet of the job: one warp-uniform word select (JW)
-// and one funnel shift per word. src: n_rows x 16 bytes in shared memory, bytes >= bw zeroed.
-// Returns the warp-wide best key of the tile (positions indexed in the window).
+// One tile = TM_S16T (16 positions x 96 rows) or TM_S16W (128 x 18) of a window, fetched from the 16-byte boundary at
+// or before its first position. src: n_rows x 16 bytes in shared memory, bytes >= bw zeroed.
+//
+// A window may be the union of the four quadrant windows of an HME level-0 search (k_hme_ctl merges them when they
+// form an exact 2 x 2 grid: one unit instead of four, lanes filled). Every routine therefore keeps FOUR running bests,
+// one per quadrant: quadrant = (x >= split_x) + 2 * (y >= split_y) in window coordinates; an ordinary window has its
+// splits beyond its size. Keys: (sad << 16 | yy << 8 | xx) with tile-local coordinates (sad <= 16*16*255, yy < 128,
+// xx < 128); min() = first minimum in raster order, inside a quadrant too.
+struct S16Split {
+    int x, y; // window coordinates of the first position of the right / bottom quadrants
+};
+
+__device__ __forceinline__ void s16_merge_best(uint32_t (&best)[4], uint32_t key, int qd) {
+#pragma unroll
+    for (int k = 0; k < 4; k++) best[k] = (qd == k) ? min(best[k], key) : best[k];
+}
+
+// lane = (search row, octet of 8 positions); a lane reads 32 bytes per block row from the 8-byte boundary at or before
+// its octet (4 LDS.64, consecutive lanes = consecutive 8-byte units); the remaining 0..7 bytes of misalignment are the
+// same for every octet of the job: one warp-uniform word select (JW) and one funnel shift per word.
 template <int JW>
-__device__ __forceinline__ void s16_tile_tasks(uint32_t buf, int pitch, uint32_t src, uint32_t h8, uint32_t t8, int sa_w, int x0,
-                                               int y0, int tw, int th, int bw, int n_rows, int row_step, bool skip_lines,
-                                               uint32_t &best_sad, uint32_t &best_idx) {
+__device__ __forceinline__ void s16_tile_tasks(uint32_t buf, int pitch, uint32_t src, uint32_t h8, uint32_t t8, int x0, int y0, int tw,
+                                               int th, int bw, int n_rows, int row_step, bool skip_lines, S16Split sp,
+                                               uint32_t (&best)[4]) {
     const int lane  = threadIdx.x & 31;
     const int n_oct = (tw + 7) >> 3;
     const bool     partial = bw < 16;
@@ -141,30 +155,28 @@ __device__ __forceinline__ void s16_tile_tasks(uint32_t buf, int pitch, uint32_t
                 }
             }
         }
+        uint32_t tb = 0xffffffffu;
+        const uint32_t idx = ((uint32_t)yy << 8) | (uint32_t)(8 * oct);
 #pragma unroll
-        for (int p = 0; p < 8; p++) {
-            const int x = 8 * oct + p;
-            if (x < tw && acc[p] < best_sad) {
-                best_sad = acc[p];
-                best_idx = (uint32_t)(y * sa_w + x0 + x);
-            }
-        }
+        for (int p = 0; p < 8; p++)
+            if (8 * oct + p < tw) tb = min(tb, (acc[p] << 16) + idx + p);
+        s16_merge_best(best, tb, (x0 + 8 * oct >= sp.x ? 1 : 0) + (y >= sp.y ? 2 : 0));
     }
 }
 
 // Vertically blocked form for the common shape (16x16 block, rows two apart: 8 block rows): a lane takes G search
 // rows of the same parity (yy0, yy0+2, ...) of one octet. Search rows two apart read the same reference rows against
 // different source rows, so each reference row is loaded and funnel-shifted ONCE (7 LDS + 21 SHF) and feeds up to G
-// x 32 VABSDIFF4: 21 SHF per 128 SADs instead of per 32. Keys: (sad << 16 | yy << 8 | x), first minimum in raster
-// order. par0 / npar: first parity and number of parities searched (skip_search_line searches odd rows only).
+// x 32 VABSDIFF4: 21 SHF per 96 SADs instead of per 32. par0 / npar: first parity and number of parities searched
+// (skip_search_line searches odd rows only).
 // G = 3: blocks of 6 search rows. Lanes then sit 6 rows apart (72 words at the 48-byte pitch of the tall tile = 8
 // banks): 4-way conflicts on the LDS.32, 28 cycles per reference row against ~58 of ALU work. With G = 4 lanes sit 8
 // rows apart = a multiple of 32 words for ANY pitch the TMA allows (multiples of 16 bytes): 16-way conflicts, measured
 // 30 % slower than no blocking at all.
 #define S16_VB_G 3
 template <int G>
-__device__ __forceinline__ void s16_tile_tasks_vb(uint32_t buf, int pitch, uint32_t src, uint32_t a, int tw, int th, int par0, int npar,
-                                                  uint32_t &best) {
+__device__ __forceinline__ void s16_tile_tasks_vb(uint32_t buf, int pitch, uint32_t src, uint32_t a, int x0, int y0, int tw, int th,
+                                                  int par0, int npar, S16Split sp, uint32_t (&best)[4]) {
     const int lane  = threadIdx.x & 31;
     const int n_oct = (tw + 7) >> 3;
     const int n_tasks = n_oct * ((th + 2 * G - 1) / (2 * G)) * npar;
@@ -215,40 +227,48 @@ __device__ __forceinline__ void s16_tile_tasks_vb(uint32_t buf, int pitch, uint3
                 }
             }
         }
+        const int right = x0 + 8 * oct >= sp.x ? 1 : 0;
 #pragma unroll
         for (int g = 0; g < G; g++) {
             const int yy = yy0 + 2 * g;
             if (yy < th) {
                 const uint32_t idx = ((uint32_t)yy << 8) | (uint32_t)(8 * oct);
+                uint32_t tb = 0xffffffffu;
 #pragma unroll
                 for (int p = 0; p < 8; p++)
-                    if (8 * oct + p < tw) best = min(best, (acc[g][p] << 16) + idx + p);
+                    if (8 * oct + p < tw) tb = min(tb, (acc[g][p] << 16) + idx + p);
+                s16_merge_best(best, tb, right + (y0 + yy >= sp.y ? 2 : 0));
             }
         }
     }
 }
 
-// a: byte offset of the tile's position 0 inside its rows ((plane x of the position) & 15)
-__device__ inline unsigned long long warp_search16_tile(uint32_t buf, int pitch, uint32_t src, uint32_t a, int sa_w, int x0, int y0,
-                                                        int tw, int th, int bw, int n_rows, int row_step, bool skip_lines) {
+// a: byte offset of the tile's position 0 inside its rows ((plane x of the position) & 15). On return best[k] is the
+// warp-wide best of quadrant k in this tile, or 0xffffffff.
+__device__ inline void warp_search16_tile(uint32_t buf, int pitch, uint32_t src, uint32_t a, int x0, int y0, int tw, int th, int bw,
+                                          int n_rows, int row_step, bool skip_lines, S16Split sp, uint32_t (&best)[4]) {
+#pragma unroll
+    for (int k = 0; k < 4; k++) best[k] = 0xffffffffu;
     // blocked form only where it fills the warp: >= 24 (octet, chain) tasks and at most one partial block in four
     const int vb_blocks = (th + 2 * S16_VB_G - 1) / (2 * S16_VB_G);
     const bool vb_ok = ((tw + 7) >> 3) * vb_blocks * (skip_lines ? 1 : 2) >= 24 && (th % (2 * S16_VB_G) == 0 || vb_blocks >= 4);
     if (bw == 16 && n_rows == 8 && row_step == 2 && vb_ok) {
-        uint32_t best = 0xffffffffu;
         // skip_search_line drops the even rows of the WINDOW: parity is relative to y0
         const int par0 = skip_lines ? ((y0 & 1) ? 0 : 1) : 0;
-        s16_tile_tasks_vb<S16_VB_G>(buf, pitch, src, a, tw, th, par0, skip_lines ? 1 : 2, best);
-        best = __reduce_min_sync(0xffffffffu, best);
-        if (best == 0xffffffffu || (best >> 16) >= 0xffffffu) return HME_KEY_NONE;
-        const uint32_t yy = (best >> 8) & 0xffu, x = best & 0xffu;
-        return ((unsigned long long)(best >> 16) << 32) | (uint32_t)((y0 + (int)yy) * sa_w + x0 + (int)x);
+        s16_tile_tasks_vb<S16_VB_G>(buf, pitch, src, a, x0, y0, tw, th, par0, skip_lines ? 1 : 2, sp, best);
+    } else {
+        const uint32_t h8 = a >> 3, t8 = (a & 3u) * 8u;
+        if (a & 4u) s16_tile_tasks<1>(buf, pitch, src, h8, t8, x0, y0, tw, th, bw, n_rows, row_step, skip_lines, sp, best);
+        else s16_tile_tasks<0>(buf, pitch, src, h8, t8, x0, y0, tw, th, bw, n_rows, row_step, skip_lines, sp, best);
     }
-    uint32_t best_sad = 0xffffff, best_idx = 0xffffffffu;
-    const uint32_t h8 = a >> 3, t8 = (a & 3u) * 8u;
-    if (a & 4u) s16_tile_tasks<1>(buf, pitch, src, h8, t8, sa_w, x0, y0, tw, th, bw, n_rows, row_step, skip_lines, best_sad, best_idx);
-    else s16_tile_tasks<0>(buf, pitch, src, h8, t8, sa_w, x0, y0, tw, th, bw, n_rows, row_step, skip_lines, best_sad, best_idx);
-    return warp_min_u64(((unsigned long long)best_sad << 32) | best_idx);
+#pragma unroll
+    for (int k = 0; k < 4; k++) best[k] = __reduce_min_sync(0xffffffffu, best[k]);
+}
+
+// tile-local key of quadrant qd -> the job's 64-bit key (sad << 32 | index inside the quadrant's own window of width wq)
+__device__ __forceinline__ unsigned long long s16_key64(uint32_t key, int x0, int y0, int qd, S16Split sp, int wq) {
+    const int x = x0 + (int)(key & 0xffu) - ((qd & 1) ? sp.x : 0), y = y0 + (int)((key >> 8) & 0xffu) - ((qd & 2) ? sp.y : 0);
+    return ((unsigned long long)(key >> 16) << 32) | (uint32_t)(y * wq + x);
 }
 
 // source block rows of the 1/16 plane -> shared memory (n_rows x 16 bytes, bytes >= bw zeroed); block origins are 16-byte aligned
@@ -268,6 +288,7 @@ __device__ __forceinline__ void warp_stage_src16(uint32_t dst, const uint8_t *sr
 struct S16Unit {
     int  pic, slot;
     int  px, py, sa_w, sa_h, x0, y0, tw, th, wide, src_off, bw, rows;
+    int  merged, w0, h0; // merged: the window is the 2 x 2 union of the quadrant windows of slots slot..slot+3, split at (w0, h0)
     bool valid;
 };
 __device__ __forceinline__ S16Unit s16_fetch_unit(const PicJob *__restrict__ jobs, uint32_t n_units) {
@@ -278,12 +299,14 @@ __device__ __forceinline__ S16Unit s16_fetch_unit(const PicJob *__restrict__ job
     un.valid = ui < n_units;
     un.pic = un.slot = un.px = un.py = un.sa_w = un.sa_h = un.x0 = un.y0 = un.wide = un.src_off = 0;
     un.tw = un.th = un.bw = un.rows = 1;
+    un.merged = 0; un.w0 = un.h0 = 32767;
     if (un.valid) {
         const uint2 q = jobs[0].s16_units[ui];
         un.pic = (int)q.x; un.slot = (int)(q.y >> 10);
         const int tile = (int)(q.y & 1023u);
         const HmeJobG &j = jobs[un.pic].hme_jobs[un.slot];
         un.px = j.px; un.py = j.py; un.sa_w = j.sa_w; un.sa_h = j.sa_h; un.wide = j.wide;
+        if (j.merged == 1) { un.merged = 1; un.w0 = j.sa_w; un.h0 = j.sa_h; un.sa_w = j.m_w; un.sa_h = j.m_h; }
         un.src_off = j.src_off; un.bw = j.bw; un.rows = j.rows;
         int tx = 0, ty = tile;
         if (j.n_tx > 1) { ty = tile / j.n_tx; tx = tile - ty * j.n_tx; } // only windows wider than 128 positions
@@ -326,10 +349,17 @@ __global__ void __launch_bounds__(32 * SEARCH_WARPS) k_search16(const PicJob *__
         const bool skip = skip_cfg && cur.bw == 16 && cur.rows <= 16;
         pipe_wait(P, stage);
         __syncwarp(); // the source rows written by other lanes
-        const unsigned long long key = warp_search16_tile(P.buf[stage], cur.wide ? TM_S16W_BOX_W : TM_S16T_BOX_W, smem_u32(s_src[warp][stage]),
-                                                         (uint32_t)(cur.px + cur.x0) & 15u, cur.sa_w, cur.x0, cur.y0, cur.tw, cur.th, cur.bw,
-                                                         cur.rows, row_step, skip);
-        if (lane == 0 && key != HME_KEY_NONE) atomicMin(&jobs[cur.pic].hme_jobs[cur.slot].key, key);
+        uint32_t best[4];
+        const S16Split sp = {cur.w0, cur.h0};
+        warp_search16_tile(P.buf[stage], cur.wide ? TM_S16W_BOX_W : TM_S16T_BOX_W, smem_u32(s_src[warp][stage]),
+                           (uint32_t)(cur.px + cur.x0) & 15u, cur.x0, cur.y0, cur.tw, cur.th, cur.bw, cur.rows, row_step, skip, sp, best);
+        if (lane < 4 && (lane == 0 || cur.merged)) {
+            const uint32_t k = lane == 0 ? best[0] : (lane == 1 ? best[1] : (lane == 2 ? best[2] : best[3]));
+            if (k != 0xffffffffu) {
+                const int wq = cur.merged ? ((lane & 1) ? cur.sa_w - cur.w0 : cur.w0) : cur.sa_w;
+                atomicMin(&jobs[cur.pic].hme_jobs[cur.slot + lane].key, s16_key64(k, cur.x0, cur.y0, lane, sp, wq));
+            }
+        }
         __syncwarp();
         cur = nxt;
         stage ^= 1;
