@@ -695,7 +695,6 @@ extern "C" uint32_t svtme_dg_detector_hme(SvtMeSession *s, int32_t src_pic_id, i
     PicJob &job = s->h_jobs[0];
     memset(&job, 0, sizeof(job));
     job.pp.ctrls.hme_search_method = SVTME_FULL_SAD_SEARCH; // :501
-    job.dg_mode = 1;
     job.src = s->pics[src_pic_id];
     job.ref[0][0] = s->pics[ref_pic_id];
     job.pic_w = s->w; job.pic_h = s->h; job.b64_cols = s->b64_cols; job.b64_rows = s->b64_rows; job.n_b64 = s->n_b64;

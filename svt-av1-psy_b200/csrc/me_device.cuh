@@ -88,8 +88,7 @@ struct PicJob {
     DevPic         src;
     DevPic         ref[2][4];
     int            pic_w, pic_h, b64_cols, b64_rows, n_b64, n_pus;
-    int            dg_mode; // 1: dynamic-GOP detector search (16x16 blocks of the 1/16 plane whatever the picture edge, pd_process.c:532-533)
-    int            reserved_[2];
+    int            reserved_[3];
     // device buffers
     SbState       *sb_state;   // [n_b64]
     uint32_t      *best_sad;   // [n_b64][2][4][85]

@@ -108,6 +108,20 @@ __device__ __forceinline__ void s16_merge_best(uint32_t (&best)[4], uint32_t key
 #pragma unroll
     for (int k = 0; k < 4; k++) best[k] = (qd == k) ? min(best[k], key) : best[k];
 }
+// a lane walks its tasks in raster order, so the quadrant changes a few times per tile at most: the running best of
+// the current quadrant lives in one register and is folded into best[] only on a change
+struct S16Run {
+    uint32_t key;
+    int      qd;
+};
+__device__ __forceinline__ void s16_run_update(S16Run &run, uint32_t (&best)[4], uint32_t key, int qd) {
+    if (qd != run.qd) {
+        s16_merge_best(best, run.key, run.qd);
+        run.key = 0xffffffffu;
+        run.qd  = qd;
+    }
+    run.key = min(run.key, key);
+}
 
 // lane = (search row, octet of 8 positions); a lane reads 32 bytes per block row from the 8-byte boundary at or before
 // its octet (4 LDS.64, consecutive lanes = consecutive 8-byte units); the remaining 0..7 bytes of misalignment are the
@@ -123,6 +137,7 @@ __device__ __forceinline__ void s16_tile_tasks(uint32_t buf, int pitch, uint32_t
     int yy = lane / n_oct, oct = lane - yy * n_oct;
     const int dyy = 32 / n_oct, doct = 32 - dyy * n_oct;
     const uint32_t rstep = (uint32_t)(row_step * pitch);
+    S16Run run = {0xffffffffu, 0};
     for (; yy < th; yy += dyy, oct += doct) {
         if (oct >= n_oct) { oct -= n_oct; yy++; if (yy >= th) break; }
         const int y = y0 + yy;
@@ -160,8 +175,9 @@ __device__ __forceinline__ void s16_tile_tasks(uint32_t buf, int pitch, uint32_t
 #pragma unroll
         for (int p = 0; p < 8; p++)
             if (8 * oct + p < tw) tb = min(tb, (acc[p] << 16) + idx + p);
-        s16_merge_best(best, tb, (x0 + 8 * oct >= sp.x ? 1 : 0) + (y >= sp.y ? 2 : 0));
+        s16_run_update(run, best, tb, (x0 + 8 * oct >= sp.x ? 1 : 0) + (y >= sp.y ? 2 : 0));
     }
+    s16_merge_best(best, run.key, run.qd);
 }
 
 // Vertically blocked form for the common shape (16x16 block, rows two apart: 8 block rows): a lane takes G search
@@ -181,6 +197,7 @@ __device__ __forceinline__ void s16_tile_tasks_vb(uint32_t buf, int pitch, uint3
     const int n_oct = (tw + 7) >> 3;
     const int n_tasks = n_oct * ((th + 2 * G - 1) / (2 * G)) * npar;
     const uint32_t t8 = (a & 3u) * 8u;
+    S16Run run = {0xffffffffu, 0};
     for (int t = lane; t < n_tasks; t += 32) {
         const int ch = t / n_oct, oct = t - ch * n_oct;
         const int yy0 = npar == 2 ? (ch >> 1) * 2 * G + (ch & 1) : ch * 2 * G + par0;
@@ -237,10 +254,11 @@ __device__ __forceinline__ void s16_tile_tasks_vb(uint32_t buf, int pitch, uint3
 #pragma unroll
                 for (int p = 0; p < 8; p++)
                     if (8 * oct + p < tw) tb = min(tb, (acc[g][p] << 16) + idx + p);
-                s16_merge_best(best, tb, right + (y0 + yy >= sp.y ? 2 : 0));
+                s16_run_update(run, best, tb, right + (y0 + yy >= sp.y ? 2 : 0));
             }
         }
     }
+    s16_merge_best(best, run.key, run.qd);
 }
 
 // a: byte offset of the tile's position 0 inside its rows ((plane x of the position) & 15). On return best[k] is the

@@ -65,13 +65,6 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
         "}\n" ::"r"(smem_u32(bar)), "r"(parity)
         : "memory");
 }
-// x must be a multiple of 16 (bytes); coordinates are relative to the plane buffer and may lie outside it (zero fill)
-__device__ __forceinline__ void tma_load_box(void *dst, const CUtensorMap *map, int x, int y, uint64_t *bar) {
-    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(
-                     smem_u32(dst)),
-                 "l"(map), "r"(x), "r"(y), "r"(smem_u32(bar))
-                 : "memory");
-}
 __device__ __forceinline__ uint2 lds64(uint32_t addr) {
     uint2 v;
     asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr));
@@ -100,7 +93,8 @@ __device__ __forceinline__ void pipe_init(TilePipe &P, uint8_t *stage0, uint32_t
     mbar_fence_init();
     __syncwarp();
 }
-// the caller guarantees that every lane has finished reading stage s (a __syncwarp after the reads)
+// x_aligned must be a multiple of 16 (bytes); coordinates are relative to the plane buffer and may lie outside it (zero
+// fill). The caller guarantees that every lane has finished reading stage s (a __syncwarp after the reads).
 __device__ __forceinline__ void pipe_issue(TilePipe &P, int s, const CUtensorMap *map, int x_aligned, int y) {
     if ((threadIdx.x & 31) == 0) {
         mbar_expect_tx(&P.bar[s], P.bytes);
@@ -230,31 +224,4 @@ __device__ __forceinline__ void tile_pass(const TLane<NS, NR> &L, uint32_t row_b
             }
         }
     }
-}
-
-// Sum 8 per-lane values over the 32 lanes with halving exchanges (9 shuffles instead of 40). Every lane returns
-// the total of position reduce8_pos(lane).
-__device__ __forceinline__ uint32_t reduce8_all(const uint32_t (&v)[8]) {
-    const int  lane = threadIdx.x & 31;
-    const bool h16 = lane & 16, h8 = lane & 8, h4 = lane & 4;
-    uint32_t u[4], t[2];
-#pragma unroll
-    for (int i = 0; i < 4; i++) {
-        const uint32_t mine = h16 ? v[4 + i] : v[i], theirs = h16 ? v[i] : v[4 + i];
-        u[i] = mine + __shfl_xor_sync(0xffffffffu, theirs, 16);
-    }
-#pragma unroll
-    for (int i = 0; i < 2; i++) {
-        const uint32_t mine = h8 ? u[2 + i] : u[i], theirs = h8 ? u[i] : u[2 + i];
-        t[i] = mine + __shfl_xor_sync(0xffffffffu, theirs, 8);
-    }
-    const uint32_t mine = h4 ? t[1] : t[0], theirs = h4 ? t[0] : t[1];
-    uint32_t r = mine + __shfl_xor_sync(0xffffffffu, theirs, 4);
-    r += __shfl_xor_sync(0xffffffffu, r, 2);
-    r += __shfl_xor_sync(0xffffffffu, r, 1);
-    return r;
-}
-__device__ __forceinline__ int reduce8_pos() {
-    const int lane = threadIdx.x & 31;
-    return ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
 }
