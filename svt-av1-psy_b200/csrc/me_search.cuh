@@ -388,7 +388,7 @@ __global__ void __launch_bounds__(32 * SEARCH_WARPS) k_search16(const PicJob *__
 // Windows here are tiny (8x3 .. 16x16 positions) and blocks large (32x16 .. 64x64 samples), so the
 // lanes are spread over the BLOCK instead of over positions: lane = band * NS + strip; a lane sums NR
 // rows of its 16-pixel strip for 8 consecutive positions per pass, from a tile that one TMA load put in
-// shared memory (me_tma.cuh); 9 shuffles add the 32 lanes. Tiles are 16 positions x 4 search rows and
+// shared memory (me_tma.cuh); REDUX.SUM adds the 32 lanes. Tiles are 16 positions x 4 search rows and
 // double-buffered per warp, across the quadrant searches of one (b64, list, ref).
 #define BLK_IDX_BITS 12 /* y * sa_w + x < 4096; SAD < 2^20 */
 
