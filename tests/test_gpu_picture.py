@@ -4,7 +4,7 @@ import pytest
 
 import svtme_b200 as me
 from oracle import pyoracle as po
-from util import (CASES, EXTRA, case_id, case_inputs, compare, compare_hme_state, extra_inputs, gpu_me, orc_me,
+from util import (CASES, EXTRA, SMALL, case_id, case_inputs, compare, compare_hme_state, extra_inputs, gpu_me, orc_me,
                   params_from_encoder_inputs)
 
 pytestmark = pytest.mark.gpu
@@ -57,6 +57,17 @@ def test_picture_me_matches_oracle(case):
     compare_hme_state(st, dbg, params)
     compare(want, got, fields=list(got.FIELDS))
     assert got.sad_ops == ops  # the device's own count of the algorithmic work equals the oracle's
+
+
+@pytest.mark.parametrize("case", SMALL, ids=case_id)
+def test_smallest_pictures_match_oracle(case):
+    src, refs, pocs, poc, enc_mode, kw = case_inputs(case)
+    params = params_from_encoder_inputs(src, refs, pocs, poc, enc_mode, **kw)
+    want, dbg, ops = orc_me(src, refs, params)
+    got, st = gpu_me(src, refs, params)
+    compare_hme_state(st, dbg, params)
+    compare(want, got, fields=list(got.FIELDS))
+    assert got.sad_ops == ops
 
 
 @pytest.mark.parametrize("name,geo,kw", EXTRA, ids=[e[0] for e in EXTRA])

@@ -14,7 +14,7 @@ from svt_av1_psy_b200.synth import PanningNoise
 pytestmark = pytest.mark.skipif(not po.ref_available() and not __import__("os").path.isdir(po.REFERENCE_ROOT),
                                 reason="reference sources not present")
 
-from util import CASES, EXTRA, RES_FIELDS, case_id, case_inputs, compare, extra_inputs, orc_me  # noqa: E402
+from util import CASES, EXTRA, RES_FIELDS, SMALL, case_id, case_inputs, compare, extra_inputs, orc_me  # noqa: E402
 
 
 def run_both(src, refs, pocs, poc, enc_mode, **kw):
@@ -27,6 +27,13 @@ def run_both(src, refs, pocs, poc, enc_mode, **kw):
 
 @pytest.mark.parametrize("case", CASES, ids=case_id)
 def test_picture_me_matches_reference(orc, case):
+    src, refs, pocs, poc, enc_mode, kw = case_inputs(case)
+    _, ref_res, ref_dbg, orc_res, orc_dbg = run_both(src, refs, pocs, poc, enc_mode, **kw)
+    compare(ref_res, orc_res, ref_dbg, orc_dbg)
+
+
+@pytest.mark.parametrize("case", SMALL, ids=case_id)
+def test_smallest_pictures_match_reference(orc, case):
     src, refs, pocs, poc, enc_mode, kw = case_inputs(case)
     _, ref_res, ref_dbg, orc_res, orc_dbg = run_both(src, refs, pocs, poc, enc_mode, **kw)
     compare(ref_res, orc_res, ref_dbg, orc_dbg)

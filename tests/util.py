@@ -22,6 +22,13 @@ CASES = [
     (320, 192, 12, 1, 4, [0], []),                       # P picture, single ref builder
     (200, 72, 4, 1, 8, [0, 4], [16, 12]),                # widths/heights that are not multiples of 64
 ]
+# smallest pictures: one b64, one partial b64 (search windows larger than the picture, every clamp active), a column of b64s
+SMALL = [
+    (64, 64, 4, 2, 8, [4, 0], [12]),
+    (72, 40, 8, 2, 8, [4, 0], [12]),
+    (136, 64, 2, 2, 8, [4, 0], [12]),
+    (64, 200, 6, 2, 8, [4, 0], [12]),
+]
 
 EXTRA = [
     ("sc_M4", dict(w=320, h=192, enc_mode=4, tl=1, poc=16, l0=[0, 8], l1=[32, 24]), dict(sc_class1=1)),
