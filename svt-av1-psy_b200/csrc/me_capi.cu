@@ -441,10 +441,11 @@ static uint32_t validate_params(const SvtMeSession *s, int32_t pic_id, const Svt
     // the MeSbResults arrays are sized by max_l0 / max_refs (pcs.c:91-96): more refs than that would alias entries
     if (pp->num_of_ref_pic_to_search[0] > pp->max_l0 || pp->max_l0 > pp->max_refs) return SVTME_ERR_BAD_PARAMETER;
     if (pp->num_of_list_to_search == 2 && pp->num_of_ref_pic_to_search[1] > pp->max_refs - pp->max_l0) return SVTME_ERR_BAD_PARAMETER;
-    { // full-pel scan indices are 12 bits per chunk of passes (me_fp3.cuh): bound the widest possible window
-        long long mw = pp->ctrls.me_sa.sa_max.width;
-        if (pp->ctrls.mv_sa_adj_enabled) mw *= pp->ctrls.mv_sa_adj_sa_multiplier;
-        if (mw * 3 / 2 + 8 > 1536) return SVTME_ERR_BAD_PARAMETER;
+    { // window sizes are int16 throughout, as in the reference; a full-pel window is cut into at most 65535 tiles
+        long long mw = pp->ctrls.me_sa.sa_max.width, mh = pp->ctrls.me_sa.sa_max.height;
+        if (pp->ctrls.mv_sa_adj_enabled) { mw *= pp->ctrls.mv_sa_adj_sa_multiplier; mh *= pp->ctrls.mv_sa_adj_sa_multiplier; }
+        mw = mw * 3 / 2 + 8; mh = mh * 3 / 2;
+        if (mw > 16384 || mh > 16384 || ((mw + 15) / 16) * ((mh + 7) / 8) > 65535) return SVTME_ERR_BAD_PARAMETER;
     }
     return SVTME_OK;
 }
