@@ -346,6 +346,12 @@ uint32_t svtme_session_sync(SvtMeSession *s);
    sets and waits for batch seq - 2 before reusing a set). No reference counterpart: the reference's ME threads
    synchronise through the picture-decision / ME FIFOs (me_process.c:75-330). */
 uint64_t svtme_session_batch_seq(SvtMeSession *s);
+/* n = 2: consecutive batches run on two compute streams (the session's stream and an internal one), so that the
+   latency-bound control kernels of one batch overlap the searches of the other. Results must then be awaited with
+   svtme_session_wait_batch / svtme_session_sync (work queued on the session's stream is no longer ordered after every
+   batch), and device buffers given to svtme_picture_upload_device* must be complete when the call is made. n = 1 (the
+   default) keeps everything on the session's stream. While kernel timing is enabled one stream is used. */
+uint32_t svtme_session_set_concurrency(SvtMeSession *s, int n);
 uint32_t svtme_session_wait_batch(SvtMeSession *s, uint64_t seq);
 
 /* Read back a device plane (level 0 = full padded, 1 = quarter, 2 = sixteenth) into host memory,

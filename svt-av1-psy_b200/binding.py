@@ -240,6 +240,12 @@ class Session:
                                            mv.ctypes.data if per_b64 else None), "svtme_dg_detector_hme")
         return m, sad, mv
 
+    def set_concurrency(self, n):
+        """2: consecutive batches alternate between two compute streams (await results with wait_batch / sync)"""
+        lib().svtme_session_set_concurrency.argtypes = [C.c_void_p, C.c_int]
+        lib().svtme_session_set_concurrency.restype = C.c_uint32
+        _check(lib().svtme_session_set_concurrency(self._h, n), "svtme_session_set_concurrency")
+
     def batch_seq(self):
         """sequence number (1, 2, ...) of the batch queued last"""
         return int(lib().svtme_session_batch_seq(self._h))

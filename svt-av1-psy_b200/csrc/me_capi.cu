@@ -46,6 +46,15 @@ struct SvtMeSession {
     std::vector<uint8_t *> res_sets[2]; // one result/scratch slab per picture of a batch
     uint8_t     *res_slab = nullptr;
     cudaStream_t up_stream = nullptr, dl_stream = nullptr; // host uploads (H2D + pyramid) / result downloads (D2H)
+    // concurrency 2: batches alternate between `stream` and `stream2` so that the latency-bound control / post kernels
+    // of one batch run under the ALU-bound searches of the other. Each set of result slabs then also owns its half of
+    // the job array and of the unit queues.
+    cudaStream_t stream2 = nullptr;
+    int          concurrency = 1;
+    cudaEvent_t  ev_built[2] = {};       // last pyramid build queued on compute stream 0 / 1
+    bool         built_recorded[2] = {false, false};
+    std::vector<uint64_t> slot_last_seq; // last batch that reads each picture slot
+    uint32_t     d_jobs_n = 0;           // pictures per set the job array holds
     cudaEvent_t  ev_me[8] = {}, ev_dl[2] = {};
     bool         dl_recorded[2] = {false, false};
     uint64_t     batch_seq = 0; // sequence number of the last launched batch (1-based)
@@ -192,10 +201,14 @@ extern "C" uint32_t svtme_session_create(SvtMeSession **out, int device, uint32_
     if (e != cudaSuccess) { cudaFree(s->pic_slab); delete s; return SVTME_ERR_INSUFFICIENT_RESOURCES; }
     cudaMemset(s->res_slab, 0, s->lay.end);
     s->res_sets[0].push_back(s->res_slab);
-    e = cudaMalloc(&s->d_jobs, sizeof(PicJob));
+    e = cudaMalloc(&s->d_jobs, sizeof(PicJob) * 2);
     if (e != cudaSuccess) { cudaFree(s->pic_slab); cudaFree(s->res_slab); delete s; return SVTME_ERR_INSUFFICIENT_RESOURCES; }
     CU_TRY(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
     s->own_stream = true;
+    CU_TRY(cudaStreamCreateWithFlags(&s->stream2, cudaStreamNonBlocking));
+    for (auto &e2 : s->ev_built) CU_TRY(cudaEventCreateWithFlags(&e2, cudaEventDisableTiming));
+    s->slot_last_seq.assign(max_pictures, 0);
+    s->d_jobs_n = 1;
     CU_TRY(cudaStreamCreateWithFlags(&s->up_stream, cudaStreamNonBlocking));
     CU_TRY(cudaStreamCreateWithFlags(&s->dl_stream, cudaStreamNonBlocking));
     for (auto &e2 : s->ev_me) CU_TRY(cudaEventCreateWithFlags(&e2, cudaEventDisableTiming));
@@ -210,11 +223,14 @@ extern "C" void svtme_session_destroy(SvtMeSession *s) {
     cudaSetDevice(s->device);
     cudaStreamSynchronize(s->up_stream);
     cudaStreamSynchronize(s->stream);
+    cudaStreamSynchronize(s->stream2);
     cudaStreamSynchronize(s->dl_stream);
     for (auto &e : s->ev) cudaEventDestroy(e);
     for (auto &e : s->ev_me) if (e) cudaEventDestroy(e);
     for (auto &e : s->ev_dl) if (e) cudaEventDestroy(e);
     if (s->up_stream) cudaStreamDestroy(s->up_stream);
+    if (s->stream2) cudaStreamDestroy(s->stream2);
+    for (auto &e : s->ev_built) if (e) cudaEventDestroy(e);
     if (s->dl_stream) cudaStreamDestroy(s->dl_stream);
     if (s->own_stream) cudaStreamDestroy(s->stream);
     cudaFree(s->pic_slab);
@@ -250,19 +266,29 @@ extern "C" uint64_t svtme_session_launch_count(SvtMeSession *s) { return s ? s->
 static uint32_t sync_all(SvtMeSession *s) {
     CU_TRY(cudaStreamSynchronize(s->up_stream));
     CU_TRY(cudaStreamSynchronize(s->stream));
+    CU_TRY(cudaStreamSynchronize(s->stream2));
     CU_TRY(cudaStreamSynchronize(s->dl_stream));
     return SVTME_OK;
 }
+
+// compute stream of the batches of result set `set` (kernel timing measures stages: one stream then)
+static cudaStream_t compute_stream(const SvtMeSession *s, int set) {
+    return (s->concurrency == 2 && !s->timing && set == 1) ? s->stream2 : s->stream;
+}
+static int stream_index(const SvtMeSession *s, int set) { return compute_stream(s, set) == s->stream2 ? 1 : 0; }
 
 // The unit queues are sized from the largest windows the controls allow; a kernel that finds one too small raises a
 // flag instead of dropping work silently. Checked at every synchronisation point.
 static uint32_t check_queue_overflow(SvtMeSession *s) {
     uint32_t flag = 0;
-    CU_TRY(cudaMemcpyAsync(&flag, (uint32_t *)(s->res_slab + s->lay.fp_counters) + 8, sizeof(flag), cudaMemcpyDeviceToHost, s->stream));
-    CU_TRY(cudaStreamSynchronize(s->stream));
+    for (int set = 0; set < 2 && !flag; set++)
+        if (!s->res_sets[set].empty()) {
+            CU_TRY(cudaMemcpyAsync(&flag, (uint32_t *)(s->res_sets[set][0] + s->lay.fp_counters) + 8, sizeof(flag), cudaMemcpyDeviceToHost, s->stream));
+            CU_TRY(cudaStreamSynchronize(s->stream));
+            if (flag) cudaMemsetAsync((uint32_t *)(s->res_sets[set][0] + s->lay.fp_counters) + 8, 0, sizeof(flag), s->stream);
+        }
     if (flag) {
         fprintf(stderr, "[svtme_b200] a search-unit queue overflowed: results of the last batches are incomplete\n");
-        cudaMemsetAsync((uint32_t *)(s->res_slab + s->lay.fp_counters) + 8, 0, sizeof(flag), s->stream);
         return SVTME_ERR_INSUFFICIENT_RESOURCES;
     }
     return SVTME_OK;
@@ -273,6 +299,16 @@ extern "C" uint32_t svtme_session_sync(SvtMeSession *s) {
     cudaSetDevice(s->device);
     uint32_t rc = sync_all(s);
     return rc != SVTME_OK ? rc : check_queue_overflow(s);
+}
+
+extern "C" uint32_t svtme_session_set_concurrency(SvtMeSession *s, int n) {
+    if (!s || n < 1 || n > 2) return SVTME_ERR_BAD_PARAMETER;
+    std::lock_guard<std::mutex> g(s->mu);
+    cudaSetDevice(s->device);
+    uint32_t rc = sync_all(s);
+    if (rc != SVTME_OK) return rc;
+    s->concurrency = n;
+    return SVTME_OK;
 }
 
 extern "C" uint64_t svtme_session_batch_seq(SvtMeSession *s) { return s ? s->batch_seq : 0; }
@@ -311,19 +347,36 @@ static uint32_t stage_host_frame(SvtMeSession *s, const void *host, size_t row_b
     else
         CU_TRY(cudaMemcpy2DAsync(dst, row_bytes, host, host_pitch, row_bytes, (size_t)s->h, cudaMemcpyHostToDevice, s->up_stream));
     CU_TRY(cudaEventRecord(s->ev_copied[j], s->up_stream));
-    CU_TRY(cudaStreamWaitEvent(s->stream, s->ev_copied[j], 0));
+    CU_TRY(cudaStreamWaitEvent(compute_stream(s, (int)((s->batch_seq + 1) & 1)), s->ev_copied[j], 0));
     s->stage_used[j] = true;
     s->stage_last = j;
     *staged = dst;
     return SVTME_OK;
 }
 
-static uint32_t finish_upload(SvtMeSession *s, int32_t pic_id, int mode, const void *d_in, int in_stride, bool staged) {
-    s->launches += (uint64_t)svtme_launch_build_pyramid(s->pics[pic_id], mode, d_in, in_stride, s->stream);
-    CU_TRY(cudaGetLastError());
-    if (staged) CU_TRY(cudaEventRecord(s->ev_ingested[s->stage_last], s->stream));
-    s->pic_valid[pic_id] = 1;
+// Pyramids are built on the compute stream of the NEXT batch (the one that will read them). A slot is not overwritten
+// before the last batch that reads it is done (it may run on the other compute stream), and a batch waits for the
+// builds queued on the other stream (after_builds / launch_me_batch).
+static uint32_t before_build(SvtMeSession *s, cudaStream_t cs, int32_t pic_id) {
+    if (s->concurrency == 2 && s->slot_last_seq[pic_id]) CU_TRY(cudaStreamWaitEvent(cs, s->ev_me[s->slot_last_seq[pic_id] % 8], 0));
     return SVTME_OK;
+}
+static uint32_t after_builds(SvtMeSession *s, cudaStream_t cs) {
+    const int k = cs == s->stream2 ? 1 : 0;
+    CU_TRY(cudaEventRecord(s->ev_built[k], cs));
+    s->built_recorded[k] = true;
+    return SVTME_OK;
+}
+
+static uint32_t finish_upload(SvtMeSession *s, int32_t pic_id, int mode, const void *d_in, int in_stride, bool staged) {
+    cudaStream_t cs = compute_stream(s, (int)((s->batch_seq + 1) & 1));
+    uint32_t rc = before_build(s, cs, pic_id);
+    if (rc != SVTME_OK) return rc;
+    s->launches += (uint64_t)svtme_launch_build_pyramid(s->pics[pic_id], mode, d_in, in_stride, cs);
+    CU_TRY(cudaGetLastError());
+    if (staged) CU_TRY(cudaEventRecord(s->ev_ingested[s->stage_last], cs));
+    s->pic_valid[pic_id] = 1;
+    return after_builds(s, cs);
 }
 
 extern "C" uint32_t svtme_picture_upload(SvtMeSession *s, int32_t pic_id, const uint8_t *luma, uint32_t stride) {
@@ -376,13 +429,18 @@ static uint32_t upload_batch(SvtMeSession *s, uint32_t n, const int32_t *pic_ids
             in[i] = src[i];
         }
     }
-    s->launches += (uint64_t)svtme_launch_build_pyramids(pics.data(), in.data(), s->w, (int)n, mode, s->stream);
+    cudaStream_t cs = compute_stream(s, (int)((s->batch_seq + 1) & 1));
+    for (uint32_t i = 0; i < n; i++) {
+        uint32_t rc = before_build(s, cs, pic_ids[i]);
+        if (rc != SVTME_OK) return rc;
+    }
+    s->launches += (uint64_t)svtme_launch_build_pyramids(pics.data(), in.data(), s->w, (int)n, mode, cs);
     CU_TRY(cudaGetLastError());
     for (uint32_t i = 0; i < n; i++) {
-        if (host) CU_TRY(cudaEventRecord(s->ev_ingested[ring[i]], s->stream));
+        if (host) CU_TRY(cudaEventRecord(s->ev_ingested[ring[i]], cs));
         s->pic_valid[pic_ids[i]] = 1;
     }
-    return SVTME_OK;
+    return after_builds(s, cs);
 }
 
 extern "C" uint32_t svtme_picture_upload_batch(SvtMeSession *s, uint32_t n, const int32_t *pic_ids, const uint8_t *const *luma,
@@ -415,6 +473,7 @@ extern "C" uint32_t svtme_picture_download_plane(SvtMeSession *s, int32_t pic_id
     const size_t W = (size_t)p.width + 2 * ep, H = (size_t)p.height + 2 * ep;
     if (dst_capacity < W * H || skip < 0) return SVTME_ERR_BAD_PARAMETER;
     CU_TRY(cudaStreamSynchronize(s->up_stream));
+    CU_TRY(cudaStreamSynchronize(s->stream2));
     CU_TRY(cudaMemcpy2DAsync(dst, W, p.buf + (size_t)skip * p.stride + skip, (size_t)p.stride, W, H, cudaMemcpyDeviceToHost, s->stream));
     CU_TRY(cudaStreamSynchronize(s->stream));
     if (stride) *stride = (uint32_t)W;
@@ -464,7 +523,7 @@ static void fold_events(SvtMeSession *s) {
 }
 
 static uint32_t ensure_batch(SvtMeSession *s, uint32_t n) {
-    if (n <= s->res_sets[0].size() && n <= s->res_sets[1].size()) return SVTME_OK;
+    if (n <= s->res_sets[0].size() && n <= s->res_sets[1].size() && n <= s->d_jobs_n) return SVTME_OK;
     uint32_t rc = sync_all(s);
     if (rc != SVTME_OK) return rc;
     for (auto &set : s->res_sets)
@@ -477,8 +536,9 @@ static uint32_t ensure_batch(SvtMeSession *s, uint32_t n) {
         }
     if (s->d_jobs) cudaFree(s->d_jobs);
     s->d_jobs = nullptr;
-    cudaError_t e = cudaMalloc(&s->d_jobs, sizeof(PicJob) * n);
+    cudaError_t e = cudaMalloc(&s->d_jobs, sizeof(PicJob) * n * 2); // one half per result set
     if (e != cudaSuccess) return SVTME_ERR_INSUFFICIENT_RESOURCES;
+    s->d_jobs_n = n;
     return SVTME_OK;
 }
 
@@ -505,25 +565,33 @@ static uint32_t launch_me_batch(SvtMeSession *s, uint32_t n, const int32_t *pic_
     uint32_t rc = ensure_batch(s, n);
     if (rc != SVTME_OK) return rc;
     if (need_units > s->fp_units_cap) { // the unit queue grows with the largest search window of the controls in use
-        CU_TRY(cudaStreamSynchronize(s->stream));
+        uint32_t rcs = sync_all(s);
+        if (rcs != SVTME_OK) return rcs;
         if (s->fp_units) cudaFree(s->fp_units);
         s->fp_units = nullptr; s->fp_units_cap = 0;
-        cudaError_t e = cudaMalloc(&s->fp_units, (size_t)need_units * sizeof(uint2));
+        cudaError_t e = cudaMalloc(&s->fp_units, (size_t)need_units * 2 * sizeof(uint2)); // one half per result set
         if (e != cudaSuccess) { fprintf(stderr, "[svtme_b200] cudaMalloc unit queue (%llu units): %s\n", (unsigned long long)need_units, cudaGetErrorString(e)); return SVTME_ERR_INSUFFICIENT_RESOURCES; }
         s->fp_units_cap = (uint32_t)need_units;
     }
     if (need_s16 > 0x7fffffffull) return SVTME_ERR_INSUFFICIENT_RESOURCES;
     if (need_s16 > s->s16_units_cap) {
-        CU_TRY(cudaStreamSynchronize(s->stream));
+        uint32_t rcs = sync_all(s);
+        if (rcs != SVTME_OK) return rcs;
         if (s->s16_units) cudaFree(s->s16_units);
         s->s16_units = nullptr; s->s16_units_cap = 0;
-        cudaError_t e = cudaMalloc(&s->s16_units, (size_t)need_s16 * sizeof(uint2));
+        cudaError_t e = cudaMalloc(&s->s16_units, (size_t)need_s16 * 2 * sizeof(uint2));
         if (e != cudaSuccess) { fprintf(stderr, "[svtme_b200] cudaMalloc HME unit queue (%llu units): %s\n", (unsigned long long)need_s16, cudaGetErrorString(e)); return SVTME_ERR_INSUFFICIENT_RESOURCES; }
         s->s16_units_cap = (uint32_t)need_s16;
     }
     const uint64_t seq = ++s->batch_seq;
     const int set = (int)(seq & 1);
-    if (s->dl_recorded[set]) CU_TRY(cudaStreamWaitEvent(s->stream, s->ev_dl[set], 0)); // the set's previous results left for the host
+    cudaStream_t cs = compute_stream(s, set);
+    if (s->dl_recorded[set]) CU_TRY(cudaStreamWaitEvent(cs, s->ev_dl[set], 0)); // the set's previous results left for the host
+    if (s->concurrency == 2) { // pictures whose pyramids were queued on the other compute stream
+        const int other = 1 - stream_index(s, set);
+        if (s->built_recorded[other]) CU_TRY(cudaStreamWaitEvent(cs, s->ev_built[other], 0));
+    }
+    PicJob *d_jobs = s->d_jobs + (size_t)set * s->d_jobs_n;
     s->h_jobs.resize(n);
     for (uint32_t i = 0; i < n; i++) {
         const SvtMePicParams *pp = &params[i];
@@ -531,9 +599,11 @@ static uint32_t launch_me_batch(SvtMeSession *s, uint32_t n, const int32_t *pic_
         memset(&job, 0, sizeof(job));
         job.pp  = *pp;
         job.src = s->pics[pic_ids[i]];
+        s->slot_last_seq[pic_ids[i]] = seq;
         for (int l = 0; l < pp->num_of_list_to_search; l++)
             for (int r = 0; r < pp->num_of_ref_pic_to_search[l]; r++) {
                 job.ref[l][r] = s->pics[pp->ref_pic_id[l][r]];
+                s->slot_last_seq[pp->ref_pic_id[l][r]] = seq;
             }
         job.pic_w = s->w; job.pic_h = s->h; job.b64_cols = s->b64_cols; job.b64_rows = s->b64_rows; job.n_b64 = s->n_b64;
         job.n_pus = pp->enable_me_8x8 ? 85 : 21;
@@ -559,19 +629,21 @@ static uint32_t launch_me_batch(SvtMeSession *s, uint32_t n, const int32_t *pic_
         job.fp_keys      = (unsigned long long *)(R + s->lay.fp_keys);
         // shared by the batch (slab 0)
         job.sad_ops      = (unsigned long long *)(s->res_slab + s->lay.ops);
-        job.fp_counters  = (uint32_t *)(s->res_slab + s->lay.fp_counters);
-        job.fp_units     = s->fp_units;
+        // per result set: counters in the set's first slab, one half of each unit queue
+        job.fp_counters  = (uint32_t *)(s->res_sets[set][0] + s->lay.fp_counters);
+        job.fp_units     = s->fp_units + (size_t)set * s->fp_units_cap;
         job.fp_units_cap = s->fp_units_cap;
-        job.s16_units     = s->s16_units;
-        job.s16_counters  = (uint32_t *)(s->res_slab + s->lay.fp_counters) + 4;
+        job.s16_units     = s->s16_units + (size_t)set * s->s16_units_cap;
+        job.s16_counters  = (uint32_t *)(s->res_sets[set][0] + s->lay.fp_counters) + 4;
         job.s16_units_cap = s->s16_units_cap;
     }
-    CU_TRY(cudaMemcpyAsync(s->d_jobs, s->h_jobs.data(), sizeof(PicJob) * n, cudaMemcpyHostToDevice, s->stream));
+    CU_TRY(cudaMemcpyAsync(d_jobs, s->h_jobs.data(), sizeof(PicJob) * n, cudaMemcpyHostToDevice, cs));
     cudaEvent_t e0 = nullptr, e1 = nullptr, e2 = nullptr;
     if (s->timing) {
         if (s->ev_used + 3 > s->ev.size()) {
             if (s->ev.size() >= 3 * 2048) {
                 CU_TRY(cudaStreamSynchronize(s->stream));
+                CU_TRY(cudaStreamSynchronize(s->stream2));
                 fold_events(s);
             } else {
                 for (int i = 0; i < 3; i++) {
@@ -584,9 +656,9 @@ static uint32_t launch_me_batch(SvtMeSession *s, uint32_t n, const int32_t *pic_
         e0 = s->ev[s->ev_used]; e1 = s->ev[s->ev_used + 1]; e2 = s->ev[s->ev_used + 2];
         s->ev_used += 3;
     }
-    s->launches += (uint64_t)svtme_launch_picture_me(s->h_jobs.data(), (int)n, s->d_jobs, s->stream, e0, e1, e2);
+    s->launches += (uint64_t)svtme_launch_picture_me(s->h_jobs.data(), (int)n, d_jobs, cs, e0, e1, e2);
     CU_TRY(cudaGetLastError());
-    CU_TRY(cudaEventRecord(s->ev_me[seq % 8], s->stream));
+    CU_TRY(cudaEventRecord(s->ev_me[seq % 8], cs));
     s->last_pps.assign(params, params + n);
     s->have_results = true;
     return SVTME_OK;
@@ -634,7 +706,7 @@ extern "C" uint32_t svtme_picture_me_batch(SvtMeSession *s, uint32_t n, const in
             rc = fetch(s, i, &results[i], 0);
             if (rc != SVTME_OK) return rc;
         }
-    if (sync) CU_TRY(cudaStreamSynchronize(results ? s->dl_stream : s->stream)); // the download waits for the batch's kernels
+    if (sync) CU_TRY(cudaStreamSynchronize(results ? s->dl_stream : compute_stream(s, (int)(s->batch_seq & 1)))); // the download waits for the batch's kernels
     return SVTME_OK;
 }
 
@@ -665,7 +737,7 @@ extern "C" uint32_t svtme_picture_me(SvtMeSession *s, int32_t pic_id, const SvtM
     uint32_t rc = launch_me_batch(s, 1, &pic_id, params);
     if (rc != SVTME_OK) return rc;
     if (results) return fetch(s, 0, results, sync);
-    if (sync) CU_TRY(cudaStreamSynchronize(s->stream));
+    if (sync) CU_TRY(cudaStreamSynchronize(compute_stream(s, (int)(s->batch_seq & 1))));
     return SVTME_OK;
 }
 
@@ -686,38 +758,45 @@ extern "C" uint32_t svtme_dg_detector_hme(SvtMeSession *s, int32_t src_pic_id, i
         if (rc != SVTME_OK) return rc;
         if (s->s16_units) cudaFree(s->s16_units);
         s->s16_units = nullptr; s->s16_units_cap = 0;
-        if (cudaMalloc(&s->s16_units, (size_t)need * sizeof(uint2)) != cudaSuccess) return SVTME_ERR_INSUFFICIENT_RESOURCES;
+        if (cudaMalloc(&s->s16_units, (size_t)need * 2 * sizeof(uint2)) != cudaSuccess) return SVTME_ERR_INSUFFICIENT_RESOURCES;
         s->s16_units_cap = need;
     }
     const uint64_t seq = ++s->batch_seq;
     const int set = (int)(seq & 1);
-    if (s->dl_recorded[set]) CU_TRY(cudaStreamWaitEvent(s->stream, s->ev_dl[set], 0));
+    cudaStream_t cs = compute_stream(s, set);
+    if (s->dl_recorded[set]) CU_TRY(cudaStreamWaitEvent(cs, s->ev_dl[set], 0));
+    if (s->concurrency == 2) {
+        const int other = 1 - stream_index(s, set);
+        if (s->built_recorded[other]) CU_TRY(cudaStreamWaitEvent(cs, s->ev_built[other], 0));
+    }
+    PicJob *d_job = s->d_jobs + (size_t)set * s->d_jobs_n;
     s->h_jobs.resize(1);
     PicJob &job = s->h_jobs[0];
     memset(&job, 0, sizeof(job));
     job.pp.ctrls.hme_search_method = SVTME_FULL_SAD_SEARCH; // :501
     job.src = s->pics[src_pic_id];
     job.ref[0][0] = s->pics[ref_pic_id];
+    s->slot_last_seq[src_pic_id] = s->slot_last_seq[ref_pic_id] = seq;
     job.pic_w = s->w; job.pic_h = s->h; job.b64_cols = s->b64_cols; job.b64_rows = s->b64_rows; job.n_b64 = s->n_b64;
     uint8_t *R = s->res_sets[set][0];
     job.hme_jobs      = (HmeJobG *)(R + s->lay.hme_jobs);
-    job.s16_units     = s->s16_units;
-    job.s16_counters  = (uint32_t *)(s->res_slab + s->lay.fp_counters) + 4;
-    job.fp_counters   = (uint32_t *)(s->res_slab + s->lay.fp_counters);
+    job.s16_units     = s->s16_units + (size_t)set * s->s16_units_cap;
+    job.s16_counters  = (uint32_t *)(R + s->lay.fp_counters) + 4;
+    job.fp_counters   = (uint32_t *)(R + s->lay.fp_counters);
     job.s16_units_cap = s->s16_units_cap;
-    CU_TRY(cudaMemcpyAsync(s->d_jobs, &job, sizeof(PicJob), cudaMemcpyHostToDevice, s->stream));
+    CU_TRY(cudaMemcpyAsync(d_job, &job, sizeof(PicJob), cudaMemcpyHostToDevice, cs));
     uint8_t *d_out = R + s->lay.ops + 32;
     unsigned long long *d_sad = (unsigned long long *)(R + s->lay.best_sad);
     int16_t *d_mv = (int16_t *)(R + s->lay.best_mv);
-    s->launches += (uint64_t)svtme_launch_dg_detector(&job, s->d_jobs, sa0, d_out, d_sad, d_mv, s->stream);
+    s->launches += (uint64_t)svtme_launch_dg_detector(&job, d_job, sa0, d_out, d_sad, d_mv, cs);
     CU_TRY(cudaGetLastError());
-    CU_TRY(cudaEventRecord(s->ev_me[seq % 8], s->stream));
+    CU_TRY(cudaEventRecord(s->ev_me[seq % 8], cs));
     s->have_results = false; // the slab no longer holds ME results
     struct { unsigned long long tot_dist; unsigned int tot_cplx, tot_active; int sum_in_vectors; } out;
-    CU_TRY(cudaMemcpyAsync(&out, d_out, sizeof(out), cudaMemcpyDeviceToHost, s->stream));
-    if (b64_sad) CU_TRY(cudaMemcpyAsync(b64_sad, d_sad, (size_t)s->n_b64 * 8, cudaMemcpyDeviceToHost, s->stream));
-    if (b64_mv) CU_TRY(cudaMemcpyAsync(b64_mv, d_mv, (size_t)s->n_b64 * 4, cudaMemcpyDeviceToHost, s->stream));
-    CU_TRY(cudaStreamSynchronize(s->stream));
+    CU_TRY(cudaMemcpyAsync(&out, d_out, sizeof(out), cudaMemcpyDeviceToHost, cs));
+    if (b64_sad) CU_TRY(cudaMemcpyAsync(b64_sad, d_sad, (size_t)s->n_b64 * 8, cudaMemcpyDeviceToHost, cs));
+    if (b64_mv) CU_TRY(cudaMemcpyAsync(b64_mv, d_mv, (size_t)s->n_b64 * 4, cudaMemcpyDeviceToHost, cs));
+    CU_TRY(cudaStreamSynchronize(cs));
     metrics->tot_dist = out.tot_dist; metrics->tot_cplx = out.tot_cplx; metrics->tot_active = out.tot_active;
     metrics->sum_in_vectors = out.sum_in_vectors;
     return SVTME_OK;
@@ -747,8 +826,9 @@ extern "C" uint32_t svtme_fetch_hme_state(SvtMeSession *s, void *dst, size_t dst
     if (!s || !dst || dst_bytes < (size_t)s->n_b64 * sizeof(SbState)) return SVTME_ERR_BAD_PARAMETER;
     std::lock_guard<std::mutex> g(s->mu);
     CU_TRY(cudaSetDevice(s->device));
-    CU_TRY(cudaMemcpyAsync(dst, s->res_sets[s->batch_seq & 1][0] + s->lay.sb_state, (size_t)s->n_b64 * sizeof(SbState), cudaMemcpyDeviceToHost, s->stream));
-    CU_TRY(cudaStreamSynchronize(s->stream));
+    cudaStream_t cs = compute_stream(s, (int)(s->batch_seq & 1));
+    CU_TRY(cudaMemcpyAsync(dst, s->res_sets[s->batch_seq & 1][0] + s->lay.sb_state, (size_t)s->n_b64 * sizeof(SbState), cudaMemcpyDeviceToHost, cs));
+    CU_TRY(cudaStreamSynchronize(cs));
     return SVTME_OK;
 }
 
@@ -757,6 +837,7 @@ extern "C" uint32_t svtme_session_sad_ops(SvtMeSession *s, int reset, uint64_t *
     std::lock_guard<std::mutex> g(s->mu);
     CU_TRY(cudaSetDevice(s->device));
     unsigned long long v[2] = {0, 0};
+    CU_TRY(cudaStreamSynchronize(s->stream2));
     CU_TRY(cudaMemcpyAsync(v, s->res_slab + s->lay.ops, sizeof(v), cudaMemcpyDeviceToHost, s->stream));
     CU_TRY(cudaStreamSynchronize(s->stream));
     if (hme_ops) *hme_ops = v[0];

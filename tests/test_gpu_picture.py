@@ -211,3 +211,58 @@ def test_batched_uploads_build_the_same_pyramids():
             for slot in (i, n + i, 2 * n + i):
                 np.testing.assert_array_equal(s.download_plane(slot, lvl), want[lvl], err_msg="picture %d slot %d level %d" % (i, slot, lvl))
     s.close()
+
+
+def test_two_compute_streams_give_the_same_results():
+    """svtme_session_set_concurrency(2): consecutive batches on alternating compute streams, uploads in between (host and
+    device), slots re-used while the other stream may still read them"""
+    import torch
+    from svt_av1_psy_b200 import abi
+    from svt_av1_psy_b200.synth import PanningNoise
+    w, h, n_slots = 320, 192, 20
+    clip = PanningNoise(w, h, seed=77, vx=2, vy=2, max_frames=64)
+
+    def run(concurrency):
+        s = me.Session(w, h, max_pictures=n_slots)
+        s.set_concurrency(concurrency)
+        outs, pend = [], []
+        for t in range(8):
+            s.upload(t % n_slots, clip.frame(t))
+        dev = {}
+        for k in range(7):
+            new = list(range(8 + 4 * k, 12 + 4 * k))
+            if k % 2:  # device uploads every other round
+                for t in new:
+                    dev[t] = torch.from_numpy(clip.frame(t)).cuda()
+                torch.cuda.synchronize()
+                s.upload_batch([t % n_slots for t in new], [dev[t].data_ptr() for t in new], w, "device")
+            else:
+                frames = [clip.frame(t) for t in new]
+                s.upload_batch([t % n_slots for t in new], [f.ctypes.data for f in frames], w, "host8")
+            ids, prms = [], []
+            for poc in range(4 * k + 2, 4 * k + 6):
+                l0, l1 = [poc - 1, poc - 2], [poc + 1]
+                refs = [[clip.frame(p) for p in l0], [clip.frame(p) for p in l1]]
+                p = params_from_encoder_inputs(clip.frame(poc), refs, [l0, l1], poc, 5, temporal_layer=2, hier_levels=5)
+                for l, lst in enumerate((l0, l1)):
+                    for r, rp in enumerate(lst):
+                        p.ref_pic_id[l][r] = rp % n_slots
+                ids.append(poc % n_slots)
+                prms.append(p)
+            res = [abi.PicResultArrays(w, h, p, pinned=True) for p in prms]
+            s.me_batch(ids, prms, res, sync=False)
+            pend.append((s.batch_seq(), res))
+            if len(pend) > 2:
+                seq, r = pend.pop(0)
+                s.wait_batch(seq)
+                outs.append([x.snapshot() for x in r])
+        s.sync()
+        outs += [[x.snapshot() for x in r] for _, r in pend]
+        s.close()
+        return outs
+
+    a, b = run(1), run(2)
+    assert len(a) == len(b) == 7
+    for ba, bb in zip(a, b):
+        for ra, rb in zip(ba, bb):
+            compare(ra, rb, fields=list(ra.FIELDS))
