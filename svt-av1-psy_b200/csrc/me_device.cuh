@@ -1,17 +1,18 @@
 // me_device.cuh — device-side data layout and the inner byte-SAD routines (sm_100a).
 //
 // Data layout in HBM
-//   * one slab per picture: three replicate-padded luma planes (full: pad 72, 1/4: pad 32,
-//     1/16: pad 16; reference_object.c:320-380, enc_handle.c:4485-4497), row stride rounded up to
-//     16 bytes, 512 bytes of slack before/after so that 4-byte aligned staging reads never leave
-//     the allocation.
-//   * per-b64 HME state (SbState) written by k_hme and read by k_fullpel / k_post.
-//   * per-(b64,list,ref) best SAD / MV arrays [85] written by k_fullpel (MeContext
+//   * one slab per picture: three replicate-padded luma planes (full: pad 80, 1/4: pad 32,
+//     1/16: pad 16; the reference pads 72/32/16, reference_object.c:320-380, enc_handle.c:4485-4497),
+//     row stride rounded up to 16 bytes, 512 bytes of slack before/after so that 16-byte aligned
+//     TMA boxes and 4-byte aligned staging reads never leave the allocation.
+//   * per-b64 HME state (SbState) written by k_hme_ctl and read by k_fp / k_post.
+//   * per-(b64,list,ref) best SAD / MV arrays [85] written by k_fp / k_fp_big (MeContext
 //     p_sb_best_sad / p_sb_best_mv, me_context.h:395-396).
 //
-// The arithmetic unit of the whole path is VABSDIFF4.U8.ACC (__vsadu4 + add): 4 pixel
-// |a-b| accumulated per lane-instruction. Measured on B200: 41.5 lane-instr/clk/SM
-// (profiles/r01_pipe_microbench.txt) = the integer roofline of this library.
+// The arithmetic unit of the whole path is VABSDIFF4.U8.ACC (sad4_acc below): 4 pixel |a-b|
+// accumulated per lane-instruction. The integer-ALU pipe it shares with shifts, adds and compares
+// issues 64 lane-instr/clk/SM on B200 (profiles/r01_vabs_peak_microbench.txt) =
+// the integer roofline of this library.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -56,7 +57,7 @@ struct SbState {
 };
 
 // One window search of the HME stage (pre-HME region or HME level-N quadrant), set up by k_hme_ctl
-// and executed by k_search16 / k_search_wide. 32 jobs per b64: slot = (list*4+ref)*4 + quadrant
+// and executed by k_search16 (1/16 plane) / k_search_blk (1/4 and full planes). 32 jobs per b64: slot = (list*4+ref)*4 + quadrant
 // (pre-HME uses quadrant 0/1 for its two regions).
 struct HmeJobG {
     unsigned long long key;  // (sad << 32) | (y*sa_w + x), atomicMin over the job's tiles
