@@ -140,29 +140,63 @@ __device__ __forceinline__ uint32_t sad4_acc(uint32_t a, uint32_t b, uint32_t c)
     return d;
 }
 
+// (hi:lo) >> 8*NB for a compile-time NB = 1..3 (bytes): one SHF on the integer-ALU pipe, the pipe that bounds every
+// search kernel. SVTME_FSR_IMAD=1 builds the shift from IMAD.HI + IMAD instead (multiplier from constant memory so that
+// ptxas cannot turn it back into shifts) to use the FMA pipe these kernels leave idle. MEASURED SLOWER on B200 and
+// therefore off: IMAD.HI issues at 32 lane-instr/clk/SM, half the IMAD rate, and slows the ALU pipe down with it;
+// 7090 against 7628 frames/s on the 1080p bench (profiles/r01_fsr_imad_experiment.md, tools/microbench/fsr_pipes.cu).
+#ifndef SVTME_FSR_IMAD
+#define SVTME_FSR_IMAD 0
+#endif
+static __constant__ uint32_t c_fsr_mul[4] = {0u, 1u << 24, 1u << 16, 1u << 8};
+template <int NB>
+__device__ __forceinline__ uint32_t fsr_bytes(uint32_t lo, uint32_t hi) {
+    if (NB == 0) return lo;
+#if SVTME_FSR_IMAD
+    uint32_t h, r;
+    const uint32_t m = c_fsr_mul[NB];
+    asm("mul.hi.u32 %0, %1, %2;" : "=r"(h) : "r"(lo), "r"(m));
+    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(hi), "r"(m), "r"(h));
+    return r;
+#else
+    return __funnelshift_r(lo, hi, 8 * NB);
+#endif
+}
+
+// sh[j][i] = the word that starts j+1 bytes into w[i] (i = 0..4): the 15 shifted words the 8 positions of a strip share
+__device__ __forceinline__ void strip_shifted_words(const uint32_t (&w)[6], uint32_t (&sh)[3][5]) {
+#pragma unroll
+    for (int i = 0; i < 5; i++) {
+        sh[0][i] = fsr_bytes<1>(w[i], w[i + 1]);
+        sh[1][i] = fsr_bytes<2>(w[i], w[i + 1]);
+        sh[2][i] = fsr_bytes<3>(w[i], w[i + 1]);
+    }
+}
+
 // acc[p] += SAD of the 16-byte strip s[0..3] against the strip starting p bytes into w[0..5]
-// for the 8 consecutive search positions p = 0..7. 32 VABSDIFF4.U8.ACC + 24 SHF.
+// for the 8 consecutive search positions p = 0..7. 32 VABSDIFF4.U8.ACC + 15 funnel shifts.
 __device__ __forceinline__ void strip16_sad8(const uint32_t (&w)[6], const uint32_t (&s)[4], uint32_t (&acc)[8]) {
+    uint32_t sh[3][5];
+    strip_shifted_words(w, sh);
 #pragma unroll
     for (int p = 0; p < 8; p++) {
-        const int o = p >> 2, sh = (p & 3) * 8;
+        const int o = p >> 2, j = p & 3;
 #pragma unroll
-        for (int k = 0; k < 4; k++) {
-            const uint32_t v = sh ? __funnelshift_r(w[o + k], w[o + k + 1], sh) : w[o + k];
-            acc[p] = sad4_acc(v, s[k], acc[p]);
-        }
+        for (int k = 0; k < 4; k++) acc[p] = sad4_acc(j ? sh[j - 1][o + k] : w[o + k], s[k], acc[p]);
     }
 }
 
 // same, but the strip is split into its left and right 8 pixels (two 8x8 blocks side by side)
 __device__ __forceinline__ void strip16_sad8_split(const uint32_t (&w)[6], const uint32_t (&s)[4],
                                                    uint32_t (&accl)[8], uint32_t (&accr)[8]) {
+    uint32_t sh[3][5];
+    strip_shifted_words(w, sh);
 #pragma unroll
     for (int p = 0; p < 8; p++) {
-        const int o = p >> 2, sh = (p & 3) * 8;
+        const int o = p >> 2, j = p & 3;
 #pragma unroll
         for (int k = 0; k < 4; k++) {
-            const uint32_t v = sh ? __funnelshift_r(w[o + k], w[o + k + 1], sh) : w[o + k];
+            const uint32_t v = j ? sh[j - 1][o + k] : w[o + k];
             if (k < 2)
                 accl[p] = sad4_acc(v, s[k], accl[p]);
             else

@@ -220,9 +220,9 @@ __device__ __forceinline__ void s16_tile_tasks_vb(uint32_t buf, int pitch, uint3
             for (int i = 0; i < 6; i++) w[i] = __funnelshift_r(c[i], c[i + 1], t8);
 #pragma unroll
             for (int i = 0; i < 5; i++) {
-                s1[i] = __funnelshift_r(w[i], w[i + 1], 8);
-                s2[i] = __funnelshift_r(w[i], w[i + 1], 16);
-                s3[i] = __funnelshift_r(w[i], w[i + 1], 24);
+                s1[i] = fsr_bytes<1>(w[i], w[i + 1]);
+                s2[i] = fsr_bytes<2>(w[i], w[i + 1]);
+                s3[i] = fsr_bytes<3>(w[i], w[i + 1]);
             }
 #pragma unroll
             for (int g = 0; g < G; g++) {
