@@ -110,6 +110,40 @@ def ref_lib():
     return _ref
 
 
+_wrap = None
+
+
+def wrap_available():
+    return os.path.exists(os.path.join(HERE, "_ref", "libsvtref_wrap.so"))
+
+
+def wrap_lib():
+    """oracle/_ref/libsvtref_wrap.so: the reference's ME callers linked with -Wl,--wrap and the product's
+    reference-side binding (svt-av1-psy_b200/shim/svtme_wrap.c): svt_aom_motion_estimation_b64 and
+    dg_detector_hme_level0 are served by the GPU library. Same harness entry points as ref_lib()."""
+    global _wrap
+    if _wrap is None:
+        path = os.path.join(HERE, "_ref", "libsvtref_wrap.so")
+        if not os.path.exists(path):
+            raise RuntimeError("oracle/_ref/libsvtref_wrap.so not built (needs /root/reference): run `make -C oracle ref`")
+        _wrap = C.CDLL(path)
+        _wrap.ref_me_picture.argtypes = [C.POINTER(RefMePicIn), C.POINTER(abi.MePicResults), C.c_void_p,
+                                         C.POINTER(C.c_double)]
+        _wrap.ref_me_picture.restype = C.c_int
+        _wrap.ref_derive_params.argtypes = [C.POINTER(RefMePicIn), C.POINTER(abi.MePicParams)]
+        _wrap.ref_derive_params_shim.argtypes = [C.POINTER(RefMePicIn), C.POINTER(abi.MePicParams)]
+        _wrap.svtme_shim_stats.argtypes = [C.POINTER(C.c_uint64)] * 3
+        _wrap.svtme_shim_stats.restype = None
+    return _wrap
+
+
+def shim_stats():
+    """(pictures, temporal-filter pairs, detector pairs) the wrapped library has run on the GPU"""
+    a, b, c = C.c_uint64(0), C.c_uint64(0), C.c_uint64(0)
+    wrap_lib().svtme_shim_stats(C.byref(a), C.byref(b), C.byref(c))
+    return a.value, b.value, c.value
+
+
 def oracle_lib():
     global _orc
     if _orc is None:
@@ -159,22 +193,46 @@ def make_pic_in(src, refs, ref_pocs, poc, enc_mode, qp=35, temporal_layer=1, hie
     return pin
 
 
-def ref_derive_params(pin):
+def ref_derive_params(pin, lib=None):
     p = abi.MePicParams()
-    ref_lib().ref_derive_params(C.byref(pin), C.byref(p))
+    (lib or ref_lib()).ref_derive_params(C.byref(pin), C.byref(p))
     return p
 
 
-def ref_me_picture(pin, params=None, debug=False):
-    """run the reference's own ME on one picture -> (PicResultArrays, debug array or None, seconds)"""
-    params = params or ref_derive_params(pin)
+def ref_derive_params_shim(pin):
+    """the parameters as the product's shim flattens them from the reference's MeContext / PCS"""
+    p = abi.MePicParams()
+    rc = wrap_lib().ref_derive_params_shim(C.byref(pin), C.byref(p))
+    assert rc == 0
+    return p
+
+
+def ref_me_picture(pin, params=None, debug=False, lib=None):
+    """run the reference's own ME on one picture -> (PicResultArrays, debug array or None, seconds).
+    lib=wrap_lib(): the same caller code, with the b64 function served by the GPU library through the shim."""
+    params = params or ref_derive_params(pin, lib)
     res = abi.PicResultArrays(pin.width, pin.height, params)
     dbg = np.zeros(res.n_b64, dtype=DEBUG_DTYPE) if debug else None
     sec = C.c_double(0)
-    rc = ref_lib().ref_me_picture(C.byref(pin), C.byref(res.struct), ptr(dbg) if debug else None, C.byref(sec))
+    rc = (lib or ref_lib()).ref_me_picture(C.byref(pin), C.byref(res.struct), ptr(dbg) if debug else None, C.byref(sec))
     if rc != 0:
         raise RuntimeError("ref_me_picture failed rc=%d" % rc)
     return res, dbg, sec.value
+
+
+def ref_me_picture_mt(pin, n_threads, params=None, lib=None):
+    """the same picture with its b64s dealt out to n_threads threads, one MeContext each (the ME segment threads)"""
+    lib = lib or ref_lib()
+    params = params or ref_derive_params(pin, lib)
+    res = abi.PicResultArrays(pin.width, pin.height, params)
+    f = lib.ref_me_picture_mt
+    f.argtypes = [C.POINTER(RefMePicIn), C.POINTER(abi.MePicResults), C.c_int, C.POINTER(C.c_double)]
+    f.restype = C.c_int
+    sec = C.c_double(0)
+    rc = f(C.byref(pin), C.byref(res.struct), n_threads, C.byref(sec))
+    if rc != 0:
+        raise RuntimeError("ref_me_picture_mt failed rc=%d" % rc)
+    return res, sec.value
 
 
 def dg_detector(lib, prefix, src, ref, per_b64=False):
@@ -205,7 +263,7 @@ class RefTfIn(C.Structure):
 
 
 def ref_tf_me_picture(centre, ref, enc_mode, hme_me_level, qp_opt=0, me_exit_th=0, qp=35, centre_poc=8, ref_poc=7,
-                      temporal_layer=0, is_ref=1, simd=0, debug=True):
+                      temporal_layer=0, is_ref=1, simd=0, debug=True, lib=None):
     """temporal-filter ME of `centre` against `ref` through the reference's own code
     -> (params, PicResultArrays, debug array)"""
     h, w = centre.shape
@@ -221,7 +279,7 @@ def ref_tf_me_picture(centre, ref, enc_mode, hme_me_level, qp_opt=0, me_exit_th=
     tmp.enable_me_8x8, tmp.max_refs, tmp.max_cand = 1, 2, 3
     res = abi.PicResultArrays(w, h, tmp)
     dbg = np.zeros(res.n_b64, dtype=DEBUG_DTYPE) if debug else None
-    f = ref_lib().ref_tf_me_picture
+    f = (lib or ref_lib()).ref_tf_me_picture
     f.argtypes = [C.POINTER(RefTfIn), C.POINTER(abi.MePicParams), C.POINTER(abi.MePicResults), C.c_void_p]
     f.restype = C.c_int
     rc = f(C.byref(tin), C.byref(params), C.byref(res.struct), ptr(dbg) if debug else None)

@@ -23,6 +23,7 @@
 #include <stdlib.h>
 #include <string.h>
 #include <time.h>
+#include <pthread.h>
 
 #include "definitions.h"
 #include "common_dsp_rtcd.h"
@@ -181,6 +182,14 @@ void ref_unpack_10bit_msb(const uint16_t *in16, uint32_t in_stride, uint8_t *out
     uint8_t *lsb = (uint8_t *)malloc((size_t)s2 * height);
     svt_unpack_and_2bcompress_c((uint16_t *)in16, in_stride, out8, out_stride, lsb, s2, width, height);
     free(lsb);
+}
+
+/* libsvtref_wrap.so only (the same harness linked with -Wl,--wrap and svt-av1-psy_b200/shim/svtme_wrap.c): the shim
+   keeps device copies of host pictures keyed by (picture number, plane address); this harness frees and reallocates its
+   planes for every call, so the copies are dropped around each one. Absent (NULL) in libsvtref.so. */
+extern void svtme_shim_forget_pictures(void) __attribute__((weak));
+static void shim_forget(void) {
+    if (svtme_shim_forget_pictures) svtme_shim_forget_pictures();
 }
 
 /* ---------------- picture planes (PA reference object geometry) ---------------- */
@@ -486,6 +495,33 @@ int ref_derive_params(const RefMePicIn *in, SvtMePicParams *out) {
     return 0;
 }
 
+/* The same derivation, exported through the PRODUCT's reference-side binding (svt-av1-psy_b200/shim/svtme_wrap.c,
+   svtme_shim_flatten) instead of export_params above: libsvtref_wrap.so only. Lets the CPU tests check the shim's
+   MeContext/PCS -> SvtMePicParams flattening against the golden parameter fixture without a GPU. */
+extern void svtme_shim_flatten(const PictureParentControlSet *pcs, const MeContext *m, SvtMePicParams *o) __attribute__((weak));
+int ref_derive_params_shim(const RefMePicIn *in, SvtMePicParams *out) {
+    if (!svtme_shim_flatten) return -2;
+    Fake f;
+    fake_init(&f, in);
+    PictureParentControlSet *pcs = f.pcs;
+    MeContext *m = (MeContext *)calloc(1, sizeof(MeContext));
+    m->me_type   = ME_OPEN_LOOP;
+    svt_aom_sig_deriv_me(f.scs, pcs, m);
+    /* what me_process.c:219-262 sets before every b64 call */
+    m->num_of_list_to_search       = (pcs->slice_type == P_SLICE) ? 1 : 2;
+    m->num_of_ref_pic_to_search[0] = pcs->ref_list0_count_try;
+    if (pcs->slice_type == B_SLICE) m->num_of_ref_pic_to_search[1] = pcs->ref_list1_count_try;
+    m->temporal_layer_index = pcs->temporal_layer_index;
+    m->is_ref               = pcs->is_ref;
+    for (int i = 0; i < m->num_of_list_to_search; i++)
+        for (int j = 0; j < m->num_of_ref_pic_to_search[i]; j++)
+            m->me_ds_ref_array[i][j].picture_number = in->ref_picture_number[i][j];
+    svtme_shim_flatten(pcs, m, out);
+    free(m);
+    fake_free(&f);
+    return 0;
+}
+
 static double now_s(void) {
     struct timespec ts;
     clock_gettime(CLOCK_MONOTONIC, &ts);
@@ -493,126 +529,116 @@ static double now_s(void) {
 }
 
 /* ---------------- whole-picture ME through the reference's own b64 function ---------------- */
-int ref_me_picture(const RefMePicIn *in, SvtMePicResults *res, RefMeDebug *dbg, double *seconds) {
+static void dump_debug(RefMeDebug *d, const MeContext *me);
+typedef struct PicRun {
+    const RefMePicIn *in;
+    Fake              f;
+    Planes            src, refs[2][4];
+    SvtMePicResults  *res;
+    RefMeDebug       *dbg;
+} PicRun;
+
+/* one b64 the way svt_aom_motion_estimation_kernel does it (me_process.c:174-271), then the dump of what the call left
+   in the MeContext and in the PCS; returns the seconds spent inside svt_aom_motion_estimation_b64 */
+static double run_b64(PicRun *run, MeContext *me, uint32_t x_b64, uint32_t y_b64) {
+    const RefMePicIn        *in  = run->in;
+    Fake                    *f   = &run->f;
+    PictureParentControlSet *pcs = f->pcs;
+    SvtMePicResults         *res = run->res;
+    const uint32_t n_pus = f->n_pus;
+    const uint8_t  max_refs = f->me_data->max_refs, max_cand = f->me_data->max_cand;
+
+    uint32_t b64_index    = (uint16_t)(x_b64 + y_b64 * f->b64_w);
+    uint32_t b64_origin_x = x_b64 * 64, b64_origin_y = y_b64 * 64;
+    EbPictureBufferDesc *ip = &run->src.full, *qp = &run->src.quarter, *sp = &run->src.sixteenth;
+    uint32_t buffer_index = (ip->org_y + b64_origin_y) * ip->stride_y + ip->org_x + b64_origin_x;
+    me->b64_src_ptr    = &ip->buffer_y[buffer_index];
+    me->b64_src_stride = ip->stride_y;
+    if (me->enable_hme_level1_flag) {
+        buffer_index = (qp->org_y + (b64_origin_y >> 1)) * qp->stride_y + qp->org_x + (b64_origin_x >> 1);
+        me->quarter_b64_buffer        = &qp->buffer_y[buffer_index];
+        me->quarter_b64_buffer_stride = qp->stride_y;
+    }
+    if (me->enable_hme_level0_flag) {
+        buffer_index = (sp->org_y + (b64_origin_y >> 2)) * sp->stride_y + sp->org_x + (b64_origin_x >> 2);
+        me->sixteenth_b64_buffer        = &sp->buffer_y[buffer_index];
+        me->sixteenth_b64_buffer_stride = sp->stride_y;
+    }
+    me->me_type                     = ME_OPEN_LOOP;
+    me->num_of_list_to_search       = (pcs->slice_type == P_SLICE) ? 1 : 2;
+    me->num_of_ref_pic_to_search[0] = pcs->ref_list0_count_try;
+    if (pcs->slice_type == B_SLICE) me->num_of_ref_pic_to_search[1] = pcs->ref_list1_count_try;
+    me->temporal_layer_index = pcs->temporal_layer_index;
+    me->is_ref               = pcs->is_ref;
+    for (int i = 0; i < me->num_of_list_to_search; i++)
+        for (int j = 0; j < me->num_of_ref_pic_to_search[i]; j++) {
+            me->me_ds_ref_array[i][j].picture_ptr           = &run->refs[i][j].full;
+            me->me_ds_ref_array[i][j].quarter_picture_ptr   = &run->refs[i][j].quarter;
+            me->me_ds_ref_array[i][j].sixteenth_picture_ptr = &run->refs[i][j].sixteenth;
+            me->me_ds_ref_array[i][j].picture_number        = in->ref_picture_number[i][j];
+        }
+
+    double t0 = now_s();
+    svt_aom_motion_estimation_b64(pcs, b64_index, b64_origin_x, b64_origin_y, me, ip);
+    const double t_me = now_s() - t0;
+
+    /* ---- dump ---- */
+    if (res) {
+        for (int l = 0; l < 2; l++)
+            for (int r = 0; r < 4; r++) {
+                size_t o = ((size_t)b64_index * 2 + l) * 4 + r;
+                int searched = l < me->num_of_list_to_search && r < me->num_of_ref_pic_to_search[l];
+                /* entries of refs with do_ref == 0 are stale: masked */
+                int valid = searched && me->search_results[l][r].do_ref;
+                if (res->p_sb_best_sad)
+                    for (int p = 0; p < 85; p++)
+                        res->p_sb_best_sad[o * 85 + p] = valid ? me->p_sb_best_sad[l][r][p] : 0;
+                if (res->p_sb_best_mv)
+                    for (int p = 0; p < 85; p++)
+                        res->p_sb_best_mv[o * 85 + p] = valid ? me->p_sb_best_mv[l][r][p] : 0;
+                if (res->search_results) {
+                    SvtMeSearchResult *sr = &res->search_results[o];
+                    memset(sr, 0, sizeof(*sr));
+                    if (searched) {
+                        sr->hme_sc_x = me->search_results[l][r].hme_sc_x;
+                        sr->hme_sc_y = me->search_results[l][r].hme_sc_y;
+                        sr->do_ref   = me->search_results[l][r].do_ref;
+                        sr->hme_sad  = me->search_results[l][r].hme_sad;
+                    }
+                }
+            }
+        MeSbResults *r = f->me_results[b64_index];
+        if (res->total_me_candidate_index)
+            memcpy(res->total_me_candidate_index + (size_t)b64_index * n_pus, r->total_me_candidate_index, n_pus);
+        if (res->me_mv_array)
+            memcpy(res->me_mv_array + (size_t)b64_index * n_pus * max_refs, r->me_mv_array,
+                   (size_t)n_pus * max_refs * 4);
+        if (res->me_candidate_array)
+            memcpy(res->me_candidate_array + (size_t)b64_index * n_pus * max_cand, r->me_candidate_array,
+                   (size_t)n_pus * max_cand);
+    }
+    if (run->dbg) dump_debug(&run->dbg[b64_index], me);
+    return t_me;
+}
+
+static int pic_run_init(PicRun *run, const RefMePicIn *in, SvtMePicResults *res, RefMeDebug *dbg) {
     if (in->width % 8 || in->height % 8 || in->num_lists < 1 || in->num_lists > 2) return -1;
     set_rtcd(in->simd);
-    Fake f;
-    fake_init(&f, in);
-    PictureParentControlSet *pcs = f.pcs;
-    SequenceControlSet      *scs = f.scs;
-
-    Planes src;
-    Planes refs[2][4];
-    planes_alloc(&src, in->src_luma, in->width, in->height);
+    shim_forget();
+    run->in = in; run->res = res; run->dbg = dbg;
+    fake_init(&run->f, in);
+    planes_alloc(&run->src, in->src_luma, in->width, in->height);
     for (int l = 0; l < in->num_lists; l++)
-        for (int r = 0; r < in->ref_count[l]; r++) planes_alloc(&refs[l][r], in->ref_luma[l][r], in->width, in->height);
+        for (int r = 0; r < in->ref_count[l]; r++) planes_alloc(&run->refs[l][r], in->ref_luma[l][r], in->width, in->height);
+    return 0;
+}
 
-    MeContext *me = (MeContext *)calloc(1, sizeof(MeContext));
-    me->me_type   = ME_OPEN_LOOP;
-    svt_aom_sig_deriv_me(scs, pcs, me); /* me_process.c:121 */
-
-    const uint32_t n_pus = f.n_pus;
-    const uint8_t  max_refs = f.me_data->max_refs, max_cand = f.me_data->max_cand;
-    double t_me = 0.0;
-
-    /* me_process.c:174-271 */
-    for (uint32_t y_b64 = 0; y_b64 < f.b64_h; y_b64++) {
-        for (uint32_t x_b64 = 0; x_b64 < f.b64_w; x_b64++) {
-            uint32_t b64_index    = (uint16_t)(x_b64 + y_b64 * f.b64_w);
-            uint32_t b64_origin_x = x_b64 * 64, b64_origin_y = y_b64 * 64;
-            EbPictureBufferDesc *ip = &src.full, *qp = &src.quarter, *sp = &src.sixteenth;
-            uint32_t buffer_index = (ip->org_y + b64_origin_y) * ip->stride_y + ip->org_x + b64_origin_x;
-            me->b64_src_ptr    = &ip->buffer_y[buffer_index];
-            me->b64_src_stride = ip->stride_y;
-            if (me->enable_hme_level1_flag) {
-                buffer_index = (qp->org_y + (b64_origin_y >> 1)) * qp->stride_y + qp->org_x + (b64_origin_x >> 1);
-                me->quarter_b64_buffer        = &qp->buffer_y[buffer_index];
-                me->quarter_b64_buffer_stride = qp->stride_y;
-            }
-            if (me->enable_hme_level0_flag) {
-                buffer_index = (sp->org_y + (b64_origin_y >> 2)) * sp->stride_y + sp->org_x + (b64_origin_x >> 2);
-                me->sixteenth_b64_buffer        = &sp->buffer_y[buffer_index];
-                me->sixteenth_b64_buffer_stride = sp->stride_y;
-            }
-            me->me_type                     = ME_OPEN_LOOP;
-            me->num_of_list_to_search       = (pcs->slice_type == P_SLICE) ? 1 : 2;
-            me->num_of_ref_pic_to_search[0] = pcs->ref_list0_count_try;
-            if (pcs->slice_type == B_SLICE) me->num_of_ref_pic_to_search[1] = pcs->ref_list1_count_try;
-            me->temporal_layer_index = pcs->temporal_layer_index;
-            me->is_ref               = pcs->is_ref;
-            for (int i = 0; i < me->num_of_list_to_search; i++)
-                for (int j = 0; j < me->num_of_ref_pic_to_search[i]; j++) {
-                    me->me_ds_ref_array[i][j].picture_ptr           = &refs[i][j].full;
-                    me->me_ds_ref_array[i][j].quarter_picture_ptr   = &refs[i][j].quarter;
-                    me->me_ds_ref_array[i][j].sixteenth_picture_ptr = &refs[i][j].sixteenth;
-                    me->me_ds_ref_array[i][j].picture_number        = in->ref_picture_number[i][j];
-                }
-
-            double t0 = now_s();
-            svt_aom_motion_estimation_b64(pcs, b64_index, b64_origin_x, b64_origin_y, me, ip);
-            t_me += now_s() - t0;
-
-            /* ---- dump ---- */
-            if (res) {
-                for (int l = 0; l < 2; l++)
-                    for (int r = 0; r < 4; r++) {
-                        size_t o = ((size_t)b64_index * 2 + l) * 4 + r;
-                        int searched = l < me->num_of_list_to_search && r < me->num_of_ref_pic_to_search[l];
-                        /* entries of refs with do_ref == 0 are stale: masked */
-                        int valid = searched && me->search_results[l][r].do_ref;
-                        if (res->p_sb_best_sad)
-                            for (int p = 0; p < 85; p++)
-                                res->p_sb_best_sad[o * 85 + p] = valid ? me->p_sb_best_sad[l][r][p] : 0;
-                        if (res->p_sb_best_mv)
-                            for (int p = 0; p < 85; p++)
-                                res->p_sb_best_mv[o * 85 + p] = valid ? me->p_sb_best_mv[l][r][p] : 0;
-                        if (res->search_results) {
-                            SvtMeSearchResult *sr = &res->search_results[o];
-                            memset(sr, 0, sizeof(*sr));
-                            if (searched) {
-                                sr->hme_sc_x = me->search_results[l][r].hme_sc_x;
-                                sr->hme_sc_y = me->search_results[l][r].hme_sc_y;
-                                sr->do_ref   = me->search_results[l][r].do_ref;
-                                sr->hme_sad  = me->search_results[l][r].hme_sad;
-                            }
-                        }
-                    }
-                MeSbResults *r = f.me_results[b64_index];
-                if (res->total_me_candidate_index)
-                    memcpy(res->total_me_candidate_index + (size_t)b64_index * n_pus, r->total_me_candidate_index, n_pus);
-                if (res->me_mv_array)
-                    memcpy(res->me_mv_array + (size_t)b64_index * n_pus * max_refs, r->me_mv_array,
-                           (size_t)n_pus * max_refs * 4);
-                if (res->me_candidate_array)
-                    memcpy(res->me_candidate_array + (size_t)b64_index * n_pus * max_cand, r->me_candidate_array,
-                           (size_t)n_pus * max_cand);
-            }
-            if (dbg) {
-                RefMeDebug *d = &dbg[b64_index];
-                memcpy(d->x_hme_l0, me->x_hme_level0_search_center, sizeof(d->x_hme_l0));
-                memcpy(d->y_hme_l0, me->y_hme_level0_search_center, sizeof(d->y_hme_l0));
-                memcpy(d->x_hme_l1, me->x_hme_level1_search_center, sizeof(d->x_hme_l1));
-                memcpy(d->y_hme_l1, me->y_hme_level1_search_center, sizeof(d->y_hme_l1));
-                memcpy(d->x_hme_l2, me->x_hme_level2_search_center, sizeof(d->x_hme_l2));
-                memcpy(d->y_hme_l2, me->y_hme_level2_search_center, sizeof(d->y_hme_l2));
-                memcpy(d->hme_l0_sad, me->hme_level0_sad, sizeof(d->hme_l0_sad));
-                memcpy(d->hme_l1_sad, me->hme_level1_sad, sizeof(d->hme_l1_sad));
-                memcpy(d->hme_l2_sad, me->hme_level2_sad, sizeof(d->hme_l2_sad));
-                for (int l = 0; l < 2; l++)
-                    for (int r = 0; r < 4; r++) {
-                        for (int s = 0; s < 2; s++) {
-                            d->prehme_mv_x[l][r][s] = me->prehme_data[l][r][s].best_mv.as_mv.col;
-                            d->prehme_mv_y[l][r][s] = me->prehme_data[l][r][s].best_mv.as_mv.row;
-                            d->prehme_sad[l][r][s]  = me->prehme_data[l][r][s].sad;
-                        }
-                        d->zz_sad[l][r]               = me->zz_sad[l][r];
-                        d->reduce_me_sr_divisor[l][r] = me->reduce_me_sr_divisor[l][r];
-                    }
-            }
-        }
-    }
+static void pic_run_finish(PicRun *run) {
+    const RefMePicIn        *in  = run->in;
+    PictureParentControlSet *pcs = run->f.pcs;
+    SvtMePicResults         *res = run->res;
     if (res) {
-#define CP(field, bytes) if (res->field) memcpy(res->field, pcs->field, (size_t)f.n_b64 * (bytes))
+#define CP(field, bytes) if (res->field) memcpy(res->field, pcs->field, (size_t)run->f.n_b64 * (bytes))
         CP(me_64x64_distortion, 4);
         CP(me_32x32_distortion, 4);
         CP(me_16x16_distortion, 4);
@@ -623,12 +649,63 @@ int ref_me_picture(const RefMePicIn *in, SvtMePicResults *res, RefMeDebug *dbg, 
         CP(rc_me_allow_gm, 1);
 #undef CP
     }
+    shim_forget();
+    planes_free(&run->src);
+    for (int l = 0; l < in->num_lists; l++)
+        for (int r = 0; r < in->ref_count[l]; r++) planes_free(&run->refs[l][r]);
+    fake_free(&run->f);
+}
+
+int ref_me_picture(const RefMePicIn *in, SvtMePicResults *res, RefMeDebug *dbg, double *seconds) {
+    PicRun run;
+    if (pic_run_init(&run, in, res, dbg)) return -1;
+    MeContext *me = (MeContext *)calloc(1, sizeof(MeContext));
+    me->me_type   = ME_OPEN_LOOP;
+    svt_aom_sig_deriv_me(run.f.scs, run.f.pcs, me); /* me_process.c:121 */
+    double t_me = 0.0;
+    for (uint32_t y_b64 = 0; y_b64 < run.f.b64_h; y_b64++)
+        for (uint32_t x_b64 = 0; x_b64 < run.f.b64_w; x_b64++) t_me += run_b64(&run, me, x_b64, y_b64);
     if (seconds) *seconds = t_me;
     free(me);
-    planes_free(&src);
-    for (int l = 0; l < in->num_lists; l++)
-        for (int r = 0; r < in->ref_count[l]; r++) planes_free(&refs[l][r]);
-    fake_free(&f);
+    pic_run_finish(&run);
+    return 0;
+}
+
+/* The same picture with the b64s dealt out to n_threads threads, each with its own MeContext, as the encoder's ME
+   threads work on the segments of one picture (me_process.c:86, :148-172; up to 20-25 threads, enc_handle.c:1066). */
+typedef struct MtArg {
+    PicRun  *run;
+    int      tid, n_threads;
+    double   seconds;
+} MtArg;
+static void *mt_worker(void *p) {
+    MtArg     *a   = (MtArg *)p;
+    PicRun    *run = a->run;
+    MeContext *me  = (MeContext *)calloc(1, sizeof(MeContext));
+    me->me_type    = ME_OPEN_LOOP;
+    svt_aom_sig_deriv_me(run->f.scs, run->f.pcs, me);
+    for (uint32_t i = (uint32_t)a->tid; i < run->f.n_b64; i += (uint32_t)a->n_threads)
+        a->seconds += run_b64(run, me, i % run->f.b64_w, i / run->f.b64_w);
+    free(me);
+    return NULL;
+}
+int ref_me_picture_mt(const RefMePicIn *in, SvtMePicResults *res, int n_threads, double *seconds) {
+    if (n_threads < 1 || n_threads > 64) return -1;
+    PicRun run;
+    if (pic_run_init(&run, in, res, NULL)) return -1;
+    pthread_t th[64];
+    MtArg     arg[64];
+    for (int t = 0; t < n_threads; t++) {
+        arg[t] = (MtArg){&run, t, n_threads, 0.0};
+        pthread_create(&th[t], NULL, mt_worker, &arg[t]);
+    }
+    double tot = 0.0;
+    for (int t = 0; t < n_threads; t++) {
+        pthread_join(th[t], NULL);
+        tot += arg[t].seconds;
+    }
+    if (seconds) *seconds = tot;
+    pic_run_finish(&run);
     return 0;
 }
 
@@ -656,6 +733,10 @@ int ref_dg_detector(const uint8_t *src_luma, const uint8_t *ref_luma, int width,
     scs->b64_size = 64;
     os.sixteenth_downsampled_picture_ptr  = &ps.sixteenth;
     orf.sixteenth_downsampled_picture_ptr = &pr.sixteenth;
+    os.input_padded_pic = &ps.full; /* read by the GPU shim only: the reference's detector needs just the 1/16 pictures */
+    orf.input_padded_pic = &pr.full;
+    src->picture_number = 1; refp->picture_number = 0;
+    shim_forget();
     ws.object_ptr = &os; wr.object_ptr = &orf;
     src->pa_ref_pic_wrapper = &ws; refp->pa_ref_pic_wrapper = &wr;
     src->scs = scs; src->aligned_width = (uint16_t)width; src->aligned_height = (uint16_t)height;
@@ -666,6 +747,7 @@ int ref_dg_detector(const uint8_t *src_luma, const uint8_t *ref_luma, int width,
     dg_detector_hme_level0(src, 0);
     out->tot_dist = dg.metrics.tot_dist; out->tot_cplx = dg.metrics.tot_cplx; out->tot_active = dg.metrics.tot_active;
     out->sum_in_vectors = dg.metrics.sum_in_vectors; out->input_resolution = (uint32_t)src->input_resolution;
+    shim_forget();
     free(scs); free(src); free(refp);
     planes_free(&ps); planes_free(&pr);
     return 0;
@@ -721,6 +803,7 @@ int ref_tf_me_picture(const RefTfIn *in, SvtMePicParams *params_out, SvtMePicRes
     pcs->tf_enable_hme_level2_flag = in->tf_hme_me_level == 0;
 
     Planes src, ref;
+    shim_forget();
     planes_alloc(&src, in->centre_luma, in->width, in->height);
     planes_alloc(&ref, in->ref_luma, in->width, in->height);
     MeContext *me = (MeContext *)calloc(1, sizeof(MeContext));
@@ -785,6 +868,7 @@ int ref_tf_me_picture(const RefTfIn *in, SvtMePicParams *params_out, SvtMePicRes
             if (dbg) dump_debug(&dbg[b64_index], me);
         }
     }
+    shim_forget();
     free(me);
     planes_free(&src);
     planes_free(&ref);

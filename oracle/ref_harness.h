@@ -55,11 +55,15 @@ typedef struct RefMeDebug {
 /* Fill `out` with the controls the reference derives for this picture (svt_aom_sig_deriv_me)
    and the PCS-level fields (enable_me_8x8, max_cand, gm flags ...). */
 int ref_derive_params(const RefMePicIn *in, SvtMePicParams *out);
+/* libsvtref_wrap.so only: the same through the product's svtme_shim_flatten (-2 in libsvtref.so) */
+int ref_derive_params_shim(const RefMePicIn *in, SvtMePicParams *out);
 
 /* Run the reference ME stage on one picture. `res` arrays follow SvtMePicResults (host memory,
    NULL = skip). `dbg` is [n_b64] or NULL. Returns 0 on success. *seconds (optional) receives the
    wall time spent inside svt_aom_motion_estimation_b64 only. */
 int ref_me_picture(const RefMePicIn *in, SvtMePicResults *res, RefMeDebug *dbg, double *seconds);
+/* the same with the b64s dealt out to n_threads threads, one MeContext each (the encoder's ME segment threads) */
+int ref_me_picture_mt(const RefMePicIn *in, SvtMePicResults *res, int n_threads, double *seconds);
 
 /* Build the three padded planes of a picture with the reference's own decimation/padding.
    Buffers must hold (w+2*72)*(h+2*72), (w/2+64)*(h/2+64), (w/4+32)*(h/4+32) bytes. */

@@ -1,0 +1,410 @@
+/*
+ * svtme_wrap.c — the reference-side binding of libsvtme_b200.so.
+ *
+ * Link the encoder (static, non-LTO libSvtAv1Enc.a) with
+ *     -Wl,--wrap=svt_aom_motion_estimation_b64 -Wl,--wrap=dg_detector_hme_level0  svtme_wrap.o  -lsvtme_b200
+ * and every caller of those two functions (me_process.c:266 open-loop ME, temporal_filtering.c:3141 temporal-filter ME,
+ * me_process.c:329 dynamic-GOP detector) reaches this file instead. The first b64 of a picture that arrives launches the
+ * WHOLE picture on the GPU; every call then copies its own b64's rows from the picture-level result arrays into the memory
+ * the reference owns (MeContext, pcs->pa_me_data->me_results[b64], the PCS statistic arrays), so the code downstream of
+ * the call sees exactly what svt_aom_motion_estimation_b64 (motion_estimation.c:3146-3223) would have left there.
+ *
+ * It compiles against the reference's own headers (pcs.h, me_context.h ...), which are not part of this repository:
+ * oracle/Makefile builds it where /root/reference exists, together with the reference's ME sources and the test harness
+ * that plays the role of me_process.c, into oracle/_ref/libsvtref_wrap.so (tests/test_wrap_shim.py).
+ *
+ * There is no CPU fallback: a failing GPU call is fatal. __real_svt_aom_motion_estimation_b64 is reached only for ME
+ * types this library does not implement (anything but ME_OPEN_LOOP and ME_MCTF; the reference has no such caller).
+ */
+#include <pthread.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include "definitions.h"
+#include "pcs.h"
+#include "sequence_control_set.h"
+#include "me_context.h"
+#include "motion_estimation.h"
+#include "reference_object.h"
+
+#include "svtme_b200.h"
+#include "svtme_wrap.h"
+
+#define SHIM_SLOTS 48 /* device picture store: sources + references alive (look-ahead + mini-GOP) */
+#define SHIM_JOBS 64  /* pictures / temporal-filter pairs whose results are being handed out */
+
+typedef struct ShimSlot {
+    int            valid;
+    uint64_t       picture_number;
+    const uint8_t *buf; /* identity of the host plane: the same picture_number exists before and after temporal filtering */
+    uint64_t       stamp;
+} ShimSlot;
+
+typedef struct ShimJob {
+    int             used;
+    const void     *pcs;
+    int             me_type;
+    uint64_t        ref_number; /* ME_MCTF: the neighbouring picture of this (centre, neighbour) pair */
+    uint32_t        n_b64, n_pus, delivered;
+    uint8_t         max_refs, max_cand;
+    SvtMePicResults res;
+    SvtMeHmeState  *hme; /* ME_MCTF only (tf_exit) */
+    void           *mem;
+} ShimJob;
+
+static struct {
+    pthread_mutex_t mu;
+    SvtMeSession   *sess;
+    uint32_t        w, h;
+    int             device;
+    uint64_t        clock;
+    ShimSlot        slot[SHIM_SLOTS];
+    ShimJob         job[SHIM_JOBS];
+    uint64_t        n_pictures, n_tf_pairs, n_dg;
+} g = {.mu = PTHREAD_MUTEX_INITIALIZER};
+
+static void shim_fatal(const char *what, uint32_t rc) {
+    fprintf(stderr, "svtme_wrap: %s failed (0x%x): the GPU motion-estimation path has no CPU fallback\n", what, rc);
+    abort();
+}
+#define SHIM_CHECK(call)                         \
+    do {                                         \
+        const uint32_t rc_ = (call);             \
+        if (rc_ != SVTME_OK) shim_fatal(#call, rc_); \
+    } while (0)
+
+/* ---- session and picture store -------------------------------------------------------------- */
+static void shim_session(uint32_t w, uint32_t h) {
+    if (g.sess && (g.w != w || g.h != h)) {
+        svtme_session_destroy(g.sess);
+        g.sess = NULL;
+    }
+    if (!g.sess) {
+        SHIM_CHECK(svtme_session_create(&g.sess, g.device, w, h, SHIM_SLOTS));
+        g.w = w;
+        g.h = h;
+        memset(g.slot, 0, sizeof(g.slot));
+    }
+}
+
+/* device slot of a host picture, uploading it when the store does not hold it. Slots touched during the current launch
+   (stamp == g.clock) are never evicted. */
+static int32_t shim_slot_of(const EbPictureBufferDesc *d, uint64_t picture_number) {
+    const uint8_t *luma = d->buffer_y + (size_t)d->org_y * d->stride_y + d->org_x;
+    int victim = -1;
+    for (int i = 0; i < SHIM_SLOTS; i++) {
+        ShimSlot *s = &g.slot[i];
+        if (s->valid && s->picture_number == picture_number && s->buf == luma) {
+            s->stamp = g.clock;
+            return i;
+        }
+        if (!s->valid) {
+            if (victim < 0 || g.slot[victim].valid) victim = i;
+        } else if (s->stamp != g.clock && (victim < 0 || (g.slot[victim].valid && s->stamp < g.slot[victim].stamp)))
+            victim = i;
+    }
+    if (victim < 0) shim_fatal("picture store full", 0);
+    SHIM_CHECK(svtme_picture_upload(g.sess, victim, luma, d->stride_y));
+    g.slot[victim] = (ShimSlot){1, picture_number, luma, g.clock};
+    return victim;
+}
+
+void svtme_shim_set_device(int device) { g.device = device; }
+
+void svtme_shim_release_picture(uint64_t picture_number) {
+    pthread_mutex_lock(&g.mu);
+    for (int i = 0; i < SHIM_SLOTS; i++)
+        if (g.slot[i].valid && g.slot[i].picture_number == picture_number) g.slot[i].valid = 0;
+    pthread_mutex_unlock(&g.mu);
+}
+
+void svtme_shim_forget_pictures(void) {
+    pthread_mutex_lock(&g.mu);
+    for (int i = 0; i < SHIM_SLOTS; i++) g.slot[i].valid = 0;
+    pthread_mutex_unlock(&g.mu);
+}
+
+void svtme_shim_shutdown(void) {
+    pthread_mutex_lock(&g.mu);
+    if (g.sess) svtme_session_destroy(g.sess);
+    g.sess = NULL;
+    for (int i = 0; i < SHIM_JOBS; i++) {
+        free(g.job[i].mem);
+        memset(&g.job[i], 0, sizeof(g.job[i]));
+    }
+    memset(g.slot, 0, sizeof(g.slot));
+    pthread_mutex_unlock(&g.mu);
+}
+
+void svtme_shim_stats(uint64_t *pictures, uint64_t *tf_pairs, uint64_t *dg_pairs) {
+    pthread_mutex_lock(&g.mu);
+    if (pictures) *pictures = g.n_pictures;
+    if (tf_pairs) *tf_pairs = g.n_tf_pairs;
+    if (dg_pairs) *dg_pairs = g.n_dg;
+    pthread_mutex_unlock(&g.mu);
+}
+
+/* ---- MeContext / PCS -> SvtMePicParams ------------------------------------------------------ */
+static SvtMeSearchArea sa_of(SearchArea a) {
+    SvtMeSearchArea r = {a.width, a.height};
+    return r;
+}
+static SvtMeSearchAreaMinMax samm_of(SearchAreaMinMax a) {
+    SvtMeSearchAreaMinMax r = {sa_of(a.sa_min), sa_of(a.sa_max)};
+    return r;
+}
+
+/* Field by field what motion_estimation.c reads from the MeContext (filled by svt_aom_sig_deriv_me /
+   svt_aom_sig_deriv_me_tf, enc_mode_config.c:694-895, and by the caller, me_process.c:219-262 /
+   temporal_filtering.c:3112-3140) and from the PCS. Members of a disabled feature are left 0: the reference leaves them
+   unset, and they are never read. */
+void svtme_shim_flatten(const PictureParentControlSet *pcs, const MeContext *m, SvtMePicParams *o) {
+    memset(o, 0, sizeof(*o));
+    SvtMeCtrls *c = &o->ctrls;
+    c->enable_hme_flag        = m->enable_hme_flag;
+    c->enable_hme_level0_flag = m->enable_hme_level0_flag;
+    c->enable_hme_level1_flag = m->enable_hme_level1_flag;
+    c->enable_hme_level2_flag = m->enable_hme_level2_flag;
+    c->hme_search_method      = m->hme_search_method;
+    c->me_search_method       = m->me_search_method;
+    c->num_hme_sa_w           = m->num_hme_sa_w;
+    c->num_hme_sa_h           = m->num_hme_sa_h;
+    c->hme_l0_sa              = samm_of(m->hme_l0_sa);
+    c->hme_l1_sa              = sa_of(m->hme_l1_sa);
+    c->hme_l2_sa              = sa_of(m->hme_l2_sa);
+    c->me_sa                  = samm_of(m->me_sa);
+    if (m->prehme_ctrl.enable) {
+        c->prehme_enable           = m->prehme_ctrl.enable;
+        c->prehme_skip_search_line = m->prehme_ctrl.skip_search_line;
+        c->prehme_l1_early_exit    = m->prehme_ctrl.l1_early_exit;
+        c->prehme_sa_cfg[0]        = samm_of(m->prehme_ctrl.prehme_sa_cfg[0]);
+        c->prehme_sa_cfg[1]        = samm_of(m->prehme_ctrl.prehme_sa_cfg[1]);
+    }
+    const MeHmeRefPruneCtrls *p = &m->me_hme_prune_ctrls;
+    c->enable_me_hme_ref_pruning               = p->enable_me_hme_ref_pruning;
+    c->prune_ref_if_hme_sad_dev_bigger_than_th = p->prune_ref_if_hme_sad_dev_bigger_than_th;
+    c->prune_ref_if_me_sad_dev_bigger_than_th  = p->prune_ref_if_me_sad_dev_bigger_than_th;
+    c->zz_sad_th    = p->zz_sad_th;
+    c->zz_sad_pct   = p->zz_sad_pct;
+    c->phme_sad_th  = p->phme_sad_th;
+    c->phme_sad_pct = p->phme_sad_pct;
+    const MeSrCtrls *s = &m->me_sr_adjustment_ctrls;
+    if (s->enable_me_sr_adjustment) {
+        c->enable_me_sr_adjustment              = s->enable_me_sr_adjustment; /* 1 or 2 (enc_mode_config.c:470-499) */
+        c->reduce_me_sr_based_on_mv_length_th   = s->reduce_me_sr_based_on_mv_length_th;
+        c->stationary_hme_sad_abs_th            = s->stationary_hme_sad_abs_th;
+        c->stationary_me_sr_divisor             = s->stationary_me_sr_divisor;
+        c->reduce_me_sr_based_on_hme_sad_abs_th = s->reduce_me_sr_based_on_hme_sad_abs_th;
+        c->me_sr_divisor_for_low_hme_sad        = s->me_sr_divisor_for_low_hme_sad;
+        c->distance_based_hme_resizing          = s->distance_based_hme_resizing;
+    }
+    if (m->me_8x8_var_ctrls.enabled) {
+        c->me_8x8_var_enabled = m->me_8x8_var_ctrls.enabled;
+        c->me_sr_div4_th      = m->me_8x8_var_ctrls.me_sr_div4_th;
+        c->me_sr_div2_th      = m->me_8x8_var_ctrls.me_sr_div2_th;
+        c->me_sr_mult2_th     = m->me_8x8_var_ctrls.me_sr_mult2_th;
+    }
+    if (m->mv_based_sa_adj.enabled) {
+        c->mv_sa_adj_enabled          = m->mv_based_sa_adj.enabled;
+        c->mv_sa_adj_nearest_ref_only = m->mv_based_sa_adj.nearest_ref_only;
+        c->mv_sa_adj_mv_size_th       = m->mv_based_sa_adj.mv_size_th;
+        c->mv_sa_adj_sa_multiplier    = m->mv_based_sa_adj.sa_multiplier;
+    }
+    c->reduce_hme_l0_sr_th_min     = m->reduce_hme_l0_sr_th_min;
+    c->reduce_hme_l0_sr_th_max     = m->reduce_hme_l0_sr_th_max;
+    c->me_early_exit_th            = m->me_early_exit_th;
+    c->me_safe_limit_zz_th         = m->me_safe_limit_zz_th;
+    c->prev_me_stage_based_exit_th = m->prev_me_stage_based_exit_th;
+    c->prune_me_candidates_th      = m->prune_me_candidates_th;
+    c->use_best_unipred_cand_only  = m->use_best_unipred_cand_only;
+
+    o->picture_number              = pcs->picture_number;
+    o->num_of_list_to_search       = m->num_of_list_to_search;
+    o->num_of_ref_pic_to_search[0] = m->num_of_ref_pic_to_search[0];
+    o->num_of_ref_pic_to_search[1] = m->num_of_list_to_search > 1 ? m->num_of_ref_pic_to_search[1] : 0;
+    o->temporal_layer_index        = m->temporal_layer_index;
+    o->is_ref                      = m->is_ref;
+    o->hierarchical_levels         = pcs->hierarchical_levels;
+    o->input_resolution            = (uint8_t)pcs->scs->input_resolution;
+    if (m->me_type == ME_MCTF) {
+        c->me_type       = SVTME_ME_MCTF;
+        c->tf_me_exit_th = m->tf_me_exit_th;
+        /* the candidate-list / GM outputs are not produced for ME_MCTF (motion_estimation.c:3195): neutral geometry */
+        o->enable_me_8x8 = o->enable_me_16x16 = 1;
+        o->max_cand = 3; o->max_refs = 2; o->max_l0 = 1;
+    } else {
+        c->me_type                     = SVTME_ME_OPEN_LOOP;
+        o->similar_brightness_refs     = pcs->similar_brightness_refs;
+        o->enable_me_8x8               = pcs->enable_me_8x8;
+        o->enable_me_16x16             = pcs->enable_me_16x16;
+        o->max_cand                    = pcs->pa_me_data->max_cand;
+        o->max_refs                    = pcs->pa_me_data->max_refs;
+        o->max_l0                      = pcs->pa_me_data->max_l0;
+        o->only_l_bwd                  = pcs->scs->mrp_ctrls.only_l_bwd;
+        o->gm_enabled                  = pcs->gm_ctrls.enabled;
+        o->gm_use_distance_based_active_th = pcs->gm_ctrls.use_distance_based_active_th;
+    }
+    for (int l = 0; l < 2; l++)
+        for (int r = 0; r < 4; r++) {
+            o->ref_pic_id[l][r] = -1;
+            if (l < o->num_of_list_to_search && r < o->num_of_ref_pic_to_search[l])
+                o->ref_picture_number[l][r] = m->me_ds_ref_array[l][r].picture_number;
+        }
+}
+
+/* ---- jobs: one per picture (open loop) or per (centre, neighbour) pair (temporal filter) ----- */
+static ShimJob *shim_find_job(const void *pcs, int me_type, uint64_t ref_number) {
+    for (int i = 0; i < SHIM_JOBS; i++) {
+        ShimJob *j = &g.job[i];
+        if (j->used && j->pcs == pcs && j->me_type == me_type && j->ref_number == ref_number) return j;
+    }
+    return NULL;
+}
+
+static ShimJob *shim_new_job(const void *pcs, int me_type, uint64_t ref_number, uint32_t n_b64, const SvtMePicParams *p) {
+    ShimJob *j = NULL;
+    for (int i = 0; i < SHIM_JOBS && !j; i++)
+        if (!g.job[i].used) j = &g.job[i];
+    if (!j) shim_fatal("job table full", 0);
+    memset(j, 0, sizeof(*j));
+    j->used = 1; j->pcs = pcs; j->me_type = me_type; j->ref_number = ref_number;
+    j->n_b64 = n_b64; j->n_pus = p->enable_me_8x8 ? 85 : 21; j->max_refs = p->max_refs; j->max_cand = p->max_cand;
+    const size_t n = n_b64, npu = j->n_pus;
+    const size_t sz[] = {n * 680 * 4, n * 680 * 4, n * 8 * sizeof(SvtMeSearchResult), n * npu, n * npu * j->max_refs * 4,
+                         n * npu * j->max_cand, n * 4, n * 4, n * 4, n * 4, n * 4, n * 4, n, n,
+                         me_type == ME_MCTF ? n * sizeof(SvtMeHmeState) : 0};
+    size_t total = 0, off[15];
+    for (int i = 0; i < 15; i++) { off[i] = total; total += (sz[i] + 63) & ~(size_t)63; }
+    uint8_t *mem = (uint8_t *)calloc(1, total ? total : 64);
+    if (!mem) shim_fatal("result allocation", 0);
+    j->mem = mem;
+    SvtMePicResults *r = &j->res;
+    r->p_sb_best_sad  = (uint32_t *)(mem + off[0]);
+    r->p_sb_best_mv   = (uint32_t *)(mem + off[1]);
+    r->search_results = (SvtMeSearchResult *)(mem + off[2]);
+    if (me_type != ME_MCTF) {
+        r->total_me_candidate_index    = mem + off[3];
+        r->me_mv_array                 = (uint32_t *)(mem + off[4]);
+        r->me_candidate_array          = mem + off[5];
+        r->me_64x64_distortion         = (uint32_t *)(mem + off[6]);
+        r->me_32x32_distortion         = (uint32_t *)(mem + off[7]);
+        r->me_16x16_distortion         = (uint32_t *)(mem + off[8]);
+        r->me_8x8_distortion           = (uint32_t *)(mem + off[9]);
+        r->rc_me_distortion            = (uint32_t *)(mem + off[10]);
+        r->me_8x8_cost_variance        = (uint32_t *)(mem + off[11]);
+        r->stationary_block_present_sb = mem + off[12];
+        r->rc_me_allow_gm              = mem + off[13];
+    } else
+        j->hme = (SvtMeHmeState *)(mem + off[14]);
+    return j;
+}
+
+/* launch the whole picture: uploads (source + every reference the store does not hold), one svtme_picture_me */
+static ShimJob *shim_launch(PictureParentControlSet *pcs, MeContext *me_ctx, EbPictureBufferDesc *input, uint64_t ref_number) {
+    const uint32_t w = (uint32_t)ALIGN_POWER_OF_TWO(input->width, 3), h = (uint32_t)ALIGN_POWER_OF_TWO(input->height, 3);
+    shim_session(w, h);
+    g.clock++;
+    SvtMePicParams p;
+    svtme_shim_flatten(pcs, me_ctx, &p);
+    const int32_t src_slot = shim_slot_of(input, pcs->picture_number);
+    for (int l = 0; l < p.num_of_list_to_search; l++)
+        for (int r = 0; r < p.num_of_ref_pic_to_search[l]; r++)
+            p.ref_pic_id[l][r] = shim_slot_of(me_ctx->me_ds_ref_array[l][r].picture_ptr, me_ctx->me_ds_ref_array[l][r].picture_number);
+    ShimJob *j = shim_new_job(pcs, me_ctx->me_type, ref_number, ((w + 63) / 64) * ((h + 63) / 64), &p);
+    SHIM_CHECK(svtme_picture_me(g.sess, src_slot, &p, &j->res, /*sync*/ 1));
+    if (j->hme) SHIM_CHECK(svtme_fetch_hme_state(g.sess, j->hme, (size_t)j->n_b64 * sizeof(SvtMeHmeState)));
+    if (me_ctx->me_type == ME_MCTF) g.n_tf_pairs++;
+    else g.n_pictures++;
+    return j;
+}
+
+EbErrorType __real_svt_aom_motion_estimation_b64(PictureParentControlSet *pcs, uint32_t b64_index, uint32_t b64_origin_x,
+                                                 uint32_t b64_origin_y, MeContext *me_ctx, EbPictureBufferDesc *input_ptr);
+
+EbErrorType __wrap_svt_aom_motion_estimation_b64(PictureParentControlSet *pcs, uint32_t b64_index, uint32_t b64_origin_x,
+                                                 uint32_t b64_origin_y, MeContext *me_ctx, EbPictureBufferDesc *input_ptr) {
+    if (me_ctx->me_type != ME_OPEN_LOOP && me_ctx->me_type != ME_MCTF)
+        return __real_svt_aom_motion_estimation_b64(pcs, b64_index, b64_origin_x, b64_origin_y, me_ctx, input_ptr);
+    const int      mctf       = me_ctx->me_type == ME_MCTF;
+    const uint64_t ref_number = mctf ? me_ctx->me_ds_ref_array[0][0].picture_number : 0;
+    pthread_mutex_lock(&g.mu);
+    ShimJob *j = shim_find_job(pcs, me_ctx->me_type, ref_number);
+    if (!j) j = shim_launch(pcs, me_ctx, input_ptr, ref_number); /* whichever segment thread arrives first launches */
+    pthread_mutex_unlock(&g.mu);
+    if (b64_index >= j->n_b64) shim_fatal("b64 index out of range", b64_index);
+
+    /* motion_estimation.c:3163-3170 */
+    const uint16_t aw = (uint16_t)ALIGN_POWER_OF_TWO(input_ptr->width, 3), ah = (uint16_t)ALIGN_POWER_OF_TWO(input_ptr->height, 3);
+    me_ctx->b64_width  = (aw - b64_origin_x) < BLOCK_SIZE_64 ? aw - b64_origin_x : BLOCK_SIZE_64;
+    me_ctx->b64_height = (ah - b64_origin_y) < BLOCK_SIZE_64 ? ah - b64_origin_y : BLOCK_SIZE_64;
+
+    const SvtMePicResults *r = &j->res;
+    for (int l = 0; l < 2; l++)
+        for (int k = 0; k < 4; k++) {
+            const size_t             o  = ((size_t)b64_index * 2 + l) * 4 + k;
+            const SvtMeSearchResult *sr = &r->search_results[o];
+            me_ctx->search_results[l][k].hme_sc_x = sr->hme_sc_x;
+            me_ctx->search_results[l][k].hme_sc_y = sr->hme_sc_y;
+            me_ctx->search_results[l][k].hme_sad  = sr->hme_sad;
+            me_ctx->search_results[l][k].do_ref   = sr->do_ref;
+            memcpy(me_ctx->p_sb_best_sad[l][k], r->p_sb_best_sad + o * 85, 85 * 4);
+            memcpy(me_ctx->p_sb_best_mv[l][k], r->p_sb_best_mv + o * 85, 85 * 4);
+        }
+    if (mctf) {
+        /* motion_estimation.c:2539-2544, :3179-3183 */
+        if (ABS(me_ctx->search_results[0][0].hme_sc_x) > ABS(me_ctx->search_results[0][0].hme_sc_y)) me_ctx->tf_tot_horz_blks++;
+        else me_ctx->tf_tot_vert_blks++;
+        if (j->hme[b64_index].tf_exit) me_ctx->tf_use_pred_64x64_only_th = (uint8_t)~0;
+    } else {
+        MeSbResults *sb = pcs->pa_me_data->me_results[b64_index];
+        const size_t np = j->n_pus;
+        memcpy(sb->total_me_candidate_index, r->total_me_candidate_index + b64_index * np, np);
+        memcpy(sb->me_mv_array, r->me_mv_array + (size_t)b64_index * np * j->max_refs, np * j->max_refs * 4);
+        memcpy(sb->me_candidate_array, r->me_candidate_array + (size_t)b64_index * np * j->max_cand, np * j->max_cand);
+        pcs->me_64x64_distortion[b64_index]         = r->me_64x64_distortion[b64_index];
+        pcs->me_32x32_distortion[b64_index]         = r->me_32x32_distortion[b64_index];
+        pcs->me_16x16_distortion[b64_index]         = r->me_16x16_distortion[b64_index];
+        pcs->me_8x8_distortion[b64_index]           = r->me_8x8_distortion[b64_index];
+        pcs->rc_me_distortion[b64_index]            = r->rc_me_distortion[b64_index];
+        pcs->me_8x8_cost_variance[b64_index]        = r->me_8x8_cost_variance[b64_index];
+        pcs->stationary_block_present_sb[b64_index] = r->stationary_block_present_sb[b64_index];
+        pcs->rc_me_allow_gm[b64_index]              = r->rc_me_allow_gm[b64_index];
+    }
+
+    pthread_mutex_lock(&g.mu);
+    if (++j->delivered == j->n_b64) { /* every b64 is asked for exactly once (me_process.c:174-271) */
+        free(j->mem);
+        memset(j, 0, sizeof(*j));
+    }
+    pthread_mutex_unlock(&g.mu);
+    return EB_ErrorNone;
+}
+
+/* ---- dynamic-GOP detector (pd_process.c:490-589; one call per ME segment, me_process.c:329) ----------------------- */
+void __wrap_dg_detector_hme_level0(struct PictureParentControlSet *ppcs, uint32_t seg_idx) {
+    (void)seg_idx;
+    DGDetectorSeg *dg = ppcs->dg_detector;
+    svt_block_on_mutex(dg->metrics_mutex);
+    if (dg->metrics.seg_completed == 0) { /* the first segment does the whole picture, the others only count down */
+        const EbPaReferenceObject *so = (const EbPaReferenceObject *)ppcs->pa_ref_pic_wrapper->object_ptr;
+        const EbPaReferenceObject *ro = (const EbPaReferenceObject *)dg->ref_pic->pa_ref_pic_wrapper->object_ptr;
+        pthread_mutex_lock(&g.mu);
+        shim_session(ppcs->aligned_width, ppcs->aligned_height);
+        g.clock++;
+        const int32_t  s = shim_slot_of(so->input_padded_pic, ppcs->picture_number);
+        const int32_t  r = shim_slot_of(ro->input_padded_pic, dg->ref_pic->picture_number);
+        SvtMeDgMetrics m = {.input_resolution = (uint32_t)ppcs->input_resolution};
+        SHIM_CHECK(svtme_dg_detector_hme(g.sess, s, r, &m, NULL, NULL));
+        g.n_dg++;
+        pthread_mutex_unlock(&g.mu);
+        dg->metrics.tot_dist += m.tot_dist;
+        dg->metrics.tot_cplx += m.tot_cplx;
+        dg->metrics.tot_active += m.tot_active;
+        dg->metrics.sum_in_vectors += m.sum_in_vectors;
+    }
+    dg->metrics.seg_completed++;
+    if (dg->metrics.seg_completed == (ppcs->me_segments_column_count * ppcs->me_segments_row_count))
+        svt_post_semaphore(dg->frame_done_sem); /* pd_process.c:583-586 */
+    svt_release_mutex(dg->metrics_mutex);
+}
