@@ -134,6 +134,7 @@ def wrap_lib():
         _wrap.ref_derive_params_shim.argtypes = [C.POINTER(RefMePicIn), C.POINTER(abi.MePicParams)]
         _wrap.svtme_shim_stats.argtypes = [C.POINTER(C.c_uint64)] * 3
         _wrap.svtme_shim_stats.restype = None
+        _wrap.svtme_shim_batches.restype = C.c_uint64
     return _wrap
 
 
@@ -233,6 +234,27 @@ def ref_me_picture_mt(pin, n_threads, params=None, lib=None):
     if rc != 0:
         raise RuntimeError("ref_me_picture_mt failed rc=%d" % rc)
     return res, sec.value
+
+
+def ref_me_minigop(pins, n_threads=4, submit=True, lib=None):
+    """several pictures released together (a mini-GOP), their b64s dealt out to n_threads ME threads; with
+    lib=wrap_lib() and submit=True they are first queued as ONE GPU batch by the shim -> [PicResultArrays]"""
+    lib = lib or ref_lib()
+    n = len(pins)
+    arr = (RefMePicIn * n)()
+    for i, p in enumerate(pins):
+        C.memmove(C.addressof(arr[i]), C.addressof(p), C.sizeof(RefMePicIn))
+    results = [abi.PicResultArrays(p.width, p.height, ref_derive_params(p, lib)) for p in pins]
+    rs = (abi.MePicResults * n)()
+    for i, r in enumerate(results):
+        C.memmove(C.addressof(rs[i]), C.addressof(r.struct), C.sizeof(abi.MePicResults))
+    f = lib.ref_me_minigop
+    f.argtypes = [C.POINTER(RefMePicIn), C.c_int, C.POINTER(abi.MePicResults), C.c_int, C.c_int]
+    f.restype = C.c_int
+    rc = f(arr, n, rs, n_threads, 1 if submit else 0)
+    if rc != 0:
+        raise RuntimeError("ref_me_minigop failed rc=%d" % rc)
+    return results
 
 
 def dg_detector(lib, prefix, src, ref, per_b64=False):

@@ -536,6 +536,10 @@ typedef struct PicRun {
     Planes            src, refs[2][4];
     SvtMePicResults  *res;
     RefMeDebug       *dbg;
+    /* the PA reference objects Picture Decision would have attached to the PCS (pd_process.c:4176): read by the GPU
+       shim's svtme_shim_submit_pictures only, the reference's b64 function gets its planes through the MeContext */
+    EbObjectWrapper     src_w, ref_w[2][4];
+    EbPaReferenceObject src_o, ref_o[2][4];
 } PicRun;
 
 /* one b64 the way svt_aom_motion_estimation_kernel does it (me_process.c:174-271), then the dump of what the call left
@@ -624,12 +628,28 @@ static double run_b64(PicRun *run, MeContext *me, uint32_t x_b64, uint32_t y_b64
 static int pic_run_init(PicRun *run, const RefMePicIn *in, SvtMePicResults *res, RefMeDebug *dbg) {
     if (in->width % 8 || in->height % 8 || in->num_lists < 1 || in->num_lists > 2) return -1;
     set_rtcd(in->simd);
-    shim_forget();
     run->in = in; run->res = res; run->dbg = dbg;
     fake_init(&run->f, in);
     planes_alloc(&run->src, in->src_luma, in->width, in->height);
     for (int l = 0; l < in->num_lists; l++)
         for (int r = 0; r < in->ref_count[l]; r++) planes_alloc(&run->refs[l][r], in->ref_luma[l][r], in->width, in->height);
+    memset(&run->src_w, 0, sizeof(run->src_w)); memset(run->ref_w, 0, sizeof(run->ref_w));
+    memset(&run->src_o, 0, sizeof(run->src_o)); memset(run->ref_o, 0, sizeof(run->ref_o));
+    run->src_o.input_padded_pic = &run->src.full;
+    run->src_o.quarter_downsampled_picture_ptr = &run->src.quarter;
+    run->src_o.sixteenth_downsampled_picture_ptr = &run->src.sixteenth;
+    run->src_o.picture_number = in->picture_number;
+    run->src_w.object_ptr = &run->src_o;
+    run->f.pcs->pa_ref_pic_wrapper = &run->src_w;
+    for (int l = 0; l < in->num_lists; l++)
+        for (int r = 0; r < in->ref_count[l]; r++) {
+            run->ref_o[l][r].input_padded_pic = &run->refs[l][r].full;
+            run->ref_o[l][r].quarter_downsampled_picture_ptr = &run->refs[l][r].quarter;
+            run->ref_o[l][r].sixteenth_downsampled_picture_ptr = &run->refs[l][r].sixteenth;
+            run->ref_o[l][r].picture_number = in->ref_picture_number[l][r];
+            run->ref_w[l][r].object_ptr = &run->ref_o[l][r];
+            run->f.pcs->ref_pa_pic_ptr_array[l][r] = &run->ref_w[l][r];
+        }
     return 0;
 }
 
@@ -649,7 +669,6 @@ static void pic_run_finish(PicRun *run) {
         CP(rc_me_allow_gm, 1);
 #undef CP
     }
-    shim_forget();
     planes_free(&run->src);
     for (int l = 0; l < in->num_lists; l++)
         for (int r = 0; r < in->ref_count[l]; r++) planes_free(&run->refs[l][r]);
@@ -658,6 +677,7 @@ static void pic_run_finish(PicRun *run) {
 
 int ref_me_picture(const RefMePicIn *in, SvtMePicResults *res, RefMeDebug *dbg, double *seconds) {
     PicRun run;
+    shim_forget();
     if (pic_run_init(&run, in, res, dbg)) return -1;
     MeContext *me = (MeContext *)calloc(1, sizeof(MeContext));
     me->me_type   = ME_OPEN_LOOP;
@@ -667,6 +687,7 @@ int ref_me_picture(const RefMePicIn *in, SvtMePicResults *res, RefMeDebug *dbg, 
         for (uint32_t x_b64 = 0; x_b64 < run.f.b64_w; x_b64++) t_me += run_b64(&run, me, x_b64, y_b64);
     if (seconds) *seconds = t_me;
     free(me);
+    shim_forget();
     pic_run_finish(&run);
     return 0;
 }
@@ -692,6 +713,7 @@ static void *mt_worker(void *p) {
 int ref_me_picture_mt(const RefMePicIn *in, SvtMePicResults *res, int n_threads, double *seconds) {
     if (n_threads < 1 || n_threads > 64) return -1;
     PicRun run;
+    shim_forget();
     if (pic_run_init(&run, in, res, NULL)) return -1;
     pthread_t th[64];
     MtArg     arg[64];
@@ -705,7 +727,53 @@ int ref_me_picture_mt(const RefMePicIn *in, SvtMePicResults *res, int n_threads,
         tot += arg[t].seconds;
     }
     if (seconds) *seconds = tot;
+    shim_forget();
     pic_run_finish(&run);
+    return 0;
+}
+
+/* n pictures released together, as Picture Decision releases a mini-GOP (pd_process.c:4373-4400): with the GPU shim they
+   are queued as one batch (svtme_shim_submit_pictures) before the ME threads start; the threads then take (picture,
+   b64) pairs in the order the ME FIFO would hand them out. Without the shim (libsvtref.so) the submit step is absent. */
+extern void svtme_shim_submit_pictures(PictureParentControlSet **pcs_list, uint32_t n) __attribute__((weak));
+typedef struct GopArg {
+    PicRun *runs;
+    int     n_pics, tid, n_threads;
+} GopArg;
+static void *gop_worker(void *p) {
+    GopArg *a = (GopArg *)p;
+    for (int k = 0; k < a->n_pics; k++) {
+        PicRun    *run = &a->runs[k];
+        MeContext *me  = (MeContext *)calloc(1, sizeof(MeContext));
+        me->me_type    = ME_OPEN_LOOP;
+        svt_aom_sig_deriv_me(run->f.scs, run->f.pcs, me);
+        for (uint32_t i = (uint32_t)a->tid; i < run->f.n_b64; i += (uint32_t)a->n_threads)
+            run_b64(run, me, i % run->f.b64_w, i / run->f.b64_w);
+        free(me);
+    }
+    return NULL;
+}
+int ref_me_minigop(const RefMePicIn *ins, int n_pics, SvtMePicResults *res, int n_threads, int submit) {
+    if (n_pics < 1 || n_pics > 32 || n_threads < 1 || n_threads > 64) return -1;
+    PicRun *runs = (PicRun *)calloc((size_t)n_pics, sizeof(PicRun));
+    shim_forget();
+    for (int k = 0; k < n_pics; k++)
+        if (pic_run_init(&runs[k], &ins[k], &res[k], NULL)) return -1;
+    if (submit && svtme_shim_submit_pictures) {
+        PictureParentControlSet *list[32];
+        for (int k = 0; k < n_pics; k++) list[k] = runs[k].f.pcs;
+        svtme_shim_submit_pictures(list, (uint32_t)n_pics);
+    }
+    pthread_t th[64];
+    GopArg    arg[64];
+    for (int t = 0; t < n_threads; t++) {
+        arg[t] = (GopArg){runs, n_pics, t, n_threads};
+        pthread_create(&th[t], NULL, gop_worker, &arg[t]);
+    }
+    for (int t = 0; t < n_threads; t++) pthread_join(th[t], NULL);
+    shim_forget();
+    for (int k = 0; k < n_pics; k++) pic_run_finish(&runs[k]);
+    free(runs);
     return 0;
 }
 

@@ -64,6 +64,9 @@ int ref_derive_params_shim(const RefMePicIn *in, SvtMePicParams *out);
 int ref_me_picture(const RefMePicIn *in, SvtMePicResults *res, RefMeDebug *dbg, double *seconds);
 /* the same with the b64s dealt out to n_threads threads, one MeContext each (the encoder's ME segment threads) */
 int ref_me_picture_mt(const RefMePicIn *in, SvtMePicResults *res, int n_threads, double *seconds);
+/* n_pics pictures released together (a mini-GOP): res[k] belongs to ins[k]; submit != 0 queues them as one GPU batch first
+   when the library was linked with the GPU shim (libsvtref_wrap.so) */
+int ref_me_minigop(const RefMePicIn *ins, int n_pics, SvtMePicResults *res, int n_threads, int submit);
 
 /* Build the three padded planes of a picture with the reference's own decimation/padding.
    Buffers must hold (w+2*72)*(h+2*72), (w/2+64)*(h/2+64), (w/4+32)*(h/4+32) bytes. */

@@ -27,11 +27,12 @@
 #include "me_context.h"
 #include "motion_estimation.h"
 #include "reference_object.h"
+#include "enc_mode_config.h"
 
 #include "svtme_b200.h"
 #include "svtme_wrap.h"
 
-#define SHIM_SLOTS 48 /* device picture store: sources + references alive (look-ahead + mini-GOP) */
+#define SHIM_SLOTS 64 /* device picture store: sources + references alive (look-ahead + mini-GOP) */
 #define SHIM_JOBS 64  /* pictures / temporal-filter pairs whose results are being handed out */
 
 typedef struct ShimSlot {
@@ -47,6 +48,8 @@ typedef struct ShimJob {
     int             me_type;
     uint64_t        ref_number; /* ME_MCTF: the neighbouring picture of this (centre, neighbour) pair */
     uint32_t        n_b64, n_pus, delivered;
+    int             pending; /* queued by svtme_shim_submit_pictures: wait for batch `seq` before the first read */
+    uint64_t        seq;
     uint8_t         max_refs, max_cand;
     SvtMePicResults res;
     SvtMeHmeState  *hme; /* ME_MCTF only (tf_exit) */
@@ -61,7 +64,7 @@ static struct {
     uint64_t        clock;
     ShimSlot        slot[SHIM_SLOTS];
     ShimJob         job[SHIM_JOBS];
-    uint64_t        n_pictures, n_tf_pairs, n_dg;
+    uint64_t        n_pictures, n_tf_pairs, n_dg, n_batches;
 } g = {.mu = PTHREAD_MUTEX_INITIALIZER};
 
 static void shim_fatal(const char *what, uint32_t rc) {
@@ -90,8 +93,7 @@ static void shim_session(uint32_t w, uint32_t h) {
 
 /* device slot of a host picture, uploading it when the store does not hold it. Slots touched during the current launch
    (stamp == g.clock) are never evicted. */
-static int32_t shim_slot_of(const EbPictureBufferDesc *d, uint64_t picture_number) {
-    const uint8_t *luma = d->buffer_y + (size_t)d->org_y * d->stride_y + d->org_x;
+static int32_t shim_slot_of_plane(const uint8_t *luma, uint32_t stride, uint64_t picture_number) {
     int victim = -1;
     for (int i = 0; i < SHIM_SLOTS; i++) {
         ShimSlot *s = &g.slot[i];
@@ -105,9 +107,15 @@ static int32_t shim_slot_of(const EbPictureBufferDesc *d, uint64_t picture_numbe
             victim = i;
     }
     if (victim < 0) shim_fatal("picture store full", 0);
-    SHIM_CHECK(svtme_picture_upload(g.sess, victim, luma, d->stride_y));
+    SHIM_CHECK(svtme_picture_upload(g.sess, victim, luma, stride));
     g.slot[victim] = (ShimSlot){1, picture_number, luma, g.clock};
     return victim;
+}
+static int32_t shim_slot_of(const EbPictureBufferDesc *d, uint64_t picture_number) {
+    /* scaled references (super-resolution / resize, me_process.c:232-249) have other dimensions: not supported */
+    if ((uint32_t)ALIGN_POWER_OF_TWO(d->width, 3) != g.w || (uint32_t)ALIGN_POWER_OF_TWO(d->height, 3) != g.h)
+        shim_fatal("reference picture size differs from the source (super-res / resize are not supported)", d->width);
+    return shim_slot_of_plane(d->buffer_y + (size_t)d->org_y * d->stride_y + d->org_x, d->stride_y, picture_number);
 }
 
 void svtme_shim_set_device(int device) { g.device = device; }
@@ -136,6 +144,8 @@ void svtme_shim_shutdown(void) {
     memset(g.slot, 0, sizeof(g.slot));
     pthread_mutex_unlock(&g.mu);
 }
+
+uint64_t svtme_shim_batches(void) { return g.n_batches; }
 
 void svtme_shim_stats(uint64_t *pictures, uint64_t *tf_pairs, uint64_t *dg_pairs) {
     pthread_mutex_lock(&g.mu);
@@ -301,13 +311,17 @@ static ShimJob *shim_new_job(const void *pcs, int me_type, uint64_t ref_number, 
 }
 
 /* launch the whole picture: uploads (source + every reference the store does not hold), one svtme_picture_me */
-static ShimJob *shim_launch(PictureParentControlSet *pcs, MeContext *me_ctx, EbPictureBufferDesc *input, uint64_t ref_number) {
+static ShimJob *shim_launch(PictureParentControlSet *pcs, MeContext *me_ctx, EbPictureBufferDesc *input, uint32_t b64_origin_x,
+                            uint32_t b64_origin_y, uint64_t ref_number) {
     const uint32_t w = (uint32_t)ALIGN_POWER_OF_TWO(input->width, 3), h = (uint32_t)ALIGN_POWER_OF_TWO(input->height, 3);
     shim_session(w, h);
     g.clock++;
     SvtMePicParams p;
     svtme_shim_flatten(pcs, me_ctx, &p);
-    const int32_t src_slot = shim_slot_of(input, pcs->picture_number);
+    /* the source samples are the ones the reference would read: me_ctx->b64_src_ptr points at this b64 inside the padded
+       source plane (me_process.c:196-197: the PA reference object's input_padded_pic, not `input`) */
+    const uint8_t *src_luma = me_ctx->b64_src_ptr - (size_t)b64_origin_y * me_ctx->b64_src_stride - b64_origin_x;
+    const int32_t  src_slot = shim_slot_of_plane(src_luma, me_ctx->b64_src_stride, pcs->picture_number);
     for (int l = 0; l < p.num_of_list_to_search; l++)
         for (int r = 0; r < p.num_of_ref_pic_to_search[l]; r++)
             p.ref_pic_id[l][r] = shim_slot_of(me_ctx->me_ds_ref_array[l][r].picture_ptr, me_ctx->me_ds_ref_array[l][r].picture_number);
@@ -330,7 +344,11 @@ EbErrorType __wrap_svt_aom_motion_estimation_b64(PictureParentControlSet *pcs, u
     const uint64_t ref_number = mctf ? me_ctx->me_ds_ref_array[0][0].picture_number : 0;
     pthread_mutex_lock(&g.mu);
     ShimJob *j = shim_find_job(pcs, me_ctx->me_type, ref_number);
-    if (!j) j = shim_launch(pcs, me_ctx, input_ptr, ref_number); /* whichever segment thread arrives first launches */
+    if (!j) j = shim_launch(pcs, me_ctx, input_ptr, b64_origin_x, b64_origin_y, ref_number); /* whichever thread arrives first launches */
+    if (j->pending) { /* queued ahead of time as part of a batch: the first reader waits for it */
+        SHIM_CHECK(svtme_session_wait_batch(g.sess, j->seq));
+        j->pending = 0;
+    }
     pthread_mutex_unlock(&g.mu);
     if (b64_index >= j->n_b64) shim_fatal("b64 index out of range", b64_index);
 
@@ -379,6 +397,79 @@ EbErrorType __wrap_svt_aom_motion_estimation_b64(PictureParentControlSet *pcs, u
     }
     pthread_mutex_unlock(&g.mu);
     return EB_ErrorNone;
+}
+
+/* ---- a mini-GOP at once ---------------------------------------------------------------------------------------------
+   Picture Decision releases the pictures of a mini-GOP together (pd_process.c:4373-4400) and open-loop ME pictures do
+   not depend on each other, so their ME can be ONE GPU batch (every kernel launched once for all of them) queued before
+   the first TASK_PAME task is consumed; the b64 calls then only wait for the batch and copy. For every picture this does
+   what svt_aom_motion_estimation_kernel does before its b64 loop (me_process.c:121, :131-146, :219-262). */
+static int same_stage_structure(const SvtMeCtrls *a, const SvtMeCtrls *b) {
+    return a->enable_hme_flag == b->enable_hme_flag && a->enable_hme_level0_flag == b->enable_hme_level0_flag &&
+        a->enable_hme_level1_flag == b->enable_hme_level1_flag && a->enable_hme_level2_flag == b->enable_hme_level2_flag &&
+        a->prehme_enable == b->prehme_enable && a->hme_search_method == b->hme_search_method &&
+        a->me_search_method == b->me_search_method && a->prehme_skip_search_line == b->prehme_skip_search_line &&
+        a->hme_l1_sa.width == b->hme_l1_sa.width && a->hme_l1_sa.height == b->hme_l1_sa.height &&
+        a->hme_l2_sa.width == b->hme_l2_sa.width && a->hme_l2_sa.height == b->hme_l2_sa.height;
+}
+
+void svtme_shim_submit_pictures(PictureParentControlSet **pcs_list, uint32_t n) {
+    if (n == 0) return;
+    if (n > SHIM_JOBS / 2) shim_fatal("svtme_shim_submit_pictures: too many pictures", n);
+    MeContext      *m      = (MeContext *)calloc(1, sizeof(MeContext));
+    SvtMePicParams *params = (SvtMePicParams *)calloc(n, sizeof(SvtMePicParams));
+    SvtMePicResults *res   = (SvtMePicResults *)calloc(n, sizeof(SvtMePicResults));
+    int32_t        *ids    = (int32_t *)calloc(n, sizeof(int32_t));
+    ShimJob       **jobs   = (ShimJob **)calloc(n, sizeof(ShimJob *));
+    if (!m || !params || !res || !ids || !jobs) shim_fatal("allocation", 0);
+    pthread_mutex_lock(&g.mu);
+    uint32_t k = 0;
+    for (uint32_t i = 0; i < n; i++) {
+        PictureParentControlSet *pcs = pcs_list[i];
+        if (pcs->slice_type == I_SLICE || shim_find_job(pcs, ME_OPEN_LOOP, 0)) continue; /* me_process.c:165 */
+        const EbPaReferenceObject *po  = (const EbPaReferenceObject *)pcs->pa_ref_pic_wrapper->object_ptr;
+        const EbPictureBufferDesc *src = po->input_padded_pic;
+        if (k == 0) {
+            shim_session((uint32_t)ALIGN_POWER_OF_TWO(src->width, 3), (uint32_t)ALIGN_POWER_OF_TWO(src->height, 3));
+            g.clock++;
+        }
+        memset(m, 0, sizeof(*m));
+        m->me_type = ME_OPEN_LOOP;
+        svt_aom_sig_deriv_me(pcs->scs, pcs, m);
+        m->num_of_list_to_search       = (pcs->slice_type == P_SLICE) ? 1 : 2;
+        m->num_of_ref_pic_to_search[0] = pcs->ref_list0_count_try;
+        if (pcs->slice_type == B_SLICE) m->num_of_ref_pic_to_search[1] = pcs->ref_list1_count_try;
+        m->temporal_layer_index = pcs->temporal_layer_index;
+        m->is_ref               = pcs->is_ref;
+        for (int l = 0; l < m->num_of_list_to_search; l++)
+            for (int r = 0; r < m->num_of_ref_pic_to_search[l]; r++) {
+                const EbPaReferenceObject *ro = (const EbPaReferenceObject *)pcs->ref_pa_pic_ptr_array[l][r]->object_ptr;
+                m->me_ds_ref_array[l][r].picture_ptr    = ro->input_padded_pic;
+                m->me_ds_ref_array[l][r].picture_number = ro->picture_number;
+            }
+        SvtMePicParams *p = &params[k];
+        svtme_shim_flatten(pcs, m, p);
+        if (k && !same_stage_structure(&params[0].ctrls, &p->ctrls)) continue; /* left to the per-picture launch */
+        ids[k] = shim_slot_of(src, pcs->picture_number);
+        for (int l = 0; l < p->num_of_list_to_search; l++)
+            for (int r = 0; r < p->num_of_ref_pic_to_search[l]; r++)
+                p->ref_pic_id[l][r] = shim_slot_of(m->me_ds_ref_array[l][r].picture_ptr, m->me_ds_ref_array[l][r].picture_number);
+        jobs[k] = shim_new_job(pcs, ME_OPEN_LOOP, 0, pcs->b64_total_count, p);
+        res[k]  = jobs[k]->res;
+        k++;
+    }
+    if (k) {
+        SHIM_CHECK(svtme_picture_me_batch(g.sess, k, ids, params, res, /*sync*/ 0));
+        const uint64_t seq = svtme_session_batch_seq(g.sess);
+        for (uint32_t i = 0; i < k; i++) {
+            jobs[i]->pending = 1;
+            jobs[i]->seq     = seq;
+        }
+        g.n_pictures += k;
+        g.n_batches++;
+    }
+    pthread_mutex_unlock(&g.mu);
+    free(m); free(params); free(res); free(ids); free(jobs);
 }
 
 /* ---- dynamic-GOP detector (pd_process.c:490-589; one call per ME segment, me_process.c:329) ----------------------- */

@@ -30,7 +30,8 @@ PICTURES = [(case_id(c), lambda c=c: case_inputs(c)) for c in CASES] + [(n, lamb
 def test_wrapped_library_exports_the_binding():
     lib = po.wrap_lib()
     for sym in ("__wrap_svt_aom_motion_estimation_b64", "__wrap_dg_detector_hme_level0", "svtme_shim_flatten", "svtme_shim_set_device",
-                "svtme_shim_release_picture", "svtme_shim_forget_pictures", "svtme_shim_shutdown", "svtme_shim_stats"):
+                "svtme_shim_release_picture", "svtme_shim_forget_pictures", "svtme_shim_shutdown", "svtme_shim_stats",
+                "svtme_shim_submit_pictures", "svtme_shim_batches"):
         assert hasattr(lib, sym), sym
 
 
@@ -87,6 +88,35 @@ def test_concurrent_me_threads_share_one_gpu_launch(n_threads):
         res, _ = po.ref_me_picture_mt(pin, n_threads, lib=po.wrap_lib())
         assert po.shim_stats()[0] == before[0] + 1, "exactly one GPU launch per picture"
         fx.compare(res, RES_FIELDS, "%d reference ME threads + GPU shim vs reference fixture" % n_threads)
+
+
+# a 320x192 preset-4 mini-GOP out of one clip: (temporal layer, poc, list 0, list 1)
+MINIGOP = [(1, 16, [0, 8, 4, 2], [32, 24, 20]), (0, 32, [0, 16, 8, 4], [0, 16, 8]), (2, 8, [0, 4, 2], [16, 32]),
+           (3, 4, [0, 2], [8, 16]), (3, 12, [8, 4], [16, 32]), (4, 2, [0], [4, 8])]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n_threads", [1, 6])
+def test_minigop_is_one_gpu_batch(orc, n_threads):
+    """svtme_shim_submit_pictures: the pictures Picture Decision releases together are queued as ONE batch before the ME
+    threads start; the b64 calls wait for it and copy. A picture whose stage structure differs (preset 12 here) is left
+    to the per-picture launch. Peer: the oracle (pinned by the fixtures) on the parameters the reference derived."""
+    from util import compare, orc_me
+    lib = po.wrap_lib()
+    pics = [(320, 192, 4, tl, poc, l0, l1) for tl, poc, l0, l1 in MINIGOP] + [CASES[7]]
+    ins = [case_inputs(c) for c in pics]
+    pins = [po.make_pic_in(src, refs, pocs, poc, enc_mode, **kw) for src, refs, pocs, poc, enc_mode, kw in ins]
+    before, batches = po.shim_stats(), lib.svtme_shim_batches()
+    got = po.ref_me_minigop(pins, n_threads=n_threads, submit=True, lib=lib)
+    assert lib.svtme_shim_batches() == batches + 1
+    assert po.shim_stats()[0] == before[0] + len(pics), "6 pictures in the batch + 1 launched on its first b64"
+    for (src, refs, pocs, poc, enc_mode, kw), pin, g in zip(ins, pins, got):
+        want, _, _ = orc_me(src, refs, po.ref_derive_params(pin, lib), debug=False)
+        compare(want, g, fields=RES_FIELDS)
+    # the two pictures that have fixtures: against the reference's own output
+    gl.PictureFixture(case_id(CASES[0])).compare(got[0], RES_FIELDS, "batched mini-GOP vs reference fixture")
+    gl.PictureFixture(case_id(CASES[2])).compare(got[1], RES_FIELDS, "batched mini-GOP vs reference fixture")
+    gl.PictureFixture(case_id(CASES[7])).compare(got[6], RES_FIELDS, "picture outside the batch vs reference fixture")
 
 
 @pytest.mark.gpu
