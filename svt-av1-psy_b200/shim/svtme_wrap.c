@@ -38,7 +38,8 @@
 typedef struct ShimSlot {
     int            valid;
     uint64_t       picture_number;
-    const uint8_t *buf; /* identity of the host plane: the same picture_number exists before and after temporal filtering */
+    const uint8_t *buf; /* identity of the host plane */
+    const void    *scope; /* who may reuse the copy, see shim_slot_of_plane */
     uint64_t       stamp;
 } ShimSlot;
 
@@ -48,6 +49,8 @@ typedef struct ShimJob {
     int             me_type;
     uint64_t        ref_number; /* ME_MCTF: the neighbouring picture of this (centre, neighbour) pair */
     uint32_t        n_b64, n_pus, delivered;
+    uint64_t        stamp;
+    int             readers; /* threads copying rows out right now: never evicted */
     int             pending; /* queued by svtme_shim_submit_pictures: wait for batch `seq` before the first read */
     uint64_t        seq;
     uint8_t         max_refs, max_cand;
@@ -92,12 +95,17 @@ static void shim_session(uint32_t w, uint32_t h) {
 }
 
 /* device slot of a host picture, uploading it when the store does not hold it. Slots touched during the current launch
-   (stamp == g.clock) are never evicted. */
-static int32_t shim_slot_of_plane(const uint8_t *luma, uint32_t stride, uint64_t picture_number) {
+   (stamp == g.clock) are never evicted.
+   `scope`: the samples behind one (picture number, plane address) change during an encode: the temporal filter rewrites a
+   base picture in place after its neighbours were searched against it (temporal_filtering.c:3842-3882), and the
+   dynamic-GOP detector looks at pictures before they are filtered. A device copy is therefore only reused inside the
+   scope it was uploaded for: open-loop ME (scope NULL: a picture is final once it is a source or a reference there), the
+   temporal filtering of ONE centre picture (scope = its PCS), the detector (scope = &g). */
+static int32_t shim_slot_of_plane(const uint8_t *luma, uint32_t stride, uint64_t picture_number, const void *scope) {
     int victim = -1;
     for (int i = 0; i < SHIM_SLOTS; i++) {
         ShimSlot *s = &g.slot[i];
-        if (s->valid && s->picture_number == picture_number && s->buf == luma) {
+        if (s->valid && s->picture_number == picture_number && s->buf == luma && s->scope == scope) {
             s->stamp = g.clock;
             return i;
         }
@@ -108,14 +116,14 @@ static int32_t shim_slot_of_plane(const uint8_t *luma, uint32_t stride, uint64_t
     }
     if (victim < 0) shim_fatal("picture store full", 0);
     SHIM_CHECK(svtme_picture_upload(g.sess, victim, luma, stride));
-    g.slot[victim] = (ShimSlot){1, picture_number, luma, g.clock};
+    g.slot[victim] = (ShimSlot){1, picture_number, luma, scope, g.clock};
     return victim;
 }
-static int32_t shim_slot_of(const EbPictureBufferDesc *d, uint64_t picture_number) {
+static int32_t shim_slot_of(const EbPictureBufferDesc *d, uint64_t picture_number, const void *scope) {
     /* scaled references (super-resolution / resize, me_process.c:232-249) have other dimensions: not supported */
     if ((uint32_t)ALIGN_POWER_OF_TWO(d->width, 3) != g.w || (uint32_t)ALIGN_POWER_OF_TWO(d->height, 3) != g.h)
         shim_fatal("reference picture size differs from the source (super-res / resize are not supported)", d->width);
-    return shim_slot_of_plane(d->buffer_y + (size_t)d->org_y * d->stride_y + d->org_x, d->stride_y, picture_number);
+    return shim_slot_of_plane(d->buffer_y + (size_t)d->org_y * d->stride_y + d->org_x, d->stride_y, picture_number, scope);
 }
 
 void svtme_shim_set_device(int device) { g.device = device; }
@@ -153,6 +161,15 @@ void svtme_shim_stats(uint64_t *pictures, uint64_t *tf_pairs, uint64_t *dg_pairs
     if (tf_pairs) *tf_pairs = g.n_tf_pairs;
     if (dg_pairs) *dg_pairs = g.n_dg;
     pthread_mutex_unlock(&g.mu);
+}
+
+/* SVTME_SHIM_STATS=1 in the environment: one line on stderr at process exit (the whole-encoder test reads it) */
+__attribute__((destructor)) static void shim_report(void) {
+    const char *e = getenv("SVTME_SHIM_STATS");
+    if (e && e[0] == '1')
+        fprintf(stderr, "svtme_wrap: on the GPU: %llu open-loop pictures (%llu batches), %llu temporal-filter pairs, %llu detector pairs\n",
+                (unsigned long long)g.n_pictures, (unsigned long long)g.n_batches, (unsigned long long)g.n_tf_pairs,
+                (unsigned long long)g.n_dg);
 }
 
 /* ---- MeContext / PCS -> SvtMePicParams ------------------------------------------------------ */
@@ -276,8 +293,17 @@ static ShimJob *shim_new_job(const void *pcs, int me_type, uint64_t ref_number, 
     ShimJob *j = NULL;
     for (int i = 0; i < SHIM_JOBS && !j; i++)
         if (!g.job[i].used) j = &g.job[i];
-    if (!j) shim_fatal("job table full", 0);
+    if (!j) {
+        /* results nobody came back for: the temporal filter skips the ME call of some blocks (temporal_filtering.c:3080-3094),
+           so a (centre, neighbour) pair may never see all its b64s. The oldest set goes; if one of its b64s is still asked
+           for, the pair is simply launched again. */
+        for (int i = 0; i < SHIM_JOBS; i++)
+            if (!g.job[i].pending && !g.job[i].readers && (!j || g.job[i].stamp < j->stamp)) j = &g.job[i];
+        if (!j) shim_fatal("job table full", 0);
+        free(j->mem);
+    }
     memset(j, 0, sizeof(*j));
+    j->stamp = g.clock;
     j->used = 1; j->pcs = pcs; j->me_type = me_type; j->ref_number = ref_number;
     j->n_b64 = n_b64; j->n_pus = p->enable_me_8x8 ? 85 : 21; j->max_refs = p->max_refs; j->max_cand = p->max_cand;
     const size_t n = n_b64, npu = j->n_pus;
@@ -321,10 +347,11 @@ static ShimJob *shim_launch(PictureParentControlSet *pcs, MeContext *me_ctx, EbP
     /* the source samples are the ones the reference would read: me_ctx->b64_src_ptr points at this b64 inside the padded
        source plane (me_process.c:196-197: the PA reference object's input_padded_pic, not `input`) */
     const uint8_t *src_luma = me_ctx->b64_src_ptr - (size_t)b64_origin_y * me_ctx->b64_src_stride - b64_origin_x;
-    const int32_t  src_slot = shim_slot_of_plane(src_luma, me_ctx->b64_src_stride, pcs->picture_number);
+    const void    *scope    = me_ctx->me_type == ME_MCTF ? (const void *)pcs : NULL;
+    const int32_t  src_slot = shim_slot_of_plane(src_luma, me_ctx->b64_src_stride, pcs->picture_number, scope);
     for (int l = 0; l < p.num_of_list_to_search; l++)
         for (int r = 0; r < p.num_of_ref_pic_to_search[l]; r++)
-            p.ref_pic_id[l][r] = shim_slot_of(me_ctx->me_ds_ref_array[l][r].picture_ptr, me_ctx->me_ds_ref_array[l][r].picture_number);
+            p.ref_pic_id[l][r] = shim_slot_of(me_ctx->me_ds_ref_array[l][r].picture_ptr, me_ctx->me_ds_ref_array[l][r].picture_number, scope);
     ShimJob *j = shim_new_job(pcs, me_ctx->me_type, ref_number, ((w + 63) / 64) * ((h + 63) / 64), &p);
     SHIM_CHECK(svtme_picture_me(g.sess, src_slot, &p, &j->res, /*sync*/ 1));
     if (j->hme) SHIM_CHECK(svtme_fetch_hme_state(g.sess, j->hme, (size_t)j->n_b64 * sizeof(SvtMeHmeState)));
@@ -349,6 +376,7 @@ EbErrorType __wrap_svt_aom_motion_estimation_b64(PictureParentControlSet *pcs, u
         SHIM_CHECK(svtme_session_wait_batch(g.sess, j->seq));
         j->pending = 0;
     }
+    j->readers++;
     pthread_mutex_unlock(&g.mu);
     if (b64_index >= j->n_b64) shim_fatal("b64 index out of range", b64_index);
 
@@ -369,6 +397,21 @@ EbErrorType __wrap_svt_aom_motion_estimation_b64(PictureParentControlSet *pcs, u
             memcpy(me_ctx->p_sb_best_sad[l][k], r->p_sb_best_sad + o * 85, 85 * 4);
             memcpy(me_ctx->p_sb_best_mv[l][k], r->p_sb_best_mv + o * 85, 85 * 4);
         }
+    /* the per-size views of the best arrays, as integer_search_b64 leaves them (motion_estimation.c:1370-1386): on the last
+       (list, reference) it searched. Read outside motion_estimation.c only by the temporal filter, whose single
+       reference is [0][0] (temporal_filtering.c:1860-2226, :2672). */
+    {
+        const int ll = me_ctx->num_of_list_to_search > 1 && me_ctx->num_of_ref_pic_to_search[1] ? 1 : 0;
+        const int lr = me_ctx->num_of_ref_pic_to_search[ll] ? me_ctx->num_of_ref_pic_to_search[ll] - 1 : 0;
+        me_ctx->p_best_sad_64x64 = &me_ctx->p_sb_best_sad[ll][lr][ME_TIER_ZERO_PU_64x64];
+        me_ctx->p_best_sad_32x32 = &me_ctx->p_sb_best_sad[ll][lr][ME_TIER_ZERO_PU_32x32_0];
+        me_ctx->p_best_sad_16x16 = &me_ctx->p_sb_best_sad[ll][lr][ME_TIER_ZERO_PU_16x16_0];
+        me_ctx->p_best_sad_8x8   = &me_ctx->p_sb_best_sad[ll][lr][ME_TIER_ZERO_PU_8x8_0];
+        me_ctx->p_best_mv64x64   = &me_ctx->p_sb_best_mv[ll][lr][ME_TIER_ZERO_PU_64x64];
+        me_ctx->p_best_mv32x32   = &me_ctx->p_sb_best_mv[ll][lr][ME_TIER_ZERO_PU_32x32_0];
+        me_ctx->p_best_mv16x16   = &me_ctx->p_sb_best_mv[ll][lr][ME_TIER_ZERO_PU_16x16_0];
+        me_ctx->p_best_mv8x8     = &me_ctx->p_sb_best_mv[ll][lr][ME_TIER_ZERO_PU_8x8_0];
+    }
     if (mctf) {
         /* motion_estimation.c:2539-2544, :3179-3183 */
         if (ABS(me_ctx->search_results[0][0].hme_sc_x) > ABS(me_ctx->search_results[0][0].hme_sc_y)) me_ctx->tf_tot_horz_blks++;
@@ -391,6 +434,7 @@ EbErrorType __wrap_svt_aom_motion_estimation_b64(PictureParentControlSet *pcs, u
     }
 
     pthread_mutex_lock(&g.mu);
+    j->readers--;
     if (++j->delivered == j->n_b64) { /* every b64 is asked for exactly once (me_process.c:174-271) */
         free(j->mem);
         memset(j, 0, sizeof(*j));
@@ -450,10 +494,10 @@ void svtme_shim_submit_pictures(PictureParentControlSet **pcs_list, uint32_t n) 
         SvtMePicParams *p = &params[k];
         svtme_shim_flatten(pcs, m, p);
         if (k && !same_stage_structure(&params[0].ctrls, &p->ctrls)) continue; /* left to the per-picture launch */
-        ids[k] = shim_slot_of(src, pcs->picture_number);
+        ids[k] = shim_slot_of(src, pcs->picture_number, NULL);
         for (int l = 0; l < p->num_of_list_to_search; l++)
             for (int r = 0; r < p->num_of_ref_pic_to_search[l]; r++)
-                p->ref_pic_id[l][r] = shim_slot_of(m->me_ds_ref_array[l][r].picture_ptr, m->me_ds_ref_array[l][r].picture_number);
+                p->ref_pic_id[l][r] = shim_slot_of(m->me_ds_ref_array[l][r].picture_ptr, m->me_ds_ref_array[l][r].picture_number, NULL);
         jobs[k] = shim_new_job(pcs, ME_OPEN_LOOP, 0, pcs->b64_total_count, p);
         res[k]  = jobs[k]->res;
         k++;
@@ -483,8 +527,8 @@ void __wrap_dg_detector_hme_level0(struct PictureParentControlSet *ppcs, uint32_
         pthread_mutex_lock(&g.mu);
         shim_session(ppcs->aligned_width, ppcs->aligned_height);
         g.clock++;
-        const int32_t  s = shim_slot_of(so->input_padded_pic, ppcs->picture_number);
-        const int32_t  r = shim_slot_of(ro->input_padded_pic, dg->ref_pic->picture_number);
+        const int32_t  s = shim_slot_of(so->input_padded_pic, ppcs->picture_number, &g);
+        const int32_t  r = shim_slot_of(ro->input_padded_pic, dg->ref_pic->picture_number, &g);
         SvtMeDgMetrics m = {.input_resolution = (uint32_t)ppcs->input_resolution};
         SHIM_CHECK(svtme_dg_detector_hme(g.sess, s, r, &m, NULL, NULL));
         g.n_dg++;
