@@ -38,6 +38,11 @@ ENCODES = [
     ("M5_720p", 1280, 720, 18, ["--preset", "5", "--lp", "6"]),
     ("M2_odd_size", 200, 136, 20, ["--preset", "2"]),                       # width / height not multiples of 64
     ("M8_10bit", 320, 192, 20, ["--preset", "8"]),                         # 10-bit input: ME reads the 8 MSBs
+    ("M12_no_8x8", 640, 360, 20, ["--preset", "12"]),                       # fastest presets: 8x8 ME off at larger sizes (21 PUs per b64)
+    ("M0_gm_mrp", 192, 128, 12, ["--preset", "0"]),                         # global-motion flags, widest windows
+    ("M6_three_layers", 320, 192, 20, ["--preset", "6", "--hierarchical-levels", "3"]),
+    ("M8_no_tf", 320, 192, 20, ["--preset", "8", "--enable-tf", "0"]),
+    ("M13_1080p", 1920, 1080, 6, ["--preset", "13", "--lp", "8"]),
 ]
 
 
