@@ -383,6 +383,10 @@ def run_ours(a):
         hbm_peak = peaks.get("hbm_gbs", 6650.0)
         n_refs = wl.mrp["l0"] + wl.mrp["l1"]
         dominant, dom_ms, dom_ops = ("k_fullpel", fp_ms, fp_ops) if fp_ms >= hme_ms else ("k_hme", hme_ms, hme_ops)
+        # the two timed groups of the launch sequence (CUDA events around each, on the session's compute stream)
+        KERNELS = {"k_hme": "HME stage = k_search16 (pre-HME, level 0) + k_search_blk (levels 1, 2) + k_hme_ctl before/between/after them; "
+                            "k_search16 is ~55 % of it (profiles/r01_final_summary.md)",
+                   "k_fullpel": "full-pel stage = k_fp / k_fp_big + k_post + k_mask_unsearched"}
         # algorithmic bytes of one launch (one picture): every plane of the source and of each reference read once
         # (1 + 1/4 + 1/16 of WxH each) + the per-b64 results the launch writes
         plane = 1.3125 * wl.w * wl.h if dominant == "k_hme" else 1.0 * wl.w * wl.h
@@ -408,16 +412,16 @@ def run_ours(a):
             "host_queue_ms_per_step": round(host_ms_resident, 3),
             "gpu_launches": int(launches),
             "clocks": clocks,
-            "roofline": {"bound": "hbm", "kernel": dominant, "achieved": round(alg_bytes / avg_s / 1e9, 2), "peak": hbm_peak,
+            "roofline": {"bound": "hbm", "kernel": KERNELS[dominant], "achieved": round(alg_bytes / avg_s / 1e9, 2), "peak": hbm_peak,
                          "unit": "GB/s", "frac": round(alg_bytes / avg_s / 1e9 / hbm_peak, 5), "traffic": traffic,
                          "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback",
                          "note": "integer-ALU bound kernel (byte SAD); see roofline_int"},
-            "roofline_int": {"bound": "int_alu(VABSDIFF4.U8.ACC)", "kernel": dominant,
+            "roofline_int": {"bound": "int_alu(VABSDIFF4.U8.ACC)", "kernel": KERNELS[dominant],
                              "achieved": round(dom_ops / (dom_ms * 1e-3) / 1e12, 3) if dom_ms else None,
                              "peak": round(int_peak / 1e12, 2), "unit": "T |a-b| ops/s",
                              "frac": round(dom_ops / (dom_ms * 1e-3) / int_peak, 4) if dom_ms else None,
                              "peak_def": "64 lane-instr/clk/SM (ALU pipe, measured 57 VABS + 7 IADD) x 4 px x 148 SM x sampled SM clock"},
-            "stage_ms_per_picture": {"k_hme": round(hme_ms / max(1, n_timed), 4), "k_fullpel": round(fp_ms / max(1, n_timed), 4)},
+            "stage_ms_per_picture": {"hme_stage": round(hme_ms / max(1, n_timed), 4), "fullpel_stage": round(fp_ms / max(1, n_timed), 4)},
             "sad_gops": round((hme_ops + fp_ops) / max(1, n_timed) * pics / (ms * 1e-3) / 1e9, 1),
             "tf_me": {"metric": "temporal-filter ME (ME_MCTF, tf hme_me_level %d, FULL_SAD) picture pairs/s, resident" % tf_level,
                       "value": round(1e3 / tf_ms, 1), "ms_per_pair": round(tf_ms, 4), "sad_gops": round(tf_ops / (tf_ms * 1e-3) / 1e9, 1)},
