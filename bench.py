@@ -40,6 +40,9 @@ def parse_args():
     ap.add_argument("--frames", type=int, default=240, help="length of the synthetic clip")
     ap.add_argument("--concurrency", type=int, default=1, choices=[1, 2], help="compute streams per session (svtme_session_set_concurrency)")
     ap.add_argument("--e2e-probe", default="full", choices=["full", "h2d", "d2h"], help="diagnostic: drop one direction of the end-to-end copies")
+    ap.add_argument("--host-numa", default="auto", choices=["auto", "off"],
+                    help="auto: run this rank's threads on (or, failing that, bind its memory to) the NUMA node of its GPU, so that "
+                         "the pinned frames and result arrays it allocates are local to the GPU's PCIe root")
     ap.add_argument("--qp", type=int, default=35)
     ap.add_argument("--cpu-baseline-pics", type=int, default=0, help="0 = one picture per host core")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -264,6 +267,42 @@ def slot_of(poc, runner):
     return poc % runner.N_SLOTS
 
 
+def _cpulist(text):
+    out = set()
+    for part in text.strip().split(","):
+        if not part:
+            continue
+        lo, _, hi = part.partition("-")
+        out.update(range(int(lo), int(hi or lo) + 1))
+    return out
+
+
+def bind_to_gpu_numa_node(torch, dev):
+    """Host placement for one-process-per-GPU runs: pinned memory is first-touch, so where this process runs decides which
+    socket's memory (and whether the inter-socket link) every H2D / D2H copy of the end-to-end pass crosses. Returns what
+    was done, for the JSON line."""
+    info = {"gpu_node": None, "policy": "none"}
+    try:
+        p = torch.cuda.get_device_properties(dev)
+        bdf = "%04x:%02x:%02x.0" % (p.pci_domain_id, p.pci_bus_id, p.pci_device_id)
+        node = int(open("/sys/bus/pci/devices/%s/numa_node" % bdf).read())
+        info["gpu_node"] = node
+        if node < 0:
+            return info
+        cpus = _cpulist(open("/sys/devices/system/node/node%d/cpulist" % node).read()) & os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            info["policy"] = "cpu affinity (%d cpus of node %d)" % (len(cpus), node)
+        else:  # the cpus this container may use are on another socket: bind the memory instead
+            import ctypes
+            mask = ctypes.c_ulong(1 << node)
+            rc = ctypes.CDLL(None, use_errno=True).syscall(238, 2, ctypes.byref(mask), 64)  # set_mempolicy(MPOL_BIND)
+            info["policy"] = "membind node %d" % node if rc == 0 else "none (set_mempolicy errno %d)" % ctypes.get_errno()
+    except Exception as e:  # no sysfs / no permission: leave the placement to the OS
+        info["policy"] = "none (%s)" % type(e).__name__
+    return info
+
+
 def run_ours(a):
     import torch
     import torch.distributed as dist
@@ -273,6 +312,7 @@ def run_ours(a):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device. The ME path has no CPU fallback (use --impl reference for the CPU arm).")
     torch.cuda.set_device(local)
+    numa = bind_to_gpu_numa_node(torch, local) if a.host_numa == "auto" else {"gpu_node": None, "policy": "off"}
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     wl = Workload(a)
@@ -405,6 +445,7 @@ def run_ours(a):
             "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
             "config": {"workload": wl.name, "pictures_per_step": wl.mgop, "batch": "one launch sequence per mini-GOP (svtme_picture_me_batch), consecutive mini-GOPs on %d compute stream(s)" % a.concurrency, "sharding": "mini-GOP m -> rank m % N",
                        "e2e_pipeline": "host uploads, kernels and result downloads on three streams; two batches in flight, every step's results land in pinned host memory inside the timed region",
+                       "host_numa": numa,
                        "l2": "inputs larger than L2: %d distinct %dx%d frames (%.0f MB) stream through the picture store, no explicit flush"
                              % (wl.n_frames, wl.w, wl.h, wl.n_frames * wl.w * wl.h / 1e6)},
             "e2e": {"value": round(e2e, 2), "unit": "frames/s", "h2d_bytes_per_step": int(h2d_step), "d2h_bytes_per_step": int(d2h_step),
