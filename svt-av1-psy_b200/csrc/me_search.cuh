@@ -14,6 +14,7 @@
 // 0xffffff. Result = 64-bit key (sad << 32 | y*sa_w + x); atomicMin over the tiles of a job keeps
 // the first minimum in raster order.
 #pragma once
+#include <type_traits>
 #include "me_device.cuh"
 #include "me_tma.cuh"
 
@@ -172,9 +173,14 @@ __device__ __forceinline__ void s16_tile_tasks(uint32_t buf, int pitch, uint32_t
         }
         uint32_t tb = 0xffffffffu;
         const uint32_t idx = ((uint32_t)yy << 8) | (uint32_t)(8 * oct);
+        if (8 * oct + 8 <= tw) {
 #pragma unroll
-        for (int p = 0; p < 8; p++)
-            if (8 * oct + p < tw) tb = min(tb, (acc[p] << 16) + idx + p);
+            for (int p = 0; p < 8; p++) tb = min(tb, (acc[p] << 16) + idx + p);
+        } else {
+#pragma unroll
+            for (int p = 0; p < 8; p++)
+                if (8 * oct + p < tw) tb = min(tb, (acc[p] << 16) + idx + p);
+        }
         s16_run_update(run, best, tb, (x0 + 8 * oct >= sp.x ? 1 : 0) + (y >= sp.y ? 2 : 0));
     }
     s16_merge_best(best, run.key, run.qd);
@@ -208,11 +214,13 @@ __device__ __forceinline__ void s16_tile_tasks_vb(uint32_t buf, int pitch, uint3
 #pragma unroll
             for (int p = 0; p < 8; p++) acc[g][p] = 0;
         // word address of the octet's first byte (LDS.32: lanes 8 bytes apart, 2-way bank conflict, far below the ALU time)
-        uint32_t row = buf + (uint32_t)(yy0 * pitch) + ((a + 8u * (uint32_t)oct) & ~3u);
-        // a real loop over the reference rows (the source row each one meets is read from shared memory, a broadcast):
-        // unrolled it is ~1100 instructions and the kernel stalls on instruction fetch
-#pragma unroll 1
-        for (int k = 0; k < 8 + G - 1; k++, row += (uint32_t)(2 * pitch)) {
+        const uint32_t row0 = buf + (uint32_t)(yy0 * pitch) + ((a + 8u * (uint32_t)oct) & ~3u);
+        // real loops over the reference rows (the source row each one meets is read from shared memory, a broadcast):
+        // unrolled it is ~1100 instructions and the kernel stalls on instruction fetch. Reference row k meets block row
+        // k - g of search row yy0 + 2g: rows G-1 .. 7 meet ALL G search rows (steady loop, no conditions), the first
+        // and last G-1 rows only some of them (one short loop with the range checks).
+        auto ref_row = [&](int k, auto all_rows) {
+            const uint32_t row = row0 + (uint32_t)(2 * k * pitch);
             uint32_t c[7], w[6], s1[5], s2[5], s3[5];
 #pragma unroll
             for (int i = 0; i < 7; i++) asm volatile("ld.shared.u32 %0, [%1];" : "=r"(c[i]) : "r"(row + 4u * i));
@@ -226,8 +234,8 @@ __device__ __forceinline__ void s16_tile_tasks_vb(uint32_t buf, int pitch, uint3
             }
 #pragma unroll
             for (int g = 0; g < G; g++) {
-                const int rr = k - g; // block row this reference row meets for search row yy0 + 2g (warp-uniform)
-                if ((unsigned)rr < 8u) {
+                const int rr = k - g; // warp-uniform
+                if (decltype(all_rows)::value || (unsigned)rr < 8u) {
                     const uint4 sv = lds128(src + 16u * (uint32_t)rr);
                     const uint32_t s[4] = {sv.x, sv.y, sv.z, sv.w};
 #pragma unroll
@@ -243,7 +251,11 @@ __device__ __forceinline__ void s16_tile_tasks_vb(uint32_t buf, int pitch, uint3
                     }
                 }
             }
-        }
+        };
+#pragma unroll 1
+        for (int j = 0; j < 2 * (G - 1); j++) ref_row(j < G - 1 ? j : j + 9 - G, std::false_type{});
+#pragma unroll 1
+        for (int k = G - 1; k < 8; k++) ref_row(k, std::true_type{});
         const int right = x0 + 8 * oct >= sp.x ? 1 : 0;
 #pragma unroll
         for (int g = 0; g < G; g++) {
@@ -251,9 +263,14 @@ __device__ __forceinline__ void s16_tile_tasks_vb(uint32_t buf, int pitch, uint3
             if (yy < th) {
                 const uint32_t idx = ((uint32_t)yy << 8) | (uint32_t)(8 * oct);
                 uint32_t tb = 0xffffffffu;
+                if (8 * oct + 8 <= tw) { // all but the last octet of a row: no per-position range checks
 #pragma unroll
-                for (int p = 0; p < 8; p++)
-                    if (8 * oct + p < tw) tb = min(tb, (acc[g][p] << 16) + idx + p);
+                    for (int p = 0; p < 8; p++) tb = min(tb, (acc[g][p] << 16) + idx + p);
+                } else {
+#pragma unroll
+                    for (int p = 0; p < 8; p++)
+                        if (8 * oct + p < tw) tb = min(tb, (acc[g][p] << 16) + idx + p);
+                }
                 s16_run_update(run, best, tb, right + (y0 + yy >= sp.y ? 2 : 0));
             }
         }
