@@ -426,7 +426,7 @@ def run_ours(a):
         # the two timed groups of the launch sequence (CUDA events around each, on the session's compute stream)
         KERNELS = {"k_hme": "HME stage = k_search16 (pre-HME, level 0) + k_search_blk (levels 1, 2) + k_hme_ctl before/between/after them; "
                             "k_search16 is ~55 % of it (profiles/r01_final_summary.md)",
-                   "k_fullpel": "full-pel stage = k_fp / k_fp_big + k_post + k_mask_unsearched"}
+                   "k_fullpel": "full-pel stage = k_fp + k_fp_big (k_post follows, outside both timed stages)"}
         # algorithmic bytes of one launch (one picture): every plane of the source and of each reference read once
         # (1 + 1/4 + 1/16 of WxH each) + the per-b64 results the launch writes
         plane = 1.3125 * wl.w * wl.h if dominant == "k_hme" else 1.0 * wl.w * wl.h

@@ -486,8 +486,7 @@ int svtme_launch_picture_me(const PicJob *h_jobs, int n, const PicJob *d_jobs, c
     }
     if (ev_fp1) cudaEventRecord(ev_fp1, st);
     k_post<<<dim3(n_b64, ny), POST_THREADS, 0, st>>>(d_jobs);
-    k_mask_unsearched<<<dim3(n_b64, ny), 96, 0, st>>>(d_jobs);
-    launches += 2;
+    launches += 1;
     return launches;
 }
 

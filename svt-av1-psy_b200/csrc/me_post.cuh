@@ -22,6 +22,7 @@ struct PostSh {
     uint64_t hme_sad[2][4];
     uint8_t  do_ref[2][4];
     uint32_t me_distortion[85];
+    uint32_t best_sad[8 * 85], best_mv[8 * 85]; // this b64's p_sb_best_sad / p_sb_best_mv: built here, read by every later step
 };
 
 __global__ void __launch_bounds__(POST_THREADS) k_post(const PicJob *__restrict__ jobs) {
@@ -31,41 +32,59 @@ __global__ void __launch_bounds__(POST_THREADS) k_post(const PicJob *__restrict_
     const SvtMeCtrls     &c   = pp.ctrls;
     const int             tid = threadIdx.x, b = blockIdx.x;
     const SbState        &st  = job.sb_state[b];
-    const uint32_t *bs = job.best_sad + (size_t)b * 2 * 4 * 85;
-    const uint32_t *bm = job.best_mv + (size_t)b * 2 * 4 * 85;
-#define BS(l, r, n) bs[((l) * 4 + (r)) * 85 + (n)]
-#define BM(l, r, n) bm[((l) * 4 + (r)) * 85 + (n)]
+    uint32_t *gbs = job.best_sad + (size_t)b * 2 * 4 * 85;
+    uint32_t *gbm = job.best_mv + (size_t)b * 2 * 4 * 85;
+#define BS(l, r, n) sh.best_sad[((l) * 4 + (r)) * 85 + (n)]
+#define BM(l, r, n) sh.best_mv[((l) * 4 + (r)) * 85 + (n)]
     const uint8_t *nref = pp.num_of_ref_pic_to_search;
     const int n_lists_cfg = pp.num_of_list_to_search;
 
-    // ---- full-pel keys -> p_sb_best_sad / p_sb_best_mv (me_context.h:395-396) ----
-    if (job.fp_keys) {
+    // ---- full-pel keys -> p_sb_best_sad / p_sb_best_mv (me_context.h:395-396), kept in shared memory; global memory
+    //      gets them once, at the end, with the entries of references that end with do_ref == 0 zeroed ----
+    {
         const bool sub = c.me_search_method == SVTME_SUB_SAD_SEARCH;
         for (int i = tid; i < 8 * 85; i += POST_THREADS) {
             const int lr = i / 85, pu = i - lr * 85;
-            if ((lr >> 2) >= n_lists_cfg || (lr & 3) >= nref[lr >> 2]) continue; // a slot the picture does not have
-            const FpJobG &fj = job.fp_jobs[(size_t)b * 8 + lr];
-            if (!fj.active) continue; // not searched: the mirrors keep stale data, as in the reference
-            const unsigned long long k = job.fp_keys[((size_t)b * 8 + lr) * 85 + pu];
-            uint32_t sad = MAX_SAD_VALUE_U32, mv = 0; // initial bests, :1368 and :3119
-            if (k != ~0ull) {
-                sad = (uint32_t)(k >> 32) << (sub ? 1 : 0);
-                const uint32_t gi = (uint32_t)k;
-                int16_t mx, my;
-                if (gi == 0) { // the variance probe at the search centre
-                    mx = fj.xc;
-                    my = fj.yc;
-                } else {
-                    mx = (int16_t)((int32_t)((gi - 1) % (uint32_t)fj.sa_w) + fj.x_origin);
-                    my = (int16_t)((int32_t)((gi - 1) / (uint32_t)fj.sa_w) + fj.y_origin);
+            const bool have = job.fp_keys && (lr >> 2) < n_lists_cfg && (lr & 3) < nref[lr >> 2] && job.fp_jobs[(size_t)b * 8 + lr].active;
+            uint32_t sad, mv;
+            if (!have) { // a slot the picture does not have, or not searched: the mirrors keep stale data, as in the reference
+                sad = gbs[i];
+                mv  = gbm[i];
+            } else {
+                const FpJobG &fj = job.fp_jobs[(size_t)b * 8 + lr];
+                const unsigned long long k = job.fp_keys[((size_t)b * 8 + lr) * 85 + pu];
+                sad = MAX_SAD_VALUE_U32; // initial bests, :1368 and :3119
+                mv  = 0;
+                if (k != ~0ull) {
+                    sad = (uint32_t)(k >> 32) << (sub ? 1 : 0);
+                    const uint32_t gi = (uint32_t)k;
+                    int16_t mx, my;
+                    if (gi == 0) { // the variance probe at the search centre
+                        mx = fj.xc;
+                        my = fj.yc;
+                    } else {
+                        mx = (int16_t)((int32_t)((gi - 1) % (uint32_t)fj.sa_w) + fj.x_origin);
+                        my = (int16_t)((int32_t)((gi - 1) / (uint32_t)fj.sa_w) + fj.y_origin);
+                    }
+                    mv = ((uint32_t)(uint16_t)my << 16) | (uint16_t)mx;
                 }
-                mv = ((uint32_t)(uint16_t)my << 16) | (uint16_t)mx;
             }
-            job.best_sad[((size_t)b * 8 + lr) * 85 + pu] = sad;
-            job.best_mv[((size_t)b * 8 + lr) * 85 + pu]  = mv;
+            sh.best_sad[i] = sad;
+            sh.best_mv[i]  = mv;
         }
         __syncthreads();
     }
+    // zero the MeContext mirrors of references that end with do_ref == 0, and of a b64 the temporal filter left early
+    // (their content is stale in the reference), so that dumps are deterministic; everything
+    // else is written as built. Called by all threads once sh.do_ref is final and nobody reads the mirrors any more.
+    auto write_mirrors = [&]() {
+        for (int i = tid; i < 8 * 85; i += POST_THREADS) {
+            const int lr = i / 85, l = lr >> 2, r = lr & 3;
+            const bool keep = l < n_lists_cfg && r < nref[l] && sh.do_ref[l][r] && !st.tf_exit;
+            gbs[i] = keep ? sh.best_sad[i] : 0u;
+            gbm[i] = keep ? sh.best_mv[i] : 0u;
+        }
+    };
 
     const bool mctf = c.me_type == SVTME_ME_MCTF; // no pruning, candidate lists, statistics or GM flags (:3173, :3196)
     // ---- me_prune_ref ----
@@ -125,6 +144,7 @@ __global__ void __launch_bounds__(POST_THREADS) k_post(const PicJob *__restrict_
             }
             job.search_results[(size_t)b * 8 + tid] = sr;
         }
+        write_mirrors();
         return;
     }
     // the two special builders start from memset(total_me_candidate_index, 1, number_of_pus) (:2625, :2734)
@@ -229,19 +249,25 @@ __global__ void __launch_bounds__(POST_THREADS) k_post(const PicJob *__restrict_
     __syncthreads();
 
     // ---- compute_distortion + perform_gm_detection + SearchResults ----
+    uint32_t d8 = 0, d16 = 0, d32 = 0;
+    uint64_t sumsq = 0;
+    if (tid < 32) { // warp 0: the sums over the 64 / 16 / 4 PUs of a size as lane-parallel reductions
+        d8  = sh.me_distortion[21 + tid] + sh.me_distortion[21 + 32 + tid];
+        d16 = tid < 16 ? sh.me_distortion[5 + tid] : 0u;
+        d32 = tid < 4 ? sh.me_distortion[1 + tid] : 0u;
+        d8  = __reduce_add_sync(0xffffffffu, d8);
+        d16 = __reduce_add_sync(0xffffffffu, d16);
+        d32 = __reduce_add_sync(0xffffffffu, d32);
+        const long long mean = (long long)(d8 / 64);
+        const long long e0 = (long long)sh.me_distortion[21 + tid] - mean, e1 = (long long)sh.me_distortion[21 + 32 + tid] - mean;
+        sumsq = (uint64_t)(e0 * e0) + (uint64_t)(e1 * e1);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) sumsq += __shfl_xor_sync(0xffffffffu, sumsq, o);
+    }
     if (tid == 0) {
         const int org_x = (b % job.b64_cols) * 64, org_y = (b / job.b64_cols) * 64;
         const uint32_t gw = (uint32_t)imin(64, job.pic_w - org_x), gh = (uint32_t)imin(64, job.pic_h - org_y);
-        uint32_t d64 = sh.me_distortion[0], d32 = 0, d16 = 0, d8 = 0;
-        for (int i = 0; i < 4; i++) d32 += sh.me_distortion[1 + i];
-        for (int i = 0; i < 16; i++) d16 += sh.me_distortion[5 + i];
-        for (int i = 0; i < 64; i++) d8 += sh.me_distortion[21 + i];
-        const uint64_t mean = d8 / 64;
-        uint64_t sumsq = 0;
-        for (int i = 0; i < 64; i++) {
-            const long long diff = (long long)sh.me_distortion[21 + i] - (long long)mean;
-            sumsq += (uint64_t)(diff * diff);
-        }
+        const uint32_t d64 = sh.me_distortion[0];
         const uint32_t pix = gw * gh, size = 64 * 64;
         job.me_8x8_cost_variance[b] = (uint32_t)(sumsq / 64);
         job.rc_me_distortion[b]     = (pp.input_resolution <= 2) ? d8 : d16;
@@ -304,23 +330,8 @@ __global__ void __launch_bounds__(POST_THREADS) k_post(const PicJob *__restrict_
         }
         job.search_results[(size_t)b * 8 + tid] = sr;
     }
+    write_mirrors();
 #undef BS
 #undef BM
 }
 
-// zero the MeContext mirrors of refs that ended with do_ref == 0 (their content is stale in the
-// reference) so that dumps are deterministic
-__global__ void k_mask_unsearched(const PicJob *__restrict__ jobs) {
-    const PicJob &job = jobs[blockIdx.y];
-    const int b = blockIdx.x, tid = threadIdx.x;
-    for (int lr = 0; lr < 8; lr++) {
-        const SvtMeSearchResult &sr = job.search_results[(size_t)b * 8 + lr];
-        const int l = lr >> 2, r = lr & 3;
-        const bool searched = l < job.pp.num_of_list_to_search && r < job.pp.num_of_ref_pic_to_search[l];
-        if (searched && sr.do_ref && !job.sb_state[b].tf_exit) continue;
-        for (int i = tid; i < 85; i += blockDim.x) {
-            job.best_sad[((size_t)b * 8 + lr) * 85 + i] = 0;
-            job.best_mv[((size_t)b * 8 + lr) * 85 + i]  = 0;
-        }
-    }
-}
