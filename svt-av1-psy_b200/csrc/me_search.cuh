@@ -124,6 +124,11 @@ __device__ __forceinline__ void s16_run_update(S16Run &run, uint32_t (&best)[4],
     run.key = min(run.key, key);
 }
 
+// x / n for 1 <= n <= 16 and 0 <= x < 4096 without the ~20-instruction integer division (n = octets of a tile row):
+// ceil(2^16 / n) * x >> 16 is exact while x * (ceil(2^16/n) - 2^16/n) < 2^16 / n, i.e. for x < 2^16 / n
+__constant__ uint16_t c_inv16[17] = {0, 0, 32768, 21846, 16384, 13108, 10923, 9363, 8192, 7282, 6554, 5958, 5462, 5042, 4682, 4370, 4096};
+__device__ __forceinline__ int div_small(int x, int n) { return n == 1 ? x : (int)(((uint32_t)x * c_inv16[n]) >> 16); }
+
 // lane = (search row, octet of 8 positions); a lane reads 32 bytes per block row from the 8-byte boundary at or before
 // its octet (4 LDS.64, consecutive lanes = consecutive 8-byte units); the remaining 0..7 bytes of misalignment are the
 // same for every octet of the job: one warp-uniform word select (JW) and one funnel shift per word.
@@ -134,9 +139,10 @@ __device__ __forceinline__ void s16_tile_tasks(uint32_t buf, int pitch, uint32_t
     const int lane  = threadIdx.x & 31;
     const int n_oct = (tw + 7) >> 3;
     const bool     partial = bw < 16;
-    const uint32_t m0 = lo_bytes_mask(bw), m1 = lo_bytes_mask(bw - 4), m2 = lo_bytes_mask(bw - 8), m3 = lo_bytes_mask(bw - 12);
-    int yy = lane / n_oct, oct = lane - yy * n_oct;
-    const int dyy = 32 / n_oct, doct = 32 - dyy * n_oct;
+    uint32_t m0 = 0xffffffffu, m1 = 0xffffffffu, m2 = 0xffffffffu, m3 = 0xffffffffu;
+    if (partial) { m0 = lo_bytes_mask(bw); m1 = lo_bytes_mask(bw - 4); m2 = lo_bytes_mask(bw - 8); m3 = lo_bytes_mask(bw - 12); }
+    int yy = div_small(lane, n_oct), oct = lane - yy * n_oct;
+    const int dyy = div_small(32, n_oct), doct = 32 - dyy * n_oct;
     const uint32_t rstep = (uint32_t)(row_step * pitch);
     S16Run run = {0xffffffffu, 0};
     for (; yy < th; yy += dyy, oct += doct) {
@@ -205,7 +211,7 @@ __device__ __forceinline__ void s16_tile_tasks_vb(uint32_t buf, int pitch, uint3
     const uint32_t t8 = (a & 3u) * 8u;
     S16Run run = {0xffffffffu, 0};
     for (int t = lane; t < n_tasks; t += 32) {
-        const int ch = t / n_oct, oct = t - ch * n_oct;
+        const int ch = div_small(t, n_oct), oct = t - ch * n_oct;
         const int yy0 = npar == 2 ? (ch >> 1) * 2 * G + (ch & 1) : ch * 2 * G + par0;
         if (yy0 >= th) continue;
         uint32_t acc[G][8];
@@ -311,7 +317,7 @@ __device__ __forceinline__ void warp_stage_src16(uint32_t dst, const uint8_t *sr
     const int lane = threadIdx.x & 31;
     if (lane < n_rows) {
         uint4 v = __ldg((const uint4 *)(src + (size_t)lane * row_step * stride));
-        v.x &= lo_bytes_mask(bw); v.y &= lo_bytes_mask(bw - 4); v.z &= lo_bytes_mask(bw - 8); v.w &= lo_bytes_mask(bw - 12);
+        if (bw < 16) { v.x &= lo_bytes_mask(bw); v.y &= lo_bytes_mask(bw - 4); v.z &= lo_bytes_mask(bw - 8); v.w &= lo_bytes_mask(bw - 12); }
         asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(dst + 16u * lane), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
     }
 }
@@ -364,6 +370,7 @@ __global__ void __launch_bounds__(32 * SEARCH_WARPS) k_search16(const PicJob *__
     uint8_t *sbase = s_dyn + ((128u - (smem_u32(s_dyn) & 127u)) & 127u);
     TilePipe P;
     pipe_init(P, sbase + (size_t)warp * 2 * TM_S16_BUF, TM_S16_BUF, s_bar[warp], 0);
+    const uint32_t src32 = smem_u32(s_src[warp][0]); // stage st at + 256 bytes
     // issue: the tile load and the source rows of the unit's block (both land in stage `st`)
     auto issue = [&](const S16Unit &un, int st) {
         const PicJob &job = jobs[un.pic];
@@ -372,7 +379,7 @@ __global__ void __launch_bounds__(32 * SEARCH_WARPS) k_search16(const PicJob *__
         pipe_issue_bytes(P, st, map, (un.px + un.x0) & ~15, un.py + un.y0,
                          un.wide ? TM_S16W_BOX_W * TM_S16W_BOX_H : TM_S16T_BOX_W * TM_S16T_BOX_H);
         const DevPlane &ss = job.src.lvl[2];
-        warp_stage_src16(smem_u32(s_src[warp][st]), ss.buf + un.src_off, ss.stride, row_step, un.rows, un.bw);
+        warp_stage_src16(src32 + 256u * (uint32_t)st, ss.buf + un.src_off, ss.stride, row_step, un.rows, un.bw);
     };
     S16Unit cur = s16_fetch_unit(jobs, n_units);
     if (!cur.valid) return;
@@ -386,7 +393,7 @@ __global__ void __launch_bounds__(32 * SEARCH_WARPS) k_search16(const PicJob *__
         __syncwarp(); // the source rows written by other lanes
         uint32_t best[4];
         const S16Split sp = {cur.w0, cur.h0};
-        warp_search16_tile(P.buf[stage], cur.wide ? TM_S16W_BOX_W : TM_S16T_BOX_W, smem_u32(s_src[warp][stage]),
+        warp_search16_tile(P.buf[stage], cur.wide ? TM_S16W_BOX_W : TM_S16T_BOX_W, src32 + 256u * (uint32_t)stage,
                            (uint32_t)(cur.px + cur.x0) & 15u, cur.x0, cur.y0, cur.tw, cur.th, cur.bw, cur.rows, row_step, skip, sp, best);
         if (lane < 4 && (lane == 0 || cur.merged)) {
             const uint32_t k = lane == 0 ? best[0] : (lane == 1 ? best[1] : (lane == 2 ? best[2] : best[3]));

@@ -50,10 +50,12 @@ __device__ __forceinline__ void mbar_init(uint64_t *bar, int count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
 }
 __device__ __forceinline__ void mbar_fence_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
-__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+// bar32: shared-window address of the mbarrier (smem_u32 once, at pipe_init: a generic->shared conversion per wait was
+// 2 % of k_search16's instructions)
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar32, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar32), "r"(bytes) : "memory");
 }
-__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+__device__ __forceinline__ void mbar_wait(uint32_t bar32, uint32_t parity) {
     asm volatile(
         "{\n"
         ".reg .pred p;\n"
@@ -62,7 +64,7 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
         "@p bra DONE_%=;\n"
         "bra WAIT_%=;\n"
         "DONE_%=:\n"
-        "}\n" ::"r"(smem_u32(bar)), "r"(parity)
+        "}\n" ::"r"(bar32), "r"(parity)
         : "memory");
 }
 __device__ __forceinline__ uint2 lds64(uint32_t addr) {
@@ -79,14 +81,15 @@ __device__ __forceinline__ uint4 lds128(uint32_t addr) {
 // one warp's double-buffered tile pipeline
 struct TilePipe {
     uint32_t  buf[2]; // shared addresses of the two stages
-    uint64_t *bar;    // two mbarriers
+    uint32_t  bar[2]; // shared addresses of the two mbarriers
     uint32_t  phase;  // bit s = parity the next wait on stage s expects
     uint32_t  bytes;
 };
 __device__ __forceinline__ void pipe_init(TilePipe &P, uint8_t *stage0, uint32_t stage_bytes, uint64_t *bars, uint32_t box_bytes) {
     P.buf[0] = smem_u32(stage0);
     P.buf[1] = P.buf[0] + stage_bytes;
-    P.bar = bars;
+    P.bar[0] = smem_u32(&bars[0]);
+    P.bar[1] = P.bar[0] + 8u;
     P.phase = 0;
     P.bytes = box_bytes;
     if ((threadIdx.x & 31) == 0) { mbar_init(&bars[0], 1); mbar_init(&bars[1], 1); }
@@ -97,24 +100,24 @@ __device__ __forceinline__ void pipe_init(TilePipe &P, uint8_t *stage0, uint32_t
 // fill). The caller guarantees that every lane has finished reading stage s (a __syncwarp after the reads).
 __device__ __forceinline__ void pipe_issue(TilePipe &P, int s, const CUtensorMap *map, int x_aligned, int y) {
     if ((threadIdx.x & 31) == 0) {
-        mbar_expect_tx(&P.bar[s], P.bytes);
+        mbar_expect_tx(P.bar[s], P.bytes);
         asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(
                          P.buf[s]),
-                     "l"(map), "r"(x_aligned), "r"(y), "r"(smem_u32(&P.bar[s]))
+                     "l"(map), "r"(x_aligned), "r"(y), "r"(P.bar[s])
                      : "memory");
     }
 }
 __device__ __forceinline__ void pipe_issue_bytes(TilePipe &P, int s, const CUtensorMap *map, int x_aligned, int y, uint32_t bytes) {
     if ((threadIdx.x & 31) == 0) {
-        mbar_expect_tx(&P.bar[s], bytes);
+        mbar_expect_tx(P.bar[s], bytes);
         asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(
                          P.buf[s]),
-                     "l"(map), "r"(x_aligned), "r"(y), "r"(smem_u32(&P.bar[s]))
+                     "l"(map), "r"(x_aligned), "r"(y), "r"(P.bar[s])
                      : "memory");
     }
 }
 __device__ __forceinline__ void pipe_wait(TilePipe &P, int s) {
-    mbar_wait(&P.bar[s], (P.phase >> s) & 1u);
+    mbar_wait(P.bar[s], (P.phase >> s) & 1u);
     P.phase ^= 1u << s;
 }
 
