@@ -182,6 +182,12 @@ class Runner:
             for r, p in enumerate(lists[l]):
                 sin.ref_picture_number[l][r] = p
         p = self.me.sig_deriv_me(sin)
+        diag = os.environ.get("SVTME_DIAG_PREHME")  # diagnostic only (NOT the reference's configuration): shrink one pre-HME region
+        if diag:
+            for i in range(2):
+                if str(i) in diag:
+                    a = p.ctrls.prehme_sa_cfg[i]
+                    a.sa_min.width, a.sa_min.height, a.sa_max.width, a.sa_max.height = 8, 3, 8, 3
         for l in range(2):
             for r, rp in enumerate(lists[l]):
                 p.ref_pic_id[l][r] = rp % self.N_SLOTS

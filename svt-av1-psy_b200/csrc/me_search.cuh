@@ -284,6 +284,37 @@ __device__ __forceinline__ void s16_tile_tasks_vb(uint32_t buf, int pitch, uint3
     s16_merge_best(best, run.key, run.qd);
 }
 
+// Tiles with few positions (the 4 rows a 100-row pre-HME window leaves after its 96-row tile, windows cut by the picture
+// edge): lane = ONE position. The octet evaluator would run its 8 block rows with 4 of 32 lanes busy (~490 warp
+// instructions for 32 positions); here a lane reads the 5 words its position touches per block row, shifts them by its own
+// byte offset and issues 4 VABSDIFF4: ~110 warp instructions per 32 positions.
+__device__ __forceinline__ void s16_tile_tasks_pos(uint32_t buf, int pitch, uint32_t src, uint32_t a, int x0, int y0, int tw, int th,
+                                                   int n_rows, int row_step, bool skip_lines, S16Split sp, uint32_t (&best)[4]) {
+    const int lane = threadIdx.x & 31;
+    S16Run run = {0xffffffffu, 0};
+    for (int t = lane; t < tw * th; t += 32) {
+        const int yy = div_small(t, tw), x = t - yy * tw;
+        if (skip_lines && ((y0 + yy) & 1) == 0) continue;
+        const uint32_t off = a + (uint32_t)x, sh = (off & 3u) * 8u;
+        uint32_t row = buf + (uint32_t)(yy * pitch) + (off & ~3u);
+        const uint32_t rstep = (uint32_t)(row_step * pitch);
+        uint32_t acc = 0;
+#pragma unroll 2
+        for (int rr = 0; rr < n_rows; rr++, row += rstep) {
+            uint32_t c[5];
+#pragma unroll
+            for (int i = 0; i < 5; i++) asm volatile("ld.shared.u32 %0, [%1];" : "=r"(c[i]) : "r"(row + 4u * i));
+            const uint4 sv = lds128(src + 16u * (uint32_t)rr);
+            acc = sad4_acc(__funnelshift_r(c[0], c[1], sh), sv.x, acc);
+            acc = sad4_acc(__funnelshift_r(c[1], c[2], sh), sv.y, acc);
+            acc = sad4_acc(__funnelshift_r(c[2], c[3], sh), sv.z, acc);
+            acc = sad4_acc(__funnelshift_r(c[3], c[4], sh), sv.w, acc);
+        }
+        s16_run_update(run, best, (acc << 16) + ((uint32_t)yy << 8) + (uint32_t)x, (x0 + x >= sp.x ? 1 : 0) + (y0 + yy >= sp.y ? 2 : 0));
+    }
+    s16_merge_best(best, run.key, run.qd);
+}
+
 // a: byte offset of the tile's position 0 inside its rows ((plane x of the position) & 15). On return best[k] is the
 // warp-wide best of quadrant k in this tile, or 0xffffffff.
 __device__ inline void warp_search16_tile(uint32_t buf, int pitch, uint32_t src, uint32_t a, int x0, int y0, int tw, int th, int bw,
@@ -297,6 +328,8 @@ __device__ inline void warp_search16_tile(uint32_t buf, int pitch, uint32_t src,
         // skip_search_line drops the even rows of the WINDOW: parity is relative to y0
         const int par0 = skip_lines ? ((y0 & 1) ? 0 : 1) : 0;
         s16_tile_tasks_vb<S16_VB_G>(buf, pitch, src, a, x0, y0, tw, th, par0, skip_lines ? 1 : 2, sp, best);
+    } else if (bw == 16 && tw <= 16 && tw * th <= 64) {
+        s16_tile_tasks_pos(buf, pitch, src, a, x0, y0, tw, th, n_rows, row_step, skip_lines, sp, best);
     } else {
         const uint32_t h8 = a >> 3, t8 = (a & 3u) * 8u;
         if (a & 4u) s16_tile_tasks<1>(buf, pitch, src, h8, t8, x0, y0, tw, th, bw, n_rows, row_step, skip_lines, sp, best);
