@@ -86,9 +86,13 @@ void svt_unpack_and_2bcompress_c(uint16_t *in16b_buffer, uint32_t in16b_stride, 
 static void memcpy_wrap(void *dst, void const *src, size_t n) { memcpy(dst, src, n); }
 
 /* The ME rows of svt_aom_setup_rtcd_internal (aom_dsp_rtcd.c:499,507-514 for x86, :1199-1214 C) */
+static void set_rtcd_planes(void) {
+    /* the two pointers the pyramid builder reads; the ME rows are left as the caller selected them */
+    svt_memcpy    = memcpy_wrap;
+    downsample_2d = svt_aom_downsample_2d_c;
+}
 static void set_rtcd(int simd) {
-    svt_memcpy                                = memcpy_wrap;
-    downsample_2d                             = svt_aom_downsample_2d_c;
+    set_rtcd_planes();
     svt_sad_loop_kernel                       = svt_sad_loop_kernel_c;
     svt_ext_sad_calculation_8x8_16x16         = svt_ext_sad_calculation_8x8_16x16_c;
     svt_ext_sad_calculation_32x32_64x64       = svt_ext_sad_calculation_32x32_64x64_c;
@@ -110,6 +114,27 @@ static void set_rtcd(int simd) {
     if (simd >= 2)
         svt_sad_loop_kernel = svt_sad_loop_kernel_avx512_intrin;
 }
+
+/* Which ME table is installed right now: 0 = C, 1 = AVX2, 2 = AVX-512 SAD loop + AVX2 (the x86 production table,
+   aom_dsp_rtcd.c:499,507-514), -1 = a mixture. ref_rtcd_table_at_last_b64() is the same probe taken by run_b64 just
+   before the most recent svt_aom_motion_estimation_b64 call, so a test can see what a picture-level run executed. */
+static int g_table_at_last_b64 = -1;
+int ref_rtcd_table(void) {
+    const int loop = svt_sad_loop_kernel == svt_sad_loop_kernel_avx512_intrin ? 2
+        : svt_sad_loop_kernel == svt_sad_loop_kernel_avx2_intrin              ? 1
+        : svt_sad_loop_kernel == svt_sad_loop_kernel_c                        ? 0 : -1;
+    const int all8 = svt_ext_all_sad_calculation_8x8_16x16 == svt_ext_all_sad_calculation_8x8_16x16_avx2 ? 1
+        : svt_ext_all_sad_calculation_8x8_16x16 == svt_ext_all_sad_calculation_8x8_16x16_c               ? 0 : -1;
+    const int e32 = svt_ext_eight_sad_calculation_32x32_64x64 == svt_ext_eight_sad_calculation_32x32_64x64_avx2 ? 1
+        : svt_ext_eight_sad_calculation_32x32_64x64 == svt_ext_eight_sad_calculation_32x32_64x64_c              ? 0 : -1;
+    const int nxm = svt_nxm_sad_kernel == svt_nxm_sad_kernel_helper_avx2 ? 1
+        : svt_nxm_sad_kernel == svt_nxm_sad_kernel_helper_c              ? 0 : -1;
+    if (loop < 0 || all8 < 0 || e32 < 0 || nxm < 0) return -1;
+    if (all8 != e32 || all8 != nxm) return -1;
+    if (loop == 0) return all8 == 0 ? 0 : -1;
+    return all8 == 1 ? loop : -1;
+}
+int ref_rtcd_table_at_last_b64(void) { return g_table_at_last_b64; }
 
 /* ---------------- RTCD kernel pass-throughs ---------------- */
 void ref_sad_loop_kernel(int simd, uint8_t *src, uint32_t src_stride, uint8_t *ref, uint32_t ref_stride,
@@ -200,6 +225,7 @@ static void shim_forget(void) {
 typedef struct Planes {
     EbPictureBufferDesc full, quarter, sixteenth;
     uint8_t            *mem[3];
+    int                 cached; /* owned by the plane cache: planes_free leaves it alone */
 } Planes;
 
 static void desc_init(EbPictureBufferDesc *d, uint8_t *buf, int w, int h, int pad) {
@@ -221,7 +247,7 @@ static void desc_init(EbPictureBufferDesc *d, uint8_t *buf, int w, int h, int pa
    reference's own svt_aom_generate_padding and downsample_2d */
 static void build_planes_into(const uint8_t *luma, int w, int h, uint8_t *full, uint8_t *quarter,
                               uint8_t *sixteenth, Planes *p) {
-    set_rtcd(0);
+    set_rtcd_planes();
     desc_init(&p->full, full, w, h, FULL_PAD);
     desc_init(&p->quarter, quarter, w >> 1, h >> 1, QUARTER_PAD);
     desc_init(&p->sixteenth, sixteenth, w >> 2, h >> 2, SIXTEENTH_PAD);
@@ -243,13 +269,79 @@ int ref_build_planes(const uint8_t *luma, int width, int height, uint8_t *full, 
     return 0;
 }
 
-static void planes_alloc(Planes *p, const uint8_t *luma, int w, int h) {
+static void planes_alloc_fresh(Planes *p, const uint8_t *luma, int w, int h) {
     p->mem[0] = (uint8_t *)calloc((size_t)(w + 2 * FULL_PAD) * (h + 2 * FULL_PAD), 1);
     p->mem[1] = (uint8_t *)calloc((size_t)((w >> 1) + 2 * QUARTER_PAD) * ((h >> 1) + 2 * QUARTER_PAD), 1);
     p->mem[2] = (uint8_t *)calloc((size_t)((w >> 2) + 2 * SIXTEENTH_PAD) * ((h >> 2) + 2 * SIXTEENTH_PAD), 1);
+    p->cached = 0;
     build_planes_into(luma, w, h, p->mem[0], p->mem[1], p->mem[2], p);
 }
+
+/* Plane cache for the timed CPU baseline (bench.py): the encoder builds a picture's pyramid ONCE (Picture Analysis) and
+   every picture that references it reads the same PA reference object; without the cache this harness would rebuild the
+   pyramids of all references for every picture searched and the baseline would be charged work the reference never does.
+   Keyed by the caller's luma pointer. Off by default: the parity tests build their planes per call. */
+#define PLANE_CACHE_MAX 1024
+static struct {
+    const uint8_t *key[PLANE_CACHE_MAX];
+    int            w[PLANE_CACHE_MAX], h[PLANE_CACHE_MAX];
+    Planes         planes[PLANE_CACHE_MAX];
+    int            n, on;
+    pthread_mutex_t mu;
+} g_cache = {.mu = PTHREAD_MUTEX_INITIALIZER};
+
+static int cache_find(const uint8_t *luma, int w, int h) {
+    for (int i = 0; i < g_cache.n; i++)
+        if (g_cache.key[i] == luma && g_cache.w[i] == w && g_cache.h[i] == h) return i;
+    return -1;
+}
+void ref_plane_cache_enable(int on) { g_cache.on = on; }
+/* build (once) and keep the pyramid of the picture whose interior luma plane is at `luma`; 0 = built, 1 = was present */
+int ref_plane_cache_build(const uint8_t *luma, int width, int height) {
+    pthread_mutex_lock(&g_cache.mu);
+    int i = cache_find(luma, width, height);
+    pthread_mutex_unlock(&g_cache.mu);
+    if (i >= 0) return 1;
+    Planes p;
+    planes_alloc_fresh(&p, luma, width, height); /* outside the lock: callers build distinct pictures in parallel */
+    p.cached = 1;
+    pthread_mutex_lock(&g_cache.mu);
+    if (g_cache.n >= PLANE_CACHE_MAX) {
+        pthread_mutex_unlock(&g_cache.mu);
+        for (int k = 0; k < 3; k++) free(p.mem[k]);
+        return -1;
+    }
+    i = g_cache.n++;
+    g_cache.key[i] = luma; g_cache.w[i] = width; g_cache.h[i] = height; g_cache.planes[i] = p;
+    pthread_mutex_unlock(&g_cache.mu);
+    return 0;
+}
+void ref_plane_cache_drop(const uint8_t *luma) {
+    pthread_mutex_lock(&g_cache.mu);
+    for (int i = 0; i < g_cache.n; i++)
+        if (g_cache.key[i] == luma || !luma) {
+            for (int k = 0; k < 3; k++) free(g_cache.planes[i].mem[k]);
+            g_cache.n--;
+            g_cache.key[i] = g_cache.key[g_cache.n]; g_cache.w[i] = g_cache.w[g_cache.n]; g_cache.h[i] = g_cache.h[g_cache.n];
+            g_cache.planes[i] = g_cache.planes[g_cache.n];
+            i--;
+        }
+    pthread_mutex_unlock(&g_cache.mu);
+}
+
+static void planes_alloc(Planes *p, const uint8_t *luma, int w, int h) {
+    if (g_cache.on) {
+        ref_plane_cache_build(luma, w, h);
+        pthread_mutex_lock(&g_cache.mu);
+        int i = cache_find(luma, w, h);
+        if (i >= 0) *p = g_cache.planes[i];
+        pthread_mutex_unlock(&g_cache.mu);
+        if (i >= 0) return;
+    }
+    planes_alloc_fresh(p, luma, w, h);
+}
 static void planes_free(Planes *p) {
+    if (p->cached) return;
     for (int i = 0; i < 3; i++) free(p->mem[i]);
 }
 
@@ -582,6 +674,7 @@ static double run_b64(PicRun *run, MeContext *me, uint32_t x_b64, uint32_t y_b64
             me->me_ds_ref_array[i][j].picture_number        = in->ref_picture_number[i][j];
         }
 
+    g_table_at_last_b64 = ref_rtcd_table();
     double t0 = now_s();
     svt_aom_motion_estimation_b64(pcs, b64_index, b64_origin_x, b64_origin_y, me, ip);
     const double t_me = now_s() - t0;
@@ -916,6 +1009,7 @@ int ref_tf_me_picture(const RefTfIn *in, SvtMePicParams *params_out, SvtMePicRes
                 params_out->gm_enabled = 0; params_out->gm_use_distance_based_active_th = 0;
                 params_out->hierarchical_levels = 5;
             }
+            g_table_at_last_b64 = ref_rtcd_table();
             svt_aom_motion_estimation_b64(pcs, b64_index, ox, oy, me, ip);
             const int exited = me->tf_use_pred_64x64_only_th == (uint8_t)~0; /* motion_estimation.c:3179-3183 */
             if (res) {

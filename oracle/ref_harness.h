@@ -68,6 +68,17 @@ int ref_me_picture_mt(const RefMePicIn *in, SvtMePicResults *res, int n_threads,
    when the library was linked with the GPU shim (libsvtref_wrap.so) */
 int ref_me_minigop(const RefMePicIn *ins, int n_pics, SvtMePicResults *res, int n_threads, int submit);
 
+/* Which ME table is installed now / was installed when the most recent svt_aom_motion_estimation_b64 call of a
+   picture-level run started: 0 = C, 1 = AVX2, 2 = AVX-512 SAD loop + AVX2, -1 = mixed */
+int ref_rtcd_table(void);
+int ref_rtcd_table_at_last_b64(void);
+
+/* Plane cache (bench.py's CPU baseline only): with it on, ref_me_picture* build the pyramid of a picture once per luma
+   pointer, as the encoder does once per picture in Picture Analysis, instead of once per use as a reference. */
+void ref_plane_cache_enable(int on);
+int  ref_plane_cache_build(const uint8_t *luma, int width, int height);
+void ref_plane_cache_drop(const uint8_t *luma); /* NULL = everything */
+
 /* Build the three padded planes of a picture with the reference's own decimation/padding.
    Buffers must hold (w+2*72)*(h+2*72), (w/2+64)*(h/2+64), (w/4+32)*(h/4+32) bytes. */
 int ref_build_planes(const uint8_t *luma, int width, int height, uint8_t *full, uint8_t *quarter,

@@ -66,6 +66,29 @@ def test_reference_simd_tables_equal_c(orc, simd):
     l0, l1 = [0, 8, 4, 2], [32, 24, 20]
     src = clip.frame(16)
     refs = [[clip.frame(p) for p in l0], [clip.frame(p) for p in l1]]
+    lib = po.ref_lib()
     a, _, _ = po.ref_me_picture(po.make_pic_in(src, refs, [l0, l1], 16, 4, simd=0))
+    assert lib.ref_rtcd_table_at_last_b64() == 0
     b, _, _ = po.ref_me_picture(po.make_pic_in(src, refs, [l0, l1], 16, 4, simd=simd))
+    # the table the picture's b64 calls really ran with (round 1 compared C with C here: the plane builder reset it)
+    assert lib.ref_rtcd_table_at_last_b64() == simd
     compare(a, b)
+
+
+def test_reference_simd_path_is_the_fast_one(orc):
+    """The CPU baseline bench.py quotes is the reference's x86 production table (aom_dsp_rtcd.c:499,507-514); a
+    picture-level run with simd=2 must execute it (probe) and be an order of magnitude faster than the C kernels."""
+    if "avx512bw" not in open("/proc/cpuinfo").read():
+        pytest.skip("host without AVX-512")
+    w, h = 1920, 1080
+    clip = PanningNoise(w, h, seed=7, vx=2, vy=1, max_frames=40)
+    l0, l1 = [0, 8, 4, 2], [32, 24, 20]
+    src = clip.frame(16)
+    refs = [[clip.frame(p) for p in l0], [clip.frame(p) for p in l1]]
+    lib = po.ref_lib()
+    b, _, t_simd = po.ref_me_picture(po.make_pic_in(src, refs, [l0, l1], 16, 4, simd=2), debug=False)
+    assert lib.ref_rtcd_table_at_last_b64() == 2
+    a, _, t_c = po.ref_me_picture(po.make_pic_in(src, refs, [l0, l1], 16, 4, simd=0), debug=False)
+    assert lib.ref_rtcd_table_at_last_b64() == 0
+    compare(a, b)
+    assert t_c > 10 * t_simd, (t_c, t_simd)
