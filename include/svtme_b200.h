@@ -328,8 +328,72 @@ uint32_t svtme_picture_me_batch(SvtMeSession *s, uint32_t n, const int32_t *pic_
 /* Copy the device results of picture `index` of the last batch. */
 uint32_t svtme_fetch_results_batch(SvtMeSession *s, uint32_t index, SvtMePicResults *results, int sync);
 
-/* Same, but results stay on the device (pointers returned via svtme_device_results). Used to
-   time the kernels with inputs and outputs resident in HBM. */
+/* ---- packed results: one download per batch ------------------------------------------------------------------------
+   The arrays of SvtMePicResults are what the rest of the encoder reads after svt_aom_motion_estimation_b64 returns:
+     SVTME_F_SB_RESULTS      total_me_candidate_index, me_mv_array, me_candidate_array = pcs->pa_me_data->me_results[b64]
+                             (me_sb_results.h:44-51; consumers: src_ops_process.c (TPL), mode decision)
+     SVTME_F_STATS           the eight per-b64 PCS arrays compute_distortion / perform_gm_detection write
+                             (motion_estimation.c:3034-3077, :2908-3031)
+     SVTME_F_SEARCH_RESULTS  me_ctx->search_results (me_context.h:348-355)
+     SVTME_F_BEST            me_ctx->p_sb_best_sad / p_sb_best_mv (me_context.h:395-396)
+     SVTME_F_WINDOWS         the full-pel windows searched (no reference counterpart; SAD-op accounting)
+   Outside motion_estimation.c the MeContext members (SEARCH_RESULTS, BEST) are read only by the temporal filter
+   (temporal_filtering.c:1860-2226, :2672: ME_MCTF); open-loop ME's caller (me_process.c:266-291) reads none of them, so
+   an open-loop consumer needs SB_RESULTS | STATS only.
+   svtme_picture_me_batch_packed runs the batch like svtme_picture_me_batch and lands the requested fields of all its
+   pictures in ONE caller-owned host slab with ONE device-to-host copy (pinned memory makes it asynchronous): picture i's
+   block starts at the sum of the block sizes of pictures 0..i-1 (svtme_packed_layout of each picture's params; every
+   block size is a multiple of 256 bytes) and holds the arrays at the offsets the layout gives, each array exactly as
+   SvtMePicResults documents it (the host's own strides: n_pus * max_refs, n_pus * max_cand). Fields that are not
+   requested are not written by the kernels at all. svtme_packed_view fills a SvtMePicResults with pointers into a block. */
+#define SVTME_F_SB_RESULTS 1u
+#define SVTME_F_STATS 2u
+#define SVTME_F_SEARCH_RESULTS 4u
+#define SVTME_F_BEST 8u
+#define SVTME_F_WINDOWS 16u
+#define SVTME_F_ALL 31u
+typedef struct SvtMePackedLayout {
+    size_t bytes;   /* size of one picture's block */
+    size_t off[15]; /* byte offset of each SvtMePicResults member, in member order; (size_t)-1 = not part of the block */
+} SvtMePackedLayout;
+uint32_t svtme_packed_layout(uint32_t width, uint32_t height, const SvtMePicParams *params, uint32_t fields,
+                             SvtMePackedLayout *out);
+void     svtme_packed_view(const SvtMePackedLayout *layout, void *block, SvtMePicResults *out);
+uint32_t svtme_picture_me_batch_packed(SvtMeSession *s, uint32_t n, const int32_t *pic_ids, const SvtMePicParams *params,
+                                       uint32_t fields, void *host_slab, size_t host_slab_bytes, int sync);
+/* Fields produced by calls that name no host arrays (svtme_picture_me_device, results == NULL): default SVTME_F_ALL. */
+uint32_t svtme_session_set_result_fields(SvtMeSession *s, uint32_t fields);
+/* Size the unit queues, result slabs and job arrays for batches of up to n_pictures pictures with these controls now,
+   instead of growing them (with a pipeline drain) when the first such batch arrives. */
+uint32_t svtme_session_reserve(SvtMeSession *s, const SvtMePicParams *params, uint32_t n_pictures);
+
+/* ---- device-resident view ---------------------------------------------------------------------
+   Later stages of the encoder re-read what already sits in HBM: global-motion pre-processing reads the three planes of a
+   picture and of its references (global_me.c:62-110, :309), the TPL dispenser reads the ME vectors and candidate lists
+   of pa_me_data (src_ops_process.c:205-299, :605-616). These two calls hand such a consumer DEVICE pointers instead of a
+   second upload / a round trip through the host.
+   svtme_picture_device_planes: the padded planes of an uploaded picture (level 0 full, 1 quarter, 2 sixteenth):
+   `origin` = interior sample (0,0), rows `stride` bytes apart, `pad` replicated samples on every side. Valid until pic_id
+   is uploaded again or the session is destroyed; work reading them must be ordered after the upload (the session's
+   stream, or after svtme_session_sync).
+   svtme_batch_results_acquire: device pointers (same arrays, same layout as SvtMePicResults; NULL = field not produced)
+   to the results of picture `index` of batch `seq`, and makes `consumer_stream` (a cudaStream_t) wait for the batch's
+   kernels. The session keeps two result sets: the arrays stay intact until batch seq + 2 is launched;
+   svtme_batch_results_release(seq, consumer_stream) makes that later batch wait for the work queued on consumer_stream
+   so far. SVTME_ERR_BAD_PARAMETER if the batch's set was already reused. */
+typedef struct SvtMeDevicePlane {
+    const uint8_t *origin;
+    uint32_t       stride, width, height, pad;
+} SvtMeDevicePlane;
+uint32_t svtme_picture_device_planes(SvtMeSession *s, int32_t pic_id, SvtMeDevicePlane planes[3]);
+uint32_t svtme_batch_results_acquire(SvtMeSession *s, uint64_t seq, uint32_t index, SvtMePicResults *device_ptrs,
+                                     void *consumer_stream);
+uint32_t svtme_batch_results_release(SvtMeSession *s, uint64_t seq, void *consumer_stream);
+/* Convenience for callers without the CUDA runtime (tests): synchronous copy of device memory to the host. */
+uint32_t svtme_copy_from_device(SvtMeSession *s, void *dst_host, const void *src_device, size_t bytes);
+
+/* Same, but results stay on the device (read them back with svtme_fetch_results, or in place through
+   svtme_batch_results_acquire). Used to time the kernels with inputs and outputs resident in HBM. */
 uint32_t svtme_picture_me_device(SvtMeSession *s, int32_t pic_id, const SvtMePicParams *params);
 
 /* Copy the device result arrays of the last svtme_picture_me_device call into `results`. */

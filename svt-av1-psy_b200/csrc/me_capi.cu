@@ -7,6 +7,8 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <algorithm>
+#include <deque>
 #include <mutex>
 #include <vector>
 
@@ -27,9 +29,43 @@
 
 static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
-struct ResultLayout { // offsets into the device result slab
-    size_t best_sad, best_mv, search_results, windows, total, mv, cand, d64, d32, d16, d8, rc, var, stat, gm, sb_state, ops, hme_jobs, fp_jobs, fp_keys, fp_counters, end;
+struct ResultLayout { // offsets into the per-picture device scratch slab (what crosses to the host lives in the download regions)
+    size_t dg_sad, dg_mv, sb_state, ops, hme_jobs, fp_jobs, fp_keys, fp_counters, end;
 };
+
+// SvtMePicResults members in declaration order, and the request group each belongs to
+enum { RF_BEST_SAD, RF_BEST_MV, RF_SEARCH, RF_WINDOWS, RF_TOTAL, RF_MV, RF_CAND, RF_D64, RF_D32, RF_D16, RF_D8, RF_RC, RF_VAR, RF_STAT, RF_GM, RF_COUNT };
+static const uint32_t rf_group[RF_COUNT] = {SVTME_F_BEST, SVTME_F_BEST, SVTME_F_SEARCH_RESULTS, SVTME_F_WINDOWS, SVTME_F_SB_RESULTS,
+                                            SVTME_F_SB_RESULTS, SVTME_F_SB_RESULTS, SVTME_F_STATS, SVTME_F_STATS, SVTME_F_STATS,
+                                            SVTME_F_STATS, SVTME_F_STATS, SVTME_F_STATS, SVTME_F_STATS, SVTME_F_STATS};
+// placement order inside a block: what every open-loop consumer wants first
+static const int rf_order[RF_COUNT] = {RF_TOTAL, RF_MV, RF_CAND, RF_D64, RF_D32, RF_D16, RF_D8, RF_RC, RF_VAR, RF_STAT, RF_GM, RF_SEARCH, RF_WINDOWS,
+                                       RF_BEST_SAD, RF_BEST_MV};
+static size_t rf_bytes(int f, size_t n_b64, size_t n_pus, size_t max_refs, size_t max_cand) {
+    switch (f) {
+    case RF_BEST_SAD: case RF_BEST_MV: return n_b64 * 8 * 85 * 4;
+    case RF_SEARCH: return n_b64 * 8 * sizeof(SvtMeSearchResult);
+    case RF_WINDOWS: return n_b64 * 8 * sizeof(SvtMeWindow);
+    case RF_TOTAL: return n_b64 * n_pus;
+    case RF_MV: return n_b64 * n_pus * max_refs * 4;
+    case RF_CAND: return n_b64 * n_pus * max_cand;
+    case RF_STAT: case RF_GM: return n_b64;
+    default: return n_b64 * 4;
+    }
+}
+static void packed_layout(size_t n_b64, size_t n_pus, size_t max_refs, size_t max_cand, uint32_t fields, SvtMePackedLayout *L) {
+    size_t o = 0;
+    for (int f = 0; f < RF_COUNT; f++) L->off[f] = (size_t)-1;
+    for (int k = 0; k < RF_COUNT; k++) {
+        const int f = rf_order[k];
+        if (!(fields & rf_group[f])) continue;
+        L->off[f] = o;
+        o = align_up(o + rf_bytes(f, n_b64, n_pus, max_refs, max_cand), 64);
+    }
+    L->bytes = align_up(o, 256);
+}
+static void **result_member(SvtMePicResults *r, int f) { return (void **)r + f; } // fifteen pointers, declaration order
+static_assert(sizeof(SvtMePicResults) == RF_COUNT * sizeof(void *), "SvtMePicResults is fifteen pointers");
 
 struct SvtMeSession {
     int          device = 0;
@@ -59,18 +95,37 @@ struct SvtMeSession {
     bool         dl_recorded[2] = {false, false};
     uint64_t     batch_seq = 0; // sequence number of the last launched batch (1-based)
     PicJob      *d_jobs = nullptr;
-    std::vector<PicJob> h_jobs;
-    std::vector<SvtMePicParams> last_pps;
+    // host copies of the job arrays: a ring of pinned arrays (the H2D copy of one is asynchronous; it is rewritten only
+    // after the event recorded behind that copy)
+    PicJob      *h_jobs_ring = nullptr;
+    cudaEvent_t  ev_jobs[4] = {};
+    bool         jobs_used[4] = {false, false, false, false};
+    uint64_t     jobs_head = 0;
     ResultLayout lay{};
-    uint8_t     *stage_slab = nullptr; // ring of staging frames for host uploads
-    cudaEvent_t  ev_copied[40] = {}, ev_ingested[40] = {};
-    bool         stage_used[40] = {};
-    uint64_t     stage_head = 0;
-    int          stage_last = 0;
+    // What a batch hands to the host: per result set one contiguous device region, the blocks of the batch's pictures
+    // back to back (svtme_packed_layout of each picture). BatchOut describes the batch that owns the set now.
+    struct BatchOut {
+        uint64_t seq = 0;
+        bool     me = false; // false: the set was last used by the detector
+        std::vector<SvtMePackedLayout> lay;
+        std::vector<size_t>            base;
+        size_t   total = 0;
+    } out[2];
+    uint8_t     *dl_region[2] = {nullptr, nullptr};
+    size_t       dl_cap[2] = {0, 0};
+    uint32_t     default_fields = SVTME_F_ALL;
+    uint32_t    *h_flags = nullptr; // pinned: [set] = the set's unit-queue overflow flag as of its last download
+    cudaEvent_t  ev_release[2] = {}; // device-resident consumers of a set (svtme_batch_results_release)
+    bool         release_recorded[2] = {false, false};
+    // host uploads go through a byte ring of staging memory: one allocation per upload call
+    struct StageAlloc { size_t begin, end; cudaEvent_t ev_ingested; };
+    uint8_t     *stage_slab = nullptr;
+    size_t       stage_cap = 0, stage_head = 0;
+    std::deque<StageAlloc>   stage_live;
+    std::vector<cudaEvent_t> stage_ev_pool;
+    cudaEvent_t  ev_copied = nullptr;
     uint2       *fp_units = nullptr, *s16_units = nullptr;
     uint32_t     fp_units_cap = 0, s16_units_cap = 0;
-    SvtMePicParams last_pp{};
-    bool         have_results = false;
     uint64_t     launches = 0;
     bool         timing = false;
     std::vector<cudaEvent_t> ev; // triples: before hme, after hme, after full-pel
@@ -118,16 +173,8 @@ static void plane_geom(int w, int h, int level, int *pw, int *ph, int *pad, int 
 static void result_layout(ResultLayout &L, int n_b64) {
     size_t o = 0;
     auto take = [&](size_t bytes) { size_t at = o; o = align_up(o + bytes, 256); return at; };
-    L.best_sad       = take((size_t)n_b64 * 8 * 85 * 4);
-    L.best_mv        = take((size_t)n_b64 * 8 * 85 * 4);
-    L.search_results = take((size_t)n_b64 * 8 * sizeof(SvtMeSearchResult));
-    L.windows        = take((size_t)n_b64 * 8 * sizeof(SvtMeWindow));
-    L.total          = take((size_t)n_b64 * 85);
-    L.mv             = take((size_t)n_b64 * 85 * 8 * 4);
-    L.cand           = take((size_t)n_b64 * 85 * 32);
-    L.d64 = take((size_t)n_b64 * 4); L.d32 = take((size_t)n_b64 * 4); L.d16 = take((size_t)n_b64 * 4);
-    L.d8  = take((size_t)n_b64 * 4); L.rc  = take((size_t)n_b64 * 4); L.var = take((size_t)n_b64 * 4);
-    L.stat = take((size_t)n_b64); L.gm = take((size_t)n_b64);
+    L.dg_sad   = take((size_t)n_b64 * 8); // dynamic-GOP detector: per-b64 SAD and vector
+    L.dg_mv    = take((size_t)n_b64 * 4);
     L.sb_state = take((size_t)n_b64 * sizeof(SbState));
     L.ops = take(64);
     L.hme_jobs    = take((size_t)n_b64 * HME_JOBS_PER_B64 * sizeof(HmeJobG));

@@ -187,6 +187,11 @@ static SvtMeSearchAreaMinMax samm_of(SearchAreaMinMax a) {
    temporal_filtering.c:3112-3140) and from the PCS. Members of a disabled feature are left 0: the reference leaves them
    unset, and they are never read. */
 void svtme_shim_flatten(const PictureParentControlSet *pcs, const MeContext *m, SvtMePicParams *o) {
+    /* --rmv 1 clamps the full-pel window to the b64's tile instead of the padded picture (motion_estimation.c:1445-1470,
+       :1507-1533). The library has no tile geometry and would search other windows than the reference: refuse, like every
+       other mode it does not implement. */
+    if (pcs->scs->static_config.restricted_motion_vector)
+        shim_fatal("restricted_motion_vector (--rmv 1: tile-restricted search windows are not implemented)", 1);
     memset(o, 0, sizeof(*o));
     SvtMeCtrls *c = &o->ctrls;
     c->enable_hme_flag        = m->enable_hme_flag;
