@@ -23,7 +23,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-INT_PEAK_LANE_INSTR_PER_CLK_SM = 64.0  # VABSDIFF4.U8.ACC issues at the integer-ALU pipe rate (57 VABS + 7 IADD measured, profiles/r01_vabs_peak_microbench.txt)
+INT_PEAK_LANE_INSTR_PER_CLK_SM = 64.0  # VABSDIFF4.U8.ACC is an ALU-pipe instruction: 64 lane-instr/clk/SM, shared with SHF/LOP3/VIMNMX (profiles/r02_int_peak.md)
 N_SM = 148
 
 
@@ -46,6 +46,7 @@ def parse_args():
     ap.add_argument("--qp", type=int, default=35)
     ap.add_argument("--cpu-baseline-s", type=float, default=12.0, help="wall-time budget of the bounded CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extra-configs", action="store_true", help="skip the short runs of the other BASELINE.json configurations")
     return ap.parse_args()
 
 
@@ -138,11 +139,18 @@ class ClockSampler:
 # ------------------------------------------------------------------------------------------------
 # our arm
 # ------------------------------------------------------------------------------------------------
+class StepPlan:
+    """Everything one step hands to the C ABI, marshalled ahead of the timed region: picture ids, parameter array, the
+    upload lists (host pointers of this step's new frames). An encoder's host code is C and keeps these arrays; building
+    them in Python inside the timed loop would time the harness, not the library."""
+    __slots__ = ("n", "ids", "prm", "uploads", "h2d")
+
+
 class Runner:
     """Drives one Session through consecutive mini-GOPs of a stream (this rank's shard)."""
     N_SLOTS = 192  # picture store: slot = poc % N_SLOTS; references reach at most 4 mini-GOPs back
 
-    def __init__(self, wl, rank, world, frames_host, device):
+    def __init__(self, wl, rank, world, frames_host, device, fields):
         import torch
         import svtme_b200 as me
         from svt_av1_psy_b200 import abi
@@ -156,13 +164,14 @@ class Runner:
             rng = np.random.default_rng(99 + rank)
             f16 = (frames_host.astype(np.uint16) << 2) | rng.integers(0, 4, frames_host.shape, dtype=np.uint16)
             self.frames16 = torch.from_numpy(f16.view(np.int16)).pin_memory()
-        self.resident = {}  # slot -> poc whose planes are in the store
+        self.resident = {}  # slot -> poc whose planes are in the store (as of the last PLANNED step)
         self.params_cache = {}
-        self.results = None
+        self.fields = fields
+        self.sess.set_result_fields(fields)  # what the kernels produce when results stay in HBM: the same arrays
+        self.slabs = None
         self.h2d = self.d2h = 0
         self.pics = 0
         self.host_batches = 0
-        self.pending = {}
         self.probe = "full"
 
     def params(self, plan):
@@ -193,84 +202,95 @@ class Runner:
                 p.ref_pic_id[l][r] = rp % self.N_SLOTS
         return p
 
-    def ensure(self, poc, host):
-        """queue the upload of picture `poc` unless its slot already holds it (flushed by one batched call per step)"""
-        slot = poc % self.N_SLOTS
-        if self.resident.get(slot) == poc:
-            return
-        f = poc % self.wl.n_frames
-        if host and self.probe == "d2h":
-            kind, ptr = "device", self.frames_dev[f].data_ptr()
-        elif host and self.frames16 is not None:
-            kind, ptr = "host10", self.frames16[f].data_ptr()
-            self.h2d += 2 * self.wl.w * self.wl.h
-        elif host:
-            kind, ptr = "host8", self.frames_pinned[f].data_ptr()
-            self.h2d += self.wl.w * self.wl.h
-        else:
-            kind, ptr = "device", self.frames_dev[f].data_ptr()
-        self.pending.setdefault(kind, ([], []))
-        self.pending[kind][0].append(slot)
-        self.pending[kind][1].append(ptr)
-        self.resident[slot] = poc
-
-    def flush_uploads(self):
-        for kind, (ids, ptrs) in self.pending.items():
-            for i in range(0, len(ids), 32):
-                self.sess.upload_batch(ids[i:i + 32], ptrs[i:i + 32], self.wl.w, kind)
-        self.pending = {}
-
-    def step(self, step_index, host):
-        """ME of the mini-GOP this rank owns at `step_index` (mini-GOP m = step*world + rank): upload its
-        pictures (and any missing reference), then ONE batched launch sequence for the whole mini-GOP."""
+    def plan_step(self, step_index, host):
+        """mini-GOP m = step*world + rank: its pictures (coding order), the frames the picture store does not hold yet"""
         wl = self.wl
         m = step_index * self.world + self.rank
         first = m * wl.mgop
-        self.ensure(first, host)  # the base/key picture that precedes the mini-GOP
+        pending = {}
+        sp = StepPlan()
+        sp.h2d = 0
+
+        def ensure(poc):
+            slot = poc % self.N_SLOTS
+            if self.resident.get(slot) == poc:
+                return
+            f = poc % wl.n_frames
+            if host and self.probe == "d2h":
+                kind, ptr = "device", self.frames_dev[f].data_ptr()
+            elif host and self.frames16 is not None:
+                kind, ptr = "host10", self.frames16[f].data_ptr()
+                sp.h2d += 2 * wl.w * wl.h
+            elif host:
+                kind, ptr = "host8", self.frames_pinned[f].data_ptr()
+                sp.h2d += wl.w * wl.h
+            else:
+                kind, ptr = "device", self.frames_dev[f].data_ptr()
+            pending.setdefault(kind, ([], []))
+            pending[kind][0].append(slot)
+            pending[kind][1].append(ptr)
+            self.resident[slot] = poc
+
+        ensure(first)  # the base/key picture that precedes the mini-GOP
         ids, prms = [], []
         for poc in wl.order(first):
             plan = wl.plan(poc)
             for p in plan["l0"] + plan["l1"]:
-                self.ensure(p, host)
-            self.ensure(poc, host)
+                ensure(p)
+            ensure(poc)
             prm = self.params_cache.get(poc)
             if prm is None:
                 prm = self.params_cache[poc] = self.params(plan)
-            ids.append(slot_of(poc, self))
+            ids.append(poc % self.N_SLOTS)
             prms.append(prm)
-        self.flush_uploads()
-        if host:
-            if self.results is None:
-                # two sets of pinned result arrays: batch k's downloads overlap batch k+1's uploads and kernels
-                self.results = [[], []]
-                for hs in self.results:
-                    for _ in range(wl.mgop):
-                        r = self.abi.PicResultArrays(wl.w, wl.h, prms[0], pinned=True)
-                        for name in ("p_sb_best_sad", "p_sb_best_mv", "search_results", "me_windows"):
-                            setattr(r.struct, name, None)  # MeContext mirrors: debug only, not consumed downstream
-                        hs.append(r)
-                r0 = self.results[0][0]
-                self.d2h_per_pic = sum(getattr(r0, f).nbytes for f in r0.FIELDS
-                                       if f not in ("p_sb_best_sad", "p_sb_best_mv", "search_results", "me_windows"))
-                self.seqs = [0, 0]
+        sp.n = len(ids)
+        sp.ids = (C.c_int32 * sp.n)(*ids)
+        sp.prm = (self.abi.MePicParams * sp.n)(*prms)
+        sp.uploads = []
+        for kind, (slots, ptrs) in pending.items():
+            for i in range(0, len(slots), 32):
+                k = len(slots[i:i + 32])
+                sp.uploads.append((kind, k, (C.c_int32 * k)(*slots[i:i + 32]), (C.c_void_p * k)(*ptrs[i:i + 32])))
+        return sp
+
+    def setup_slabs(self, sp):
+        """two pinned result slabs used by alternate batches: batch k's download overlaps batch k+1's uploads and kernels"""
+        import torch
+        lay = self.sess.packed_layout(sp.prm[0], self.fields)
+        self.slab_bytes = lay.bytes * self.wl.mgop
+        self.slabs = [torch.zeros(self.slab_bytes, dtype=torch.uint8).pin_memory() for _ in range(2)]
+        self.block_bytes = lay.bytes
+        self.seqs = [0, 0]
+        self.sess.reserve(sp.prm[0], self.wl.mgop)
+
+    def run_step(self, sp, host):
+        """the C calls of one step: batched uploads, ONE launch sequence, (host) ONE download of the whole batch"""
+        L = self.me.lib()
+        h = self.sess._h
+        for kind, k, slots, ptrs in sp.uploads:
+            fn = L.svtme_picture_upload_batch if kind == "host8" else (L.svtme_picture_upload_10bit_batch if kind == "host10" else L.svtme_picture_upload_device_batch)
+            rc = fn(h, k, slots, ptrs, self.wl.w)
+            if rc:
+                raise RuntimeError("upload failed 0x%x" % rc)
+        self.h2d += sp.h2d
+        if host and self.probe != "h2d":
             k = self.host_batches & 1
-            if self.probe == "h2d":
-                self.sess.me_batch(ids, prms, None, sync=False)
-                self.pics += len(ids)
-                return
-            self.sess.wait_batch(self.seqs[k])  # this set's previous results are in host memory (and consumed) before reuse
-            self.sess.me_batch(ids, prms, self.results[k][:len(ids)], sync=False)
+            self.sess.wait_batch(self.seqs[k])  # this slab's previous results are in host memory (and consumed) before reuse
+            self.sess.me_batch_packed(sp.ids, sp.prm, sp.n, self.fields, self.slabs[k].data_ptr(), self.slab_bytes)
             self.seqs[k] = self.sess.batch_seq()
             self.host_batches += 1
-            self.d2h += self.d2h_per_pic * len(ids)
+            self.d2h += self.block_bytes * sp.n
         else:
-            self.sess.me_batch(ids, prms, None, sync=False)
-        self.pics += len(ids)
-        self.batches = getattr(self, "batches", 0) + 1
+            rc = L.svtme_picture_me_batch(h, sp.n, sp.ids, sp.prm, None, 0)
+            if rc:
+                raise RuntimeError("svtme_picture_me_batch failed 0x%x" % rc)
+        self.pics += sp.n
 
-
-def slot_of(poc, runner):
-    return poc % runner.N_SLOTS
+    def step(self, step_index, host):
+        sp = self.plan_step(step_index, host)
+        if host and self.slabs is None:
+            self.setup_slabs(sp)
+        self.run_step(sp, host)
 
 
 def _cpulist(text):
@@ -309,6 +329,94 @@ def bind_to_gpu_numa_node(torch, dev):
     return info
 
 
+def read_peaks():
+    try:
+        return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except OSError:
+        return {}
+
+
+def measure(wl, frames, rank, world, local, a, steps, warmup, sampler, detail):
+    """resident pass + per-kernel timing pass + end-to-end pass(es) of one workload -> dict (valid on every rank; the
+    times are the max over ranks). detail: also the temporal-filter ME and detector lines (the headline workload)."""
+    import torch
+    import torch.distributed as dist
+    from svt_av1_psy_b200 import abi
+    consumer = abi.F_SB_RESULTS | abi.F_STATS  # what open-loop ME's consumers read (include/svtme_b200.h, DESIGN.md section 5)
+    run = Runner(wl, rank, world, frames, local, consumer)
+    run.probe = a.e2e_probe
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+
+    def timed(host, first_step, n_steps, smp=None):
+        plans = [run.plan_step(s, host) for s in range(first_step, first_step + n_steps)]  # marshalled outside the timed region
+        if host and run.slabs is None:
+            run.setup_slabs(plans[0])
+        barrier()
+        run.pics = run.h2d = run.d2h = 0
+        l0 = run.sess.launch_count()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0 = time.time()
+        e0.record()
+        for sp in plans:
+            run.run_step(sp, host)
+        run.host_ms = (time.time() - t0) * 1e3 / n_steps  # host time to queue one step (no waiting unless the pipeline is full)
+        run.sess.sync()  # every stream of the session: uploads, kernels (two compute streams) and downloads are done
+        e1.record()
+        barrier()
+        if smp:
+            smp.window(t0, time.time())
+        ms = e0.elapsed_time(e1)
+        if world > 1:
+            t = torch.tensor([ms], device="cuda", dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms, run.pics, run.sess.launch_count() - l0
+
+    # ---- device-resident pass: raw frames already in HBM, results stay in HBM ----
+    for s in range(warmup):
+        run.step(s, host=False)
+    run.sess.set_concurrency(a.concurrency)  # 2: consecutive mini-GOPs on two compute streams
+    ms, pics, launches = timed(False, warmup, steps, sampler)
+    out = {"value": world * pics / (ms * 1e-3), "ms_per_step": ms / steps, "launches": launches, "host_queue_ms": run.host_ms, "pics": pics, "ms": ms}
+    # per-kernel times and the |a-b| operation count for the roofline: a short pass with CUDA events behind every launch
+    # (the session then keeps its batches on one stream, so the kernels of different mini-GOPs do not overlap)
+    run.sess.enable_timing(True)
+    run.sess.kernel_time(reset=True)
+    run.sess.kernel_times(reset=True)
+    run.sess.sad_ops_by_stage(reset=True)
+    t_steps = min(steps, 12)
+    _, n_timed, _ = timed(False, warmup + steps, t_steps)
+    fp_ms, hme_ms, _ = run.sess.kernel_time(reset=True)
+    out["kernel_ms"] = run.sess.kernel_times(reset=True)
+    out["ops"] = run.sess.sad_ops_by_stage(reset=True)
+    out["n_timed"], out["hme_ms"], out["fp_ms"] = n_timed, hme_ms, fp_ms
+    run.sess.enable_timing(False)
+
+    # ---- end-to-end pass: pinned host frames in, the consumers' result arrays out, every step ----
+    def e2e_pass(fields, base):
+        run.resident.clear()
+        run.fields, run.slabs = fields, None
+        run.sess.set_result_fields(fields)
+        for s in range(base, base + min(warmup, 2)):
+            run.step(s, host=True)
+        base += min(warmup, 2)
+        ms_e, pics_e, _ = timed(True, base, steps, sampler)
+        return {"value": world * pics_e / (ms_e * 1e-3), "unit": "frames/s", "h2d_bytes_per_step": int(run.h2d // max(1, steps)),
+                "d2h_bytes_per_step": int(run.d2h // max(1, steps)), "ms_per_step": ms_e / steps, "host_queue_ms_per_step": run.host_ms}, base + steps
+
+    base = warmup + steps + t_steps
+    out["e2e"], base = e2e_pass(consumer, base)
+    if detail:  # the same with the MeContext members (p_sb_best_sad / p_sb_best_mv, search_results) crossing PCIe too
+        out["e2e_all"], base = e2e_pass(consumer | abi.F_BEST | abi.F_SEARCH_RESULTS, base)
+        run.sess.set_result_fields(consumer)
+    out["run"] = run
+    return out
+
+
 def run_ours(a):
     import torch
     import torch.distributed as dist
@@ -323,67 +431,14 @@ def run_ours(a):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     wl = Workload(a)
     frames = make_clip(wl, rank)
-    run = Runner(wl, rank, world, frames, local)
-    run.probe = a.e2e_probe
-
-    def barrier():
-        torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
-
-    def timed(host, first_step, n_steps, sampler=None):
-        barrier()
-        run.pics = run.h2d = run.d2h = 0
-        l0 = run.sess.launch_count()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        t0 = time.time()
-        e0.record()
-        for s in range(first_step, first_step + n_steps):
-            run.step(s, host)
-        run.host_ms = (time.time() - t0) * 1e3 / n_steps  # host time to queue one step (no waiting unless the pipeline is full)
-        run.sess.sync()  # every stream of the session: uploads, kernels (two compute streams) and downloads are done
-        e1.record()
-        barrier()
-        if sampler:
-            sampler.window(t0, time.time())
-        ms = e0.elapsed_time(e1)
-        if world > 1:
-            t = torch.tensor([ms], device="cuda", dtype=torch.float64)
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            ms = float(t.item())
-        return ms, run.pics, run.sess.launch_count() - l0
-
     sampler = ClockSampler(local)
     sampler.start()
-    # ---- device-resident pass: raw frames already in HBM, results stay in HBM ----
-    for s in range(a.warmup):
-        run.step(s, host=False)
-    run.sess.set_concurrency(a.concurrency)  # 2: consecutive mini-GOPs on two compute streams
-    ms, pics, launches = timed(False, a.warmup, a.steps, sampler)
-    host_ms_resident = run.host_ms
-    value = world * pics / (ms * 1e-3)
-    # stage times and the |a-b| operation count for the roofline: a short pass with the per-stage CUDA events on (the
-    # session then keeps its batches on one stream, so the stages of different mini-GOPs do not overlap)
-    run.sess.enable_timing(True)
-    run.sess.kernel_time(reset=True)
-    run.sess.sad_ops(reset=True)
-    t_steps = min(a.steps, 12)
-    _, n_timed, _ = timed(False, a.warmup + a.steps, t_steps)
-    fp_ms, hme_ms, _ = run.sess.kernel_time(reset=True)
-    hme_ops, fp_ops = run.sess.sad_ops(reset=True)
-    run.sess.enable_timing(False)
-
-    # ---- end-to-end pass: pinned host frames in, MeSbResults + statistics out, every step ----
-    run.resident.clear()
-    base = a.warmup + a.steps + t_steps
-    for s in range(base, base + min(a.warmup, 2)):
-        run.step(s, host=True)
-    base += min(a.warmup, 2)
-    ms_e, pics_e, _ = timed(True, base, a.steps, sampler)
-    host_ms_e2e = run.host_ms
+    m = measure(wl, frames, rank, world, local, a, a.steps, a.warmup, sampler, detail=True)
     clocks = sampler.stop()
-    h2d_step, d2h_step = run.h2d // max(1, a.steps), run.d2h // max(1, a.steps)
-    e2e = world * pics_e / (ms_e * 1e-3)
+    run = m["run"]
+    value, e2e = m["value"], m["e2e"]
+    n_timed, hme_ms, fp_ms, ops = m["n_timed"], m["hme_ms"], m["fp_ms"], m["ops"]
+    hme_ops, fp_ops = ops[0], ops[1]
 
     # ---- dynamic-GOP detector HME: pairs of resident pictures, metrics back to the host each call ----
     dg_pairs = 64
@@ -400,7 +455,7 @@ def run_ours(a):
     dg_ms = d0.elapsed_time(d1) / dg_pairs
 
     # ---- temporal-filter ME: (centre, neighbour) pairs of resident pictures, batches of 32 ----
-    from svt_av1_psy_b200 import binding as _b
+    from svt_av1_psy_b200 import abi, binding as _b
     tf_level, tf_batches = 1, 6
     tf_ids = [slots[i % len(slots)] for i in range(32)]
     tf_prms = []
@@ -408,6 +463,7 @@ def run_ours(a):
         p = _b.sig_deriv_me_tf(wl.preset, wl.w, wl.h, tf_level, qp_opt=1, me_exit_th=0, qp=wl.qp, centre_poc=100 + i, ref_poc=99 + i)
         p.ref_pic_id[0][0] = slots[(i + 1) % len(slots)]
         tf_prms.append(p)
+    run.sess.set_result_fields(abi.F_BEST | abi.F_SEARCH_RESULTS)  # what the temporal filter reads (temporal_filtering.c:1860-2226, :2672)
     run.sess.me_batch(tf_ids, tf_prms, None, sync=True)
     run.sess.sad_ops(reset=True)
     t0e, t1e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -419,62 +475,74 @@ def run_ours(a):
     torch.cuda.synchronize()
     tf_ms = t0e.elapsed_time(t1e) / (tf_batches * 32)
     tf_ops = sum(run.sess.sad_ops(reset=True)) / (tf_batches * 32)
+    del run, m["run"]
+
+    # ---- the other BASELINE.json configurations (each a short run of its own; see extra_configs) ----
+    extra = extra_configs(a, rank, world, local) if not a.no_extra_configs else {}
 
     if rank == 0:
-        peaks = {}
-        try:
-            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-        except OSError:
-            pass
+        peaks = read_peaks()
         hbm_peak = peaks.get("hbm_gbs", 6650.0)
         n_refs = wl.mrp["l0"] + wl.mrp["l1"]
-        dominant, dom_ms, dom_ops = ("k_fullpel", fp_ms, fp_ops) if fp_ms >= hme_ms else ("k_hme", hme_ms, hme_ops)
-        # the two timed groups of the launch sequence (CUDA events around each, on the session's compute stream)
-        KERNELS = {"k_hme": "HME stage = k_search16 (pre-HME, level 0) + k_search_blk (levels 1, 2) + k_hme_ctl before/between/after them; "
-                            "k_search16 is ~55 % of it (profiles/r01_final_summary.md)",
-                   "k_fullpel": "full-pel stage = k_fp + k_fp_big (k_post follows, outside both timed stages)"}
-        # algorithmic bytes of one launch (one picture): every plane of the source and of each reference read once
-        # (1 + 1/4 + 1/16 of WxH each) + the per-b64 results the launch writes
-        plane = 1.3125 * wl.w * wl.h if dominant == "k_hme" else 1.0 * wl.w * wl.h
         n_b64 = ((wl.w + 63) // 64) * ((wl.h + 63) // 64)
-        out_b = n_b64 * (1512 if dominant == "k_hme" else 8 * 85 * 8)
-        alg_bytes = (1 + n_refs) * plane + out_b
-        avg_s = dom_ms * 1e-3 / max(1, n_timed)
-        # dram__bytes_read.sum + dram__bytes_write.sum of the HME-stage kernels, per picture, from the ncu --set full
-        # capture of this workload (profiles/r01_final_summary.md: 355 MB per mini-GOP of 32 pictures); null for other workloads
-        traffic = round(355.4e6 / 32) if (dominant == "k_hme" and (wl.w, wl.h, wl.preset, wl.bits) == (1920, 1080, 4, 8)) else None
         sm_mhz = clocks.get("sm_mhz") or peaks.get("sm_max_mhz", 1965.0)
         int_peak = INT_PEAK_LANE_INSTR_PER_CLK_SM * 4 * N_SM * sm_mhz * 1e6  # |a-b| ops/s at the sampled clock
+        # the dominant KERNEL of the sequence by its own CUDA-event time, and the |a-b| operations it executed
+        kms = m["kernel_ms"]
+        kernel_ops = {"k_search16 (pre-HME)": ops[2], "k_search16 (HME level 0)": ops[3], "k_search_blk (HME level 1)": ops[4],
+                      "k_search_blk (HME level 2)": ops[5], "k_fp": fp_ops, "k_fp_big": 0}
+        dom = max(kms, key=lambda k: kms[k]) if kms else None
+        dom_ms = kms.get(dom, 0.0)
+        dom_ops = kernel_ops.get(dom, 0)
+        if dom in ("k_fp", "k_fp_big"):  # one search split over two kernels: their times together
+            dom, dom_ms = "k_fp + k_fp_big", kms.get("k_fp", 0) + kms.get("k_fp_big", 0)
+        n_launch = max(1, n_timed // wl.mgop)  # launches of the dominant kernel in the timed pass = mini-GOPs
+        # algorithmic bytes of one launch of that kernel (one mini-GOP): the planes it reads, once each, + what it writes
+        lvl = {"k_search16 (pre-HME)": 1 / 16, "k_search16 (HME level 0)": 1 / 16, "k_search_blk (HME level 1)": 1 / 4}.get(dom, 1.0)
+        alg_bytes = wl.mgop * ((1 + n_refs) * lvl * wl.w * wl.h + n_b64 * 8 * 4 * 40)  # + the job records (keys) of a launch
+        avg_s = dom_ms * 1e-3 / max(1, n_launch)
+        traffic = ncu_traffic(dom, wl)
         line = {
             "metric": "open-loop ME frames/s", "value": round(value, 2), "unit": "frames/s", "n_gpus": world,
-            "steps": a.steps, "warmup": a.warmup, "ms_per_step": round(ms / a.steps, 4), "higher_is_better": True,
+            "steps": a.steps, "warmup": a.warmup, "ms_per_step": round(m["ms_per_step"], 4), "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
             "config": {"workload": wl.name, "pictures_per_step": wl.mgop, "batch": "one launch sequence per mini-GOP (svtme_picture_me_batch), consecutive mini-GOPs on %d compute stream(s)" % a.concurrency, "sharding": "mini-GOP m -> rank m % N",
-                       "e2e_pipeline": "host uploads, kernels and result downloads on three streams; two batches in flight, every step's results land in pinned host memory inside the timed region",
+                       "results": "the arrays open-loop ME's consumers read: MeSbResults (total_me_candidate_index, me_mv_array, me_candidate_array) + the eight per-b64 PCS statistics; "
+                                  "e2e_all_fields adds the MeContext members (p_sb_best_sad / p_sb_best_mv, search_results), which only the temporal filter reads after the call",
+                       "e2e_pipeline": "host uploads, kernels and result downloads on three streams; two batches in flight; per step the new frames cross as merged H2D copies and the whole batch's results land in pinned host memory by ONE D2H copy (svtme_picture_me_batch_packed), inside the timed region",
                        "host_numa": numa,
                        "l2": "inputs larger than L2: %d distinct %dx%d frames (%.0f MB) stream through the picture store, no explicit flush"
                              % (wl.n_frames, wl.w, wl.h, wl.n_frames * wl.w * wl.h / 1e6)},
-            "e2e": {"value": round(e2e, 2), "unit": "frames/s", "h2d_bytes_per_step": int(h2d_step), "d2h_bytes_per_step": int(d2h_step),
-                    "ms_per_step": round(ms_e / a.steps, 4), "host_queue_ms_per_step": round(host_ms_e2e, 3)},
-            "host_queue_ms_per_step": round(host_ms_resident, 3),
-            "gpu_launches": int(launches),
+            "e2e": {k: (round(v, 3) if isinstance(v, float) else v) for k, v in e2e.items()},
+            "e2e_all_fields": {k: (round(v, 3) if isinstance(v, float) else v) for k, v in m["e2e_all"].items()},
+            "host_queue_ms_per_step": round(m["host_queue_ms"], 3),
+            "gpu_launches": int(m["launches"]),
             "clocks": clocks,
-            "roofline": {"bound": "hbm", "kernel": KERNELS[dominant], "achieved": round(alg_bytes / avg_s / 1e9, 2), "peak": hbm_peak,
-                         "unit": "GB/s", "frac": round(alg_bytes / avg_s / 1e9 / hbm_peak, 5), "traffic": traffic,
+            "roofline": {"bound": "hbm", "kernel": dom, "achieved": round(alg_bytes / avg_s / 1e9, 2) if avg_s else None, "peak": hbm_peak,
+                         "unit": "GB/s", "frac": round(alg_bytes / avg_s / 1e9 / hbm_peak, 5) if avg_s else None, "traffic": traffic,
+                         "avg_launch_ms": round(avg_s * 1e3, 4), "launch": "one mini-GOP of %d pictures" % wl.mgop,
                          "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback",
                          "note": "integer-ALU bound kernel (byte SAD); see roofline_int"},
-            "roofline_int": {"bound": "int_alu(VABSDIFF4.U8.ACC)", "kernel": KERNELS[dominant],
+            "roofline_int": {"bound": "int_alu(VABSDIFF4.U8.ACC)", "kernel": dom,
                              "achieved": round(dom_ops / (dom_ms * 1e-3) / 1e12, 3) if dom_ms else None,
                              "peak": round(int_peak / 1e12, 2), "unit": "T |a-b| ops/s",
                              "frac": round(dom_ops / (dom_ms * 1e-3) / int_peak, 4) if dom_ms else None,
-                             "peak_def": "64 lane-instr/clk/SM (ALU pipe, measured 57 VABS + 7 IADD) x 4 px x 148 SM x sampled SM clock"},
+                             "peak_def": "64 lane-instr/clk/SM on the ALU pipe (profiles/r02_int_peak.md: VABSDIFF4, SHF, LOP3, VIMNMX share it; ncu pipe counts) x 4 px x 148 SM x sampled SM clock",
+                             "stage_frac": {"hme_stage": round(hme_ops / (hme_ms * 1e-3) / int_peak, 4) if hme_ms else None,
+                                            "fullpel_stage": round(fp_ops / (fp_ms * 1e-3) / int_peak, 4) if fp_ms else None,
+                                            "whole_step": round((hme_ops + fp_ops) / max(1, n_timed) * m["pics"] / (m["ms"] * 1e-3) / int_peak, 4)}},
+            "kernel_ms_per_picture": {k: round(v / max(1, n_timed), 5) for k, v in kms.items()},
+            "kernel_frac_of_int_peak": dict(
+                [(k, round(kernel_ops[k] / (kms[k] * 1e-3) / int_peak, 4)) for k in kms if k not in ("k_fp", "k_fp_big") and kernel_ops.get(k) and kms[k]] +
+                [("k_fp + k_fp_big", round(fp_ops / ((kms.get("k_fp", 0) + kms.get("k_fp_big", 0)) * 1e-3) / int_peak, 4))] if kms.get("k_fp") else []),
             "stage_ms_per_picture": {"hme_stage": round(hme_ms / max(1, n_timed), 4), "fullpel_stage": round(fp_ms / max(1, n_timed), 4)},
-            "sad_gops": round((hme_ops + fp_ops) / max(1, n_timed) * pics / (ms * 1e-3) / 1e9, 1),
+            "sad_gops": round((hme_ops + fp_ops) / max(1, n_timed) * m["pics"] / (m["ms"] * 1e-3) / 1e9, 1),
             "tf_me": {"metric": "temporal-filter ME (ME_MCTF, tf hme_me_level %d, FULL_SAD) picture pairs/s, resident" % tf_level,
                       "value": round(1e3 / tf_ms, 1), "ms_per_pair": round(tf_ms, 4), "sad_gops": round(tf_ops / (tf_ms * 1e-3) / 1e9, 1)},
             "dg_detector": {"metric": "dynamic-GOP detector HME picture pairs/s (svtme_dg_detector_hme, synchronous, metrics to host)",
                             "value": round(1e3 / dg_ms, 1), "ms_per_pair": round(dg_ms, 4),
                             "sad_gops_nominal_window": round(n_b64 * 128 * 128 * 256 / (dg_ms * 1e-3) / 1e9, 1) if wl.w * wl.h >= 0xA1400 else None},
+            "configs": extra,
         }
         if not a.no_cpu_baseline and world == 1:
             line["cpu_baseline"] = cpu_baseline(wl, frames, a.cpu_baseline_s)
@@ -482,6 +550,132 @@ def run_ours(a):
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+
+
+def ncu_traffic(kernel, wl):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel` from the committed ncu --set full capture of this
+    workload (profiles/r02_ncu_full_1080p_m4.json, written by tools/ncu_summary.py from the .ncu-rep); None when there is
+    no capture for the workload or the kernel."""
+    if (wl.w, wl.h, wl.preset, wl.bits) != (1920, 1080, 4, 8) or not kernel:
+        return None
+    try:
+        cap = json.load(open(os.path.join(ROOT, "profiles", "r02_ncu_full_1080p_m4.json")))
+    except (OSError, ValueError):
+        return None
+    names = [kernel] if kernel != "k_fp + k_fp_big" else ["k_fp", "k_fp_big"]
+    tot = 0
+    for n in names:
+        if n not in cap.get("kernels", {}):
+            return None
+        tot += cap["kernels"][n]["dram_bytes"]
+    return int(tot)
+
+
+def extra_configs(a, rank, world, local):
+    """BASELINE.json configs[2..4] as short runs inside the same bench invocation (the driver only ever runs bench.py
+    --gpus N): 3840x2160 10-bit preset 4 at every N; at N = 1 also 7680x4320 preset 2 and 1920x1080 preset -2; and the
+    16 concurrent 1080p streams of configs[4], 16 / N per rank, one session each. Shorter clips than the headline run
+    (still larger than L2); per-config values are whole-job aggregates like the headline."""
+    import copy
+    import torch
+    out = {}
+    peaks = read_peaks()
+
+    def one(name, w, h, bits, preset, frames_n, steps, warmup):
+        b = copy.copy(a)
+        b.width, b.height, b.bits, b.preset, b.frames = w, h, bits, preset, frames_n
+        wl = Workload(b)
+        frames = make_clip(wl, rank)
+        smp = ClockSampler(local)
+        smp.start()
+        m = measure(wl, frames, rank, world, local, b, steps, warmup, smp, detail=False)
+        clocks = smp.stop()
+        del m["run"]
+        torch.cuda.empty_cache()
+        sm_mhz = clocks.get("sm_mhz") or peaks.get("sm_max_mhz", 1965.0)
+        int_peak = INT_PEAK_LANE_INSTR_PER_CLK_SM * 4 * N_SM * sm_mhz * 1e6
+        ops, n_timed = m["ops"], max(1, m["n_timed"])
+        out[name] = {
+            "workload": wl.name, "value": round(m["value"], 2), "unit": "frames/s", "steps": steps, "warmup": warmup,
+            "pictures_per_step": wl.mgop, "ms_per_step": round(m["ms_per_step"], 4),
+            "e2e": {k: (round(v, 3) if isinstance(v, float) else v) for k, v in m["e2e"].items()},
+            "roofline_int": {"whole_step_frac": round((ops[0] + ops[1]) / n_timed * m["pics"] / (m["ms"] * 1e-3) / int_peak, 4),
+                             "hme_stage_frac": round(ops[0] / (m["hme_ms"] * 1e-3) / int_peak, 4) if m["hme_ms"] else None,
+                             "fullpel_stage_frac": round(ops[1] / (m["fp_ms"] * 1e-3) / int_peak, 4) if m["fp_ms"] else None,
+                             "peak": round(int_peak / 1e12, 2), "unit": "T |a-b| ops/s"},
+            "sad_gops": round((ops[0] + ops[1]) / n_timed * m["pics"] / (m["ms"] * 1e-3) / 1e9, 1),
+            "stage_ms_per_picture": {"hme_stage": round(m["hme_ms"] / n_timed, 4), "fullpel_stage": round(m["fp_ms"] / n_timed, 4)},
+            "kernel_ms_per_picture": {k: round(v / n_timed, 5) for k, v in m["kernel_ms"].items()},
+            "clocks": clocks,
+        }
+
+    one("3840x2160 10-bit preset 4", 3840, 2160, 10, 4, 96, 6, 3)
+    if world == 1:
+        one("7680x4320 8-bit preset 2", 7680, 4320, 8, 2, 48, 3, 3)
+        one("1920x1080 8-bit preset -2", 1920, 1080, 8, -2, 96, 3, 3)
+    if 16 % world == 0:
+        out["16 concurrent 1920x1080 streams"] = streams16(a, rank, world, local)
+    return out
+
+
+def streams16(a, rank, world, local):
+    """configs[4]: 16 concurrent 1080p preset-4 streams over N GPUs, 16 / N sessions per rank, mini-GOPs of the streams
+    submitted round-robin (each session has its own three CUDA streams: the streams overlap on the GPU)."""
+    import copy
+    import torch
+    import torch.distributed as dist
+    from svt_av1_psy_b200 import abi
+    per_rank = 16 // world
+    b = copy.copy(a)
+    b.width, b.height, b.bits, b.preset, b.frames = 1920, 1080, 8, 4, 64
+    wl = Workload(b)
+    fields = abi.F_SB_RESULTS | abi.F_STATS
+    runs = [Runner(wl, 0, 1, make_clip(wl, 100 + rank * per_rank + k), local, fields) for k in range(per_rank)]
+    steps, warmup = 3, 3
+    res = {}
+    smp = ClockSampler(local)
+    smp.start()
+    for host in (False, True):
+        for r in runs:
+            r.resident.clear()
+        for s in range(warmup):
+            for r in runs:
+                r.step(s + (100 if host else 0), host)
+        plans = [[r.plan_step(warmup + s + (100 if host else 0), host) for r in runs] for s in range(steps)]
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        for r in runs:
+            r.pics = r.h2d = r.d2h = 0
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0 = time.time()
+        e0.record()
+        for ps in plans:
+            for r, sp in zip(runs, ps):
+                r.run_step(sp, host)
+        for r in runs:
+            r.sess.sync()
+        e1.record()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        smp.window(t0, time.time())
+        ms = e0.elapsed_time(e1)
+        if world > 1:
+            t = torch.tensor([ms], device="cuda", dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        pics = sum(r.pics for r in runs) * world
+        res["e2e" if host else "resident"] = {"value": round(pics / (ms * 1e-3), 2), "unit": "frames/s (all 16 streams)", "ms": round(ms, 3)}
+        if host:
+            res["e2e"]["h2d_bytes_per_step"] = int(sum(r.h2d for r in runs) // steps)
+            res["e2e"]["d2h_bytes_per_step"] = int(sum(r.d2h for r in runs) // steps)
+    res["clocks"] = smp.stop()
+    res["workload"] = "16 streams of %s, %d sessions per rank x %d ranks, %d mini-GOPs per stream timed" % (wl.name, per_rank, world, steps)
+    for r in runs:
+        r.sess.close()
+    torch.cuda.empty_cache()
+    return res
 
 
 # ------------------------------------------------------------------------------------------------
@@ -581,7 +775,7 @@ def cpu_baseline(wl, frames, budget_s=12.0):
     arm = CpuArm(wl, frames, cores)
     arm.step(wl.order(wl.mgop))  # warm-up mini-GOP (also fills the plane cache with the reference pictures)
     n_pics, sec, m = 0, 0.0, 2
-    while sec < budget_s and m < 2 + 8:
+    while sec < budget_s and m < 2 + 256:
         pocs = wl.order(m * wl.mgop)
         sec += arm.step(pocs)
         n_pics += len(pocs)

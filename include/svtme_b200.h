@@ -255,7 +255,9 @@ void svtme_downsample_2d(uint8_t *input_samples, uint32_t input_stride, uint32_t
    refused with SVTME_ERR_BAD_PARAMETER and a message on stderr. All calls share the one scratch
    array: do not let two of them run on the GPU at the same time (other streams or threads). The
    first call on a device fetches the array's address from the CUDA runtime; issue that first call
-   before starting any stream capture. Output semantics are those of svt_sad_loop_kernel:
+   before starting any stream capture. Only the bytes svt_sad_loop_kernel itself reads are touched
+   (block_width bytes per source row, search_area_width + block_width - 1 per reference row): the
+   buffers may end flush with their allocation and need no alignment. Output semantics are those of svt_sad_loop_kernel:
    *d_best_sad = 0xffffff and the centres untouched when no position was evaluated. */
 #define SVTME_NOALLOC_MAX_WIDTH 1024
 #define SVTME_NOALLOC_MAX_BANDS 1024
@@ -389,6 +391,10 @@ uint32_t svtme_picture_device_planes(SvtMeSession *s, int32_t pic_id, SvtMeDevic
 uint32_t svtme_batch_results_acquire(SvtMeSession *s, uint64_t seq, uint32_t index, SvtMePicResults *device_ptrs,
                                      void *consumer_stream);
 uint32_t svtme_batch_results_release(SvtMeSession *s, uint64_t seq, void *consumer_stream);
+/* Page-locked host memory for frames and result slabs (copies from / to it are asynchronous and run at full PCIe rate);
+   for callers that do not link the CUDA runtime themselves. NULL on failure. A CUDA device must exist. */
+void *svtme_host_alloc(size_t bytes);
+void  svtme_host_free(void *p);
 /* Convenience for callers without the CUDA runtime (tests): synchronous copy of device memory to the host. */
 uint32_t svtme_copy_from_device(SvtMeSession *s, void *dst_host, const void *src_device, size_t bytes);
 
@@ -441,10 +447,17 @@ uint32_t svtme_session_enable_timing(SvtMeSession *s, int on);
 uint32_t svtme_session_kernel_time(SvtMeSession *s, int reset, double *fullpel_ms,
                                    double *hme_ms, uint64_t *n_launch);
 
+/* Per-kernel device time (ms) accumulated by the timed batches since the last reset: ms[tag] for tag = 1 .. the first
+   tag whose svtme_kernel_name is NULL (CUDA events behind every launch of the sequence, on the launching stream). */
+const char *svtme_kernel_name(int tag);
+uint32_t    svtme_session_kernel_times(SvtMeSession *s, int reset, double *ms, int n_ms);
+
 /* Algorithmic work done by the kernels since the last reset: "SAD operations" = search positions x
    block pixels compared (|a-b| and accumulate), the unit of SURVEY.md 8(d) / BASELINE.md. Counted on
    the device by the thread that sets up each search. */
 uint32_t svtme_session_sad_ops(SvtMeSession *s, int reset, uint64_t *hme_ops, uint64_t *fullpel_ops);
+/* The same split by stage: [0] HME stage total, [1] full-pel, [2] pre-HME, [3] HME level 0, [4] level 1, [5] level 2. */
+uint32_t svtme_session_sad_ops_by_stage(SvtMeSession *s, int reset, uint64_t ops[6]);
 
 /* Per-b64 HME-stage state of the last svtme_picture_me* call (parity debugging): n_b64 records of
    SvtMeHmeState. No reference counterpart as an array; the fields mirror MeContext members

@@ -152,6 +152,20 @@ class MePicResults(C.Structure):
     ]
 
 
+F_SB_RESULTS, F_STATS, F_SEARCH_RESULTS, F_BEST, F_WINDOWS, F_ALL = 1, 2, 4, 8, 16, 31
+ABSENT = (1 << (8 * C.sizeof(C.c_size_t))) - 1
+
+
+class PackedLayout(C.Structure):
+    """SvtMePackedLayout: block size and the offset of each SvtMePicResults member (ABSENT = not part of the block)"""
+    _fields_ = [("bytes", C.c_size_t), ("off", C.c_size_t * 15)]
+
+
+class DevicePlane(C.Structure):
+    """SvtMeDevicePlane"""
+    _fields_ = [("origin", C.c_void_p), ("stride", C.c_uint32), ("width", C.c_uint32), ("height", C.c_uint32), ("pad", C.c_uint32)]
+
+
 # numpy dtypes of the packed result records
 import numpy as np  # noqa: E402
 
@@ -186,11 +200,11 @@ class PicResultArrays:
         "stationary_block_present_sb", "rc_me_allow_gm",
     )
 
-    def __init__(self, width, height, params, pinned=False):
+    @staticmethod
+    def shapes_of(width, height, params):
         n = n_b64_of(width, height)
         n_pus = PU_COUNT if params.enable_me_8x8 else 21
-        self.n_b64, self.n_pus = n, n_pus
-        shapes = {
+        return n, n_pus, {
             "p_sb_best_sad": ((n, 2, 4, 85), np.uint32),
             "p_sb_best_mv": ((n, 2, 4, 85), np.uint32),
             "search_results": ((n, 2, 4), SEARCH_RESULT_DTYPE),
@@ -207,7 +221,25 @@ class PicResultArrays:
             "stationary_block_present_sb": ((n,), np.uint8),
             "rc_me_allow_gm": ((n,), np.uint8),
         }
+
+    def __init__(self, width, height, params, pinned=False, block=None, layout=None):
+        """block + layout: views into one picture's block of a packed result slab (svtme_picture_me_batch_packed) instead
+        of arrays of their own; members the layout does not hold are None"""
+        n, n_pus, shapes = self.shapes_of(width, height, params)
+        self.n_b64, self.n_pus = n, n_pus
         self.struct = MePicResults()
+        self._keep = []
+        if block is not None:
+            for i, name in enumerate(self.FIELDS):
+                shape, dt = shapes[name]
+                if layout.off[i] == ABSENT:
+                    setattr(self, name, None)
+                    continue
+                nbytes = int(np.prod(shape)) * np.dtype(dt).itemsize
+                arr = block[layout.off[i]:layout.off[i] + nbytes].view(dt).reshape(shape)
+                setattr(self, name, arr)
+                setattr(self.struct, name, arr.ctypes.data)
+            return
         self._keep = []
         for name, (shape, dt) in shapes.items():
             if pinned:

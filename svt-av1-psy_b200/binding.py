@@ -81,6 +81,36 @@ def lib():
         L.svtme_fetch_hme_state.restype = C.c_uint32
         L.svtme_session_sad_ops.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
         L.svtme_session_sad_ops.restype = C.c_uint32
+        for fn in (L.svtme_picture_upload_batch, L.svtme_picture_upload_10bit_batch, L.svtme_picture_upload_device_batch):
+            fn.argtypes = [C.c_void_p, C.c_uint32, C.POINTER(C.c_int32), C.POINTER(C.c_void_p), C.c_uint32]
+            fn.restype = C.c_uint32
+        L.svtme_kernel_name.argtypes = [C.c_int]
+        L.svtme_kernel_name.restype = C.c_char_p
+        L.svtme_session_kernel_times.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_double), C.c_int]
+        L.svtme_session_kernel_times.restype = C.c_uint32
+        L.svtme_session_sad_ops_by_stage.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_uint64)]
+        L.svtme_session_sad_ops_by_stage.restype = C.c_uint32
+        L.svtme_packed_layout.argtypes = [C.c_uint32, C.c_uint32, C.POINTER(abi.MePicParams), C.c_uint32, C.POINTER(abi.PackedLayout)]
+        L.svtme_packed_layout.restype = C.c_uint32
+        L.svtme_picture_me_batch_packed.argtypes = [C.c_void_p, C.c_uint32, C.POINTER(C.c_int32), C.POINTER(abi.MePicParams), C.c_uint32,
+                                                    C.c_void_p, C.c_size_t, C.c_int]
+        L.svtme_picture_me_batch_packed.restype = C.c_uint32
+        L.svtme_session_set_result_fields.argtypes = [C.c_void_p, C.c_uint32]
+        L.svtme_session_set_result_fields.restype = C.c_uint32
+        L.svtme_session_reserve.argtypes = [C.c_void_p, C.POINTER(abi.MePicParams), C.c_uint32]
+        L.svtme_session_reserve.restype = C.c_uint32
+        L.svtme_picture_device_planes.argtypes = [C.c_void_p, C.c_int32, C.POINTER(abi.DevicePlane)]
+        L.svtme_picture_device_planes.restype = C.c_uint32
+        L.svtme_batch_results_acquire.argtypes = [C.c_void_p, C.c_uint64, C.c_uint32, C.POINTER(abi.MePicResults), C.c_void_p]
+        L.svtme_batch_results_acquire.restype = C.c_uint32
+        L.svtme_batch_results_release.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p]
+        L.svtme_batch_results_release.restype = C.c_uint32
+        L.svtme_copy_from_device.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]
+        L.svtme_copy_from_device.restype = C.c_uint32
+        L.svtme_host_alloc.argtypes = [C.c_size_t]
+        L.svtme_host_alloc.restype = C.c_void_p
+        L.svtme_host_free.argtypes = [C.c_void_p]
+        L.svtme_host_free.restype = None
         L.svtme_abi_sizeof.argtypes = [C.c_int]
         L.svtme_abi_sizeof.restype = C.c_uint32
         _LIB = L
@@ -194,8 +224,6 @@ class Session:
         pp = (C.c_void_p * n)(*ptrs)
         fn = {"host8": lib().svtme_picture_upload_batch, "host10": lib().svtme_picture_upload_10bit_batch,
               "device": lib().svtme_picture_upload_device_batch}[kind]
-        fn.argtypes = [C.c_void_p, C.c_uint32, C.POINTER(C.c_int32), C.POINTER(C.c_void_p), C.c_uint32]
-        fn.restype = C.c_uint32
         _check(fn(self._h, n, ids, pp, stride), "svtme_picture_upload_*_batch")
 
     def me(self, pic_id, params, results=None, sync=True):
@@ -214,6 +242,42 @@ class Session:
             res = (abi.MePicResults * n)(*[r.struct for r in results_list])
         _check(lib().svtme_picture_me_batch(self._h, n, ids, prm, res, 1 if sync else 0), "svtme_picture_me_batch")
         return results_list
+
+    def packed_layout(self, params, fields):
+        lay = abi.PackedLayout()
+        _check(lib().svtme_packed_layout(self.width, self.height, C.byref(params), fields, C.byref(lay)), "svtme_packed_layout")
+        return lay
+
+    def me_batch_packed(self, ids_array, params_array, n, fields, slab_ptr, slab_bytes, sync=False):
+        """one launch sequence + ONE device-to-host copy for the whole batch; ids_array / params_array: ctypes arrays the
+        caller keeps (no per-call marshalling), slab_ptr: host memory of slab_bytes bytes (pinned for an asynchronous copy)"""
+        _check(lib().svtme_picture_me_batch_packed(self._h, n, ids_array, params_array, fields, slab_ptr, slab_bytes, 1 if sync else 0),
+               "svtme_picture_me_batch_packed")
+
+    def set_result_fields(self, fields):
+        _check(lib().svtme_session_set_result_fields(self._h, fields), "svtme_session_set_result_fields")
+
+    def reserve(self, params, n_pictures):
+        _check(lib().svtme_session_reserve(self._h, C.byref(params), n_pictures), "svtme_session_reserve")
+
+    def device_planes(self, pic_id):
+        planes = (abi.DevicePlane * 3)()
+        _check(lib().svtme_picture_device_planes(self._h, pic_id, planes), "svtme_picture_device_planes")
+        return planes
+
+    def acquire_results(self, seq, index, consumer_stream=None):
+        """device pointers (abi.MePicResults) to picture `index` of batch `seq`; consumer_stream waits for the batch"""
+        r = abi.MePicResults()
+        _check(lib().svtme_batch_results_acquire(self._h, seq, index, C.byref(r), C.c_void_p(consumer_stream)), "svtme_batch_results_acquire")
+        return r
+
+    def release_results(self, seq, consumer_stream=None):
+        _check(lib().svtme_batch_results_release(self._h, seq, C.c_void_p(consumer_stream)), "svtme_batch_results_release")
+
+    def read_device(self, dev_ptr, nbytes):
+        out = np.zeros(nbytes, np.uint8)
+        _check(lib().svtme_copy_from_device(self._h, out.ctypes.data, C.c_void_p(dev_ptr), nbytes), "svtme_copy_from_device")
+        return out
 
     def fetch_batch(self, index, results, sync=True):
         _check(lib().svtme_fetch_results_batch(self._h, index, C.byref(results.struct), 1 if sync else 0), "svtme_fetch_results_batch")
@@ -284,6 +348,24 @@ class Session:
         a, b = C.c_uint64(), C.c_uint64()
         _check(lib().svtme_session_sad_ops(self._h, 1 if reset else 0, C.byref(a), C.byref(b)), "svtme_session_sad_ops")
         return int(a.value), int(b.value)
+
+    def sad_ops_by_stage(self, reset=False):
+        """[HME stage total, full-pel, pre-HME, HME level 0, level 1, level 2]"""
+        v = (C.c_uint64 * 6)()
+        _check(lib().svtme_session_sad_ops_by_stage(self._h, 1 if reset else 0, v), "svtme_session_sad_ops_by_stage")
+        return [int(x) for x in v]
+
+    def kernel_times(self, reset=False):
+        """{kernel name: device ms accumulated by the timed batches}"""
+        ms = (C.c_double * 16)()
+        _check(lib().svtme_session_kernel_times(self._h, 1 if reset else 0, ms, 16), "svtme_session_kernel_times")
+        out = {}
+        for tag in range(1, 16):
+            name = lib().svtme_kernel_name(tag)
+            if not name:
+                break
+            out[name.decode()] = ms[tag]
+        return out
 
     def launch_count(self):
         return int(lib().svtme_session_launch_count(self._h))

@@ -107,8 +107,10 @@ struct SvtMeSession {
     struct BatchOut {
         uint64_t seq = 0;
         bool     me = false; // false: the set was last used by the detector
+        struct Geo { size_t n_pus, max_refs, max_cand; };
         std::vector<SvtMePackedLayout> lay;
         std::vector<size_t>            base;
+        std::vector<Geo>               geo;
         size_t   total = 0;
     } out[2];
     uint8_t     *dl_region[2] = {nullptr, nullptr};
@@ -132,6 +134,9 @@ struct SvtMeSession {
     size_t       ev_used = 0;
     double       acc_hme_ms = 0, acc_fp_ms = 0;
     uint64_t     n_timed = 0;
+    std::vector<SvtMeTimeline> tls; // per-kernel timelines of the timed batches not folded yet
+    std::vector<cudaEvent_t>   tl_pool;
+    double       acc_tag_ms[SVTME_TL_TAGS] = {};
     std::mutex   mu;
 };
 
@@ -260,6 +265,12 @@ extern "C" uint32_t svtme_session_create(SvtMeSession **out, int device, uint32_
     CU_TRY(cudaStreamCreateWithFlags(&s->dl_stream, cudaStreamNonBlocking));
     for (auto &e2 : s->ev_me) CU_TRY(cudaEventCreateWithFlags(&e2, cudaEventDisableTiming));
     for (auto &e2 : s->ev_dl) CU_TRY(cudaEventCreateWithFlags(&e2, cudaEventDisableTiming));
+    for (auto &e2 : s->ev_jobs) CU_TRY(cudaEventCreateWithFlags(&e2, cudaEventDisableTiming));
+    for (auto &e2 : s->ev_release) CU_TRY(cudaEventCreateWithFlags(&e2, cudaEventDisableTiming));
+    CU_TRY(cudaEventCreateWithFlags(&s->ev_copied, cudaEventDisableTiming));
+    CU_TRY(cudaMallocHost(&s->h_flags, 2 * sizeof(uint32_t)));
+    s->h_flags[0] = s->h_flags[1] = 0;
+    CU_TRY(cudaMallocHost(&s->h_jobs_ring, sizeof(PicJob) * 4));
     CU_TRY(cudaDeviceSynchronize());
     *out = s;
     return SVTME_OK;
@@ -273,6 +284,8 @@ extern "C" void svtme_session_destroy(SvtMeSession *s) {
     cudaStreamSynchronize(s->stream2);
     cudaStreamSynchronize(s->dl_stream);
     for (auto &e : s->ev) cudaEventDestroy(e);
+    for (auto &t : s->tls) for (auto &e : t.ev) cudaEventDestroy(e);
+    for (auto &e : s->tl_pool) cudaEventDestroy(e);
     for (auto &e : s->ev_me) if (e) cudaEventDestroy(e);
     for (auto &e : s->ev_dl) if (e) cudaEventDestroy(e);
     if (s->up_stream) cudaStreamDestroy(s->up_stream);
@@ -286,8 +299,14 @@ extern "C" void svtme_session_destroy(SvtMeSession *s) {
         for (uint8_t *p : set) cudaFree(p);
     if (s->d_jobs) cudaFree(s->d_jobs);
     if (s->stage_slab) cudaFree(s->stage_slab);
-    for (auto &e : s->ev_copied) if (e) cudaEventDestroy(e);
-    for (auto &e : s->ev_ingested) if (e) cudaEventDestroy(e);
+    if (s->ev_copied) cudaEventDestroy(s->ev_copied);
+    for (auto &a : s->stage_live) cudaEventDestroy(a.ev_ingested);
+    for (auto &e : s->stage_ev_pool) cudaEventDestroy(e);
+    for (auto &e : s->ev_jobs) if (e) cudaEventDestroy(e);
+    for (auto &e : s->ev_release) if (e) cudaEventDestroy(e);
+    for (auto &p : s->dl_region) if (p) cudaFree(p);
+    if (s->h_flags) cudaFreeHost(s->h_flags);
+    if (s->h_jobs_ring) cudaFreeHost(s->h_jobs_ring);
     if (s->fp_units) cudaFree(s->fp_units);
     if (s->s16_units) cudaFree(s->s16_units);
     delete s;
@@ -325,7 +344,12 @@ static cudaStream_t compute_stream(const SvtMeSession *s, int set) {
 static int stream_index(const SvtMeSession *s, int set) { return compute_stream(s, set) == s->stream2 ? 1 : 0; }
 
 // The unit queues are sized from the largest windows the controls allow; a kernel that finds one too small raises a
-// flag instead of dropping work silently. Checked at every synchronisation point.
+// flag instead of dropping work silently. The flag of a result set travels to the host behind every download of the set
+// (h_flags, checked by svtme_session_wait_batch and the sync = 1 paths) and is read directly at svtme_session_sync.
+static uint32_t report_overflow() {
+    fprintf(stderr, "[svtme_b200] a search-unit queue overflowed: results of the last batches are incomplete\n");
+    return SVTME_ERR_INSUFFICIENT_RESOURCES;
+}
 static uint32_t check_queue_overflow(SvtMeSession *s) {
     uint32_t flag = 0;
     for (int set = 0; set < 2 && !flag; set++)
@@ -334,11 +358,15 @@ static uint32_t check_queue_overflow(SvtMeSession *s) {
             CU_TRY(cudaStreamSynchronize(s->stream));
             if (flag) cudaMemsetAsync((uint32_t *)(s->res_sets[set][0] + s->lay.fp_counters) + 8, 0, sizeof(flag), s->stream);
         }
-    if (flag) {
-        fprintf(stderr, "[svtme_b200] a search-unit queue overflowed: results of the last batches are incomplete\n");
-        return SVTME_ERR_INSUFFICIENT_RESOURCES;
-    }
-    return SVTME_OK;
+    s->h_flags[0] = s->h_flags[1] = 0;
+    return flag ? report_overflow() : SVTME_OK;
+}
+// after a download of `set` has completed on the host side
+static uint32_t check_downloaded_flag(SvtMeSession *s, int set) {
+    if (!s->h_flags[set]) return SVTME_OK;
+    s->h_flags[set] = 0;
+    cudaMemsetAsync((uint32_t *)(s->res_sets[set][0] + s->lay.fp_counters) + 8, 0, sizeof(uint32_t), s->dl_stream);
+    return report_overflow();
 }
 
 extern "C" uint32_t svtme_session_sync(SvtMeSession *s) {
@@ -362,12 +390,21 @@ extern "C" uint64_t svtme_session_batch_seq(SvtMeSession *s) { return s ? s->bat
 
 extern "C" uint32_t svtme_session_wait_batch(SvtMeSession *s, uint64_t seq) {
     if (!s) return SVTME_ERR_BAD_PARAMETER;
-    if (seq == 0 || seq > s->batch_seq) return SVTME_OK;
+    cudaEvent_t ev;
+    bool downloaded;
+    const int set = (int)(seq & 1);
+    { // the events live as long as the session; only the bookkeeping needs the lock (other threads may be launching)
+        std::lock_guard<std::mutex> g(s->mu);
+        if (seq == 0 || seq > s->batch_seq) return SVTME_OK;
+        // results of batch `seq` were copied by the download recorded in ev_dl[set] (or by a later one of the same set)
+        downloaded = s->dl_recorded[set];
+        ev = downloaded ? s->ev_dl[set] : s->ev_me[seq % 8];
+    }
     cudaSetDevice(s->device);
-    // results of batch `seq` were copied by the download recorded in ev_dl[seq & 1] (or by a later one of the same set)
-    if (s->dl_recorded[seq & 1]) CU_TRY(cudaEventSynchronize(s->ev_dl[seq & 1]));
-    else CU_TRY(cudaEventSynchronize(s->ev_me[seq % 8]));
-    return SVTME_OK;
+    CU_TRY(cudaEventSynchronize(ev));
+    if (!downloaded) return SVTME_OK;
+    std::lock_guard<std::mutex> g(s->mu);
+    return check_downloaded_flag(s, set);
 }
 
 // Host uploads: the frame crosses PCIe as ONE linear copy into a ring of staging frames on the upload stream (pure
@@ -376,28 +413,32 @@ extern "C" uint32_t svtme_session_wait_batch(SvtMeSession *s, uint64_t seq) {
 // Measured: building the pyramid on the upload stream gated every copy behind a kernel waiting for an SM slot next
 // to the persistent search kernels, and a pitched 2-D copy into the padded plane reaches ~11 GB/s.
 #define SVTME_STAGE_FRAMES 40
-static uint32_t stage_host_frame(SvtMeSession *s, const void *host, size_t row_bytes, size_t host_pitch, void **staged) {
-    const size_t frame_bytes = (size_t)s->w * s->h * 2; // fits 8-bit and 16-bit input
+// a region of the staging ring; the regions it overlaps were consumed by pyramid builds queued earlier: the upload
+// stream waits for those before the copy engine overwrites them
+static uint32_t stage_alloc(SvtMeSession *s, size_t bytes, uint8_t **dst, cudaEvent_t *ev_ingested) {
     if (!s->stage_slab) {
-        cudaError_t e = cudaMalloc(&s->stage_slab, frame_bytes * SVTME_STAGE_FRAMES);
-        if (e != cudaSuccess) { fprintf(stderr, "[svtme_b200] cudaMalloc staging ring: %s\n", cudaGetErrorString(e)); return SVTME_ERR_INSUFFICIENT_RESOURCES; }
-        for (int i = 0; i < SVTME_STAGE_FRAMES; i++) {
-            CU_TRY(cudaEventCreateWithFlags(&s->ev_copied[i], cudaEventDisableTiming));
-            CU_TRY(cudaEventCreateWithFlags(&s->ev_ingested[i], cudaEventDisableTiming));
-        }
+        s->stage_cap = (size_t)s->w * s->h * 2 * SVTME_STAGE_FRAMES; // 40 frames of 16-bit samples
+        cudaError_t e = cudaMalloc(&s->stage_slab, s->stage_cap);
+        if (e != cudaSuccess) { s->stage_cap = 0; fprintf(stderr, "[svtme_b200] cudaMalloc staging ring: %s\n", cudaGetErrorString(e)); return SVTME_ERR_INSUFFICIENT_RESOURCES; }
     }
-    const int j = (int)(s->stage_head++ % SVTME_STAGE_FRAMES);
-    uint8_t *dst = s->stage_slab + frame_bytes * j;
-    if (s->stage_used[j]) CU_TRY(cudaStreamWaitEvent(s->up_stream, s->ev_ingested[j], 0)); // its previous frame was consumed
-    if (host_pitch == row_bytes)
-        CU_TRY(cudaMemcpyAsync(dst, host, row_bytes * s->h, cudaMemcpyHostToDevice, s->up_stream));
-    else
-        CU_TRY(cudaMemcpy2DAsync(dst, row_bytes, host, host_pitch, row_bytes, (size_t)s->h, cudaMemcpyHostToDevice, s->up_stream));
-    CU_TRY(cudaEventRecord(s->ev_copied[j], s->up_stream));
-    CU_TRY(cudaStreamWaitEvent(compute_stream(s, (int)((s->batch_seq + 1) & 1)), s->ev_copied[j], 0));
-    s->stage_used[j] = true;
-    s->stage_last = j;
-    *staged = dst;
+    bytes = align_up(bytes, 256);
+    if (bytes > s->stage_cap) return SVTME_ERR_BAD_PARAMETER;
+    if (s->stage_head + bytes > s->stage_cap) s->stage_head = 0;
+    const size_t b = s->stage_head, e = b + bytes;
+    s->stage_head = e;
+    while (!s->stage_live.empty()) { // FIFO in ring order: the overlapping regions are the oldest ones
+        SvtMeSession::StageAlloc &a = s->stage_live.front();
+        if (a.end <= b || a.begin >= e) break;
+        CU_TRY(cudaStreamWaitEvent(s->up_stream, a.ev_ingested, 0));
+        s->stage_ev_pool.push_back(a.ev_ingested);
+        s->stage_live.pop_front();
+    }
+    cudaEvent_t ev;
+    if (!s->stage_ev_pool.empty()) { ev = s->stage_ev_pool.back(); s->stage_ev_pool.pop_back(); }
+    else CU_TRY(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+    s->stage_live.push_back({b, e, ev});
+    *dst = s->stage_slab + b;
+    *ev_ingested = ev;
     return SVTME_OK;
 }
 
@@ -415,45 +456,9 @@ static uint32_t after_builds(SvtMeSession *s, cudaStream_t cs) {
     return SVTME_OK;
 }
 
-static uint32_t finish_upload(SvtMeSession *s, int32_t pic_id, int mode, const void *d_in, int in_stride, bool staged) {
-    cudaStream_t cs = compute_stream(s, (int)((s->batch_seq + 1) & 1));
-    uint32_t rc = before_build(s, cs, pic_id);
-    if (rc != SVTME_OK) return rc;
-    s->launches += (uint64_t)svtme_launch_build_pyramid(s->pics[pic_id], mode, d_in, in_stride, cs);
-    CU_TRY(cudaGetLastError());
-    if (staged) CU_TRY(cudaEventRecord(s->ev_ingested[s->stage_last], cs));
-    s->pic_valid[pic_id] = 1;
-    return after_builds(s, cs);
-}
-
-extern "C" uint32_t svtme_picture_upload(SvtMeSession *s, int32_t pic_id, const uint8_t *luma, uint32_t stride) {
-    if (!s || !luma || pic_id < 0 || pic_id >= s->max_pics || stride < (uint32_t)s->w) return SVTME_ERR_BAD_PARAMETER;
-    std::lock_guard<std::mutex> g(s->mu);
-    CU_TRY(cudaSetDevice(s->device));
-    void *staged = nullptr;
-    uint32_t rc = stage_host_frame(s, luma, (size_t)s->w, stride, &staged);
-    if (rc != SVTME_OK) return rc;
-    return finish_upload(s, pic_id, 0, staged, s->w, true);
-}
-
-extern "C" uint32_t svtme_picture_upload_device(SvtMeSession *s, int32_t pic_id, const uint8_t *d_luma, uint32_t stride) {
-    if (!s || !d_luma || pic_id < 0 || pic_id >= s->max_pics || stride < (uint32_t)s->w) return SVTME_ERR_BAD_PARAMETER;
-    std::lock_guard<std::mutex> g(s->mu);
-    CU_TRY(cudaSetDevice(s->device));
-    return finish_upload(s, pic_id, 0, d_luma, (int)stride, false);
-}
-
-extern "C" uint32_t svtme_picture_upload_10bit(SvtMeSession *s, int32_t pic_id, const uint16_t *luma16, uint32_t stride_in_samples) {
-    if (!s || !luma16 || pic_id < 0 || pic_id >= s->max_pics || stride_in_samples < (uint32_t)s->w) return SVTME_ERR_BAD_PARAMETER;
-    std::lock_guard<std::mutex> g(s->mu);
-    CU_TRY(cudaSetDevice(s->device));
-    void *staged = nullptr;
-    uint32_t rc = stage_host_frame(s, luma16, (size_t)s->w * 2, (size_t)stride_in_samples * 2, &staged);
-    if (rc != SVTME_OK) return rc;
-    return finish_upload(s, pic_id, 2, staged, s->w, true);
-}
-
-// Batched uploads: the pyramids of n pictures are built by two launches instead of 2n.
+// Uploads of n pictures: host frames are copied into ONE region of the staging ring, frames that are adjacent in host
+// memory (a decoded clip, the frames of a mini-GOP in a capture buffer) as one copy, whatever the order they were named
+// in; then the pyramids of all n are built by two launches.
 static uint32_t upload_batch(SvtMeSession *s, uint32_t n, const int32_t *pic_ids, const void *const *src, size_t row_bytes,
                              size_t host_pitch, int mode, bool host) {
     if (!s || !pic_ids || !src || n == 0 || n > SVTME_STAGE_FRAMES) return SVTME_ERR_BAD_PARAMETER;
@@ -463,31 +468,67 @@ static uint32_t upload_batch(SvtMeSession *s, uint32_t n, const int32_t *pic_ids
     CU_TRY(cudaSetDevice(s->device));
     std::vector<DevPic>       pics(n);
     std::vector<const void *> in(n);
-    std::vector<int>          ring(n, -1);
+    cudaStream_t cs = compute_stream(s, (int)((s->batch_seq + 1) & 1));
+    cudaEvent_t ev_ingested = nullptr;
+    if (host) {
+        const size_t frame_bytes = row_bytes * (size_t)s->h;
+        uint8_t *region = nullptr;
+        uint32_t rc = stage_alloc(s, frame_bytes * n, &region, &ev_ingested);
+        if (rc != SVTME_OK) return rc;
+        std::vector<uint32_t> order(n);
+        for (uint32_t i = 0; i < n; i++) order[i] = i;
+        std::sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return (uintptr_t)src[a] < (uintptr_t)src[b]; });
+        for (uint32_t k = 0; k < n;) {
+            uint32_t run = 1;
+            if (host_pitch == row_bytes)
+                while (k + run < n && (const uint8_t *)src[order[k + run]] == (const uint8_t *)src[order[k]] + frame_bytes * run) run++;
+            uint8_t *dst = region + frame_bytes * k;
+            if (host_pitch == row_bytes)
+                CU_TRY(cudaMemcpyAsync(dst, src[order[k]], frame_bytes * run, cudaMemcpyHostToDevice, s->up_stream));
+            else
+                CU_TRY(cudaMemcpy2DAsync(dst, row_bytes, src[order[k]], host_pitch, row_bytes, (size_t)s->h, cudaMemcpyHostToDevice, s->up_stream));
+            for (uint32_t j = 0; j < run; j++) in[order[k + j]] = region + frame_bytes * (k + j);
+            k += run;
+        }
+        CU_TRY(cudaEventRecord(s->ev_copied, s->up_stream));
+        CU_TRY(cudaStreamWaitEvent(cs, s->ev_copied, 0));
+    }
     for (uint32_t i = 0; i < n; i++) {
         pics[i] = s->pics[pic_ids[i]];
-        if (host) {
-            void *staged = nullptr;
-            uint32_t rc = stage_host_frame(s, src[i], row_bytes, host_pitch, &staged);
-            if (rc != SVTME_OK) return rc;
-            in[i] = staged;
-            ring[i] = s->stage_last;
-        } else {
-            in[i] = src[i];
-        }
-    }
-    cudaStream_t cs = compute_stream(s, (int)((s->batch_seq + 1) & 1));
-    for (uint32_t i = 0; i < n; i++) {
+        if (!host) in[i] = src[i];
         uint32_t rc = before_build(s, cs, pic_ids[i]);
         if (rc != SVTME_OK) return rc;
     }
     s->launches += (uint64_t)svtme_launch_build_pyramids(pics.data(), in.data(), s->w, (int)n, mode, cs);
     CU_TRY(cudaGetLastError());
-    for (uint32_t i = 0; i < n; i++) {
-        if (host) CU_TRY(cudaEventRecord(s->ev_ingested[ring[i]], cs));
-        s->pic_valid[pic_ids[i]] = 1;
-    }
+    if (host) CU_TRY(cudaEventRecord(ev_ingested, cs));
+    for (uint32_t i = 0; i < n; i++) s->pic_valid[pic_ids[i]] = 1;
     return after_builds(s, cs);
+}
+
+extern "C" uint32_t svtme_picture_upload(SvtMeSession *s, int32_t pic_id, const uint8_t *luma, uint32_t stride) {
+    if (!s || !luma || stride < (uint32_t)s->w) return SVTME_ERR_BAD_PARAMETER;
+    const void *p = luma;
+    return upload_batch(s, 1, &pic_id, &p, (size_t)s->w, stride, 0, true);
+}
+
+extern "C" uint32_t svtme_picture_upload_device(SvtMeSession *s, int32_t pic_id, const uint8_t *d_luma, uint32_t stride) {
+    if (!s || !d_luma || pic_id < 0 || pic_id >= s->max_pics || stride < (uint32_t)s->w) return SVTME_ERR_BAD_PARAMETER;
+    std::lock_guard<std::mutex> g(s->mu);
+    CU_TRY(cudaSetDevice(s->device));
+    cudaStream_t cs = compute_stream(s, (int)((s->batch_seq + 1) & 1));
+    uint32_t rc = before_build(s, cs, pic_id);
+    if (rc != SVTME_OK) return rc;
+    s->launches += (uint64_t)svtme_launch_build_pyramid(s->pics[pic_id], 0, d_luma, (int)stride, cs);
+    CU_TRY(cudaGetLastError());
+    s->pic_valid[pic_id] = 1;
+    return after_builds(s, cs);
+}
+
+extern "C" uint32_t svtme_picture_upload_10bit(SvtMeSession *s, int32_t pic_id, const uint16_t *luma16, uint32_t stride_in_samples) {
+    if (!s || !luma16 || stride_in_samples < (uint32_t)s->w) return SVTME_ERR_BAD_PARAMETER;
+    const void *p = luma16;
+    return upload_batch(s, 1, &pic_id, &p, (size_t)s->w * 2, (size_t)stride_in_samples * 2, 2, true);
 }
 
 extern "C" uint32_t svtme_picture_upload_batch(SvtMeSession *s, uint32_t n, const int32_t *pic_ids, const uint8_t *const *luma,
@@ -556,7 +597,18 @@ static uint32_t validate_params(const SvtMeSession *s, int32_t pic_id, const Svt
     return SVTME_OK;
 }
 
+static void fold_timelines(SvtMeSession *s) {
+    for (SvtMeTimeline &t : s->tls) {
+        for (int i = 1; i < t.n; i++) {
+            float ms = 0;
+            if (cudaEventElapsedTime(&ms, t.ev[i - 1], t.ev[i]) == cudaSuccess) s->acc_tag_ms[t.tag[i]] += ms;
+        }
+        for (int i = 0; i < SVTME_TL_MAX; i++) s->tl_pool.push_back(t.ev[i]);
+    }
+    s->tls.clear();
+}
 static void fold_events(SvtMeSession *s) {
+    fold_timelines(s);
     for (size_t i = 0; i + 3 <= s->ev_used; i += 3) {
         float a = 0, b = 0;
         if (cudaEventElapsedTime(&a, s->ev[i], s->ev[i + 1]) == cudaSuccess &&
@@ -585,11 +637,105 @@ static uint32_t ensure_batch(SvtMeSession *s, uint32_t n) {
     s->d_jobs = nullptr;
     cudaError_t e = cudaMalloc(&s->d_jobs, sizeof(PicJob) * n * 2); // one half per result set
     if (e != cudaSuccess) return SVTME_ERR_INSUFFICIENT_RESOURCES;
+    if (s->h_jobs_ring) cudaFreeHost(s->h_jobs_ring);
+    s->h_jobs_ring = nullptr;
+    if (cudaMallocHost(&s->h_jobs_ring, sizeof(PicJob) * n * 4) != cudaSuccess) return SVTME_ERR_INSUFFICIENT_RESOURCES;
+    for (auto &u : s->jobs_used) u = false;
     s->d_jobs_n = n;
     return SVTME_OK;
 }
 
-static uint32_t launch_me_batch(SvtMeSession *s, uint32_t n, const int32_t *pic_ids, const SvtMePicParams *params) {
+// a pinned job array nobody is copying from any more
+static uint32_t next_job_array(SvtMeSession *s, PicJob **out, int *slot) {
+    const int k = (int)(s->jobs_head++ & 3);
+    if (s->jobs_used[k]) CU_TRY(cudaEventSynchronize(s->ev_jobs[k])); // four batches back: long done
+    *out = s->h_jobs_ring + (size_t)k * s->d_jobs_n;
+    *slot = k;
+    return SVTME_OK;
+}
+
+static uint32_t ensure_units(SvtMeSession *s, uint64_t need_units, uint64_t need_s16) {
+    if (need_units > 0x7fffffffull || need_s16 > 0x7fffffffull) return SVTME_ERR_INSUFFICIENT_RESOURCES;
+    if (need_units > s->fp_units_cap) { // the unit queue grows with the largest search window of the controls in use
+        uint32_t rcs = sync_all(s);
+        if (rcs != SVTME_OK) return rcs;
+        if (s->fp_units) cudaFree(s->fp_units);
+        s->fp_units = nullptr; s->fp_units_cap = 0;
+        cudaError_t e = cudaMalloc(&s->fp_units, (size_t)need_units * 2 * sizeof(uint2)); // one half per result set
+        if (e != cudaSuccess) { fprintf(stderr, "[svtme_b200] cudaMalloc unit queue (%llu units): %s\n", (unsigned long long)need_units, cudaGetErrorString(e)); return SVTME_ERR_INSUFFICIENT_RESOURCES; }
+        s->fp_units_cap = (uint32_t)need_units;
+    }
+    if (need_s16 > s->s16_units_cap) {
+        uint32_t rcs = sync_all(s);
+        if (rcs != SVTME_OK) return rcs;
+        if (s->s16_units) cudaFree(s->s16_units);
+        s->s16_units = nullptr; s->s16_units_cap = 0;
+        cudaError_t e = cudaMalloc(&s->s16_units, (size_t)need_s16 * 2 * sizeof(uint2));
+        if (e != cudaSuccess) { fprintf(stderr, "[svtme_b200] cudaMalloc HME unit queue (%llu units): %s\n", (unsigned long long)need_s16, cudaGetErrorString(e)); return SVTME_ERR_INSUFFICIENT_RESOURCES; }
+        s->s16_units_cap = (uint32_t)need_s16;
+    }
+    return SVTME_OK;
+}
+
+static uint32_t ensure_download_region(SvtMeSession *s, int set, size_t bytes) {
+    if (bytes <= s->dl_cap[set]) return SVTME_OK;
+    uint32_t rc = sync_all(s);
+    if (rc != SVTME_OK) return rc;
+    if (s->dl_region[set]) cudaFree(s->dl_region[set]);
+    s->dl_region[set] = nullptr; s->dl_cap[set] = 0;
+    cudaError_t e = cudaMalloc(&s->dl_region[set], bytes);
+    if (e != cudaSuccess) { fprintf(stderr, "[svtme_b200] cudaMalloc result region (%zu bytes): %s\n", bytes, cudaGetErrorString(e)); return SVTME_ERR_INSUFFICIENT_RESOURCES; }
+    cudaMemset(s->dl_region[set], 0, bytes);
+    s->dl_cap[set] = bytes;
+    return SVTME_OK;
+}
+
+extern "C" uint32_t svtme_session_reserve(SvtMeSession *s, const SvtMePicParams *params, uint32_t n_pictures) {
+    if (!s || !params || n_pictures == 0 || n_pictures > 4096) return SVTME_ERR_BAD_PARAMETER;
+    std::lock_guard<std::mutex> g(s->mu);
+    CU_TRY(cudaSetDevice(s->device));
+    uint32_t rc = ensure_batch(s, n_pictures);
+    if (rc != SVTME_OK) return rc;
+    rc = ensure_units(s, (uint64_t)svtme_fp_units_cap(*params, s->n_b64) * n_pictures, (uint64_t)svtme_s16_units_cap(*params, s->n_b64) * n_pictures);
+    if (rc != SVTME_OK) return rc;
+    SvtMePackedLayout L;
+    packed_layout((size_t)s->n_b64, 85, 8, 32, SVTME_F_ALL, &L); // the largest block any picture of this size can have
+    for (int set = 0; set < 2; set++) {
+        rc = ensure_download_region(s, set, L.bytes * n_pictures);
+        if (rc != SVTME_OK) return rc;
+    }
+    return SVTME_OK;
+}
+
+extern "C" uint32_t svtme_session_set_result_fields(SvtMeSession *s, uint32_t fields) {
+    if (!s || (fields & ~SVTME_F_ALL)) return SVTME_ERR_BAD_PARAMETER;
+    std::lock_guard<std::mutex> g(s->mu);
+    s->default_fields = fields;
+    return SVTME_OK;
+}
+
+extern "C" uint32_t svtme_packed_layout(uint32_t width, uint32_t height, const SvtMePicParams *params, uint32_t fields,
+                                        SvtMePackedLayout *out) {
+    if (!params || !out || !width || !height || (fields & ~SVTME_F_ALL) || params->max_refs > 8 || params->max_cand > 32) return SVTME_ERR_BAD_PARAMETER;
+    const size_t n_b64 = (size_t)((width + 63) / 64) * ((height + 63) / 64);
+    packed_layout(n_b64, params->enable_me_8x8 ? 85 : 21, params->max_refs, params->max_cand, fields, out);
+    return SVTME_OK;
+}
+
+extern "C" void svtme_packed_view(const SvtMePackedLayout *layout, void *block, SvtMePicResults *out) {
+    for (int f = 0; f < RF_COUNT; f++)
+        *result_member(out, f) = layout->off[f] == (size_t)-1 ? nullptr : (void *)((uint8_t *)block + layout->off[f]);
+}
+
+static uint32_t fields_of_results(const SvtMePicResults *r) {
+    uint32_t m = 0;
+    for (int f = 0; f < RF_COUNT; f++)
+        if (*result_member(const_cast<SvtMePicResults *>(r), f)) m |= rf_group[f];
+    return m;
+}
+
+// fields[i]: what picture i must produce (SVTME_F_*)
+static uint32_t launch_me_batch(SvtMeSession *s, uint32_t n, const int32_t *pic_ids, const SvtMePicParams *params, const uint32_t *fields) {
     if (!s || !pic_ids || !params || n == 0 || n > 4096) return SVTME_ERR_BAD_PARAMETER;
     CU_TRY(cudaSetDevice(s->device));
     uint64_t need_units = 0, need_s16 = 0;
@@ -608,41 +754,42 @@ static uint32_t launch_me_batch(SvtMeSession *s, uint32_t n, const int32_t *pic_
         need_units += svtme_fp_units_cap(params[i], s->n_b64);
         need_s16 += svtme_s16_units_cap(params[i], s->n_b64);
     }
-    if (need_units > 0x7fffffffull) return SVTME_ERR_INSUFFICIENT_RESOURCES;
     uint32_t rc = ensure_batch(s, n);
     if (rc != SVTME_OK) return rc;
-    if (need_units > s->fp_units_cap) { // the unit queue grows with the largest search window of the controls in use
-        uint32_t rcs = sync_all(s);
-        if (rcs != SVTME_OK) return rcs;
-        if (s->fp_units) cudaFree(s->fp_units);
-        s->fp_units = nullptr; s->fp_units_cap = 0;
-        cudaError_t e = cudaMalloc(&s->fp_units, (size_t)need_units * 2 * sizeof(uint2)); // one half per result set
-        if (e != cudaSuccess) { fprintf(stderr, "[svtme_b200] cudaMalloc unit queue (%llu units): %s\n", (unsigned long long)need_units, cudaGetErrorString(e)); return SVTME_ERR_INSUFFICIENT_RESOURCES; }
-        s->fp_units_cap = (uint32_t)need_units;
-    }
-    if (need_s16 > 0x7fffffffull) return SVTME_ERR_INSUFFICIENT_RESOURCES;
-    if (need_s16 > s->s16_units_cap) {
-        uint32_t rcs = sync_all(s);
-        if (rcs != SVTME_OK) return rcs;
-        if (s->s16_units) cudaFree(s->s16_units);
-        s->s16_units = nullptr; s->s16_units_cap = 0;
-        cudaError_t e = cudaMalloc(&s->s16_units, (size_t)need_s16 * 2 * sizeof(uint2));
-        if (e != cudaSuccess) { fprintf(stderr, "[svtme_b200] cudaMalloc HME unit queue (%llu units): %s\n", (unsigned long long)need_s16, cudaGetErrorString(e)); return SVTME_ERR_INSUFFICIENT_RESOURCES; }
-        s->s16_units_cap = (uint32_t)need_s16;
-    }
-    const uint64_t seq = ++s->batch_seq;
+    rc = ensure_units(s, need_units, need_s16);
+    if (rc != SVTME_OK) return rc;
+    const uint64_t seq = s->batch_seq + 1;
     const int set = (int)(seq & 1);
+    SvtMeSession::BatchOut &bo = s->out[set];
+    std::vector<SvtMePackedLayout> lay(n);
+    std::vector<size_t> base(n);
+    size_t total = 0;
+    for (uint32_t i = 0; i < n; i++) {
+        packed_layout((size_t)s->n_b64, params[i].enable_me_8x8 ? 85 : 21, params[i].max_refs, params[i].max_cand, fields[i], &lay[i]);
+        base[i] = total;
+        total += lay[i].bytes;
+    }
+    rc = ensure_download_region(s, set, total);
+    if (rc != SVTME_OK) return rc;
+    s->batch_seq = seq;
+    bo.seq = seq; bo.me = true; bo.lay.swap(lay); bo.base.swap(base); bo.total = total;
+    bo.geo.resize(n);
+    for (uint32_t i = 0; i < n; i++) bo.geo[i] = {(size_t)(params[i].enable_me_8x8 ? 85 : 21), (size_t)params[i].max_refs, (size_t)params[i].max_cand};
     cudaStream_t cs = compute_stream(s, set);
     if (s->dl_recorded[set]) CU_TRY(cudaStreamWaitEvent(cs, s->ev_dl[set], 0)); // the set's previous results left for the host
+    if (s->release_recorded[set]) { CU_TRY(cudaStreamWaitEvent(cs, s->ev_release[set], 0)); s->release_recorded[set] = false; } // ... and its device-side readers are done
     if (s->concurrency == 2) { // pictures whose pyramids were queued on the other compute stream
         const int other = 1 - stream_index(s, set);
         if (s->built_recorded[other]) CU_TRY(cudaStreamWaitEvent(cs, s->ev_built[other], 0));
     }
     PicJob *d_jobs = s->d_jobs + (size_t)set * s->d_jobs_n;
-    s->h_jobs.resize(n);
+    PicJob *h_jobs = nullptr;
+    int jslot = 0;
+    rc = next_job_array(s, &h_jobs, &jslot);
+    if (rc != SVTME_OK) return rc;
     for (uint32_t i = 0; i < n; i++) {
         const SvtMePicParams *pp = &params[i];
-        PicJob &job = s->h_jobs[i];
+        PicJob &job = h_jobs[i];
         memset(&job, 0, sizeof(job));
         job.pp  = *pp;
         job.src = s->pics[pic_ids[i]];
@@ -655,22 +802,25 @@ static uint32_t launch_me_batch(SvtMeSession *s, uint32_t n, const int32_t *pic_
         job.pic_w = s->w; job.pic_h = s->h; job.b64_cols = s->b64_cols; job.b64_rows = s->b64_rows; job.n_b64 = s->n_b64;
         job.n_pus = pp->enable_me_8x8 ? 85 : 21;
         uint8_t *R = s->res_sets[set][i];
+        uint8_t *D = s->dl_region[set] + bo.base[i];
+        const SvtMePackedLayout &L = bo.lay[i];
+        auto at = [&](int f) -> uint8_t * { return L.off[f] == (size_t)-1 ? nullptr : D + L.off[f]; }; // nullptr: not produced
         job.sb_state       = (SbState *)(R + s->lay.sb_state);
-        job.best_sad       = (uint32_t *)(R + s->lay.best_sad);
-        job.best_mv        = (uint32_t *)(R + s->lay.best_mv);
-        job.windows        = (SvtMeWindow *)(R + s->lay.windows);
-        job.search_results = (SvtMeSearchResult *)(R + s->lay.search_results);
-        job.total_me_candidate_index = R + s->lay.total;
-        job.me_mv_array              = (uint32_t *)(R + s->lay.mv);
-        job.me_candidate_array       = R + s->lay.cand;
-        job.me_64x64_distortion = (uint32_t *)(R + s->lay.d64);
-        job.me_32x32_distortion = (uint32_t *)(R + s->lay.d32);
-        job.me_16x16_distortion = (uint32_t *)(R + s->lay.d16);
-        job.me_8x8_distortion   = (uint32_t *)(R + s->lay.d8);
-        job.rc_me_distortion    = (uint32_t *)(R + s->lay.rc);
-        job.me_8x8_cost_variance = (uint32_t *)(R + s->lay.var);
-        job.stationary_block_present_sb = R + s->lay.stat;
-        job.rc_me_allow_gm              = R + s->lay.gm;
+        job.best_sad       = (uint32_t *)at(RF_BEST_SAD);
+        job.best_mv        = (uint32_t *)at(RF_BEST_MV);
+        job.windows        = (SvtMeWindow *)at(RF_WINDOWS);
+        job.search_results = (SvtMeSearchResult *)at(RF_SEARCH);
+        job.total_me_candidate_index = at(RF_TOTAL);
+        job.me_mv_array              = (uint32_t *)at(RF_MV);
+        job.me_candidate_array       = at(RF_CAND);
+        job.me_64x64_distortion = (uint32_t *)at(RF_D64);
+        job.me_32x32_distortion = (uint32_t *)at(RF_D32);
+        job.me_16x16_distortion = (uint32_t *)at(RF_D16);
+        job.me_8x8_distortion   = (uint32_t *)at(RF_D8);
+        job.rc_me_distortion    = (uint32_t *)at(RF_RC);
+        job.me_8x8_cost_variance = (uint32_t *)at(RF_VAR);
+        job.stationary_block_present_sb = at(RF_STAT);
+        job.rc_me_allow_gm              = at(RF_GM);
         job.hme_jobs     = (HmeJobG *)(R + s->lay.hme_jobs);
         job.fp_jobs      = (FpJobG *)(R + s->lay.fp_jobs);
         job.fp_keys      = (unsigned long long *)(R + s->lay.fp_keys);
@@ -684,7 +834,9 @@ static uint32_t launch_me_batch(SvtMeSession *s, uint32_t n, const int32_t *pic_
         job.s16_counters  = (uint32_t *)(s->res_sets[set][0] + s->lay.fp_counters) + 4;
         job.s16_units_cap = s->s16_units_cap;
     }
-    CU_TRY(cudaMemcpyAsync(d_jobs, s->h_jobs.data(), sizeof(PicJob) * n, cudaMemcpyHostToDevice, cs));
+    CU_TRY(cudaMemcpyAsync(d_jobs, h_jobs, sizeof(PicJob) * n, cudaMemcpyHostToDevice, cs));
+    CU_TRY(cudaEventRecord(s->ev_jobs[jslot], cs));
+    s->jobs_used[jslot] = true;
     cudaEvent_t e0 = nullptr, e1 = nullptr, e2 = nullptr;
     if (s->timing) {
         if (s->ev_used + 3 > s->ev.size()) {
@@ -703,88 +855,187 @@ static uint32_t launch_me_batch(SvtMeSession *s, uint32_t n, const int32_t *pic_
         e0 = s->ev[s->ev_used]; e1 = s->ev[s->ev_used + 1]; e2 = s->ev[s->ev_used + 2];
         s->ev_used += 3;
     }
-    s->launches += (uint64_t)svtme_launch_picture_me(s->h_jobs.data(), (int)n, d_jobs, cs, e0, e1, e2);
+    SvtMeTimeline *tl = nullptr;
+    if (s->timing) {
+        if (s->tls.size() >= 256) {
+            CU_TRY(cudaStreamSynchronize(s->stream));
+            fold_timelines(s);
+        }
+        s->tls.emplace_back();
+        tl = &s->tls.back();
+        tl->n = 0;
+        for (int i = 0; i < SVTME_TL_MAX; i++) {
+            if (!s->tl_pool.empty()) { tl->ev[i] = s->tl_pool.back(); s->tl_pool.pop_back(); }
+            else CU_TRY(cudaEventCreate(&tl->ev[i]));
+        }
+    }
+    s->launches += (uint64_t)svtme_launch_picture_me(h_jobs, (int)n, d_jobs, cs, e0, e1, e2, tl);
     CU_TRY(cudaGetLastError());
     CU_TRY(cudaEventRecord(s->ev_me[seq % 8], cs));
-    s->last_pps.assign(params, params + n);
-    s->have_results = true;
     return SVTME_OK;
 }
 
-static uint32_t fetch(SvtMeSession *s, uint32_t index, SvtMePicResults *res, int sync) {
-    if (!s->have_results || !res || index >= s->last_pps.size()) return SVTME_ERR_BAD_PARAMETER;
-    const SvtMePicParams &pp = s->last_pps[index];
-    const size_t n = (size_t)s->n_b64, n_pus = pp.enable_me_8x8 ? 85 : 21;
-    const int set = (int)(s->batch_seq & 1);
-    uint8_t *R = s->res_sets[set][index];
-    CU_TRY(cudaStreamWaitEvent(s->dl_stream, s->ev_me[s->batch_seq % 8], 0));
-#define D2H(dst, off, bytes)                                                                               \
-    if (res->dst) CU_TRY(cudaMemcpyAsync(res->dst, R + s->lay.off, (bytes), cudaMemcpyDeviceToHost, s->dl_stream))
-    D2H(p_sb_best_sad, best_sad, n * 8 * 85 * 4);
-    D2H(p_sb_best_mv, best_mv, n * 8 * 85 * 4);
-    D2H(search_results, search_results, n * 8 * sizeof(SvtMeSearchResult));
-    D2H(me_windows, windows, n * 8 * sizeof(SvtMeWindow));
-    D2H(total_me_candidate_index, total, n * n_pus);
-    D2H(me_mv_array, mv, n * n_pus * pp.max_refs * 4);
-    D2H(me_candidate_array, cand, n * n_pus * pp.max_cand);
-    D2H(me_64x64_distortion, d64, n * 4);
-    D2H(me_32x32_distortion, d32, n * 4);
-    D2H(me_16x16_distortion, d16, n * 4);
-    D2H(me_8x8_distortion, d8, n * 4);
-    D2H(rc_me_distortion, rc, n * 4);
-    D2H(me_8x8_cost_variance, var, n * 4);
-    D2H(stationary_block_present_sb, stat, n);
-    D2H(rc_me_allow_gm, gm, n);
-#undef D2H
+// the download stream waits for the kernels of the batch that owns `set`; afterwards: the set's overflow flag, the event
+static uint32_t begin_download(SvtMeSession *s, int set) {
+    CU_TRY(cudaStreamWaitEvent(s->dl_stream, s->ev_me[s->out[set].seq % 8], 0));
+    return SVTME_OK;
+}
+static uint32_t end_download(SvtMeSession *s, int set) {
+    CU_TRY(cudaMemcpyAsync(&s->h_flags[set], (uint32_t *)(s->res_sets[set][0] + s->lay.fp_counters) + 8, sizeof(uint32_t), cudaMemcpyDeviceToHost, s->dl_stream));
     CU_TRY(cudaEventRecord(s->ev_dl[set], s->dl_stream));
     s->dl_recorded[set] = true;
-    if (sync) CU_TRY(cudaStreamSynchronize(s->dl_stream));
+    return SVTME_OK;
+}
+static uint32_t finish_sync(SvtMeSession *s, int set, bool downloaded) {
+    if (downloaded) {
+        CU_TRY(cudaStreamSynchronize(s->dl_stream)); // the download waited for the batch's kernels
+        return check_downloaded_flag(s, set);
+    }
+    CU_TRY(cudaStreamSynchronize(compute_stream(s, set)));
+    return SVTME_OK;
+}
+
+// per-field copies of picture `index` of the batch that owns `set` into the caller's arrays (between begin_/end_download)
+static uint32_t fetch_fields(SvtMeSession *s, int set, uint32_t index, SvtMePicResults *res) {
+    const SvtMeSession::BatchOut &bo = s->out[set];
+    if (!bo.me || !res || index >= bo.lay.size()) return SVTME_ERR_BAD_PARAMETER;
+    const SvtMePackedLayout &L = bo.lay[index];
+    const uint8_t *D = s->dl_region[set] + bo.base[index];
+    const SvtMeSession::BatchOut::Geo &g = bo.geo[index];
+    for (int f = 0; f < RF_COUNT; f++)
+        if (*result_member(res, f) && L.off[f] == (size_t)-1) return SVTME_ERR_BAD_PARAMETER; // the batch was not asked to produce this field
+    for (int f = 0; f < RF_COUNT; f++) {
+        void *dst = *result_member(res, f);
+        if (dst) CU_TRY(cudaMemcpyAsync(dst, D + L.off[f], rf_bytes(f, (size_t)s->n_b64, g.n_pus, g.max_refs, g.max_cand), cudaMemcpyDeviceToHost, s->dl_stream));
+    }
     return SVTME_OK;
 }
 
 extern "C" uint32_t svtme_picture_me_batch(SvtMeSession *s, uint32_t n, const int32_t *pic_ids, const SvtMePicParams *params,
                                            SvtMePicResults *results, int sync) {
-    if (!s) return SVTME_ERR_BAD_PARAMETER;
+    if (!s || n == 0 || n > 4096) return SVTME_ERR_BAD_PARAMETER;
     std::lock_guard<std::mutex> g(s->mu);
-    uint32_t rc = launch_me_batch(s, n, pic_ids, params);
-    if (rc != SVTME_OK) return rc;
+    std::vector<uint32_t> fields(n, s->default_fields);
     if (results)
+        for (uint32_t i = 0; i < n; i++) fields[i] = fields_of_results(&results[i]);
+    uint32_t rc = launch_me_batch(s, n, pic_ids, params, fields.data());
+    if (rc != SVTME_OK) return rc;
+    const int set = (int)(s->batch_seq & 1);
+    if (results) {
+        rc = begin_download(s, set);
+        for (uint32_t i = 0; i < n && rc == SVTME_OK; i++) rc = fetch_fields(s, set, i, &results[i]);
+        if (rc != SVTME_OK) return rc;
+        rc = end_download(s, set);
+        if (rc != SVTME_OK) return rc;
+    }
+    return sync ? finish_sync(s, set, results != nullptr) : SVTME_OK;
+}
+
+extern "C" uint32_t svtme_picture_me_batch_packed(SvtMeSession *s, uint32_t n, const int32_t *pic_ids, const SvtMePicParams *params,
+                                                  uint32_t fields, void *host_slab, size_t host_slab_bytes, int sync) {
+    if (!s || n == 0 || n > 4096 || !host_slab || !fields || (fields & ~SVTME_F_ALL)) return SVTME_ERR_BAD_PARAMETER;
+    std::lock_guard<std::mutex> g(s->mu);
+    { // the slab must hold the batch before anything is queued
+        size_t total = 0;
+        SvtMePackedLayout L;
         for (uint32_t i = 0; i < n; i++) {
-            rc = fetch(s, i, &results[i], 0);
-            if (rc != SVTME_OK) return rc;
+            if (params[i].max_refs > 8 || params[i].max_cand > 32) return SVTME_ERR_BAD_PARAMETER;
+            packed_layout((size_t)s->n_b64, params[i].enable_me_8x8 ? 85 : 21, params[i].max_refs, params[i].max_cand, fields, &L);
+            total += L.bytes;
         }
-    if (sync) CU_TRY(cudaStreamSynchronize(results ? s->dl_stream : compute_stream(s, (int)(s->batch_seq & 1)))); // the download waits for the batch's kernels
-    return SVTME_OK;
+        if (total > host_slab_bytes) return SVTME_ERR_BAD_PARAMETER;
+    }
+    std::vector<uint32_t> f(n, fields);
+    uint32_t rc = launch_me_batch(s, n, pic_ids, params, f.data());
+    if (rc != SVTME_OK) return rc;
+    const int set = (int)(s->batch_seq & 1);
+    rc = begin_download(s, set);
+    if (rc != SVTME_OK) return rc;
+    CU_TRY(cudaMemcpyAsync(host_slab, s->dl_region[set], s->out[set].total, cudaMemcpyDeviceToHost, s->dl_stream)); // the whole batch: ONE copy
+    rc = end_download(s, set);
+    if (rc != SVTME_OK) return rc;
+    return sync ? finish_sync(s, set, true) : SVTME_OK;
 }
 
 extern "C" uint32_t svtme_fetch_results_batch(SvtMeSession *s, uint32_t index, SvtMePicResults *results, int sync) {
     if (!s) return SVTME_ERR_BAD_PARAMETER;
     std::lock_guard<std::mutex> g(s->mu);
     CU_TRY(cudaSetDevice(s->device));
-    return fetch(s, index, results, sync);
+    const int set = (int)(s->batch_seq & 1);
+    if (s->out[set].seq != s->batch_seq) return SVTME_ERR_BAD_PARAMETER;
+    uint32_t rc = begin_download(s, set);
+    if (rc == SVTME_OK) rc = fetch_fields(s, set, index, results);
+    if (rc == SVTME_OK) rc = end_download(s, set);
+    if (rc != SVTME_OK) return rc;
+    return sync ? finish_sync(s, set, true) : SVTME_OK;
 }
 
 extern "C" uint32_t svtme_picture_me_device(SvtMeSession *s, int32_t pic_id, const SvtMePicParams *params) {
     if (!s) return SVTME_ERR_BAD_PARAMETER;
     std::lock_guard<std::mutex> g(s->mu);
-    return launch_me_batch(s, 1, &pic_id, params);
+    return launch_me_batch(s, 1, &pic_id, params, &s->default_fields);
 }
 
 extern "C" uint32_t svtme_fetch_results(SvtMeSession *s, SvtMePicResults *results, int sync) {
-    if (!s) return SVTME_ERR_BAD_PARAMETER;
-    std::lock_guard<std::mutex> g(s->mu);
-    CU_TRY(cudaSetDevice(s->device));
-    return fetch(s, 0, results, sync);
+    return svtme_fetch_results_batch(s, 0, results, sync);
 }
 
 extern "C" uint32_t svtme_picture_me(SvtMeSession *s, int32_t pic_id, const SvtMePicParams *params, SvtMePicResults *results,
                                      int sync) {
-    if (!s) return SVTME_ERR_BAD_PARAMETER;
+    return svtme_picture_me_batch(s, 1, &pic_id, params, results, sync);
+}
+
+// ---- device-resident view ----------------------------------------------------
+extern "C" uint32_t svtme_picture_device_planes(SvtMeSession *s, int32_t pic_id, SvtMeDevicePlane planes[3]) {
+    if (!s || !planes || pic_id < 0 || pic_id >= s->max_pics) return SVTME_ERR_BAD_PARAMETER;
     std::lock_guard<std::mutex> g(s->mu);
-    uint32_t rc = launch_me_batch(s, 1, &pic_id, params);
-    if (rc != SVTME_OK) return rc;
-    if (results) return fetch(s, 0, results, sync);
-    if (sync) CU_TRY(cudaStreamSynchronize(compute_stream(s, (int)(s->batch_seq & 1))));
+    if (!s->pic_valid[pic_id]) return SVTME_ERR_BAD_PARAMETER;
+    for (int i = 0; i < 3; i++) {
+        const DevPlane &p = s->pics[pic_id].lvl[i];
+        planes[i].origin = p.buf + (size_t)p.org_y * p.stride + p.org_x;
+        planes[i].stride = (uint32_t)p.stride; planes[i].width = (uint32_t)p.width; planes[i].height = (uint32_t)p.height;
+        planes[i].pad = (uint32_t)p.org_x;
+    }
+    return SVTME_OK;
+}
+
+extern "C" uint32_t svtme_batch_results_acquire(SvtMeSession *s, uint64_t seq, uint32_t index, SvtMePicResults *device_ptrs,
+                                                void *consumer_stream) {
+    if (!s || !device_ptrs || seq == 0) return SVTME_ERR_BAD_PARAMETER;
+    std::lock_guard<std::mutex> g(s->mu);
+    CU_TRY(cudaSetDevice(s->device));
+    const int set = (int)(seq & 1);
+    const SvtMeSession::BatchOut &bo = s->out[set];
+    if (bo.seq != seq || !bo.me || index >= bo.lay.size()) return SVTME_ERR_BAD_PARAMETER; // a later batch owns the set by now
+    svtme_packed_view(&bo.lay[index], s->dl_region[set] + bo.base[index], device_ptrs);
+    CU_TRY(cudaStreamWaitEvent((cudaStream_t)consumer_stream, s->ev_me[seq % 8], 0));
+    return SVTME_OK;
+}
+
+extern "C" uint32_t svtme_batch_results_release(SvtMeSession *s, uint64_t seq, void *consumer_stream) {
+    if (!s || seq == 0) return SVTME_ERR_BAD_PARAMETER;
+    std::lock_guard<std::mutex> g(s->mu);
+    CU_TRY(cudaSetDevice(s->device));
+    const int set = (int)(seq & 1);
+    if (s->out[set].seq != seq) return SVTME_ERR_BAD_PARAMETER;
+    CU_TRY(cudaEventRecord(s->ev_release[set], (cudaStream_t)consumer_stream));
+    s->release_recorded[set] = true;
+    return SVTME_OK;
+}
+
+extern "C" void *svtme_host_alloc(size_t bytes) {
+    void *p = nullptr;
+    if (cudaMallocHost(&p, bytes ? bytes : 1) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    return p;
+}
+extern "C" void svtme_host_free(void *p) {
+    if (p) cudaFreeHost(p);
+}
+
+extern "C" uint32_t svtme_copy_from_device(SvtMeSession *s, void *dst_host, const void *src_device, size_t bytes) {
+    if (!s || !dst_host || !src_device) return SVTME_ERR_BAD_PARAMETER;
+    CU_TRY(cudaSetDevice(s->device));
+    CU_TRY(cudaMemcpy(dst_host, src_device, bytes, cudaMemcpyDeviceToHost));
     return SVTME_OK;
 }
 
@@ -816,9 +1067,14 @@ extern "C" uint32_t svtme_dg_detector_hme(SvtMeSession *s, int32_t src_pic_id, i
         const int other = 1 - stream_index(s, set);
         if (s->built_recorded[other]) CU_TRY(cudaStreamWaitEvent(cs, s->ev_built[other], 0));
     }
+    if (s->release_recorded[set]) { CU_TRY(cudaStreamWaitEvent(cs, s->ev_release[set], 0)); s->release_recorded[set] = false; }
+    s->out[set].seq = seq; s->out[set].me = false; // the set no longer holds ME results
     PicJob *d_job = s->d_jobs + (size_t)set * s->d_jobs_n;
-    s->h_jobs.resize(1);
-    PicJob &job = s->h_jobs[0];
+    PicJob *h_job = nullptr;
+    int jslot = 0;
+    rc = next_job_array(s, &h_job, &jslot);
+    if (rc != SVTME_OK) return rc;
+    PicJob &job = *h_job;
     memset(&job, 0, sizeof(job));
     job.pp.ctrls.hme_search_method = SVTME_FULL_SAD_SEARCH; // :501
     job.src = s->pics[src_pic_id];
@@ -832,13 +1088,14 @@ extern "C" uint32_t svtme_dg_detector_hme(SvtMeSession *s, int32_t src_pic_id, i
     job.fp_counters   = (uint32_t *)(R + s->lay.fp_counters);
     job.s16_units_cap = s->s16_units_cap;
     CU_TRY(cudaMemcpyAsync(d_job, &job, sizeof(PicJob), cudaMemcpyHostToDevice, cs));
+    CU_TRY(cudaEventRecord(s->ev_jobs[jslot], cs));
+    s->jobs_used[jslot] = true;
     uint8_t *d_out = R + s->lay.ops + 32;
-    unsigned long long *d_sad = (unsigned long long *)(R + s->lay.best_sad);
-    int16_t *d_mv = (int16_t *)(R + s->lay.best_mv);
+    unsigned long long *d_sad = (unsigned long long *)(R + s->lay.dg_sad);
+    int16_t *d_mv = (int16_t *)(R + s->lay.dg_mv);
     s->launches += (uint64_t)svtme_launch_dg_detector(&job, d_job, sa0, d_out, d_sad, d_mv, cs);
     CU_TRY(cudaGetLastError());
     CU_TRY(cudaEventRecord(s->ev_me[seq % 8], cs));
-    s->have_results = false; // the slab no longer holds ME results
     struct { unsigned long long tot_dist; unsigned int tot_cplx, tot_active; int sum_in_vectors; } out;
     CU_TRY(cudaMemcpyAsync(&out, d_out, sizeof(out), cudaMemcpyDeviceToHost, cs));
     if (b64_sad) CU_TRY(cudaMemcpyAsync(b64_sad, d_sad, (size_t)s->n_b64 * 8, cudaMemcpyDeviceToHost, cs));
@@ -869,6 +1126,35 @@ extern "C" uint32_t svtme_session_kernel_time(SvtMeSession *s, int reset, double
     return SVTME_OK;
 }
 
+static const char *const tl_names[SVTME_TL_TAGS] = {"", "k_zz", "k_hme_ctl", "k_search16 (pre-HME)", "k_search16 (HME level 0)", "k_search_blk (HME level 1)",
+                                                    "k_search_blk (HME level 2)", "k_fp", "k_fp_big", "k_post"};
+extern "C" const char *svtme_kernel_name(int tag) { return tag > 0 && tag < SVTME_TL_TAGS ? tl_names[tag] : nullptr; }
+
+extern "C" uint32_t svtme_session_kernel_times(SvtMeSession *s, int reset, double *ms, int n_ms) {
+    if (!s || !ms || n_ms < 0) return SVTME_ERR_BAD_PARAMETER;
+    std::lock_guard<std::mutex> g(s->mu);
+    CU_TRY(cudaSetDevice(s->device));
+    CU_TRY(cudaStreamSynchronize(s->stream));
+    fold_timelines(s);
+    for (int i = 0; i < n_ms; i++) ms[i] = i < SVTME_TL_TAGS ? s->acc_tag_ms[i] : 0.0;
+    if (reset)
+        for (auto &v : s->acc_tag_ms) v = 0;
+    return SVTME_OK;
+}
+
+extern "C" uint32_t svtme_session_sad_ops_by_stage(SvtMeSession *s, int reset, uint64_t ops[6]) {
+    if (!s || !ops) return SVTME_ERR_BAD_PARAMETER;
+    std::lock_guard<std::mutex> g(s->mu);
+    CU_TRY(cudaSetDevice(s->device));
+    unsigned long long v[6] = {0, 0, 0, 0, 0, 0};
+    CU_TRY(cudaStreamSynchronize(s->stream2));
+    CU_TRY(cudaMemcpyAsync(v, s->res_slab + s->lay.ops, sizeof(v), cudaMemcpyDeviceToHost, s->stream));
+    CU_TRY(cudaStreamSynchronize(s->stream));
+    for (int i = 0; i < 6; i++) ops[i] = v[i];
+    if (reset) CU_TRY(cudaMemsetAsync(s->res_slab + s->lay.ops, 0, sizeof(v), s->stream));
+    return SVTME_OK;
+}
+
 extern "C" uint32_t svtme_fetch_hme_state(SvtMeSession *s, void *dst, size_t dst_bytes) {
     if (!s || !dst || dst_bytes < (size_t)s->n_b64 * sizeof(SbState)) return SVTME_ERR_BAD_PARAMETER;
     std::lock_guard<std::mutex> g(s->mu);
@@ -889,7 +1175,7 @@ extern "C" uint32_t svtme_session_sad_ops(SvtMeSession *s, int reset, uint64_t *
     CU_TRY(cudaStreamSynchronize(s->stream));
     if (hme_ops) *hme_ops = v[0];
     if (fullpel_ops) *fullpel_ops = v[1];
-    if (reset) CU_TRY(cudaMemsetAsync(s->res_slab + s->lay.ops, 0, sizeof(v), s->stream));
+    if (reset) CU_TRY(cudaMemsetAsync(s->res_slab + s->lay.ops, 0, 6 * sizeof(unsigned long long), s->stream));
     return SVTME_OK;
 }
 

@@ -439,7 +439,10 @@ __global__ void __launch_bounds__(32 * CTL_WARPS) k_hme_ctl(const PicJob *__rest
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) ops += __shfl_xor_sync(0xffffffffu, ops, o);
-    if (lane == 0 && ops && job.sad_ops) atomicAdd(&job.sad_ops[0], ops);
+    if (lane == 0 && ops && job.sad_ops) {
+        atomicAdd(&job.sad_ops[0], ops);
+        if (op.build_stage >= 0) atomicAdd(&job.sad_ops[2 + op.build_stage], ops); // [2] pre-HME, [3..5] HME level 0..2 (ops are counted when a stage is built)
+    }
     __syncwarp();
     for (int i = lane; i < (int)(sizeof(SbState) / 4); i += 32) gw[i] = sw[i];
 }

@@ -102,7 +102,7 @@ struct PicJob {
     uint32_t      *me_64x64_distortion, *me_32x32_distortion, *me_16x16_distortion, *me_8x8_distortion;
     uint32_t      *rc_me_distortion, *me_8x8_cost_variance;
     uint8_t       *stationary_block_present_sb, *rc_me_allow_gm;
-    unsigned long long *sad_ops; // [0] HME stage, [1] full-pel stage: algorithmic |a-b| operations
+    unsigned long long *sad_ops; // [0] HME stage, [1] full-pel stage, [2] pre-HME, [3..5] HME level 0..2: algorithmic |a-b| operations
     // v2 pipeline scratch
     HmeJobG            *hme_jobs;  // [n_b64][HME_JOBS_PER_B64]
     FpJobG             *fp_jobs;   // [n_b64][8]

@@ -168,7 +168,7 @@ __global__ void __launch_bounds__(32 * FP_WARPS) k_fp(const PicJob *__restrict__
     const SbState &st = job.sb_state[b];
     unsigned long long *gk = job.fp_keys + (size_t)u * 85;
     if (!st.do_ref[l][r] || st.tf_exit) { // :1294-1295; temporal filter: HME was good enough (:3179-3183)
-        if (lane == 0) { fj.active = 0; job.windows[u] = SvtMeWindow{0, 0, 0, 0}; }
+        if (lane == 0) { fj.active = 0; if (job.windows) job.windows[u] = SvtMeWindow{0, 0, 0, 0}; }
         return;
     }
     const B64Geo    g   = b64_geo(job, b);
@@ -307,7 +307,7 @@ __global__ void __launch_bounds__(32 * FP_WARPS) k_fp(const PicJob *__restrict__
         const int n_units = inline_scan ? 0 : n_tiles;
         fj.xc = xc; fj.yc = yc; fj.x_origin = x_origin; fj.y_origin = y_origin; fj.sa_w = sa_w; fj.sa_h = sa_h;
         fj.n_tx = (uint16_t)ntx; fj.n_ty = (uint16_t)nty; fj.active = 1; fj.probe = probe ? 1 : 0;
-        job.windows[u] = SvtMeWindow{x_origin, y_origin, sa_w, sa_h};
+        if (job.windows) job.windows[u] = SvtMeWindow{x_origin, y_origin, sa_w, sa_h};
         if (n_units) {
             const uint32_t base = atomicAdd(&job.fp_counters[0], (uint32_t)n_units);
             for (int i = 0; i < n_units && base + i < job.fp_units_cap; i++)

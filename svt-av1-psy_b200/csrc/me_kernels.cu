@@ -340,7 +340,13 @@ uint32_t svtme_fp_units_cap(const SvtMePicParams &pp, int n_b64) {
 // is the union of what the pictures need (an extra round is a no-op for pictures without the
 // dependency it serves).
 int svtme_launch_picture_me(const PicJob *h_jobs, int n, const PicJob *d_jobs, cudaStream_t st, cudaEvent_t ev_hme0,
-                            cudaEvent_t ev_hme1, cudaEvent_t ev_fp1) {
+                            cudaEvent_t ev_hme1, cudaEvent_t ev_fp1, SvtMeTimeline *tl) {
+    // per-kernel timing (svtme_session_enable_timing): an event behind every launch, tagged with the kernel it closes
+    auto mark = [&](int tag) {
+        if (!tl || tl->n >= SVTME_TL_MAX) return;
+        cudaEventRecord(tl->ev[tl->n], st);
+        tl->tag[tl->n++] = tag;
+    };
     const PicJob         &j0 = h_jobs[0];
     const SvtMeCtrls     &c  = j0.pp.ctrls; // HME flags / search methods are equal across a batch (validated by the caller)
     int launches = 0;
@@ -363,9 +369,11 @@ int svtme_launch_picture_me(const PicJob *h_jobs, int n, const PicJob *d_jobs, c
     opt_in_shared_memory();
     if (ev_hme0) cudaEventRecord(ev_hme0, st);
     cudaMemsetAsync(j0.fp_counters, 0, 2 * sizeof(uint32_t), st);
+    mark(SVTME_TL_START);
     if (any_zz) {
         k_zz<<<dim3((n_b64 * max_act + SEARCH_WARPS - 1) / SEARCH_WARPS, ny), 32 * SEARCH_WARPS, 0, st>>>(d_jobs);
         launches++;
+        mark(SVTME_TL_ZZ);
     }
     bool first = true;
     int  post = ST_NONE;
@@ -376,6 +384,7 @@ int svtme_launch_picture_me(const PicJob *h_jobs, int n, const PicJob *d_jobs, c
         if (build == ST_PREHME || build == ST_L0) cudaMemsetAsync(j0.s16_counters, 0, 2 * sizeof(uint32_t), st);
         k_hme_ctl<<<dim3(ctl_grid, ny), 32 * CTL_WARPS, 0, st>>>(d_jobs, op);
         launches++;
+        mark(SVTME_TL_CTL);
         first = false;
         post  = ST_NONE;
     };
@@ -391,9 +400,10 @@ int svtme_launch_picture_me(const PicJob *h_jobs, int n, const PicJob *d_jobs, c
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&k, k_search16, 32 * SEARCH_WARPS, s16_smem);
         g_s16_ctas_per_sm = k > 0 ? k : 1;
     }
-    auto search16 = [&](int skip) {
+    auto search16 = [&](int skip, int tag) {
         k_search16<<<n_sm * g_s16_ctas_per_sm, 32 * SEARCH_WARPS, s16_smem, st>>>(d_jobs, skip);
         launches++;
+        mark(tag);
     };
     auto search_wide = [&](int level) {
         const dim3 grid((n_b64 * max_act + SEARCH_WARPS - 1) / SEARCH_WARPS, ny);
@@ -406,19 +416,20 @@ int svtme_launch_picture_me(const PicJob *h_jobs, int n, const PicJob *d_jobs, c
             else k_search_blk<false, 2><<<grid, 32 * SEARCH_WARPS, smem, st>>>(d_jobs);
         }
         launches++;
+        mark(level == 1 ? SVTME_TL_BLK_L1 : SVTME_TL_BLK_L2);
     };
     int fin_pending = ST_NONE;
     if (c.prehme_enable) {
         if (any_l1dep) {
             emit(ST_NONE, ST_PREHME, LIST0);
-            search16(c.prehme_skip_search_line);
+            search16(c.prehme_skip_search_line, SVTME_TL_S16_PREHME);
             post = ST_PREHME; pmask = LIST0;
             emit(ST_NONE, ST_PREHME, LIST1);
-            search16(c.prehme_skip_search_line);
+            search16(c.prehme_skip_search_line, SVTME_TL_S16_PREHME);
             post = ST_PREHME; pmask = LIST1;
         } else {
             emit(ST_NONE, ST_PREHME, ALL);
-            search16(c.prehme_skip_search_line);
+            search16(c.prehme_skip_search_line, SVTME_TL_S16_PREHME);
             post = ST_PREHME; pmask = ALL;
         }
         fin_pending = ST_PREHME;
@@ -427,14 +438,14 @@ int svtme_launch_picture_me(const PicJob *h_jobs, int n, const PicJob *d_jobs, c
         if (c.enable_hme_level0_flag) {
             if (any_dep) {
                 emit(fin_pending, ST_L0, 0x01u);
-                search16(0);
+                search16(0, SVTME_TL_S16_L0);
                 post = ST_L0; pmask = 0x01u;
                 emit(ST_NONE, ST_L0, ALL & ~0x01u);
-                search16(0);
+                search16(0, SVTME_TL_S16_L0);
                 post = ST_L0; pmask = ALL & ~0x01u;
             } else {
                 emit(fin_pending, ST_L0, ALL);
-                search16(0);
+                search16(0, SVTME_TL_S16_L0);
                 post = ST_L0; pmask = ALL;
             }
             fin_pending = ST_NONE;
@@ -467,13 +478,12 @@ int svtme_launch_picture_me(const PicJob *h_jobs, int n, const PicJob *d_jobs, c
     const dim3 plan_grid((n_b64 * max_act + FP_WARPS - 1) / FP_WARPS, ny);
     const int big_grid = n_sm * g_fp_search_ctas_per_sm;
     auto fp_round = [&](int phase) {
-        if (fsub) {
-            k_fp<true><<<plan_grid, 32 * FP_WARPS, fp_smem, st>>>(d_jobs, phase);
-            k_fp_big<true><<<big_grid, 32 * FP_WARPS, fp_smem, st>>>(d_jobs);
-        } else {
-            k_fp<false><<<plan_grid, 32 * FP_WARPS, fp_smem, st>>>(d_jobs, phase);
-            k_fp_big<false><<<big_grid, 32 * FP_WARPS, fp_smem, st>>>(d_jobs);
-        }
+        if (fsub) k_fp<true><<<plan_grid, 32 * FP_WARPS, fp_smem, st>>>(d_jobs, phase);
+        else k_fp<false><<<plan_grid, 32 * FP_WARPS, fp_smem, st>>>(d_jobs, phase);
+        mark(SVTME_TL_FP);
+        if (fsub) k_fp_big<true><<<big_grid, 32 * FP_WARPS, fp_smem, st>>>(d_jobs);
+        else k_fp_big<false><<<big_grid, 32 * FP_WARPS, fp_smem, st>>>(d_jobs);
+        mark(SVTME_TL_FP_BIG);
         launches += 2;
     };
     if (any_sr2) {
@@ -486,6 +496,7 @@ int svtme_launch_picture_me(const PicJob *h_jobs, int n, const PicJob *d_jobs, c
     }
     if (ev_fp1) cudaEventRecord(ev_fp1, st);
     k_post<<<dim3(n_b64, ny), POST_THREADS, 0, st>>>(d_jobs);
+    mark(SVTME_TL_POST);
     launches += 1;
     return launches;
 }

@@ -18,8 +18,17 @@ int  svtme_launch_dg_detector(const PicJob *h_job, const PicJob *d_job, int sa0,
                               int16_t *d_b64_mv, cudaStream_t st);
 uint32_t svtme_fp_units_cap(const SvtMePicParams &pp, int n_b64);
 uint32_t svtme_s16_units_cap(const SvtMePicParams &pp, int n_b64);
+// per-kernel timeline of one launch sequence: event i was recorded behind the launch tagged tag[i]
+enum { SVTME_TL_START = 0, SVTME_TL_ZZ, SVTME_TL_CTL, SVTME_TL_S16_PREHME, SVTME_TL_S16_L0, SVTME_TL_BLK_L1, SVTME_TL_BLK_L2, SVTME_TL_FP,
+       SVTME_TL_FP_BIG, SVTME_TL_POST, SVTME_TL_TAGS };
+#define SVTME_TL_MAX 32
+struct SvtMeTimeline {
+    cudaEvent_t ev[SVTME_TL_MAX];
+    int         tag[SVTME_TL_MAX];
+    int         n;
+};
 int  svtme_launch_picture_me(const PicJob *h_jobs, int n, const PicJob *d_jobs, cudaStream_t st, cudaEvent_t ev_hme0,
-                             cudaEvent_t ev_hme1, cudaEvent_t ev_fp1);
+                             cudaEvent_t ev_hme1, cudaEvent_t ev_fp1, SvtMeTimeline *tl);
 int  svtme_launch_kat_sad_loop(const uint8_t *d_src, int src_stride, const uint8_t *d_ref, int ref_stride, int bh, int bw,
                                int src_stride_raw, int skip, int sa_w, int sa_h, unsigned long long *d_key, uint8_t *d_pitched,
                                size_t pitched_cap, cudaStream_t st);

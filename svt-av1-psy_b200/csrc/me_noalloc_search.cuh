@@ -26,12 +26,42 @@ struct HmeSh {
 
 // Stage the b64's source block of one pyramid level into shared memory: n_rows rows of
 // `words` 32-bit words, row r taken from src + r*row_step*stride; bytes >= bw are zeroed.
+// The caller's buffers may end flush with their allocation, so only the bytes svt_sad_loop_kernel itself would read are
+// touched: bw bytes per source row, sa_w + bw - 1 bytes per reference row.
 __device__ inline void hme_stage_src(uint32_t *dst, int words, const uint8_t *src, int stride, int row_step, int n_rows,
                                      int bw, int tid) {
     for (int i = tid; i < n_rows * words; i += HME_THREADS) {
         const int r = i / words, k = i - r * words;
-        uint32_t  v = ldg_u32_unaligned(src + (size_t)r * row_step * stride + 4 * k);
-        dst[i]      = v & lo_bytes_mask(bw - 4 * k);
+        const uint8_t *p = src + (size_t)r * row_step * stride + 4 * k;
+        uint32_t v = 0;
+        for (int b = 0; b < 4 && 4 * k + b < bw; b++) v |= (uint32_t)__ldg(p + b) << (8 * b);
+        dst[i] = v;
+    }
+}
+
+// smem word (r, c) = bytes [4c, 4c + 4) of row r of the rectangle at g (row pitch gstride), bytes at or beyond `need`
+// read as zero and are not loaded. Whole aligned words are used where both aligned words under a staged word lie inside
+// the row's needed bytes, single bytes at the two ends of a row.
+__device__ inline void stage_rect_exact(uint32_t *smem, int smem_stride_words, const uint8_t *g, int gstride, int rows,
+                                        int words_per_row, int need, int tid, int nthreads) {
+    const int total = rows * words_per_row;
+    for (int i = tid; i < total; i += nthreads) {
+        const int r = i / words_per_row, c = i - r * words_per_row;
+        const uint8_t *row = g + (size_t)r * gstride, *p = row + 4 * c;
+        const int n = need - 4 * c; // bytes of this word that exist
+        uint32_t v = 0;
+        if (n > 0) {
+            const uintptr_t a = (uintptr_t)p, lo = a & ~(uintptr_t)3;
+            if (n >= 4 && lo >= (uintptr_t)row && lo + 8 <= (uintptr_t)row + (uintptr_t)need) {
+                const uint32_t *q = (const uint32_t *)lo;
+                v = __funnelshift_r(__ldg(q), __ldg(q + 1), (uint32_t)(a & 3) * 8);
+            } else if (n >= 4 && (a & 3) == 0) {
+                v = __ldg((const uint32_t *)p);
+            } else {
+                for (int b = 0; b < 4 && b < n; b++) v |= (uint32_t)__ldg(p + b) << (8 * b);
+            }
+        }
+        smem[r * smem_stride_words + c] = v;
     }
 }
 
@@ -63,7 +93,7 @@ __device__ inline void hme_search_staged(HmeSh &sh, const HmeJob &j, int job_ind
     for (int y0 = 0; y0 < j.sa_h; y0 += tile_h) {
         const int th = imin(tile_h, j.sa_h - y0);
         __syncthreads(); // previous tile fully consumed
-        stage_rect(win, stride, j.ref + (size_t)y0 * j.ref_stride, j.ref_stride, th + span, stride, tid, HME_THREADS);
+        stage_rect_exact(win, stride, j.ref + (size_t)y0 * j.ref_stride, j.ref_stride, th + span, stride, j.sa_w + bw - 1, tid, HME_THREADS);
         __syncthreads();
         const int n_task = n_oct * th;
         for (int t = tid; t < n_task; t += HME_THREADS) {

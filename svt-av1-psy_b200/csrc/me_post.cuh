@@ -23,7 +23,23 @@ struct PostSh {
     uint8_t  do_ref[2][4];
     uint32_t me_distortion[85];
     uint32_t best_sad[8 * 85], best_mv[8 * 85]; // this b64's p_sb_best_sad / p_sb_best_mv: built here, read by every later step
+    // this b64's MeSbResults arrays (me_sb_results.h:44-51), built here and written to HBM once, as whole words
+    uint32_t mv[85 * 8];
+    uint8_t  cand[85 * 32];
+    uint8_t  total[88];
 };
+
+// n bytes from shared memory to global memory at any alignment: whole aligned words where the destination has them
+__device__ __forceinline__ void post_store_bytes(uint8_t *dst, const uint8_t *src, uint32_t n, int tid) {
+    const uint32_t head = (uint32_t)((4u - ((uintptr_t)dst & 3u)) & 3u);
+    const uint32_t h = head < n ? head : n, n_words = (n - h) >> 2, tail = h + 4u * n_words;
+    for (uint32_t i = tid; i < n_words; i += POST_THREADS) {
+        const uint8_t *q = src + h + 4u * i;
+        *(uint32_t *)(dst + h + 4u * i) = (uint32_t)q[0] | ((uint32_t)q[1] << 8) | ((uint32_t)q[2] << 16) | ((uint32_t)q[3] << 24);
+    }
+    if ((uint32_t)tid < h) dst[tid] = src[tid];
+    if ((uint32_t)tid < n - tail) dst[tail + tid] = src[tail + tid];
+}
 
 __global__ void __launch_bounds__(POST_THREADS) k_post(const PicJob *__restrict__ jobs) {
     const PicJob &job = jobs[blockIdx.y];
@@ -32,8 +48,9 @@ __global__ void __launch_bounds__(POST_THREADS) k_post(const PicJob *__restrict_
     const SvtMeCtrls     &c   = pp.ctrls;
     const int             tid = threadIdx.x, b = blockIdx.x;
     const SbState        &st  = job.sb_state[b];
-    uint32_t *gbs = job.best_sad + (size_t)b * 2 * 4 * 85;
-    uint32_t *gbm = job.best_mv + (size_t)b * 2 * 4 * 85;
+    // result arrays the caller did not ask for are NULL (svtme_picture_me_batch_packed / SvtMePicResults members): nothing is written
+    uint32_t *gbs = job.best_sad ? job.best_sad + (size_t)b * 2 * 4 * 85 : nullptr;
+    uint32_t *gbm = job.best_mv ? job.best_mv + (size_t)b * 2 * 4 * 85 : nullptr;
 #define BS(l, r, n) sh.best_sad[((l) * 4 + (r)) * 85 + (n)]
 #define BM(l, r, n) sh.best_mv[((l) * 4 + (r)) * 85 + (n)]
     const uint8_t *nref = pp.num_of_ref_pic_to_search;
@@ -46,11 +63,10 @@ __global__ void __launch_bounds__(POST_THREADS) k_post(const PicJob *__restrict_
         for (int i = tid; i < 8 * 85; i += POST_THREADS) {
             const int lr = i / 85, pu = i - lr * 85;
             const bool have = job.fp_keys && (lr >> 2) < n_lists_cfg && (lr & 3) < nref[lr >> 2] && job.fp_jobs[(size_t)b * 8 + lr].active;
-            uint32_t sad, mv;
-            if (!have) { // a slot the picture does not have, or not searched: the mirrors keep stale data, as in the reference
-                sad = gbs[i];
-                mv  = gbm[i];
-            } else {
+            uint32_t sad = 0, mv = 0;
+            // !have: a slot the picture does not have, or a reference that was not searched (do_ref == 0 before the full-pel
+            // stage): stale in the reference, never consumed (a reference is only used while its do_ref is set), zero here
+            if (have) {
                 const FpJobG &fj = job.fp_jobs[(size_t)b * 8 + lr];
                 const unsigned long long k = job.fp_keys[((size_t)b * 8 + lr) * 85 + pu];
                 sad = MAX_SAD_VALUE_U32; // initial bests, :1368 and :3119
@@ -78,6 +94,7 @@ __global__ void __launch_bounds__(POST_THREADS) k_post(const PicJob *__restrict_
     // (their content is stale in the reference), so that dumps are deterministic; everything
     // else is written as built. Called by all threads once sh.do_ref is final and nobody reads the mirrors any more.
     auto write_mirrors = [&]() {
+        if (!gbs) return;
         for (int i = tid; i < 8 * 85; i += POST_THREADS) {
             const int lr = i / 85, l = lr >> 2, r = lr & 3;
             const bool keep = l < n_lists_cfg && r < nref[l] && sh.do_ref[l][r] && !st.tf_exit;
@@ -117,33 +134,50 @@ __global__ void __launch_bounds__(POST_THREADS) k_post(const PicJob *__restrict_
 
     // ---- candidate construction: thread n = ME z-order PU index ----
     const uint32_t n_pus  = (uint32_t)job.n_pus;
-    uint8_t  *o_total = job.total_me_candidate_index + (size_t)b * n_pus;
-    uint32_t *o_mv    = job.me_mv_array + (size_t)b * n_pus * pp.max_refs;
-    uint8_t  *o_cand  = job.me_candidate_array + (size_t)b * n_pus * pp.max_cand;
+    const bool want_sb = job.total_me_candidate_index != nullptr, want_stats = job.me_64x64_distortion != nullptr;
+    uint8_t  *o_total = sh.total; // built in shared memory, stored at the end
+    uint32_t *o_mv    = sh.mv;
+    uint8_t  *o_cand  = sh.cand;
+    auto write_sb_results = [&]() {
+        if (!want_sb) return;
+        post_store_bytes(job.total_me_candidate_index + (size_t)b * n_pus, sh.total, n_pus, tid);
+        uint32_t *g_mv = job.me_mv_array + (size_t)b * n_pus * pp.max_refs;
+        for (uint32_t i = tid; i < n_pus * pp.max_refs; i += POST_THREADS) g_mv[i] = sh.mv[i];
+        post_store_bytes(job.me_candidate_array + (size_t)b * n_pus * pp.max_cand, sh.cand, n_pus * pp.max_cand, tid);
+    };
+    auto write_search_results = [&]() {
+        if (tid >= 8) return;
+        const int l = tid >> 2, r = tid & 3;
+        SvtMeSearchResult sr;
+        sr.hme_sc_x = 0; sr.hme_sc_y = 0; sr.do_ref = 0; sr.pad_[0] = sr.pad_[1] = sr.pad_[2] = 0; sr.hme_sad = 0;
+        if (l < n_lists_cfg && r < nref[l]) {
+            sr.hme_sc_x = st.hme_sc_x[l][r];
+            sr.hme_sc_y = st.hme_sc_y[l][r];
+            sr.do_ref   = sh.do_ref[l][r];
+            sr.hme_sad  = sh.hme_sad[l][r];
+        } else if (job.windows) {
+            job.windows[(size_t)b * 8 + tid] = SvtMeWindow{0, 0, 0, 0};
+        }
+        if (job.search_results) job.search_results[(size_t)b * 8 + tid] = sr;
+    };
     if (mctf) { // the temporal filter consumes p_sb_best_sad / p_sb_best_mv and SearchResults only
         for (uint32_t i = tid; i < n_pus; i += POST_THREADS) o_total[i] = 0;
         for (uint32_t i = tid; i < n_pus * pp.max_refs; i += POST_THREADS) o_mv[i] = 0;
         for (uint32_t i = tid; i < n_pus * pp.max_cand; i += POST_THREADS) o_cand[i] = 0;
-        if (tid == 0) {
+        if (tid == 0 && want_stats) {
             job.me_64x64_distortion[b] = job.me_32x32_distortion[b] = job.me_16x16_distortion[b] = job.me_8x8_distortion[b] = 0;
             job.rc_me_distortion[b] = job.me_8x8_cost_variance[b] = 0;
             job.stationary_block_present_sb[b] = 0;
             job.rc_me_allow_gm[b]              = 0;
         }
-        if (tid < 8) {
-            const int l = tid >> 2, r = tid & 3;
-            SvtMeSearchResult sr;
-            sr.hme_sc_x = 0; sr.hme_sc_y = 0; sr.do_ref = 0; sr.pad_[0] = sr.pad_[1] = sr.pad_[2] = 0; sr.hme_sad = 0;
-            if (l < n_lists_cfg && r < nref[l]) {
-                sr.hme_sc_x = st.hme_sc_x[l][r];
-                sr.hme_sc_y = st.hme_sc_y[l][r];
-                sr.do_ref   = sh.do_ref[l][r];
-                sr.hme_sad  = sh.hme_sad[l][r];
-            } else {
-                job.windows[(size_t)b * 8 + tid] = SvtMeWindow{0, 0, 0, 0};
-            }
-            job.search_results[(size_t)b * 8 + tid] = sr;
-        }
+        __syncthreads();
+        write_sb_results();
+        write_search_results();
+        write_mirrors();
+        return;
+    }
+    if (!want_sb && !want_stats) { // only the MeContext members were asked for
+        write_search_results();
         write_mirrors();
         return;
     }
@@ -264,7 +298,7 @@ __global__ void __launch_bounds__(POST_THREADS) k_post(const PicJob *__restrict_
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) sumsq += __shfl_xor_sync(0xffffffffu, sumsq, o);
     }
-    if (tid == 0) {
+    if (tid == 0 && want_stats) {
         const int org_x = (b % job.b64_cols) * 64, org_y = (b / job.b64_cols) * 64;
         const uint32_t gw = (uint32_t)imin(64, job.pic_w - org_x), gh = (uint32_t)imin(64, job.pic_h - org_y);
         const uint32_t d64 = sh.me_distortion[0];
@@ -316,20 +350,8 @@ __global__ void __launch_bounds__(POST_THREADS) k_post(const PicJob *__restrict_
         job.stationary_block_present_sb[b] = stationary;
         job.rc_me_allow_gm[b]              = allow_gm;
     }
-    if (tid < 8) {
-        const int l = tid >> 2, r = tid & 3;
-        SvtMeSearchResult sr;
-        sr.hme_sc_x = 0; sr.hme_sc_y = 0; sr.do_ref = 0; sr.pad_[0] = sr.pad_[1] = sr.pad_[2] = 0; sr.hme_sad = 0;
-        if (l < n_lists_cfg && r < nref[l]) {
-            sr.hme_sc_x = st.hme_sc_x[l][r];
-            sr.hme_sc_y = st.hme_sc_y[l][r];
-            sr.do_ref   = sh.do_ref[l][r];
-            sr.hme_sad  = sh.hme_sad[l][r];
-        } else {
-            job.windows[(size_t)b * 8 + tid] = SvtMeWindow{0, 0, 0, 0};
-        }
-        job.search_results[(size_t)b * 8 + tid] = sr;
-    }
+    write_sb_results();
+    write_search_results();
     write_mirrors();
 #undef BS
 #undef BM

@@ -57,7 +57,15 @@ typedef struct ShimJob {
     SvtMePicResults res;
     SvtMeHmeState  *hme; /* ME_MCTF only (tf_exit) */
     void           *mem;
+    struct ShimBatch *batch; /* queued by svtme_shim_submit_pictures: `res` points into the batch's slab */
 } ShimJob;
+
+/* the host slab one svtme_picture_me_batch_packed call fills (one device-to-host copy for the whole mini-GOP); freed when
+   the last of its pictures has handed out its last b64 */
+typedef struct ShimBatch {
+    void *slab;
+    int   live;
+} ShimBatch;
 
 static struct {
     pthread_mutex_t mu;
@@ -70,6 +78,7 @@ static struct {
     uint64_t        n_pictures, n_tf_pairs, n_dg, n_batches;
 } g = {.mu = PTHREAD_MUTEX_INITIALIZER};
 
+static void shim_job_free(ShimJob *j);
 static void shim_fatal(const char *what, uint32_t rc) {
     fprintf(stderr, "svtme_wrap: %s failed (0x%x): the GPU motion-estimation path has no CPU fallback\n", what, rc);
     abort();
@@ -145,10 +154,7 @@ void svtme_shim_shutdown(void) {
     pthread_mutex_lock(&g.mu);
     if (g.sess) svtme_session_destroy(g.sess);
     g.sess = NULL;
-    for (int i = 0; i < SHIM_JOBS; i++) {
-        free(g.job[i].mem);
-        memset(&g.job[i], 0, sizeof(g.job[i]));
-    }
+    for (int i = 0; i < SHIM_JOBS; i++) shim_job_free(&g.job[i]);
     memset(g.slot, 0, sizeof(g.slot));
     pthread_mutex_unlock(&g.mu);
 }
@@ -286,6 +292,15 @@ void svtme_shim_flatten(const PictureParentControlSet *pcs, const MeContext *m, 
 }
 
 /* ---- jobs: one per picture (open loop) or per (centre, neighbour) pair (temporal filter) ----- */
+static void shim_job_free(ShimJob *j) {
+    free(j->mem);
+    if (j->batch && --j->batch->live == 0) {
+        svtme_host_free(j->batch->slab);
+        free(j->batch);
+    }
+    memset(j, 0, sizeof(*j));
+}
+
 static ShimJob *shim_find_job(const void *pcs, int me_type, uint64_t ref_number) {
     for (int i = 0; i < SHIM_JOBS; i++) {
         ShimJob *j = &g.job[i];
@@ -294,7 +309,7 @@ static ShimJob *shim_find_job(const void *pcs, int me_type, uint64_t ref_number)
     return NULL;
 }
 
-static ShimJob *shim_new_job(const void *pcs, int me_type, uint64_t ref_number, uint32_t n_b64, const SvtMePicParams *p) {
+static ShimJob *shim_new_job(const void *pcs, int me_type, uint64_t ref_number, uint32_t n_b64, const SvtMePicParams *p, int own_arrays) {
     ShimJob *j = NULL;
     for (int i = 0; i < SHIM_JOBS && !j; i++)
         if (!g.job[i].used) j = &g.job[i];
@@ -305,12 +320,13 @@ static ShimJob *shim_new_job(const void *pcs, int me_type, uint64_t ref_number, 
         for (int i = 0; i < SHIM_JOBS; i++)
             if (!g.job[i].pending && !g.job[i].readers && (!j || g.job[i].stamp < j->stamp)) j = &g.job[i];
         if (!j) shim_fatal("job table full", 0);
-        free(j->mem);
+        shim_job_free(j);
     }
     memset(j, 0, sizeof(*j));
     j->stamp = g.clock;
     j->used = 1; j->pcs = pcs; j->me_type = me_type; j->ref_number = ref_number;
     j->n_b64 = n_b64; j->n_pus = p->enable_me_8x8 ? 85 : 21; j->max_refs = p->max_refs; j->max_cand = p->max_cand;
+    if (!own_arrays) return j; /* the caller points j->res into a batch slab */
     const size_t n = n_b64, npu = j->n_pus;
     const size_t sz[] = {n * 680 * 4, n * 680 * 4, n * 8 * sizeof(SvtMeSearchResult), n * npu, n * npu * j->max_refs * 4,
                          n * npu * j->max_cand, n * 4, n * 4, n * 4, n * 4, n * 4, n * 4, n, n,
@@ -357,7 +373,7 @@ static ShimJob *shim_launch(PictureParentControlSet *pcs, MeContext *me_ctx, EbP
     for (int l = 0; l < p.num_of_list_to_search; l++)
         for (int r = 0; r < p.num_of_ref_pic_to_search[l]; r++)
             p.ref_pic_id[l][r] = shim_slot_of(me_ctx->me_ds_ref_array[l][r].picture_ptr, me_ctx->me_ds_ref_array[l][r].picture_number, scope);
-    ShimJob *j = shim_new_job(pcs, me_ctx->me_type, ref_number, ((w + 63) / 64) * ((h + 63) / 64), &p);
+    ShimJob *j = shim_new_job(pcs, me_ctx->me_type, ref_number, ((w + 63) / 64) * ((h + 63) / 64), &p, 1);
     SHIM_CHECK(svtme_picture_me(g.sess, src_slot, &p, &j->res, /*sync*/ 1));
     if (j->hme) SHIM_CHECK(svtme_fetch_hme_state(g.sess, j->hme, (size_t)j->n_b64 * sizeof(SvtMeHmeState)));
     if (me_ctx->me_type == ME_MCTF) g.n_tf_pairs++;
@@ -440,10 +456,7 @@ EbErrorType __wrap_svt_aom_motion_estimation_b64(PictureParentControlSet *pcs, u
 
     pthread_mutex_lock(&g.mu);
     j->readers--;
-    if (++j->delivered == j->n_b64) { /* every b64 is asked for exactly once (me_process.c:174-271) */
-        free(j->mem);
-        memset(j, 0, sizeof(*j));
-    }
+    if (++j->delivered == j->n_b64) shim_job_free(j); /* every b64 is asked for exactly once (me_process.c:174-271) */
     pthread_mutex_unlock(&g.mu);
     return EB_ErrorNone;
 }
@@ -467,10 +480,9 @@ void svtme_shim_submit_pictures(PictureParentControlSet **pcs_list, uint32_t n) 
     if (n > SHIM_JOBS / 2) shim_fatal("svtme_shim_submit_pictures: too many pictures", n);
     MeContext      *m      = (MeContext *)calloc(1, sizeof(MeContext));
     SvtMePicParams *params = (SvtMePicParams *)calloc(n, sizeof(SvtMePicParams));
-    SvtMePicResults *res   = (SvtMePicResults *)calloc(n, sizeof(SvtMePicResults));
     int32_t        *ids    = (int32_t *)calloc(n, sizeof(int32_t));
     ShimJob       **jobs   = (ShimJob **)calloc(n, sizeof(ShimJob *));
-    if (!m || !params || !res || !ids || !jobs) shim_fatal("allocation", 0);
+    if (!m || !params || !ids || !jobs) shim_fatal("allocation", 0);
     pthread_mutex_lock(&g.mu);
     uint32_t k = 0;
     for (uint32_t i = 0; i < n; i++) {
@@ -503,12 +515,30 @@ void svtme_shim_submit_pictures(PictureParentControlSet **pcs_list, uint32_t n) 
         for (int l = 0; l < p->num_of_list_to_search; l++)
             for (int r = 0; r < p->num_of_ref_pic_to_search[l]; r++)
                 p->ref_pic_id[l][r] = shim_slot_of(m->me_ds_ref_array[l][r].picture_ptr, m->me_ds_ref_array[l][r].picture_number, NULL);
-        jobs[k] = shim_new_job(pcs, ME_OPEN_LOOP, 0, pcs->b64_total_count, p);
-        res[k]  = jobs[k]->res;
+        jobs[k] = shim_new_job(pcs, ME_OPEN_LOOP, 0, pcs->b64_total_count, p, 0);
         k++;
     }
     if (k) {
-        SHIM_CHECK(svtme_picture_me_batch(g.sess, k, ids, params, res, /*sync*/ 0));
+        /* what the b64 calls hand out: the MeSbResults arrays and PCS statistics, plus the MeContext members */
+        const uint32_t   fields = SVTME_F_SB_RESULTS | SVTME_F_STATS | SVTME_F_SEARCH_RESULTS | SVTME_F_BEST;
+        SvtMePackedLayout *lay  = (SvtMePackedLayout *)calloc(k, sizeof(SvtMePackedLayout));
+        ShimBatch         *bt   = (ShimBatch *)calloc(1, sizeof(ShimBatch));
+        if (!lay || !bt) shim_fatal("allocation", 0);
+        size_t total = 0;
+        for (uint32_t i = 0; i < k; i++) {
+            SHIM_CHECK(svtme_packed_layout(g.w, g.h, &params[i], fields, &lay[i]));
+            total += lay[i].bytes;
+        }
+        bt->slab = svtme_host_alloc(total);
+        if (!bt->slab) shim_fatal("pinned result slab", 0);
+        bt->live = (int)k;
+        size_t at = 0;
+        for (uint32_t i = 0; i < k; i++) {
+            svtme_packed_view(&lay[i], (uint8_t *)bt->slab + at, &jobs[i]->res);
+            jobs[i]->batch = bt;
+            at += lay[i].bytes;
+        }
+        SHIM_CHECK(svtme_picture_me_batch_packed(g.sess, k, ids, params, fields, bt->slab, total, /*sync*/ 0));
         const uint64_t seq = svtme_session_batch_seq(g.sess);
         for (uint32_t i = 0; i < k; i++) {
             jobs[i]->pending = 1;
@@ -516,9 +546,10 @@ void svtme_shim_submit_pictures(PictureParentControlSet **pcs_list, uint32_t n) 
         }
         g.n_pictures += k;
         g.n_batches++;
+        free(lay);
     }
     pthread_mutex_unlock(&g.mu);
-    free(m); free(params); free(res); free(ids); free(jobs);
+    free(m); free(params); free(ids); free(jobs);
 }
 
 /* ---- dynamic-GOP detector (pd_process.c:490-589; one call per ME segment, me_process.c:329) ----------------------- */

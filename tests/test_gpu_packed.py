@@ -1,0 +1,209 @@
+"""-m gpu: the throughput forms of the C ABI.
+  * svtme_picture_me_batch_packed: one device-to-host copy for a whole batch, any subset of the result groups, against the
+    oracle and against the per-array form (svtme_picture_me_batch);
+  * merged host uploads: frames adjacent in host memory, named in any order, mixed with frames that are not adjacent;
+  * the device-resident view: a later stage reads planes and ME vectors in HBM, no second upload.
+CPU part (no GPU): svtme_packed_layout is a pure function of the geometry."""
+import copy
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import svtme_b200 as me
+from svt_av1_psy_b200 import abi
+from util import CASES, case_inputs, compare, orc_me, params_from_encoder_inputs
+
+GROUPS = {"total_me_candidate_index": abi.F_SB_RESULTS, "me_mv_array": abi.F_SB_RESULTS, "me_candidate_array": abi.F_SB_RESULTS,
+          "search_results": abi.F_SEARCH_RESULTS, "me_windows": abi.F_WINDOWS, "p_sb_best_sad": abi.F_BEST, "p_sb_best_mv": abi.F_BEST}
+
+
+def group_of(field):
+    return GROUPS.get(field, abi.F_STATS)
+
+
+def test_packed_layout_is_dense_and_ordered():
+    p = abi.MePicParams()
+    p.enable_me_8x8, p.max_refs, p.max_cand = 1, 7, 23
+    w, h = 1920, 1080
+    n, n_pus, shapes = abi.PicResultArrays.shapes_of(w, h, p)
+    for fields in (abi.F_SB_RESULTS | abi.F_STATS, abi.F_ALL, abi.F_BEST | abi.F_SEARCH_RESULTS, abi.F_STATS):
+        lay = abi.PackedLayout()
+        assert me.lib().svtme_packed_layout(w, h, C.byref(p), fields, C.byref(lay)) == abi.OK
+        spans = []
+        for i, name in enumerate(abi.PicResultArrays.FIELDS):
+            shape, dt = shapes[name]
+            nbytes = int(np.prod(shape)) * np.dtype(dt).itemsize
+            if group_of(name) & fields:
+                assert lay.off[i] != abi.ABSENT and lay.off[i] % 64 == 0
+                spans.append((lay.off[i], lay.off[i] + nbytes))
+            else:
+                assert lay.off[i] == abi.ABSENT
+        spans.sort()
+        for (a0, a1), (b0, b1) in zip(spans, spans[1:]):
+            assert a1 <= b0
+        assert spans[0][0] == 0 and spans[-1][1] <= lay.bytes < spans[-1][1] + 256 and lay.bytes % 256 == 0
+    # what an open-loop consumer downloads per 1080p picture (preset 4: 85 PUs, 7 references, 23 candidates)
+    lay = abi.PackedLayout()
+    me.lib().svtme_packed_layout(w, h, C.byref(p), abi.F_SB_RESULTS | abi.F_STATS, C.byref(lay))
+    assert lay.bytes < 2.3e6
+    assert me.lib().svtme_packed_layout(w, h, C.byref(p), 64, C.byref(lay)) == abi.ERR_BAD_PARAMETER
+
+
+def _batch(n_pics=5):
+    """n_pics pictures of one stream (one session): sources, references, parameters with slot ids"""
+    src0, refs0, pocs, poc, enc_mode, kw = case_inputs(CASES[0])  # 320x192 preset 4, 4+3 references
+    h, w = src0.shape
+    rng = np.random.default_rng(11)
+    planes = [src0] + [r for lst in refs0 for r in lst]
+    pics = []
+    for k in range(n_pics):
+        src = np.roll(src0, (k, 2 * k), (0, 1)) if k else src0
+        src = np.clip(src.astype(np.int16) + rng.integers(-2, 3, src.shape), 0, 255).astype(np.uint8)
+        params = params_from_encoder_inputs(src, refs0, pocs, poc, enc_mode, **kw)
+        pics.append((src, params))
+    return w, h, planes, refs0, pics
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("fields", [abi.F_SB_RESULTS | abi.F_STATS, abi.F_ALL, abi.F_BEST | abi.F_SEARCH_RESULTS | abi.F_WINDOWS])
+def test_packed_batch_matches_oracle(orc, fields):
+    import torch
+    w, h, planes, refs, pics = _batch()
+    s = me.Session(w, h, max_pictures=16)
+    for i, pl in enumerate(planes[1:]):
+        s.upload(1 + i, pl)
+    ids, prms = [], []
+    for k, (src, params) in enumerate(pics):
+        s.upload(8 + k, src)
+        p = copy.copy(params)
+        pid = 1
+        for l in range(len(refs)):
+            for r in range(len(refs[l])):
+                p.ref_pic_id[l][r] = pid
+                pid += 1
+        ids.append(8 + k)
+        prms.append(p)
+    n = len(ids)
+    lay = s.packed_layout(prms[0], fields)
+    slab = torch.zeros(lay.bytes * n, dtype=torch.uint8).pin_memory()
+    slab.fill_(0xA5)
+    ids_a, prm_a = (C.c_int32 * n)(*ids), (abi.MePicParams * n)(*prms)
+    for rep in range(2):  # twice: the two result sets of the session
+        s.me_batch_packed(ids_a, prm_a, n, fields, slab.data_ptr(), slab.numel(), sync=False)
+        s.wait_batch(s.batch_seq())
+        block = slab.numpy()
+        for k, (src, params) in enumerate(pics):
+            want, _, _ = orc_me(src, refs, params, debug=False)
+            got = abi.PicResultArrays(w, h, prms[k], block=block[k * lay.bytes:(k + 1) * lay.bytes], layout=lay)
+            names = [f for f in got.FIELDS if getattr(got, f) is not None]
+            assert set(names) == {f for f in got.FIELDS if group_of(f) & fields}
+            compare(want, got, fields=names)
+    # the per-array form of the same batch gives the same bytes
+    res = [abi.PicResultArrays(w, h, p) for p in prms]
+    s.me_batch(ids, prms, res, sync=True)
+    block = slab.numpy()
+    for k in range(n):
+        got = abi.PicResultArrays(w, h, prms[k], block=block[k * lay.bytes:(k + 1) * lay.bytes], layout=lay)
+        for f in got.FIELDS:
+            if getattr(got, f) is not None:
+                np.testing.assert_array_equal(getattr(got, f), getattr(res[k], f), err_msg=f)
+    # a slab that is too small is refused before anything is queued
+    with pytest.raises(me.binding.SvtMeError):
+        s.me_batch_packed(ids_a, prm_a, n, fields, slab.data_ptr(), slab.numel() - 256)
+    # a field the batch was not asked to produce cannot be fetched afterwards
+    if not fields & abi.F_BEST:
+        s.me_batch_packed(ids_a, prm_a, n, fields, slab.data_ptr(), slab.numel(), sync=True)
+        with pytest.raises(me.binding.SvtMeError):
+            s.fetch_batch(0, abi.PicResultArrays(w, h, prms[0]))
+    s.close()
+
+
+@pytest.mark.gpu
+def test_merged_uploads(orc):
+    """frames adjacent in host memory cross as one copy whatever the order they are named in; pitched and scattered
+    frames take the per-frame path; the planes on the device are the same either way"""
+    import torch
+    w, h = 320, 192
+    rng = np.random.default_rng(5)
+    clip = torch.from_numpy(rng.integers(0, 256, (7, h, w), dtype=np.uint8)).pin_memory()
+    lone = torch.from_numpy(rng.integers(0, 256, (h, w), dtype=np.uint8)).pin_memory()
+    s = me.Session(w, h, max_pictures=16)
+    order = [4, 0, 6, 5, 1]  # frames 0-1 and 4-6 are two runs; plus one frame elsewhere
+    ids = [10, 11, 12, 13, 14, 15]
+    ptrs = [clip[f].data_ptr() for f in order] + [lone.data_ptr()]
+    for rep in range(40):  # several laps of the staging ring
+        s.upload_batch(ids, ptrs, w, "host8")
+    want = [clip[f].numpy() for f in order] + [lone.numpy()]
+    ref = me.Session(w, h, max_pictures=2)
+    for pid, luma in zip(ids, want):
+        ref.upload(0, luma)
+        for lvl in range(3):
+            np.testing.assert_array_equal(s.download_plane(pid, lvl), ref.download_plane(0, lvl), err_msg="picture %d level %d" % (pid, lvl))
+    # 10-bit frames through the same ring
+    clip16 = torch.from_numpy(rng.integers(0, 1024, (3, h, w), dtype=np.uint16).view(np.int16)).pin_memory()
+    s.upload_batch([1, 2, 3], [clip16[f].data_ptr() for f in (2, 0, 1)], w, "host10")
+    for pid, f in zip((1, 2, 3), (2, 0, 1)):
+        ref.upload(0, (clip16[f].numpy().view(np.uint16) >> 2).astype(np.uint8))
+        np.testing.assert_array_equal(s.download_plane(pid, 2), ref.download_plane(0, 2))
+    s.close()
+    ref.close()
+
+
+@pytest.mark.gpu
+def test_device_resident_view(orc):
+    """row f4: GM pre-processing / TPL-style consumers read the planes and the ME vectors where they are"""
+    import torch
+    w, h, planes, refs, pics = _batch(3)
+    s = me.Session(w, h, max_pictures=16)
+    for i, pl in enumerate(planes[1:]):
+        s.upload(1 + i, pl)
+    ids, prms = [], []
+    for k, (src, params) in enumerate(pics):
+        s.upload(8 + k, src)
+        p = copy.copy(params)
+        pid = 1
+        for l in range(len(refs)):
+            for r in range(len(refs[l])):
+                p.ref_pic_id[l][r] = pid
+                pid += 1
+        ids.append(8 + k)
+        prms.append(p)
+    # planes: the device view of a picture = what the oracle builds from the same luma
+    s.sync()
+    dp = s.device_planes(8)
+    for lvl in range(3):
+        pl = dp[lvl]
+        assert (pl.width, pl.height) == (w >> lvl, h >> lvl) and pl.stride >= pl.width + 2 * pl.pad
+        rows = s.read_device(pl.origin - pl.pad * pl.stride - pl.pad, (pl.height + 2 * pl.pad) * pl.stride).reshape(pl.height + 2 * pl.pad, pl.stride)
+        exp = s.download_plane(8, lvl)  # padded by 72 / 32 / 16 as the reference's buffers
+        ep = (72, 32, 16)[lvl]
+        got = rows[pl.pad - ep:pl.pad + pl.height + ep, pl.pad - ep:pl.pad + pl.width + ep]
+        np.testing.assert_array_equal(got, exp)
+    # results: read the MeSbResults arrays of every picture of the batch in place, compare with the host copy
+    fields = abi.F_SB_RESULTS | abi.F_STATS
+    n = len(ids)
+    lay = s.packed_layout(prms[0], fields)
+    slab = torch.zeros(lay.bytes * n, dtype=torch.uint8).pin_memory()
+    ids_a, prm_a = (C.c_int32 * n)(*ids), (abi.MePicParams * n)(*prms)
+    s.me_batch_packed(ids_a, prm_a, n, fields, slab.data_ptr(), slab.numel(), sync=False)
+    seq = s.batch_seq()
+    consumer = torch.cuda.Stream()
+    views = [s.acquire_results(seq, k, consumer.cuda_stream) for k in range(n)]
+    consumer.synchronize()  # the consumer's stream was made to wait for the batch's kernels
+    s.wait_batch(seq)
+    for k in range(n):
+        host = abi.PicResultArrays(w, h, prms[k], block=slab.numpy()[k * lay.bytes:(k + 1) * lay.bytes], layout=lay)
+        dev = views[k]
+        assert dev.p_sb_best_sad is None and dev.search_results is None  # not produced
+        for f in ("total_me_candidate_index", "me_mv_array", "me_candidate_array", "me_8x8_distortion", "rc_me_allow_gm"):
+            a = getattr(host, f)
+            got = s.read_device(getattr(dev, f), a.nbytes).view(a.dtype).reshape(a.shape)
+            np.testing.assert_array_equal(got, a, err_msg="picture %d %s" % (k, f))
+    s.release_results(seq, consumer.cuda_stream)
+    # two batches later the set is reused: the view is refused
+    s.me_batch_packed(ids_a, prm_a, n, fields, slab.data_ptr(), slab.numel(), sync=True)
+    s.me_batch_packed(ids_a, prm_a, n, fields, slab.data_ptr(), slab.numel(), sync=True)
+    with pytest.raises(me.binding.SvtMeError):
+        s.acquire_results(seq, 0, consumer.cuda_stream)
+    s.close()
