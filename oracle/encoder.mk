@@ -10,7 +10,12 @@
 #                                      -Wl,--wrap=svt_aom_motion_estimation_b64 -Wl,--wrap=dg_detector_hme_level0
 #                                      against libsvtme_b200.so: every open-loop ME, temporal-filter ME and dynamic-GOP
 #                                      detector search of the encode runs on the GPU
-# Both must write the same bitstream. The one header cmake would generate (EbVersion.h: two string defines from
+#   oracle/_ref/enc/SvtAv1EncApp_gpu_batched   the same again, with ONE object replaced: pd_process.c patched by
+#                                      oracle/pd_process_submit.patch (applied to a COPY under oracle/_ref/enc/, the reference
+#                                      tree is not touched): Picture Decision hands every mini-GOP to
+#                                      svtme_shim_submit_pictures before posting its ME tasks = the throughput path
+#                                      (one GPU batch and one result download per mini-GOP)
+# All three must write the same bitstream. The one header cmake would generate (EbVersion.h: two string defines from
 # EbVersion.h.in) is written here.
 REF   ?= /root/reference
 RS    := $(REF)/Source
@@ -29,7 +34,7 @@ LIB_OBJS := $(patsubst $(REF)/%.c,$(OUT)/obj/%.o,$(LIB_SRCS))
 APP_OBJS := $(patsubst $(REF)/%.c,$(OUT)/obj/%.o,$(APP_SRCS))
 
 .PHONY: all clean
-all: $(OUT)/SvtAv1EncApp_ref $(OUT)/SvtAv1EncApp_gpu
+all: $(OUT)/SvtAv1EncApp_ref $(OUT)/SvtAv1EncApp_gpu $(OUT)/SvtAv1EncApp_gpu_batched
 
 $(OUT)/EbVersion.h:
 	@mkdir -p $(OUT)
@@ -47,6 +52,18 @@ $(OUT)/SvtAv1EncApp_ref: $(LIB_OBJS) $(APP_OBJS)
 
 $(OUT)/SvtAv1EncApp_gpu: $(LIB_OBJS) $(APP_OBJS) $(OUT)/svtme_wrap.o $(PKG)/libsvtme_b200.so
 	@$(CC) -o $@ $(APP_OBJS) $(LIB_OBJS) $(OUT)/svtme_wrap.o \
+	    -Wl,--wrap=svt_aom_motion_estimation_b64 -Wl,--wrap=dg_detector_hme_level0 \
+	    -L$(PKG) -lsvtme_b200 -Wl,-rpath,'$$ORIGIN/../../../svt-av1-psy_b200' -lm -lpthread
+
+PD_OBJ := $(OUT)/obj/Source/Lib/Codec/pd_process.o
+$(OUT)/pd_process_submit.c: $(RS)/Lib/Codec/pd_process.c $(HERE)pd_process_submit.patch | $(OUT)/EbVersion.h
+	@patch -s -o $@ $< $(HERE)pd_process_submit.patch
+
+$(OUT)/pd_process_submit.o: $(OUT)/pd_process_submit.c
+	@$(CC) $(CFLAGS) $(INC) -c $< -o $@
+
+$(OUT)/SvtAv1EncApp_gpu_batched: $(LIB_OBJS) $(APP_OBJS) $(OUT)/svtme_wrap.o $(OUT)/pd_process_submit.o $(PKG)/libsvtme_b200.so
+	@$(CC) -o $@ $(APP_OBJS) $(filter-out $(PD_OBJ),$(LIB_OBJS)) $(OUT)/pd_process_submit.o $(OUT)/svtme_wrap.o \
 	    -Wl,--wrap=svt_aom_motion_estimation_b64 -Wl,--wrap=dg_detector_hme_level0 \
 	    -L$(PKG) -lsvtme_b200 -Wl,-rpath,'$$ORIGIN/../../../svt-av1-psy_b200' -lm -lpthread
 

@@ -23,6 +23,7 @@ from svt_av1_psy_b200.synth import PanningNoise
 
 ENC_DIR = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle", "_ref", "enc")
 REF_APP, GPU_APP = os.path.join(ENC_DIR, "SvtAv1EncApp_ref"), os.path.join(ENC_DIR, "SvtAv1EncApp_gpu")
+BATCHED_APP = os.path.join(ENC_DIR, "SvtAv1EncApp_gpu_batched")  # + oracle/pd_process_submit.patch: mini-GOPs submitted as GPU batches
 
 pytestmark = pytest.mark.skipif(not (os.path.exists(REF_APP) and os.path.exists(GPU_APP)),
                                 reason="oracle/_ref/enc not built (make -f oracle/encoder.mk, needs the reference's sources)")
@@ -96,3 +97,29 @@ def test_gpu_encoder_writes_the_reference_bitstream(tmp_path, name, w, h, n, arg
     assert len(a) > 32 + 12 * n
     assert a == b, "bitstreams differ (%d vs %d bytes); GPU: %d pictures, %d TF pairs, %d DG pairs" % (len(a), len(b), pictures, tf_pairs, dg_pairs)
     print("%s: %d bytes identical; on the GPU: %d pictures, %d TF pairs, %d DG pairs" % (name, len(a), pictures, tf_pairs, dg_pairs))
+
+
+# the throughput path inside the real encoder: Picture Decision (patched copy of pd_process.c, oracle/pd_process_submit.patch)
+# hands every mini-GOP to svtme_shim_submit_pictures, which queues ONE GPU batch and ONE packed result download for it
+BATCHED = [e for e in ENCODES if e[0] in ("M8_default", "M4_lp4", "M5_720p", "M2_odd_size", "M8_10bit", "M6_three_layers")] + [
+    ("M4_1080p_65", 1920, 1080, 40, ["--preset", "4", "--lp", "8"]),
+]
+
+
+@pytest.mark.gpu
+@pytest.mark.skipif(not os.path.exists(BATCHED_APP), reason="SvtAv1EncApp_gpu_batched not built")
+@pytest.mark.parametrize("name,w,h,n,args", BATCHED, ids=[e[0] for e in BATCHED])
+def test_batched_gpu_encoder_writes_the_reference_bitstream(tmp_path, name, w, h, n, args):
+    y4m = str(tmp_path / "in.y4m")
+    write_y4m(y4m, w, h, n, seed=len(name) + w, ten_bit=name.endswith("10bit"))
+    ref_ivf, gpu_ivf = str(tmp_path / "ref.ivf"), str(tmp_path / "gpu.ivf")
+    encode(REF_APP, y4m, ref_ivf, args)
+    log = encode(BATCHED_APP, y4m, gpu_ivf, args, env={"SVTME_SHIM_STATS": "1"})
+    m = re.search(r"svtme_wrap: on the GPU: (\d+) open-loop pictures \((\d+) batches\), (\d+) temporal-filter pairs, (\d+) detector pairs", log)
+    assert m, "no report from the shim:\n" + log[-1500:]
+    pictures, batches, tf_pairs, dg_pairs = (int(v) for v in m.groups())
+    assert batches > 0, "no mini-GOP went through svtme_shim_submit_pictures"
+    assert pictures >= n - 1 - n // 16
+    a, b = open(ref_ivf, "rb").read(), open(gpu_ivf, "rb").read()
+    assert a == b, "bitstreams differ (%d vs %d bytes); GPU: %d pictures in %d batches" % (len(a), len(b), pictures, batches)
+    print("%s: %d bytes identical; on the GPU: %d pictures (%d batches), %d TF pairs, %d DG pairs" % (name, len(a), pictures, batches, tf_pairs, dg_pairs))
