@@ -38,7 +38,7 @@ def parse_args():
     ap.add_argument("--preset", type=int, default=4)
     ap.add_argument("--bits", type=int, default=8, choices=[8, 10])
     ap.add_argument("--frames", type=int, default=240, help="length of the synthetic clip")
-    ap.add_argument("--concurrency", type=int, default=1, choices=[1, 2], help="compute streams per session (svtme_session_set_concurrency)")
+    ap.add_argument("--concurrency", type=int, default=2, choices=[1, 2], help="compute streams per session (svtme_session_set_concurrency)")
     ap.add_argument("--e2e-probe", default="full", choices=["full", "h2d", "d2h"], help="diagnostic: drop one direction of the end-to-end copies")
     ap.add_argument("--host-numa", default="auto", choices=["auto", "off"],
                     help="auto: run this rank's threads on (or, failing that, bind its memory to) the NUMA node of its GPU, so that "

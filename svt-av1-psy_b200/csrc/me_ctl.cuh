@@ -61,26 +61,23 @@ __device__ inline void ctl_make_job(HmeJobG &j, const DevPlane &ref, int16_t org
     j.active = 1;
 }
 
-// append the tiles of a staged search to the batch-wide unit queue of k_search16
-__device__ inline void ctl_enqueue_tiles(const PicJob &job, const HmeJobG &j, int slot_in_pic) {
-    const uint32_t n = (uint32_t)j.n_tx * j.n_ty;
-    if (!n) return;
-    // one atomic per group of lanes that enqueue together (the counter is shared by the whole batch)
-    const uint32_t peers = __activemask();
+// Append the searches a warp just built to the batch-wide unit queue of k_search16. One queue entry = one (b64, list,
+// ref): the up to four jobs of slots 4 lr .. 4 lr + 3 (the two pre-HME regions, or the four level-0 quadrants / their
+// merged window) are searched by ONE warp, tile after tile, so that what a tile search needs besides its tile (the unit
+// record, the job records, the source block rows) is fetched once per (b64, list, ref) and not once per tile, and a
+// job's best position is kept in registers until its last tile. Called by all 32 lanes; has_work: this lane's job was
+// built in this launch and has at least one tile to search.
+__device__ inline void ctl_enqueue_units(const PicJob &job, bool has_work, int b) {
     const int      lane  = threadIdx.x & 31;
-    uint32_t pre = 0, tot = 0;
-    for (int i = 0; i < 32; i++) {
-        if (!((peers >> i) & 1)) continue;
-        const uint32_t ni = __shfl_sync(peers, n, i);
-        if (i < lane) pre += ni;
-        tot += ni;
-    }
+    const uint32_t work  = __ballot_sync(0xffffffffu, has_work);
+    const bool     lead  = (lane & 3) == 0 && ((work >> lane) & 0xfu) != 0; // first lane of a (list, ref) group with work
+    const uint32_t leads = __ballot_sync(0xffffffffu, lead);
+    if (!leads) return;
     uint32_t base = 0;
-    const int leader = __ffs(peers) - 1;
-    if (lane == leader) base = atomicAdd(&job.s16_counters[0], tot);
-    base = __shfl_sync(peers, base, leader) + pre;
-    for (uint32_t i = 0; i < n && base + i < job.s16_units_cap; i++)
-        job.s16_units[base + i] = make_uint2(blockIdx.y, ((uint32_t)slot_in_pic << 10) | i);
+    const int first = __ffs(leads) - 1;
+    if (lane == first) base = atomicAdd(&job.s16_counters[0], (uint32_t)__popc(leads)); // one atomic per warp (the counter is shared by the batch)
+    base = __shfl_sync(0xffffffffu, base, first) + (uint32_t)__popc(leads & ((1u << lane) - 1u));
+    if (lead && base < job.s16_units_cap) job.s16_units[base] = make_uint2(blockIdx.y, (uint32_t)(b * HME_JOBS_PER_B64 + lane));
 }
 
 // key -> (sad, centre); centre keeps its value when no position was evaluated
@@ -287,7 +284,7 @@ __global__ void __launch_bounds__(32 * CTL_WARPS) k_hme_ctl(const PicJob *__rest
     __syncwarp();
 
     // ---- BUILD ----
-    bool l0_built = false;
+    bool l0_built = false, s16_work = false; // s16_work: this lane built a 1/16-plane search that k_search16 must run
     const bool in_build = searched && ((op.build_mask >> lr) & 1);
     const int16_t ox16 = (int16_t)g.org_x, oy16 = (int16_t)g.org_y;
     if (op.build_stage == ST_PREHME && in_build && q < 2 && hme_ref) {
@@ -317,7 +314,7 @@ __global__ void __launch_bounds__(32 * CTL_WARPS) k_hme_ctl(const PicJob *__rest
                          w, h, (int16_t)(rf.org_x - 1), (int16_t)(rf.org_y - 1), false, rows0, bw0);
             const bool sk = c.prehme_skip_search_line && bw0 == 16 && rows0 <= 16;
             if (j.sa_w > 0 && j.sa_h > 0) ops += (unsigned long long)j.sa_w * (sk ? j.sa_h / 2 : j.sa_h) * bw0 * rows0;
-            ctl_enqueue_tiles(job, j, b * HME_JOBS_PER_B64 + lane);
+            s16_work = j.n_tx && j.n_ty;
         }
     } else if (op.build_stage == ST_L0 && in_build) {
         const int bw0 = g.b64_w >> 2, rows0 = sub ? (g.b64_h >> 2) >> 1 : (g.b64_h >> 2);
@@ -429,14 +426,15 @@ __global__ void __launch_bounds__(32 * CTL_WARPS) k_hme_ctl(const PicJob *__rest
                 s16_tile_geometry(v_w[0] + v_w[1], v_h[0] + v_h[2], &tw, &th, &ntx, &nty, &wide);
                 j.merged = 1; j.m_w = (int16_t)(v_w[0] + v_w[1]); j.m_h = (int16_t)(v_h[0] + v_h[2]);
                 j.tile_w = (uint16_t)tw; j.tile_h = (uint16_t)th; j.n_tx = (uint8_t)ntx; j.n_ty = (uint8_t)nty; j.wide = (uint8_t)wide;
-                ctl_enqueue_tiles(job, j, b * HME_JOBS_PER_B64 + lane);
+                s16_work = ntx && nty;
             } else {
                 j.merged = 2;
             }
         } else if (l0_built) {
-            ctl_enqueue_tiles(job, j, b * HME_JOBS_PER_B64 + lane);
+            s16_work = j.n_tx && j.n_ty;
         }
     }
+    if (op.build_stage == ST_PREHME || op.build_stage == ST_L0) ctl_enqueue_units(job, s16_work, b); // warp-uniform
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) ops += __shfl_xor_sync(0xffffffffu, ops, o);
     if (lane == 0 && ops && job.sad_ops) {

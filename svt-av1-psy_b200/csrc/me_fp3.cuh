@@ -200,19 +200,42 @@ __global__ void __launch_bounds__(32 * FP_WARPS) k_fp(const PicJob *__restrict__
     if (c.me_early_exit_th) {
         if (st.zz_sad[l][r] < (c.me_early_exit_th / 6)) sa_w = sa_h = 1;
     }
+    // plane coordinates of the reference sample under the block's top-left sample at MV (0,0)
+    const int bx = ref.org_x + g.org_x, by = ref.org_y + g.org_y;
+    FpLane<SUB> L;
+    bool lane_ready = false;
     if (!c.me_early_exit_th) {
         uint8_t hme_is_accurate = 1;
         if ((xc != 0 || yc != 0) && pp.is_ref) {
             // check_00_center :1139-1206 (the COST_PRECISION shift is monotonic)
             const int16_t ox = (int16_t)g.org_x, oy = (int16_t)g.org_y, pad = 63;
-            const uint8_t *p0 = ref.buf + ((int16_t)ref.org_x + ox + ((int16_t)ref.org_y + oy) * ref.stride);
-            const uint32_t zero_mv_sad = warp_nxm_sad2(src_full, sf.stride << 1, p0, ref.stride << 1, g.b64_h >> 1, g.b64_w) << 1;
-            xc = ((ox + xc) < -pad) ? (int16_t)(-pad - ox) : xc;
-            xc = ((ox + xc) > (int16_t)ref.width - 1) ? (int16_t)(xc - ((ox + xc) - ((int16_t)ref.width - 1))) : xc;
-            yc = ((oy + yc) < -pad) ? (int16_t)(-pad - oy) : yc;
-            yc = ((oy + yc) > (int16_t)ref.height - 1) ? (int16_t)(yc - ((oy + yc) - ((int16_t)ref.height - 1))) : yc;
-            const uint8_t *p1 = ref.buf + ((int16_t)(ref.org_x + ox) + xc + ((int16_t)(ref.org_y + oy) + yc) * ref.stride);
-            const uint32_t hme_mv_sad = warp_nxm_sad2(src_full, sf.stride << 1, p1, ref.stride << 1, g.b64_h >> 1, g.b64_w) << 1;
+            int16_t xh = xc, yh = yc;
+            xh = ((ox + xh) < -pad) ? (int16_t)(-pad - ox) : xh;
+            xh = ((ox + xh) > (int16_t)ref.width - 1) ? (int16_t)(xh - ((ox + xh) - ((int16_t)ref.width - 1))) : xh;
+            yh = ((oy + yh) < -pad) ? (int16_t)(-pad - oy) : yh;
+            yh = ((oy + yh) > (int16_t)ref.height - 1) ? (int16_t)(yh - ((oy + yh) - ((int16_t)ref.height - 1))) : yh;
+            uint32_t zero_mv_sad, hme_mv_sad;
+            if (SUB && g.b64_w == 64 && g.b64_h == 64) {
+                // both SADs (64 wide, the 32 even rows: svt_nxm_sad_kernel with doubled strides) from TMA tiles and the
+                // lane's source rows, which the scan needs anyway: two tile loads in flight together, ~60 instructions per
+                // position, no per-lane global loads (the unaligned-LDG form below was a quarter of this kernel's
+                // instructions and its largest stall, profiles/r02_ncu_notes.md)
+                pipe_issue(P, 0, map, bx & ~15, by);
+                pipe_issue(P, 1, map, (bx + xh) & ~15, by + yh);
+                fp_lane_init<SUB>(L, src_full, sf.stride, 64, 64);
+                lane_ready = true;
+                pipe_wait(P, 0);
+                zero_mv_sad = __reduce_add_sync(0xffffffffu, tile_sad1<4, FpLane<SUB>::NR>(L.T, P.buf[0], (uint32_t)(bx & 15))) << 1;
+                pipe_wait(P, 1);
+                hme_mv_sad = __reduce_add_sync(0xffffffffu, tile_sad1<4, FpLane<SUB>::NR>(L.T, P.buf[1], (uint32_t)((bx + xh) & 15))) << 1;
+                __syncwarp(); // both stages are free again
+            } else {
+                const uint8_t *p0 = ref.buf + ((int16_t)ref.org_x + ox + ((int16_t)ref.org_y + oy) * ref.stride);
+                zero_mv_sad = warp_nxm_sad2(src_full, sf.stride << 1, p0, ref.stride << 1, g.b64_h >> 1, g.b64_w) << 1;
+                const uint8_t *p1 = ref.buf + ((int16_t)(ref.org_x + ox) + xh + ((int16_t)(ref.org_y + oy) + yh) * ref.stride);
+                hme_mv_sad = warp_nxm_sad2(src_full, sf.stride << 1, p1, ref.stride << 1, g.b64_h >> 1, g.b64_w) << 1;
+            }
+            xc = xh; yc = yh;
             const uint64_t zero_cost = (uint64_t)(zero_mv_sad << 8), hme_cost = (uint64_t)(hme_mv_sad << 8);
             if ((zero_cost < hme_cost ? zero_cost : hme_cost) == zero_cost) xc = yc = 0;
             best_hme_sad = hme_mv_sad;
@@ -229,13 +252,10 @@ __global__ void __launch_bounds__(32 * FP_WARPS) k_fp(const PicJob *__restrict__
             }
         }
     }
-    // plane coordinates of the reference sample under the block's top-left sample at MV (0,0)
-    const int bx = ref.org_x + g.org_x, by = ref.org_y + g.org_y;
     const bool probe = c.me_8x8_var_enabled && (sa_w * sa_h > 24);
     const int  ptx = bx + xc - 8, pty = by + yc - 4; // the probe tile: 16 x 8 positions around the search centre
     if (probe) pipe_issue(P, 0, map, ptx & ~15, pty);
-    FpLane<SUB> L;
-    fp_lane_init<SUB>(L, src_full, sf.stride, 64, 64); // the full-pel stage always works on 64x64 (padded source)
+    if (!lane_ready) fp_lane_init<SUB>(L, src_full, sf.stride, 64, 64); // the full-pel stage always works on 64x64 (padded source)
     if (probe) { // :1393-1441: one position at the search centre, then the variance of its 64 8x8 SADs
         pipe_wait(P, 0);
         uint32_t raw[3];

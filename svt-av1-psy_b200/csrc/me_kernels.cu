@@ -1,5 +1,6 @@
 // me_kernels.cu — kernel definitions and their host-side launchers (sm_100a only).
 #include <cuda.h>
+#include <cstdlib>
 #include <cstring>
 #include "me_launch.h"
 
@@ -196,6 +197,18 @@ int svtme_launch_downsample_generic(const uint8_t *d_in, int in_stride, int in_w
 // picture pipeline (v2): flat warp-per-tile searches, control in k_hme_ctl between them
 // ------------------------------------------------------------------------------------------
 static int g_fp_search_ctas_per_sm = 0, g_s16_ctas_per_sm = 0;
+// experiment knob (SVTME_PERSISTENT_SLACK=k): the persistent search kernels leave k CTA slots per SM free, so that with
+// two compute streams (svtme_session_set_concurrency) the control / post kernels of one batch can run under the searches
+// of the other. 0 = fill the SM (default).
+static int persistent_slack() {
+    static int v = -1;
+    if (v < 0) {
+        const char *e = getenv("SVTME_PERSISTENT_SLACK");
+        v = e ? atoi(e) : 0;
+        if (v < 0) v = 0;
+    }
+    return v;
+}
 
 // kernels whose dynamic shared memory exceeds the 48 KB default opt in once per device
 static void opt_in_shared_memory() {
@@ -244,7 +257,15 @@ __global__ void __launch_bounds__(128) k_dg_build(const PicJob *__restrict__ job
     const int16_t ox = (int16_t)(-(sa_w >> 1)), oy = (int16_t)(-(sa_h >> 1));
     ctl_make_job(j, ref, (int16_t)(g.org_x >> 2), (int16_t)(g.org_y >> 2), ox, oy, sa_w, sa_h, (int16_t)(ref.org_x - 1),
                  (int16_t)(ref.org_y - 1), true, 16, 16);
-    ctl_enqueue_tiles(job, j, b * HME_JOBS_PER_B64);
+    // one unit per b64 (slots 1..3 of its group are never active here: the slab's job records start zeroed and the
+    // picture pipeline leaves every job it posted inactive)
+    job.hme_jobs[(size_t)b * HME_JOBS_PER_B64 + 1].active = 0;
+    job.hme_jobs[(size_t)b * HME_JOBS_PER_B64 + 2].active = 0;
+    job.hme_jobs[(size_t)b * HME_JOBS_PER_B64 + 3].active = 0;
+    if (j.n_tx && j.n_ty) {
+        const uint32_t at = atomicAdd(&job.s16_counters[0], 1u);
+        if (at < job.s16_units_cap) job.s16_units[at] = make_uint2(0u, (uint32_t)(b * HME_JOBS_PER_B64));
+    }
 }
 
 // per-b64 result (:470-486) and the metrics (:540-575)
@@ -272,9 +293,8 @@ __global__ void __launch_bounds__(128) k_dg_reduce(const PicJob *__restrict__ jo
 }
 
 uint32_t svtme_dg_units_cap(int sa0, int n_b64) {
-    int tw, th, ntx, nty, wide;
-    s16_tile_geometry((sa0 + 7) & ~7, sa0, &tw, &th, &ntx, &nty, &wide);
-    return (uint32_t)(ntx * nty * n_b64);
+    (void)sa0;
+    return (uint32_t)n_b64; // one unit per b64
 }
 
 int svtme_launch_dg_detector(const PicJob *h_job, const PicJob *d_job, int sa0, void *d_out, unsigned long long *d_b64_sad,
@@ -299,25 +319,8 @@ int svtme_launch_dg_detector(const PicJob *h_job, const PicJob *d_job, int sa0, 
 }
 
 uint32_t svtme_s16_units_cap(const SvtMePicParams &pp, int n_b64) {
-    const SvtMeCtrls &c = pp.ctrls;
-    auto tiles_of = [&](int w, int h) {
-        int tw, th, ntx, nty, wide;
-        s16_tile_geometry(w, h, &tw, &th, &ntx, &nty, &wide);
-        return (long long)(ntx * nty < 1 ? 1 : ntx * nty);
-    };
-    long long per_b64 = 0;
-    if (c.prehme_enable)
-        per_b64 = 8 * (tiles_of(c.prehme_sa_cfg[0].sa_max.width, c.prehme_sa_cfg[0].sa_max.height) +
-                       tiles_of(c.prehme_sa_cfg[1].sa_max.width, c.prehme_sa_cfg[1].sa_max.height));
-    const int qw = ((((c.hme_l0_sa.sa_max.width / 2) + 15) & ~15) + 7) & ~7;
-    // per reference: four quadrant windows, or their 2 x 2 union as one window (k_hme_ctl merges exact grids)
-    const int qh = c.hme_l0_sa.sa_max.height / 2;
-    const long long l0_sep = 4 * tiles_of(qw, qh), l0_mrg = tiles_of(2 * qw, 2 * qh);
-    const long long l0 = 8 * (l0_sep > l0_mrg ? l0_sep : l0_mrg);
-    if (l0 > per_b64) per_b64 = l0;
-    long long cap = per_b64 * n_b64;
-    if (cap > 0x7fffffffLL) cap = 0x7fffffffLL;
-    return (uint32_t)cap;
+    (void)pp;
+    return (uint32_t)(8 * n_b64); // one unit per (b64, list, ref) and stage
 }
 
 uint32_t svtme_fp_units_cap(const SvtMePicParams &pp, int n_b64) {
@@ -399,6 +402,7 @@ int svtme_launch_picture_me(const PicJob *h_jobs, int n, const PicJob *d_jobs, c
         int k = 0;
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&k, k_search16, 32 * SEARCH_WARPS, s16_smem);
         g_s16_ctas_per_sm = k > 0 ? k : 1;
+        if (g_s16_ctas_per_sm > persistent_slack()) g_s16_ctas_per_sm -= persistent_slack();
     }
     auto search16 = [&](int skip, int tag) {
         k_search16<<<n_sm * g_s16_ctas_per_sm, 32 * SEARCH_WARPS, s16_smem, st>>>(d_jobs, skip);
@@ -474,6 +478,7 @@ int svtme_launch_picture_me(const PicJob *h_jobs, int n, const PicJob *d_jobs, c
         int k = 0;
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&k, k_fp_big<true>, 32 * FP_WARPS, fp_smem);
         g_fp_search_ctas_per_sm = k > 0 ? k : 1;
+        if (g_fp_search_ctas_per_sm > persistent_slack()) g_fp_search_ctas_per_sm -= persistent_slack();
     }
     const dim3 plan_grid((n_b64 * max_act + FP_WARPS - 1) / FP_WARPS, ny);
     const int big_grid = n_sm * g_fp_search_ctas_per_sm;

@@ -356,38 +356,81 @@ __device__ __forceinline__ void warp_stage_src16(uint32_t dst, const uint8_t *sr
 }
 
 // ---- k_search16 ------------------------------------------------------------------------------
-// persistent warps pull (picture, job, tile) units from the queue k_hme_ctl filled; the tile of the next unit is
-// in flight while the current one is searched. Everything a unit needs was precomputed into its HmeJobG: the
-// per-unit code runs once per ~1-3 rounds of tasks and used to be a quarter of the kernel's instructions.
-struct S16Unit {
-    int  pic, slot;
-    int  px, py, sa_w, sa_h, x0, y0, tw, th, wide, src_off, bw, rows;
-    int  merged, w0, h0; // merged: the window is the 2 x 2 union of the quadrant windows of slots slot..slot+3, split at (w0, h0)
-    bool valid;
+// Persistent warps pull UNITS from the queue k_hme_ctl filled. A unit = one (picture, b64, list, ref): the jobs of its
+// four slots (two pre-HME regions, or four level-0 quadrants / their merged window) are searched by this warp tile after
+// tile. Per unit, once: the queue ticket, the unit record, the source block rows; per job, once: the job record and the
+// store of its best position (kept in registers over its tiles: no atomics); per tile: one TMA load, in flight while the
+// previous tile is searched, and the search. (Round 1 made every tile a queue unit: ~650 of the ~1590 instructions a
+// unit executed were this per-unit work, profiles/r02_k_search16_units.md.)
+// Where a warp is in its walk (unit -> job -> tile), packed: the cursor is alive across every tile search and the
+// evaluators need the registers.
+struct S16Cursor {
+    int      pic, slot0, src_off, tile; // unit record; tile index inside the current job
+    uint32_t u;                         // bw | rows << 8 | remaining-jobs mask << 16 | current job q << 20 | new_unit << 24 | valid << 25
+    uint32_t pxy, wh, split, misc;      // job: px | py << 16; sa_w | sa_h << 16; w0 | h0 << 16; n_tiles | n_tx << 16 | wide << 24 | merged << 25
 };
-__device__ __forceinline__ S16Unit s16_fetch_unit(const PicJob *__restrict__ jobs, uint32_t n_units) {
-    S16Unit un;
+#define S16C_VALID(c) (((c).u >> 25) & 1u)
+#define S16C_NEW_UNIT(c) (((c).u >> 24) & 1u)
+
+__device__ __forceinline__ void s16_load_job(const PicJob *__restrict__ jobs, S16Cursor &c) {
+    const HmeJobG &j = jobs[c.pic].hme_jobs[c.slot0 + (int)((c.u >> 20) & 3u)];
+    int sa_w = j.sa_w, sa_h = j.sa_h, w0 = 32767, h0 = 32767, merged = 0;
+    if (j.merged == 1) { merged = 1; w0 = sa_w; h0 = sa_h; sa_w = j.m_w; sa_h = j.m_h; }
+    c.pxy   = (uint32_t)(uint16_t)j.px | ((uint32_t)(uint16_t)j.py << 16);
+    c.wh    = (uint32_t)sa_w | ((uint32_t)sa_h << 16);
+    c.split = (uint32_t)w0 | ((uint32_t)h0 << 16);
+    c.misc  = ((uint32_t)j.n_tx * (uint32_t)j.n_ty) | ((uint32_t)j.n_tx << 16) | ((uint32_t)j.wide << 24) | ((uint32_t)merged << 25);
+    c.tile  = 0;
+}
+// next unit of the queue: ticket, record, which of its four jobs have tiles
+__device__ __forceinline__ void s16_next_unit(const PicJob *__restrict__ jobs, uint32_t n_units, S16Cursor &c) {
+    const int lane = threadIdx.x & 31;
     uint32_t ui = 0;
-    if ((threadIdx.x & 31) == 0) ui = atomicAdd(&jobs[0].s16_counters[1], 1u);
+    if (lane == 0) ui = atomicAdd(&jobs[0].s16_counters[1], 1u);
     ui = __shfl_sync(0xffffffffu, ui, 0);
-    un.valid = ui < n_units;
-    un.pic = un.slot = un.px = un.py = un.sa_w = un.sa_h = un.x0 = un.y0 = un.wide = un.src_off = 0;
-    un.tw = un.th = un.bw = un.rows = 1;
-    un.merged = 0; un.w0 = un.h0 = 32767;
-    if (un.valid) {
-        const uint2 q = jobs[0].s16_units[ui];
-        un.pic = (int)q.x; un.slot = (int)(q.y >> 10);
-        const int tile = (int)(q.y & 1023u);
-        const HmeJobG &j = jobs[un.pic].hme_jobs[un.slot];
-        un.px = j.px; un.py = j.py; un.sa_w = j.sa_w; un.sa_h = j.sa_h; un.wide = j.wide;
-        if (j.merged == 1) { un.merged = 1; un.w0 = j.sa_w; un.h0 = j.sa_h; un.sa_w = j.m_w; un.sa_h = j.m_h; }
-        un.src_off = j.src_off; un.bw = j.bw; un.rows = j.rows;
-        int tx = 0, ty = tile;
-        if (j.n_tx > 1) { ty = tile / j.n_tx; tx = tile - ty * j.n_tx; } // only windows wider than 128 positions
-        un.x0 = tx * j.tile_w; un.y0 = ty * j.tile_h;
-        un.tw = imin(j.tile_w, un.sa_w - un.x0); un.th = imin(j.tile_h, un.sa_h - un.y0);
+    c.u = 0;
+    if (ui >= n_units) return;
+    const uint2 rec = jobs[0].s16_units[ui];
+    c.pic = (int)rec.x; c.slot0 = (int)rec.y;
+    bool has = false;
+    if (lane < 4) {
+        const HmeJobG &j = jobs[c.pic].hme_jobs[c.slot0 + lane];
+        has = j.active && j.merged != 2 && j.n_tx && j.n_ty && j.sa_w > 0 && j.sa_h > 0;
     }
-    return un;
+    uint32_t todo = __ballot_sync(0xffffffffu, has) & 0xfu;
+    if (!todo) return; // cannot happen: k_hme_ctl enqueues only groups with work
+    const uint32_t q = (uint32_t)__ffs(todo) - 1u;
+    todo &= todo - 1u;
+    const HmeJobG &j0 = jobs[c.pic].hme_jobs[c.slot0 + (int)q];
+    c.src_off = j0.src_off; // the jobs of a unit compare the same block
+    c.u = (uint32_t)j0.bw | ((uint32_t)j0.rows << 8) | (todo << 16) | (q << 20) | (1u << 24) | (1u << 25);
+    s16_load_job(jobs, c);
+}
+// step to the next tile: same job, next job of the unit, or next unit
+__device__ __forceinline__ void s16_advance(const PicJob *__restrict__ jobs, uint32_t n_units, S16Cursor &c) {
+    c.u &= ~(1u << 24);
+    if (++c.tile < (int)(c.misc & 0xffffu)) return;
+    const uint32_t todo = (c.u >> 16) & 0xfu;
+    if (todo) {
+        const uint32_t q = (uint32_t)__ffs(todo) - 1u;
+        c.u = (c.u & ~(0xffu << 16)) | ((todo & (todo - 1u)) << 16) | (q << 20);
+        s16_load_job(jobs, c);
+        return;
+    }
+    s16_next_unit(jobs, n_units, c);
+}
+struct S16Tile { // tile coordinates inside the job's window
+    int x0, y0, tw, th;
+};
+__device__ __forceinline__ S16Tile s16_tile_of(const S16Cursor &c) {
+    S16Tile t;
+    const int n_tx = (int)((c.misc >> 16) & 0xffu), wide = (int)((c.misc >> 24) & 1u);
+    const int tile_w = wide ? S16W_TILE_W : S16T_TILE_W, tile_h = wide ? S16W_TILE_H : S16T_TILE_H;
+    int tx = 0, ty = c.tile;
+    if (n_tx > 1) { ty = c.tile / n_tx; tx = c.tile - ty * n_tx; } // only windows wider than 128 positions
+    t.x0 = tx * tile_w; t.y0 = ty * tile_h;
+    t.tw = imin(tile_w, (int)(c.wh & 0xffffu) - t.x0); t.th = imin(tile_h, (int)(c.wh >> 16) - t.y0);
+    return t;
 }
 
 __global__ void __launch_bounds__(32 * SEARCH_WARPS) k_search16(const PicJob *__restrict__ jobs, int skip_cfg) {
@@ -403,40 +446,61 @@ __global__ void __launch_bounds__(32 * SEARCH_WARPS) k_search16(const PicJob *__
     uint8_t *sbase = s_dyn + ((128u - (smem_u32(s_dyn) & 127u)) & 127u);
     TilePipe P;
     pipe_init(P, sbase + (size_t)warp * 2 * TM_S16_BUF, TM_S16_BUF, s_bar[warp], 0);
-    const uint32_t src32 = smem_u32(s_src[warp][0]); // stage st at + 256 bytes
-    // issue: the tile load and the source rows of the unit's block (both land in stage `st`)
-    auto issue = [&](const S16Unit &un, int st) {
-        const PicJob &job = jobs[un.pic];
-        const int lr = (un.slot & (HME_JOBS_PER_B64 - 1)) >> 2;
-        const CUtensorMap *map = (const CUtensorMap *)job.ref[lr >> 2][lr & 3].tmap + (un.wide ? TM_S16W : TM_S16T);
-        pipe_issue_bytes(P, st, map, (un.px + un.x0) & ~15, un.py + un.y0,
-                         un.wide ? TM_S16W_BOX_W * TM_S16W_BOX_H : TM_S16T_BOX_W * TM_S16T_BOX_H);
-        const DevPlane &ss = job.src.lvl[2];
-        warp_stage_src16(src32 + 256u * (uint32_t)st, ss.buf + un.src_off, ss.stride, row_step, un.rows, un.bw);
+    const uint32_t src32 = smem_u32(s_src[warp][0]); // source rows of the unit with parity sb at + 256 sb bytes
+    S16Cursor c;
+    s16_next_unit(jobs, n_units, c);
+    if (!S16C_VALID(c)) return;
+    // issue: the tile load into stage `st`; the source rows of a NEW unit's block go to source buffer `sb`
+    auto issue = [&](const S16Cursor &cc, const S16Tile &t, int st, int sb) {
+        const PicJob &job = jobs[cc.pic];
+        const int lr = (cc.slot0 & (HME_JOBS_PER_B64 - 1)) >> 2;
+        const int wide = (int)((cc.misc >> 24) & 1u);
+        const CUtensorMap *map = (const CUtensorMap *)job.ref[lr >> 2][lr & 3].tmap + (wide ? TM_S16W : TM_S16T);
+        const int px = (int)(int16_t)(cc.pxy & 0xffffu), py = (int)(int16_t)(cc.pxy >> 16);
+        pipe_issue_bytes(P, st, map, (px + t.x0) & ~15, py + t.y0, wide ? TM_S16W_BOX_W * TM_S16W_BOX_H : TM_S16T_BOX_W * TM_S16T_BOX_H);
+        if (S16C_NEW_UNIT(cc)) {
+            const DevPlane &ss = job.src.lvl[2];
+            warp_stage_src16(src32 + 256u * (uint32_t)sb, ss.buf + cc.src_off, ss.stride, row_step, (int)((cc.u >> 8) & 0xffu), (int)(cc.u & 0xffu));
+        }
     };
-    S16Unit cur = s16_fetch_unit(jobs, n_units);
-    if (!cur.valid) return;
-    int stage = 0;
-    issue(cur, stage);
-    while (cur.valid) {
-        const S16Unit nxt = s16_fetch_unit(jobs, n_units);
-        if (nxt.valid) issue(nxt, stage ^ 1);
-        const bool skip = skip_cfg && cur.bw == 16 && cur.rows <= 16;
+    int stage = 0, sbuf = 0; // sbuf: source buffer of the unit being searched
+    issue(c, s16_tile_of(c), stage, sbuf);
+    unsigned long long run_key = HME_KEY_NONE; // lanes 0..3: best of quadrant `lane` of the current job over its tiles so far
+    while (true) {
+        // everything the search of the current tile needs, before the cursor moves on
+        const S16Tile t = s16_tile_of(c);
+        const int bw = (int)(c.u & 0xffu), rows = (int)((c.u >> 8) & 0xffu), wide = (int)((c.misc >> 24) & 1u), merged = (int)((c.misc >> 25) & 1u);
+        const int px = (int)(int16_t)(c.pxy & 0xffffu), sa_w = (int)(c.wh & 0xffffu);
+        const S16Split sp = {(int)(c.split & 0xffffu), (int)(c.split >> 16)};
+        const bool last_of_job = c.tile + 1 == (int)(c.misc & 0xffffu);
+        unsigned long long *key_out = &jobs[c.pic].hme_jobs[c.slot0 + (int)((c.u >> 20) & 3u) + lane].key;
+        const int cur_sbuf = sbuf;
+        // the tile after this one: its load overlaps this tile's search
+        s16_advance(jobs, n_units, c);
+        if (S16C_VALID(c)) {
+            if (S16C_NEW_UNIT(c)) sbuf ^= 1;
+            issue(c, s16_tile_of(c), stage ^ 1, sbuf);
+        }
+        const bool skip = skip_cfg && bw == 16 && rows <= 16;
         pipe_wait(P, stage);
         __syncwarp(); // the source rows written by other lanes
         uint32_t best[4];
-        const S16Split sp = {cur.w0, cur.h0};
-        warp_search16_tile(P.buf[stage], cur.wide ? TM_S16W_BOX_W : TM_S16T_BOX_W, src32 + 256u * (uint32_t)stage,
-                           (uint32_t)(cur.px + cur.x0) & 15u, cur.x0, cur.y0, cur.tw, cur.th, cur.bw, cur.rows, row_step, skip, sp, best);
-        if (lane < 4 && (lane == 0 || cur.merged)) {
+        warp_search16_tile(P.buf[stage], wide ? TM_S16W_BOX_W : TM_S16T_BOX_W, src32 + 256u * (uint32_t)cur_sbuf,
+                           (uint32_t)(px + t.x0) & 15u, t.x0, t.y0, t.tw, t.th, bw, rows, row_step, skip, sp, best);
+        if (lane < 4 && (lane == 0 || merged)) {
             const uint32_t k = lane == 0 ? best[0] : (lane == 1 ? best[1] : (lane == 2 ? best[2] : best[3]));
             if (k != 0xffffffffu) {
-                const int wq = cur.merged ? ((lane & 1) ? cur.sa_w - cur.w0 : cur.w0) : cur.sa_w;
-                atomicMin(&jobs[cur.pic].hme_jobs[cur.slot + lane].key, s16_key64(k, cur.x0, cur.y0, lane, sp, wq));
+                const int wq = merged ? ((lane & 1) ? sa_w - sp.x : sp.x) : sa_w;
+                const unsigned long long k64 = s16_key64(k, t.x0, t.y0, lane, sp, wq);
+                run_key = k64 < run_key ? k64 : run_key;
+            }
+            if (last_of_job) { // this warp alone searched the job: plain store
+                *key_out = run_key;
+                run_key = HME_KEY_NONE;
             }
         }
         __syncwarp();
-        cur = nxt;
+        if (!S16C_VALID(c)) break;
         stage ^= 1;
     }
 }

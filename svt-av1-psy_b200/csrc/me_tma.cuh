@@ -228,3 +228,21 @@ __device__ __forceinline__ void tile_pass(const TLane<NS, NR> &L, uint32_t row_b
         }
     }
 }
+
+// SAD of the lane's rows of its strip at ONE position whose first byte lies beta bytes into tile row `row_base` (any
+// alignment: five aligned words per row, one funnel shift and one VABSDIFF4 per word). Full blocks only (L.full).
+template <int NS, int NR>
+__device__ __forceinline__ uint32_t tile_sad1(const TLane<NS, NR> &L, uint32_t row_base, uint32_t beta) {
+    const uint32_t base = row_base + (beta & ~3u), sh = (beta & 3u) * 8u;
+    uint32_t acc = 0;
+#pragma unroll
+    for (int q = 0; q < NR; q++) {
+        const uint32_t addr = base + L.roff[q];
+        uint32_t c[5];
+#pragma unroll
+        for (int i = 0; i < 5; i++) asm volatile("ld.shared.u32 %0, [%1];" : "=r"(c[i]) : "r"(addr + 4u * i));
+#pragma unroll
+        for (int i = 0; i < 4; i++) acc = sad4_acc(__funnelshift_r(c[i], c[i + 1], sh), L.src[q][i], acc);
+    }
+    return acc;
+}
