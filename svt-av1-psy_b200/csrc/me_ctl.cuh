@@ -108,13 +108,17 @@ __device__ inline void ctl_set_quadrants(SbState &st, int lvl, int l, int r, int
 
 __global__ void __launch_bounds__(32 * CTL_WARPS) k_hme_ctl(const PicJob *__restrict__ jobs, const CtlOp op) {
     const PicJob &job = jobs[blockIdx.y];
-    __shared__ __align__(16) SbState s_st[CTL_WARPS];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int b = blockIdx.x * CTL_WARPS + warp;
     if (b >= job.n_b64) return;
     const SvtMePicParams &pp = job.pp;
     const SvtMeCtrls     &c  = pp.ctrls;
-    SbState &st = s_st[warp];
+    // The per-b64 state is worked on where it lives (global memory, through L1/L2): a launch touches a few hundred of its
+    // 1552 bytes (the levels and references of the stage it posts / builds). Round 1 staged the whole record into shared
+    // memory and wrote it back in every launch: 5 x ~44 MB of DRAM traffic per mini-GOP, more than the searches read.
+    // Lanes exchange values through it; every such hand-over is separated by __syncwarp(), which orders memory accesses
+    // among the lanes of the warp.
+    SbState &st = job.sb_state[b];
     const B64Geo g = b64_geo(job, b);
     const bool sub = c.hme_search_method == SVTME_SUB_SAD_SEARCH;
     const int  row_step = sub ? 2 : 1;
@@ -125,13 +129,15 @@ __global__ void __launch_bounds__(32 * CTL_WARPS) k_hme_ctl(const PicJob *__rest
     unsigned long long ops = 0;
 
     // ---- state in ----
-    uint32_t *sw = (uint32_t *)&st, *gw = (uint32_t *)&job.sb_state[b];
+    uint32_t *gw = (uint32_t *)&job.sb_state[b];
     if (op.init) {
-        for (int i = lane; i < (int)(sizeof(SbState) / 4); i += 32) sw[i] = 0u;
+        uint32_t zz = 0;
+        if (lane < 8) zz = gw[offsetof(SbState, zz_sad) / 4 + lane]; // written by k_zz for the refs it covers
+        __syncwarp();
+        for (int i = lane; i < (int)(sizeof(SbState) / 4); i += 32) gw[i] = 0u;
         __syncwarp();
         if (lane < 8) {
             const int l8 = lane >> 2, r8 = lane & 3;
-            const uint32_t zz = gw[offsetof(SbState, zz_sad) / 4 + lane]; // written by k_zz for the refs it covers
             const bool has_zz = (c.me_early_exit_th || c.me_safe_limit_zz_th) && l8 < pp.num_of_list_to_search &&
                 r8 < pp.num_of_ref_pic_to_search[l8] && (pp.temporal_layer_index > 0 || l8 == 0);
             st.do_ref[l8][r8]               = 1;
@@ -160,8 +166,6 @@ __global__ void __launch_bounds__(32 * CTL_WARPS) k_hme_ctl(const PicJob *__rest
                         for (int rr = 1; rr < pp.num_of_ref_pic_to_search[ll]; rr++) st.do_ref[ll][rr] = 0;
             }
         }
-    } else {
-        for (int i = lane; i < (int)(sizeof(SbState) / 4); i += 32) sw[i] = gw[i];
     }
     __syncwarp();
 
@@ -441,6 +445,4 @@ __global__ void __launch_bounds__(32 * CTL_WARPS) k_hme_ctl(const PicJob *__rest
         atomicAdd(&job.sad_ops[0], ops);
         if (op.build_stage >= 0) atomicAdd(&job.sad_ops[2 + op.build_stage], ops); // [2] pre-HME, [3..5] HME level 0..2 (ops are counted when a stage is built)
     }
-    __syncwarp();
-    for (int i = lane; i < (int)(sizeof(SbState) / 4); i += 32) gw[i] = sw[i];
 }

@@ -61,12 +61,13 @@ __device__ __forceinline__ void fp_eval_pass(FpLane<SUB> &L, uint32_t row_base, 
     const int  lane = threadIdx.x & 31;
     const bool h4 = lane & 4, h1 = lane & 1, h8 = lane & 8;
     uint32_t s8[8];
+    const bool all8 = nv >= 8; // warp-uniform; the usual case (windows are multiples of 8 positions wide): no range tests
 #pragma unroll
     for (int p = 0; p < 8; p++) {
         s8[p] = accl[p] + accr[p];
-        if (p < nv) {
-            L.kl = min(L.kl, (accl[p] << FP_IDX_BITS) + idx0 + p);
-            L.kr = min(L.kr, (accr[p] << FP_IDX_BITS) + idx0 + p);
+        if (all8 || p < nv) {
+            L.kl = min(L.kl, accl[p] * (1u << FP_IDX_BITS) + idx0 + p);
+            L.kr = min(L.kr, accr[p] * (1u << FP_IDX_BITS) + idx0 + p);
         }
     }
     uint32_t t16[4], u[2];
@@ -75,7 +76,7 @@ __device__ __forceinline__ void fp_eval_pass(FpLane<SUB> &L, uint32_t row_base, 
     for (int i = 0; i < 4; i++) { // the other 8-row band of the 16x16: it keeps the other four positions
         const uint32_t mine = h4 ? s8[4 + i] : s8[i], theirs = h4 ? s8[i] : s8[4 + i];
         t16[i] = mine + __shfl_xor_sync(0xffffffffu, theirs, 4);
-        if (p16 + i < nv) L.k16 = min(L.k16, (t16[i] << FP_IDX_BITS) + idx0 + p16 + i);
+        if (all8 || p16 + i < nv) L.k16 = min(L.k16, t16[i] * (1u << FP_IDX_BITS) + idx0 + p16 + i);
     }
 #pragma unroll
     for (int i = 0; i < 2; i++) { // the other strip of the 32x32

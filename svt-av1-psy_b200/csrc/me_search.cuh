@@ -535,10 +535,19 @@ __device__ __forceinline__ void blk_tile_eval(const TLane<NS, NR> &L, uint32_t b
             // warp-wide sums on the reduction unit (REDUX.SUM), one per position, instead of a shuffle tree on the
             // ALU pipe that bounds this kernel; every lane then keeps the running minimum (the values are uniform)
             const uint32_t idx0 = (uint32_t)((TM_BLK_TILE_H * ty + yy) * sa_w + TM_BLK_TILE_W * tx + 8 * o);
+            if (8 * o + 8 <= n_x) { // a whole octet (every window of 8 or more positions per row): no per-position range test;
+                                    // key = sad * 2^12 + idx0 as a multiply-add (FMA pipe), "+ p, min" as one add-min
 #pragma unroll
-            for (int p = 0; p < 8; p++) {
-                const uint32_t sad = __reduce_add_sync(0xffffffffu, acc[p]);
-                if (8 * o + p < n_x) best = min(best, (sad << BLK_IDX_BITS) | (idx0 + (uint32_t)p));
+                for (int p = 0; p < 8; p++) {
+                    const uint32_t sad = __reduce_add_sync(0xffffffffu, acc[p]);
+                    best = min(best, sad * (1u << BLK_IDX_BITS) + idx0 + (uint32_t)p);
+                }
+            } else {
+#pragma unroll
+                for (int p = 0; p < 8; p++) {
+                    const uint32_t sad = __reduce_add_sync(0xffffffffu, acc[p]);
+                    if (8 * o + p < n_x) best = min(best, (sad << BLK_IDX_BITS) | (idx0 + (uint32_t)p));
+                }
             }
         }
     }
