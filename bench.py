@@ -409,7 +409,9 @@ def measure(wl, frames, rank, world, local, a, steps, warmup, sampler, detail):
                 "d2h_bytes_per_step": int(run.d2h // max(1, steps)), "ms_per_step": ms_e / steps, "host_queue_ms_per_step": run.host_ms}, base + steps
 
     base = warmup + steps + t_steps
-    out["e2e"], base = e2e_pass(consumer, base)
+    # the two MeSbResults arrays cross PCIe at the picture's own strides (SVTME_F_SB_COMPACT: 8 instead of 23 candidate bytes
+    # per PU at this preset); a consumer expands a b64's rows with svtme_sb_expand_b64 when it copies them into pa_me_data
+    out["e2e"], base = e2e_pass(consumer | abi.F_SB_COMPACT, base)
     if detail:  # the same with the MeContext members (p_sb_best_sad / p_sb_best_mv, search_results) crossing PCIe too
         out["e2e_all"], base = e2e_pass(consumer | abi.F_BEST | abi.F_SEARCH_RESULTS, base)
         run.sess.set_result_fields(consumer)
@@ -508,7 +510,8 @@ def run_ours(a):
             "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
             "config": {"workload": wl.name, "pictures_per_step": wl.mgop, "batch": "one launch sequence per mini-GOP (svtme_picture_me_batch), consecutive mini-GOPs on %d compute stream(s)" % a.concurrency, "sharding": "mini-GOP m -> rank m % N",
                        "results": "the arrays open-loop ME's consumers read: MeSbResults (total_me_candidate_index, me_mv_array, me_candidate_array) + the eight per-b64 PCS statistics; "
-                                  "e2e_all_fields adds the MeContext members (p_sb_best_sad / p_sb_best_mv, search_results), which only the temporal filter reads after the call",
+                                  "end to end their rows cross PCIe at the picture's own strides (SVTME_F_SB_COMPACT, expanded per b64 by svtme_sb_expand_b64); "
+                                  "e2e_all_fields is the same pass at the reference's strides plus the MeContext members (p_sb_best_sad / p_sb_best_mv, search_results), which only the temporal filter reads after the call",
                        "e2e_pipeline": "host uploads, kernels and result downloads on three streams; two batches in flight; per step the new frames cross as merged H2D copies and the whole batch's results land in pinned host memory by ONE D2H copy (svtme_picture_me_batch_packed), inside the timed region",
                        "host_numa": numa,
                        "l2": "inputs larger than L2: %d distinct %dx%d frames (%.0f MB) stream through the picture store, no explicit flush"
@@ -629,7 +632,7 @@ def streams16(a, rank, world, local):
     b = copy.copy(a)
     b.width, b.height, b.bits, b.preset, b.frames = 1920, 1080, 8, 4, 64
     wl = Workload(b)
-    fields = abi.F_SB_RESULTS | abi.F_STATS
+    fields = abi.F_SB_RESULTS | abi.F_SB_COMPACT | abi.F_STATS
     runs = [Runner(wl, 0, 1, make_clip(wl, 100 + rank * per_rank + k), local, fields) for k in range(per_rank)]
     steps, warmup = 3, 3
     res = {}

@@ -354,12 +354,30 @@ uint32_t svtme_fetch_results_batch(SvtMeSession *s, uint32_t index, SvtMePicResu
 #define SVTME_F_BEST 8u
 #define SVTME_F_WINDOWS 16u
 #define SVTME_F_ALL 31u
+/* With SVTME_F_SB_RESULTS: me_mv_array and me_candidate_array cross PCIe at the strides THIS picture can fill instead of
+   the sequence-wide max_refs / max_cand the reference allocates (pcs.c:91-96): a row of me_mv_array holds the picture's own
+   n0 + n1 references (list 1 starts at n0), a row of me_candidate_array the most candidates construct_me_candidate_array*
+   can emit for its reference counts (n0 + n1 unipred + the bipred pairs only_l_bwd allows, motion_estimation.c:2602-2905):
+   8 instead of 23 bytes per PU at presets 0-4. svtme_sb_strides reports the strides; svtme_sb_expand_b64 writes one
+   b64's rows at the reference's strides (what a consumer does anyway when it copies the rows into pa_me_data). */
+#define SVTME_F_SB_COMPACT 32u
+typedef struct SvtMeSbStrides {
+    uint8_t mv_stride;    /* entries per PU row of me_mv_array */
+    uint8_t mv_l1_offset; /* first list-1 entry inside a row */
+    uint8_t cand_stride;  /* bytes per PU row of me_candidate_array */
+    uint8_t n_pus;
+} SvtMeSbStrides;
+void svtme_sb_strides(const SvtMePicParams *params, uint32_t fields, SvtMeSbStrides *out);
+/* dst_* : one b64's arrays at the reference's strides (n_pus, n_pus * max_refs, n_pus * max_cand entries; zero filled
+   first); src: the picture-level arrays of a block produced with `fields` */
+void svtme_sb_expand_b64(const SvtMePicParams *params, uint32_t fields, const SvtMePicResults *src, uint32_t b64_index,
+                         uint8_t *dst_total, uint32_t *dst_mv, uint8_t *dst_cand);
 typedef struct SvtMePackedLayout {
     size_t bytes;   /* size of one picture's block */
     size_t off[15]; /* byte offset of each SvtMePicResults member, in member order; (size_t)-1 = not part of the block */
 } SvtMePackedLayout;
 uint32_t svtme_packed_layout(uint32_t width, uint32_t height, const SvtMePicParams *params, uint32_t fields,
-                             SvtMePackedLayout *out);
+                             SvtMePackedLayout *out); /* fields may include SVTME_F_SB_COMPACT */
 void     svtme_packed_view(const SvtMePackedLayout *layout, void *block, SvtMePicResults *out);
 uint32_t svtme_picture_me_batch_packed(SvtMeSession *s, uint32_t n, const int32_t *pic_ids, const SvtMePicParams *params,
                                        uint32_t fields, void *host_slab, size_t host_slab_bytes, int sync);

@@ -153,12 +153,18 @@ class MePicResults(C.Structure):
 
 
 F_SB_RESULTS, F_STATS, F_SEARCH_RESULTS, F_BEST, F_WINDOWS, F_ALL = 1, 2, 4, 8, 16, 31
+F_SB_COMPACT = 32  # me_mv_array / me_candidate_array rows at the picture's own strides (SbStrides)
 ABSENT = (1 << (8 * C.sizeof(C.c_size_t))) - 1
 
 
 class PackedLayout(C.Structure):
     """SvtMePackedLayout: block size and the offset of each SvtMePicResults member (ABSENT = not part of the block)"""
     _fields_ = [("bytes", C.c_size_t), ("off", C.c_size_t * 15)]
+
+
+class SbStrides(C.Structure):
+    """SvtMeSbStrides"""
+    _fields_ = [("mv_stride", C.c_uint8), ("mv_l1_offset", C.c_uint8), ("cand_stride", C.c_uint8), ("n_pus", C.c_uint8)]
 
 
 class DevicePlane(C.Structure):
@@ -201,17 +207,20 @@ class PicResultArrays:
     )
 
     @staticmethod
-    def shapes_of(width, height, params):
+    def shapes_of(width, height, params, strides=None):
+        """strides: SbStrides of a compact block (rows of the two MeSbResults arrays at the picture's own strides)"""
         n = n_b64_of(width, height)
         n_pus = PU_COUNT if params.enable_me_8x8 else 21
+        mv_stride = strides.mv_stride if strides is not None else max(1, params.max_refs)
+        cand_stride = strides.cand_stride if strides is not None else max(1, params.max_cand)
         return n, n_pus, {
             "p_sb_best_sad": ((n, 2, 4, 85), np.uint32),
             "p_sb_best_mv": ((n, 2, 4, 85), np.uint32),
             "search_results": ((n, 2, 4), SEARCH_RESULT_DTYPE),
             "me_windows": ((n, 2, 4), WINDOW_DTYPE),
             "total_me_candidate_index": ((n, n_pus), np.uint8),
-            "me_mv_array": ((n, n_pus * max(1, params.max_refs)), np.uint32),
-            "me_candidate_array": ((n, n_pus * max(1, params.max_cand)), np.uint8),
+            "me_mv_array": ((n, n_pus * mv_stride), np.uint32),
+            "me_candidate_array": ((n, n_pus * cand_stride), np.uint8),
             "me_64x64_distortion": ((n,), np.uint32),
             "me_32x32_distortion": ((n,), np.uint32),
             "me_16x16_distortion": ((n,), np.uint32),
@@ -222,10 +231,10 @@ class PicResultArrays:
             "rc_me_allow_gm": ((n,), np.uint8),
         }
 
-    def __init__(self, width, height, params, pinned=False, block=None, layout=None):
+    def __init__(self, width, height, params, pinned=False, block=None, layout=None, strides=None):
         """block + layout: views into one picture's block of a packed result slab (svtme_picture_me_batch_packed) instead
-        of arrays of their own; members the layout does not hold are None"""
-        n, n_pus, shapes = self.shapes_of(width, height, params)
+        of arrays of their own; members the layout does not hold are None; strides: the block is compact"""
+        n, n_pus, shapes = self.shapes_of(width, height, params, strides)
         self.n_b64, self.n_pus = n, n_pus
         self.struct = MePicResults()
         self._keep = []

@@ -107,6 +107,10 @@ def lib():
         L.svtme_batch_results_release.restype = C.c_uint32
         L.svtme_copy_from_device.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]
         L.svtme_copy_from_device.restype = C.c_uint32
+        L.svtme_sb_strides.argtypes = [C.POINTER(abi.MePicParams), C.c_uint32, C.POINTER(abi.SbStrides)]
+        L.svtme_sb_strides.restype = None
+        L.svtme_sb_expand_b64.argtypes = [C.POINTER(abi.MePicParams), C.c_uint32, C.POINTER(abi.MePicResults), C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.svtme_sb_expand_b64.restype = None
         L.svtme_host_alloc.argtypes = [C.c_size_t]
         L.svtme_host_alloc.restype = C.c_void_p
         L.svtme_host_free.argtypes = [C.c_void_p]
@@ -253,6 +257,21 @@ class Session:
         caller keeps (no per-call marshalling), slab_ptr: host memory of slab_bytes bytes (pinned for an asynchronous copy)"""
         _check(lib().svtme_picture_me_batch_packed(self._h, n, ids_array, params_array, fields, slab_ptr, slab_bytes, 1 if sync else 0),
                "svtme_picture_me_batch_packed")
+
+    @staticmethod
+    def sb_strides(params, fields):
+        st = abi.SbStrides()
+        lib().svtme_sb_strides(C.byref(params), fields, C.byref(st))
+        return st
+
+    @staticmethod
+    def sb_expand(params, fields, res, out):
+        """compact block arrays `res` -> `out` (PicResultArrays with the reference's strides), b64 by b64 through the C helper"""
+        n_pus = 85 if params.enable_me_8x8 else 21
+        for b in range(out.n_b64):
+            lib().svtme_sb_expand_b64(C.byref(params), fields, C.byref(res.struct), b, out.total_me_candidate_index[b].ctypes.data,
+                                      out.me_mv_array[b].ctypes.data, out.me_candidate_array[b].ctypes.data)
+        return out
 
     def set_result_fields(self, fields):
         _check(lib().svtme_session_set_result_fields(self._h, fields), "svtme_session_set_result_fields")

@@ -53,6 +53,42 @@ static size_t rf_bytes(int f, size_t n_b64, size_t n_pus, size_t max_refs, size_
     default: return n_b64 * 4;
     }
 }
+extern "C" void svtme_sb_strides(const SvtMePicParams *pp, uint32_t fields, SvtMeSbStrides *out) {
+    out->n_pus = pp->enable_me_8x8 ? 85 : 21;
+    out->mv_stride = pp->max_refs; out->mv_l1_offset = pp->max_l0; out->cand_stride = pp->max_cand;
+    if (!(fields & SVTME_F_SB_COMPACT)) return;
+    const uint32_t n0 = pp->num_of_ref_pic_to_search[0], n1 = pp->num_of_list_to_search > 1 ? pp->num_of_ref_pic_to_search[1] : 0;
+    // construct_me_candidate_array* (motion_estimation.c:2602-2905): unipred of every reference, then the bipred pairs
+    uint32_t cand = n0 + n1;
+    if (n1) cand += pp->only_l_bwd ? 1u : n0 * n1 + (n0 - 1u) + (n1 == 3 ? 1u : 0u);
+    if (cand < 1) cand = 1;
+    if (cand < out->cand_stride) out->cand_stride = (uint8_t)cand;
+    if (n0 + n1 >= 1 && n0 + n1 <= out->mv_stride) { out->mv_stride = (uint8_t)(n0 + n1); out->mv_l1_offset = (uint8_t)n0; }
+}
+
+extern "C" void svtme_sb_expand_b64(const SvtMePicParams *pp, uint32_t fields, const SvtMePicResults *src, uint32_t b, uint8_t *dst_total,
+                                    uint32_t *dst_mv, uint8_t *dst_cand) {
+    SvtMeSbStrides st;
+    svtme_sb_strides(pp, fields, &st);
+    const size_t np = st.n_pus;
+    memcpy(dst_total, src->total_me_candidate_index + (size_t)b * np, np);
+    if (st.mv_stride == pp->max_refs && st.mv_l1_offset == pp->max_l0 && st.cand_stride == pp->max_cand) {
+        memcpy(dst_mv, src->me_mv_array + (size_t)b * np * pp->max_refs, np * pp->max_refs * 4);
+        memcpy(dst_cand, src->me_candidate_array + (size_t)b * np * pp->max_cand, np * pp->max_cand);
+        return;
+    }
+    memset(dst_mv, 0, np * pp->max_refs * 4);
+    memset(dst_cand, 0, np * pp->max_cand);
+    const uint32_t *mv = src->me_mv_array + (size_t)b * np * st.mv_stride;
+    const uint8_t  *cd = src->me_candidate_array + (size_t)b * np * st.cand_stride;
+    const uint32_t n0 = st.mv_l1_offset, n1 = st.mv_stride - st.mv_l1_offset;
+    for (size_t pu = 0; pu < np; pu++) {
+        memcpy(dst_mv + pu * pp->max_refs, mv + pu * st.mv_stride, n0 * 4);
+        memcpy(dst_mv + pu * pp->max_refs + pp->max_l0, mv + pu * st.mv_stride + n0, n1 * 4);
+        memcpy(dst_cand + pu * pp->max_cand, cd + pu * st.cand_stride, st.cand_stride);
+    }
+}
+
 static void packed_layout(size_t n_b64, size_t n_pus, size_t max_refs, size_t max_cand, uint32_t fields, SvtMePackedLayout *L) {
     size_t o = 0;
     for (int f = 0; f < RF_COUNT; f++) L->off[f] = (size_t)-1;
@@ -708,7 +744,7 @@ extern "C" uint32_t svtme_session_reserve(SvtMeSession *s, const SvtMePicParams 
 }
 
 extern "C" uint32_t svtme_session_set_result_fields(SvtMeSession *s, uint32_t fields) {
-    if (!s || (fields & ~SVTME_F_ALL)) return SVTME_ERR_BAD_PARAMETER;
+    if (!s || (fields & ~(SVTME_F_ALL | SVTME_F_SB_COMPACT))) return SVTME_ERR_BAD_PARAMETER;
     std::lock_guard<std::mutex> g(s->mu);
     s->default_fields = fields;
     return SVTME_OK;
@@ -716,9 +752,11 @@ extern "C" uint32_t svtme_session_set_result_fields(SvtMeSession *s, uint32_t fi
 
 extern "C" uint32_t svtme_packed_layout(uint32_t width, uint32_t height, const SvtMePicParams *params, uint32_t fields,
                                         SvtMePackedLayout *out) {
-    if (!params || !out || !width || !height || (fields & ~SVTME_F_ALL) || params->max_refs > 8 || params->max_cand > 32) return SVTME_ERR_BAD_PARAMETER;
+    if (!params || !out || !width || !height || (fields & ~(SVTME_F_ALL | SVTME_F_SB_COMPACT)) || params->max_refs > 8 || params->max_cand > 32) return SVTME_ERR_BAD_PARAMETER;
     const size_t n_b64 = (size_t)((width + 63) / 64) * ((height + 63) / 64);
-    packed_layout(n_b64, params->enable_me_8x8 ? 85 : 21, params->max_refs, params->max_cand, fields, out);
+    SvtMeSbStrides st;
+    svtme_sb_strides(params, fields, &st);
+    packed_layout(n_b64, st.n_pus, st.mv_stride, st.cand_stride, fields, out);
     return SVTME_OK;
 }
 
@@ -764,8 +802,10 @@ static uint32_t launch_me_batch(SvtMeSession *s, uint32_t n, const int32_t *pic_
     std::vector<SvtMePackedLayout> lay(n);
     std::vector<size_t> base(n);
     size_t total = 0;
+    std::vector<SvtMeSbStrides> strides(n);
     for (uint32_t i = 0; i < n; i++) {
-        packed_layout((size_t)s->n_b64, params[i].enable_me_8x8 ? 85 : 21, params[i].max_refs, params[i].max_cand, fields[i], &lay[i]);
+        svtme_sb_strides(&params[i], fields[i], &strides[i]);
+        packed_layout((size_t)s->n_b64, strides[i].n_pus, strides[i].mv_stride, strides[i].cand_stride, fields[i], &lay[i]);
         base[i] = total;
         total += lay[i].bytes;
     }
@@ -774,7 +814,7 @@ static uint32_t launch_me_batch(SvtMeSession *s, uint32_t n, const int32_t *pic_
     s->batch_seq = seq;
     bo.seq = seq; bo.me = true; bo.lay.swap(lay); bo.base.swap(base); bo.total = total;
     bo.geo.resize(n);
-    for (uint32_t i = 0; i < n; i++) bo.geo[i] = {(size_t)(params[i].enable_me_8x8 ? 85 : 21), (size_t)params[i].max_refs, (size_t)params[i].max_cand};
+    for (uint32_t i = 0; i < n; i++) bo.geo[i] = {(size_t)strides[i].n_pus, (size_t)strides[i].mv_stride, (size_t)strides[i].cand_stride};
     cudaStream_t cs = compute_stream(s, set);
     if (s->dl_recorded[set]) CU_TRY(cudaStreamWaitEvent(cs, s->ev_dl[set], 0)); // the set's previous results left for the host
     if (s->release_recorded[set]) { CU_TRY(cudaStreamWaitEvent(cs, s->ev_release[set], 0)); s->release_recorded[set] = false; } // ... and its device-side readers are done
@@ -801,6 +841,7 @@ static uint32_t launch_me_batch(SvtMeSession *s, uint32_t n, const int32_t *pic_
             }
         job.pic_w = s->w; job.pic_h = s->h; job.b64_cols = s->b64_cols; job.b64_rows = s->b64_rows; job.n_b64 = s->n_b64;
         job.n_pus = pp->enable_me_8x8 ? 85 : 21;
+        job.mv_stride = strides[i].mv_stride; job.mv_l1_off = strides[i].mv_l1_offset; job.cand_stride = strides[i].cand_stride;
         uint8_t *R = s->res_sets[set][i];
         uint8_t *D = s->dl_region[set] + bo.base[i];
         const SvtMePackedLayout &L = bo.lay[i];
@@ -933,14 +974,16 @@ extern "C" uint32_t svtme_picture_me_batch(SvtMeSession *s, uint32_t n, const in
 
 extern "C" uint32_t svtme_picture_me_batch_packed(SvtMeSession *s, uint32_t n, const int32_t *pic_ids, const SvtMePicParams *params,
                                                   uint32_t fields, void *host_slab, size_t host_slab_bytes, int sync) {
-    if (!s || n == 0 || n > 4096 || !host_slab || !fields || (fields & ~SVTME_F_ALL)) return SVTME_ERR_BAD_PARAMETER;
+    if (!s || n == 0 || n > 4096 || !host_slab || !(fields & SVTME_F_ALL) || (fields & ~(SVTME_F_ALL | SVTME_F_SB_COMPACT))) return SVTME_ERR_BAD_PARAMETER;
     std::lock_guard<std::mutex> g(s->mu);
     { // the slab must hold the batch before anything is queued
         size_t total = 0;
         SvtMePackedLayout L;
         for (uint32_t i = 0; i < n; i++) {
             if (params[i].max_refs > 8 || params[i].max_cand > 32) return SVTME_ERR_BAD_PARAMETER;
-            packed_layout((size_t)s->n_b64, params[i].enable_me_8x8 ? 85 : 21, params[i].max_refs, params[i].max_cand, fields, &L);
+            SvtMeSbStrides st;
+            svtme_sb_strides(&params[i], fields, &st);
+            packed_layout((size_t)s->n_b64, st.n_pus, st.mv_stride, st.cand_stride, fields, &L);
             total += L.bytes;
         }
         if (total > host_slab_bytes) return SVTME_ERR_BAD_PARAMETER;

@@ -89,7 +89,7 @@ struct PicJob {
     DevPic         src;
     DevPic         ref[2][4];
     int            pic_w, pic_h, b64_cols, b64_rows, n_b64, n_pus;
-    int            reserved_[3];
+    int            mv_stride, mv_l1_off, cand_stride; // row geometry of me_mv_array / me_candidate_array as they are written (svtme_sb_strides)
     // device buffers
     SbState       *sb_state;   // [n_b64]
     uint32_t      *best_sad;   // [n_b64][2][4][85]

@@ -135,15 +135,17 @@ __global__ void __launch_bounds__(POST_THREADS) k_post(const PicJob *__restrict_
     // ---- candidate construction: thread n = ME z-order PU index ----
     const uint32_t n_pus  = (uint32_t)job.n_pus;
     const bool want_sb = job.total_me_candidate_index != nullptr, want_stats = job.me_64x64_distortion != nullptr;
+    // row geometry of the two MeSbResults arrays: the reference's (max_refs, max_l0, max_cand) or this picture's own (SVTME_F_SB_COMPACT)
+    const uint32_t mv_stride = (uint32_t)job.mv_stride, mv_l1 = (uint32_t)job.mv_l1_off, cand_stride = (uint32_t)job.cand_stride;
     uint8_t  *o_total = sh.total; // built in shared memory, stored at the end
     uint32_t *o_mv    = sh.mv;
     uint8_t  *o_cand  = sh.cand;
     auto write_sb_results = [&]() {
         if (!want_sb) return;
         post_store_bytes(job.total_me_candidate_index + (size_t)b * n_pus, sh.total, n_pus, tid);
-        uint32_t *g_mv = job.me_mv_array + (size_t)b * n_pus * pp.max_refs;
-        for (uint32_t i = tid; i < n_pus * pp.max_refs; i += POST_THREADS) g_mv[i] = sh.mv[i];
-        post_store_bytes(job.me_candidate_array + (size_t)b * n_pus * pp.max_cand, sh.cand, n_pus * pp.max_cand, tid);
+        uint32_t *g_mv = job.me_mv_array + (size_t)b * n_pus * mv_stride;
+        for (uint32_t i = tid; i < n_pus * mv_stride; i += POST_THREADS) g_mv[i] = sh.mv[i];
+        post_store_bytes(job.me_candidate_array + (size_t)b * n_pus * cand_stride, sh.cand, n_pus * cand_stride, tid);
     };
     auto write_search_results = [&]() {
         if (tid >= 8) return;
@@ -162,8 +164,8 @@ __global__ void __launch_bounds__(POST_THREADS) k_post(const PicJob *__restrict_
     };
     if (mctf) { // the temporal filter consumes p_sb_best_sad / p_sb_best_mv and SearchResults only
         for (uint32_t i = tid; i < n_pus; i += POST_THREADS) o_total[i] = 0;
-        for (uint32_t i = tid; i < n_pus * pp.max_refs; i += POST_THREADS) o_mv[i] = 0;
-        for (uint32_t i = tid; i < n_pus * pp.max_cand; i += POST_THREADS) o_cand[i] = 0;
+        for (uint32_t i = tid; i < n_pus * mv_stride; i += POST_THREADS) o_mv[i] = 0;
+        for (uint32_t i = tid; i < n_pus * cand_stride; i += POST_THREADS) o_cand[i] = 0;
         if (tid == 0 && want_stats) {
             job.me_64x64_distortion[b] = job.me_32x32_distortion[b] = job.me_16x16_distortion[b] = job.me_8x8_distortion[b] = 0;
             job.rc_me_distortion[b] = job.me_8x8_cost_variance[b] = 0;
@@ -184,8 +186,8 @@ __global__ void __launch_bounds__(POST_THREADS) k_post(const PicJob *__restrict_
     // the two special builders start from memset(total_me_candidate_index, 1, number_of_pus) (:2625, :2734)
     const uint8_t total_init = (nref[0] == 1 && nref[1] <= 1) ? 1 : 0;
     for (uint32_t i = tid; i < n_pus; i += POST_THREADS) o_total[i] = total_init;
-    for (uint32_t i = tid; i < n_pus * pp.max_refs; i += POST_THREADS) o_mv[i] = 0;
-    for (uint32_t i = tid; i < n_pus * pp.max_cand; i += POST_THREADS) o_cand[i] = 0;
+    for (uint32_t i = tid; i < n_pus * mv_stride; i += POST_THREADS) o_mv[i] = 0;
+    for (uint32_t i = tid; i < n_pus * cand_stride; i += POST_THREADS) o_cand[i] = 0;
     __syncthreads();
     if (tid < 85) {
         const uint32_t n   = (uint32_t)tid;
@@ -195,8 +197,8 @@ __global__ void __launch_bounds__(POST_THREADS) k_post(const PicJob *__restrict_
             const uint8_t pu = c_z_to_raster[n];
             sh.me_distortion[pu] = BS(0, 0, n);
             if (sh.do_ref[0][0] && use) {
-                o_cand[pu * pp.max_cand] = cand_byte(0, 0, 0, 0, 0);
-                o_mv[pu * pp.max_refs]   = BM(0, 0, n);
+                o_cand[pu * cand_stride] = cand_byte(0, 0, 0, 0, 0);
+                o_mv[pu * mv_stride]   = BM(0, 0, n);
             }
         } else if (nref[0] == 1 && nref[1] == 1) {
             // construct_me_candidate_array_mrp_off
@@ -222,17 +224,17 @@ __global__ void __launch_bounds__(POST_THREADS) k_post(const PicJob *__restrict_
                     }
                 }
                 if (min_list != -1 && min_list != (int)l) {
-                    if (use) o_mv[pu * pp.max_refs + (l ? pp.max_l0 : 0)] = BM(l, 0, n);
+                    if (use) o_mv[pu * mv_stride + (l ? mv_l1 : 0)] = BM(l, 0, n);
                     continue;
                 }
                 if (use) {
-                    o_cand[pu * pp.max_cand + off]                  = cand_byte(l, 0, 0, l == 0 ? l : 24, l == 1 ? l : 24);
-                    o_mv[pu * pp.max_refs + (l ? pp.max_l0 : 0)] = BM(l, 0, n);
+                    o_cand[pu * cand_stride + off]                  = cand_byte(l, 0, 0, l == 0 ? l : 24, l == 1 ? l : 24);
+                    o_mv[pu * mv_stride + (l ? mv_l1 : 0)] = BM(l, 0, n);
                 }
                 off++;
             }
             if (doref[0] && doref[1] && use) {
-                o_cand[pu * pp.max_cand + off] = cand_byte(2, 0, 0, 0, 1);
+                o_cand[pu * cand_stride + off] = cand_byte(2, 0, 0, 0, 1);
                 o_total[pu]                    = (uint8_t)(off + 1);
             }
         } else {
@@ -260,8 +262,8 @@ __global__ void __launch_bounds__(POST_THREADS) k_post(const PicJob *__restrict_
                         }
                     }
                     if (use) {
-                        o_cand[pu * pp.max_cand + off]                       = cand_byte(l, r, r, l == 0 ? l : 24, l == 1 ? l : 24);
-                        o_mv[pu * pp.max_refs + (l ? pp.max_l0 : 0) + r] = BM(l, r, n);
+                        o_cand[pu * cand_stride + off]                       = cand_byte(l, r, r, l == 0 ? l : 24, l == 1 ? l : 24);
+                        o_mv[pu * mv_stride + (l ? mv_l1 : 0) + r] = BM(l, r, n);
                     }
                     off++;
                 }
@@ -269,12 +271,12 @@ __global__ void __launch_bounds__(POST_THREADS) k_post(const PicJob *__restrict_
                 for (uint32_t a = 0; a < nref[0]; a++)
                     for (uint32_t bb = 0; bb < nref[1]; bb++) {
                         if (pp.only_l_bwd && (a > 0 || bb > 0)) continue;
-                        if (doref[0][a] && doref[1][bb]) o_cand[pu * pp.max_cand + off++] = cand_byte(2, a, bb, 0, 1);
+                        if (doref[0][a] && doref[1][bb]) o_cand[pu * cand_stride + off++] = cand_byte(2, a, bb, 0, 1);
                     }
                 if (!pp.only_l_bwd) {
                     for (uint32_t a = 1; a < nref[0]; a++)
-                        if (doref[0][0] && doref[0][a]) o_cand[pu * pp.max_cand + off++] = cand_byte(2, 0, a, 0, 0);
-                    if (nref[1] == 3 && doref[1][0] && doref[1][2]) o_cand[pu * pp.max_cand + off++] = cand_byte(2, 0, 2, 1, 1);
+                        if (doref[0][0] && doref[0][a]) o_cand[pu * cand_stride + off++] = cand_byte(2, 0, a, 0, 0);
+                    if (nref[1] == 3 && doref[1][0] && doref[1][2]) o_cand[pu * cand_stride + off++] = cand_byte(2, 0, 2, 1, 1);
                 }
             }
             if (use) o_total[pu] = off;
@@ -320,7 +322,7 @@ __global__ void __launch_bounds__(POST_THREADS) k_post(const PicJob *__restrict_
             for (unsigned i = 0; i < n_blk; i++) {
                 uint8_t n = (uint8_t)((low_res ? 21 : 5) + i);
                 if (low_res && !pp.enable_me_8x8) n = (uint8_t)(5 + ((i >> 3) >> 1) * 4 + ((i & 7) >> 1));
-                const uint8_t  cb  = o_cand[n * pp.max_cand];
+                const uint8_t  cb  = o_cand[n * cand_stride];
                 const unsigned dir = cb & 3;
                 const uint32_t l = (dir == 0 || dir == 2) ? ((cb >> 6) & 1) : ((cb >> 7) & 1);
                 const uint32_t r = (dir == 0 || dir == 2) ? ((cb >> 2) & 3) : ((cb >> 4) & 3);

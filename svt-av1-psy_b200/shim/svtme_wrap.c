@@ -54,6 +54,8 @@ typedef struct ShimJob {
     int             pending; /* queued by svtme_shim_submit_pictures: wait for batch `seq` before the first read */
     uint64_t        seq;
     uint8_t         max_refs, max_cand;
+    uint32_t        fields;  /* result groups of `res` (SVTME_F_SB_COMPACT: rows at the picture's own strides) */
+    SvtMePicParams  params;
     SvtMePicResults res;
     SvtMeHmeState  *hme; /* ME_MCTF only (tf_exit) */
     void           *mem;
@@ -326,6 +328,8 @@ static ShimJob *shim_new_job(const void *pcs, int me_type, uint64_t ref_number, 
     j->stamp = g.clock;
     j->used = 1; j->pcs = pcs; j->me_type = me_type; j->ref_number = ref_number;
     j->n_b64 = n_b64; j->n_pus = p->enable_me_8x8 ? 85 : 21; j->max_refs = p->max_refs; j->max_cand = p->max_cand;
+    j->params = *p;
+    j->fields = SVTME_F_SB_RESULTS | SVTME_F_STATS | SVTME_F_SEARCH_RESULTS | SVTME_F_BEST;
     if (!own_arrays) return j; /* the caller points j->res into a batch slab */
     const size_t n = n_b64, npu = j->n_pus;
     const size_t sz[] = {n * 680 * 4, n * 680 * 4, n * 8 * sizeof(SvtMeSearchResult), n * npu, n * npu * j->max_refs * 4,
@@ -440,10 +444,9 @@ EbErrorType __wrap_svt_aom_motion_estimation_b64(PictureParentControlSet *pcs, u
         if (j->hme[b64_index].tf_exit) me_ctx->tf_use_pred_64x64_only_th = (uint8_t)~0;
     } else {
         MeSbResults *sb = pcs->pa_me_data->me_results[b64_index];
-        const size_t np = j->n_pus;
-        memcpy(sb->total_me_candidate_index, r->total_me_candidate_index + b64_index * np, np);
-        memcpy(sb->me_mv_array, r->me_mv_array + (size_t)b64_index * np * j->max_refs, np * j->max_refs * 4);
-        memcpy(sb->me_candidate_array, r->me_candidate_array + (size_t)b64_index * np * j->max_cand, np * j->max_cand);
+        /* this b64's rows at the reference's strides (a batch downloads them at the picture's own, narrower strides) */
+        svtme_sb_expand_b64(&j->params, j->fields, r, b64_index, sb->total_me_candidate_index, (uint32_t *)sb->me_mv_array,
+                            (uint8_t *)sb->me_candidate_array);
         pcs->me_64x64_distortion[b64_index]         = r->me_64x64_distortion[b64_index];
         pcs->me_32x32_distortion[b64_index]         = r->me_32x32_distortion[b64_index];
         pcs->me_16x16_distortion[b64_index]         = r->me_16x16_distortion[b64_index];
@@ -520,7 +523,7 @@ void svtme_shim_submit_pictures(PictureParentControlSet **pcs_list, uint32_t n) 
     }
     if (k) {
         /* what the b64 calls hand out: the MeSbResults arrays and PCS statistics, plus the MeContext members */
-        const uint32_t   fields = SVTME_F_SB_RESULTS | SVTME_F_STATS | SVTME_F_SEARCH_RESULTS | SVTME_F_BEST;
+        const uint32_t   fields = SVTME_F_SB_RESULTS | SVTME_F_SB_COMPACT | SVTME_F_STATS | SVTME_F_SEARCH_RESULTS | SVTME_F_BEST;
         SvtMePackedLayout *lay  = (SvtMePackedLayout *)calloc(k, sizeof(SvtMePackedLayout));
         ShimBatch         *bt   = (ShimBatch *)calloc(1, sizeof(ShimBatch));
         if (!lay || !bt) shim_fatal("allocation", 0);
@@ -535,7 +538,8 @@ void svtme_shim_submit_pictures(PictureParentControlSet **pcs_list, uint32_t n) 
         size_t at = 0;
         for (uint32_t i = 0; i < k; i++) {
             svtme_packed_view(&lay[i], (uint8_t *)bt->slab + at, &jobs[i]->res);
-            jobs[i]->batch = bt;
+            jobs[i]->batch  = bt;
+            jobs[i]->fields = fields;
             at += lay[i].bytes;
         }
         SHIM_CHECK(svtme_picture_me_batch_packed(g.sess, k, ids, params, fields, bt->slab, total, /*sync*/ 0));

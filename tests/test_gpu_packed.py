@@ -50,6 +50,22 @@ def test_packed_layout_is_dense_and_ordered():
     assert me.lib().svtme_packed_layout(w, h, C.byref(p), 64, C.byref(lay)) == abi.ERR_BAD_PARAMETER
 
 
+def test_compact_strides():
+    """the picture's own strides: n0 + n1 vectors and the candidates construct_me_candidate_array* can emit"""
+    p = abi.MePicParams()
+    p.enable_me_8x8, p.max_refs, p.max_cand, p.max_l0 = 1, 7, 23, 4
+    p.num_of_list_to_search = 2
+    for n0, n1, only_l_bwd, want in [(4, 3, 1, (7, 4, 8)), (4, 3, 0, (7, 4, 23)), (2, 1, 1, (3, 2, 4)), (2, 2, 0, (4, 2, 9)), (1, 1, 1, (2, 1, 3))]:
+        p.num_of_ref_pic_to_search[0], p.num_of_ref_pic_to_search[1], p.only_l_bwd = n0, n1, only_l_bwd
+        st = me.Session.sb_strides(p, abi.F_SB_RESULTS | abi.F_SB_COMPACT)
+        assert (st.mv_stride, st.mv_l1_offset, st.cand_stride) == want and st.n_pus == 85
+        st = me.Session.sb_strides(p, abi.F_SB_RESULTS)
+        assert (st.mv_stride, st.mv_l1_offset, st.cand_stride) == (7, 4, 23)
+    p.num_of_list_to_search, p.num_of_ref_pic_to_search[0], p.num_of_ref_pic_to_search[1] = 1, 1, 0
+    st = me.Session.sb_strides(p, abi.F_SB_COMPACT)
+    assert (st.mv_stride, st.mv_l1_offset, st.cand_stride) == (1, 1, 1)
+
+
 def _batch(n_pics=5):
     """n_pics pictures of one stream (one session): sources, references, parameters with slot ids"""
     src0, refs0, pocs, poc, enc_mode, kw = case_inputs(CASES[0])  # 320x192 preset 4, 4+3 references
@@ -206,4 +222,41 @@ def test_device_resident_view(orc):
     s.me_batch_packed(ids_a, prm_a, n, fields, slab.data_ptr(), slab.numel(), sync=True)
     with pytest.raises(me.binding.SvtMeError):
         s.acquire_results(seq, 0, consumer.cuda_stream)
+    s.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", [CASES[0], CASES[3], CASES[4], CASES[6], CASES[7]], ids=lambda c: "%dx%d_M%d" % (c[0], c[1], c[2]))
+def test_compact_wire_format_expands_to_the_oracle(orc, case):
+    """SVTME_F_SB_COMPACT: fewer bytes cross PCIe, svtme_sb_expand_b64 gives the reference's arrays back (general, MRP,
+    mrp-off and single-reference candidate builders, only_l_bwd on and off)"""
+    import torch
+    src, refs, pocs, poc, enc_mode, kw = case_inputs(case)
+    h, w = src.shape
+    params = params_from_encoder_inputs(src, refs, pocs, poc, enc_mode, **kw)
+    want, _, _ = orc_me(src, refs, params, debug=False)
+    s = me.Session(w, h, max_pictures=12)
+    s.upload(0, src)
+    p = copy.copy(params)
+    pid = 1
+    for l in range(len(refs)):
+        for r, plane in enumerate(refs[l]):
+            s.upload(pid, plane)
+            p.ref_pic_id[l][r] = pid
+            pid += 1
+    fields = abi.F_SB_RESULTS | abi.F_SB_COMPACT | abi.F_STATS
+    lay, full = s.packed_layout(p, fields), s.packed_layout(p, abi.F_SB_RESULTS | abi.F_STATS)
+    st = me.Session.sb_strides(p, fields)
+    assert lay.bytes <= full.bytes
+    if st.cand_stride < p.max_cand or st.mv_stride < p.max_refs:
+        assert lay.bytes < full.bytes
+    slab = torch.zeros(lay.bytes, dtype=torch.uint8).pin_memory()
+    s.me_batch_packed((C.c_int32 * 1)(0), (abi.MePicParams * 1)(p), 1, fields, slab.data_ptr(), slab.numel(), sync=True)
+    got_c = abi.PicResultArrays(w, h, p, block=slab.numpy(), layout=lay, strides=st)
+    got = me.Session.sb_expand(p, fields, got_c, abi.PicResultArrays(w, h, p))
+    for f in ("total_me_candidate_index", "me_mv_array", "me_candidate_array"):
+        np.testing.assert_array_equal(getattr(got, f), getattr(want, f), err_msg=f)
+    for f in got_c.FIELDS:
+        if group_of(f) == abi.F_STATS:
+            np.testing.assert_array_equal(getattr(got_c, f), getattr(want, f), err_msg=f)
     s.close()
