@@ -172,6 +172,7 @@ class Runner:
         self.h2d = self.d2h = 0
         self.pics = 0
         self.host_batches = 0
+        self.call_s = 0.0
         self.probe = "full"
 
     def params(self, plan):
@@ -267,6 +268,7 @@ class Runner:
         """the C calls of one step: batched uploads, ONE launch sequence, (host) ONE download of the whole batch"""
         L = self.me.lib()
         h = self.sess._h
+        t_call = time.perf_counter()
         for kind, k, slots, ptrs in sp.uploads:
             fn = L.svtme_picture_upload_batch if kind == "host8" else (L.svtme_picture_upload_10bit_batch if kind == "host10" else L.svtme_picture_upload_device_batch)
             rc = fn(h, k, slots, ptrs, self.wl.w)
@@ -275,7 +277,9 @@ class Runner:
         self.h2d += sp.h2d
         if host and self.probe != "h2d":
             k = self.host_batches & 1
+            t_wait = time.perf_counter()
             self.sess.wait_batch(self.seqs[k])  # this slab's previous results are in host memory (and consumed) before reuse
+            t_call += time.perf_counter() - t_wait  # waiting for the pipeline is not host work
             self.sess.me_batch_packed(sp.ids, sp.prm, sp.n, self.fields, self.slabs[k].data_ptr(), self.slab_bytes)
             self.seqs[k] = self.sess.batch_seq()
             self.host_batches += 1
@@ -285,6 +289,7 @@ class Runner:
             if rc:
                 raise RuntimeError("svtme_picture_me_batch failed 0x%x" % rc)
         self.pics += sp.n
+        self.call_s += time.perf_counter() - t_call  # host time inside the library's entry points (queueing the step)
 
     def step(self, step_index, host):
         sp = self.plan_step(step_index, host)
@@ -357,13 +362,15 @@ def measure(wl, frames, rank, world, local, a, steps, warmup, sampler, detail):
             run.setup_slabs(plans[0])
         barrier()
         run.pics = run.h2d = run.d2h = 0
+        run.call_s = 0.0
         l0 = run.sess.launch_count()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         t0 = time.time()
         e0.record()
         for sp in plans:
             run.run_step(sp, host)
-        run.host_ms = (time.time() - t0) * 1e3 / n_steps  # host time to queue one step (no waiting unless the pipeline is full)
+        run.host_ms = (time.time() - t0) * 1e3 / n_steps  # host wall time per step of the queueing loop (includes waiting for a free result slab / job array when the pipeline is full)
+        run.host_call_ms = run.call_s * 1e3 / n_steps     # of which inside the library's entry points, waits excluded
         run.sess.sync()  # every stream of the session: uploads, kernels (two compute streams) and downloads are done
         e1.record()
         barrier()
@@ -406,7 +413,8 @@ def measure(wl, frames, rank, world, local, a, steps, warmup, sampler, detail):
         base += min(warmup, 2)
         ms_e, pics_e, _ = timed(True, base, steps, sampler)
         return {"value": world * pics_e / (ms_e * 1e-3), "unit": "frames/s", "h2d_bytes_per_step": int(run.h2d // max(1, steps)),
-                "d2h_bytes_per_step": int(run.d2h // max(1, steps)), "ms_per_step": ms_e / steps, "host_queue_ms_per_step": run.host_ms}, base + steps
+                "d2h_bytes_per_step": int(run.d2h // max(1, steps)), "ms_per_step": ms_e / steps, "host_queue_ms_per_step": run.host_ms,
+                "host_call_ms_per_step": run.host_call_ms}, base + steps
 
     base = warmup + steps + t_steps
     # the two MeSbResults arrays cross PCIe at the picture's own strides (SVTME_F_SB_COMPACT: 8 instead of 23 candidate bytes
