@@ -47,6 +47,7 @@ def parse_args():
     ap.add_argument("--cpu-baseline-s", type=float, default=12.0, help="wall-time budget of the bounded CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extra-configs", action="store_true", help="skip the short runs of the other BASELINE.json configurations")
+    ap.add_argument("--extra-configs", default="4k,8k,m-2,streams", help="which of the other BASELINE.json configurations to run (comma list)")
     return ap.parse_args()
 
 
@@ -173,6 +174,7 @@ class Runner:
         self.pics = 0
         self.host_batches = 0
         self.call_s = 0.0
+        self.upload16 = True  # 10-bit workloads: upload the 16-bit samples (split on the device) / the 8-MSB plane the encoder keeps
         self.probe = "full"
 
     def params(self, plan):
@@ -219,7 +221,7 @@ class Runner:
             f = poc % wl.n_frames
             if host and self.probe == "d2h":
                 kind, ptr = "device", self.frames_dev[f].data_ptr()
-            elif host and self.frames16 is not None:
+            elif host and self.frames16 is not None and self.upload16:
                 kind, ptr = "host10", self.frames16[f].data_ptr()
                 sp.h2d += 2 * wl.w * wl.h
             elif host:
@@ -420,6 +422,12 @@ def measure(wl, frames, rank, world, local, a, steps, warmup, sampler, detail):
     # the two MeSbResults arrays cross PCIe at the picture's own strides (SVTME_F_SB_COMPACT: 8 instead of 23 candidate bytes
     # per PU at this preset); a consumer expands a b64's rows with svtme_sb_expand_b64 when it copies them into pa_me_data
     out["e2e"], base = e2e_pass(consumer | abi.F_SB_COMPACT, base)
+    if wl.bits == 10:
+        # the encoder itself hands ME the 8-MSB plane of a 10-bit picture (its PA reference buffers are 8-bit, reference_object.c:327):
+        # the same pass with that plane as the host input instead of the 16-bit samples (half the H2D bytes)
+        run.upload16 = False
+        out["e2e_msb_planes"], base = e2e_pass(consumer | abi.F_SB_COMPACT, base)
+        run.upload16 = True
     if detail:  # the same with the MeContext members (p_sb_best_sad / p_sb_best_mv, search_results) crossing PCIe too
         out["e2e_all"], base = e2e_pass(consumer | abi.F_BEST | abi.F_SEARCH_RESULTS, base)
         run.sess.set_result_fields(consumer)
@@ -610,6 +618,7 @@ def extra_configs(a, rank, world, local):
             "workload": wl.name, "value": round(m["value"], 2), "unit": "frames/s", "steps": steps, "warmup": warmup,
             "pictures_per_step": wl.mgop, "ms_per_step": round(m["ms_per_step"], 4),
             "e2e": {k: (round(v, 3) if isinstance(v, float) else v) for k, v in m["e2e"].items()},
+            **({"e2e_msb_planes": {k: (round(v, 3) if isinstance(v, float) else v) for k, v in m["e2e_msb_planes"].items()}} if "e2e_msb_planes" in m else {}),
             "roofline_int": {"whole_step_frac": round((ops[0] + ops[1]) / n_timed * m["pics"] / (m["ms"] * 1e-3) / int_peak, 4),
                              "hme_stage_frac": round(ops[0] / (m["hme_ms"] * 1e-3) / int_peak, 4) if m["hme_ms"] else None,
                              "fullpel_stage_frac": round(ops[1] / (m["fp_ms"] * 1e-3) / int_peak, 4) if m["fp_ms"] else None,
@@ -620,12 +629,15 @@ def extra_configs(a, rank, world, local):
             "clocks": clocks,
         }
 
-    one("3840x2160 10-bit preset 4", 3840, 2160, 10, 4, 96, 6, 3)
-    if world == 1:
-        one("7680x4320 8-bit preset 2", 7680, 4320, 8, 2, 48, 3, 3)
-        one("1920x1080 8-bit preset -2", 1920, 1080, 8, -2, 96, 3, 3)
-    if 16 % world == 0:
+    want = set(a.extra_configs.split(","))
+    if 16 % world == 0 and "streams" in want:  # first: sixteen sessions are created before the large configurations have churned device memory
         out["16 concurrent 1920x1080 streams"] = streams16(a, rank, world, local)
+    if "4k" in want:
+        one("3840x2160 10-bit preset 4", 3840, 2160, 10, 4, 96, 6, 3)
+    if world == 1 and "8k" in want:
+        one("7680x4320 8-bit preset 2", 7680, 4320, 8, 2, 48, 3, 3)
+    if world == 1 and "m-2" in want:
+        one("1920x1080 8-bit preset -2", 1920, 1080, 8, -2, 96, 3, 3)
     return out
 
 

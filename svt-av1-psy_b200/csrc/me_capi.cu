@@ -1121,7 +1121,8 @@ extern "C" uint32_t svtme_dg_detector_hme(SvtMeSession *s, int32_t src_pic_id, i
     memset(&job, 0, sizeof(job));
     job.pp.ctrls.hme_search_method = SVTME_FULL_SAD_SEARCH; // :501
     job.src = s->pics[src_pic_id];
-    job.ref[0][0] = s->pics[ref_pic_id];
+    for (int l = 0; l < 2; l++) // the bands of a window occupy the job slots of all eight (list, ref) groups: all of them search this reference
+        for (int r = 0; r < 4; r++) job.ref[l][r] = s->pics[ref_pic_id];
     s->slot_last_seq[src_pic_id] = s->slot_last_seq[ref_pic_id] = seq;
     job.pic_w = s->w; job.pic_h = s->h; job.b64_cols = s->b64_cols; job.b64_rows = s->b64_rows; job.n_b64 = s->n_b64;
     uint8_t *R = s->res_sets[set][0];

@@ -245,26 +245,36 @@ struct DgOut { // device mirror of SvtMeDgMetrics' outputs
     int                sum_in_vectors;
 };
 
-// one lane per b64: window of its 16x16 block (:410-455), job + tiles for k_search16
+// one lane per b64: window of its 16x16 block (:410-455). The window is cut into bands of one tile height, one job and one
+// queue unit per band (slots 4k of the b64's eight (list, ref) groups, which this search does not use otherwise): a pair
+// of pictures has only n_b64 windows, and a unit is searched by one warp, so the bands are what keeps every SM busy.
 __global__ void __launch_bounds__(128) k_dg_build(const PicJob *__restrict__ jobs, int sa0) {
     const PicJob &job = jobs[0];
     const int b = blockIdx.x * blockDim.x + threadIdx.x;
     if (b >= job.n_b64) return;
     const B64Geo    g   = b64_geo(job, b);
     const DevPlane &ref = job.ref[0][0].lvl[2];
-    HmeJobG &j = job.hme_jobs[(size_t)b * HME_JOBS_PER_B64];
+    HmeJobG *jb = job.hme_jobs + (size_t)b * HME_JOBS_PER_B64;
+    HmeJobG J;
     int16_t sa_w = (int16_t)((sa0 + 7) & ~0x07), sa_h = (int16_t)sa0;
     const int16_t ox = (int16_t)(-(sa_w >> 1)), oy = (int16_t)(-(sa_h >> 1));
-    ctl_make_job(j, ref, (int16_t)(g.org_x >> 2), (int16_t)(g.org_y >> 2), ox, oy, sa_w, sa_h, (int16_t)(ref.org_x - 1),
+    ctl_make_job(J, ref, (int16_t)(g.org_x >> 2), (int16_t)(g.org_y >> 2), ox, oy, sa_w, sa_h, (int16_t)(ref.org_x - 1),
                  (int16_t)(ref.org_y - 1), true, 16, 16);
-    // one unit per b64 (slots 1..3 of its group are never active here: the slab's job records start zeroed and the
-    // picture pipeline leaves every job it posted inactive)
-    job.hme_jobs[(size_t)b * HME_JOBS_PER_B64 + 1].active = 0;
-    job.hme_jobs[(size_t)b * HME_JOBS_PER_B64 + 2].active = 0;
-    job.hme_jobs[(size_t)b * HME_JOBS_PER_B64 + 3].active = 0;
-    if (j.n_tx && j.n_ty) {
-        const uint32_t at = atomicAdd(&job.s16_counters[0], 1u);
-        if (at < job.s16_units_cap) job.s16_units[at] = make_uint2(0u, (uint32_t)(b * HME_JOBS_PER_B64));
+    const int band_h = J.tile_h, n_bands = J.sa_w > 0 && J.sa_h > 0 ? imin(8, (J.sa_h + band_h - 1) / band_h) : 0;
+    for (int k = 0; k < HME_JOBS_PER_B64; k++) jb[k].active = 0;
+    if (!n_bands) { // an empty window (cannot happen with the detector's sizes): the record k_dg_reduce falls back to
+        jb[0] = J;
+        jb[0].active = 0;
+    }
+    uint32_t at = n_bands ? atomicAdd(&job.s16_counters[0], (uint32_t)n_bands) : 0u;
+    for (int k = 0; k < n_bands; k++) {
+        HmeJobG Jk = J;
+        Jk.py = (int16_t)(J.py + k * band_h);
+        Jk.origin_y = (int16_t)(J.origin_y + k * band_h);
+        Jk.sa_h = (int16_t)(k + 1 == n_bands ? J.sa_h - k * band_h : band_h); // (8 bands of 18 rows hold the largest window: 128 rows)
+        Jk.n_ty = (uint8_t)((Jk.sa_h + band_h - 1) / band_h);
+        jb[4 * k] = Jk;
+        if (at + k < job.s16_units_cap) job.s16_units[at + k] = make_uint2(0u, (uint32_t)(b * HME_JOBS_PER_B64 + 4 * k));
     }
 }
 
@@ -274,10 +284,22 @@ __global__ void __launch_bounds__(128) k_dg_reduce(const PicJob *__restrict__ jo
     const PicJob &job = jobs[0];
     const int b = blockIdx.x * blockDim.x + threadIdx.x;
     if (b >= job.n_b64) return;
-    const HmeJobG &j = job.hme_jobs[(size_t)b * HME_JOBS_PER_B64];
-    uint64_t sad = 0;
+    const HmeJobG *jb = job.hme_jobs + (size_t)b * HME_JOBS_PER_B64;
+    // first minimum in raster order over the bands: bands are consecutive row ranges, so a tie goes to the earlier band
+    uint64_t sad = 0xffffff;
     int16_t  col = 0, row = 0;
-    ctl_job_result(j, false, 4, sad, col, row);
+    bool     found = false;
+    for (int k = 0; k < 8; k++) {
+        const HmeJobG &j = jb[4 * k];
+        if (!j.active || (uint32_t)j.key == 0xffffffffu) continue;
+        uint64_t s = 0;
+        int16_t  c = 0, r = 0;
+        ctl_job_result(j, false, 4, s, c, r);
+        if (!found || s < sad) { sad = s; col = c; row = r; found = true; }
+    }
+    if (!found) { // no position was evaluated: the reference's initial values (pd_process.c:470-486 with svt_sad_loop_kernel's 0xffffff)
+        ctl_job_result(jb[0], false, 4, sad, col, row);
+    }
     b64_sad[b] = sad;
     b64_mv[2 * b] = col; b64_mv[2 * b + 1] = row;
     const int bx = b % job.b64_cols, by = b / job.b64_cols, cols = job.b64_cols, rows = job.b64_rows;
@@ -294,7 +316,7 @@ __global__ void __launch_bounds__(128) k_dg_reduce(const PicJob *__restrict__ jo
 
 uint32_t svtme_dg_units_cap(int sa0, int n_b64) {
     (void)sa0;
-    return (uint32_t)n_b64; // one unit per b64
+    return (uint32_t)(8 * n_b64); // at most eight bands per b64
 }
 
 int svtme_launch_dg_detector(const PicJob *h_job, const PicJob *d_job, int sa0, void *d_out, unsigned long long *d_b64_sad,
