@@ -383,6 +383,11 @@ uint32_t svtme_picture_me_batch_packed(SvtMeSession *s, uint32_t n, const int32_
                                        uint32_t fields, void *host_slab, size_t host_slab_bytes, int sync);
 /* Fields produced by calls that name no host arrays (svtme_picture_me_device, results == NULL): default SVTME_F_ALL. */
 uint32_t svtme_session_set_result_fields(SvtMeSession *s, uint32_t fields);
+/* Work granularity of the 1/16-plane searches (pre-HME, HME level 0): 0 = one queue unit per (b64, list, ref), its jobs and
+   tiles searched by one warp (large batches: least per-unit work); 1 = one unit per job (small batches: a single picture
+   has too few (b64, list, ref) groups to occupy every warp of the GPU); -1 = chosen per batch from its size (default).
+   Results do not depend on it. */
+uint32_t svtme_session_set_unit_granularity(SvtMeSession *s, int mode);
 /* Size the unit queues, result slabs and job arrays for batches of up to n_pictures pictures with these controls now,
    instead of growing them (with a pipeline drain) when the first such batch arrives. */
 uint32_t svtme_session_reserve(SvtMeSession *s, const SvtMePicParams *params, uint32_t n_pictures);

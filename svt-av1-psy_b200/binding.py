@@ -97,6 +97,8 @@ def lib():
         L.svtme_picture_me_batch_packed.restype = C.c_uint32
         L.svtme_session_set_result_fields.argtypes = [C.c_void_p, C.c_uint32]
         L.svtme_session_set_result_fields.restype = C.c_uint32
+        L.svtme_session_set_unit_granularity.argtypes = [C.c_void_p, C.c_int]
+        L.svtme_session_set_unit_granularity.restype = C.c_uint32
         L.svtme_session_reserve.argtypes = [C.c_void_p, C.POINTER(abi.MePicParams), C.c_uint32]
         L.svtme_session_reserve.restype = C.c_uint32
         L.svtme_picture_device_planes.argtypes = [C.c_void_p, C.c_int32, C.POINTER(abi.DevicePlane)]
@@ -275,6 +277,10 @@ class Session:
 
     def set_result_fields(self, fields):
         _check(lib().svtme_session_set_result_fields(self._h, fields), "svtme_session_set_result_fields")
+
+    def set_unit_granularity(self, mode):
+        """-1 auto, 0 one k_search16 unit per (b64, list, ref), 1 one per job"""
+        _check(lib().svtme_session_set_unit_granularity(self._h, mode), "svtme_session_set_unit_granularity")
 
     def reserve(self, params, n_pictures):
         _check(lib().svtme_session_reserve(self._h, C.byref(params), n_pictures), "svtme_session_reserve")

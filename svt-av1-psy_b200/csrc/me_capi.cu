@@ -152,6 +152,7 @@ struct SvtMeSession {
     uint8_t     *dl_region[2] = {nullptr, nullptr};
     size_t       dl_cap[2] = {0, 0};
     uint32_t     default_fields = SVTME_F_ALL;
+    int          s16_unit_mode = -1; // svtme_session_set_unit_granularity
     uint32_t    *h_flags = nullptr; // pinned: [set] = the set's unit-queue overflow flag as of its last download
     cudaEvent_t  ev_release[2] = {}; // device-resident consumers of a set (svtme_batch_results_release)
     bool         release_recorded[2] = {false, false};
@@ -743,6 +744,13 @@ extern "C" uint32_t svtme_session_reserve(SvtMeSession *s, const SvtMePicParams 
     return SVTME_OK;
 }
 
+extern "C" uint32_t svtme_session_set_unit_granularity(SvtMeSession *s, int mode) {
+    if (!s || mode < -1 || mode > 1) return SVTME_ERR_BAD_PARAMETER;
+    std::lock_guard<std::mutex> g(s->mu);
+    s->s16_unit_mode = mode;
+    return SVTME_OK;
+}
+
 extern "C" uint32_t svtme_session_set_result_fields(SvtMeSession *s, uint32_t fields) {
     if (!s || (fields & ~(SVTME_F_ALL | SVTME_F_SB_COMPACT))) return SVTME_ERR_BAD_PARAMETER;
     std::lock_guard<std::mutex> g(s->mu);
@@ -874,6 +882,9 @@ static uint32_t launch_me_batch(SvtMeSession *s, uint32_t n, const int32_t *pic_
         job.s16_units     = s->s16_units + (size_t)set * s->s16_units_cap;
         job.s16_counters  = (uint32_t *)(s->res_sets[set][0] + s->lay.fp_counters) + 4;
         job.s16_units_cap = s->s16_units_cap;
+        // units of k_search16 = (b64, list, ref) groups when the batch has enough of them to occupy the GPU several times over
+        // (~3000 resident warps), single jobs otherwise
+        job.s16_split = s->s16_unit_mode >= 0 ? s->s16_unit_mode : ((size_t)n * s->n_b64 * 8 < 24000 ? 1 : 0);
     }
     CU_TRY(cudaMemcpyAsync(d_jobs, h_jobs, sizeof(PicJob) * n, cudaMemcpyHostToDevice, cs));
     CU_TRY(cudaEventRecord(s->ev_jobs[jslot], cs));

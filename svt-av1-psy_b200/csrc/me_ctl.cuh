@@ -70,14 +70,17 @@ __device__ inline void ctl_make_job(HmeJobG &j, const DevPlane &ref, int16_t org
 __device__ inline void ctl_enqueue_units(const PicJob &job, bool has_work, int b) {
     const int      lane  = threadIdx.x & 31;
     const uint32_t work  = __ballot_sync(0xffffffffu, has_work);
-    const bool     lead  = (lane & 3) == 0 && ((work >> lane) & 0xfu) != 0; // first lane of a (list, ref) group with work
+    // small batches (one picture, a temporal-filter pair): every job is a unit of its own (bit 31 of the record), so that
+    // a few hundred b64s still spread over all warps of the GPU
+    const bool     lead  = job.s16_split ? has_work : ((lane & 3) == 0 && ((work >> lane) & 0xfu) != 0); // else: first lane of a (list, ref) group with work
     const uint32_t leads = __ballot_sync(0xffffffffu, lead);
     if (!leads) return;
     uint32_t base = 0;
     const int first = __ffs(leads) - 1;
     if (lane == first) base = atomicAdd(&job.s16_counters[0], (uint32_t)__popc(leads)); // one atomic per warp (the counter is shared by the batch)
     base = __shfl_sync(0xffffffffu, base, first) + (uint32_t)__popc(leads & ((1u << lane) - 1u));
-    if (lead && base < job.s16_units_cap) job.s16_units[base] = make_uint2(blockIdx.y, (uint32_t)(b * HME_JOBS_PER_B64 + lane));
+    if (lead && base < job.s16_units_cap)
+        job.s16_units[base] = make_uint2(blockIdx.y, (uint32_t)(b * HME_JOBS_PER_B64 + lane) | (job.s16_split ? 0x80000000u : 0u));
 }
 
 // key -> (sad, centre); centre keeps its value when no position was evaluated

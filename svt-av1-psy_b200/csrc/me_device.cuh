@@ -113,6 +113,7 @@ struct PicJob {
     uint2              *s16_units;    // unit queue of k_search16: x = picture in batch, y = (job slot in picture << 8) | tile
     uint32_t           *s16_counters; // [0] number of units, [1] queue head
     uint32_t            s16_units_cap;
+    int                 s16_split;    // 1: k_hme_ctl makes every 1/16-plane job a queue unit of its own (small batches)
 };
 
 // ------------------------------------------------------------------------------------------

@@ -342,7 +342,7 @@ int svtme_launch_dg_detector(const PicJob *h_job, const PicJob *d_job, int sa0, 
 
 uint32_t svtme_s16_units_cap(const SvtMePicParams &pp, int n_b64) {
     (void)pp;
-    return (uint32_t)(8 * n_b64); // one unit per (b64, list, ref) and stage
+    return (uint32_t)(32 * n_b64); // one unit per (b64, list, ref) and stage, or one per job slot in small batches
 }
 
 uint32_t svtme_fp_units_cap(const SvtMePicParams &pp, int n_b64) {

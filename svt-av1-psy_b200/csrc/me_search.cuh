@@ -391,9 +391,11 @@ __device__ __forceinline__ void s16_next_unit(const PicJob *__restrict__ jobs, u
     c.u = 0;
     if (ui >= n_units) return;
     const uint2 rec = jobs[0].s16_units[ui];
-    c.pic = (int)rec.x; c.slot0 = (int)rec.y;
+    const bool single = (rec.y >> 31) != 0; // the unit is ONE job (small batches), not the four slots of a (list, ref)
+    const int  slot   = (int)(rec.y & 0x7fffffffu);
+    c.pic = (int)rec.x; c.slot0 = slot & ~3;
     bool has = false;
-    if (lane < 4) {
+    if (lane < 4 && (!single || lane == (slot & 3))) {
         const HmeJobG &j = jobs[c.pic].hme_jobs[c.slot0 + lane];
         has = j.active && j.merged != 2 && j.n_tx && j.n_ty && j.sa_w > 0 && j.sa_h > 0;
     }

@@ -266,3 +266,20 @@ def test_two_compute_streams_give_the_same_results():
     for ba, bb in zip(a, b):
         for ra, rb in zip(ba, bb):
             compare(ra, rb, fields=list(ra.FIELDS))
+
+
+@pytest.mark.parametrize("case", [CASES[0], CASES[2], CASES[3], CASES[4], CASES[8]], ids=case_id)
+@pytest.mark.parametrize("mode", [0, 1])
+def test_unit_granularity_does_not_change_results(case, mode):
+    """k_search16 walks (b64, list, ref) groups in large batches and single jobs in small ones: both against the oracle"""
+    src, refs, pocs, poc, enc_mode, kw = case_inputs(case)
+    params = params_from_encoder_inputs(src, refs, pocs, poc, enc_mode, **kw)
+    want, dbg, ops = orc_me(src, refs, params)
+    h, w = src.shape
+    s = me.Session(w, h, max_pictures=12)
+    s.set_unit_granularity(mode)
+    got, st = gpu_me(src, refs, params, session=s)
+    s.close()
+    compare_hme_state(st, dbg, params)
+    compare(want, got, fields=list(got.FIELDS))
+    assert got.sad_ops == ops
