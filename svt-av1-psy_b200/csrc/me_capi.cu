@@ -357,6 +357,7 @@ extern "C" uint32_t svtme_session_set_stream(SvtMeSession *s, void *cuda_stream)
     cudaSetDevice(s->device);
     CU_TRY(cudaStreamSynchronize(s->up_stream));
     CU_TRY(cudaStreamSynchronize(s->stream));
+    CU_TRY(cudaStreamSynchronize(s->stream2));
     CU_TRY(cudaStreamSynchronize(s->dl_stream));
     if (s->own_stream) cudaStreamDestroy(s->stream);
     s->stream     = (cudaStream_t)cuda_stream;
