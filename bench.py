@@ -39,7 +39,7 @@ def parse_args():
     ap.add_argument("--bits", type=int, default=8, choices=[8, 10])
     ap.add_argument("--frames", type=int, default=240, help="length of the synthetic clip")
     ap.add_argument("--concurrency", type=int, default=2, choices=[1, 2], help="compute streams per session (svtme_session_set_concurrency)")
-    ap.add_argument("--e2e-probe", default="full", choices=["full", "h2d", "d2h"], help="diagnostic: drop one direction of the end-to-end copies")
+    ap.add_argument("--e2e-probe", default="full", choices=["full", "h2d", "d2h", "upload"], help="diagnostic: drop one direction of the end-to-end copies; upload = host uploads and pyramid builds only, no ME")
     ap.add_argument("--host-numa", default="auto", choices=["auto", "off"],
                     help="auto: run this rank's threads on (or, failing that, bind its memory to) the NUMA node of its GPU, so that "
                          "the pinned frames and result arrays it allocates are local to the GPU's PCIe root")
@@ -102,6 +102,8 @@ class ClockSampler:
     def start(self):
         """nvidia-smi takes ~1 s to produce its first line: started once, before the warm-up; samples are
         stamped on arrival and only those that fall inside a timed window are reported."""
+        if os.environ.get("SVTME_NO_SAMPLER"):  # diagnostic: is the polling itself disturbing the copies?
+            return
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
                                           "-lms", "20"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
@@ -277,6 +279,10 @@ class Runner:
             if rc:
                 raise RuntimeError("upload failed 0x%x" % rc)
         self.h2d += sp.h2d
+        if host and self.probe == "upload":
+            self.pics += sp.n
+            self.call_s += time.perf_counter() - t_call
+            return
         if host and self.probe != "h2d":
             k = self.host_batches & 1
             t_wait = time.perf_counter()

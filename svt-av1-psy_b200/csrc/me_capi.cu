@@ -887,7 +887,7 @@ static uint32_t launch_me_batch(SvtMeSession *s, uint32_t n, const int32_t *pic_
         // (~3000 resident warps), single jobs otherwise
         job.s16_split = s->s16_unit_mode >= 0 ? s->s16_unit_mode : ((size_t)n * s->n_b64 * 8 < 24000 ? 1 : 0);
     }
-    CU_TRY(cudaMemcpyAsync(d_jobs, h_jobs, sizeof(PicJob) * n, cudaMemcpyHostToDevice, cs));
+    svtme_launch_copy_from_pinned(d_jobs, h_jobs, sizeof(PicJob) * n, cs); // a kernel, not a copy-engine transfer (me_kernels.cu)
     CU_TRY(cudaEventRecord(s->ev_jobs[jslot], cs));
     s->jobs_used[jslot] = true;
     cudaEvent_t e0 = nullptr, e1 = nullptr, e2 = nullptr;
@@ -1143,7 +1143,7 @@ extern "C" uint32_t svtme_dg_detector_hme(SvtMeSession *s, int32_t src_pic_id, i
     job.s16_counters  = (uint32_t *)(R + s->lay.fp_counters) + 4;
     job.fp_counters   = (uint32_t *)(R + s->lay.fp_counters);
     job.s16_units_cap = s->s16_units_cap;
-    CU_TRY(cudaMemcpyAsync(d_job, &job, sizeof(PicJob), cudaMemcpyHostToDevice, cs));
+    svtme_launch_copy_from_pinned(d_job, &job, sizeof(PicJob), cs);
     CU_TRY(cudaEventRecord(s->ev_jobs[jslot], cs));
     s->jobs_used[jslot] = true;
     uint8_t *d_out = R + s->lay.ops + 32;

@@ -84,7 +84,7 @@ struct FpJobG {
 };
 
 // everything one picture's kernels need; passed by value as a __grid_constant__ parameter
-struct PicJob {
+struct alignas(16) PicJob { // a multiple of 16 bytes: the job array is fetched by a kernel in 16-byte words
     SvtMePicParams pp;
     DevPic         src;
     DevPic         ref[2][4];
@@ -115,6 +115,8 @@ struct PicJob {
     uint32_t            s16_units_cap;
     int                 s16_split;    // 1: k_hme_ctl makes every 1/16-plane job a queue unit of its own (small batches)
 };
+
+static_assert(sizeof(PicJob) % 16 == 0, "PicJob is copied in 16-byte words");
 
 // ------------------------------------------------------------------------------------------
 // small helpers

@@ -38,4 +38,7 @@ int  svtme_launch_kat_octet(const uint8_t *d_src, int src_stride, const uint8_t 
 int  svtme_encode_tmap(void *out, const void *base, size_t pitch, size_t rows, uint32_t box_w, uint32_t box_h);
 int  svtme_launch_kat_nxm(const uint8_t *d_src, int src_stride, const uint8_t *d_ref, int ref_stride, int h, int w,
                           uint32_t *d_out, cudaStream_t st);
+void svtme_launch_zero_words(void *d_p, int n_words, cudaStream_t st);
+// dst: device memory, src: pinned host memory (device-visible under unified addressing); sizes rounded up to 16 bytes
+void svtme_launch_copy_from_pinned(void *d_dst, const void *h_src, size_t bytes, cudaStream_t st);
 int  svtme_launch_fill32(uint32_t *d_p, uint32_t n, uint32_t v, cudaStream_t st);

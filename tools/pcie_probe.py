@@ -4,8 +4,10 @@ can at best reach when every rank moves its frames up and its results down throu
 
   python -m torch.distributed.run --nproc-per-node 8 --master-addr 127.0.0.1 tools/pcie_probe.py
 
-Each active rank copies 64 MB pinned buffers (H2D only, D2H only, both directions on two streams) for ~0.5 s per phase,
-timed with CUDA events; rank 0 prints per-GPU and aggregate GB/s for every k. No kernels of this repository run here."""
+Each active rank copies 64 MB chunks (H2D only, D2H only, both directions on two streams), walking through 512 MB of
+pinned host memory per direction so that the host side of every copy is DRAM traffic as in the bench (a single 64 MB
+buffer copied over and over is served from the CPU's last-level cache and overstates what eight ranks can get), timed
+with CUDA events; rank 0 prints per-GPU and aggregate GB/s for every k. No kernels of this repository run here."""
 import json
 import os
 
@@ -21,8 +23,10 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     nbytes = 64 << 20
-    h_up = torch.empty(nbytes, dtype=torch.uint8).pin_memory()
-    h_dn = torch.empty(nbytes, dtype=torch.uint8).pin_memory()
+    n_chunks = 8
+    h_up = torch.empty(nbytes * n_chunks, dtype=torch.uint8).pin_memory()
+    h_dn = torch.empty(nbytes * n_chunks, dtype=torch.uint8).pin_memory()
+    h_up.fill_(1)
     d_up = torch.empty(nbytes, dtype=torch.uint8, device="cuda")
     d_dn = torch.empty(nbytes, dtype=torch.uint8, device="cuda")
     s_up, s_dn = torch.cuda.Stream(), torch.cuda.Stream()
@@ -42,13 +46,14 @@ def main():
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
             if active:
-                for _ in range(reps):
+                for i in range(reps):
+                    c = (i % n_chunks) * nbytes
                     if mode in ("h2d", "both"):
                         with torch.cuda.stream(s_up):
-                            d_up.copy_(h_up, non_blocking=True)
+                            d_up.copy_(h_up[c:c + nbytes], non_blocking=True)
                     if mode in ("d2h", "both"):
                         with torch.cuda.stream(s_dn):
-                            h_dn.copy_(d_dn, non_blocking=True)
+                            h_dn[c:c + nbytes].copy_(d_dn, non_blocking=True)
             s_up.synchronize()
             s_dn.synchronize()
             torch.cuda.current_stream().wait_stream(s_up)
@@ -64,7 +69,7 @@ def main():
             out["k=%d %s" % (k, mode)] = {"per_gpu_GBps_each_direction": round(agg / k, 2),
                                           "aggregate_GBps": round(agg * (2 if mode == "both" else 1), 1)}
     if rank == 0:
-        print(json.dumps({"pcie_probe": out, "n_gpus": world, "buffer_MB": nbytes >> 20}, indent=1))
+        print(json.dumps({"pcie_probe": out, "n_gpus": world, "chunk_MB": nbytes >> 20, "host_MB_per_direction": (nbytes * n_chunks) >> 20}, indent=1))
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
