@@ -153,13 +153,14 @@ class Runner:
     """Drives one Session through consecutive mini-GOPs of a stream (this rank's shard)."""
     N_SLOTS = 192  # picture store: slot = poc % N_SLOTS; references reach at most 4 mini-GOPs back
 
-    def __init__(self, wl, rank, world, frames_host, device, fields):
+    def __init__(self, wl, rank, world, frames_host, device, fields, own_stream=False):
         import torch
         import svtme_b200 as me
         from svt_av1_psy_b200 import abi
         self.wl, self.rank, self.world, self.me, self.abi, self.torch = wl, rank, world, me, abi, torch
         self.sess = me.Session(wl.w, wl.h, max_pictures=self.N_SLOTS, device=device)
-        self.sess.set_stream(torch.cuda.current_stream().cuda_stream)
+        if not own_stream:  # own_stream: the session keeps the compute stream it created (several sessions run concurrently on the GPU)
+            self.sess.set_stream(torch.cuda.current_stream().cuda_stream)
         self.frames_pinned = torch.from_numpy(frames_host).pin_memory()
         self.frames_dev = self.frames_pinned.to("cuda", non_blocking=False)
         self.frames16 = None
@@ -301,6 +302,9 @@ class Runner:
 
     def step(self, step_index, host):
         sp = self.plan_step(step_index, host)
+        if not getattr(self, "reserved", False):  # queues, result regions and job arrays sized once, before anything is timed
+            self.sess.reserve(sp.prm[0], self.wl.mgop)
+            self.reserved = True
         if host and self.slabs is None:
             self.setup_slabs(sp)
         self.run_step(sp, host)
@@ -659,7 +663,7 @@ def streams16(a, rank, world, local):
     b.width, b.height, b.bits, b.preset, b.frames = 1920, 1080, 8, 4, 64
     wl = Workload(b)
     fields = abi.F_SB_RESULTS | abi.F_SB_COMPACT | abi.F_STATS
-    runs = [Runner(wl, 0, 1, make_clip(wl, 100 + rank * per_rank + k), local, fields) for k in range(per_rank)]
+    runs = [Runner(wl, 0, 1, make_clip(wl, 100 + rank * per_rank + k), local, fields, own_stream=True) for k in range(per_rank)]
     steps, warmup = 3, 3
     res = {}
     smp = ClockSampler(local)
