@@ -28,20 +28,39 @@ struct CtlOp {
     uint32_t build_mask;
 };
 
-// tile geometry of a 1/16-plane search: shared by the builder (device) and the queue bound (host)
-__host__ __device__ inline void s16_tile_geometry(int sa_w, int sa_h, int *tile_w, int *tile_h, int *n_tx, int *n_ty, int *wide) {
+// tile geometry of a 1/16-plane search: shared by the builder (device) and the detector / known-answer launchers (host).
+// vb_shape: the block is 16 wide, 8 rows two apart (the production shape). The wide tile's box holds 18 search rows; a
+// window is cut into tiles of 18, 16 or 12 rows, whichever leaves the evaluators (s16_eval_choice) the fewest warp
+// instructions: 96 x 80 positions are 5 tiles of 16 rows (3 full passes of the two-row blocked evaluator each) instead
+// of 4 x 18 + 8 (3 passes of the three-row one at 3/4 occupancy each), 64 x 48 are 4 x 12 instead of 18 + 18 + 12.
+__host__ __device__ inline void s16_tile_geometry(int sa_w, int sa_h, int *tile_w, int *tile_h, int *n_tx, int *n_ty, int *wide,
+                                                  bool vb_shape = false, bool vb2 = false) {
     *wide = sa_w > S16T_TILE_W;
     *tile_w = *wide ? S16W_TILE_W : S16T_TILE_W;
     *tile_h = *wide ? S16W_TILE_H : S16T_TILE_H;
     if (sa_w <= 0 || sa_h <= 0) { *n_tx = 0; *n_ty = 0; return; }
     *n_tx = (sa_w + *tile_w - 1) / *tile_w;
+    if (*wide && vb_shape && sa_h > 12) {
+        int best_cost = 1 << 30;
+        for (int h = S16W_TILE_H; h >= 12; h = h == 18 ? 16 : h - 4) { // 18, 16, 12
+            int cost = 0;
+            for (int tx = 0; tx < *n_tx; tx++) {
+                const int tw = (sa_w - tx * *tile_w) < *tile_w ? (sa_w - tx * *tile_w) : *tile_w;
+                int c_full = 0, c_rem = 0;
+                s16_eval_choice(tw, h, 16, 8, 2, false, true, vb2, &c_full);
+                if (sa_h % h) s16_eval_choice(tw, sa_h % h, 16, 8, 2, false, true, vb2, &c_rem);
+                cost += (sa_h / h) * (c_full + 150) + (sa_h % h ? c_rem + 150 : 0); // + the per-tile work (load, cursor, reduction)
+            }
+            if (cost < best_cost) { best_cost = cost; *tile_h = h; }
+        }
+    }
     *n_ty = (sa_h + *tile_h - 1) / *tile_h;
 }
 
 // window clamp + plane address shared by prehme_core and hme_level_0/1/2
 __device__ inline void ctl_make_job(HmeJobG &j, const DevPlane &ref, int16_t org_x, int16_t org_y, int16_t origin_x,
                                     int16_t origin_y, int16_t sa_w, int16_t sa_h, int16_t pad_w, int16_t pad_h,
-                                    bool round_w8, int rows, int bw) {
+                                    bool round_w8, int rows, int bw, bool vb_rows = false, bool vb2 = false) {
     clamp_axis(org_x, origin_x, sa_w, pad_w, (int16_t)ref.width);
     if (round_w8) sa_w = (int16_t)((sa_w < 8) ? sa_w : sa_w & ~0x07);
     clamp_axis(org_y, origin_y, sa_h, pad_h, (int16_t)ref.height);
@@ -49,7 +68,7 @@ __device__ inline void ctl_make_job(HmeJobG &j, const DevPlane &ref, int16_t org
     const int16_t y_tl = (int16_t)(((int16_t)ref.org_y + org_y) + origin_y);
     j.sa_w = sa_w; j.sa_h = sa_h; j.origin_x = origin_x; j.origin_y = origin_y;
     int tw, th, ntx, nty, wide;
-    s16_tile_geometry(sa_w, sa_h, &tw, &th, &ntx, &nty, &wide);
+    s16_tile_geometry(sa_w, sa_h, &tw, &th, &ntx, &nty, &wide, bw == 16 && rows == 8 && vb_rows, vb2);
     j.tile_w = (uint16_t)tw; j.tile_h = (uint16_t)th; j.n_tx = (uint8_t)ntx; j.n_ty = (uint8_t)nty; j.wide = (uint8_t)wide;
     j.px = x_tl; j.py = y_tl;
     // the block the job compares: offset of its top-left sample in the SOURCE plane of the same level (all planes of a
@@ -318,7 +337,7 @@ __global__ void __launch_bounds__(32 * CTL_WARPS) k_hme_ctl(const PicJob *__rest
             const int16_t h = (int16_t)(uint16_t)min((uint32_t)c.prehme_sa_cfg[s].sa_min.height * factor, (uint32_t)c.prehme_sa_cfg[s].sa_max.height);
             const DevPlane &rf = job.ref[l][r].lvl[2];
             ctl_make_job(j, rf, (int16_t)(ox16 >> 2), (int16_t)(oy16 >> 2), (int16_t)(-(int16_t)(w >> 1)), (int16_t)(-(int16_t)(h >> 1)),
-                         w, h, (int16_t)(rf.org_x - 1), (int16_t)(rf.org_y - 1), false, rows0, bw0);
+                         w, h, (int16_t)(rf.org_x - 1), (int16_t)(rf.org_y - 1), false, rows0, bw0, sub, false);
             const bool sk = c.prehme_skip_search_line && bw0 == 16 && rows0 <= 16;
             if (j.sa_w > 0 && j.sa_h > 0) ops += (unsigned long long)j.sa_w * (sk ? j.sa_h / 2 : j.sa_h) * bw0 * rows0;
             s16_work = j.n_tx && j.n_ty;
@@ -367,7 +386,7 @@ __global__ void __launch_bounds__(32 * CTL_WARPS) k_hme_ctl(const PicJob *__rest
             const int16_t oy = (int16_t)(-(int16_t)((sh0 * c.num_hme_sa_h) >> 1) + (int16_t)(sh0 * qb));
             const DevPlane &rf = job.ref[l][r].lvl[2];
             ctl_make_job(j, rf, (int16_t)(ox16 >> 2), (int16_t)(oy16 >> 2), ox, oy, w, sh0, (int16_t)(rf.org_x - 1),
-                         (int16_t)(rf.org_y - 1), true, rows0, bw0);
+                         (int16_t)(rf.org_y - 1), true, rows0, bw0, sub, true);
             if (j.sa_w > 0 && j.sa_h > 0) ops += (unsigned long long)j.sa_w * j.sa_h * bw0 * rows0;
             l0_built = true; // enqueued below, once the four quadrants of a reference know whether they merge
         }
@@ -430,7 +449,7 @@ __global__ void __launch_bounds__(32 * CTL_WARPS) k_hme_ctl(const PicJob *__rest
         if (grid) {
             if (q == 0) {
                 int tw, th, ntx, nty, wide;
-                s16_tile_geometry(v_w[0] + v_w[1], v_h[0] + v_h[2], &tw, &th, &ntx, &nty, &wide);
+                s16_tile_geometry(v_w[0] + v_w[1], v_h[0] + v_h[2], &tw, &th, &ntx, &nty, &wide, j.bw == 16 && j.rows == 8 && sub, true);
                 j.merged = 1; j.m_w = (int16_t)(v_w[0] + v_w[1]); j.m_h = (int16_t)(v_h[0] + v_h[2]);
                 j.tile_w = (uint16_t)tw; j.tile_h = (uint16_t)th; j.n_tx = (uint8_t)ntx; j.n_ty = (uint8_t)nty; j.wide = (uint8_t)wide;
                 s16_work = ntx && nty;

@@ -234,7 +234,8 @@ static void opt_in_shared_memory() {
     cudaGetDevice(&dev);
     if (done_for == dev) return;
     const int blk2 = SEARCH_WARPS * 2 * TM_L2_BUF + 128, blk1 = SEARCH_WARPS * 2 * TM_L1_BUF + 128, fp = FP_WARPS * 2 * TM_FP_BUF + 128;
-    cudaFuncSetAttribute(k_search16, cudaFuncAttributeMaxDynamicSharedMemorySize, SEARCH_WARPS * 2 * TM_S16_BUF + 128);
+    cudaFuncSetAttribute(k_search16<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SEARCH_WARPS * 2 * TM_S16_BUF + 128);
+    cudaFuncSetAttribute(k_search16<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SEARCH_WARPS * 2 * TM_S16_BUF + 128);
     cudaFuncSetAttribute(k_search_blk<true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, blk1);
     cudaFuncSetAttribute(k_search_blk<false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, blk1);
     cudaFuncSetAttribute(k_search_blk<true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, blk2);
@@ -349,10 +350,10 @@ int svtme_launch_dg_detector(const PicJob *h_job, const PicJob *d_job, int sa0, 
     const size_t s16_smem = (size_t)SEARCH_WARPS * 2 * TM_S16_BUF + 128;
     if (!g_s16_ctas_per_sm) {
         int k = 0;
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&k, k_search16, 32 * SEARCH_WARPS, s16_smem);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&k, k_search16<true>, 32 * SEARCH_WARPS, s16_smem);
         g_s16_ctas_per_sm = k > 0 ? k : 1;
     }
-    k_search16<<<n_sm * g_s16_ctas_per_sm, 32 * SEARCH_WARPS, s16_smem, st>>>(d_job, 0);
+    k_search16<true><<<n_sm * g_s16_ctas_per_sm, 32 * SEARCH_WARPS, s16_smem, st>>>(d_job, 0);
     k_dg_reduce<<<(n_b64 + 127) / 128, 128, 0, st>>>(d_job, (DgOut *)d_out, d_b64_sad, d_b64_mv);
     return 3;
 }
@@ -439,12 +440,13 @@ int svtme_launch_picture_me(const PicJob *h_jobs, int n, const PicJob *d_jobs, c
     const size_t s16_smem = (size_t)SEARCH_WARPS * 2 * TM_S16_BUF + 128;
     if (!g_s16_ctas_per_sm) {
         int k = 0;
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&k, k_search16, 32 * SEARCH_WARPS, s16_smem);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&k, k_search16<true>, 32 * SEARCH_WARPS, s16_smem);
         g_s16_ctas_per_sm = k > 0 ? k : 1;
         if (g_s16_ctas_per_sm > persistent_slack()) g_s16_ctas_per_sm -= persistent_slack();
     }
     auto search16 = [&](int skip, int tag) {
-        k_search16<<<n_sm * g_s16_ctas_per_sm, 32 * SEARCH_WARPS, s16_smem, st>>>(d_jobs, skip);
+        if (tag == SVTME_TL_S16_PREHME) k_search16<false><<<n_sm * g_s16_ctas_per_sm, 32 * SEARCH_WARPS, s16_smem, st>>>(d_jobs, skip);
+        else k_search16<true><<<n_sm * g_s16_ctas_per_sm, 32 * SEARCH_WARPS, s16_smem, st>>>(d_jobs, skip);
         launches++;
         mark(tag);
     };
@@ -594,7 +596,7 @@ __global__ void __launch_bounds__(32 * SEARCH_WARPS) k_kat_search16(const __grid
     __syncwarp();
     uint32_t best[4];
     const S16Split sp = {32767, 32767};
-    warp_search16_tile(P.buf[0], wide ? TM_S16W_BOX_W : TM_S16T_BOX_W, smem_u32(s_src[warp]), (uint32_t)x0 & 15u, x0, y0,
+    warp_search16_tile<false>(P.buf[0], wide ? TM_S16W_BOX_W : TM_S16T_BOX_W, smem_u32(s_src[warp]), (uint32_t)x0 & 15u, x0, y0,
                        imin(tile_w, sa_w - x0), imin(tile_h, sa_h - y0), bw, bh, row_step, skip && bw == 16 && bh <= 16, sp, best);
     const unsigned long long key = best[0] == 0xffffffffu ? HME_KEY_NONE : s16_key64(best[0], x0, y0, 0, sp, sa_w);
     if (lane == 0 && key != HME_KEY_NONE) atomicMin(out_key, key);

@@ -315,20 +315,51 @@ __device__ __forceinline__ void s16_tile_tasks_pos(uint32_t buf, int pitch, uint
     s16_merge_best(best, run.key, run.qd);
 }
 
+// Which evaluator searches a tile of tw x th positions: the one with the fewest warp instructions = passes over the 32
+// lanes x instructions per pass (measured loop bodies: a reference row costs 28 load / shift instructions, a block row of
+// 8 positions 33).
+//   general : task = (search row, octet)                   8 x 61 per pass
+//   vb<G>   : task = (G search rows of one parity, octet)  (7 + G) x 28 + 8 G x 33 per pass
+//   pos     : task = one position                          8 x 14 per pass
+// Shared with the tile geometry (k_hme_ctl picks the tile height of a window by the same model).
+enum { S16_EVAL_GEN = 0, S16_EVAL_VB2 = 1, S16_EVAL_VB3 = 2, S16_EVAL_POS = 3 };
+__host__ __device__ inline int s16_eval_choice(int tw, int th, int bw, int n_rows, int row_step, bool skip_lines, bool wide_pitch, bool vb2,
+                                               int *cost_out) {
+    const int n_oct = (tw + 7) >> 3, npar = skip_lines ? 1 : 2, rows_eff = skip_lines ? (th + 1) >> 1 : th;
+    int cost = ((n_oct * rows_eff + 31) >> 5) * 500, which = S16_EVAL_GEN;
+    if (bw == 16 && tw <= 16) {
+        const int c = ((tw * th + 31) >> 5) * (14 * n_rows + 10);
+        if (c <= cost) { cost = c; which = S16_EVAL_POS; }
+    }
+    if (bw == 16 && n_rows == 8 && row_step == 2) {
+        // G = 2 only in the wide tile (the 48-byte pitch of the tall one puts lanes 4 rows apart on 4 banks) and not for the 3-row
+        // pre-HME strips (measured: one pass with half-empty chains 39.8 us per picture, two general passes 36.9)
+        if (vb2 && wide_pitch && th >= 8) {
+            const int c = ((n_oct * ((th + 3) >> 2) * npar + 31) >> 5) * 840;
+            if (c <= cost) { cost = c; which = S16_EVAL_VB2; }
+        }
+        const int c = ((n_oct * ((th + 5) / 6) * npar + 31) >> 5) * 1140;
+        if (c <= cost) { cost = c; which = S16_EVAL_VB3; }
+    }
+    if (cost_out) *cost_out = cost;
+    return which;
+}
+
 // a: byte offset of the tile's position 0 inside its rows ((plane x of the position) & 15). On return best[k] is the
 // warp-wide best of quadrant k in this tile, or 0xffffffff.
+template <bool VB2>
 __device__ inline void warp_search16_tile(uint32_t buf, int pitch, uint32_t src, uint32_t a, int x0, int y0, int tw, int th, int bw,
                                           int n_rows, int row_step, bool skip_lines, S16Split sp, uint32_t (&best)[4]) {
+    const bool wide_pitch = pitch != TM_S16T_BOX_W;
 #pragma unroll
     for (int k = 0; k < 4; k++) best[k] = 0xffffffffu;
-    // blocked form only where it fills the warp: >= 24 (octet, chain) tasks and at most one partial block in four
-    const int vb_blocks = (th + 2 * S16_VB_G - 1) / (2 * S16_VB_G);
-    const bool vb_ok = ((tw + 7) >> 3) * vb_blocks * (skip_lines ? 1 : 2) >= 24 && (th % (2 * S16_VB_G) == 0 || vb_blocks >= 4);
-    if (bw == 16 && n_rows == 8 && row_step == 2 && vb_ok) {
-        // skip_search_line drops the even rows of the WINDOW: parity is relative to y0
-        const int par0 = skip_lines ? ((y0 & 1) ? 0 : 1) : 0;
-        s16_tile_tasks_vb<S16_VB_G>(buf, pitch, src, a, x0, y0, tw, th, par0, skip_lines ? 1 : 2, sp, best);
-    } else if (bw == 16 && tw <= 16 && tw * th <= 64) {
+    const int which = s16_eval_choice(tw, th, bw, n_rows, row_step, skip_lines, wide_pitch, VB2, nullptr);
+    const int par0 = skip_lines ? ((y0 & 1) ? 0 : 1) : 0; // skip_search_line drops the even rows of the WINDOW: parity is relative to y0
+    if (which == S16_EVAL_VB3) {
+        s16_tile_tasks_vb<3>(buf, pitch, src, a, x0, y0, tw, th, par0, skip_lines ? 1 : 2, sp, best);
+    } else if (VB2 && which == S16_EVAL_VB2) {
+        s16_tile_tasks_vb<2>(buf, pitch, src, a, x0, y0, tw, th, par0, skip_lines ? 1 : 2, sp, best);
+    } else if (which == S16_EVAL_POS) {
         s16_tile_tasks_pos(buf, pitch, src, a, x0, y0, tw, th, n_rows, row_step, skip_lines, sp, best);
     } else {
         const uint32_t h8 = a >> 3, t8 = (a & 3u) * 8u;
@@ -367,7 +398,7 @@ __device__ __forceinline__ void warp_stage_src16(uint32_t dst, const uint8_t *sr
 struct S16Cursor {
     int      pic, slot0, src_off, tile; // unit record; tile index inside the current job
     uint32_t u;                         // bw | rows << 8 | remaining-jobs mask << 16 | current job q << 20 | new_unit << 24 | valid << 25
-    uint32_t pxy, wh, split, misc;      // job: px | py << 16; sa_w | sa_h << 16; w0 | h0 << 16; n_tiles | n_tx << 16 | wide << 24 | merged << 25
+    uint32_t pxy, wh, split, misc;      // job: px | py << 16; sa_w | sa_h << 16; w0 | h0 << 16; n_tiles | n_tx << 16 | wide << 24 | merged << 25 | tile_h / 2 << 26
 };
 #define S16C_VALID(c) (((c).u >> 25) & 1u)
 #define S16C_NEW_UNIT(c) (((c).u >> 24) & 1u)
@@ -379,7 +410,8 @@ __device__ __forceinline__ void s16_load_job(const PicJob *__restrict__ jobs, S1
     c.pxy   = (uint32_t)(uint16_t)j.px | ((uint32_t)(uint16_t)j.py << 16);
     c.wh    = (uint32_t)sa_w | ((uint32_t)sa_h << 16);
     c.split = (uint32_t)w0 | ((uint32_t)h0 << 16);
-    c.misc  = ((uint32_t)j.n_tx * (uint32_t)j.n_ty) | ((uint32_t)j.n_tx << 16) | ((uint32_t)j.wide << 24) | ((uint32_t)merged << 25);
+    c.misc  = ((uint32_t)j.n_tx * (uint32_t)j.n_ty) | ((uint32_t)j.n_tx << 16) | ((uint32_t)j.wide << 24) | ((uint32_t)merged << 25) |
+              ((uint32_t)(j.tile_h >> 1) << 26); // tile heights are even (96; 18 / 16 / 12)
     c.tile  = 0;
 }
 // next unit of the queue: ticket, record, which of its four jobs have tiles
@@ -427,7 +459,7 @@ struct S16Tile { // tile coordinates inside the job's window
 __device__ __forceinline__ S16Tile s16_tile_of(const S16Cursor &c) {
     S16Tile t;
     const int n_tx = (int)((c.misc >> 16) & 0xffu), wide = (int)((c.misc >> 24) & 1u);
-    const int tile_w = wide ? S16W_TILE_W : S16T_TILE_W, tile_h = wide ? S16W_TILE_H : S16T_TILE_H;
+    const int tile_w = wide ? S16W_TILE_W : S16T_TILE_W, tile_h = (int)(c.misc >> 26) << 1;
     int tx = 0, ty = c.tile;
     if (n_tx > 1) { ty = c.tile / n_tx; tx = c.tile - ty * n_tx; } // only windows wider than 128 positions
     t.x0 = tx * tile_w; t.y0 = ty * tile_h;
@@ -435,6 +467,9 @@ __device__ __forceinline__ S16Tile s16_tile_of(const S16Cursor &c) {
     return t;
 }
 
+// VB2: with the two-row blocked evaluator (the level-0 launch: windows of 16 .. 96 rows; the pre-HME launch leaves it out,
+// its code only costs instruction-cache space there: 36.9 -> 38.5 us per picture with it compiled in and never chosen)
+template <bool VB2>
 __global__ void __launch_bounds__(32 * SEARCH_WARPS) k_search16(const PicJob *__restrict__ jobs, int skip_cfg) {
     extern __shared__ __align__(128) uint8_t s_dyn[];
     __shared__ __align__(16) uint32_t s_src[SEARCH_WARPS][2][16 * 4];
@@ -487,7 +522,7 @@ __global__ void __launch_bounds__(32 * SEARCH_WARPS) k_search16(const PicJob *__
         pipe_wait(P, stage);
         __syncwarp(); // the source rows written by other lanes
         uint32_t best[4];
-        warp_search16_tile(P.buf[stage], wide ? TM_S16W_BOX_W : TM_S16T_BOX_W, src32 + 256u * (uint32_t)cur_sbuf,
+        warp_search16_tile<VB2>(P.buf[stage], wide ? TM_S16W_BOX_W : TM_S16T_BOX_W, src32 + 256u * (uint32_t)cur_sbuf,
                            (uint32_t)(px + t.x0) & 15u, t.x0, t.y0, t.tw, t.th, bw, rows, row_step, skip, sp, best);
         if (lane < 4 && (lane == 0 || merged)) {
             const uint32_t k = lane == 0 ? best[0] : (lane == 1 ? best[1] : (lane == 2 ? best[2] : best[3]));
