@@ -260,13 +260,16 @@ class Runner:
         return sp
 
     def setup_slabs(self, sp):
-        """two pinned result slabs used by alternate batches: batch k's download overlaps batch k+1's uploads and kernels"""
+        """three pinned result slabs used in turn: the host queues batch k + 2 (which reuses the device region of batch k, the
+        library waits for that download on the device, before the batch's first writing kernel) without waiting for batch k's
+        download itself; it waits only for batch k - 1's, whose slab it is about to hand out again. With two slabs the host had
+        to wait for the download of batch k before it could queue batch k + 2, and the second compute stream ran dry."""
         import torch
         lay = self.sess.packed_layout(sp.prm[0], self.fields)
         self.slab_bytes = lay.bytes * self.wl.mgop
-        self.slabs = [torch.zeros(self.slab_bytes, dtype=torch.uint8).pin_memory() for _ in range(2)]
+        self.slabs = [torch.zeros(self.slab_bytes, dtype=torch.uint8).pin_memory() for _ in range(3)]
         self.block_bytes = lay.bytes
-        self.seqs = [0, 0]
+        self.seqs = [0, 0, 0]
         self.sess.reserve(sp.prm[0], self.wl.mgop)
 
     def run_step(self, sp, host):
@@ -285,7 +288,7 @@ class Runner:
             self.call_s += time.perf_counter() - t_call
             return
         if host and self.probe != "h2d":
-            k = self.host_batches & 1
+            k = self.host_batches % 3
             t_wait = time.perf_counter()
             self.sess.wait_batch(self.seqs[k])  # this slab's previous results are in host memory (and consumed) before reuse
             t_call += time.perf_counter() - t_wait  # waiting for the pipeline is not host work

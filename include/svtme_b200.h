@@ -435,9 +435,12 @@ uint32_t svtme_session_sync(SvtMeSession *s);
    streams: with sync = 0, svtme_picture_me_batch returns once the batch is queued, and the uploads of the next
    pictures and the next batch's kernels overlap its downloads. svtme_session_batch_seq returns the sequence number
    (1, 2, ...) of the batch queued last; svtme_session_wait_batch blocks until the results of batch `seq` are in the
-   host arrays it was given. At most two batches may be in flight per set of host arrays (the caller alternates two
-   sets and waits for batch seq - 2 before reusing a set). No reference counterpart: the reference's ME threads
-   synchronise through the picture-decision / ME FIFOs (me_process.c:75-330). */
+   host arrays it was given (the batch's own download, not a later batch's). The caller rotates its host arrays: with
+   k sets it waits for batch seq - k before it hands a set out again. Three sets keep both compute streams of
+   svtme_session_set_concurrency(2) busy: the device-side result region of batch seq - 2 is reused by batch seq, and the
+   library makes the first kernel that writes it wait for that download on the device, so the host need not. (With two
+   sets the host itself waits for the download of batch seq - 2 before it can queue batch seq.) No reference counterpart:
+   the reference's ME threads synchronise through the picture-decision / ME FIFOs (me_process.c:75-330). */
 uint64_t svtme_session_batch_seq(SvtMeSession *s);
 /* n = 2: consecutive batches run on two compute streams (the session's stream and an internal one), so that the
    latency-bound control kernels of one batch overlap the searches of the other. Results must then be awaited with

@@ -129,6 +129,8 @@ struct SvtMeSession {
     uint32_t     d_jobs_n = 0;           // pictures per set the job array holds
     cudaEvent_t  ev_me[8] = {}, ev_dl[2] = {};
     bool         dl_recorded[2] = {false, false};
+    cudaEvent_t  ev_dl_seq[8] = {};      // the last download of batch seq (slot seq % 8): what svtme_session_wait_batch waits for
+    uint64_t     dl_seq[8] = {};
     uint64_t     batch_seq = 0; // sequence number of the last launched batch (1-based)
     PicJob      *d_jobs = nullptr;
     // host copies of the job arrays: a ring of pinned arrays (the H2D copy of one is asynchronous; it is rewritten only
@@ -302,6 +304,7 @@ extern "C" uint32_t svtme_session_create(SvtMeSession **out, int device, uint32_
     CU_TRY(cudaStreamCreateWithFlags(&s->dl_stream, cudaStreamNonBlocking));
     for (auto &e2 : s->ev_me) CU_TRY(cudaEventCreateWithFlags(&e2, cudaEventDisableTiming));
     for (auto &e2 : s->ev_dl) CU_TRY(cudaEventCreateWithFlags(&e2, cudaEventDisableTiming));
+    for (auto &e2 : s->ev_dl_seq) CU_TRY(cudaEventCreateWithFlags(&e2, cudaEventDisableTiming));
     for (auto &e2 : s->ev_jobs) CU_TRY(cudaEventCreateWithFlags(&e2, cudaEventDisableTiming));
     for (auto &e2 : s->ev_release) CU_TRY(cudaEventCreateWithFlags(&e2, cudaEventDisableTiming));
     CU_TRY(cudaEventCreateWithFlags(&s->ev_copied, cudaEventDisableTiming));
@@ -325,6 +328,7 @@ extern "C" void svtme_session_destroy(SvtMeSession *s) {
     for (auto &e : s->tl_pool) cudaEventDestroy(e);
     for (auto &e : s->ev_me) if (e) cudaEventDestroy(e);
     for (auto &e : s->ev_dl) if (e) cudaEventDestroy(e);
+    for (auto &e : s->ev_dl_seq) if (e) cudaEventDestroy(e);
     if (s->up_stream) cudaStreamDestroy(s->up_stream);
     if (s->stream2) cudaStreamDestroy(s->stream2);
     for (auto &e : s->ev_built) if (e) cudaEventDestroy(e);
@@ -433,10 +437,11 @@ extern "C" uint32_t svtme_session_wait_batch(SvtMeSession *s, uint64_t seq) {
     const int set = (int)(seq & 1);
     { // the events live as long as the session; only the bookkeeping needs the lock (other threads may be launching)
         std::lock_guard<std::mutex> g(s->mu);
-        if (seq == 0 || seq > s->batch_seq) return SVTME_OK;
-        // results of batch `seq` were copied by the download recorded in ev_dl[set] (or by a later one of the same set)
-        downloaded = s->dl_recorded[set];
-        ev = downloaded ? s->ev_dl[set] : s->ev_me[seq % 8];
+        if (seq == 0 || seq > s->batch_seq || seq + 8 <= s->batch_seq) return SVTME_OK; // eight batches on: its region was handed out again after its downloads
+        // the batch's own last download (not a later batch's of the same set: a caller that rotates three or more host
+        // buffers waits for batch k - 2 while batch k's download may not even have started)
+        downloaded = s->dl_seq[seq % 8] == seq;
+        ev = downloaded ? s->ev_dl_seq[seq % 8] : s->ev_me[seq % 8];
     }
     cudaSetDevice(s->device);
     CU_TRY(cudaEventSynchronize(ev));
@@ -825,8 +830,12 @@ static uint32_t launch_me_batch(SvtMeSession *s, uint32_t n, const int32_t *pic_
     bo.geo.resize(n);
     for (uint32_t i = 0; i < n; i++) bo.geo[i] = {(size_t)strides[i].n_pus, (size_t)strides[i].mv_stride, (size_t)strides[i].cand_stride};
     cudaStream_t cs = compute_stream(s, set);
-    if (s->dl_recorded[set]) CU_TRY(cudaStreamWaitEvent(cs, s->ev_dl[set], 0)); // the set's previous results left for the host
-    if (s->release_recorded[set]) { CU_TRY(cudaStreamWaitEvent(cs, s->ev_release[set], 0)); s->release_recorded[set] = false; } // ... and its device-side readers are done
+    // the set's previous results have left for the host and its device-side readers are done: waited for inside the launch
+    // sequence, before the first kernel that writes the region (svtme_launch_picture_me)
+    cudaEvent_t out_free[2];
+    int n_out_free = 0;
+    if (s->dl_recorded[set]) out_free[n_out_free++] = s->ev_dl[set];
+    if (s->release_recorded[set]) { out_free[n_out_free++] = s->ev_release[set]; s->release_recorded[set] = false; }
     if (s->concurrency == 2) { // pictures whose pyramids were queued on the other compute stream
         const int other = 1 - stream_index(s, set);
         if (s->built_recorded[other]) CU_TRY(cudaStreamWaitEvent(cs, s->ev_built[other], 0));
@@ -922,7 +931,7 @@ static uint32_t launch_me_batch(SvtMeSession *s, uint32_t n, const int32_t *pic_
             else CU_TRY(cudaEventCreate(&tl->ev[i]));
         }
     }
-    s->launches += (uint64_t)svtme_launch_picture_me(h_jobs, (int)n, d_jobs, cs, e0, e1, e2, tl);
+    s->launches += (uint64_t)svtme_launch_picture_me(h_jobs, (int)n, d_jobs, cs, e0, e1, e2, tl, out_free, n_out_free);
     CU_TRY(cudaGetLastError());
     CU_TRY(cudaEventRecord(s->ev_me[seq % 8], cs));
     return SVTME_OK;
@@ -937,6 +946,9 @@ static uint32_t end_download(SvtMeSession *s, int set) {
     CU_TRY(cudaMemcpyAsync(&s->h_flags[set], (uint32_t *)(s->res_sets[set][0] + s->lay.fp_counters) + 8, sizeof(uint32_t), cudaMemcpyDeviceToHost, s->dl_stream));
     CU_TRY(cudaEventRecord(s->ev_dl[set], s->dl_stream));
     s->dl_recorded[set] = true;
+    const uint64_t seq = s->out[set].seq;
+    CU_TRY(cudaEventRecord(s->ev_dl_seq[seq % 8], s->dl_stream));
+    s->dl_seq[seq % 8] = seq;
     return SVTME_OK;
 }
 static uint32_t finish_sync(SvtMeSession *s, int set, bool downloaded) {

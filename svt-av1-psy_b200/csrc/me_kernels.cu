@@ -383,7 +383,7 @@ uint32_t svtme_fp_units_cap(const SvtMePicParams &pp, int n_b64) {
 // is the union of what the pictures need (an extra round is a no-op for pictures without the
 // dependency it serves).
 int svtme_launch_picture_me(const PicJob *h_jobs, int n, const PicJob *d_jobs, cudaStream_t st, cudaEvent_t ev_hme0,
-                            cudaEvent_t ev_hme1, cudaEvent_t ev_fp1, SvtMeTimeline *tl) {
+                            cudaEvent_t ev_hme1, cudaEvent_t ev_fp1, SvtMeTimeline *tl, const cudaEvent_t *out_free, int n_out_free) {
     // per-kernel timing (svtme_session_enable_timing): an event behind every launch, tagged with the kernel it closes
     auto mark = [&](int tag) {
         if (!tl || tl->n >= SVTME_TL_MAX) return;
@@ -513,6 +513,11 @@ int svtme_launch_picture_me(const PicJob *h_jobs, int n, const PicJob *d_jobs, c
     if (ev_hme1) cudaEventRecord(ev_hme1, st);
 
     // ---- full-pel ----
+    // k_fp and k_post are the first kernels that write the output arrays of the jobs (the batch's result region): only
+    // here does the sequence wait for the readers of the region's previous contents (the download of the batch two
+    // before this one, a device-side consumer), not at its start. The HME stage, two thirds of the sequence, then runs
+    // under that download instead of behind it.
+    for (int i = 0; i < n_out_free; i++) cudaStreamWaitEvent(st, out_free[i], 0);
     const bool fsub = c.me_search_method == SVTME_SUB_SAD_SEARCH;
     const size_t fp_smem = (size_t)FP_WARPS * 2 * TM_FP_BUF + 128;
     if (!g_fp_search_ctas_per_sm) {

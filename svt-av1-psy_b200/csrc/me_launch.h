@@ -28,7 +28,7 @@ struct SvtMeTimeline {
     int         n;
 };
 int  svtme_launch_picture_me(const PicJob *h_jobs, int n, const PicJob *d_jobs, cudaStream_t st, cudaEvent_t ev_hme0,
-                             cudaEvent_t ev_hme1, cudaEvent_t ev_fp1, SvtMeTimeline *tl);
+                             cudaEvent_t ev_hme1, cudaEvent_t ev_fp1, SvtMeTimeline *tl, const cudaEvent_t *out_free, int n_out_free);
 int  svtme_launch_kat_sad_loop(const uint8_t *d_src, int src_stride, const uint8_t *d_ref, int ref_stride, int bh, int bw,
                                int src_stride_raw, int skip, int sa_w, int sa_h, unsigned long long *d_key, uint8_t *d_pitched,
                                size_t pitched_cap, cudaStream_t st);

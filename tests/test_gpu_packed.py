@@ -136,6 +136,69 @@ def test_packed_batch_matches_oracle(orc, fields):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("concurrency", [1, 2])
+def test_three_slabs_in_rotation(orc, concurrency):
+    """The bench's end-to-end pipeline: batches queued without waiting into three host slabs in turn, two compute streams;
+    the library alone orders the reuse of its two device-side result regions (the first writing kernel of batch k waits
+    for the download of batch k - 2), svtme_session_wait_batch(seq) waits for that batch's OWN download."""
+    import torch
+    w, h, planes, refs, pics = _batch(6)
+    s = me.Session(w, h, max_pictures=16)
+    s.set_concurrency(concurrency)
+    for i, pl in enumerate(planes[1:]):
+        s.upload(1 + i, pl)
+    fields = abi.F_SB_RESULTS | abi.F_SB_COMPACT | abi.F_STATS
+    prms = []
+    for k, (src, params) in enumerate(pics):
+        s.upload(8 + k, src)
+        p = copy.copy(params)
+        pid = 1
+        for l in range(len(refs)):
+            for r in range(len(refs[l])):
+                p.ref_pic_id[l][r] = pid
+                pid += 1
+        prms.append(p)
+    lay = s.packed_layout(prms[0], fields)
+    strides = me.Session.sb_strides(prms[0], fields)
+    slabs = [torch.zeros(lay.bytes * 2, dtype=torch.uint8).pin_memory() for _ in range(3)]
+    s.reserve(prms[0], 2)
+    # batch b = pictures (b, (b + 1) % 6): six batches, each slab used twice
+    seqs, want = [], {}
+    checked = 0
+    for b in range(6):
+        k = b % 3
+        if b >= 3:  # the slab's previous batch: wait, check, hand out again
+            s.wait_batch(seqs[b - 3])
+            checked += _check_slab(slabs[k], lay, strides, w, h, prms, refs, pics, [b - 3, (b - 2) % 6], want)
+            slabs[k].fill_(0x5A)
+        pair = [b, (b + 1) % 6]
+        ids_a, prm_a = (C.c_int32 * 2)(*[8 + i for i in pair]), (abi.MePicParams * 2)(*[prms[i] for i in pair])
+        s.me_batch_packed(ids_a, prm_a, 2, fields, slabs[k].data_ptr(), slabs[k].numel(), sync=False)
+        seqs.append(s.batch_seq())
+    for b in (5, 3, 4):  # out of order
+        s.wait_batch(seqs[b])
+        checked += _check_slab(slabs[b % 3], lay, strides, w, h, prms, refs, pics, [b, (b + 1) % 6], want)
+    assert checked == 12
+    s.sync()
+    s.close()
+
+
+def _check_slab(slab, lay, strides, w, h, prms, refs, pics, pair, want):
+    block = slab.numpy()
+    for j, i in enumerate(pair):
+        if i not in want:
+            want[i] = orc_me(pics[i][0], refs, pics[i][1], debug=False)[0]
+        got_c = abi.PicResultArrays(w, h, prms[i], block=block[j * lay.bytes:(j + 1) * lay.bytes], layout=lay, strides=strides)
+        got = me.Session.sb_expand(prms[i], abi.F_SB_RESULTS | abi.F_SB_COMPACT | abi.F_STATS, got_c, abi.PicResultArrays(w, h, prms[i]))
+        for f in ("total_me_candidate_index", "me_mv_array", "me_candidate_array"):
+            np.testing.assert_array_equal(getattr(got, f), getattr(want[i], f), err_msg="picture %d %s" % (i, f))
+        for f in got_c.FIELDS:
+            if group_of(f) == abi.F_STATS:
+                np.testing.assert_array_equal(getattr(got_c, f), getattr(want[i], f), err_msg="picture %d %s" % (i, f))
+    return len(pair)
+
+
+@pytest.mark.gpu
 def test_merged_uploads(orc):
     """frames adjacent in host memory cross as one copy whatever the order they are named in; pitched and scattered
     frames take the per-frame path; the planes on the device are the same either way"""
