@@ -129,17 +129,19 @@ __device__ __forceinline__ void s16_run_update(S16Run &run, uint32_t (&best)[4],
 __constant__ uint16_t c_inv16[17] = {0, 0, 32768, 21846, 16384, 13108, 10923, 9363, 8192, 7282, 6554, 5958, 5462, 5042, 4682, 4370, 4096};
 __device__ __forceinline__ int div_small(int x, int n) { return n == 1 ? x : (int)(((uint32_t)x * c_inv16[n]) >> 16); }
 
-// lane = (search row, octet of 8 positions); a lane reads 32 bytes per block row from the 8-byte boundary at or before
-// its octet (4 LDS.64, consecutive lanes = consecutive 8-byte units); the remaining 0..7 bytes of misalignment are the
-// same for every octet of the job: the word offset goes into the address (7 LDS.32), one funnel shift per word. The row
+// lane = (search row, octet of 8 positions); a lane reads 28 bytes per block row from the 4-byte boundary at or before
+// its octet (7 LDS.32, consecutive lanes 8 bytes apart); the remaining 0..3 bytes of misalignment are the same for
+// every octet of the job: one funnel shift per word. PARTIAL: blocks narrower than 16 (right picture edge), kept out of
+// line (s16_tile_tasks_partial) so that the code every other block runs stays small. The row
 // loops of this and the per-position evaluator are NOT unrolled: the pre-HME launch was stalling on instruction fetch
 // (ncu: 1.2 warps per issue cycle in no_instruction); 2928 -> 1936 SASS instructions, 37.4 -> 35.2 us per picture.
+template <bool PARTIAL>
 __device__ __forceinline__ void s16_tile_tasks(uint32_t buf, int pitch, uint32_t src, uint32_t a4, uint32_t t8, int x0, int y0, int tw,
                                                int th, int bw, int n_rows, int row_step, bool skip_lines, S16Split sp,
                                                uint32_t (&best)[4]) {
     const int lane  = threadIdx.x & 31;
     const int n_oct = (tw + 7) >> 3;
-    const bool     partial = bw < 16;
+    constexpr bool partial = PARTIAL;
     uint32_t m0 = 0xffffffffu, m1 = 0xffffffffu, m2 = 0xffffffffu, m3 = 0xffffffffu;
     if (partial) { m0 = lo_bytes_mask(bw); m1 = lo_bytes_mask(bw - 4); m2 = lo_bytes_mask(bw - 8); m3 = lo_bytes_mask(bw - 12); }
     int yy = div_small(lane, n_oct), oct = lane - yy * n_oct;
@@ -191,6 +193,14 @@ __device__ __forceinline__ void s16_tile_tasks(uint32_t buf, int pitch, uint32_t
         s16_run_update(run, best, tb, (x0 + 8 * oct >= sp.x ? 1 : 0) + (y >= sp.y ? 2 : 0));
     }
     s16_merge_best(best, run.key, run.qd);
+}
+
+__device__ __noinline__ uint4 s16_tile_tasks_partial(uint32_t buf, int pitch, uint32_t src, uint32_t a4, uint32_t t8, int x0, int y0, int tw, int th,
+                                                    int bw, int n_rows, int row_step, bool skip_lines, int spx, int spy) {
+    uint32_t best[4] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu};
+    const S16Split sp = {spx, spy};
+    s16_tile_tasks<true>(buf, pitch, src, a4, t8, x0, y0, tw, th, bw, n_rows, row_step, skip_lines, sp, best);
+    return make_uint4(best[0], best[1], best[2], best[3]);
 }
 
 // Vertically blocked form for the common shape (16x16 block, rows two apart: 8 block rows): a lane takes G search
@@ -363,7 +373,12 @@ __device__ inline void warp_search16_tile(uint32_t buf, int pitch, uint32_t src,
     } else if (which == S16_EVAL_POS) {
         s16_tile_tasks_pos(buf, pitch, src, a, x0, y0, tw, th, n_rows, row_step, skip_lines, sp, best);
     } else {
-        s16_tile_tasks(buf, pitch, src, a & ~3u, (a & 3u) * 8u, x0, y0, tw, th, bw, n_rows, row_step, skip_lines, sp, best);
+        if (bw < 16) {
+            const uint4 b4 = s16_tile_tasks_partial(buf, pitch, src, a & ~3u, (a & 3u) * 8u, x0, y0, tw, th, bw, n_rows, row_step, skip_lines, sp.x, sp.y);
+            best[0] = b4.x; best[1] = b4.y; best[2] = b4.z; best[3] = b4.w;
+        } else {
+            s16_tile_tasks<false>(buf, pitch, src, a & ~3u, (a & 3u) * 8u, x0, y0, tw, th, bw, n_rows, row_step, skip_lines, sp, best);
+        }
     }
 #pragma unroll
     for (int k = 0; k < 4; k++) best[k] = __reduce_min_sync(0xffffffffu, best[k]);
@@ -395,7 +410,8 @@ __device__ __forceinline__ void warp_stage_src16(uint32_t dst, const uint8_t *sr
 // Where a warp is in its walk (unit -> job -> tile), packed: the cursor is alive across every tile search and the
 // evaluators need the registers.
 struct S16Cursor {
-    int      pic, slot0, src_off, tile; // unit record; tile index inside the current job
+    int      pic, slot0, src_off;       // unit record
+    uint32_t tile;                      // tile inside the current job: tx | ty << 8 | index << 16 (stepped, never divided)
     uint32_t u;                         // bw | rows << 8 | remaining-jobs mask << 16 | current job q << 20 | new_unit << 24 | valid << 25
     uint32_t pxy, wh, split, misc;      // job: px | py << 16; sa_w | sa_h << 16; w0 | h0 << 16; n_tiles | n_tx << 16 | wide << 24 | merged << 25 | tile_h / 2 << 26
 };
@@ -442,7 +458,10 @@ __device__ __forceinline__ void s16_next_unit(const PicJob *__restrict__ jobs, u
 // step to the next tile: same job, next job of the unit, or next unit
 __device__ __forceinline__ void s16_advance(const PicJob *__restrict__ jobs, uint32_t n_units, S16Cursor &c) {
     c.u &= ~(1u << 24);
-    if (++c.tile < (int)(c.misc & 0xffffu)) return;
+    uint32_t t = c.tile + 0x10001u; // next index, next column
+    if ((t & 0xffu) == ((c.misc >> 16) & 0xffu)) t = (t & ~0xffu) + 0x100u; // first column of the next tile row
+    c.tile = t;
+    if ((t >> 16) < (c.misc & 0xffffu)) return;
     const uint32_t todo = (c.u >> 16) & 0xfu;
     if (todo) {
         const uint32_t q = (uint32_t)__ffs(todo) - 1u;
@@ -459,8 +478,7 @@ __device__ __forceinline__ S16Tile s16_tile_of(const S16Cursor &c) {
     S16Tile t;
     const int n_tx = (int)((c.misc >> 16) & 0xffu), wide = (int)((c.misc >> 24) & 1u);
     const int tile_w = wide ? S16W_TILE_W : S16T_TILE_W, tile_h = (int)(c.misc >> 26) << 1;
-    int tx = 0, ty = c.tile;
-    if (n_tx > 1) { ty = c.tile / n_tx; tx = c.tile - ty * n_tx; } // only windows wider than 128 positions
+    const int tx = (int)(c.tile & 0xffu), ty = (int)((c.tile >> 8) & 0xffu);
     t.x0 = tx * tile_w; t.y0 = ty * tile_h;
     t.tw = imin(tile_w, (int)(c.wh & 0xffffu) - t.x0); t.th = imin(tile_h, (int)(c.wh >> 16) - t.y0);
     return t;
@@ -508,7 +526,7 @@ __global__ void __launch_bounds__(32 * SEARCH_WARPS) k_search16(const PicJob *__
         const int bw = (int)(c.u & 0xffu), rows = (int)((c.u >> 8) & 0xffu), wide = (int)((c.misc >> 24) & 1u), merged = (int)((c.misc >> 25) & 1u);
         const int px = (int)(int16_t)(c.pxy & 0xffffu), sa_w = (int)(c.wh & 0xffffu);
         const S16Split sp = {(int)(c.split & 0xffffu), (int)(c.split >> 16)};
-        const bool last_of_job = c.tile + 1 == (int)(c.misc & 0xffffu);
+        const bool last_of_job = (c.tile >> 16) + 1u == (c.misc & 0xffffu);
         unsigned long long *key_out = &jobs[c.pic].hme_jobs[c.slot0 + (int)((c.u >> 20) & 3u) + lane].key;
         const int cur_sbuf = sbuf;
         // the tile after this one: its load overlaps this tile's search
