@@ -131,11 +131,12 @@ __device__ __forceinline__ int div_small(int x, int n) { return n == 1 ? x : (in
 
 // lane = (search row, octet of 8 positions); a lane reads 28 bytes per block row from the 4-byte boundary at or before
 // its octet (7 LDS.32, consecutive lanes 8 bytes apart); the remaining 0..3 bytes of misalignment are the same for
-// every octet of the job: one funnel shift per word. PARTIAL: blocks narrower than 16 (right picture edge), kept out of
-// line (s16_tile_tasks_partial) so that the code every other block runs stays small. The row
+// every octet of the job: one funnel shift per word unless ALIGNED (no misalignment, nearly every window). PARTIAL: blocks
+// narrower than 16 (right picture edge). Those and the unaligned windows are kept out of line (s16_tile_tasks_slow) so
+// that the code every other tile runs stays small. The row
 // loops of this and the per-position evaluator are NOT unrolled: the pre-HME launch was stalling on instruction fetch
 // (ncu: 1.2 warps per issue cycle in no_instruction); 2928 -> 1936 SASS instructions, 37.4 -> 35.2 us per picture.
-template <bool PARTIAL>
+template <bool PARTIAL, bool ALIGNED>
 __device__ __forceinline__ void s16_tile_tasks(uint32_t buf, int pitch, uint32_t src, uint32_t a4, uint32_t t8, int x0, int y0, int tw,
                                                int th, int bw, int n_rows, int row_step, bool skip_lines, S16Split sp,
                                                uint32_t (&best)[4]) {
@@ -156,12 +157,16 @@ __device__ __forceinline__ void s16_tile_tasks(uint32_t buf, int pitch, uint32_t
         uint32_t row = buf + (uint32_t)(yy * pitch) + a4 + 8u * (uint32_t)oct; // a4: the window's byte offset in the tile rows, rounded down to a word
 #pragma unroll 1
         for (int rr = 0; rr < n_rows; rr++, row += rstep) {
-            uint32_t c[7], w[6];
+            uint32_t w7[7], w[6];
 #pragma unroll
-            for (int i = 0; i < 7; i++) asm volatile("ld.shared.u32 %0, [%1];" : "=r"(c[i]) : "r"(row + 4u * i));
+            for (int i = 0; i < 7; i++) asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w7[i]) : "r"(row + 4u * i));
             const uint4 sv = lds128(src + 16u * rr);
+            if (!ALIGNED) { // see s16_tile_tasks_vb: nearly every window starts on a word boundary
 #pragma unroll
-            for (int k = 0; k < 6; k++) w[k] = __funnelshift_r(c[k], c[k + 1], t8);
+                for (int k = 0; k < 6; k++) w7[k] = __funnelshift_r(w7[k], w7[k + 1], t8);
+            }
+#pragma unroll
+            for (int k = 0; k < 6; k++) w[k] = w7[k];
             const uint32_t s[4] = {sv.x, sv.y, sv.z, sv.w};
             if (!partial) {
                 strip16_sad8(w, s, acc);
@@ -195,11 +200,12 @@ __device__ __forceinline__ void s16_tile_tasks(uint32_t buf, int pitch, uint32_t
     s16_merge_best(best, run.key, run.qd);
 }
 
-__device__ __noinline__ uint4 s16_tile_tasks_partial(uint32_t buf, int pitch, uint32_t src, uint32_t a4, uint32_t t8, int x0, int y0, int tw, int th,
+__device__ __noinline__ uint4 s16_tile_tasks_slow(uint32_t buf, int pitch, uint32_t src, uint32_t a4, uint32_t t8, int x0, int y0, int tw, int th,
                                                     int bw, int n_rows, int row_step, bool skip_lines, int spx, int spy) {
     uint32_t best[4] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu};
     const S16Split sp = {spx, spy};
-    s16_tile_tasks<true>(buf, pitch, src, a4, t8, x0, y0, tw, th, bw, n_rows, row_step, skip_lines, sp, best);
+    if (bw < 16) s16_tile_tasks<true, false>(buf, pitch, src, a4, t8, x0, y0, tw, th, bw, n_rows, row_step, skip_lines, sp, best);
+    else s16_tile_tasks<false, false>(buf, pitch, src, a4, t8, x0, y0, tw, th, bw, n_rows, row_step, skip_lines, sp, best);
     return make_uint4(best[0], best[1], best[2], best[3]);
 }
 
@@ -213,7 +219,7 @@ __device__ __noinline__ uint4 s16_tile_tasks_partial(uint32_t buf, int pitch, ui
 // rows apart = a multiple of 32 words for ANY pitch the TMA allows (multiples of 16 bytes): 16-way conflicts, measured
 // 30 % slower than no blocking at all.
 #define S16_VB_G 3
-template <int G>
+template <int G, bool ALIGNED>
 __device__ __forceinline__ void s16_tile_tasks_vb(uint32_t buf, int pitch, uint32_t src, uint32_t a, int x0, int y0, int tw, int th,
                                                   int par0, int npar, S16Split sp, uint32_t (&best)[4]) {
     const int lane  = threadIdx.x & 31;
@@ -238,11 +244,17 @@ __device__ __forceinline__ void s16_tile_tasks_vb(uint32_t buf, int pitch, uint3
         // and last G-1 rows only some of them (one short loop with the range checks).
         auto ref_row = [&](int k, auto all_rows) {
             const uint32_t row = row0 + (uint32_t)(2 * k * pitch);
-            uint32_t c[7], w[6], s1[5], s2[5], s3[5];
+            uint32_t w[7], s1[5], s2[5], s3[5];
 #pragma unroll
-            for (int i = 0; i < 7; i++) asm volatile("ld.shared.u32 %0, [%1];" : "=r"(c[i]) : "r"(row + 4u * i));
+            for (int i = 0; i < 7; i++) asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w[i]) : "r"(row + 4u * i));
+            // windows start on a word boundary of the plane unless the picture edge clamped them (block origins are multiples
+            // of 16 samples, window origins multiples of 4): ALIGNED has no alignment shifts (6 of the 21 per reference row;
+            // written as "if (t8)" ptxas predicates them and they still issue: no gain; without them pre-HME 34.4 -> 32.2 us,
+            // level 0 15.1 -> 14.4). The other windows take the same code with the shifts, out of line (s16_vb_unaligned).
+            if (!ALIGNED) {
 #pragma unroll
-            for (int i = 0; i < 6; i++) w[i] = __funnelshift_r(c[i], c[i + 1], t8);
+                for (int i = 0; i < 6; i++) w[i] = __funnelshift_r(w[i], w[i + 1], t8);
+            }
 #pragma unroll
             for (int i = 0; i < 5; i++) {
                 s1[i] = fsr_bytes<1>(w[i], w[i + 1]);
@@ -293,6 +305,16 @@ __device__ __forceinline__ void s16_tile_tasks_vb(uint32_t buf, int pitch, uint3
         }
     }
     s16_merge_best(best, run.key, run.qd);
+}
+
+template <bool VB2>
+__device__ __noinline__ uint4 s16_vb_unaligned(int g, uint32_t buf, int pitch, uint32_t src, uint32_t a, int x0, int y0, int tw, int th, int par0,
+                                               int npar, int spx, int spy) {
+    uint32_t best[4] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu};
+    const S16Split sp = {spx, spy};
+    if (VB2 && g == 2) s16_tile_tasks_vb<2, false>(buf, pitch, src, a, x0, y0, tw, th, par0, npar, sp, best);
+    else s16_tile_tasks_vb<3, false>(buf, pitch, src, a, x0, y0, tw, th, par0, npar, sp, best);
+    return make_uint4(best[0], best[1], best[2], best[3]);
 }
 
 // Tiles with few positions (the 4 rows a 100-row pre-HME window leaves after its 96-row tile, windows cut by the picture
@@ -366,19 +388,23 @@ __device__ inline void warp_search16_tile(uint32_t buf, int pitch, uint32_t src,
     for (int k = 0; k < 4; k++) best[k] = 0xffffffffu;
     const int which = s16_eval_choice(tw, th, bw, n_rows, row_step, skip_lines, wide_pitch, VB2, nullptr);
     const int par0 = skip_lines ? ((y0 & 1) ? 0 : 1) : 0; // skip_search_line drops the even rows of the WINDOW: parity is relative to y0
-    if (which == S16_EVAL_VB3) {
-        s16_tile_tasks_vb<3>(buf, pitch, src, a, x0, y0, tw, th, par0, skip_lines ? 1 : 2, sp, best);
-    } else if (VB2 && which == S16_EVAL_VB2) {
-        s16_tile_tasks_vb<2>(buf, pitch, src, a, x0, y0, tw, th, par0, skip_lines ? 1 : 2, sp, best);
+    const bool aligned = (a & 3u) == 0u;
+    if (which == S16_EVAL_VB3 || (VB2 && which == S16_EVAL_VB2)) {
+        if (!aligned) {
+            const uint4 b4 = s16_vb_unaligned<VB2>(which == S16_EVAL_VB3 ? 3 : 2, buf, pitch, src, a, x0, y0, tw, th, par0, skip_lines ? 1 : 2, sp.x, sp.y);
+            best[0] = b4.x; best[1] = b4.y; best[2] = b4.z; best[3] = b4.w;
+        } else if (!VB2 || which == S16_EVAL_VB3) {
+            s16_tile_tasks_vb<3, true>(buf, pitch, src, a, x0, y0, tw, th, par0, skip_lines ? 1 : 2, sp, best);
+        } else {
+            s16_tile_tasks_vb<2, true>(buf, pitch, src, a, x0, y0, tw, th, par0, skip_lines ? 1 : 2, sp, best);
+        }
     } else if (which == S16_EVAL_POS) {
         s16_tile_tasks_pos(buf, pitch, src, a, x0, y0, tw, th, n_rows, row_step, skip_lines, sp, best);
+    } else if (bw < 16 || !aligned) {
+        const uint4 b4 = s16_tile_tasks_slow(buf, pitch, src, a & ~3u, (a & 3u) * 8u, x0, y0, tw, th, bw, n_rows, row_step, skip_lines, sp.x, sp.y);
+        best[0] = b4.x; best[1] = b4.y; best[2] = b4.z; best[3] = b4.w;
     } else {
-        if (bw < 16) {
-            const uint4 b4 = s16_tile_tasks_partial(buf, pitch, src, a & ~3u, (a & 3u) * 8u, x0, y0, tw, th, bw, n_rows, row_step, skip_lines, sp.x, sp.y);
-            best[0] = b4.x; best[1] = b4.y; best[2] = b4.z; best[3] = b4.w;
-        } else {
-            s16_tile_tasks<false>(buf, pitch, src, a & ~3u, (a & 3u) * 8u, x0, y0, tw, th, bw, n_rows, row_step, skip_lines, sp, best);
-        }
+        s16_tile_tasks<false, true>(buf, pitch, src, a, 0u, x0, y0, tw, th, bw, n_rows, row_step, skip_lines, sp, best);
     }
 #pragma unroll
     for (int k = 0; k < 4; k++) best[k] = __reduce_min_sync(0xffffffffu, best[k]);
@@ -487,7 +513,7 @@ __device__ __forceinline__ S16Tile s16_tile_of(const S16Cursor &c) {
 // VB2: with the two-row blocked evaluator (the level-0 launch: windows of 16 .. 96 rows; the pre-HME launch leaves it out,
 // its code only costs instruction-cache space there: 36.9 -> 38.5 us per picture with it compiled in and never chosen)
 template <bool VB2>
-__global__ void __launch_bounds__(32 * SEARCH_WARPS) k_search16(const PicJob *__restrict__ jobs, int skip_cfg) {
+__global__ void __launch_bounds__(32 * SEARCH_WARPS, 5) k_search16(const PicJob *__restrict__ jobs, int skip_cfg) {
     extern __shared__ __align__(128) uint8_t s_dyn[];
     __shared__ __align__(16) uint32_t s_src[SEARCH_WARPS][2][16 * 4];
     __shared__ __align__(8) uint64_t s_bar[SEARCH_WARPS][2];
