@@ -168,7 +168,14 @@ __global__ void __launch_bounds__(32 * FP_WARPS) k_fp(const PicJob *__restrict__
     if (phase == 2 && !(l || r)) return;
     const SbState &st = job.sb_state[b];
     unsigned long long *gk = job.fp_keys + (size_t)u * 85;
-    if (!st.do_ref[l][r] || st.tf_exit) { // :1294-1295; temporal filter: HME was good enough (:3179-3183)
+    // everything this warp reads of the b64's state and of other warps' results, requested together, before the first
+    // branch that depends on any of it (the loads are one round trip instead of four dependent ones)
+    const uint8_t st_do_ref = st.do_ref[l][r], st_tf_exit = st.tf_exit;
+    const int16_t st_xc = st.hme_sc_x[l][r], st_yc = st.hme_sc_y[l][r];
+    const uint32_t st_div = st.reduce_me_sr_divisor[l][r], st_zz = st.zz_sad[l][r];
+    const auto st_sr_hme_sad = st.sr_hme_sad[l][r];
+    const unsigned long long key00 = phase == 2 ? job.fp_keys[(size_t)b * 8 * 85] : 0ull; // p_sb_best_sad[0][0][0]: written by the phase-1 launch
+    if (!st_do_ref || st_tf_exit) { // :1294-1295; temporal filter: HME was good enough (:3179-3183)
         if (lane == 0) { fj.active = 0; if (job.windows) job.windows[u] = SvtMeWindow{0, 0, 0, 0}; }
         return;
     }
@@ -184,7 +191,7 @@ __global__ void __launch_bounds__(32 * FP_WARPS) k_fp(const PicJob *__restrict__
     unsigned long long ops = 0;
 
     // window sizing :1296-1366 (all lanes compute the same scalars; SADs are warp-cooperative)
-    int16_t xc = st.hme_sc_x[l][r], yc = st.hme_sc_y[l][r];
+    int16_t xc = st_xc, yc = st_yc;
     int16_t sa_w = (int16_t)c.me_sa.sa_min.width, sa_h = (int16_t)c.me_sa.sa_min.height;
     const uint16_t dist = c.me_type == SVTME_ME_MCTF ? ref_distance(pp, l, r) : scaled_picture_distance(ref_distance(pp, l, r)); // :1302-1304
     sa_w = (int16_t)imin((sa_w * dist), c.me_sa.sa_max.width);
@@ -193,18 +200,18 @@ __global__ void __launch_bounds__(32 * FP_WARPS) k_fp(const PicJob *__restrict__
         if (iabs(xc) > c.mv_sa_adj_mv_size_th) sa_w = (int16_t)(sa_w * c.mv_sa_adj_sa_multiplier);
         if (iabs(yc) > c.mv_sa_adj_mv_size_th) sa_h = (int16_t)(sa_h * c.mv_sa_adj_sa_multiplier);
     }
-    const uint32_t div = st.reduce_me_sr_divisor[l][r];
+    const uint32_t div = st_div;
     sa_w = (int16_t)((max(1u, ((uint32_t)sa_w / div)) + 7) & ~0x07u);
     sa_h = (int16_t)max(3u, ((uint32_t)sa_h / div));
     const int16_t sa_h0 = sa_h, sa_w0 = sa_w;
     uint64_t best_hme_sad = ~0ull;
     if (c.me_early_exit_th) {
-        if (st.zz_sad[l][r] < (c.me_early_exit_th / 6)) sa_w = sa_h = 1;
+        if (st_zz < (c.me_early_exit_th / 6)) sa_w = sa_h = 1;
     }
     // plane coordinates of the reference sample under the block's top-left sample at MV (0,0)
     const int bx = ref.org_x + g.org_x, by = ref.org_y + g.org_y;
     FpLane<SUB> L;
-    bool lane_ready = false;
+    bool lane_ready = false, probe_loaded = false; // probe_loaded: stages 0 / 1 hold the probe tiles of centre (0,0) / the HME centre
     if (!c.me_early_exit_th) {
         uint8_t hme_is_accurate = 1;
         if ((xc != 0 || yc != 0) && pp.is_ref) {
@@ -221,15 +228,19 @@ __global__ void __launch_bounds__(32 * FP_WARPS) k_fp(const PicJob *__restrict__
                 // lane's source rows, which the scan needs anyway: two tile loads in flight together, ~60 instructions per
                 // position, no per-lane global loads (the unaligned-LDG form below was a quarter of this kernel's
                 // instructions and its largest stall, profiles/r02_ncu_notes.md)
-                pipe_issue(P, 0, map, bx & ~15, by);
-                pipe_issue(P, 1, map, (bx + xh) & ~15, by + yh);
+                // The two tiles are fetched where the PROBE tile of either outcome lies (8 columns and 4 rows before the
+                // position): whichever centre wins, its probe tile is already in shared memory and the probe below does
+                // not wait for a third load (the set-up of a warp is a chain of dependent latencies: job record, b64 state,
+                // these tiles, the probe tile; ncu: long-scoreboard and barrier waits are the kernel's largest stalls).
+                pipe_issue(P, 0, map, (bx - 8) & ~15, by - 4);
+                pipe_issue(P, 1, map, (bx + xh - 8) & ~15, by + yh - 4);
                 fp_lane_init<SUB>(L, src_full, sf.stride, 64, 64);
                 lane_ready = true;
                 pipe_wait(P, 0);
-                zero_mv_sad = __reduce_add_sync(0xffffffffu, tile_sad1<4, FpLane<SUB>::NR>(L.T, P.buf[0], (uint32_t)(bx & 15))) << 1;
+                zero_mv_sad = __reduce_add_sync(0xffffffffu, tile_sad1<4, FpLane<SUB>::NR>(L.T, P.buf[0] + 4u * TM_FP_BOX_W, (uint32_t)((bx - 8) & 15) + 8u)) << 1;
                 pipe_wait(P, 1);
-                hme_mv_sad = __reduce_add_sync(0xffffffffu, tile_sad1<4, FpLane<SUB>::NR>(L.T, P.buf[1], (uint32_t)((bx + xh) & 15))) << 1;
-                __syncwarp(); // both stages are free again
+                hme_mv_sad = __reduce_add_sync(0xffffffffu, tile_sad1<4, FpLane<SUB>::NR>(L.T, P.buf[1] + 4u * TM_FP_BOX_W, (uint32_t)((bx + xh - 8) & 15) + 8u)) << 1;
+                probe_loaded = true;
             } else {
                 const uint8_t *p0 = ref.buf + ((int16_t)ref.org_x + ox + ((int16_t)ref.org_y + oy) * ref.stride);
                 zero_mv_sad = warp_nxm_sad2(src_full, sf.stride << 1, p0, ref.stride << 1, g.b64_h >> 1, g.b64_w) << 1;
@@ -244,9 +255,9 @@ __global__ void __launch_bounds__(32 * FP_WARPS) k_fp(const PicJob *__restrict__
             ops += 2ull * (unsigned long long)(g.b64_h >> 1) * g.b64_w;
         }
         if (c.enable_me_sr_adjustment == 2) {
-            if ((hme_is_accurate && (best_hme_sad < (24 * 24))) || (pp.is_ref && st.sr_hme_sad[l][r] < (24 * 24)))
+            if ((hme_is_accurate && (best_hme_sad < (24 * 24))) || (pp.is_ref && st_sr_hme_sad < (24 * 24)))
                 sa_h = (int16_t)(sa_h / 2);
-            const uint32_t best00 = (uint32_t)(job.fp_keys[(size_t)b * 8 * 85] >> 32) << (SUB ? 1 : 0); // p_sb_best_sad[0][0][0]
+            const uint32_t best00 = (uint32_t)(key00 >> 32) << (SUB ? 1 : 0); // p_sb_best_sad[0][0][0]; only references other than (0,0) use it: phase 2
             if ((l || r) && best00 < 5000 && sa_h == sa_h0 && sa_w == sa_w0) {
                 sa_h = (int16_t)(sa_h >> 1);
                 sa_w = (int16_t)(sa_w >> 1);
@@ -255,12 +266,13 @@ __global__ void __launch_bounds__(32 * FP_WARPS) k_fp(const PicJob *__restrict__
     }
     const bool probe = c.me_8x8_var_enabled && (sa_w * sa_h > 24);
     const int  ptx = bx + xc - 8, pty = by + yc - 4; // the probe tile: 16 x 8 positions around the search centre
-    if (probe) pipe_issue(P, 0, map, ptx & ~15, pty);
+    const int  pst = probe_loaded && (xc != 0 || yc != 0) ? 1 : 0; // the stage that holds it
+    if (probe && !probe_loaded) pipe_issue(P, 0, map, ptx & ~15, pty);
     if (!lane_ready) fp_lane_init<SUB>(L, src_full, sf.stride, 64, 64); // the full-pel stage always works on 64x64 (padded source)
     if (probe) { // :1393-1441: one position at the search centre, then the variance of its 64 8x8 SADs
-        pipe_wait(P, 0);
+        if (!probe_loaded) pipe_wait(P, 0);
         uint32_t raw[3];
-        fp_eval_pass<SUB>(L, P.buf[0] + 4u * TM_FP_BOX_W, (uint32_t)(ptx & 15) + 8u, 0u, 1, raw);
+        fp_eval_pass<SUB>(L, P.buf[pst] + 4u * TM_FP_BOX_W, (uint32_t)(ptx & 15) + 8u, 0u, 1, raw);
         const uint32_t dbl  = SUB ? 1 : 0;
         const uint32_t mean = (raw[2] << dbl) / 64;
         const int32_t  dl = (int32_t)(raw[0] << dbl) - (int32_t)mean, dr = (int32_t)(raw[1] << dbl) - (int32_t)mean;
@@ -296,7 +308,7 @@ __global__ void __launch_bounds__(32 * FP_WARPS) k_fp(const PicJob *__restrict__
     // one loop, one call site of the scan (code size): the probe tile when it covers the window, else the window's tiles
     if (inline_scan) {
         __syncwarp();
-        int stage = in_probe_tile ? 0 : 1;
+        int stage = in_probe_tile ? pst : pst ^ 1;
         if (!in_probe_tile) pipe_issue(P, stage, map, wx & ~15, wy);
         const int n_iter = in_probe_tile ? 1 : n_tiles;
         for (int t = 0; t < n_iter; t++) {
