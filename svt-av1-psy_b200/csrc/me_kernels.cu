@@ -353,7 +353,7 @@ int svtme_launch_dg_detector(const PicJob *h_job, const PicJob *d_job, int sa0, 
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&k, k_search16<true>, 32 * SEARCH_WARPS, s16_smem);
         g_s16_ctas_per_sm = k > 0 ? k : 1;
     }
-    k_search16<true><<<n_sm * g_s16_ctas_per_sm, 32 * SEARCH_WARPS, s16_smem, st>>>(d_job, 0);
+    k_search16<true><<<n_sm * g_s16_ctas_per_sm, 32 * SEARCH_WARPS, s16_smem, st>>>(d_job, 0, h_job->pp.ctrls.hme_search_method == SVTME_SUB_SAD_SEARCH ? 2 : 1);
     k_dg_reduce<<<(n_b64 + 127) / 128, 128, 0, st>>>(d_job, (DgOut *)d_out, d_b64_sad, d_b64_mv);
     return 3;
 }
@@ -445,8 +445,8 @@ int svtme_launch_picture_me(const PicJob *h_jobs, int n, const PicJob *d_jobs, c
         if (g_s16_ctas_per_sm > persistent_slack()) g_s16_ctas_per_sm -= persistent_slack();
     }
     auto search16 = [&](int skip, int tag) {
-        if (tag == SVTME_TL_S16_PREHME) k_search16<false><<<n_sm * g_s16_ctas_per_sm, 32 * SEARCH_WARPS, s16_smem, st>>>(d_jobs, skip);
-        else k_search16<true><<<n_sm * g_s16_ctas_per_sm, 32 * SEARCH_WARPS, s16_smem, st>>>(d_jobs, skip);
+        if (tag == SVTME_TL_S16_PREHME) k_search16<false><<<n_sm * g_s16_ctas_per_sm, 32 * SEARCH_WARPS, s16_smem, st>>>(d_jobs, skip, sub ? 2 : 1);
+        else k_search16<true><<<n_sm * g_s16_ctas_per_sm, 32 * SEARCH_WARPS, s16_smem, st>>>(d_jobs, skip, sub ? 2 : 1);
         launches++;
         mark(tag);
     };

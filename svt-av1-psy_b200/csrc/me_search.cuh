@@ -513,7 +513,7 @@ __device__ __forceinline__ S16Tile s16_tile_of(const S16Cursor &c) {
 // VB2: with the two-row blocked evaluator (the level-0 launch: windows of 16 .. 96 rows; the pre-HME launch leaves it out,
 // its code only costs instruction-cache space there: 36.9 -> 38.5 us per picture with it compiled in and never chosen)
 template <bool VB2>
-__global__ void __launch_bounds__(32 * SEARCH_WARPS, 5) k_search16(const PicJob *__restrict__ jobs, int skip_cfg) {
+__global__ void __launch_bounds__(32 * SEARCH_WARPS, 5) k_search16(const PicJob *__restrict__ jobs, int skip_cfg, int row_step) {
     extern __shared__ __align__(128) uint8_t s_dyn[];
     __shared__ __align__(16) uint32_t s_src[SEARCH_WARPS][2][16 * 4];
     __shared__ __align__(8) uint64_t s_bar[SEARCH_WARPS][2];
@@ -522,7 +522,8 @@ __global__ void __launch_bounds__(32 * SEARCH_WARPS, 5) k_search16(const PicJob 
     const uint32_t n_units = min(job0.s16_counters[0], job0.s16_units_cap);
     if (blockIdx.x == 0 && threadIdx.x == 0 && job0.s16_counters[0] > job0.s16_units_cap) job0.fp_counters[8] = 1; // queue overflow: reported by the host
     if (n_units == 0) return;
-    const int row_step = job0.pp.ctrls.hme_search_method == SVTME_SUB_SAD_SEARCH ? 2 : 1;
+    // row_step (2: SAD over every other block row, hme_search_method == SUB_SAD_SEARCH) is a launch argument: read from the job
+    // record it was re-read from global memory for every tile
     uint8_t *sbase = s_dyn + ((128u - (smem_u32(s_dyn) & 127u)) & 127u);
     TilePipe P;
     pipe_init(P, sbase + (size_t)warp * 2 * TM_S16_BUF, TM_S16_BUF, s_bar[warp], 0);
