@@ -787,6 +787,15 @@ static uint32_t fields_of_results(const SvtMePicResults *r) {
 }
 
 // fields[i]: what picture i must produce (SVTME_F_*)
+// reciprocals for div_by() (me_device.cuh): b64 index -> row, compact unit index -> b64
+static void picjob_set_inverses(PicJob &job) {
+    auto inv = [](int d) -> uint32_t { return d > 1 ? (uint32_t)(((1ull << 32) + (uint64_t)d - 1) / (uint64_t)d) : 0u; };
+    const SvtMePicParams &pp = job.pp;
+    const int na = pp.num_of_ref_pic_to_search[0] + (pp.num_of_list_to_search > 1 ? pp.num_of_ref_pic_to_search[1] : 0);
+    job.inv_cols = inv(job.b64_cols);
+    job.inv_refs = (uint64_t)job.n_b64 * 8 * (uint64_t)(na > 0 ? na : 1) < (1ull << 32) ? inv(na) : 0u;
+}
+
 static uint32_t launch_me_batch(SvtMeSession *s, uint32_t n, const int32_t *pic_ids, const SvtMePicParams *params, const uint32_t *fields) {
     if (!s || !pic_ids || !params || n == 0 || n > 4096) return SVTME_ERR_BAD_PARAMETER;
     CU_TRY(cudaSetDevice(s->device));
@@ -859,6 +868,7 @@ static uint32_t launch_me_batch(SvtMeSession *s, uint32_t n, const int32_t *pic_
             }
         job.pic_w = s->w; job.pic_h = s->h; job.b64_cols = s->b64_cols; job.b64_rows = s->b64_rows; job.n_b64 = s->n_b64;
         job.n_pus = pp->enable_me_8x8 ? 85 : 21;
+        picjob_set_inverses(job);
         job.mv_stride = strides[i].mv_stride; job.mv_l1_off = strides[i].mv_l1_offset; job.cand_stride = strides[i].cand_stride;
         uint8_t *R = s->res_sets[set][i];
         uint8_t *D = s->dl_region[set] + bo.base[i];

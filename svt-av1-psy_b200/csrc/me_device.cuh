@@ -114,7 +114,12 @@ struct alignas(16) PicJob { // a multiple of 16 bytes: the job array is fetched 
     uint32_t           *s16_counters; // [0] number of units, [1] queue head
     uint32_t            s16_units_cap;
     int                 s16_split;    // 1: k_hme_ctl makes every 1/16-plane job a queue unit of its own (small batches)
+    uint32_t            inv_cols, inv_refs; // ceil(2^32 / b64_cols), ceil(2^32 / searched references): div_by(); 0 = divide
 };
+
+// n / d without the ~20-instruction integer division every warp of the per-b64 kernels started with: inv = ceil(2^32 / d) from
+// the host (picjob_set_inverses), exact while n * d < 2^32; inv == 0 (d == 1, or a job record filled elsewhere): divide
+__device__ __forceinline__ int div_by(int n, int d, uint32_t inv) { return inv ? (int)__umulhi((uint32_t)n, inv) : n / d; }
 
 static_assert(sizeof(PicJob) % 16 == 0, "PicJob is copied in 16-byte words");
 

@@ -301,7 +301,8 @@ __global__ void __launch_bounds__(POST_THREADS) k_post(const PicJob *__restrict_
         for (int o = 16; o > 0; o >>= 1) sumsq += __shfl_xor_sync(0xffffffffu, sumsq, o);
     }
     if (tid == 0 && want_stats) {
-        const int org_x = (b % job.b64_cols) * 64, org_y = (b / job.b64_cols) * 64;
+        const int b_row = div_by(b, job.b64_cols, job.inv_cols);
+        const int org_x = (b - b_row * job.b64_cols) * 64, org_y = b_row * 64;
         const uint32_t gw = (uint32_t)imin(64, job.pic_w - org_x), gh = (uint32_t)imin(64, job.pic_h - org_y);
         const uint32_t d64 = sh.me_distortion[0];
         const uint32_t pix = gw * gh, size = 64 * 64;

@@ -25,8 +25,9 @@ struct B64Geo {
 };
 __device__ __forceinline__ B64Geo b64_geo(const PicJob &job, int b) {
     B64Geo g;
-    g.org_x = (b % job.b64_cols) * 64;
-    g.org_y = (b / job.b64_cols) * 64;
+    const int by = div_by(b, job.b64_cols, job.inv_cols);
+    g.org_x = (b - by * job.b64_cols) * 64;
+    g.org_y = by * 64;
     g.b64_w = imin(64, job.pic_w - g.org_x); // motion_estimation.c:3163-3170, picture already 8-aligned
     g.b64_h = imin(64, job.pic_h - g.org_y);
     return g;
@@ -39,7 +40,7 @@ __device__ __forceinline__ bool compact_unit(const PicJob &job, int uc, int &b, 
     const int n0 = pp.num_of_ref_pic_to_search[0], n1 = pp.num_of_list_to_search > 1 ? pp.num_of_ref_pic_to_search[1] : 0;
     const int na = n0 + n1;
     if (na <= 0 || uc >= job.n_b64 * na) return false;
-    b = uc / na;
+    b = div_by(uc, na, job.inv_refs);
     const int k = uc - b * na;
     l = k >= n0 ? 1 : 0;
     r = l ? k - n0 : k;
