@@ -35,7 +35,7 @@ def main():
     launches, kernels = [], {}
     for r in rows[2:]:
         name = r[ix["Kernel Name"]]
-        if name.startswith("k_search16"):
+        if "k_search16" in name:
             label = "k_search16 (pre-HME)" if n16 == 0 else "k_search16 (HME level 0)"
             n16 += 1
         elif "k_search_blk" in name:
