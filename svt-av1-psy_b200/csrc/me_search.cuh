@@ -3,16 +3,15 @@
 //
 //   k_zz          zero-MV SAD per (b64, ref)                      init_zz_sad        motion_estimation.c:2452
 //   k_search16    pre-HME regions and HME level-0 quadrants       prehme_core :1638, hme_level_0 :820
-//                 (blocks <= 16 wide on the 1/16 plane): unit = (job, tile of the window); one TMA load
-//                 brings the tile (+ the rows/cols the block reaches) into the warp's shared memory,
-//                 then each lane evaluates 8 consecutive positions per task (strip16_sad8: 15 SHF +
-//                 32 VABSDIFF4 per block row, + 6 SHF when the window is not 8-byte aligned)
+//                 (blocks <= 16 wide on the 1/16 plane): a warp walks the tiles of the windows of one (b64, list,
+//                 ref); one TMA load brings a tile (+ the rows/cols the block reaches) into the warp's shared
+//                 memory; one of four evaluators, chosen per tile by a cost model, searches it (s16_eval_choice)
 //   k_search_blk  HME level 1 / 2 (32- / 64-wide blocks, windows of 8x3 .. 16x16 positions): lanes
 //                 spread over the block, TMA tiles (see below)
 //
 // All follow svt_sad_loop_kernel (compute_sad_c.c:58-101): raster order, strict '<', best starts at
-// 0xffffff. Result = 64-bit key (sad << 32 | y*sa_w + x); atomicMin over the tiles of a job keeps
-// the first minimum in raster order.
+// 0xffffff. Result = 64-bit key (sad << 32 | y*sa_w + x); the minimum over the tiles of a job keeps the
+// first minimum in raster order (one warp searches all tiles of a job: a running key in registers, a plain store).
 #pragma once
 #include <type_traits>
 #include "me_device.cuh"
@@ -94,7 +93,7 @@ __global__ void __launch_bounds__(32 * SEARCH_WARPS) k_zz(const PicJob *__restri
 }
 
 // ---- 1/16-plane searches (blocks <= 16 wide): tiles through TMA ---------------------------------
-// One tile = TM_S16T (16 positions x 96 rows) or TM_S16W (128 x 18) of a window, fetched from the 16-byte boundary at
+// One tile = TM_S16T (16 positions x 96 rows) or TM_S16W (128 x 18 / 16 / 12: s16_tile_geometry) of a window, fetched from the 16-byte boundary at
 // or before its first position. src: n_rows x 16 bytes in shared memory, bytes >= bw zeroed.
 //
 // A window may be the union of the four quadrant windows of an HME level-0 search (k_hme_ctl merges them when they
