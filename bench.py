@@ -537,7 +537,7 @@ def run_ours(a):
             "metric": "open-loop ME frames/s", "value": round(value, 2), "unit": "frames/s", "n_gpus": world,
             "steps": a.steps, "warmup": a.warmup, "ms_per_step": round(m["ms_per_step"], 4), "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-            "config": {"workload": wl.name, "pictures_per_step": wl.mgop, "batch": "one launch sequence per mini-GOP (svtme_picture_me_batch), consecutive mini-GOPs on %d compute stream(s)" % a.concurrency, "sharding": "mini-GOP m -> rank m % N",
+            "config": {"workload": wl.name, "pictures_per_step": wl.mgop, "batch": "one launch sequence per mini-GOP (svtme_picture_me_batch), consecutive mini-GOPs on %d compute stream(s); end to end: three pinned result slabs in rotation" % a.concurrency, "sharding": "mini-GOP m -> rank m % N",
                        "results": "the arrays open-loop ME's consumers read: MeSbResults (total_me_candidate_index, me_mv_array, me_candidate_array) + the eight per-b64 PCS statistics; "
                                   "end to end their rows cross PCIe at the picture's own strides (SVTME_F_SB_COMPACT, expanded per b64 by svtme_sb_expand_b64); "
                                   "e2e_all_fields is the same pass at the reference's strides plus the MeContext members (p_sb_best_sad / p_sb_best_mv, search_results), which only the temporal filter reads after the call",
