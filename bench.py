@@ -262,7 +262,7 @@ class Runner:
     def setup_slabs(self, sp):
         """three pinned result slabs used in turn: the host queues batch k + 2 (which reuses the device region of batch k, the
         library waits for that download on the device, before the batch's first writing kernel) without waiting for batch k's
-        download itself; it waits only for batch k - 1's, whose slab it is about to hand out again. With two slabs the host had
+        download itself; it waits only for the batch that last used the slab it is about to hand out again (batch k - 1). With two slabs the host had
         to wait for the download of batch k before it could queue batch k + 2, and the second compute stream ran dry."""
         import torch
         lay = self.sess.packed_layout(sp.prm[0], self.fields)
@@ -541,7 +541,7 @@ def run_ours(a):
                        "results": "the arrays open-loop ME's consumers read: MeSbResults (total_me_candidate_index, me_mv_array, me_candidate_array) + the eight per-b64 PCS statistics; "
                                   "end to end their rows cross PCIe at the picture's own strides (SVTME_F_SB_COMPACT, expanded per b64 by svtme_sb_expand_b64); "
                                   "e2e_all_fields is the same pass at the reference's strides plus the MeContext members (p_sb_best_sad / p_sb_best_mv, search_results), which only the temporal filter reads after the call",
-                       "e2e_pipeline": "host uploads, kernels and result downloads on three streams; two batches in flight; per step the new frames cross as merged H2D copies and the whole batch's results land in pinned host memory by ONE D2H copy (svtme_picture_me_batch_packed), inside the timed region",
+                       "e2e_pipeline": "host uploads, kernels and result downloads on three streams; three host result slabs in rotation (up to three batches queued); per step the new frames cross as merged H2D copies and the whole batch's results land in pinned host memory by ONE D2H copy (svtme_picture_me_batch_packed), inside the timed region",
                        "host_numa": numa,
                        "l2": "inputs larger than L2: %d distinct %dx%d frames (%.0f MB) stream through the picture store, no explicit flush"
                              % (wl.n_frames, wl.w, wl.h, wl.n_frames * wl.w * wl.h / 1e6)},
