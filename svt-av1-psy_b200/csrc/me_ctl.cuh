@@ -1,7 +1,7 @@
 // me_ctl.cuh — k_hme_ctl: the scalar control of the HME stage between two search kernels.
 //
 // One warp per b64; lane = job slot = (list*4 + ref)*4 + quadrant. The per-b64 state (SbState, the
-// MeContext fields of me_context.h:435-452,329-355) is staged in shared memory. One launch does
+// MeContext fields of me_context.h:435-452,329-355) is worked on in place, in global memory. One launch does
 //   1. POST     : turn the keys of the searches that just ran into SADs / search centres
 //                 (tail of prehme_core :1727-1734, hme_level_0/1/2 :911-917 / :1013-1019 / :1106-1110,
 //                 worst-quadrant replacement :2075-2102)

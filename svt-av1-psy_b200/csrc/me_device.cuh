@@ -60,7 +60,7 @@ struct SbState {
 // and executed by k_search16 (1/16 plane) / k_search_blk (1/4 and full planes). 32 jobs per b64: slot = (list*4+ref)*4 + quadrant
 // (pre-HME uses quadrant 0/1 for its two regions).
 struct HmeJobG {
-    unsigned long long key;  // (sad << 32) | (y*sa_w + x), atomicMin over the job's tiles
+    unsigned long long key;  // (sad << 32) | (y*sa_w + x): minimum over the job's tiles (k_search16: one warp, plain store; detector bands: k_dg_reduce)
     int16_t            sa_w, sa_h, origin_x, origin_y;
     uint16_t           tile_w, tile_h; // positions per tile (tile_w multiple of 8)
     uint8_t            n_tx, n_ty, active, wide; // wide: 1 = 128x18-position tiles, 0 = 16x96 (1/16-plane searches)
