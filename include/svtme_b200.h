@@ -478,6 +478,14 @@ uint32_t svtme_session_kernel_time(SvtMeSession *s, int reset, double *fullpel_m
 const char *svtme_kernel_name(int tag);
 uint32_t    svtme_session_kernel_times(SvtMeSession *s, int reset, double *ms, int n_ms);
 
+/* How k_search16 cuts a 1/16-plane search window of sa_w x sa_h positions into tiles and which evaluator takes each kind
+   of tile: the plan k_hme_ctl makes on the device, computed on the host (no GPU needed; tests, diagnostics). block16x8: the
+   block is 16 wide and 8 rows two apart (the production shape of the sub-sampled SAD search); level0: the launch that also
+   has the two-row blocked evaluator. out[0..3] = tile width, tile height, tiles per row, tile rows; out[4], out[5] =
+   evaluator of a full tile and of a tile of the last tile row (0 general, 1 two-row blocked, 2 three-row blocked, 3 one
+   position per lane); out[6] = the cost model's warp instructions for the whole window. No reference counterpart. */
+void svtme_s16_tile_plan(int sa_w, int sa_h, int block16x8, int level0, int out[7]);
+
 /* Algorithmic work done by the kernels since the last reset: "SAD operations" = search positions x
    block pixels compared (|a-b| and accumulate), the unit of SURVEY.md 8(d) / BASELINE.md. Counted on
    the device by the thread that sets up each search. */

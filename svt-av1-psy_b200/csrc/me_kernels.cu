@@ -745,3 +745,25 @@ int svtme_launch_fill32(uint32_t *d_p, uint32_t n, uint32_t v, cudaStream_t st) 
     if (n) k_fill32<<<(n + 255) / 256, 256, 0, st>>>(d_p, n, v);
     return n ? 1 : 0;
 }
+
+// ------------------------------------------------------------------------------------------
+// the tile plan of a 1/16-plane window, on the host (include/svtme_b200.h)
+// ------------------------------------------------------------------------------------------
+extern "C" void svtme_s16_tile_plan(int sa_w, int sa_h, int block16x8, int level0, int out[7]) {
+    int tw = 0, th = 0, ntx = 0, nty = 0, wide = 0;
+    s16_tile_geometry(sa_w, sa_h, &tw, &th, &ntx, &nty, &wide, block16x8 != 0, level0 != 0);
+    out[0] = tw; out[1] = th; out[2] = ntx; out[3] = nty;
+    const int bw = 16, rows = block16x8 ? 8 : 16, step = block16x8 ? 2 : 1;
+    int total = 0;
+    out[4] = out[5] = -1;
+    for (int ty = 0; ty < nty; ty++)
+        for (int tx = 0; tx < ntx; tx++) {
+            const int w = sa_w - tx * tw < tw ? sa_w - tx * tw : tw, h = sa_h - ty * th < th ? sa_h - ty * th : th;
+            int cost = 0;
+            const int which = s16_eval_choice(w, h, bw, rows, step, false, wide != 0, level0 != 0, &cost);
+            total += cost;
+            if (tx == 0 && ty == 0) out[4] = which;
+            if (tx == 0 && ty == nty - 1) out[5] = which;
+        }
+    out[6] = total;
+}
