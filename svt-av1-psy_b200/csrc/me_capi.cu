@@ -432,19 +432,30 @@ extern "C" uint64_t svtme_session_batch_seq(SvtMeSession *s) { return s ? s->bat
 
 extern "C" uint32_t svtme_session_wait_batch(SvtMeSession *s, uint64_t seq) {
     if (!s) return SVTME_ERR_BAD_PARAMETER;
-    cudaEvent_t ev;
-    bool downloaded;
+    cudaEvent_t ev[4];
+    int n_ev = 0;
+    bool downloaded = false;
     const int set = (int)(seq & 1);
     { // the events live as long as the session; only the bookkeeping needs the lock (other threads may be launching)
         std::lock_guard<std::mutex> g(s->mu);
-        if (seq == 0 || seq > s->batch_seq || seq + 8 <= s->batch_seq) return SVTME_OK; // eight batches on: its region was handed out again after its downloads
-        // the batch's own last download (not a later batch's of the same set: a caller that rotates three or more host
-        // buffers waits for batch k - 2 while batch k's download may not even have started)
-        downloaded = s->dl_seq[seq % 8] == seq;
-        ev = downloaded ? s->ev_dl_seq[seq % 8] : s->ev_me[seq % 8];
+        if (seq == 0 || seq > s->batch_seq) return SVTME_OK;
+        if (seq + 8 <= s->batch_seq) {
+            // eight or more batches were queued since (a caller with nine or more host buffers that never waited): the
+            // batch's own event slots were handed on. Everything queued later on the same streams completes after it:
+            // the newest batch of either compute stream, and the newest download of either result set.
+            ev[n_ev++] = s->ev_me[s->batch_seq % 8];
+            ev[n_ev++] = s->ev_me[(s->batch_seq - 1) % 8];
+            for (int k = 0; k < 2; k++)
+                if (s->dl_recorded[k]) { ev[n_ev++] = s->ev_dl[k]; downloaded = true; }
+        } else {
+            // the batch's own last download (not a later batch's of the same set: a caller that rotates three or more host
+            // buffers waits for batch k - 2 while batch k's download may not even have started)
+            downloaded = s->dl_seq[seq % 8] == seq;
+            ev[n_ev++] = downloaded ? s->ev_dl_seq[seq % 8] : s->ev_me[seq % 8];
+        }
     }
     cudaSetDevice(s->device);
-    CU_TRY(cudaEventSynchronize(ev));
+    for (int i = 0; i < n_ev; i++) CU_TRY(cudaEventSynchronize(ev[i]));
     if (!downloaded) return SVTME_OK;
     std::lock_guard<std::mutex> g(s->mu);
     return check_downloaded_flag(s, set);

@@ -183,6 +183,45 @@ def test_three_slabs_in_rotation(orc, concurrency):
     s.close()
 
 
+@pytest.mark.gpu
+def test_wait_for_a_batch_older_than_the_event_ring(orc):
+    """ten batches queued into ten slabs without a single wait: waiting for the first one (its event slots were handed
+    on to batch 9) still returns only when its results are in host memory"""
+    import torch
+    w, h, planes, refs, pics = _batch(6)
+    s = me.Session(w, h, max_pictures=16)
+    s.set_concurrency(2)
+    for i, pl in enumerate(planes[1:]):
+        s.upload(1 + i, pl)
+    fields = abi.F_SB_RESULTS | abi.F_SB_COMPACT | abi.F_STATS
+    prms = []
+    for k, (src, params) in enumerate(pics):
+        s.upload(8 + k, src)
+        p = copy.copy(params)
+        pid = 1
+        for l in range(len(refs)):
+            for r in range(len(refs[l])):
+                p.ref_pic_id[l][r] = pid
+                pid += 1
+        prms.append(p)
+    lay = s.packed_layout(prms[0], fields)
+    strides = me.Session.sb_strides(prms[0], fields)
+    slabs = [torch.zeros(lay.bytes * 2, dtype=torch.uint8).pin_memory() for _ in range(10)]
+    s.reserve(prms[0], 2)
+    seqs, want = [], {}
+    for b in range(10):
+        pair = [b % 6, (b + 1) % 6]
+        ids_a, prm_a = (C.c_int32 * 2)(*[8 + i for i in pair]), (abi.MePicParams * 2)(*[prms[i] for i in pair])
+        s.me_batch_packed(ids_a, prm_a, 2, fields, slabs[b].data_ptr(), slabs[b].numel(), sync=False)
+        seqs.append(s.batch_seq())
+    s.wait_batch(seqs[0])
+    _check_slab(slabs[0], lay, strides, w, h, prms, refs, pics, [0, 1], want)
+    s.wait_batch(seqs[9])
+    _check_slab(slabs[9], lay, strides, w, h, prms, refs, pics, [9 % 6, 10 % 6], want)
+    s.sync()
+    s.close()
+
+
 def _check_slab(slab, lay, strides, w, h, prms, refs, pics, pair, want):
     block = slab.numpy()
     for j, i in enumerate(pair):
